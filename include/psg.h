@@ -1,0 +1,166 @@
+/* psg.h -- C ABI of the B200-native PSgradientSDF photometric-optimizer hot path.
+ *
+ * Drop-in boundary: the reference reaches this path through two C++ classes,
+ *   Sdf / VolumetricGradSdf   (cpp/include/sdf_tracker/Sdf.h:24-141, VolumetricGradSdf.h:65-122)
+ *   Optimizer / PsOptimizer / LedOptimizer (cpp/include/ps_optimizer/Optimizer.h:24-182)
+ * called from cpp/voxel_ps/src/main_ps.cpp:183-330.  Every entry point below names the reference
+ * interface it replaces.  Plain pointers and sizes only; all pointers are HOST pointers unless a
+ * parameter says otherwise; the library owns all device memory.  The host keeps ownership of every
+ * buffer it passes (images are copied at psg_opt_set_keyframes).
+ *
+ * Conventions: matrices are row-major; poses are camera-to-world 4x4 (main_ps.cpp:219);
+ * colour images are float32 BGR (ImageLoader.h:167-188); depth is float32 metres; voxels are ordered
+ * lin = i + W*j + W*H*k (VoxelGrid.h:79-81); a voxel record is 8 floats
+ * {dist, grad.x, grad.y, grad.z, weight, r, g, b} (Sdfvoxel.h:6-13).
+ *
+ * Errors: every function returns 0 on success and a non-zero psg_status otherwise;
+ * psg_last_error() returns a description of the last failure on the calling thread.  There is no CPU
+ * fallback: without a usable sm_100 device every call that needs one fails with PSG_ERR_CUDA.
+ * Not thread-safe per handle (the reference is single-threaded).
+ */
+#ifndef PSG_H
+#define PSG_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct psg_volume psg_volume;
+typedef struct psg_optimizer psg_optimizer;
+
+typedef enum {
+    PSG_OK = 0,
+    PSG_ERR_INVALID = 1,     /* bad argument */
+    PSG_ERR_CUDA = 2,        /* CUDA runtime / device error */
+    PSG_ERR_STATE = 3,       /* call order violated (e.g. step before init) */
+    PSG_ERR_UNSUPPORTED = 4  /* feature of the reference not provided on this path */
+} psg_status;
+
+/* ModelType / LossFunction (cpp/include/ps_optimizer/OptimizerSettings.h:7-21) */
+typedef enum { PSG_MODEL_SH1 = 0, PSG_MODEL_SH2 = 1, PSG_MODEL_LED = 2 } psg_model;
+typedef enum { PSG_LOSS_L2 = 0, PSG_LOSS_CAUCHY = 1, PSG_LOSS_HUBER = 2, PSG_LOSS_TUKEY = 3, PSG_LOSS_TRUNC_L2 = 4 } psg_loss;
+typedef enum { PSG_BLOCK_ALBEDO = 0, PSG_BLOCK_LIGHT = 1, PSG_BLOCK_DIST = 2, PSG_BLOCK_POSE = 3 } psg_block;
+
+/* struct OptimizerSettings (OptimizerSettings.h:23-51), the fields the path reads. */
+typedef struct {
+    int model;           /* psg_model */
+    int loss;            /* psg_loss */
+    float lambda;        /* robust-loss scale */
+    float reg_weight_rho;
+    float reg_weight_n;
+    float reg_weight_l;
+} psg_settings;
+
+/* What one optimize*All call did (PsOptimizer.cpp:85-234): size of the system, whether the CG reported
+ * Eigen::Success, its iteration count and error estimate, and whether the update was applied (the SH path
+ * applies albedo/distance only on Success, the LED path applies pose only on Success). */
+typedef struct {
+    int n;
+    int cg_success;
+    int cg_iterations;
+    float cg_error;
+    int applied;
+    long long n_accepted;   /* albedo channels / distances whose gated update was accepted (OptimizerAux.cpp:149,183) */
+} psg_step_info;
+
+const char* psg_last_error(void);
+/* Number of kernels this library has launched in the calling process so far (for bench.py's gpu_launches). */
+long long psg_kernel_launches(void);
+int psg_device_count(int* count);
+
+/* ------------------------------------------------------------------ volume (Sdf / VolumetricGradSdf) */
+
+/* VolumetricGradSdf(grid_dim, voxel_size, shift, T) + set_zmin/set_zmax (VolumetricGradSdf.h:65-70,
+ * Sdf.h:105-111, main_ps.cpp:183-186).  max_frames bounds the per-voxel visibility record (one bit per
+ * input frame, VolumetricGradSdf.h:42); device selects the CUDA device. */
+int psg_volume_create(psg_volume** out, const int dims[3], float voxel_size, const float shift[3], float T,
+                      float zmin, float zmax, int max_frames, int device);
+int psg_volume_destroy(psg_volume* vol);
+/* grid_dim_, voxel_size_, origin_ (VoxelGrid.h:30-34) -- these change after psg_opt_upsample. */
+int psg_volume_geometry(const psg_volume* vol, int dims[3], float* voxel_size, float origin[3]);
+
+/* Sdf::increase_counter() (optional) followed by VolumetricGradSdf::update(color, depth, K, pose, NEst)
+ * (VolumetricGradSdf.cpp:51-138).  nx, ny, nz, n_sq_inv are what NormalEstimator::compute / n_sq_inv_ptr()
+ * hand to update() (NormalEstimator.h:150-176,183).  R, t = pose.rotationMatrix(), pose.translation(). */
+int psg_volume_integrate(psg_volume* vol, const float* color_bgr, const float* depth, const float* nx,
+                         const float* ny, const float* nz, const float* n_sq_inv, int H, int W,
+                         const float K[9], const float R[9], const float t[3], int increase_counter);
+
+/* tsdf_ as an array of SdfVoxel records, N x 8 floats (replaces the optimizer's `friend` access,
+ * VolumetricGradSdf.h:26-30; consumed by the PLY / marching-cubes / .sdf writers). */
+int psg_volume_download(psg_volume* vol, float* aos8);
+int psg_volume_upload(psg_volume* vol, const float* aos8);
+/* vis_ (VolumetricGradSdf.h:42) as bit words: words[w * N + lin], bit k of word w = vis[64 w + k];
+ * nwords = ceil(max_frames / 64).  The vector's length is (index of highest set bit) + 1. */
+int psg_volume_vis_words(const psg_volume* vol, int* nwords);
+int psg_volume_download_vis(psg_volume* vol, uint64_t* words);
+int psg_volume_upload_vis(psg_volume* vol, const uint64_t* words, int frame_counter);
+
+/* ------------------------------------------------------------------ optimizer (Optimizer / PsOptimizer / LedOptimizer) */
+
+/* PsOptimizer / LedOptimizer(tSDF, voxel_size, K, save_path, settings) (main_ps.cpp:193-202).  The optimizer
+ * keeps a non-owning pointer to vol, like the reference. */
+int psg_opt_create(psg_optimizer** out, psg_volume* vol, float voxel_size, const float K[9],
+                   const psg_settings* settings);
+int psg_opt_destroy(psg_optimizer* opt);
+
+/* setImages + setKeyframes + setPoses (Optimizer.h:137-154, main_ps.cpp:323-326): F keyframes (F <= 64),
+ * frame_idx[k] = input-frame ordinal of keyframe k, poses F x 16, images F x H x W x 3 float BGR. */
+int psg_opt_set_keyframes(psg_optimizer* opt, int F, const int* frame_idx, const float* poses16,
+                          const float* images_bgr, int H, int W);
+
+/* {Ps,Led}Optimizer::init() (PsOptimizer.cpp:25-42, LedOptimizer.cpp:25-36): initial light, select_vis()
+ * (Optimizer.cpp:30-47), getSurfaceVoxel() (OptimizerAux.cpp:237-257), LED computeLightIntensive(). */
+int psg_opt_init(psg_optimizer* opt);
+int psg_opt_num_surface(const psg_optimizer* opt, int* S);
+/* surface_points_ (Optimizer.h:44), ascending lin indices, and the keyframe-indexed visibility of each. */
+int psg_opt_get_surface(psg_optimizer* opt, int* lin, uint64_t* vis_keyframes /* may be NULL */);
+
+int psg_opt_light_len(const psg_optimizer* opt, int* n);  /* SH: F*4 or F*9 ; LED: 3 */
+int psg_opt_get_light(psg_optimizer* opt, float* light);
+int psg_opt_set_light(psg_optimizer* opt, const float* light);
+int psg_opt_get_poses(psg_optimizer* opt, float* poses16);
+int psg_opt_set_poses(psg_optimizer* opt, const float* poses16);
+/* settings_->reg_weight_{rho,n,l}: the reference's outer loop rescales them (PsOptimizer.cpp:277,283,403) */
+int psg_opt_get_reg(const psg_optimizer* opt, float reg3[3]);
+int psg_opt_set_reg(psg_optimizer* opt, const float reg3[3]);
+
+/* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */
+int psg_opt_init_albedo(psg_optimizer* opt);
+
+/* getPSEnergy() (PsOptimizer.cpp:47-78, LedOptimizer.cpp:40-71): sum of robust losses over active
+ * (surface voxel, keyframe) pairs divided by S, accumulated in double; n_active = number of such pairs. */
+int psg_opt_energy(psg_optimizer* opt, double* E, long long* n_active);
+/* getNormalEnergy / getLaplacianEnergy / getAlbedoRegEnergy (Optimizer.cpp:86-136); any pointer may be NULL. */
+int psg_opt_reg_energies(psg_optimizer* opt, double* E_normal, double* E_laplacian, double* E_albedo);
+
+/* computeResidual() (PsOptimizerJa.cpp:567-626): residual and IRLS weight per (surface row, keyframe, channel),
+ * S x F x 3 each, zeros for inactive pairs.  Diagnostic / parity probe; not used by the step functions. */
+int psg_opt_residual(psg_optimizer* opt, float* r3, float* w3);
+/* Per pair: getIntensity's projected pixel (col m, row n) and in-bounds flag (OptimizerAux.cpp:207-231),
+ * sampled RGB and rendered RGB.  S x F (x 3).  Diagnostic / parity probe. */
+int psg_opt_probe_pairs(psg_optimizer* opt, float* m, float* n, unsigned char* ok, float* I3, float* rend3);
+
+/* optimizeAlbedoAll / optimizeLightAll / optimizeDistAll / optimizePosesAll
+ * (PsOptimizer.cpp:85-234, LedOptimizer.cpp:134-275).  flags: PSG_REG_* bits select the regularisers
+ * the reference passes as booleans. */
+#define PSG_REG_ALBEDO 1
+#define PSG_REG_NORMAL 2
+#define PSG_REG_LAPLACIAN 4
+int psg_opt_step(psg_optimizer* opt, int block, float damping, int flags, psg_step_info* info /* may be NULL */);
+/* Normal equations of the last psg_opt_step for the small dense blocks (diagnostic / parity probe):
+ * light: F blocks of nb x nb (+ nb rhs) or LED 3 (+3); pose: F blocks of 6 x 6 (+6).  Row-major, after damping. */
+int psg_opt_last_system(psg_optimizer* opt, double* H_blocks, double* b, double* delta);
+/* Distance / albedo block of the last step: rhs b, solution delta (n floats each). */
+int psg_opt_last_vectors(psg_optimizer* opt, float* b, float* delta);
+
+/* Optimizer::subsampling() (OptimizerAux.cpp:622-684): every voxel splits into 8; the volume handle is
+ * updated in place (dims x2, voxel size /2, origin shifted, VoxelGrid.h:143-149) and the surface is re-extracted. */
+int psg_opt_upsample(psg_optimizer* opt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSG_H */

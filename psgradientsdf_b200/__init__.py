@@ -1,0 +1,320 @@
+"""psgradientsdf_b200 -- B200-native hot path of PSgradientSDF's photometric optimizer.
+
+The product is the sm_100a shared library ``libpsg_b200.so`` (C ABI in ``include/psg.h``, sources in ``csrc/``).
+This module is a thin ctypes binding of that ABI plus Python look-alikes of the reference's two classes
+(``VolumetricGradSdf`` and ``PsOptimizer`` / ``LedOptimizer``, cpp/include/sdf_tracker/VolumetricGradSdf.h and
+cpp/include/ps_optimizer/*.h) used by the tests and bench.py.  There is no CPU fallback: loading fails loudly when
+the library has not been built, and every compute call fails with the library's error text when no CUDA device is
+usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpsg_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "psg.h")
+
+MODEL = {"SH1": 0, "SH2": 1, "LED": 2}
+LOSS = {"l2": 0, "cauchy": 1, "huber": 2, "tukey": 3, "trunc_l2": 4}
+BLOCK = {"albedo": 0, "light": 1, "dist": 2, "pose": 3}
+REG_ALBEDO, REG_NORMAL, REG_LAPLACIAN = 1, 2, 4
+
+
+class PsgError(RuntimeError):
+    pass
+
+
+class Settings(C.Structure):
+    _fields_ = [("model", C.c_int), ("loss", C.c_int), ("lam", C.c_float), ("reg_weight_rho", C.c_float),
+                ("reg_weight_n", C.c_float), ("reg_weight_l", C.c_float)]
+
+
+class StepInfo(C.Structure):
+    _fields_ = [("n", C.c_int), ("cg_success", C.c_int), ("cg_iterations", C.c_int), ("cg_error", C.c_float),
+                ("applied", C.c_int), ("n_accepted", C.c_longlong)]
+
+
+class LoopConfig(C.Structure):
+    _fields_ = [("light", C.c_int), ("albedo", C.c_int), ("distance", C.c_int), ("pose", C.c_int),
+                ("max_it", C.c_int), ("conv_threshold", C.c_float), ("damping", C.c_float), ("upsample", C.c_int),
+                ("write_artifacts", C.c_int)]
+
+
+_lib = None
+f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+
+
+def lib():
+    """Load libpsg_b200.so (built by psgradientsdf_b200.build / __graft_entry__.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PsgError(f"{LIB_PATH} is missing: run `python -m psgradientsdf_b200.build` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.psg_last_error.restype = C.c_char_p
+        L.psg_kernel_launches.restype = C.c_longlong
+        vp = C.c_void_p
+        L.psg_volume_create.argtypes = [C.POINTER(vp), i32p, C.c_float, f32p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
+        L.psg_volume_destroy.argtypes = [vp]
+        L.psg_volume_geometry.argtypes = [vp, i32p, C.POINTER(C.c_float), f32p]
+        L.psg_volume_integrate.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, f32p, f32p, f32p, C.c_int]
+        L.psg_volume_download.argtypes = [vp, f32p]
+        L.psg_volume_upload.argtypes = [vp, f32p]
+        L.psg_volume_vis_words.argtypes = [vp, C.POINTER(C.c_int)]
+        L.psg_volume_download_vis.argtypes = [vp, u64p]
+        L.psg_volume_upload_vis.argtypes = [vp, u64p, C.c_int]
+        L.psg_opt_create.argtypes = [C.POINTER(vp), vp, C.c_float, f32p, C.POINTER(Settings)]
+        L.psg_opt_destroy.argtypes = [vp]
+        L.psg_opt_set_keyframes.argtypes = [vp, C.c_int, i32p, f32p, vp, C.c_int, C.c_int]
+        L.psg_opt_init.argtypes = [vp]
+        L.psg_opt_num_surface.argtypes = [vp, C.POINTER(C.c_int)]
+        L.psg_opt_get_surface.argtypes = [vp, vp, vp]
+        L.psg_opt_light_len.argtypes = [vp, C.POINTER(C.c_int)]
+        L.psg_opt_get_light.argtypes = [vp, f32p]
+        L.psg_opt_set_light.argtypes = [vp, f32p]
+        L.psg_opt_get_poses.argtypes = [vp, f32p]
+        L.psg_opt_set_poses.argtypes = [vp, f32p]
+        L.psg_opt_get_reg.argtypes = [vp, f32p]
+        L.psg_opt_set_reg.argtypes = [vp, f32p]
+        L.psg_opt_init_albedo.argtypes = [vp]
+        L.psg_opt_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+        L.psg_opt_reg_energies.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.psg_opt_residual.argtypes = [vp, f32p, f32p]
+        L.psg_opt_probe_pairs.argtypes = [vp, f32p, f32p, vp, f32p, f32p]
+        L.psg_opt_step.argtypes = [vp, C.c_int, C.c_float, C.c_int, C.POINTER(StepInfo)]
+        L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
+        L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
+        L.psg_opt_upsample.argtypes = [vp]
+        _lib = L
+    return _lib
+
+
+def _check(status: int) -> None:
+    if status != 0:
+        raise PsgError(f"psg status {status}: {lib().psg_last_error().decode(errors='replace')}")
+
+
+def kernel_launches() -> int:
+    return int(lib().psg_kernel_launches())
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class VolumetricGradSdf:
+    """Look-alike of the reference's volume class (VolumetricGradSdf.h:65-122) over psg_volume_*."""
+
+    def __init__(self, grid_dim, voxel_size, shift, T, max_frames=64, device=0):
+        self.h = C.c_void_p()
+        self.grid_dim = np.ascontiguousarray(grid_dim, np.int32)
+        self._zmin, self._zmax = 0.5, 10.0   # Sdf.h:39-40 defaults
+        self._args = (self.grid_dim, float(voxel_size), np.ascontiguousarray(shift, np.float32), float(T), int(max_frames), int(device))
+        self._created = False
+        self._pending_counter = False
+
+    def set_zmin(self, z):
+        self._zmin = float(z)
+
+    def set_zmax(self, z):
+        self._zmax = float(z)
+
+    def _ensure(self):
+        if not self._created:
+            gd, vs, sh, T, mf, dev = self._args
+            _check(lib().psg_volume_create(C.byref(self.h), gd, vs, sh, T, self._zmin, self._zmax, mf, dev))
+            self._created = True
+
+    def close(self):
+        if self._created:
+            lib().psg_volume_destroy(self.h)
+            self._created = False
+
+    def increase_counter(self):
+        self._pending_counter = True
+
+    def update(self, color, depth, K, R, t, nx, ny, nz, n_sq_inv):
+        """Sdf::update(color, depth, K, pose, NEst) with the estimator's outputs passed explicitly."""
+        self._ensure()
+        H, W = depth.shape
+        c = lambda a: np.ascontiguousarray(a, np.float32)
+        arrs = [c(color), c(depth), c(nx), c(ny), c(nz), c(n_sq_inv)]
+        _check(lib().psg_volume_integrate(self.h, *[_ptr(a) for a in arrs], H, W, c(K).reshape(9), c(R).reshape(9),
+                                          c(t).reshape(3), int(self._pending_counter)))
+        self._pending_counter = False
+
+    @property
+    def N(self):
+        dims, _, _ = self.geometry()
+        return int(dims[0]) * int(dims[1]) * int(dims[2])
+
+    def geometry(self):
+        self._ensure()
+        dims = np.zeros(3, np.int32)
+        vs = C.c_float()
+        org = np.zeros(3, np.float32)
+        _check(lib().psg_volume_geometry(self.h, dims, C.byref(vs), org))
+        return dims, np.float32(vs.value), org
+
+    def download(self):
+        self._ensure()
+        a = np.zeros((self.N, 8), np.float32)
+        _check(lib().psg_volume_download(self.h, a))
+        return a
+
+    def upload(self, aos):
+        self._ensure()
+        _check(lib().psg_volume_upload(self.h, np.ascontiguousarray(aos, np.float32)))
+
+    def vis(self):
+        self._ensure()
+        nw = C.c_int()
+        _check(lib().psg_volume_vis_words(self.h, C.byref(nw)))
+        w = np.zeros((nw.value, self.N), np.uint64)
+        _check(lib().psg_volume_download_vis(self.h, w))
+        return w
+
+    def set_vis(self, words, frame_counter):
+        self._ensure()
+        _check(lib().psg_volume_upload_vis(self.h, np.ascontiguousarray(words, np.uint64), int(frame_counter)))
+
+
+class Optimizer:
+    """Look-alike of Optimizer / PsOptimizer / LedOptimizer (Optimizer.h:24-182) over psg_opt_*."""
+
+    def __init__(self, tSDF: VolumetricGradSdf, voxel_size, K, model="SH1", loss="cauchy", lam=0.2, reg_rho=0.0,
+                 reg_n=0.0, reg_l=0.0):
+        tSDF._ensure()
+        self.vol = tSDF
+        self.model = model
+        self.h = C.c_void_p()
+        st = Settings(MODEL[model], LOSS[loss], lam, reg_rho, reg_n, reg_l)
+        _check(lib().psg_opt_create(C.byref(self.h), tSDF.h, float(voxel_size), np.ascontiguousarray(K, np.float32).reshape(9),
+                                    C.byref(st)))
+        self._F = 0
+
+    def close(self):
+        if self.h:
+            lib().psg_opt_destroy(self.h)
+            self.h = C.c_void_p()
+
+    # setImages + setKeyframes + setPoses (main_ps.cpp:323-326)
+    def set_keyframes(self, frame_idx, poses, images):
+        F, H, W, _ = images.shape
+        self._F = F
+        img = np.ascontiguousarray(images, np.float32)
+        _check(lib().psg_opt_set_keyframes(self.h, F, np.ascontiguousarray(frame_idx, np.int32),
+                                           np.ascontiguousarray(poses, np.float32).reshape(-1), _ptr(img), H, W))
+
+    def init(self):
+        _check(lib().psg_opt_init(self.h))
+
+    @property
+    def S(self):
+        s = C.c_int()
+        _check(lib().psg_opt_num_surface(self.h, C.byref(s)))
+        return s.value
+
+    @property
+    def F(self):
+        return self._F
+
+    def surface(self):
+        s = np.zeros(self.S, np.int32)
+        _check(lib().psg_opt_get_surface(self.h, _ptr(s), None))
+        return s
+
+    def vis_keyframes(self):
+        v = np.zeros(self.S, np.uint64)
+        _check(lib().psg_opt_get_surface(self.h, None, _ptr(v)))
+        return v
+
+    def light(self):
+        n = C.c_int()
+        _check(lib().psg_opt_light_len(self.h, C.byref(n)))
+        l = np.zeros(n.value, np.float32)
+        _check(lib().psg_opt_get_light(self.h, l))
+        return l
+
+    def set_light(self, l):
+        _check(lib().psg_opt_set_light(self.h, np.ascontiguousarray(l, np.float32).reshape(-1)))
+
+    def poses(self):
+        p = np.zeros(self.F * 16, np.float32)
+        _check(lib().psg_opt_get_poses(self.h, p))
+        return p.reshape(self.F, 4, 4)
+
+    def set_poses(self, p):
+        _check(lib().psg_opt_set_poses(self.h, np.ascontiguousarray(p, np.float32).reshape(-1)))
+
+    def reg(self):
+        r = np.zeros(3, np.float32)
+        _check(lib().psg_opt_get_reg(self.h, r))
+        return r
+
+    def set_reg(self, rho, n, l):
+        _check(lib().psg_opt_set_reg(self.h, np.array([rho, n, l], np.float32)))
+
+    def init_albedo(self):
+        _check(lib().psg_opt_init_albedo(self.h))
+
+    def energy(self):
+        e = C.c_double()
+        na = C.c_longlong()
+        _check(lib().psg_opt_energy(self.h, C.byref(e), C.byref(na)))
+        return e.value, na.value
+
+    def reg_energies(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        _check(lib().psg_opt_reg_energies(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def residual(self):
+        r = np.zeros((self.S, self.F, 3), np.float32)
+        w = np.zeros((self.S, self.F, 3), np.float32)
+        _check(lib().psg_opt_residual(self.h, r, w))
+        return r, w
+
+    def probe_pairs(self):
+        S, F = self.S, self.F
+        m = np.zeros((S, F), np.float32)
+        n = np.zeros((S, F), np.float32)
+        ok = np.zeros((S, F), np.uint8)
+        I = np.zeros((S, F, 3), np.float32)
+        rend = np.zeros((S, F, 3), np.float32)
+        _check(lib().psg_opt_probe_pairs(self.h, m, n, _ptr(ok), I, rend))
+        return m, n, ok, I, rend
+
+    def step(self, which, damping=1.0, albedo_reg=False, normal_reg=False, laplacian_reg=False):
+        flags = (REG_ALBEDO if albedo_reg else 0) | (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0)
+        info = StepInfo()
+        _check(lib().psg_opt_step(self.h, BLOCK[which], damping, flags, C.byref(info)))
+        return dict(n=info.n, cg_success=bool(info.cg_success), iters=info.cg_iterations, err=info.cg_error,
+                    applied=bool(info.applied), n_accepted=info.n_accepted)
+
+    def last_system(self, which):
+        """(H_blocks, b, delta) of the last light / pose step as float64 arrays."""
+        led = self.model == "LED"
+        bs = 6 if which == "pose" else (3 if led else (9 if self.model == "SH2" else 4))
+        nblk = 1 if (which == "light" and led) else self.F
+        H = np.zeros((nblk, bs, bs))
+        b = np.zeros(nblk * bs)
+        d = np.zeros(nblk * bs)
+        _check(lib().psg_opt_last_system(self.h, _ptr(H), _ptr(b), _ptr(d)))
+        return H, b, d
+
+    def last_vectors(self, which):
+        n = 3 * self.S if which == "albedo" else self.S
+        b = np.zeros(n, np.float32)
+        d = np.zeros(n, np.float32)
+        _check(lib().psg_opt_last_vectors(self.h, _ptr(b), _ptr(d)))
+        return b, d
+
+    def upsample(self):
+        _check(lib().psg_opt_upsample(self.h))

@@ -1,0 +1,621 @@
+// C ABI (include/psg.h) and the host-side control of the optimizer blocks: small dense solves, pose / light updates.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include <atomic>
+
+#include "psg_host.h"
+
+namespace psg {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+
+// Eigen::ConjugateGradient<SparseMatrix<float>, Lower, DiagonalPreconditioner<float>> on a small dense symmetric system
+// (the light and pose blocks: F independent 4x4 / 9x9 / 6x6 blocks solved jointly, exactly as the reference does,
+// PsOptimizer.cpp:184-191, 217-227).  Only the lower triangle is read.  Returns Eigen's verdict.
+struct CgVerdict { int success; int iters; float err; };
+static CgVerdict eigen_like_cg(int nblocks, int bs, const float* H /* nblocks * bs * bs */, const float* b, float* x) {
+    const int n = nblocks * bs;
+    std::vector<float> res(b, b + n), p(n), z(n), tmp(n), invd(n);
+    for (int i = 0; i < n; ++i) {
+        x[i] = 0.f;
+        const float d = H[(size_t)(i / bs) * bs * bs + (i % bs) * bs + (i % bs)];
+        invd[i] = d != 0.f ? 1.f / d : 1.f;
+    }
+    const float tol = 1.1920929e-07f;
+    const int maxIters = 2 * n;
+    float rhsNorm2 = 0.f;
+    for (int i = 0; i < n; ++i) rhsNorm2 += b[i] * b[i];
+    if (rhsNorm2 == 0.f) return {1, 0, 0.f};
+    float threshold = tol * tol * rhsNorm2;
+    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+    float residualNorm2 = rhsNorm2;
+    if (residualNorm2 < threshold) return {1, 0, std::sqrt(residualNorm2 / rhsNorm2)};
+    float absNew = 0.f;
+    for (int i = 0; i < n; ++i) { p[i] = invd[i] * res[i]; absNew += res[i] * p[i]; }
+    int it = 0;
+    while (it < maxIters) {
+        for (int blk = 0; blk < nblocks; ++blk) {
+            const float* Hb = H + (size_t)blk * bs * bs;
+            float* t = tmp.data() + blk * bs;
+            const float* pp = p.data() + blk * bs;
+            for (int i = 0; i < bs; ++i) t[i] = 0.f;
+            for (int i = 0; i < bs; ++i) {
+                t[i] += Hb[i * bs + i] * pp[i];
+                for (int k = 0; k < i; ++k) { t[i] += Hb[i * bs + k] * pp[k]; t[k] += Hb[i * bs + k] * pp[i]; }
+            }
+        }
+        float pt = 0.f;
+        for (int i = 0; i < n; ++i) pt += p[i] * tmp[i];
+        const float alpha = absNew / pt;
+        residualNorm2 = 0.f;
+        for (int i = 0; i < n; ++i) { x[i] += alpha * p[i]; res[i] -= alpha * tmp[i]; residualNorm2 += res[i] * res[i]; }
+        if (residualNorm2 < threshold) break;
+        const float absOld = absNew;
+        absNew = 0.f;
+        for (int i = 0; i < n; ++i) { z[i] = invd[i] * res[i]; absNew += res[i] * z[i]; }
+        const float beta = absNew / absOld;
+        for (int i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
+        ++it;
+    }
+    const float err = std::sqrt(residualNorm2 / rhsNorm2);
+    return {err <= tol ? 1 : 0, it, err};
+}
+
+// Sophus SO3::exp (third/Sophus/sophus/so3.hpp:583-619) followed by Eigen's Quaternion::toRotationMatrix
+static void so3_exp_matrix(const float* w, float* Rm) {
+    const float theta_sq = w[0] * w[0] + (w[1] * w[1] + w[2] * w[2]);
+    float imag, real;
+    if (theta_sq < 1e-10f * 1e-10f) {
+        const float t4 = theta_sq * theta_sq;
+        imag = 0.5f - (float)(1.0 / 48.0) * theta_sq + (float)(1.0 / 3840.0) * t4;
+        real = 1.f - (float)(1.0 / 8.0) * theta_sq + (float)(1.0 / 384.0) * t4;
+    } else {
+        const float theta = std::sqrt(theta_sq);
+        const float half = 0.5f * theta;
+        imag = std::sin(half) / theta;
+        real = std::cos(half);
+    }
+    const float qw = real, qx = imag * w[0], qy = imag * w[1], qz = imag * w[2];
+    const float tx = 2.f * qx, ty = 2.f * qy, tz = 2.f * qz;
+    const float twx = tx * qw, twy = ty * qw, twz = tz * qw, txx = tx * qx, txy = ty * qx, txz = tz * qx;
+    const float tyy = ty * qy, tyz = tz * qy, tzz = tz * qz;
+    Rm[0] = 1.f - (tyy + tzz); Rm[1] = txy - twz; Rm[2] = txz + twy;
+    Rm[3] = txy + twz; Rm[4] = 1.f - (txx + tzz); Rm[5] = tyz - twx;
+    Rm[6] = txz - twy; Rm[7] = tyz + twx; Rm[8] = 1.f - (txx + tyy);
+}
+
+// Optimizer::updatePose (OptimizerAux.cpp:190-205): t <- t - xi[0:3], R <- R * exp(-xi[3:6])
+static void update_poses(psg_optimizer* o, const float* d) {
+    for (int f = 0; f < o->F; ++f) {
+        float* P = o->poses.data() + 16 * f;
+        float R[9], E[9];
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) R[3 * a + b] = P[4 * a + b];
+        const float w[3] = { -d[6 * f + 3], -d[6 * f + 4], -d[6 * f + 5] };
+        so3_exp_matrix(w, E);
+        P[3] = P[3] - d[6 * f]; P[7] = P[7] - d[6 * f + 1]; P[11] = P[11] - d[6 * f + 2];
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b)
+            P[4 * a + b] = R[3 * a] * E[b] + (R[3 * a + 1] * E[3 + b] + R[3 * a + 2] * E[6 + b]);
+    }
+    o->frames_dirty = true;
+}
+
+static void sh_eval_host(const float* n, int nb, float* sh) {
+    sh[0] = 1.f; sh[1] = n[0]; sh[2] = n[1]; sh[3] = n[2];
+    if (nb == 9) {
+        sh[4] = n[0] * n[1]; sh[5] = n[0] * n[2]; sh[6] = n[1] * n[2];
+        sh[7] = n[0] * n[0] - n[1] * n[1]; sh[8] = n[0] * n[0] - n[2] * n[2];
+    }
+}
+
+// All transfers run on the handle's (non-blocking) stream: a plain cudaMemcpy would not order against it.
+static void copy_sync(void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st) {
+    PSG_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, st));
+    PSG_CUDA(cudaStreamSynchronize(st));
+}
+
+// float4-padded BGR texels
+__global__ void __launch_bounds__(256) k_pad_images(const float* __restrict__ src, float4* __restrict__ dst, long long npix) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], 0.f);
+}
+
+}  // namespace psg
+
+using namespace psg;
+
+#define PSG_TRY try {
+#define PSG_CATCH                                                      \
+    }                                                                  \
+    catch (const psg::CudaError&) { return PSG_ERR_CUDA; }             \
+    catch (const std::exception& e) { psg::set_error("%s", e.what()); return PSG_ERR_INVALID; }
+
+extern "C" {
+
+const char* psg_last_error(void) { return g_err; }
+long long psg_kernel_launches(void) { return g_launches.load(); }
+
+int psg_device_count(int* count) {
+    PSG_TRY
+    PSG_CUDA(cudaGetDeviceCount(count));
+    return PSG_OK;
+    PSG_CATCH
+}
+
+// ------------------------------------------------------------------ volume
+int psg_volume_create(psg_volume** out, const int dims[3], float voxel_size, const float shift[3], float T, float zmin,
+                      float zmax, int max_frames, int device) {
+    if (!out || !dims || !shift) { set_error("psg_volume_create: null argument"); return PSG_ERR_INVALID; }
+    if (dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 || (long long)dims[0] * dims[1] * dims[2] > (1ll << 31) - 64) {
+        set_error("psg_volume_create: grid %d x %d x %d not supported (needs 0 < W*H*D < 2^31)", dims[0], dims[1], dims[2]);
+        return PSG_ERR_INVALID;
+    }
+    if (max_frames < 1) { set_error("psg_volume_create: max_frames must be >= 1"); return PSG_ERR_INVALID; }
+    psg_volume* v = nullptr;
+    PSG_TRY
+    int ndev = 0;
+    PSG_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { set_error("psg_volume_create: device %d not available (%d devices)", device, ndev); return PSG_ERR_CUDA; }
+    PSG_CUDA(cudaSetDevice(device));
+    v = new psg_volume;
+    v->device = device;
+    for (int a = 0; a < 3; ++a) { v->dims[a] = dims[a]; v->shift[a] = shift[a]; }
+    v->N = (long long)dims[0] * dims[1] * dims[2];
+    v->vs = voxel_size;
+    // VoxelGrid(grid_dim, voxel_size, shift): origin = shift - 0.5 * voxel_size * dim (VoxelGrid.h:127-133)
+    const float half_vs = (float)(0.5 * (double)voxel_size);
+    for (int a = 0; a < 3; ++a) v->origin[a] = shift[a] - half_vs * (float)dims[a];
+    v->T = T; v->invT = (float)(1.0 / (double)T);   // Sdf(T): inv_T_(1./T_) (Sdf.h:83-87)
+    v->zmin = zmin; v->zmax = zmax;
+    v->max_frames = max_frames; v->nwords = (max_frames + 63) / 64;
+    PSG_CUDA(cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking));
+    for (int a = 0; a < 8; ++a) v->f[a].alloc((size_t)v->N);
+    v->vis.alloc((size_t)v->N * v->nwords);
+    launch_fill_volume(v);
+    PSG_CUDA(cudaStreamSynchronize(v->stream));
+    *out = v;
+    return PSG_OK;
+    }
+    catch (const psg::CudaError&) { if (v) psg_volume_destroy(v); return PSG_ERR_CUDA; }
+}
+
+int psg_volume_destroy(psg_volume* v) {
+    if (!v) return PSG_OK;
+    cudaSetDevice(v->device);
+    for (int a = 0; a < 8; ++a) v->f[a].release();
+    v->vis.release(); v->frame.release(); v->staging.release();
+    if (v->stream) cudaStreamDestroy(v->stream);
+    delete v;
+    return PSG_OK;
+}
+
+int psg_volume_geometry(const psg_volume* v, int dims[3], float* voxel_size, float origin[3]) {
+    if (!v) { set_error("null volume"); return PSG_ERR_INVALID; }
+    for (int a = 0; a < 3; ++a) { if (dims) dims[a] = v->dims[a]; if (origin) origin[a] = v->origin[a]; }
+    if (voxel_size) *voxel_size = v->vs;
+    return PSG_OK;
+}
+
+int psg_volume_integrate(psg_volume* v, const float* color_bgr, const float* depth, const float* nx, const float* ny,
+                         const float* nz, const float* n_sq_inv, int H, int W, const float K[9], const float R[9],
+                         const float t[3], int increase_counter) {
+    if (!v || !color_bgr || !depth || !nx || !ny || !nz || !n_sq_inv || !K || !R || !t || H <= 0 || W <= 0) {
+        set_error("psg_volume_integrate: null or empty argument");
+        return PSG_ERR_INVALID;
+    }
+    const int counter = v->counter + (increase_counter ? 1 : 0);
+    if (counter >= 64 * v->nwords) {
+        set_error("psg_volume_integrate: frame %d exceeds max_frames %d given at creation", counter, v->max_frames);
+        return PSG_ERR_INVALID;
+    }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(v->device));
+    const size_t HW = (size_t)H * W;
+    v->staging.alloc(HW * 8);
+    float* st = v->staging.p;
+    PSG_CUDA(cudaMemcpyAsync(st, color_bgr, HW * 3 * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    PSG_CUDA(cudaMemcpyAsync(st + 3 * HW, depth, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    PSG_CUDA(cudaMemcpyAsync(st + 4 * HW, nx, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    PSG_CUDA(cudaMemcpyAsync(st + 5 * HW, ny, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    PSG_CUDA(cudaMemcpyAsync(st + 6 * HW, nz, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    PSG_CUDA(cudaMemcpyAsync(st + 7 * HW, n_sq_inv, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+    launch_pack_frame(v, st, H, W);
+    v->counter = counter;
+    launch_integrate(v, H, W, K, R, t, counter);
+    PSG_CUDA(cudaStreamSynchronize(v->stream));
+    return PSG_OK;
+    PSG_CATCH
+}
+
+static const long long kChunk = 1ll << 24;   // voxels per staging chunk (512 MiB of AoS)
+
+int psg_volume_download(psg_volume* v, float* aos8) {
+    if (!v || !aos8) { set_error("psg_volume_download: null argument"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(v->device));
+    const long long chunk = v->N < kChunk ? v->N : kChunk;
+    v->staging.alloc((size_t)chunk * 8);
+    for (long long b = 0; b < v->N; b += chunk) {
+        const long long c = (v->N - b) < chunk ? (v->N - b) : chunk;
+        launch_soa_to_aos(v, v->staging.p, b, c);
+        PSG_CUDA(cudaMemcpyAsync(aos8 + 8 * b, v->staging.p, (size_t)c * 8 * sizeof(float), cudaMemcpyDeviceToHost, v->stream));
+        PSG_CUDA(cudaStreamSynchronize(v->stream));
+    }
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_volume_upload(psg_volume* v, const float* aos8) {
+    if (!v || !aos8) { set_error("psg_volume_upload: null argument"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(v->device));
+    const long long chunk = v->N < kChunk ? v->N : kChunk;
+    v->staging.alloc((size_t)chunk * 8);
+    for (long long b = 0; b < v->N; b += chunk) {
+        const long long c = (v->N - b) < chunk ? (v->N - b) : chunk;
+        PSG_CUDA(cudaMemcpyAsync(v->staging.p, aos8 + 8 * b, (size_t)c * 8 * sizeof(float), cudaMemcpyHostToDevice, v->stream));
+        launch_aos_to_soa(v, v->staging.p, b, c);
+        PSG_CUDA(cudaStreamSynchronize(v->stream));
+    }
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_volume_vis_words(const psg_volume* v, int* nwords) {
+    if (!v || !nwords) { set_error("null argument"); return PSG_ERR_INVALID; }
+    *nwords = v->nwords;
+    return PSG_OK;
+}
+int psg_volume_download_vis(psg_volume* v, uint64_t* words) {
+    if (!v || !words) { set_error("null argument"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(v->device));
+    copy_sync(words, v->vis.p, (size_t)v->N * v->nwords * sizeof(uint64_t), cudaMemcpyDeviceToHost, v->stream);
+    return PSG_OK;
+    PSG_CATCH
+}
+int psg_volume_upload_vis(psg_volume* v, const uint64_t* words, int frame_counter) {
+    if (!v || !words) { set_error("null argument"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(v->device));
+    copy_sync(v->vis.p, words, (size_t)v->N * v->nwords * sizeof(uint64_t), cudaMemcpyHostToDevice, v->stream);
+    v->counter = frame_counter;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+// ------------------------------------------------------------------ optimizer
+int psg_opt_create(psg_optimizer** out, psg_volume* vol, float voxel_size, const float K[9], const psg_settings* set) {
+    if (!out || !vol || !K || !set) { set_error("psg_opt_create: null argument"); return PSG_ERR_INVALID; }
+    if (set->model < 0 || set->model > 2) { set_error("psg_opt_create: unknown model %d", set->model); return PSG_ERR_INVALID; }
+    if (set->loss < 0 || set->loss > 4) { set_error("psg_opt_create: unknown loss %d", set->loss); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(vol->device));
+    psg_optimizer* o = new psg_optimizer;
+    o->vol = vol; o->set = *set;
+    o->nb = set->model == PSG_MODEL_SH2 ? 9 : 4;
+    o->vs = voxel_size; o->vs_inv = 1.f / voxel_size;   // Optimizer.cpp:22-23
+    memcpy(o->K, K, sizeof(o->K));
+    o->stream = vol->stream;
+    *out = o;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_destroy(psg_optimizer* o) {
+    if (!o) return PSG_OK;
+    cudaSetDevice(o->vol->device);
+    o->images.release(); o->frames.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
+    o->svis.release(); o->pos.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
+    o->frame_idx_dev.release(); o->red.release(); o->vecs.release(); o->pcg_partials.release();
+    delete o;
+    return PSG_OK;
+}
+
+int psg_opt_set_keyframes(psg_optimizer* o, int F, const int* frame_idx, const float* poses16, const float* images,
+                          int H, int W) {
+    if (!o || (F > 0 && (!frame_idx || !poses16 || !images)) || F < 0 || H <= 0 || W <= 0) {
+        set_error("psg_opt_set_keyframes: null or empty argument");
+        return PSG_ERR_INVALID;
+    }
+    if (F > kMaxFrames) { set_error("psg_opt_set_keyframes: %d keyframes given, at most %d supported", F, kMaxFrames); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    o->F = F; o->H = H; o->W = W;
+    o->frame_idx.assign(frame_idx, frame_idx + F);
+    o->poses.assign(poses16, poses16 + 16 * (size_t)F);
+    const long long npix = (long long)F * H * W;
+    o->images.alloc((size_t)(npix > 0 ? npix : 1));
+    // stage one keyframe at a time through the volume's staging buffer
+    const long long per = (long long)H * W;
+    o->vol->staging.alloc((size_t)per * 3);
+    for (int f = 0; f < F; ++f) {
+        PSG_CUDA(cudaMemcpyAsync(o->vol->staging.p, images + (size_t)f * per * 3, (size_t)per * 3 * sizeof(float),
+                                 cudaMemcpyHostToDevice, o->stream));
+        k_pad_images<<<(unsigned)((per + 255) / 256), 256, 0, o->stream>>>(o->vol->staging.p, o->images.p + (size_t)f * per, per);
+        count_launch();
+        PSG_LAUNCH_CHECK();
+    }
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    o->frames_dirty = true;
+    o->inited = false;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_init(psg_optimizer* o) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const bool led = o->set.model == PSG_MODEL_LED;
+    if (led) {
+        o->light.assign(3, 1.f);
+    } else {
+        // PsOptimizer::init (PsOptimizer.cpp:30-37): l_f = SH(R_f * (0,0,-1)), l_f[0] = 0.02
+        o->light.assign((size_t)o->F * o->nb, 0.f);
+        for (int f = 0; f < o->F; ++f) {
+            const float* P = o->poses.data() + 16 * f;
+            const float s[3] = {0.f, 0.f, -1.f};
+            float d[3];
+            for (int a = 0; a < 3; ++a) d[a] = P[4 * a] * s[0] + (P[4 * a + 1] * s[1] + P[4 * a + 2] * s[2]);
+            sh_eval_host(d, o->nb, o->light.data() + (size_t)f * o->nb);
+            o->light[(size_t)f * o->nb] = 0.02f;
+        }
+    }
+    o->frames_dirty = true;
+    build_surface(o, true);
+    o->inited = true;
+    if (led && o->S > 0) {
+        // LedOptimizer::computeLightIntensive (LedOptimizer.cpp:76-112)
+        double sums[6];
+        sweep_led_light_init(o, sums);
+        for (int c = 0; c < 3; ++c) o->light[c] = (float)sums[c] / (float)sums[3 + c];
+    }
+    return PSG_OK;
+    PSG_CATCH
+}
+
+#define PSG_NEED_INIT(o)                                                                   \
+    if (!(o)) { set_error("null optimizer"); return PSG_ERR_INVALID; }                     \
+    if (!(o)->inited) { set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
+
+int psg_opt_num_surface(const psg_optimizer* o, int* S) {
+    PSG_NEED_INIT(o)
+    *S = o->S;
+    return PSG_OK;
+}
+
+int psg_opt_get_surface(psg_optimizer* o, int* lin, uint64_t* vis) {
+    PSG_NEED_INIT(o)
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (o->S > 0) {
+        if (lin) copy_sync(lin, o->lin.p, (size_t)o->S * sizeof(int), cudaMemcpyDeviceToHost, o->stream);
+        if (vis) copy_sync(vis, o->svis.p, (size_t)o->S * sizeof(uint64_t), cudaMemcpyDeviceToHost, o->stream);
+    }
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_light_len(const psg_optimizer* o, int* n) {
+    if (!o || !n) { set_error("null argument"); return PSG_ERR_INVALID; }
+    *n = o->set.model == PSG_MODEL_LED ? 3 : o->F * o->nb;
+    return PSG_OK;
+}
+int psg_opt_get_light(psg_optimizer* o, float* light) {
+    PSG_NEED_INIT(o)
+    memcpy(light, o->light.data(), o->light.size() * sizeof(float));
+    return PSG_OK;
+}
+int psg_opt_set_light(psg_optimizer* o, const float* light) {
+    PSG_NEED_INIT(o)
+    memcpy(o->light.data(), light, o->light.size() * sizeof(float));
+    o->frames_dirty = true;
+    return PSG_OK;
+}
+int psg_opt_get_poses(psg_optimizer* o, float* poses16) {
+    if (!o || !poses16) { set_error("null argument"); return PSG_ERR_INVALID; }
+    memcpy(poses16, o->poses.data(), o->poses.size() * sizeof(float));
+    return PSG_OK;
+}
+int psg_opt_set_poses(psg_optimizer* o, const float* poses16) {
+    if (!o || !poses16) { set_error("null argument"); return PSG_ERR_INVALID; }
+    memcpy(o->poses.data(), poses16, o->poses.size() * sizeof(float));
+    o->frames_dirty = true;
+    return PSG_OK;
+}
+int psg_opt_get_reg(const psg_optimizer* o, float r[3]) {
+    if (!o || !r) { set_error("null argument"); return PSG_ERR_INVALID; }
+    r[0] = o->set.reg_weight_rho; r[1] = o->set.reg_weight_n; r[2] = o->set.reg_weight_l;
+    return PSG_OK;
+}
+int psg_opt_set_reg(psg_optimizer* o, const float r[3]) {
+    if (!o || !r) { set_error("null argument"); return PSG_ERR_INVALID; }
+    o->set.reg_weight_rho = r[0]; o->set.reg_weight_n = r[1]; o->set.reg_weight_l = r[2];
+    return PSG_OK;
+}
+
+int psg_opt_init_albedo(psg_optimizer* o) {
+    PSG_NEED_INIT(o)
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    sweep_init_albedo(o);
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_energy(psg_optimizer* o, double* E, long long* n_active) {
+    PSG_NEED_INIT(o)
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    double sum = 0.0; long long na = 0;
+    sweep_energy(o, &sum, &na);
+    if (E) *E = sum / (double)o->S;   // E / surface_points_.size() (PsOptimizer.cpp:77)
+    if (n_active) *n_active = na;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
+    PSG_NEED_INIT(o)
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    double a = 0, b = 0, c = 0;
+    reg_energies(o, &a, &b, &c);
+    if (En) *En = a / (double)o->S;
+    if (El) *El = b / (double)o->S;
+    if (Er) *Er = c / (double)o->S;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+static int probe_common(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const size_t SF = (size_t)o->S * o->F;
+    if (SF == 0) return PSG_OK;
+    DevBuf<float> buf; DevBuf<unsigned char> okb;
+    buf.alloc(SF * 14); okb.alloc(SF);
+    PSG_CUDA(cudaMemsetAsync(buf.p, 0, SF * 14 * sizeof(float), o->stream));
+    PSG_CUDA(cudaMemsetAsync(okb.p, 0, SF, o->stream));
+    float* dm = buf.p; float* dn = dm + SF; float* dI = dn + SF; float* dr = dI + 3 * SF; float* dres = dr + 3 * SF; float* dw = dres + 3 * SF;
+    sweep_probe(o, dm, dn, okb.p, dI, dr, dres, dw);
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    if (m) copy_sync(m, dm, SF * 4, cudaMemcpyDeviceToHost, o->stream);
+    if (n) copy_sync(n, dn, SF * 4, cudaMemcpyDeviceToHost, o->stream);
+    if (ok) copy_sync(ok, okb.p, SF, cudaMemcpyDeviceToHost, o->stream);
+    if (I3) copy_sync(I3, dI, SF * 12, cudaMemcpyDeviceToHost, o->stream);
+    if (rend3) copy_sync(rend3, dr, SF * 12, cudaMemcpyDeviceToHost, o->stream);
+    if (r3) copy_sync(r3, dres, SF * 12, cudaMemcpyDeviceToHost, o->stream);
+    if (w3) copy_sync(w3, dw, SF * 12, cudaMemcpyDeviceToHost, o->stream);
+    buf.release(); okb.release();
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_residual(psg_optimizer* o, float* r3, float* w3) {
+    PSG_NEED_INIT(o)
+    return probe_common(o, nullptr, nullptr, nullptr, nullptr, nullptr, r3, w3);
+}
+int psg_opt_probe_pairs(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3) {
+    PSG_NEED_INIT(o)
+    return probe_common(o, m, n, ok, I3, rend3, nullptr, nullptr);
+}
+
+int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step_info* info) {
+    PSG_NEED_INIT(o)
+    if (block < 0 || block > 3) { set_error("psg_opt_step: unknown block %d", block); return PSG_ERR_INVALID; }
+    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO)) {
+        set_error("psg_opt_step: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
+                  "the reference's README asks for reg albedo = 0");
+        return PSG_ERR_UNSUPPORTED;
+    }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const bool led = o->set.model == PSG_MODEL_LED;
+    psg_step_info inf;
+    memset(&inf, 0, sizeof(inf));
+    o->last_block = block;
+    if (block == PSG_BLOCK_ALBEDO) {
+        const size_t n = (size_t)3 * o->S;
+        o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
+        float* bdev = o->vecs.p; float* ddev = o->vecs.p + n;
+        long long acc = 0;
+        sweep_albedo(o, damping, &acc, bdev, ddev);
+        inf.n = (int)n; inf.cg_success = 1; inf.cg_iterations = 0; inf.cg_error = 0.f; inf.applied = 1; inf.n_accepted = acc;
+        o->last_n = (int)n;
+    } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
+        std::vector<double> Hd, bd;
+        sweep_small_block(o, block, Hd, bd);
+        const int bs = block == PSG_BLOCK_POSE ? 6 : (led ? 3 : o->nb);
+        const int nblk = (block == PSG_BLOCK_LIGHT && led) ? 1 : o->F;
+        const int n = bs * nblk;
+        // H.diagonal() += damping * H.diagonal(): every block but the SH light block (PsOptimizer.cpp:175-203)
+        const bool damp = !(block == PSG_BLOCK_LIGHT && !led);
+        std::vector<float> Hf(Hd.size()), bf(bd.size()), x((size_t)n, 0.f);
+        for (size_t i = 0; i < Hd.size(); ++i) Hf[i] = (float)Hd[i];
+        for (size_t i = 0; i < bd.size(); ++i) bf[i] = (float)bd[i];
+        if (damp && damping != 0.f)
+            for (int i = 0; i < n; ++i) {
+                float& d = Hf[(size_t)(i / bs) * bs * bs + (i % bs) * bs + (i % bs)];
+                d = d + damping * d;
+            }
+        const CgVerdict v = eigen_like_cg(nblk, bs, Hf.data(), bf.data(), x.data());
+        inf.n = n; inf.cg_success = v.success; inf.cg_iterations = v.iters; inf.cg_error = v.err;
+        o->lastH.assign(Hf.begin(), Hf.end());
+        o->lastb.assign(bf.begin(), bf.end());
+        o->lastdelta.assign(x.begin(), x.end());
+        o->last_n = n;
+        if (block == PSG_BLOCK_LIGHT) {
+            // light_[frame] -= delta (PsOptimizer.cpp:199-201, LedOptimizer.cpp:159), unconditionally
+            for (int i = 0; i < n; ++i) o->light[i] -= x[i];
+            o->frames_dirty = true;
+            inf.applied = 1;
+        } else {
+            // SH: updatePose unconditionally (PsOptimizer.cpp:232); LED: only on Success (LedOptimizer.cpp:271-273)
+            if (!led || v.success) { update_poses(o, x.data()); inf.applied = 1; }
+        }
+    } else {
+        sweep_dist(o, flags);
+        int ok = 1, iters = 0; float err = 0.f;
+        solve_dist(o, damping, &ok, &iters, &err);
+        inf.n = o->S; inf.cg_success = ok; inf.cg_iterations = iters; inf.cg_error = err;
+        o->last_n = o->S;
+        // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242)
+        if (led || ok) { long long acc = 0; apply_dist_update(o, &acc); inf.applied = 1; inf.n_accepted = acc; }
+    }
+    if (info) *info = inf;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_last_system(psg_optimizer* o, double* H, double* b, double* delta) {
+    PSG_NEED_INIT(o)
+    if (o->last_block != PSG_BLOCK_LIGHT && o->last_block != PSG_BLOCK_POSE) { set_error("last step was not a light or pose block"); return PSG_ERR_STATE; }
+    if (H) memcpy(H, o->lastH.data(), o->lastH.size() * sizeof(double));
+    if (b) memcpy(b, o->lastb.data(), o->lastb.size() * sizeof(double));
+    if (delta) memcpy(delta, o->lastdelta.data(), o->lastdelta.size() * sizeof(double));
+    return PSG_OK;
+}
+
+int psg_opt_last_vectors(psg_optimizer* o, float* b, float* delta) {
+    PSG_NEED_INIT(o)
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const size_t S = (size_t)o->S;
+    if (o->last_block == PSG_BLOCK_ALBEDO) {
+        if (b) copy_sync(b, o->vecs.p, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
+        if (delta) copy_sync(delta, o->vecs.p + 3 * S, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
+    } else if (o->last_block == PSG_BLOCK_DIST) {
+        if (b) copy_sync(b, o->vecs.p + 14 * S, S * 4, cudaMemcpyDeviceToHost, o->stream);
+        if (delta) copy_sync(delta, o->vecs.p + 17 * S, S * 4, cudaMemcpyDeviceToHost, o->stream);
+    } else { set_error("last step was not an albedo or distance block"); return PSG_ERR_STATE; }
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_upsample(psg_optimizer* o) {
+    PSG_NEED_INIT(o)
+    if (8 * o->vol->N > (1ll << 31) - 64) { set_error("psg_opt_upsample: upsampled grid exceeds 2^31 voxels"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    launch_upsample(o);
+    build_surface(o, false);
+    return PSG_OK;
+    PSG_CATCH
+}
+
+}  // extern "C"

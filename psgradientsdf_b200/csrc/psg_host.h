@@ -1,0 +1,125 @@
+// Host-side state behind the opaque C handles (include/psg.h) and the launcher prototypes each .cu file exports.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/psg.h"
+#include "psg_device.cuh"
+
+namespace psg {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+struct CudaError { int code; };
+#define PSG_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            psg::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e__)); \
+            throw psg::CudaError{(int)e__};                                                     \
+        }                                                                                       \
+    } while (0)
+#define PSG_LAUNCH_CHECK() PSG_CUDA(cudaGetLastError())
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        if (count == 0) count = 1;
+        PSG_CUDA(cudaMalloc((void**)&p, count * sizeof(T)));
+        n = count;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+    }
+};
+
+}  // namespace psg
+
+struct psg_volume {
+    int device = 0;
+    int dims[3] = {0, 0, 0};
+    long long N = 0;
+    float vs = 0.f, shift[3] = {0, 0, 0}, origin[3] = {0, 0, 0}, T = 0.f, invT = 0.f, zmin = 0.f, zmax = 0.f;
+    int max_frames = 64, nwords = 1, counter = 0;
+    psg::DevBuf<float> f[8];                 // dist gx gy gz w r g b
+    psg::DevBuf<unsigned long long> vis;     // nwords * N
+    psg::DevBuf<float> frame;                // packed per-pixel fusion inputs (8 floats / pixel)
+    psg::DevBuf<float> staging;              // H2D staging for planar inputs / AoS transfers
+    cudaStream_t stream = nullptr;
+    psg::VolView view() const;
+};
+
+struct psg_optimizer {
+    psg_volume* vol = nullptr;
+    psg_settings set{};
+    int nb = 4;                              // SH basis size
+    float vs = 0.f, vs_inv = 0.f;            // Optimizer::voxel_size_, voxel_size_inv_
+    float K[9] = {0};
+    int F = 0, H = 0, W = 0;
+    std::vector<int> frame_idx;
+    std::vector<float> poses;                // F x 16 (host copy, authoritative)
+    std::vector<float> light;                // F x nb or 3
+    psg::DevBuf<float4> images;              // F x H x W texels (b, g, r, 0)
+    psg::DevBuf<psg::FrameParams> frames;    // F
+    bool frames_dirty = true;
+    bool inited = false;
+    // surface work list
+    int S = 0;
+    psg::DevBuf<int> lin, nbr_lin, nbr_row, inc;
+    psg::DevBuf<unsigned long long> svis;
+    psg::DevBuf<unsigned char> pos;
+    psg::DevBuf<unsigned int> mask, prefix;  // membership bitmask over the volume + exclusive popcount prefix
+    psg::DevBuf<unsigned int> block_counts;
+    psg::DevBuf<int> frame_idx_dev;
+    // reductions / systems
+    psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
+    psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
+    psg::DevBuf<double> pcg_partials;
+    std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
+    std::vector<float> lastvb, lastvd;
+    int last_n = 0, last_block = -1;
+    cudaStream_t stream = nullptr;
+};
+
+namespace psg {
+
+// ---- volume.cu
+void launch_fill_volume(psg_volume* v);
+void launch_integrate(psg_volume* v, int H, int W, const float* K, const float* R, const float* t, int counter);
+void launch_pack_frame(psg_volume* v, const float* planar_dev, int H, int W);
+void launch_aos_to_soa(psg_volume* v, const float* aos_dev, long long begin, long long count);
+void launch_soa_to_aos(psg_volume* v, float* aos_dev, long long begin, long long count);
+
+// ---- surface.cu
+void build_surface(psg_optimizer* o, bool reindex_vis);
+void launch_upsample(psg_optimizer* o);
+
+// ---- sweep.cu
+struct SweepOut {
+    double E = 0.0;
+    long long n_active = 0;
+};
+void upload_frames(psg_optimizer* o);
+void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
+void sweep_init_albedo(psg_optimizer* o);
+void sweep_led_light_init(psg_optimizer* o, double sums[6]);
+void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3);
+void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b_dev, float* delta_dev);
+void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& H, std::vector<double>& b);
+void sweep_dist(psg_optimizer* o, int flags);
+void reg_energies(psg_optimizer* o, double* En, double* El, double* Er);
+
+// ---- pcg.cu
+void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float* err);
+void apply_dist_update(psg_optimizer* o, long long* accepted);
+
+}  // namespace psg

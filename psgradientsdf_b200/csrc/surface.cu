@@ -1,0 +1,287 @@
+// Keyframe-visibility selection, surface-voxel compaction into a dense ordered work list, finite-difference
+// neighbour tables, and 2x upsampling.
+//
+// Replaces Optimizer::select_vis (cpp/include/ps_optimizer/Optimizer.cpp:30-47), Optimizer::getSurfaceVoxel
+// (OptimizerAux.cpp:237-257), the std::find membership tests of Optimizer::ifValidDirection
+// (Optimizer.cpp:462-474) and Optimizer::subsampling (OptimizerAux.cpp:622-684).
+//
+// Membership is a bitmask over the volume (1 bit / voxel) plus an exclusive popcount prefix per 32-voxel word
+// (a rank structure, 0.25 B / voxel instead of a 4 B / voxel row map): member(l) is a bit test and
+// row(l) = prefix[l/32] + popc(mask[l/32] below bit l%32), which is also what keeps the list in ascending lin order.
+#include "psg_host.h"
+
+namespace psg {
+
+struct SelectParams {
+    int F;
+    int frame_idx[kMaxFrames];
+    double thr;   // sqrt(3.0) * voxel_size, evaluated in double (OptimizerAux.cpp:249)
+};
+
+// Optimizer::select_vis for one voxel: keyframe slot k takes vis[frame_idx[k]] while frame_idx[k] < vis.size()
+// (slots are filled consecutively, exactly like the push_back loop), the rest is padded with false.
+__device__ __forceinline__ unsigned long long select_vis(const VolView& v, long long lin, const SelectParams& P) {
+    int len = 0;
+    for (int w = v.nwords - 1; w >= 0; --w) {
+        const unsigned long long word = v.vis[(long long)w * v.N + lin];
+        if (word) { len = 64 * w + (64 - __clzll((long long)word)); break; }
+    }
+    if (len == 0) return 0ull;
+    unsigned long long out = 0ull;
+    int posn = 0;
+    for (int k = 0; k < P.F; ++k) {
+        const int fi = P.frame_idx[k];
+        if ((unsigned)fi < (unsigned)len) {
+            const unsigned long long word = v.vis[(long long)(fi >> 6) * v.N + lin];
+            out |= ((word >> (fi & 63)) & 1ull) << posn;
+            ++posn;
+        }
+    }
+    return out;
+}
+
+// Pass 1: surface predicate per voxel -> membership words + per-block counts.
+// Each warp owns consecutive 32-voxel words; a block owns words [blockIdx.x * wpb, (blockIdx.x + 1) * wpb).
+__global__ void __launch_bounds__(256) k_surface_mask(VolView v, SelectParams P, unsigned* __restrict__ mask,
+                                                     unsigned* __restrict__ block_counts, long long nwords_total, int wpb) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const long long w0 = (long long)blockIdx.x * wpb;
+    unsigned cnt = 0;
+    for (long long w = w0 + warp; w < w0 + wpb && w < nwords_total; w += nwarps) {
+        const long long lin = w * 32 + lane;
+        bool on = false;
+        if (lin < v.N) {
+            const float d = v.dist[lin];
+            if (fabs((double)d) <= P.thr) on = select_vis(v, lin, P) != 0ull;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, on);
+        if (lane == 0) { mask[w] = m; cnt += __popc(m); }
+    }
+    __shared__ unsigned s_cnt[8];
+    if (lane == 0) s_cnt[warp] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = 0;
+        for (int i = 0; i < nwarps; ++i) t += s_cnt[i];
+        block_counts[blockIdx.x] = t;
+    }
+}
+
+// Pass 2: exclusive scan of the per-block counts (single block, chunked with a carry); total -> counts[n].
+__global__ void __launch_bounds__(1024) k_scan_counts(unsigned* __restrict__ counts, int n) {
+    __shared__ unsigned s_warp[32];
+    __shared__ unsigned s_carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned x = i < n ? counts[i] : 0u;
+        unsigned inc = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned ws = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, ws, o); if (lane >= o) ws += y; }
+            s_warp[lane] = ws;   // inclusive
+        }
+        __syncthreads();
+        const unsigned carry = s_carry;
+        const unsigned warp_off = warp ? s_warp[warp - 1] : 0u;
+        if (i < n) counts[i] = carry + warp_off + inc - x;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + warp_off + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) counts[n] = s_carry;
+}
+
+// Pass 3: per-word exclusive prefix, then ordered scatter of lin and keyframe visibility.
+__global__ void __launch_bounds__(256) k_surface_scatter(VolView v, SelectParams P, const unsigned* __restrict__ mask,
+                                                        const unsigned* __restrict__ block_offsets,
+                                                        unsigned* __restrict__ prefix, long long nwords_total, int wpb,
+                                                        int* __restrict__ lin_out, unsigned long long* __restrict__ vis_out) {
+    __shared__ unsigned s_warp[8];
+    __shared__ unsigned s_carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const long long w0 = (long long)blockIdx.x * wpb;
+    if (threadIdx.x == 0) s_carry = block_offsets[blockIdx.x];
+    __syncthreads();
+    // phase A: prefix per word, one word per thread per chunk
+    for (long long base = w0; base < w0 + wpb && base < nwords_total; base += blockDim.x) {
+        const long long w = base + threadIdx.x;
+        const bool in = (w < w0 + wpb) && (w < nwords_total);
+        const unsigned x = in ? __popc(mask[w]) : 0u;
+        unsigned inc = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        unsigned warp_off = 0;
+        for (int i = 0; i < warp; ++i) warp_off += s_warp[i];
+        const unsigned carry = s_carry;
+        if (in) prefix[w] = carry + warp_off + inc - x;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) s_carry = carry + warp_off + inc;
+        __syncthreads();
+    }
+    // phase B: scatter (prefix[] written above by this block; visible after the barrier)
+    for (long long w = w0 + warp; w < w0 + wpb && w < nwords_total; w += nwarps) {
+        const unsigned m = mask[w];
+        if (m == 0u) continue;
+        if ((m >> lane) & 1u) {
+            const unsigned row = prefix[w] + __popc(m & ((1u << lane) - 1u));
+            const long long lin = w * 32 + lane;
+            lin_out[row] = (int)lin;
+            vis_out[row] = select_vis(v, lin, P);
+        }
+    }
+}
+
+__device__ __forceinline__ bool is_member(const unsigned* mask, long long l) { return (mask[l >> 5] >> (l & 31)) & 1u; }
+__device__ __forceinline__ int row_of(const unsigned* mask, const unsigned* prefix, long long l) {
+    const unsigned m = mask[l >> 5];
+    return (int)(prefix[l >> 5] + __popc(m & ((1u << (l & 31)) - 1u)));
+}
+
+// Pass 4: finite-difference neighbour per axis as Optimizer::computeDistGrad chooses it (Optimizer.cpp:287-347):
+// forward neighbour if it is a surface voxel, else the backward neighbour unchecked.  Neighbours are addressed by
+// linear offset exactly as idx2line does.  A backward neighbour below index 0 (undefined behaviour in the reference)
+// is recorded as -1 and treated as "same value as the centre".
+// inc[6*S]: surface rows whose 4-voxel stencil contains this row as neighbour along axis a (see pcg.cu).
+__global__ void __launch_bounds__(256) k_neighbors(VolView v, const unsigned* __restrict__ mask, const unsigned* __restrict__ prefix,
+                                                  const int* __restrict__ lin_in, int S, int* __restrict__ nbr_lin,
+                                                  int* __restrict__ nbr_row, unsigned char* __restrict__ pos, int* __restrict__ inc) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const long long lin = lin_in[s];
+    const long long stride[3] = { 1, v.dims[0], (long long)v.dims[0] * v.dims[1] };
+    unsigned char pb = 0;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const long long fwd = lin + stride[a];
+        const bool valid = fwd < v.N && is_member(mask, fwd);   // idx[a] + 1 <= dim[a] always holds inside the grid
+        long long nl = valid ? fwd : lin - stride[a];
+        if (nl < 0) nl = -1;
+        if (valid) pb |= (unsigned char)(1u << a);
+        nbr_lin[a * S + s] = (int)nl;
+        nbr_row[a * S + s] = (nl >= 0 && is_member(mask, nl)) ? row_of(mask, prefix, nl) : -1;
+        // incident stencils
+        const long long tm = lin - stride[a];
+        inc[a * S + s] = (tm >= 0 && is_member(mask, tm)) ? row_of(mask, prefix, tm) : -1;
+        int ip = -1;
+        if (valid) {   // t+ = fwd is a member; it points back at us iff its own forward neighbour is not a member
+            const long long f2 = fwd + stride[a];
+            const bool fwd_has_fwd = f2 < v.N && is_member(mask, f2);
+            if (!fwd_has_fwd) ip = row_of(mask, prefix, fwd);
+        }
+        inc[(3 + a) * S + s] = ip;
+    }
+    pos[s] = pb;
+}
+
+// Optimizer::subsampling / VolumetricGradSdf::subsample (OptimizerAux.cpp:622-684, VolumetricGradSdf.cpp:469-494):
+// one thread per CHILD voxel gathers from its parent.
+__global__ void __launch_bounds__(256) k_upsample(VolView src, VolView dst, float vs4) {
+    const long long lin = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lin >= dst.N) return;
+    const int W0 = dst.dims[0], W1 = dst.dims[1];
+    const int i = (int)(lin % W0);
+    const long long rest = lin / W0;
+    const int j = (int)(rest % W1);
+    const int k = (int)(rest / W1);
+    const long long pl = (long long)(i >> 1) + (long long)src.dims[0] * (j >> 1) + (long long)src.dims[0] * src.dims[1] * (k >> 1);
+    const float pd = src.dist[pl];
+    if (pd == src.T) {   // never-fused parents are skipped; children keep the fill value (dist = T, rgb = 0.5)
+        dst.dist[lin] = src.T; dst.gx[lin] = 0.f; dst.gy[lin] = 0.f; dst.gz[lin] = 0.f;
+        dst.w[lin] = 0.f; dst.r[lin] = 0.5f; dst.g[lin] = 0.5f; dst.b[lin] = 0.5f;
+        for (int w = 0; w < dst.nwords; ++w) dst.vis[(long long)w * dst.N + lin] = 0ull;
+        return;
+    }
+    const float g0[3] = { src.gx[pl], src.gy[pl], src.gz[pl] };
+    float g[3];
+    normalized3(g0, g);
+    const float a = (i & 1) ? g[0] : -g[0], b = (j & 1) ? g[1] : -g[1], c = (k & 1) ? g[2] : -g[2];
+    dst.dist[lin] = pd + vs4 * ((a + b) + c);
+    dst.gx[lin] = g0[0]; dst.gy[lin] = g0[1]; dst.gz[lin] = g0[2];
+    dst.w[lin] = src.w[pl]; dst.r[lin] = src.r[pl]; dst.g[lin] = src.g[pl]; dst.b[lin] = src.b[pl];
+    for (int w = 0; w < dst.nwords; ++w) dst.vis[(long long)w * dst.N + lin] = src.vis[(long long)w * src.N + pl];
+}
+
+void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
+    psg_volume* vol = o->vol;
+    const VolView v = vol->view();
+    SelectParams P;
+    P.F = o->F;
+    for (int k = 0; k < o->F; ++k) P.frame_idx[k] = o->frame_idx[k];
+    P.thr = sqrt(3.0) * (double)o->vs;
+
+    const long long nw = (v.N + 31) / 32;
+    // words per block: at least 32 (1024 voxels), grown so that the single-block scan sees <= 16384 counts
+    long long wpb = 32;
+    while ((nw + wpb - 1) / wpb > 16384) wpb *= 2;
+    const int nblocks = (int)((nw + wpb - 1) / wpb);
+    o->mask.alloc((size_t)nw);
+    o->prefix.alloc((size_t)nw);
+    o->block_counts.alloc((size_t)nblocks + 1);
+
+    k_surface_mask<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, nw, (int)wpb);
+    PSG_LAUNCH_CHECK();
+    k_scan_counts<<<1, 1024, 0, o->stream>>>(o->block_counts.p, nblocks);
+    PSG_LAUNCH_CHECK();
+    count_launch(2);
+    unsigned total = 0;
+    PSG_CUDA(cudaMemcpyAsync(&total, o->block_counts.p + nblocks, sizeof(unsigned), cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    o->S = (int)total;
+    const size_t S = (size_t)(o->S > 0 ? o->S : 1);
+    o->lin.alloc(S); o->svis.alloc(S); o->nbr_lin.alloc(3 * S); o->nbr_row.alloc(3 * S); o->pos.alloc(S); o->inc.alloc(6 * S);
+    if (o->S > 0) {
+        k_surface_scatter<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->prefix.p, nw, (int)wpb,
+                                                          o->lin.p, o->svis.p);
+        PSG_LAUNCH_CHECK();
+        k_neighbors<<<(o->S + 255) / 256, 256, 0, o->stream>>>(v, o->mask.p, o->prefix.p, o->lin.p, o->S, o->nbr_lin.p,
+                                                               o->nbr_row.p, o->pos.p, o->inc.p);
+        PSG_LAUNCH_CHECK();
+        count_launch(2);
+    }
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+}
+
+void launch_upsample(psg_optimizer* o) {
+    psg_volume* vol = o->vol;
+    const VolView src = vol->view();
+    psg_volume nv_store;   // temporary owner of the new planes
+    DevBuf<float> nf[8];
+    DevBuf<unsigned long long> nvis;
+    const long long N8 = 8 * vol->N;
+    for (int a = 0; a < 8; ++a) nf[a].alloc((size_t)N8);
+    nvis.alloc((size_t)N8 * vol->nwords);
+    VolView dst = src;
+    for (int a = 0; a < 3; ++a) dst.dims[a] = 2 * src.dims[a];
+    dst.N = N8;
+    dst.dist = nf[0].p; dst.gx = nf[1].p; dst.gy = nf[2].p; dst.gz = nf[3].p;
+    dst.w = nf[4].p; dst.r = nf[5].p; dst.g = nf[6].p; dst.b = nf[7].p; dst.vis = nvis.p;
+    const float vs4 = (float)(0.25 * (double)vol->vs);
+    k_upsample<<<(unsigned)((N8 + 255) / 256), 256, 0, o->stream>>>(src, dst, vs4);
+    PSG_LAUNCH_CHECK();
+    count_launch();
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    for (int a = 0; a < 8; ++a) { vol->f[a].release(); vol->f[a] = nf[a]; nf[a].p = nullptr; }
+    vol->vis.release(); vol->vis = nvis; nvis.p = nullptr;
+    // VoxelGrid::grid_subsample (VoxelGrid.h:143-149)
+    vol->vs = (float)((double)vol->vs * 0.5);
+    for (int a = 0; a < 3; ++a) vol->dims[a] *= 2;
+    vol->N = N8;
+    const float half_vs = (float)(0.5 * (double)vol->vs);
+    for (int a = 0; a < 3; ++a) vol->origin[a] = (vol->shift[a] - half_vs * (float)vol->dims[a]) - half_vs * 1.f;
+    // Optimizer: voxel_size_ *= 0.5; voxel_size_inv_ = 1.0 / voxel_size_ (OptimizerAux.cpp:679-680)
+    o->vs = (float)((double)o->vs * 0.5);
+    o->vs_inv = (float)(1.0 / (double)o->vs);
+    (void)nv_store;
+}
+
+}  // namespace psg

@@ -1,0 +1,840 @@
+// The per-(surface voxel, keyframe) photometric sweep: projection, bilinear sampling, shading, robust loss and the
+// Jacobian contribution of the active block, plus the reductions that turn them into normal equations.
+//
+// One kernel template, k_sweep<MODEL, MODE>.  A thread owns one surface voxel (its record lives in registers for
+// the whole sweep); the block walks the keyframes any of its voxels sees, in ascending order, all lanes on the
+// same keyframe (uniform pose / light, gathers into one image).  Per-voxel sums (albedo, distance stencil) are
+// therefore formed in the reference's own order (ascending keyframe, then channel).  Per-keyframe sums (light,
+// pose) are reduced with a warp butterfly reduce-scatter, then per-warp shared-memory slices, then one
+// double-precision atomic per block and entry.
+//
+// Reference functions covered: Optimizer::getIntensity + interpolateImage + computeImageGradient
+// (OptimizerAux.cpp:207-231, Auxilary.h:41-123), {Ps,Led}Optimizer::renderedIntensity, computeResidual,
+// getPSEnergy, rhoJacobian/albedoJacobian, lightJacobian, poseJacobian, distJacobian
+// (PsOptimizerJa.cpp, LedOptimizerJa.cpp), Optimizer::computeDistGrad / normalJacobian / distRegJacobian /
+// computeDistLaplacian / distLaplacianJacobian (Optimizer.cpp), Optimizer::initAlbedo (Optimizer.cpp:50-81),
+// LedOptimizer::computeLightIntensive (LedOptimizer.cpp:76-112), Optimizer::updateAlbedo (OptimizerAux.cpp:120-150).
+#include "psg_host.h"
+
+namespace psg {
+
+enum Mode { M_ENERGY = 0, M_INIT_ALBEDO, M_LED_INIT, M_PROBE, M_ALBEDO, M_LIGHT, M_POSE, M_DIST };
+
+constexpr int kBlock = 128;
+constexpr int kWarps = kBlock / 32;
+
+struct SweepArgs {
+    VolView vol;
+    SurfView surf;
+    Camera cam;
+    LossParams loss;
+    const FrameParams* frames;
+    const float4* images;
+    int F;
+    float vs_inv;
+    float led[3];
+    float damping, reg_n, reg_l;
+    int flags;
+    double* red;        // reductions (zeroed by the launcher)
+    float* out0;        // mode dependent per-voxel outputs
+    float* out1;
+    // probe outputs
+    float* pm; float* pn; unsigned char* pok; float* pI; float* prend; float* pr; float* pw;
+};
+
+struct Footprint { int x, y; float4 t00, t01, t10, t11; };
+
+__device__ __forceinline__ const float4* texel_ptr(const SweepArgs& A, int f, int row, int col) {
+    return A.images + ((long long)f * A.cam.H + row) * A.cam.W + col;
+}
+
+// interpolateImage (Auxilary.h:41-61) called as interpolateImage(row = n, col = m): weights partly double, each
+// weight * texel rounded to float, four float adds left to right; nearest texel in the last row / column.
+__device__ __forceinline__ void sample_image(const SweepArgs& A, int f, float rowf, float colf, Footprint& fp, float* rgb) {
+    const int x = (int)floorf(rowf), y = (int)floorf(colf);
+    fp.x = x; fp.y = y;
+    float bgr[3];
+    if (x + 1 < A.cam.H && y + 1 < A.cam.W) {
+        const float4* p0 = texel_ptr(A, f, x, y);
+        const float4* p1 = p0 + A.cam.W;
+        fp.t00 = __ldg(p0); fp.t01 = __ldg(p0 + 1); fp.t10 = __ldg(p1); fp.t11 = __ldg(p1 + 1);
+        const double wy1 = (double)y + 1.0 - (double)colf;
+        const double wx1 = (double)x + 1.0 - (double)rowf;
+        const float fx_ = rowf - (float)x;
+        const float fy_ = colf - (float)y;
+        const double a1 = wy1 * (double)fx_;
+        const double a2 = wy1 * wx1;
+        const float a3 = fy_ * fx_;
+        const double a4 = (double)fy_ * wx1;
+        const float c10[3] = { fp.t10.x, fp.t10.y, fp.t10.z }, c00[3] = { fp.t00.x, fp.t00.y, fp.t00.z };
+        const float c11[3] = { fp.t11.x, fp.t11.y, fp.t11.z }, c01[3] = { fp.t01.x, fp.t01.y, fp.t01.z };
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float s = (float)((double)c10[c] * a1) + (float)((double)c00[c] * a2);
+            s = s + c11[c] * a3;
+            s = s + (float)((double)c01[c] * a4);
+            bgr[c] = s;
+        }
+    } else {
+        fp.t00 = __ldg(texel_ptr(A, f, x, y));
+        fp.t01 = fp.t00; fp.t10 = fp.t00; fp.t11 = fp.t00;
+        bgr[0] = fp.t00.x; bgr[1] = fp.t00.y; bgr[2] = fp.t00.z;
+    }
+    rgb[0] = bgr[2]; rgb[1] = bgr[1]; rgb[2] = bgr[0];
+}
+
+__device__ __forceinline__ void sub_bgr(const float4& a, const float4& b, float* o) { o[0] = a.x - b.x; o[1] = a.y - b.y; o[2] = a.z - b.z; }
+__device__ __forceinline__ void negadd_bgr(const float4& a, const float4& b, float* o) { o[0] = -a.x + b.x; o[1] = -a.y + b.y; o[2] = -a.z + b.z; }
+
+// computeImageGradient (Auxilary.h:64-123), both directions at once: g0 = along columns, g1 = along rows (RGB).
+// `fp` holds the 2x2 footprint at (x, y) when it is interior.  The reference's reads one element past the image at
+// the bottom-right corner cell are clamped to the centre texel.
+__device__ __forceinline__ void image_gradient(const SweepArgs& A, int f, float rowf, float colf, const Footprint& fp,
+                                               float* g0, float* g1) {
+    const int x = fp.x, y = fp.y, H = A.cam.H, W = A.cam.W;
+    const float w01 = rowf - (float)x, w11 = colf - (float)y;
+    const float w00 = (float)(1.0 - (double)w01), w10 = (float)(1.0 - (double)w11);
+    float v0[3], v1[3];
+    if (x + 1 < H && y + 1 < W) {
+        sub_bgr(fp.t01, fp.t00, v0); sub_bgr(fp.t11, fp.t10, v1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g0[c] = w00 * v0[2 - c] + w01 * v1[2 - c];
+        sub_bgr(fp.t10, fp.t00, v0); sub_bgr(fp.t11, fp.t01, v1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g1[c] = w10 * v0[2 - c] + w11 * v1[2 - c];
+        return;
+    }
+    const float4 c00 = __ldg(texel_ptr(A, f, x, y));
+    // direction 0
+    if (x + 1 >= H) {
+        const float4 c01 = (y + 1 < W) ? __ldg(texel_ptr(A, f, x, y + 1)) : c00;
+        sub_bgr(c01, c00, v0);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g0[c] = v0[2 - c];
+    } else {   // x + 1 < H && y + 1 >= W : backward differences
+        negadd_bgr(__ldg(texel_ptr(A, f, x, y - 1)), c00, v0);
+        negadd_bgr(__ldg(texel_ptr(A, f, x + 1, y - 1)), __ldg(texel_ptr(A, f, x + 1, y)), v1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g0[c] = w00 * v0[2 - c] + w01 * v1[2 - c];
+    }
+    // direction 1
+    if (x + 1 >= H && y + 1 < W) {
+        negadd_bgr(__ldg(texel_ptr(A, f, x - 1, y)), c00, v0);
+        negadd_bgr(__ldg(texel_ptr(A, f, x - 1, y + 1)), __ldg(texel_ptr(A, f, x, y + 1)), v1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g1[c] = w10 * v0[2 - c] + w11 * v1[2 - c];
+    } else {   // y + 1 >= W
+        const float4 c10 = (x + 1 < H) ? __ldg(texel_ptr(A, f, x + 1, y)) : c00;
+        sub_bgr(c10, c00, v0);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g1[c] = v0[2 - c];
+    }
+}
+
+// Optimizer::normalJacobian(grad, direction, lag = false) (Optimizer.cpp:269-284)
+__device__ __forceinline__ void normal_jacobian(float vs_inv, const float* grad, const float* direction, float* Jn) {
+    float nd[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) nd[a] = -vs_inv * direction[a];
+    const float N_inv = (float)(1.0 / (double)fmaxf(norm3(grad), 0.001f));
+    const float dN = (float)(cube_d(N_inv) * (double)dot3(nd, grad));
+#pragma unroll
+    for (int a = 0; a < 3; ++a) Jn[a] = N_inv * nd[a] - dN * grad[a];
+}
+
+// V values per lane -> per-warp shared slice, lane l adds the warp sum of value l.
+template <int V>
+__device__ __forceinline__ void warp_accumulate(float* vals, int lane, float* slice /* >= V floats */) {
+    if (V <= 32) {
+        const float s = warp_reduce_scatter<V>(vals, lane);
+        if (lane < V) slice[lane] += s;
+    }
+}
+
+template <int MODEL, int MODE>
+__global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
+    constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
+    constexpr bool LED = (MODEL == PSG_MODEL_LED);
+    // per-frame reduction width (padded to a multiple of 32 lanes / power of two)
+    constexpr int VLIGHT = LED ? 0 : (NB == 4 ? 16 : 64);
+    constexpr int VRED = (MODE == M_POSE) ? 32 : ((MODE == M_LIGHT) ? VLIGHT : 0);
+
+    extern __shared__ float s_dyn[];
+    __shared__ FrameParams s_frames[kMaxFrames];
+    __shared__ unsigned long long s_or[kWarps];
+    __shared__ double s_red[kWarps][8];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = A.surf.S;
+    const int s = blockIdx.x * kBlock + tid;
+    const bool live = s < S;
+
+    // stage per-keyframe parameters
+    {
+        const float* src = reinterpret_cast<const float*>(A.frames);
+        float* dst = reinterpret_cast<float*>(s_frames);
+        const int nfl = A.F * (int)(sizeof(FrameParams) / sizeof(float));
+        for (int i = tid; i < nfl; i += kBlock) dst[i] = src[i];
+    }
+    if constexpr (VRED > 0) {
+        const int n = kWarps * A.F * VRED;
+        for (int i = tid; i < n; i += kBlock) s_dyn[i] = 0.f;
+    }
+
+    // ---- voxel record
+    int lin = 0, idx[3] = {0, 0, 0};
+    unsigned long long vis = 0ull;
+    float dist = 0.f, g[3] = {0, 0, 0}, gh[3] = {0, 0, 0}, rho[3] = {0, 0, 0}, q0[3] = {0, 0, 0};
+    float fd[3] = {0, 0, 0}, posf[3] = {1, 1, 1}, nfd[3] = {0, 0, 0};
+    if (live) {
+        lin = A.surf.lin[s];
+        vis = A.surf.vis[s];
+        line2idx(lin, A.vol.dims, idx);
+        dist = A.vol.dist[lin];
+        g[0] = A.vol.gx[lin]; g[1] = A.vol.gy[lin]; g[2] = A.vol.gz[lin];
+        rho[0] = A.vol.r[lin]; rho[1] = A.vol.g[lin]; rho[2] = A.vol.b[lin];
+        normalized3(g, gh);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) q0[a] = (A.vol.origin[a] + A.vol.vs * (float)idx[a]) - dist * gh[a];
+        // Optimizer::computeDistGrad (Optimizer.cpp:287-364)
+        const unsigned char pb = A.surf.pos[s];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int nl = A.surf.nbr_lin[a * S + s];
+            posf[a] = ((pb >> a) & 1) ? 1.f : -1.f;
+            const float dn = nl >= 0 ? A.vol.dist[nl] : dist;
+            fd[a] = (posf[a] * (dn - dist)) * A.vs_inv;
+        }
+        normalized3(fd, nfd);
+    }
+    float sh_n[NB];   // SH basis at the finite-difference normal (shading in the residual)
+    float sh_g[NB];   // SH basis at the stored gradient (albedo / light Jacobians)
+    sh_eval<NB>(nfd, sh_n);
+    sh_eval<NB>(gh, sh_g);
+
+    // ---- block-wide union of visibility
+    {
+        unsigned lo = (unsigned)vis, hi = (unsigned)(vis >> 32);
+        lo = __reduce_or_sync(0xffffffffu, lo);
+        hi = __reduce_or_sync(0xffffffffu, hi);
+        if (lane == 0) s_or[warp] = ((unsigned long long)hi << 32) | lo;
+    }
+    __syncthreads();
+    unsigned long long uni = 0ull;
+#pragma unroll
+    for (int i = 0; i < kWarps; ++i) uni |= s_or[i];
+    const unsigned long long warp_uni = s_or[warp];
+
+    // ---- mode-specific per-voxel state
+    double acc_d[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // ENERGY: [0] loss; LED_INIT: I[3], rend[3]; LED light: H[3], b[3]
+    long long cnt = 0;
+    float vacc[14];                               // ALBEDO: H[3], b[3]; INIT_ALBEDO: sum[3]; DIST: A(10) + b(4)
+#pragma unroll
+    for (int i = 0; i < 14; ++i) vacc[i] = 0.f;
+    int icount = 0;
+
+    // DIST: frame independent parts of distJacobian (PsOptimizerJa.cpp:194-221)
+    float dn[4][3], dx[4][3];
+    int cols[4] = { s, -1, -1, -1 };
+    if constexpr (MODE == M_DIST) {
+        if (live) {
+            normal_jacobian(A.vs_inv, fd, posf, dn[0]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                float dir[3] = {0.f, 0.f, 0.f};
+                dir[k] = LED ? (0.f + posf[k]) : (0.f - posf[k]);   // LedOptimizerJa.cpp:158 "+=" vs PsOptimizerJa.cpp:201 "-="
+                normal_jacobian(A.vs_inv, fd, dir, dn[k + 1]);
+                cols[k + 1] = A.surf.nbr_row[k * S + s];
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) dx[0][a] = -gh[a] - dist * dn[0][a];
+#pragma unroll
+            for (int k = 1; k < 4; ++k)
+#pragma unroll
+                for (int a = 0; a < 3; ++a) dx[k][a] = -dist * dn[k][a];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { dn[k][a] = 0.f; dx[k][a] = 0.f; }
+        }
+    }
+
+    const float fx = A.cam.fx, fy = A.cam.fy, cx = A.cam.cx, cy = A.cam.cy;
+
+    // ---- keyframe loop (ascending, uniform across the block)
+    while (uni) {
+        const int f = __ffsll((long long)uni) - 1;
+        uni &= uni - 1;
+        if constexpr (VRED > 0) { if (!((warp_uni >> f) & 1ull)) continue; }   // warp-uniform: nothing to reduce for this warp
+        const FrameParams& P = s_frames[f];
+        const bool act = live && ((vis >> f) & 1ull);
+
+        bool ok = false;
+        float pt[3] = {0, 0, 1}, I[3] = {0, 0, 0}, rend[3] = {0, 0, 0}, r[3] = {0, 0, 0}, w[3] = {0, 0, 0};
+        float m = 0.f, n = 0.f;
+        Footprint fp; fp.x = 0; fp.y = 0;
+        if (act) {
+            const float q[3] = { q0[0] - P.t[0], q0[1] - P.t[1], q0[2] - P.t[2] };
+            matT_vec(P.R, q, pt);
+            const float z_inv = (float)(1.0 / (double)pt[2]);
+            m = fx * pt[0] * z_inv + cx;
+            n = fy * pt[1] * z_inv + cy;
+            ok = !(m < 0.f || m >= (float)A.cam.W || n < 0.f || n >= (float)A.cam.H) && (m == m) && (n == n);
+            if (ok) {
+                sample_image(A, f, n, m, fp, I);
+                float irr;
+                if constexpr (LED) {   // LedOptimizerJa.cpp:15-29
+                    float nR[3];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) nR[a] = sum3((-nfd[0]) * P.R[a], (-nfd[1]) * P.R[3 + a], (-nfd[2]) * P.R[6 + a]);
+                    irr = dot3(nR, pt);
+                    irr /= (float)cube_d(norm3(pt));
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) rend[c] = rho[c] * A.led[c] * irr;
+                } else {     // PsOptimizerJa.cpp:30-40
+                    irr = dot_sh<NB>(P.light, sh_n);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) rend[c] = rho[c] * irr;
+                }
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { r[c] = I[c] - rend[c]; w[c] = irls_weight(A.loss, r[c]); }
+            }
+        }
+
+        if constexpr (MODE == M_ENERGY) {
+            if (ok) { acc_d[0] += (double)robust_loss3(A.loss, r); ++cnt; }
+        } else if constexpr (MODE == M_INIT_ALBEDO) {
+            if (ok) { vacc[0] += I[0]; vacc[1] += I[1]; vacc[2] += I[2]; ++icount; }
+        } else if constexpr (MODE == M_LED_INIT) {
+            if (ok) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { acc_d[c] += (double)I[c]; acc_d[3 + c] += (double)rend[c]; }
+            }
+        } else if constexpr (MODE == M_PROBE) {
+            if (act) {
+                const long long k = (long long)s * A.F + f;
+                A.pm[k] = m; A.pn[k] = n; A.pok[k] = ok ? 1 : 0;
+                if (ok) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) { A.pI[3 * k + c] = I[c]; A.prend[3 * k + c] = rend[c]; A.pr[3 * k + c] = r[c]; A.pw[3 * k + c] = w[c]; }
+                }
+            }
+        } else if constexpr (MODE == M_ALBEDO) {
+            if (ok) {
+                float Jr[3];
+                if constexpr (LED) {   // LedOptimizerJa.cpp:85-99
+                    float gR[3];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) gR[a] = sum3(gh[0] * P.R[a], gh[1] * P.R[3 + a], gh[2] * P.R[6 + a]);
+                    float refl = dot3(gR, pt);
+                    refl /= (float)cube_d(norm3(pt));
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) Jr[c] = refl * A.led[c];
+                } else {     // PsOptimizerJa.cpp:118-122
+                    const float j = -dot_sh<NB>(P.light, sh_g);
+                    Jr[0] = j; Jr[1] = j; Jr[2] = j;
+                }
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { vacc[c] += (Jr[c] * w[c]) * Jr[c]; vacc[3 + c] += (Jr[c] * w[c]) * r[c]; }
+            }
+        } else if constexpr (MODE == M_LIGHT) {
+            if constexpr (LED) {       // LedOptimizerJa.cpp:101-115: one global 3-vector, diagonal system
+                if (ok) {
+                    float gR[3];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) gR[a] = sum3(gh[0] * P.R[a], gh[1] * P.R[3 + a], gh[2] * P.R[6 + a]);
+                    float refl = dot3(gR, pt);
+                    refl /= (float)cube_d(norm3(pt));
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const float j = refl * rho[c];
+                        acc_d[c] += (double)((j * w[c]) * j);
+                        acc_d[3 + c] += (double)((j * w[c]) * r[c]);
+                    }
+                }
+            } else {         // PsOptimizerJa.cpp:132-143: rows -rho_c * SH(g_hat), lower triangle + rhs
+                constexpr int NT = NB * (NB + 1) / 2;
+                float vals[VLIGHT > 0 ? VLIGHT : 1];
+#pragma unroll
+                for (int i = 0; i < VLIGHT; ++i) vals[i] = 0.f;
+                if (ok) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        float J[NB];
+#pragma unroll
+                        for (int i = 0; i < NB; ++i) J[i] = (-rho[c]) * sh_g[i];
+                        int t = 0;
+#pragma unroll
+                        for (int i = 0; i < NB; ++i) {
+                            const float jw = J[i] * w[c];
+#pragma unroll
+                            for (int k = 0; k <= i; ++k) { vals[t] += jw * J[k]; ++t; }
+                            vals[NT + i] += jw * r[c];
+                        }
+                    }
+                }
+                float* slice = s_dyn + ((long long)warp * A.F + f) * VRED;
+                if constexpr (VLIGHT == 16) {
+                    warp_accumulate<16>(vals, lane, slice);
+                } else {
+                    warp_accumulate<32>(vals, lane, slice);
+                    warp_accumulate<32>(vals + 32, lane, slice + 32);
+                }
+            }
+        } else if constexpr (MODE == M_POSE || MODE == M_DIST) {
+            // shared front part of poseJacobian / distJacobian: division-form projection and its own bounds test
+            bool okj = false;
+            float Aim[9];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) Aim[i] = 0.f;
+            if (ok) {
+                const float mj = fx * pt[0] / pt[2] + cx;
+                const float nj = fy * pt[1] / pt[2] + cy;
+                okj = !(mj < 0.f || mj >= (float)A.cam.W || nj < 0.f || nj >= (float)A.cam.H);
+                if (okj) {
+                    const int xj = (int)floorf(nj), yj = (int)floorf(mj);
+                    if (xj != fp.x || yj != fp.y) { float dummy[3]; sample_image(A, f, nj, mj, fp, dummy); }
+                    float g0[3], g1[3];
+                    image_gradient(A, f, nj, mj, fp, g0, g1);
+                    const float z_inv = (float)(1.0 / (double)pt[2]);
+                    const float z_inv_sq = z_inv * z_inv;
+                    const float pi[6] = { fx * z_inv, 0.f, -fx * pt[0] * z_inv_sq, 0.f, fy * z_inv, -fy * pt[1] * z_inv_sq };
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) Aim[3 * c + j] = g0[c] * pi[j] + g1[c] * pi[3 + j];
+                }
+            }
+            if constexpr (MODE == M_POSE) {
+                float vals[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) vals[i] = 0.f;
+                if (okj) {
+                    const float Sk[9] = { 0.f, -pt[2], pt[1], pt[2], 0.f, -pt[0], -pt[1], pt[0], 0.f };
+                    float J[3][6];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) {
+                            J[c][j] = sum3((-Aim[3 * c]) * P.R[3 * j], (-Aim[3 * c + 1]) * P.R[3 * j + 1], (-Aim[3 * c + 2]) * P.R[3 * j + 2]);
+                            J[c][3 + j] = sum3(Aim[3 * c] * Sk[j], Aim[3 * c + 1] * Sk[3 + j], Aim[3 * c + 2] * Sk[6 + j]);
+                        }
+                    if constexpr (LED) {   // LedOptimizerJa.cpp:63-78
+                        const float l3 = (float)cube_d(norm3(pt));
+                        const float l5 = (float)pow5_d(norm3(pt));
+                        float skp[3], nR[3];
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) skp[a] = sum3(Sk[3 * a] * pt[0], Sk[3 * a + 1] * pt[1], Sk[3 * a + 2] * pt[2]);
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) nR[a] = sum3(gh[0] * P.R[a], gh[1] * P.R[3 + a], gh[2] * P.R[6 + a]);
+                        const float nRp = dot3(nR, pt);
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            const float kt = -(rho[c] * A.led[c] / l3);
+                            const float kr = -3 * rho[c] * A.led[c] / l5 * nRp;
+#pragma unroll
+                            for (int j = 0; j < 3; ++j) { J[c][j] = J[c][j] + kt * gh[j]; J[c][3 + j] = J[c][3 + j] + kr * skp[j]; }
+                        }
+                    }
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        int t = 0;
+#pragma unroll
+                        for (int i = 0; i < 6; ++i) {
+                            const float jw = J[c][i] * w[c];
+#pragma unroll
+                            for (int k = 0; k <= i; ++k) { vals[t] += jw * J[c][k]; ++t; }
+                            vals[21 + i] += jw * r[c];
+                        }
+                    }
+                }
+                float* slice = s_dyn + ((long long)warp * A.F + f) * VRED;
+                warp_accumulate<32>(vals, lane, slice);
+            } else if (okj) {   // M_DIST
+                // M = A * R^T, dI_k = M * dx_k
+                float Mx[9];
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int j = 0; j < 3; ++j)
+                        Mx[3 * c + j] = sum3(Aim[3 * c] * P.R[3 * j], Aim[3 * c + 1] * P.R[3 * j + 1], Aim[3 * c + 2] * P.R[3 * j + 2]);
+                float Jd[4][3];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) mat_vec(Mx, dx[k], Jd[k]);   // dI_k for now
+                if constexpr (LED) {   // LedOptimizerJa.cpp:178-207
+                    float gR[3], pRt[3];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) gR[a] = sum3(nfd[0] * P.R[a], nfd[1] * P.R[3 + a], nfd[2] * P.R[6 + a]);
+                    const float gRp = dot3(gR, pt);
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) pRt[a] = sum3(pt[0] * P.R[3 * a], pt[1] * P.R[3 * a + 1], pt[2] * P.R[3 * a + 2]);
+                    const float radius = (float)cube_d(norm3(pt));
+                    const double r5 = pow5_d(norm3(pt));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float dR_[3];
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) dR_[a] = sum3(dn[k][0] * P.R[a], dn[k][1] * P.R[3 + a], dn[k][2] * P.R[6 + a]);
+                        float dm = dot3(dR_, pt) + dot3(nfd, dx[k]);
+                        const float dm2 = (float)((double)(-3 * dot3(pRt, dx[k])) / r5);
+                        dm = dm / radius + dm2 * gRp;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) Jd[k][c] = Jd[k][c] + (rho[c] * A.led[c]) * dm;
+                    }
+                } else if constexpr (NB == 4) {   // PsOptimizerJa.cpp:225-240
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            const float d0 = rho[c] * P.light[1], d1 = rho[c] * P.light[2], d2 = rho[c] * P.light[3];
+                            Jd[k][c] = Jd[k][c] - sum3(d0 * dn[k][0], d1 * dn[k][1], d2 * dn[k][2]);
+                        }
+                } else {                // PsOptimizerJa.cpp:242-278
+                    const float D[27] = { 0, 1, 0, 0, nfd[1], nfd[2], 0, 2 * nfd[0], 2 * nfd[0],
+                                          0, 0, 1, 0, nfd[0], 0, nfd[2], -2 * nfd[1], 0,
+                                          0, 0, 0, 1, 0, nfd[0], nfd[1], 0, -2 * nfd[2] };
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float dsh[9];
+#pragma unroll
+                        for (int i = 0; i < 9; ++i) dsh[i] = sum3(D[i] * dn[k][0], D[9 + i] * dn[k][1], D[18 + i] * dn[k][2]);
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            float a[9];
+#pragma unroll
+                            for (int i = 0; i < 9; ++i) a[i] = (rho[c] * P.light[i]) * dsh[i];
+                            const float sdot = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + (a[7] + a[8])));
+                            Jd[k][c] = Jd[k][c] - sdot;
+                        }
+                    }
+                }
+                // stencil normal equations, lower triangle in slot order: (0,0),(1,0),(1,1),(2,0)...(3,3), then b[4]
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    int t = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float jw = Jd[i][c] * w[c];
+#pragma unroll
+                        for (int k = 0; k <= i; ++k) { if (cols[i] >= 0 && cols[k] >= 0) vacc[t] += jw * Jd[k][c]; ++t; }
+                        if (cols[i] >= 0) vacc[10 + i] += jw * r[c];
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- epilogues
+    if constexpr (MODE == M_ENERGY || MODE == M_LED_INIT || (MODE == M_LIGHT && LED)) {
+        constexpr int ND = (MODE == M_ENERGY) ? 1 : 6;
+#pragma unroll
+        for (int i = 0; i < ND; ++i) { const double v = warp_sum(acc_d[i]); if (lane == 0) s_red[warp][i] = v; }
+        const long long c2 = warp_sum_ll(cnt);
+        if (lane == 0) s_red[warp][7] = (double)c2;
+        __syncthreads();
+        if (tid < ND) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < kWarps; ++i) v += s_red[i][tid];
+            atomicAdd(&A.red[tid], v);
+        }
+        if (tid == 7) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < kWarps; ++i) v += s_red[i][7];
+            atomicAdd(&A.red[7], v);
+        }
+    }
+    if constexpr (MODE == M_INIT_ALBEDO) {
+        if (live && icount) {
+            A.vol.r[lin] = vacc[0] / (float)icount;
+            A.vol.g[lin] = vacc[1] / (float)icount;
+            A.vol.b[lin] = vacc[2] / (float)icount;
+        }
+    }
+    if constexpr (MODE == M_ALBEDO) {
+        // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
+        // Optimizer::updateAlbedo gate (OptimizerAux.cpp:120-147): accept a channel only if it stays strictly in (0, 1)
+        int accepted = 0;
+        if (live) {
+            float* chan[3] = { A.vol.r, A.vol.g, A.vol.b };
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float Hd = vacc[c];
+                if (A.damping != 0.f) Hd = Hd + A.damping * Hd;
+                const float inv = (Hd != 0.f) ? 1.f / Hd : 1.f;
+                const float delta = inv * vacc[3 + c];
+                const float nv = rho[c] - delta;
+                if ((double)nv > 0.0 && (double)nv < 1.0) { chan[c][lin] = nv; ++accepted; }
+                if (A.out0) { A.out0[3 * (long long)s + c] = vacc[3 + c]; A.out1[3 * (long long)s + c] = delta; }
+            }
+        }
+        const long long c2 = warp_sum_ll(accepted);
+        if (lane == 0) s_red[warp][0] = (double)c2;
+        __syncthreads();
+        if (tid == 0) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < kWarps; ++i) v += s_red[i][0];
+            atomicAdd(&A.red[0], v);
+        }
+    }
+    if constexpr (VRED > 0) {
+        __syncthreads();
+        const int n = A.F * VRED;
+        for (int i = tid; i < n; i += kBlock) {
+            double v = 0.0;
+#pragma unroll
+            for (int wv = 0; wv < kWarps; ++wv) v += (double)s_dyn[(long long)wv * n + i];
+            if (v != 0.0) atomicAdd(&A.red[i], v);
+        }
+    }
+    if constexpr (MODE == M_DIST) {
+        if (live) {
+            // Eikonal rows (Optimizer.cpp:196-218, 477-537), scaled by reg_weight_n (PsOptimizer.cpp:136-142)
+            if (A.flags & PSG_REG_NORMAL) {
+                float nd[3], Jr[4];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) nd[a] = -A.vs_inv * posf[a];
+                Jr[0] = dot3(fd, nd);
+#pragma unroll
+                for (int a = 0; a < 3; ++a) Jr[a + 1] = fd[a] * (0.f + A.vs_inv * posf[a]);
+                const float gn = norm3(fd);
+                if (gn > 0.f) {
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) Jr[a] /= gn;
+                }
+                const float rr = gn - 1;
+                int t = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+#pragma unroll
+                    for (int k = 0; k <= i; ++k) { if (cols[i] >= 0 && cols[k] >= 0) vacc[t] += A.reg_n * (Jr[i] * Jr[k]); ++t; }
+                    if (cols[i] >= 0) vacc[10 + i] += A.reg_n * (Jr[i] * rr);
+                }
+            }
+            // Laplacian: only the diagonal entry reaches the matrix (Optimizer.cpp:540-590; PsOptimizer.cpp:144-150)
+            if (A.flags & PSG_REG_LAPLACIAN) {
+                const long long stride[3] = { 1, A.vol.dims[0], (long long)A.vol.dims[0] * A.vol.dims[1] };
+                float dd[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+                    const float d1 = (l1 < A.vol.N) ? A.vol.dist[l1] : dist;
+                    const float d0 = (l0 >= 0) ? A.vol.dist[l0] : dist;
+                    dd[a] = d1 + d0 - 2 * dist;
+                }
+                const float lap = (dd[0] + dd[1] + dd[2]) * A.vs_inv * A.vs_inv;
+                const float jd = -6 * (A.vs_inv * A.vs_inv);
+                vacc[0] += A.reg_l * (jd * jd);
+                vacc[10] += A.reg_l * (jd * lap);
+            }
+#pragma unroll
+            for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ launchers
+static SweepArgs base_args(psg_optimizer* o) {
+    upload_frames(o);   // (re)allocates o->frames on first use, so it must precede the pointer capture below
+    SweepArgs A;
+    memset(&A, 0, sizeof(A));
+    A.vol = o->vol->view();
+    A.surf.S = o->S; A.surf.lin = o->lin.p; A.surf.vis = o->svis.p; A.surf.nbr_lin = o->nbr_lin.p;
+    A.surf.nbr_row = o->nbr_row.p; A.surf.pos = o->pos.p;
+    A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
+    A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
+    A.frames = o->frames.p; A.images = o->images.p; A.F = o->F;
+    A.vs_inv = o->vs_inv;
+    if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
+    A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
+    o->red.alloc(kMaxFrames * 64 + 8);
+    A.red = o->red.p;
+    return A;
+}
+
+void upload_frames(psg_optimizer* o) {
+    if (!o->frames_dirty) return;
+    std::vector<FrameParams> fr((size_t)(o->F > 0 ? o->F : 1));
+    memset(fr.data(), 0, fr.size() * sizeof(FrameParams));
+    for (int f = 0; f < o->F; ++f) {
+        const float* P = o->poses.data() + 16 * f;
+        for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
+        if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
+    }
+    o->frames.alloc(fr.size());
+    PSG_CUDA(cudaMemcpyAsync(o->frames.p, fr.data(), fr.size() * sizeof(FrameParams), cudaMemcpyHostToDevice, o->stream));
+    PSG_CUDA(cudaStreamSynchronize(o->stream));   // fr is a temporary
+    o->frames_dirty = false;
+}
+
+template <int MODE>
+static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
+    if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
+    if (o->S == 0) return;
+    const int grid = (o->S + kBlock - 1) / kBlock;
+#define PSG_SWEEP_CASE(MODEL)                                                                                          \
+    case MODEL: {                                                                                                      \
+        if (dyn_smem > 48 * 1024)                                                                                      \
+            PSG_CUDA(cudaFuncSetAttribute(k_sweep<MODEL, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem)); \
+        k_sweep<MODEL, MODE><<<grid, kBlock, dyn_smem, o->stream>>>(A);                                                \
+    } break;
+    switch (o->set.model) {
+        PSG_SWEEP_CASE(PSG_MODEL_SH1)
+        PSG_SWEEP_CASE(PSG_MODEL_SH2)
+        PSG_SWEEP_CASE(PSG_MODEL_LED)
+        default: set_error("unknown model %d", o->set.model); throw CudaError{-1};
+    }
+#undef PSG_SWEEP_CASE
+    count_launch();
+    PSG_LAUNCH_CHECK();
+}
+
+static void fetch_red(psg_optimizer* o, double* dst, size_t n) {
+    PSG_CUDA(cudaMemcpyAsync(dst, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+}
+
+void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
+    SweepArgs A = base_args(o);
+    launch_sweep<M_ENERGY>(o, A, 8, 0);
+    double r[8];
+    fetch_red(o, r, 8);
+    *E_sum = r[0];
+    *n_active = (long long)(r[7] + 0.5);
+}
+
+void sweep_init_albedo(psg_optimizer* o) {
+    SweepArgs A = base_args(o);
+    launch_sweep<M_INIT_ALBEDO>(o, A, 0, 0);
+}
+
+void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
+    SweepArgs A = base_args(o);
+    launch_sweep<M_LED_INIT>(o, A, 8, 0);
+    double r[8];
+    fetch_red(o, r, 8);
+    for (int i = 0; i < 6; ++i) sums[i] = r[i];
+}
+
+void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
+    SweepArgs A = base_args(o);
+    A.pm = m; A.pn = n; A.pok = ok; A.pI = I3; A.prend = rend3; A.pr = r3; A.pw = w3;
+    launch_sweep<M_PROBE>(o, A, 0, 0);
+}
+
+void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b_dev, float* delta_dev) {
+    SweepArgs A = base_args(o);
+    A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
+    launch_sweep<M_ALBEDO>(o, A, 8, 0);
+    double r[8];
+    fetch_red(o, r, 8);
+    *accepted = (long long)(r[0] + 0.5);
+}
+
+// light / pose: returns per-keyframe lower triangles + rhs as accumulated on the device (doubles).
+void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, std::vector<double>& bout) {
+    SweepArgs A = base_args(o);
+    const bool led = o->set.model == PSG_MODEL_LED;
+    if (block == PSG_BLOCK_LIGHT && led) {
+        launch_sweep<M_LIGHT>(o, A, 8, 0);
+        double r[8];
+        fetch_red(o, r, 8);
+        Hout.assign(9, 0.0); bout.assign(3, 0.0);
+        for (int c = 0; c < 3; ++c) { Hout[4 * c] = r[c]; bout[c] = r[3 + c]; }
+        return;
+    }
+    const int nbk = block == PSG_BLOCK_POSE ? 6 : o->nb;
+    const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
+    const int NT = nbk * (nbk + 1) / 2;
+    const size_t nred = (size_t)o->F * V;
+    const size_t smem = (size_t)kWarps * o->F * V * sizeof(float);
+    if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, smem);
+    else launch_sweep<M_LIGHT>(o, A, nred, smem);
+    std::vector<double> r(nred);
+    fetch_red(o, r.data(), nred);
+    Hout.assign((size_t)o->F * nbk * nbk, 0.0);
+    bout.assign((size_t)o->F * nbk, 0.0);
+    for (int f = 0; f < o->F; ++f) {
+        const double* v = r.data() + (size_t)f * V;
+        int t = 0;
+        for (int i = 0; i < nbk; ++i) {
+            for (int k = 0; k <= i; ++k) {
+                Hout[(size_t)f * nbk * nbk + i * nbk + k] = v[t];
+                Hout[(size_t)f * nbk * nbk + k * nbk + i] = v[t];
+                ++t;
+            }
+            bout[(size_t)f * nbk + i] = v[NT + i];
+        }
+    }
+}
+
+void sweep_dist(psg_optimizer* o, int flags) {
+    SweepArgs A = base_args(o);
+    A.flags = flags;
+    o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
+    A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
+    launch_sweep<M_DIST>(o, A, 0, 0);
+}
+
+// ---- regulariser energies (Optimizer.cpp:86-136) -------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_reg_energy(VolView vol, SurfView surf, float vs_inv, double* red) {
+    __shared__ double s_red[kWarps][3];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = surf.S;
+    const int s = blockIdx.x * kBlock + tid;
+    double en = 0.0, el = 0.0, er = 0.0;
+    if (s < S) {
+        const int lin = surf.lin[s];
+        const float dist = vol.dist[lin];
+        const float rho[3] = { vol.r[lin], vol.g[lin], vol.b[lin] };
+        const unsigned char pb = surf.pos[s];
+        const long long stride[3] = { 1, vol.dims[0], (long long)vol.dims[0] * vol.dims[1] };
+        float fd[3], dd[3], G[9];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int nl = surf.nbr_lin[a * S + s];
+            const float p = ((pb >> a) & 1) ? 1.f : -1.f;
+            const float dn = nl >= 0 ? vol.dist[nl] : dist;
+            fd[a] = (p * (dn - dist)) * vs_inv;
+            const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+            const float d1 = (l1 < vol.N) ? vol.dist[l1] : dist;
+            const float d0 = (l0 >= 0) ? vol.dist[l0] : dist;
+            dd[a] = d1 + d0 - 2 * dist;
+            // Optimizer::computeAlbedoGrad (Optimizer.cpp:396-460)
+            const float nr = nl >= 0 ? vol.r[nl] : rho[0], ng = nl >= 0 ? vol.g[nl] : rho[1], nbb = nl >= 0 ? vol.b[nl] : rho[2];
+            G[a] = (p * (nr - rho[0])) * vs_inv; G[3 + a] = (p * (ng - rho[1])) * vs_inv; G[6 + a] = (p * (nbb - rho[2])) * vs_inv;
+        }
+        const float e = norm3(fd) - 1;
+        en = (double)(e * e);
+        const float lap = (dd[0] + dd[1] + dd[2]) * vs_inv * vs_inv;
+        el = (double)(lap * lap);
+        er = (double)((norm3(G) + norm3(G + 3)) + norm3(G + 6));
+    }
+    en = warp_sum(en); el = warp_sum(el); er = warp_sum(er);
+    if (lane == 0) { s_red[warp][0] = en; s_red[warp][1] = el; s_red[warp][2] = er; }
+    __syncthreads();
+    if (tid < 3) {
+        double v = 0.0;
+#pragma unroll
+        for (int i = 0; i < kWarps; ++i) v += s_red[i][tid];
+        atomicAdd(&red[tid], v);
+    }
+}
+
+void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
+    SweepArgs A = base_args(o);
+    PSG_CUDA(cudaMemsetAsync(A.red, 0, 8 * sizeof(double), o->stream));
+    if (o->S > 0) {
+        k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red);
+        count_launch();
+        PSG_LAUNCH_CHECK();
+    }
+    double r[8];
+    fetch_red(o, r, 8);
+    *En = r[0]; *El = r[1]; *Er = r[2];
+}
+
+}  // namespace psg
