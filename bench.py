@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py -- photometric-optimizer hot path on synthetic RGB-D keyframes (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU code (oracle/_ref), rank 0 only
+
+A *step* is one outer ("LM") iteration of the alternating optimizer over the whole keyframe set
+(PsOptimizer.cpp:303-360): albedo, light, distance and pose blocks, each followed by the energy evaluation the
+reference logs -- 8 residual(+Jacobian) sweeps over all active (surface voxel, keyframe) pairs, the distance PCG and
+the small host solves.  metric = active pair evaluations per second (pairs x sweeps executed / time);
+ms_per_step = ms per LM iteration.
+
+`value`      : inputs resident in HBM when the timed region starts (volume fused, keyframes uploaded, surface list built).
+`e2e`        : the same iteration driven from HOST buffers through the C ABI: every step re-sends the keyframe images and
+               poses from pinned host memory (psg_opt_set_keyframes), rebuilds the surface list (psg_opt_init), runs
+               initAlbedo + one LM iteration and reads energies, poses and light back.
+`roofline`   : dominant kernel by device time, timed live with CUDA events on the launching stream (psg_profile_*).
+`cpu_baseline`: the reference's getPSEnergy() on this box's host (1 thread: the reference is single-threaded), on a
+               bounded sample of the same workload.
+At N > 1 each rank runs the same workload on its own GPU (replicas, weak scaling; the z-slab partition with halo
+exchange is not in this round) -- see DESIGN.md.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "active voxel-frame residual+Jacobian evaluations per second (128^3 SH1 LM iteration)"
+UNIT = "evals/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--grid", type=int, default=128)
+    ap.add_argument("--frames", type=int, default=30)
+    ap.add_argument("--model", default="SH1", choices=["SH1", "SH2", "LED"])
+    ap.add_argument("--height", type=int, default=480)
+    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-keyframes", type=int, default=4, help="keyframes in the reference-arm sample")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"synthetic TUM-style RGB-D orbit, {a.model}, {a.grid}^3 grid, {a.frames} keyframes {a.width}x{a.height}, "
+            f"light+albedo+distance+pose")
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_scene(a):
+    from psgradientsdf_b200 import synth
+    sc = synth.make_scene(F=a.frames, H=a.height, W=a.width, model=a.model)
+    vs, T = synth.grid_for_scene(a.grid)
+    return sc, vs, T
+
+
+def se3_parts(pose):
+    """R, t the reference's SE3(pose) hands to update(); orthonormal input poses make this the identity up to rounding,
+    and the same R, t go to every implementation."""
+    from oracle import pyref
+    if pyref.available():
+        return pyref.se3_from_matrix(pose)
+    return pose[:3, :3].copy(), pose[:3, 3].copy()
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def reference_sample(a, sc, vs, T, nkey):
+    """The reference's own optimizer on the same fused volume with `nkey` of the keyframes."""
+    from oracle import pyref
+    G = a.grid
+    rv = pyref.RefVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5)
+    reg_l = 5.0 if a.model == "LED" else 0.0
+    ro = pyref.RefOptimizer(rv, a.model, vs, sc.K, "/tmp/", reg_n=10.0, reg_l=reg_l)
+    for f in range(a.frames):
+        rv.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
+    keys = np.unique(np.linspace(0, a.frames - 1, nkey).round().astype(np.int32))
+    ro.set_keyframes(keys, sc.poses_init[keys], sc.color[keys])
+    ro.init()
+    ro.init_albedo()
+    _, _, A = ro.energy()
+    return rv, ro, int(A), keys
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pyref
+    if not pyref.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpsgref.so missing (reference sources were not built)"}))
+        return
+    sc, vs, T = build_scene(a)
+    rv, ro, A, keys = reference_sample(a, sc, vs, T, a.ref_keyframes)
+    for _ in range(a.warmup):
+        ro.ps_energy()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        ro.ps_energy()
+    dt = time.perf_counter() - t0
+    val = A * a.steps / dt
+    sample = (f"getPSEnergy() (PsOptimizer.cpp:47-78) over the full fused {a.grid}^3 volume with {len(keys)} of the "
+              f"{a.frames} keyframes: S={ro.S} surface voxels, {A} active pairs per step")
+    out = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+           "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic", "impl": "reference",
+           "config": {"workload": workload_name(a), "sample": sample},
+           "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": "reference", "sample": sample,
+                            "host_cores": os.cpu_count()},
+           "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def lm_iteration(go, model, damping=1.0):
+    """One pass of the reference's while-body (PsOptimizer.cpp:303-360 / LedOptimizer.cpp:343-403)."""
+    order = ["light", "albedo", "dist", "pose"] if model == "LED" else ["albedo", "light", "dist", "pose"]
+    E = None
+    for blk in order:
+        go.step(blk, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
+        E = go.energy()
+        if blk == "dist":
+            go.reg_energies()
+    return E
+
+
+def sweep_bytes(A, S, F, out_block):
+    """Algorithmic bytes of one sweep (SURVEY.md 8d / BASELINE.md): 48 A + 80 S + out_block S + 128 F."""
+    return 48 * A + 80 * S + out_block * S + 128 * F
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    import psgradientsdf_b200 as psg
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    sc, vs, T = build_scene(a)
+    G, F = a.grid, a.frames
+    reg_l = 5.0 if a.model == "LED" else 0.0
+    gv = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(64, F), device=local)
+    gv.set_zmin(0.5); gv.set_zmax(3.5)
+    go = psg.Optimizer(gv, vs, sc.K, model=a.model, reg_n=10.0, reg_l=reg_l)
+    for f in range(F):
+        R, t = se3_parts(sc.poses_gt[f])
+        if f > 0:
+            gv.increase_counter()
+        gv.update(sc.color[f], sc.depth[f], sc.K, R, t, sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv)
+    fi = np.arange(F, dtype=np.int32)
+    # pinned host copies of the per-step inputs (e2e leg)
+    img_pin = torch.from_numpy(np.ascontiguousarray(sc.color)).pin_memory()
+    pose_pin = torch.from_numpy(np.ascontiguousarray(sc.poses_init)).pin_memory()
+    images_np, poses_np = img_pin.numpy(), pose_pin.numpy()
+
+    def handoff():
+        go.set_keyframes(fi, poses_np, images_np)
+        go.init()
+        go.init_albedo()
+
+    handoff()
+    S = go.S
+    E0, A = go.energy()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")   # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sweeps_per_step = 8   # 4 block sweeps + 4 energy sweeps
+    # ---- device-resident leg
+    for _ in range(a.warmup):
+        lm_iteration(go, a.model)
+    psg.profile_reset(); psg.profile_enable(True)
+    sampler = ClockSampler(local); sampler.start()
+    launches0 = psg.kernel_launches()
+    barrier()
+    t_total = 0.0
+    E = None
+    for _ in range(a.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        E = lm_iteration(go, a.model)
+        torch.cuda.synchronize()
+        t_total += time.perf_counter() - t0
+    barrier()
+    launches = psg.kernel_launches() - launches0
+    clocks = sampler.stop()
+    prof = psg.profile_table()
+    psg.profile_enable(False)
+    tt = torch.tensor([t_total], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_max = float(tt.item())
+    value = world * A * sweeps_per_step * a.steps / t_max
+
+    # ---- e2e leg: host buffers -> C ABI every step
+    h2d = images_np.nbytes + poses_np.nbytes
+    d2h = poses_np.nbytes + 4 * go.light().size + 8 * 6
+    for _ in range(min(a.warmup, 2)):
+        handoff(); lm_iteration(go, a.model)
+    barrier()
+    te = 0.0
+    for _ in range(a.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        handoff()
+        lm_iteration(go, a.model)
+        go.poses(); go.light()
+        torch.cuda.synchronize()
+        te += time.perf_counter() - t0
+    barrier()
+    tte = torch.tensor([te], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(tte, op=dist.ReduceOp.MAX)
+    e2e_value = world * A * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel
+    peak, peak_src = peaks()
+    out_block = {"k_sweep<ALBEDO>": 24, "k_sweep<DIST>": 56}
+    best = None
+    table = {}
+    for name, (n, ms) in prof.items():
+        table[name] = {"launches": n, "ms_total": round(ms, 4), "ms_avg": round(ms / n, 5)}
+        if name.startswith("k_sweep<") and (best is None or ms > prof[best][1]):
+            best = name
+    roof = None
+    if best:
+        n, ms = prof[best]
+        bytes_launch = sweep_bytes(A, S, F, out_block.get(best, 0))
+        ach = bytes_launch / (ms / n * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "avg_launch_ms": ms / n}
+
+    # ---- CPU baseline (reference, 1 thread) on a bounded sample
+    cpu = None
+    if not a.no_cpu_baseline:
+        from oracle import pyoracle, pyref
+        if pyref.available():
+            rv, ro, A_s, keys = reference_sample(a, sc, vs, T, a.ref_keyframes)
+            t0 = time.perf_counter(); ro.ps_energy(); dt = time.perf_counter() - t0
+            cpu = {"value": A_s / dt, "unit": UNIT, "cores": 1, "kind": "reference", "host_cores": os.cpu_count(),
+                   "sample": f"one getPSEnergy() sweep, reference sources, {len(keys)} of {F} keyframes on the full fused "
+                             f"{G}^3 volume: S={ro.S}, {A_s} active pairs, {dt:.2f} s"}
+            ro.close(); rv.close()
+        # the O(1)-membership C port on the full workload, for the non-pathological comparison (BASELINE.md CPU-B)
+        ov = pyoracle.OrVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5, max(64, F))
+        oo = pyoracle.OrOptimizer(ov, a.model, vs, sc.K, reg_n=10.0, reg_l=reg_l)
+        for f in range(F):
+            R, t = se3_parts(sc.poses_gt[f])
+            ov.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, R, t, f > 0)
+        oo.set_keyframes(fi, sc.poses_init, sc.color); oo.init(); oo.init_albedo()
+        t0 = time.perf_counter(); _, _, A_o = oo.energy(); dt = time.perf_counter() - t0
+        port = {"value": A_o / dt, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": f"one energy sweep of oracle/psg_oracle.c (dense row map) on the full workload: {A_o} pairs, {dt:.2f} s"}
+        if cpu is None:
+            cpu = port
+        else:
+            cpu["port"] = port
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": workload_name(a), "surface_voxels": S, "active_pairs": A, "keyframes": F,
+                      "sweeps_per_step": sweeps_per_step, "energy_after_last_step": E[0] if E else None,
+                      "l2": "flushed between steps (256 MiB device write); per-step host timing bracketed by device syncs, summed",
+                      "multi_gpu": "replicas (each rank runs the full workload on its own GPU)" if world > 1 else "single GPU"},
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "ms_per_step": 1e3 * float(tte.item()) / a.steps,
+                   "step": "psg_opt_set_keyframes (pinned host images + poses) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},
+           "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "kernels": table}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

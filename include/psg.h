@@ -70,6 +70,15 @@ const char* psg_last_error(void);
 long long psg_kernel_launches(void);
 int psg_device_count(int* count);
 
+/* Built-in launch timer (no counterpart in the reference, which only has wall-clock Timer::tic/toc, Timer.h:29-49).
+ * When enabled, every kernel launch is bracketed by CUDA events on the stream it is launched on; psg_profile_get
+ * returns the launch count and summed device time of kernel `id` (0 <= id < psg_profile_kernels()). */
+int psg_profile_enable(int on);
+int psg_profile_reset(void);
+int psg_profile_kernels(void);
+const char* psg_profile_name(int id);
+int psg_profile_get(int id, long long* launches, double* total_ms);
+
 /* ------------------------------------------------------------------ volume (Sdf / VolumetricGradSdf) */
 
 /* VolumetricGradSdf(grid_dim, voxel_size, shift, T) + set_zmin/set_zmax (VolumetricGradSdf.h:65-70,
@@ -127,6 +136,11 @@ int psg_opt_set_poses(psg_optimizer* opt, const float* poses16);
 int psg_opt_get_reg(const psg_optimizer* opt, float reg3[3]);
 int psg_opt_set_reg(psg_optimizer* opt, const float reg3[3]);
 
+/* Tuning knob without a counterpart in the reference: how many warps share the keyframes of one group of 32 surface
+ * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
+ * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */
+int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
+
 /* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */
 int psg_opt_init_albedo(psg_optimizer* opt);
 
@@ -159,6 +173,33 @@ int psg_opt_last_vectors(psg_optimizer* opt, float* b, float* delta);
 /* Optimizer::subsampling() (OptimizerAux.cpp:622-684): every voxel splits into 8; the volume handle is
  * updated in place (dims x2, voxel size /2, origin shifted, VoxelGrid.h:143-149) and the surface is re-extracted. */
 int psg_opt_upsample(psg_optimizer* opt);
+
+/* {Ps,Led}Optimizer::alternatingOptimize(light, albedo, distance, pose) (PsOptimizer.cpp:239-428,
+ * LedOptimizer.cpp:279-478) with the settings it reads from OptimizerSettings (max_it, conv_threshold, damping, upsample,
+ * OptimizerSettings.h:24-33).  Runs initAlbedo, the regulariser-weight normalisation and the outer loop; writes
+ * <save_path>optimizer_doc.txt, after_poses_opt_<it>.txt, after_iter_<it>_pointcloud.ply, upsample_after_5_pointcloud.ply,
+ * final_refined_pointcloud.ply (LED: refined_sdf.sdf) when write_artifacts != 0 (save_path must exist and end in '/',
+ * as in the reference).  Mesh files are not written (marching cubes is outside this path). */
+typedef struct {
+    int light, albedo, distance, pose;   /* the --light/--albedo/--distance/--pose switches (main_ps.cpp:79-82) */
+    int max_it;
+    float conv_threshold;
+    float damping;
+    int upsample;
+    int write_artifacts;
+    int verbose;                         /* echo the reference's stdout lines */
+} psg_loop_config;
+typedef struct {
+    int iterations;                      /* outer iterations executed */
+    int converged;                       /* rel_diff < conv_threshold (the reference returns true) */
+    int diverged;                        /* total energy went up (the reference returns false) */
+    float last_rel_diff;
+    double E, E_normal, E_laplacian, E_albedo, E_total;   /* after the last block */
+    double ms_per_iteration;             /* host wall clock over the loop body, file dumps excluded */
+    float iteration_ms[64];
+} psg_loop_result;
+int psg_opt_alternating_optimize(psg_optimizer* opt, const psg_loop_config* cfg, const char* save_path,
+                                 psg_loop_result* result /* may be NULL */);
 
 #ifdef __cplusplus
 }

@@ -62,7 +62,7 @@ def lib():
         L.ref_opt_init_albedo.argtypes = [C.c_void_p]
         L.ref_opt_energy.restype = C.c_float
         L.ref_opt_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
-        for n in ("ref_opt_normal_energy", "ref_opt_laplacian_energy", "ref_opt_albedo_reg_energy"):
+        for n in ("ref_opt_ps_energy", "ref_opt_normal_energy", "ref_opt_laplacian_energy", "ref_opt_albedo_reg_energy"):
             getattr(L, n).restype = C.c_float
             getattr(L, n).argtypes = [C.c_void_p]
         L.ref_opt_probe_pairs.argtypes = [C.c_void_p, f32p, f32p, u8p, f32p, f32p]
@@ -212,6 +212,10 @@ class RefOptimizer:
         na = C.c_longlong()
         e = lib().ref_opt_energy(self.h, C.byref(e64), C.byref(na))
         return np.float32(e), e64.value, na.value
+
+    def ps_energy(self):
+        """getPSEnergy() only (what bench.py times)."""
+        return np.float32(lib().ref_opt_ps_energy(self.h))
 
     def normal_energy(self):
         return np.float32(lib().ref_opt_normal_energy(self.h))

@@ -328,6 +328,8 @@ float ref_opt_energy(void* h, double* E64, long long* n_active) {
     if (n_active) *n_active = cnt;
     return E;
 }
+// getPSEnergy() alone (timing leg of bench.py)
+float ref_opt_ps_energy(void* h) { return static_cast<RefOpt*>(h)->opt->getPSEnergy(); }
 float ref_opt_normal_energy(void* h) { return static_cast<RefOpt*>(h)->opt->getNormalEnergy(); }
 float ref_opt_laplacian_energy(void* h) { return static_cast<RefOpt*>(h)->opt->getLaplacianEnergy(); }
 float ref_opt_albedo_reg_energy(void* h) { return static_cast<RefOpt*>(h)->opt->getAlbedoRegEnergy(); }

@@ -41,7 +41,13 @@ class StepInfo(C.Structure):
 class LoopConfig(C.Structure):
     _fields_ = [("light", C.c_int), ("albedo", C.c_int), ("distance", C.c_int), ("pose", C.c_int),
                 ("max_it", C.c_int), ("conv_threshold", C.c_float), ("damping", C.c_float), ("upsample", C.c_int),
-                ("write_artifacts", C.c_int)]
+                ("write_artifacts", C.c_int), ("verbose", C.c_int)]
+
+
+class LoopResult(C.Structure):
+    _fields_ = [("iterations", C.c_int), ("converged", C.c_int), ("diverged", C.c_int), ("last_rel_diff", C.c_float),
+                ("E", C.c_double), ("E_normal", C.c_double), ("E_laplacian", C.c_double), ("E_albedo", C.c_double),
+                ("E_total", C.c_double), ("ms_per_iteration", C.c_double), ("iteration_ms", C.c_float * 64)]
 
 
 _lib = None
@@ -83,6 +89,7 @@ def lib():
         L.psg_opt_get_reg.argtypes = [vp, f32p]
         L.psg_opt_set_reg.argtypes = [vp, f32p]
         L.psg_opt_init_albedo.argtypes = [vp]
+        L.psg_opt_set_sweep_split.argtypes = [vp, C.c_int]
         L.psg_opt_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_opt_reg_energies.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.psg_opt_residual.argtypes = [vp, f32p, f32p]
@@ -91,6 +98,11 @@ def lib():
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
         L.psg_opt_upsample.argtypes = [vp]
+        L.psg_opt_alternating_optimize.argtypes = [vp, C.POINTER(LoopConfig), C.c_char_p, C.POINTER(LoopResult)]
+        L.psg_profile_enable.argtypes = [C.c_int]
+        L.psg_profile_name.restype = C.c_char_p
+        L.psg_profile_name.argtypes = [C.c_int]
+        L.psg_profile_get.argtypes = [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -102,6 +114,25 @@ def _check(status: int) -> None:
 
 def kernel_launches() -> int:
     return int(lib().psg_kernel_launches())
+
+
+def profile_enable(on: bool = True) -> None:
+    lib().psg_profile_enable(int(on))
+
+
+def profile_reset() -> None:
+    lib().psg_profile_reset()
+
+
+def profile_table() -> dict:
+    """{kernel name: (launches, total device ms)} from the built-in CUDA-event launch timer."""
+    out = {}
+    for i in range(lib().psg_profile_kernels()):
+        n, ms = C.c_longlong(), C.c_double()
+        _check(lib().psg_profile_get(i, C.byref(n), C.byref(ms)))
+        if n.value:
+            out[lib().psg_profile_name(i).decode()] = (n.value, ms.value)
+    return out
 
 
 def _ptr(a: np.ndarray):
@@ -264,6 +295,9 @@ class Optimizer:
     def init_albedo(self):
         _check(lib().psg_opt_init_albedo(self.h))
 
+    def set_sweep_split(self, warps: int):
+        _check(lib().psg_opt_set_sweep_split(self.h, int(warps)))
+
     def energy(self):
         e = C.c_double()
         na = C.c_longlong()
@@ -318,3 +352,15 @@ class Optimizer:
 
     def upsample(self):
         _check(lib().psg_opt_upsample(self.h))
+
+    def alternatingOptimize(self, light=True, albedo=True, distance=True, pose=True, max_it=100, conv_threshold=1e-4,
+                            damping=1.0, upsample=False, save_path=None, verbose=False):
+        """{Ps,Led}Optimizer::alternatingOptimize; returns the LoopResult as a dict."""
+        cfg = LoopConfig(int(light), int(albedo), int(distance), int(pose), int(max_it), float(conv_threshold),
+                         float(damping), int(upsample), int(save_path is not None), int(verbose))
+        res = LoopResult()
+        _check(lib().psg_opt_alternating_optimize(self.h, C.byref(cfg), save_path.encode() if save_path else None,
+                                                  C.byref(res)))
+        d = {k: getattr(res, k) for k, _ in LoopResult._fields_ if k != "iteration_ms"}
+        d["iteration_ms"] = [res.iteration_ms[i] for i in range(min(res.iterations, 64))]
+        return d

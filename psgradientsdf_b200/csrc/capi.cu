@@ -21,6 +21,39 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches += n; }
 
+// ---- launch timer: CUDA events on the launching stream around every kernel, summed per kernel id on request
+static const char* const kKernelNames[KID_COUNT] = {
+    "k_fill_volume", "k_pack_frame", "k_integrate", "k_aos_soa", "k_surface_mask", "k_scan_counts", "k_surface_scatter",
+    "k_neighbors", "k_upsample", "k_sweep<ENERGY>", "k_sweep<INIT_ALBEDO>", "k_sweep<LED_INIT>", "k_sweep<PROBE>",
+    "k_sweep<ALBEDO>", "k_sweep<LIGHT>", "k_sweep<POSE>", "k_sweep<DIST>", "k_reg_energy", "k_dist_assemble", "k_dist_pcg",
+    "k_dist_update", "k_grad_update", "k_pad_images" };
+static bool g_prof_on = false;
+struct ProfRec { int id; cudaEvent_t e0, e1; };
+static std::vector<ProfRec> g_prof_recs;
+static long long g_prof_count[KID_COUNT] = {0};
+static double g_prof_ms[KID_COUNT] = {0};
+
+Prof::Prof(cudaStream_t stream, int kernel_id) : st(stream), id(kernel_id) {
+    g_launches += 1;
+    if (g_prof_on) {
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0, st);
+    }
+}
+Prof::~Prof() {
+    if (e0) { cudaEventRecord(e1, st); g_prof_recs.push_back({id, e0, e1}); }
+}
+static void prof_collect() {
+    for (const ProfRec& r : g_prof_recs) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(r.e1) == cudaSuccess && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+            g_prof_count[r.id] += 1; g_prof_ms[r.id] += (double)ms;
+        }
+        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+    }
+    g_prof_recs.clear();
+}
+
 // Eigen::ConjugateGradient<SparseMatrix<float>, Lower, DiagonalPreconditioner<float>> on a small dense symmetric system
 // (the light and pose blocks: F independent 4x4 / 9x9 / 6x6 blocks solved jointly, exactly as the reference does,
 // PsOptimizer.cpp:184-191, 217-227).  Only the lower triangle is read.  Returns Eigen's verdict.
@@ -146,6 +179,26 @@ extern "C" {
 
 const char* psg_last_error(void) { return g_err; }
 long long psg_kernel_launches(void) { return g_launches.load(); }
+
+int psg_profile_enable(int on) {
+    prof_collect();
+    g_prof_on = on != 0;
+    return PSG_OK;
+}
+int psg_profile_reset(void) {
+    prof_collect();
+    for (int i = 0; i < KID_COUNT; ++i) { g_prof_count[i] = 0; g_prof_ms[i] = 0.0; }
+    return PSG_OK;
+}
+int psg_profile_kernels(void) { return KID_COUNT; }
+const char* psg_profile_name(int id) { return (id >= 0 && id < KID_COUNT) ? kKernelNames[id] : ""; }
+int psg_profile_get(int id, long long* launches, double* total_ms) {
+    if (id < 0 || id >= KID_COUNT) { set_error("psg_profile_get: bad kernel id %d", id); return PSG_ERR_INVALID; }
+    prof_collect();
+    if (launches) *launches = g_prof_count[id];
+    if (total_ms) *total_ms = g_prof_ms[id];
+    return PSG_OK;
+}
 
 int psg_device_count(int* count) {
     PSG_TRY
@@ -319,7 +372,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     cudaSetDevice(o->vol->device);
     o->images.release(); o->frames.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
     o->svis.release(); o->pos.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
-    o->frame_idx_dev.release(); o->red.release(); o->vecs.release(); o->pcg_partials.release();
+    o->frame_idx_dev.release(); o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release();
     delete o;
     return PSG_OK;
 }
@@ -344,8 +397,8 @@ int psg_opt_set_keyframes(psg_optimizer* o, int F, const int* frame_idx, const f
     for (int f = 0; f < F; ++f) {
         PSG_CUDA(cudaMemcpyAsync(o->vol->staging.p, images + (size_t)f * per * 3, (size_t)per * 3 * sizeof(float),
                                  cudaMemcpyHostToDevice, o->stream));
-        k_pad_images<<<(unsigned)((per + 255) / 256), 256, 0, o->stream>>>(o->vol->staging.p, o->images.p + (size_t)f * per, per);
-        count_launch();
+        { Prof pf(o->stream, KID_PAD_IMAGES);
+          k_pad_images<<<(unsigned)((per + 255) / 256), 256, 0, o->stream>>>(o->vol->staging.p, o->images.p + (size_t)f * per, per); }
         PSG_LAUNCH_CHECK();
     }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -444,6 +497,16 @@ int psg_opt_get_reg(const psg_optimizer* o, float r[3]) {
 int psg_opt_set_reg(psg_optimizer* o, const float r[3]) {
     if (!o || !r) { set_error("null argument"); return PSG_ERR_INVALID; }
     o->set.reg_weight_rho = r[0]; o->set.reg_weight_n = r[1]; o->set.reg_weight_l = r[2];
+    return PSG_OK;
+}
+
+int psg_opt_set_sweep_split(psg_optimizer* o, int warps) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (warps != 0 && warps != 1 && warps != 2 && warps != 4 && warps != 8) {
+        set_error("psg_opt_set_sweep_split: %d is not one of 0, 1, 2, 4, 8", warps);
+        return PSG_ERR_INVALID;
+    }
+    o->sweep_split = warps;
     return PSG_OK;
 }
 

@@ -243,7 +243,7 @@ void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float
     A.damping = damping;
     A.max_iters = 2 * S;
 
-    k_dist_assemble<<<(S + kPcgBlock - 1) / kPcgBlock, kPcgBlock, 0, o->stream>>>(A);
+    { Prof pf(o->stream, KID_PCG_ASSEMBLE); k_dist_assemble<<<(S + kPcgBlock - 1) / kPcgBlock, kPcgBlock, 0, o->stream>>>(A); }
     PSG_LAUNCH_CHECK();
 
     int dev = 0, sms = 0, per_sm = 0;
@@ -258,8 +258,8 @@ void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float
     o->pcg_partials.alloc((size_t)3 * grid);
     A.partials = o->pcg_partials.p;
     void* args[] = { &A };
-    PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
-    count_launch(2);
+    { Prof pf(o->stream, KID_PCG_SOLVE);
+      PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg, dim3(grid), dim3(kPcgBlock), args, 0, o->stream)); }
     float res[4];
     PSG_CUDA(cudaMemcpyAsync(res, A.result, sizeof(res), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -282,11 +282,10 @@ void apply_dist_update(psg_optimizer* o, long long* accepted) {
     SurfView sv;
     sv.S = S; sv.lin = o->lin.p; sv.vis = o->svis.p; sv.nbr_lin = o->nbr_lin.p; sv.nbr_row = o->nbr_row.p; sv.pos = o->pos.p;
     const double thr = sqrt(3.0) * (double)o->vs;
-    k_dist_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, S, delta, thr, cnt);
+    { Prof pf(o->stream, KID_DIST_UPDATE); k_dist_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, S, delta, thr, cnt); }
     PSG_LAUNCH_CHECK();
-    k_grad_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, sv, o->vs_inv);
+    { Prof pf(o->stream, KID_GRAD_UPDATE); k_grad_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, sv, o->vs_inv); }
     PSG_LAUNCH_CHECK();
-    count_launch(2);
     unsigned long long h = 0;
     PSG_CUDA(cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));

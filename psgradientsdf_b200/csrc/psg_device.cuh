@@ -29,7 +29,7 @@ struct VolView {
 struct FramePose { float R[9]; float t[3]; };   // camera-to-world rotation (row-major) and translation
 
 // Per-keyframe parameters, one entry per keyframe, read uniformly by a whole warp.
-struct FrameParams {
+struct __align__(16) FrameParams {
     float R[9];
     float t[3];
     float light[9];   // SH coefficients of this keyframe (4 or 9 used); unused for LED

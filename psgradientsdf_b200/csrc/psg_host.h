@@ -14,6 +14,20 @@ namespace psg {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 
+// Kernel ids for the built-in launch timer (psg_profile_* in include/psg.h).
+enum KernelId {
+    KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
+    KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
+    KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_COUNT
+};
+// Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
+struct Prof {
+    cudaStream_t st; int id; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    Prof(cudaStream_t stream, int kernel_id);
+    ~Prof();
+};
+
 struct CudaError { int code; };
 #define PSG_CUDA(call)                                                                          \
     do {                                                                                        \
@@ -82,6 +96,9 @@ struct psg_optimizer {
     psg::DevBuf<int> frame_idx_dev;
     // reductions / systems
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
+    psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
+    psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
+    int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
     psg::DevBuf<double> pcg_partials;
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step

@@ -228,11 +228,10 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     o->prefix.alloc((size_t)nw);
     o->block_counts.alloc((size_t)nblocks + 1);
 
-    k_surface_mask<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, nw, (int)wpb);
+    { Prof pf(o->stream, KID_SURF_MASK); k_surface_mask<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, nw, (int)wpb); }
     PSG_LAUNCH_CHECK();
-    k_scan_counts<<<1, 1024, 0, o->stream>>>(o->block_counts.p, nblocks);
+    { Prof pf(o->stream, KID_SURF_SCAN); k_scan_counts<<<1, 1024, 0, o->stream>>>(o->block_counts.p, nblocks); }
     PSG_LAUNCH_CHECK();
-    count_launch(2);
     unsigned total = 0;
     PSG_CUDA(cudaMemcpyAsync(&total, o->block_counts.p + nblocks, sizeof(unsigned), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -240,13 +239,14 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     const size_t S = (size_t)(o->S > 0 ? o->S : 1);
     o->lin.alloc(S); o->svis.alloc(S); o->nbr_lin.alloc(3 * S); o->nbr_row.alloc(3 * S); o->pos.alloc(S); o->inc.alloc(6 * S);
     if (o->S > 0) {
-        k_surface_scatter<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->prefix.p, nw, (int)wpb,
-                                                          o->lin.p, o->svis.p);
+        { Prof pf(o->stream, KID_SURF_SCATTER);
+          k_surface_scatter<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->prefix.p, nw, (int)wpb,
+                                                            o->lin.p, o->svis.p); }
         PSG_LAUNCH_CHECK();
-        k_neighbors<<<(o->S + 255) / 256, 256, 0, o->stream>>>(v, o->mask.p, o->prefix.p, o->lin.p, o->S, o->nbr_lin.p,
-                                                               o->nbr_row.p, o->pos.p, o->inc.p);
+        { Prof pf(o->stream, KID_SURF_NEIGHBORS);
+          k_neighbors<<<(o->S + 255) / 256, 256, 0, o->stream>>>(v, o->mask.p, o->prefix.p, o->lin.p, o->S, o->nbr_lin.p,
+                                                                 o->nbr_row.p, o->pos.p, o->inc.p); }
         PSG_LAUNCH_CHECK();
-        count_launch(2);
     }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
 }
@@ -266,9 +266,8 @@ void launch_upsample(psg_optimizer* o) {
     dst.dist = nf[0].p; dst.gx = nf[1].p; dst.gy = nf[2].p; dst.gz = nf[3].p;
     dst.w = nf[4].p; dst.r = nf[5].p; dst.g = nf[6].p; dst.b = nf[7].p; dst.vis = nvis.p;
     const float vs4 = (float)(0.25 * (double)vol->vs);
-    k_upsample<<<(unsigned)((N8 + 255) / 256), 256, 0, o->stream>>>(src, dst, vs4);
+    { Prof pf(o->stream, KID_UPSAMPLE); k_upsample<<<(unsigned)((N8 + 255) / 256), 256, 0, o->stream>>>(src, dst, vs4); }
     PSG_LAUNCH_CHECK();
-    count_launch();
     PSG_CUDA(cudaStreamSynchronize(o->stream));
     for (int a = 0; a < 8; ++a) { vol->f[a].release(); vol->f[a] = nf[a]; nf[a].p = nullptr; }
     vol->vis.release(); vol->vis = nvis; nvis.p = nullptr;

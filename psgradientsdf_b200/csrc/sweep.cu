@@ -20,7 +20,10 @@ namespace psg {
 
 enum Mode { M_ENERGY = 0, M_INIT_ALBEDO, M_LED_INIT, M_PROBE, M_ALBEDO, M_LIGHT, M_POSE, M_DIST };
 
-constexpr int kBlock = 128;
+// A block is 32 surface voxels (one per lane) times W warps; the warps split the keyframes the 32 voxels see
+// between them (W = 1, 2, 4 or 8, chosen at launch so that small surfaces still fill the 148 SMs).
+constexpr int kMaxSplit = 8;
+constexpr int kBlock = 128;   // block size of the auxiliary per-voxel kernels in this file
 constexpr int kWarps = kBlock / 32;
 
 struct SweepArgs {
@@ -36,6 +39,8 @@ struct SweepArgs {
     float damping, reg_n, reg_l;
     int flags;
     double* red;        // reductions (zeroed by the launcher)
+    double* partials;   // [gridDim.x][8] per-block scalar partials, combined in block order by the last block
+    unsigned* counter;  // arrival counter for that (self-resetting)
     float* out0;        // mode dependent per-voxel outputs
     float* out1;
     // probe outputs
@@ -142,44 +147,55 @@ __device__ __forceinline__ void normal_jacobian(float vs_inv, const float* grad,
     for (int a = 0; a < 3; ++a) Jn[a] = N_inv * nd[a] - dN * grad[a];
 }
 
-// V values per lane -> per-warp shared slice, lane l adds the warp sum of value l.
+// V values per lane -> lane l adds the warp sum of value l to dst[l] (one double atomic per lane and keyframe).
 template <int V>
-__device__ __forceinline__ void warp_accumulate(float* vals, int lane, float* slice /* >= V floats */) {
-    if (V <= 32) {
-        const float s = warp_reduce_scatter<V>(vals, lane);
-        if (lane < V) slice[lane] += s;
+__device__ __forceinline__ void warp_accumulate(float* vals, int lane, double* dst /* >= V doubles */) {
+    const float s = warp_reduce_scatter<V>(vals, lane);
+    if (lane < V && s != 0.f) atomicAdd(&dst[lane], (double)s);
+}
+
+// Deterministic grid-wide sum of n <= 8 per-block doubles: every block parks its values, the last block to arrive adds
+// them up in block order (fixed association) and writes out[0..n).
+__device__ __forceinline__ void grid_sum_scalars(const double* block_vals, int n, double* partials, unsigned* counter,
+                                                 double* out, bool* s_last) {
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < n; ++i) partials[(size_t)blockIdx.x * 8 + i] = block_vals[i];
+        __threadfence();
+        const unsigned ticket = atomicAdd(counter, 1u);
+        *s_last = (ticket == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (*s_last && threadIdx.x < 32) {
+        __threadfence();
+        for (int i = 0; i < n; ++i) {
+            double t = 0.0;
+            for (unsigned b = threadIdx.x; b < gridDim.x; b += 32) t += partials[(size_t)b * 8 + i];
+            t = warp_sum(t);
+            if (threadIdx.x == 0) out[i] = t;
+        }
+        if (threadIdx.x == 0) *counter = 0u;
     }
 }
 
 template <int MODEL, int MODE>
-__global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
+__global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
     constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
     constexpr bool LED = (MODEL == PSG_MODEL_LED);
-    // per-frame reduction width (padded to a multiple of 32 lanes / power of two)
+    // per-keyframe reduction width (padded to a power of two / multiple of 32 lanes)
     constexpr int VLIGHT = LED ? 0 : (NB == 4 ? 16 : 64);
     constexpr int VRED = (MODE == M_POSE) ? 32 : ((MODE == M_LIGHT) ? VLIGHT : 0);
+    // per-voxel accumulators that the keyframe-splitting warps have to combine
+    constexpr int NACC = (MODE == M_DIST) ? 14 : ((MODE == M_ALBEDO) ? 6 : ((MODE == M_INIT_ALBEDO) ? 4 : 0));
 
-    extern __shared__ float s_dyn[];
-    __shared__ FrameParams s_frames[kMaxFrames];
-    __shared__ unsigned long long s_or[kWarps];
-    __shared__ double s_red[kWarps][8];
+    extern __shared__ float s_dyn[];   // [W][NACC][32]
+    __shared__ double s_red[kMaxSplit][8];
+    __shared__ double s_tot[8];
+    __shared__ bool s_last;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int S = A.surf.S;
-    const int s = blockIdx.x * kBlock + tid;
+    const int s = blockIdx.x * 32 + lane;
     const bool live = s < S;
-
-    // stage per-keyframe parameters
-    {
-        const float* src = reinterpret_cast<const float*>(A.frames);
-        float* dst = reinterpret_cast<float*>(s_frames);
-        const int nfl = A.F * (int)(sizeof(FrameParams) / sizeof(float));
-        for (int i = tid; i < nfl; i += kBlock) dst[i] = src[i];
-    }
-    if constexpr (VRED > 0) {
-        const int n = kWarps * A.F * VRED;
-        for (int i = tid; i < n; i += kBlock) s_dyn[i] = 0.f;
-    }
 
     // ---- voxel record
     int lin = 0, idx[3] = {0, 0, 0};
@@ -212,18 +228,13 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
     sh_eval<NB>(nfd, sh_n);
     sh_eval<NB>(gh, sh_g);
 
-    // ---- block-wide union of visibility
+    // ---- keyframes any of the 32 voxels sees (every warp of the block holds the same 32 voxels)
+    unsigned long long uni;
     {
-        unsigned lo = (unsigned)vis, hi = (unsigned)(vis >> 32);
-        lo = __reduce_or_sync(0xffffffffu, lo);
-        hi = __reduce_or_sync(0xffffffffu, hi);
-        if (lane == 0) s_or[warp] = ((unsigned long long)hi << 32) | lo;
+        const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)vis);
+        const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(vis >> 32));
+        uni = ((unsigned long long)hi << 32) | lo;
     }
-    __syncthreads();
-    unsigned long long uni = 0ull;
-#pragma unroll
-    for (int i = 0; i < kWarps; ++i) uni |= s_or[i];
-    const unsigned long long warp_uni = s_or[warp];
 
     // ---- mode-specific per-voxel state
     double acc_d[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // ENERGY: [0] loss; LED_INIT: I[3], rend[3]; LED light: H[3], b[3]
@@ -262,12 +273,21 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
 
     const float fx = A.cam.fx, fy = A.cam.fy, cx = A.cam.cx, cy = A.cam.cy;
 
-    // ---- keyframe loop (ascending, uniform across the block)
+    // ---- keyframe loop: ascending, every lane of a warp on the same keyframe; warp w takes every W-th visible keyframe
+    int slot = 0;
     while (uni) {
         const int f = __ffsll((long long)uni) - 1;
         uni &= uni - 1;
-        if constexpr (VRED > 0) { if (!((warp_uni >> f) & 1ull)) continue; }   // warp-uniform: nothing to reduce for this warp
-        const FrameParams& P = s_frames[f];
+        const bool mine = (slot & (W - 1)) == warp;
+        ++slot;
+        if (!mine) continue;
+        FrameParams P;
+        {
+            const float4* src = reinterpret_cast<const float4*>(A.frames + f);
+            float4* dst = reinterpret_cast<float4*>(&P);
+#pragma unroll
+            for (int i = 0; i < (int)(sizeof(FrameParams) / 16); ++i) dst[i] = __ldg(src + i);
+        }
         const bool act = live && ((vis >> f) & 1ull);
 
         bool ok = false;
@@ -374,12 +394,12 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
                         }
                     }
                 }
-                float* slice = s_dyn + ((long long)warp * A.F + f) * VRED;
+                double* dst = A.red + (long long)f * VRED;
                 if constexpr (VLIGHT == 16) {
-                    warp_accumulate<16>(vals, lane, slice);
+                    warp_accumulate<16>(vals, lane, dst);
                 } else {
-                    warp_accumulate<32>(vals, lane, slice);
-                    warp_accumulate<32>(vals + 32, lane, slice + 32);
+                    warp_accumulate<32>(vals, lane, dst);
+                    warp_accumulate<32>(vals + 32, lane, dst + 32);
                 }
             }
         } else if constexpr (MODE == M_POSE || MODE == M_DIST) {
@@ -449,8 +469,7 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
                         }
                     }
                 }
-                float* slice = s_dyn + ((long long)warp * A.F + f) * VRED;
-                warp_accumulate<32>(vals, lane, slice);
+                warp_accumulate<32>(vals, lane, A.red + (long long)f * VRED);
             } else if (okj) {   // M_DIST
                 // M = A * R^T, dI_k = M * dx_k
                 float Mx[9];
@@ -526,6 +545,25 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
     }
 
     // ---- epilogues
+    // (a) per-voxel partial sums of the keyframe-splitting warps -> warp 0, in warp order
+    if constexpr (NACC > 0) {
+        if (W > 1) {
+            if constexpr (MODE == M_INIT_ALBEDO) vacc[3] = (float)icount;
+#pragma unroll
+            for (int i = 0; i < NACC; ++i) s_dyn[(warp * NACC + i) * 32 + lane] = vacc[i];
+            __syncthreads();
+            if (warp == 0) {
+#pragma unroll
+                for (int i = 0; i < NACC; ++i) {
+                    float t = s_dyn[i * 32 + lane];
+                    for (int wv = 1; wv < W; ++wv) t += s_dyn[(wv * NACC + i) * 32 + lane];
+                    vacc[i] = t;
+                }
+                if constexpr (MODE == M_INIT_ALBEDO) icount = (int)(vacc[3] + 0.5f);
+            }
+        }
+    }
+    // (b) scalar sums: warp -> block (warp order) -> grid (block order, last block)
     if constexpr (MODE == M_ENERGY || MODE == M_LED_INIT || (MODE == M_LIGHT && LED)) {
         constexpr int ND = (MODE == M_ENERGY) ? 1 : 6;
 #pragma unroll
@@ -533,21 +571,16 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
         const long long c2 = warp_sum_ll(cnt);
         if (lane == 0) s_red[warp][7] = (double)c2;
         __syncthreads();
-        if (tid < ND) {
+        if (tid < 8) {
             double v = 0.0;
-#pragma unroll
-            for (int i = 0; i < kWarps; ++i) v += s_red[i][tid];
-            atomicAdd(&A.red[tid], v);
+            if (tid < ND || tid == 7) for (int i = 0; i < W; ++i) v += s_red[i][tid];
+            s_tot[tid] = v;
         }
-        if (tid == 7) {
-            double v = 0.0;
-#pragma unroll
-            for (int i = 0; i < kWarps; ++i) v += s_red[i][7];
-            atomicAdd(&A.red[7], v);
-        }
+        __syncthreads();
+        grid_sum_scalars(s_tot, 8, A.partials, A.counter, A.red, &s_last);
     }
     if constexpr (MODE == M_INIT_ALBEDO) {
-        if (live && icount) {
+        if (warp == 0 && live && icount) {
             A.vol.r[lin] = vacc[0] / (float)icount;
             A.vol.g[lin] = vacc[1] / (float)icount;
             A.vol.b[lin] = vacc[2] / (float)icount;
@@ -557,7 +590,7 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
         // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
         // Optimizer::updateAlbedo gate (OptimizerAux.cpp:120-147): accept a channel only if it stays strictly in (0, 1)
         int accepted = 0;
-        if (live) {
+        if (warp == 0 && live) {
             float* chan[3] = { A.vol.r, A.vol.g, A.vol.b };
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
@@ -571,27 +604,12 @@ __global__ void __launch_bounds__(kBlock) k_sweep(SweepArgs A) {
             }
         }
         const long long c2 = warp_sum_ll(accepted);
-        if (lane == 0) s_red[warp][0] = (double)c2;
+        if (tid == 0) { for (int i = 0; i < 8; ++i) s_tot[i] = 0.0; s_tot[0] = (double)c2; }
         __syncthreads();
-        if (tid == 0) {
-            double v = 0.0;
-#pragma unroll
-            for (int i = 0; i < kWarps; ++i) v += s_red[i][0];
-            atomicAdd(&A.red[0], v);
-        }
-    }
-    if constexpr (VRED > 0) {
-        __syncthreads();
-        const int n = A.F * VRED;
-        for (int i = tid; i < n; i += kBlock) {
-            double v = 0.0;
-#pragma unroll
-            for (int wv = 0; wv < kWarps; ++wv) v += (double)s_dyn[(long long)wv * n + i];
-            if (v != 0.0) atomicAdd(&A.red[i], v);
-        }
+        grid_sum_scalars(s_tot, 1, A.partials, A.counter, A.red, &s_last);
     }
     if constexpr (MODE == M_DIST) {
-        if (live) {
+        if (warp == 0 && live) {
             // Eikonal rows (Optimizer.cpp:196-218, 477-537), scaled by reg_weight_n (PsOptimizer.cpp:136-142)
             if (A.flags & PSG_REG_NORMAL) {
                 float nd[3], Jr[4];
@@ -652,6 +670,14 @@ static SweepArgs base_args(psg_optimizer* o) {
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
     o->red.alloc(kMaxFrames * 64 + 8);
     A.red = o->red.p;
+    const size_t grid = (size_t)(o->S + 31) / 32 + 1;
+    o->sweep_partials.alloc(grid * 8);
+    if (!o->sweep_counter.p) {
+        o->sweep_counter.alloc(4);
+        PSG_CUDA(cudaMemsetAsync(o->sweep_counter.p, 0, 4 * sizeof(unsigned), o->stream));
+    }
+    A.partials = o->sweep_partials.p;
+    A.counter = o->sweep_counter.p;
     return A;
 }
 
@@ -674,12 +700,19 @@ template <int MODE>
 static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
     if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
     if (o->S == 0) return;
-    const int grid = (o->S + kBlock - 1) / kBlock;
+    const int grid = (o->S + 31) / 32;
+    // keyframe split: double W while the launch still has fewer warps than the GPU holds (148 SMs x 48 warps)
+    int W = 1;
+    while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 48) W *= 2;
+    if (o->sweep_split > 0) W = o->sweep_split;
+    const int kBlockDim = 32 * W;
+    if (W > 1 && dyn_smem < (size_t)W * 14 * 32 * sizeof(float)) dyn_smem = (size_t)W * 14 * 32 * sizeof(float);
 #define PSG_SWEEP_CASE(MODEL)                                                                                          \
     case MODEL: {                                                                                                      \
         if (dyn_smem > 48 * 1024)                                                                                      \
             PSG_CUDA(cudaFuncSetAttribute(k_sweep<MODEL, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem)); \
-        k_sweep<MODEL, MODE><<<grid, kBlock, dyn_smem, o->stream>>>(A);                                                \
+        Prof pf(o->stream, KID_SWEEP_ENERGY + MODE);                                                                   \
+        k_sweep<MODEL, MODE><<<grid, kBlockDim, dyn_smem, o->stream>>>(A);                                                \
     } break;
     switch (o->set.model) {
         PSG_SWEEP_CASE(PSG_MODEL_SH1)
@@ -688,7 +721,6 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
         default: set_error("unknown model %d", o->set.model); throw CudaError{-1};
     }
 #undef PSG_SWEEP_CASE
-    count_launch();
     PSG_LAUNCH_CHECK();
 }
 
@@ -750,9 +782,8 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
     const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
     const int NT = nbk * (nbk + 1) / 2;
     const size_t nred = (size_t)o->F * V;
-    const size_t smem = (size_t)kWarps * o->F * V * sizeof(float);
-    if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, smem);
-    else launch_sweep<M_LIGHT>(o, A, nred, smem);
+    if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, 0);
+    else launch_sweep<M_LIGHT>(o, A, nred, 0);
     std::vector<double> r(nred);
     fetch_red(o, r.data(), nred);
     Hout.assign((size_t)o->F * nbk * nbk, 0.0);
@@ -828,8 +859,7 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
     SweepArgs A = base_args(o);
     PSG_CUDA(cudaMemsetAsync(A.red, 0, 8 * sizeof(double), o->stream));
     if (o->S > 0) {
-        k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red);
-        count_launch();
+        { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red); }
         PSG_LAUNCH_CHECK();
     }
     double r[8];

@@ -117,15 +117,13 @@ static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + 
 
 void launch_fill_volume(psg_volume* v) {
     const VolView view = v->view();
-    k_fill_volume<<<148 * 8, 256, 0, v->stream>>>(view);
-    count_launch();
+    { Prof pf(v->stream, KID_FILL); k_fill_volume<<<148 * 8, 256, 0, v->stream>>>(view); }
     PSG_LAUNCH_CHECK();
 }
 
 void launch_pack_frame(psg_volume* v, const float* planar_dev, int H, int W) {
     v->frame.alloc((size_t)H * W * 8);
-    k_pack_frame<<<blocks_for((long long)H * W, 256), 256, 0, v->stream>>>(planar_dev, v->frame.p, H * W);
-    count_launch();
+    { Prof pf(v->stream, KID_PACK_FRAME); k_pack_frame<<<blocks_for((long long)H * W, 256), 256, 0, v->stream>>>(planar_dev, v->frame.p, H * W); }
     PSG_LAUNCH_CHECK();
 }
 
@@ -136,19 +134,16 @@ void launch_integrate(psg_volume* v, int H, int W, const float* K, const float* 
     for (int a = 0; a < 3; ++a) P.t[a] = t[a];
     P.H = H; P.W = W; P.counter = counter;
     const VolView view = v->view();
-    k_integrate<<<blocks_for(v->N, 256), 256, 0, v->stream>>>(view, v->frame.p, P);
-    count_launch();
+    { Prof pf(v->stream, KID_FUSE); k_integrate<<<blocks_for(v->N, 256), 256, 0, v->stream>>>(view, v->frame.p, P); }
     PSG_LAUNCH_CHECK();
 }
 
 void launch_aos_to_soa(psg_volume* v, const float* aos_dev, long long begin, long long count) {
-    k_aos_to_soa<<<blocks_for(count, 256), 256, 0, v->stream>>>(v->view(), aos_dev, begin, count);
-    count_launch();
+    { Prof pf(v->stream, KID_AOS); k_aos_to_soa<<<blocks_for(count, 256), 256, 0, v->stream>>>(v->view(), aos_dev, begin, count); }
     PSG_LAUNCH_CHECK();
 }
 void launch_soa_to_aos(psg_volume* v, float* aos_dev, long long begin, long long count) {
-    k_soa_to_aos<<<blocks_for(count, 256), 256, 0, v->stream>>>(v->view(), aos_dev, begin, count);
-    count_launch();
+    { Prof pf(v->stream, KID_AOS); k_soa_to_aos<<<blocks_for(count, 256), 256, 0, v->stream>>>(v->view(), aos_dev, begin, count); }
     PSG_LAUNCH_CHECK();
 }
 

@@ -103,7 +103,8 @@ def _rodrigues(w: np.ndarray) -> np.ndarray:
 def make_scene(F: int = 8, H: int = 120, W: int = 160, model: str = "SH1", seed: int = 1234,
                radius: float = 1.5, r0: float = 0.35, elev_amp: float = 0.35,
                pose_sigma_t: float = 0.002, pose_sigma_r_deg: float = 0.2) -> Scene:
-    rng = np.random.default_rng(seed)
+    rng = np.random.default_rng(seed)            # lights
+    rng_pose = np.random.default_rng(seed + 1)   # pose perturbations (same for every model)
     sx, sy = W / 640.0, H / 480.0
     fx, fy = 525.0 * sx, 525.0 * sy
     cx, cy = (319.5 + 0.5) * sx - 0.5, (239.5 + 0.5) * sy - 0.5
@@ -140,21 +141,37 @@ def make_scene(F: int = 8, H: int = 120, W: int = 160, model: str = "SH1", seed:
         T = poses_gt[f].astype(np.float64)                              # what the optimizer could at best recover
         R, t = T[:3, :3], T[:3, 3]
         dirs = rays_cam @ R.T                                           # world, |.| >= 1, camera z advances by s
-        # sphere tracing along s (camera depth); |dirs| >= 1 so a step of sdf/|dirs| is safe
         dn = np.linalg.norm(dirs, axis=-1)
-        s = np.full((H, W), radius - r0 * 1.25)
-        alive = np.ones((H, W), dtype=bool)
-        for _ in range(96):
-            p = t + dirs * s[..., None]
-            d = sdf(p, r0)
-            step = 0.8 * d / dn
-            s = np.where(alive, s + step, s)
-            alive &= s < radius + r0 * 1.5
+        # only rays that pass within the bounding sphere can hit; trace those as flat arrays
+        rb = r0 * 1.12
+        tca = -(dirs @ t) / (dn * dn)                                   # parameter of closest approach
+        d2 = np.sum((t + dirs * tca[..., None]) ** 2, axis=-1)
+        cand = d2 < rb * rb
+        ci = np.nonzero(cand.ravel())[0]
+        dc = dirs.reshape(-1, 3)[ci]
+        dnc = dn.ravel()[ci]
+        sc_ = tca.ravel()[ci] - np.sqrt(np.maximum(rb * rb - d2.ravel()[ci], 0.0)) / dnc   # entry into the bounding sphere
+        send = tca.ravel()[ci] + np.sqrt(np.maximum(rb * rb - d2.ravel()[ci], 0.0)) / dnc
+        alive = np.ones(ci.size, dtype=bool)
+        for _ in range(64):
+            pc = t + dc * sc_[:, None]
+            d = sdf(pc, r0)
+            sc_ = np.where(alive, sc_ + 0.8 * d / dnc, sc_)
+            alive &= sc_ < send
+        pc = t + dc * sc_[:, None]
+        hitc = alive & (np.abs(sdf(pc, r0)) < 2e-4)
+        s = np.zeros(H * W)
+        s[ci] = np.where(hitc, sc_, 0.0)
+        s = s.reshape(H, W)
+        hit = np.zeros(H * W, dtype=bool)
+        hit[ci] = hitc
+        hit = hit.reshape(H, W)
         p = t + dirs * s[..., None]
-        hit = alive & (np.abs(sdf(p, r0)) < 2e-4)
         z16 = np.where(hit, np.clip(np.rint(s * 5000.0), 0, 65535), 0).astype(np.uint16)
         depth[f] = z16.astype(np.float32) * unit
-        n_w = sdf_grad(p, r0)                                           # outward, world
+        n_w = np.zeros((H * W, 3))
+        n_w[ci] = sdf_grad(pc, r0)                                      # outward, world
+        n_w = n_w.reshape(H, W, 3)
         n_c = -(n_w @ R)                                                # inward, camera frame
         nxs[f] = np.where(hit, n_c[..., 0], 0).astype(np.float32)
         nys[f] = np.where(hit, n_c[..., 1], 0).astype(np.float32)
@@ -162,7 +179,7 @@ def make_scene(F: int = 8, H: int = 120, W: int = 160, model: str = "SH1", seed:
         rho = albedo(p)
         if model == "LED":
             p_c = rays_cam * s[..., None]
-            irr = -np.sum((n_w @ R) * p_c, axis=-1) / np.linalg.norm(p_c, axis=-1) ** 3
+            irr = -np.sum((n_w @ R) * p_c, axis=-1) / np.maximum(np.linalg.norm(p_c, axis=-1), 1e-9) ** 3
             # scaled so that intensities land in a sensible range at ~1.2 m
             rgb = rho * (light_gt.astype(np.float64) * 1.3)[None, None, :] * irr[..., None]
         else:
@@ -180,8 +197,8 @@ def make_scene(F: int = 8, H: int = 120, W: int = 160, model: str = "SH1", seed:
         # perturbed initial pose
         dT = np.eye(4)
         if f > 0:
-            dT[:3, :3] = _rodrigues(np.deg2rad(pose_sigma_r_deg) * rng.standard_normal(3))
-            dT[:3, 3] = pose_sigma_t * rng.standard_normal(3)
+            dT[:3, :3] = _rodrigues(np.deg2rad(pose_sigma_r_deg) * rng_pose.standard_normal(3))
+            dT[:3, 3] = pose_sigma_t * rng_pose.standard_normal(3)
         poses_init[f] = (T @ dT).astype(np.float32)
     if model == "LED":
         light_gt = (light_gt * np.float32(1.3)).astype(np.float32)

@@ -1,0 +1,67 @@
+"""CPU: host-side logic that needs no device -- scene generator determinism and conventions, bench.py's byte model,
+and the world_size-2 (gloo) rank plumbing bench.py relies on."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+from psgradientsdf_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_scene_is_deterministic_and_quantised():
+    a = synth.make_scene(F=3, H=60, W=80, model="SH1")
+    b = synth.make_scene(F=3, H=60, W=80, model="SH1")
+    assert np.array_equal(a.color, b.color) and np.array_equal(a.depth, b.depth) and np.array_equal(a.poses_init, b.poses_init)
+    inv255 = np.float32(1.0) / np.float32(255.0)
+    u8 = np.rint(a.color * 255.0).astype(np.uint8)
+    assert np.array_equal(u8.astype(np.float32) * inv255, a.color)            # u8 * (1/255 as float), ImageLoader.h:181
+    u16 = np.rint(a.depth * 5000.0).astype(np.uint16)
+    assert np.array_equal(u16.astype(np.float32) * (np.float32(1.0) / np.float32(5000.0)), a.depth)
+    assert (a.depth > 0).mean() > 0.05
+    # poses are rigid, keyframe 0 is unperturbed
+    for P in a.poses_init:
+        R = P[:3, :3].astype(np.float64)
+        assert np.abs(R @ R.T - np.eye(3)).max() < 1e-5 and abs(np.linalg.det(R) - 1) < 1e-5
+    assert np.array_equal(a.poses_init[0], a.poses_gt[0])
+    # normals are inward pointing (away from the camera) where depth is valid
+    assert (a.nz[a.depth > 0] > 0).mean() > 0.99
+
+
+def test_models_share_geometry():
+    a = synth.make_scene(F=2, H=48, W=64, model="SH1")
+    b = synth.make_scene(F=2, H=48, W=64, model="LED")
+    assert np.array_equal(a.depth, b.depth) and np.array_equal(a.poses_init, b.poses_init) and not np.array_equal(a.color, b.color)
+
+
+def test_sweep_byte_model():
+    sys.path.insert(0, ROOT)
+    import bench
+    # 48 A + 80 S + out_block S + 128 F
+    assert bench.sweep_bytes(1000, 100, 10, 24) == 48000 + 8000 + 2400 + 1280
+    assert "128^3" in bench.METRIC
+
+
+_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+t = torch.tensor([1.0 + rank], dtype=torch.float64)
+dist.all_reduce(t, op=dist.ReduceOp.MAX)          # bench.py: max-over-ranks timing
+u = torch.tensor([float(rank + 1)], dtype=torch.float64)
+dist.all_reduce(u, op=dist.ReduceOp.SUM)          # small normal-equation blocks are summed over ranks
+assert t.item() == world and u.item() == world * (world + 1) / 2
+dist.barrier(); dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
+def test_two_rank_gloo_plumbing(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(_WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29611", str(script)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.count("ok") == 2

@@ -1,0 +1,92 @@
+"""CPU: the C restatement against the reference's own code run here (oracle/_ref), on inputs other than the committed
+fixtures, plus the harness self-check (the re-played block step leaves the same state as the reference's optimize*All).
+Skipped where the reference build is absent."""
+import numpy as np
+import pytest
+
+from tests.common import MODELS, assert_bit_equal, block_order, handoff, make_oracle, make_ref, rel_err, scene
+
+
+def _need_ref():
+    from oracle import pyref
+    if not pyref.available():
+        pytest.skip("oracle/_ref/libpsgref.so not present (needs /root/reference at build time)")
+
+
+@pytest.mark.parametrize("model", MODELS)
+def test_oracle_vs_reference_one_iteration(model):
+    _need_ref()
+    G = 28
+    sc = scene(model)
+    rv, ro = make_ref(model, G, sc)
+    ov, oo = make_oracle(model, G, sc)
+    assert_bit_equal(rv.download(), ov.download(), "fused volume")
+    (wr, lr), (wo, lo) = rv.vis(1), ov.vis()
+    assert_bit_equal(wr, wo, "visibility bits"); assert_bit_equal(lr, lo, "visibility vector lengths")
+    handoff(ro, sc); handoff(oo, sc)
+    assert_bit_equal(ro.surface(), oo.surface(), "surface list")
+    assert_bit_equal(ro.light(), oo.light(), "initial light")
+    ro.init_albedo(); oo.init_albedo()
+    assert_bit_equal(rv.download(), ov.download(), "volume after initAlbedo")
+    for nm, x, y in zip(["m", "n", "ok", "I", "rend"], ro.probe_pairs(), oo.probe_pairs()):
+        assert_bit_equal(x, y, nm)
+    gr, go_ = ro.dist_grad(), oo.dist_grad()
+    assert_bit_equal(gr[0], go_[0], "FD gradient"); assert_bit_equal(gr[1], go_[1], "FD direction")
+    rr, orr = ro.residual(), oo.residual()
+    assert_bit_equal(rr[0], orr[0], "residual"); assert_bit_equal(rr[1], orr[1], "weight")
+    er, eo = ro.energy(), oo.energy()
+    assert er[0] == eo[0] and er[1] == eo[1] and er[2] == eo[2], "energy (float serial, double re-sum, pair count)"
+    assert ro.normal_energy() == oo.normal_energy() and ro.laplacian_energy() == oo.laplacian_energy()
+    first = True
+    for blk in block_order(model):
+        kw = dict(damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
+        r1, r2 = ro.block(blk, apply=True, **kw), oo.block(blk, apply=True, **kw)
+        # the verdict gates the update for SH albedo / distance and LED pose only; the SH2 light systems sit at the
+        # edge of float convergence, where the verdict depends on the dot-product summation order
+        if blk != "light":
+            assert r1["info"] == r2["info"], (blk, r1["info"], r2["info"])
+        if first:
+            assert_bit_equal(r1["b"], r2["b"], f"{blk} rhs")
+            assert abs(r1["H"] - r2["H"]).max() == 0 if r1["H"].nnz else True
+        else:
+            assert rel_err(r1["b"], r2["b"]) < 2e-5
+        assert rel_err(r1["delta"], r2["delta"]) < (5e-4 if model == "SH2" else 5e-5), (blk, rel_err(r1["delta"], r2["delta"]))
+        er, eo = ro.energy(), oo.energy()
+        assert er[2] == eo[2] and abs(er[1] - eo[1]) <= 2e-6 * er[1], (blk, er, eo)
+        first = False
+
+
+@pytest.mark.parametrize("model", ["SH1", "LED"])
+def test_harness_replay_equals_reference_step(model):
+    """ref_opt_block (re-played Eigen statements) and the reference's own optimize*All leave bit-identical state."""
+    _need_ref()
+    G = 24
+    sc = scene(model)
+    rv1, ro1 = make_ref(model, G, sc)
+    rv2, ro2 = make_ref(model, G, sc)
+    for o in (ro1, ro2):
+        handoff(o, sc); o.init_albedo()
+    for blk in block_order(model):
+        ro1.block(blk, apply=True, damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
+        ro2.block_reference(blk, 1.0, False, True, model == "LED")
+        assert_bit_equal(rv1.download(), rv2.download(), f"volume after {blk}")
+        assert_bit_equal(ro1.light(), ro2.light(), f"light after {blk}")
+        assert_bit_equal(ro1.poses(), ro2.poses(), f"poses after {blk}")
+
+
+def test_subsampling_vs_reference():
+    _need_ref()
+    model, G = "SH1", 20
+    sc = scene(model)
+    rv, ro = make_ref(model, G, sc)
+    ov, oo = make_oracle(model, G, sc)
+    handoff(ro, sc); handoff(oo, sc)
+    ro.init_albedo(); oo.init_albedo()
+    ro.subsampling(); oo.subsampling()
+    assert_bit_equal(rv.download(), ov.download(), "upsampled volume")
+    assert_bit_equal(ro.surface(), oo.surface(), "surface after upsampling")
+    assert np.array_equal(rv.geometry()[0], ov.geometry()[0])
+    assert_bit_equal(np.asarray(rv.geometry()[2]), np.asarray(ov.geometry()[2]), "origin")
+    assert ro.voxel_size() == oo.voxel_size()
+    er, eo = ro.energy(), oo.energy()
+    assert er[0] == eo[0] and er[2] == eo[2]
