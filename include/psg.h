@@ -147,6 +147,17 @@ int psg_opt_init_albedo(psg_optimizer* opt);
 /* getPSEnergy() (PsOptimizer.cpp:47-78, LedOptimizer.cpp:40-71): sum of robust losses over active
  * (surface voxel, keyframe) pairs divided by S, accumulated in double; n_active = number of such pairs. */
 int psg_opt_energy(psg_optimizer* opt, double* E, long long* n_active);
+/* Same result as psg_opt_energy, for hosts that must not trigger device allocations once they are running (all GPU
+ * memory already committed to another owner, or a loop that cannot absorb the stall of an allocation).  It has no
+ * counterpart in the reference.  The kernel's scratch (results, per-block partial sums, arrival counter, per-keyframe
+ * table) lives in one ~4.2 MB array inside the loaded module, present on every GPU that loads the library until exit;
+ * nothing is allocated or freed.  Limits and rules:
+ *   - at most 2 097 152 surface voxels and device ordinals below 64; larger inputs are rejected with PSG_ERR_INVALID;
+ *   - the first call on a device looks up the array's device address; make that first call before any stream capture;
+ *   - all calls on a device share the array (it keeps the previous call's contents, the parts that must be zero are
+ *     cleared at the start of every call), so two calls that overlap on the GPU race -- serialise them. */
+int psg_opt_energy_noalloc(psg_optimizer* opt, double* E, long long* n_active);
+
 /* getNormalEnergy / getLaplacianEnergy / getAlbedoRegEnergy (Optimizer.cpp:86-136); any pointer may be NULL. */
 int psg_opt_reg_energies(psg_optimizer* opt, double* E_normal, double* E_laplacian, double* E_albedo);
 

@@ -91,6 +91,7 @@ def lib():
         L.psg_opt_init_albedo.argtypes = [vp]
         L.psg_opt_set_sweep_split.argtypes = [vp, C.c_int]
         L.psg_opt_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+        L.psg_opt_energy_noalloc.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_opt_reg_energies.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.psg_opt_residual.argtypes = [vp, f32p, f32p]
         L.psg_opt_probe_pairs.argtypes = [vp, f32p, f32p, vp, f32p, f32p]
@@ -302,6 +303,13 @@ class Optimizer:
         e = C.c_double()
         na = C.c_longlong()
         _check(lib().psg_opt_energy(self.h, C.byref(e), C.byref(na)))
+        return e.value, na.value
+
+    def energy_noalloc(self):
+        """psg_opt_energy_noalloc: same value as energy(), computed without any device allocation (see include/psg.h)."""
+        e = C.c_double()
+        na = C.c_longlong()
+        _check(lib().psg_opt_energy_noalloc(self.h, C.byref(e), C.byref(na)))
         return e.value, na.value
 
     def reg_energies(self):

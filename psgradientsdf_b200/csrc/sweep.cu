@@ -867,4 +867,98 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
     *En = r[0]; *El = r[1]; *Er = r[2];
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Energy evaluation that performs no device allocation.
+//
+// Some hosts hand the whole GPU memory to one owner at start-up (a framework's caching allocator, a fixed partition
+// per tenant, a real-time process that pre-allocates everything before it goes live).  For them a cudaMalloc issued
+// from inside the optimisation loop is not acceptable: it can fail although "enough" memory exists, and it stalls the
+// device while the driver services it.  psg_opt_energy() may allocate (reduction buffers and the per-keyframe table
+// grow on demand); this variant runs the same kernel with all of its scratch in one array that is part of the loaded
+// module, so the only device memory it touches beyond the caller's volume / keyframes is that array.
+//
+// Layout of the array: 8 doubles of results | arrival counter | per-keyframe parameters (64 entries) | per-block
+// partial sums for up to kNoAllocMaxSurface / 32 blocks.  About 4.2 MB, held by every GPU that loads the library until
+// the process exits.
+constexpr int kNoAllocMaxSurface = 1 << 21;   // 2 097 152 surface voxels
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocScratch {
+    double red[8];
+    unsigned counter[8];
+    FrameParams frames[kMaxFrames];
+    double partials[((size_t)kNoAllocMaxSurface / 32 + 1) * 8];
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+// device address of the array per device ordinal (the symbol name itself is only a host-side handle)
+static NoAllocScratch* g_noalloc_dev[kNoAllocMaxDevices] = { nullptr };
+
 }  // namespace psg
+
+extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_active) {
+    using namespace psg;
+    if (!o) { set_error("psg_opt_energy_noalloc: null optimizer"); return PSG_ERR_INVALID; }
+    if (!o->inited) { set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
+    if (o->S > kNoAllocMaxSurface) {
+        set_error("psg_opt_energy_noalloc: %d surface voxels exceed the built-in scratch (at most %d); use psg_opt_energy",
+                  o->S, kNoAllocMaxSurface);
+        return PSG_ERR_INVALID;
+    }
+    const int dev = o->vol->device;
+    if (dev < 0 || dev >= kNoAllocMaxDevices) { set_error("psg_opt_energy_noalloc: device ordinal %d not supported", dev); return PSG_ERR_INVALID; }
+    try {
+        PSG_CUDA(cudaSetDevice(dev));
+        if (!g_noalloc_dev[dev]) {
+            // one-time set-up for this device, with the device current: resolve the array's device address
+            void* ptr = nullptr;
+            PSG_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+            g_noalloc_dev[dev] = static_cast<NoAllocScratch*>(ptr);
+        }
+        NoAllocScratch* sc = g_noalloc_dev[dev];
+        if (o->S == 0) { const double zero = 0.0; if (E) *E = zero / zero; if (n_active) *n_active = 0; return PSG_OK; }   // E / S with S = 0, as psg_opt_energy
+
+        // per-keyframe parameters, built on the stack and copied into the array
+        FrameParams fr[kMaxFrames];
+        memset(fr, 0, sizeof(fr));
+        for (int f = 0; f < o->F; ++f) {
+            const float* P = o->poses.data() + 16 * f;
+            for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
+            if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
+        }
+        PSG_CUDA(cudaMemcpyAsync(sc->frames, fr, sizeof(FrameParams) * (size_t)(o->F > 0 ? o->F : 1), cudaMemcpyHostToDevice, o->stream));
+        // the array keeps whatever the previous call left: results and the arrival counter must start at zero
+        PSG_CUDA(cudaMemsetAsync(sc, 0, sizeof(sc->red) + sizeof(sc->counter), o->stream));
+
+        SweepArgs A;
+        memset(&A, 0, sizeof(A));
+        A.vol = o->vol->view();
+        A.surf.S = o->S; A.surf.lin = o->lin.p; A.surf.vis = o->svis.p; A.surf.nbr_lin = o->nbr_lin.p;
+        A.surf.nbr_row = o->nbr_row.p; A.surf.pos = o->pos.p;
+        A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
+        A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
+        A.frames = sc->frames; A.images = o->images.p; A.F = o->F;
+        A.vs_inv = o->vs_inv;
+        if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
+        A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
+        A.red = sc->red; A.partials = sc->partials; A.counter = sc->counter;
+
+        const int grid = (o->S + 31) / 32;
+        int W = 1;
+        while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 48) W *= 2;
+        if (o->sweep_split > 0) W = o->sweep_split;
+        const size_t smem = W > 1 ? (size_t)W * 14 * 32 * sizeof(float) : 0;
+        switch (o->set.model) {
+            case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+            case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+            default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+        }
+        count_launch();
+        PSG_LAUNCH_CHECK();
+        double r[8];
+        PSG_CUDA(cudaMemcpyAsync(r, sc->red, sizeof(r), cudaMemcpyDeviceToHost, o->stream));
+        PSG_CUDA(cudaStreamSynchronize(o->stream));
+        if (E) *E = r[0] / (double)o->S;
+        if (n_active) *n_active = (long long)(r[7] + 0.5);
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
