@@ -6,8 +6,9 @@
 
 A *step* is one outer ("LM") iteration of the alternating optimizer over the whole keyframe set
 (PsOptimizer.cpp:303-360): albedo, light, distance and pose blocks, each followed by the energy evaluation the
-reference logs -- 8 residual(+Jacobian) sweeps over all active (surface voxel, keyframe) pairs, the distance PCG and
-the small host solves.  metric = active pair evaluations per second (pairs x sweeps executed / time);
+reference logs.  The reference spends 8 sweeps over all active (surface voxel, keyframe) pairs on that; here every
+block's sweep also returns the energy of the state it started from, so 5 sweeps give the same 4 updates and 4 logged
+energies, plus the distance PCG and the small host solves.  metric = active pair evaluations per second (pairs x sweeps executed / time);
 ms_per_step = ms per LM iteration.
 
 `value`      : inputs resident in HBM when the timed region starts (volume fused, keyframes uploaded, surface list built).
@@ -180,13 +181,13 @@ def run_reference(a):
 def lm_iteration(go, model, damping=1.0):
     """One pass of the reference's while-body (PsOptimizer.cpp:303-360 / LedOptimizer.cpp:343-403)."""
     order = ["light", "albedo", "dist", "pose"] if model == "LED" else ["albedo", "light", "dist", "pose"]
-    E = None
+    energies = []
     for blk in order:
-        go.step(blk, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
-        E = go.energy()
+        info = go.step(blk, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
+        energies.append(info["energy_before"])      # = the value the reference logs after the previous block
         if blk == "dist":
             go.reg_energies()
-    return E
+    return go.energy()                              # after the last block: the convergence test needs it
 
 
 def sweep_bytes(A, S, F, out_block):
@@ -242,11 +243,10 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    sweeps_per_step = 8   # 4 block sweeps + 4 energy sweeps
+    sweeps_per_step = 5   # 4 block sweeps (each also yields the energy of the state it starts from) + 1 energy sweep
     # ---- device-resident leg
     for _ in range(a.warmup):
         lm_iteration(go, a.model)
-    psg.profile_reset(); psg.profile_enable(True)
     sampler = ClockSampler(local); sampler.start()
     launches0 = psg.kernel_launches()
     barrier()
@@ -262,6 +262,14 @@ def run_ours(a):
     barrier()
     launches = psg.kernel_launches() - launches0
     clocks = sampler.stop()
+    # same K steps once more with the library's CUDA-event launch timer on (kept out of the timed region above: two event
+    # records per launch would be charged to the step)
+    psg.profile_reset(); psg.profile_enable(True)
+    for _ in range(a.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        lm_iteration(go, a.model)
+    torch.cuda.synchronize()
     prof = psg.profile_table()
     psg.profile_enable(False)
     tt = torch.tensor([t_total], dtype=torch.float64, device=f"cuda:{local}")

@@ -63,6 +63,10 @@ typedef struct {
     float cg_error;
     int applied;
     long long n_accepted;   /* albedo channels / distances whose gated update was accepted (OptimizerAux.cpp:149,183) */
+    /* getPSEnergy() of the state the block started from: the block's sweep forms every residual anyway, so the value the
+     * reference logs after the PREVIOUS block comes for free (same definition as psg_opt_energy). */
+    double energy_before;
+    long long n_active_before;
 } psg_step_info;
 
 const char* psg_last_error(void);
@@ -140,6 +144,9 @@ int psg_opt_set_reg(psg_optimizer* opt, const float reg3[3]);
  * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
  * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */
 int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
+/* Distance solve: 0 (default) = one thread-block cluster when the surface has at most 65 536 voxels, else a cooperative
+ * grid; 2 = always the cooperative-grid kernel.  Both run the same iteration and return the same iterates. */
+int psg_opt_set_pcg_mode(psg_optimizer* opt, int mode);
 
 /* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */
 int psg_opt_init_albedo(psg_optimizer* opt);

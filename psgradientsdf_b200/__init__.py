@@ -35,7 +35,8 @@ class Settings(C.Structure):
 
 class StepInfo(C.Structure):
     _fields_ = [("n", C.c_int), ("cg_success", C.c_int), ("cg_iterations", C.c_int), ("cg_error", C.c_float),
-                ("applied", C.c_int), ("n_accepted", C.c_longlong)]
+                ("applied", C.c_int), ("n_accepted", C.c_longlong), ("energy_before", C.c_double),
+                ("n_active_before", C.c_longlong)]
 
 
 class LoopConfig(C.Structure):
@@ -90,6 +91,7 @@ def lib():
         L.psg_opt_set_reg.argtypes = [vp, f32p]
         L.psg_opt_init_albedo.argtypes = [vp]
         L.psg_opt_set_sweep_split.argtypes = [vp, C.c_int]
+        L.psg_opt_set_pcg_mode.argtypes = [vp, C.c_int]
         L.psg_opt_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_opt_energy_noalloc.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_opt_reg_energies.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -296,6 +298,9 @@ class Optimizer:
     def init_albedo(self):
         _check(lib().psg_opt_init_albedo(self.h))
 
+    def set_pcg_mode(self, mode: int):
+        _check(lib().psg_opt_set_pcg_mode(self.h, int(mode)))
+
     def set_sweep_split(self, warps: int):
         _check(lib().psg_opt_set_sweep_split(self.h, int(warps)))
 
@@ -338,7 +343,8 @@ class Optimizer:
         info = StepInfo()
         _check(lib().psg_opt_step(self.h, BLOCK[which], damping, flags, C.byref(info)))
         return dict(n=info.n, cg_success=bool(info.cg_success), iters=info.cg_iterations, err=info.cg_error,
-                    applied=bool(info.applied), n_accepted=info.n_accepted)
+                    applied=bool(info.applied), n_accepted=info.n_accepted, energy_before=info.energy_before,
+                    n_active_before=info.n_active_before)
 
     def last_system(self, which):
         """(H_blocks, b, delta) of the last light / pose step as float64 arrays."""

@@ -33,10 +33,17 @@ static std::vector<ProfRec> g_prof_recs;
 static long long g_prof_count[KID_COUNT] = {0};
 static double g_prof_ms[KID_COUNT] = {0};
 
+static std::vector<cudaEvent_t> g_event_pool;   // events are recycled: creating two per launch costs more than the launch
+static cudaEvent_t pool_get() {
+    if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
 Prof::Prof(cudaStream_t stream, int kernel_id) : st(stream), id(kernel_id) {
     g_launches += 1;
     if (g_prof_on) {
-        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        e0 = pool_get(); e1 = pool_get();
         cudaEventRecord(e0, st);
     }
 }
@@ -49,7 +56,7 @@ static void prof_collect() {
         if (cudaEventSynchronize(r.e1) == cudaSuccess && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
             g_prof_count[r.id] += 1; g_prof_ms[r.id] += (double)ms;
         }
-        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+        g_event_pool.push_back(r.e0); g_event_pool.push_back(r.e1);
     }
     g_prof_recs.clear();
 }
@@ -169,6 +176,15 @@ __global__ void __launch_bounds__(256) k_pad_images(const float* __restrict__ sr
 
 using namespace psg;
 
+void psg_optimizer::ensure_host_staging() {
+    if (host_staging) return;
+    void* p = nullptr;
+    const size_t bytes = (kMaxFrames * 64 + 8) * sizeof(double) + kMaxFrames * sizeof(FrameParams);
+    PSG_CUDA(cudaMallocHost(&p, bytes));
+    host_staging = static_cast<double*>(p);
+    host_frames = reinterpret_cast<FrameParams*>(host_staging + kMaxFrames * 64 + 8);
+}
+
 #define PSG_TRY try {
 #define PSG_CATCH                                                      \
     }                                                                  \
@@ -286,6 +302,7 @@ int psg_volume_integrate(psg_volume* v, const float* color_bgr, const float* dep
     PSG_CUDA(cudaMemcpyAsync(st + 7 * HW, n_sq_inv, HW * sizeof(float), cudaMemcpyHostToDevice, v->stream));
     launch_pack_frame(v, st, H, W);
     v->counter = counter;
+    v->generation++;
     launch_integrate(v, H, W, K, R, t, counter);
     PSG_CUDA(cudaStreamSynchronize(v->stream));
     return PSG_OK;
@@ -322,6 +339,7 @@ int psg_volume_upload(psg_volume* v, const float* aos8) {
         launch_aos_to_soa(v, v->staging.p, b, c);
         PSG_CUDA(cudaStreamSynchronize(v->stream));
     }
+    v->generation++;
     return PSG_OK;
     PSG_CATCH
 }
@@ -371,8 +389,10 @@ int psg_opt_destroy(psg_optimizer* o) {
     if (!o) return PSG_OK;
     cudaSetDevice(o->vol->device);
     o->images.release(); o->frames.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
-    o->svis.release(); o->pos.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
-    o->frame_idx_dev.release(); o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release();
+    o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
+    o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
+    if (o->host_staging) cudaFreeHost(o->host_staging);
+    o->frame_idx_dev.release(); o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
     delete o;
     return PSG_OK;
 }
@@ -510,6 +530,13 @@ int psg_opt_set_sweep_split(psg_optimizer* o, int warps) {
     return PSG_OK;
 }
 
+int psg_opt_set_pcg_mode(psg_optimizer* o, int mode) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (mode != 0 && mode != 2) { set_error("psg_opt_set_pcg_mode: %d is not 0 or 2", mode); return PSG_ERR_INVALID; }
+    o->pcg_mode = mode;
+    return PSG_OK;
+}
+
 int psg_opt_init_albedo(psg_optimizer* o) {
     PSG_NEED_INIT(o)
     PSG_TRY
@@ -640,6 +667,8 @@ int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step
         // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242)
         if (led || ok) { long long acc = 0; apply_dist_update(o, &acc); inf.applied = 1; inf.n_accepted = acc; }
     }
+    inf.energy_before = o->S > 0 ? o->last_energy_sum / (double)o->S : 0.0;
+    inf.n_active_before = o->last_active;
     if (info) *info = inf;
     return PSG_OK;
     PSG_CATCH

@@ -184,23 +184,41 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
     std::vector<float> E_vec(1, E_total);
 
     const char* kAlbedo = "albedo"; const char* kLight = "light"; const char* kDist = "distance"; const char* kPose = "pose";
+    // The reference evaluates getPSEnergy() after every block.  Here every block's own sweep already yields the energy of
+    // the state it started from (psg_step_info::energy_before), so the log line of block k is completed when block k+1 has
+    // run, and only the last enabled block of an iteration needs an explicit energy sweep.
+    const char* pending_label = nullptr;
+    auto finish_pending = [&](float E_now) {
+        if (!pending_label) return;
+        e.E = E_now;
+        if (echo) std::cout << "===> [" << R.iterations << "]: after " << pending_label << " optimization: ";
+        if (file.is_open()) file << "===> [" << R.iterations << "]: after " << pending_label << " optimization: \n";
+        E_total = total_energy(o, e, file, echo);
+        pending_label = nullptr;
+    };
     auto run_block = [&](int block, const char* label) -> int {
         int flags = 0;
         if (block == PSG_BLOCK_ALBEDO && albedo_reg) flags |= PSG_REG_ALBEDO;
         if (block == PSG_BLOCK_DIST && normal_reg) flags |= PSG_REG_NORMAL;
         if (block == PSG_BLOCK_DIST && laplacian_reg) flags |= PSG_REG_LAPLACIAN;
-        const int st = psg_opt_step(o, block, damping, flags, nullptr);
+        psg_step_info info;
+        const int st = psg_opt_step(o, block, damping, flags, &info);
         if (st != PSG_OK) return st;
-        const int st2 = ps_energy(o, &e.E);
-        if (st2 != PSG_OK) return st2;
+        finish_pending((float)info.energy_before);   // the previous block's line, with the regulariser energies of that time
         if (block == PSG_BLOCK_ALBEDO && albedo_reg) { psg_opt_reg_energies(o, nullptr, nullptr, &dr); e.Er = (float)dr; }
         if (block == PSG_BLOCK_DIST) {
             if (normal_reg) { psg_opt_reg_energies(o, &dn, nullptr, nullptr); e.En = (float)dn; }
             if (laplacian_reg) { psg_opt_reg_energies(o, nullptr, &dl, nullptr); e.El = (float)dl; }
         }
-        if (echo) std::cout << "===> [" << R.iterations << "]: after " << label << " optimization: ";
-        if (file.is_open()) file << "===> [" << R.iterations << "]: after " << label << " optimization: \n";
-        E_total = total_energy(o, e, file, echo);
+        pending_label = label;
+        return PSG_OK;
+    };
+    auto end_of_iteration = [&]() -> int {
+        if (!pending_label) return PSG_OK;
+        float E_now = 0.f;
+        const int st = ps_energy(o, &E_now);
+        if (st != PSG_OK) return st;
+        finish_pending(E_now);
         return PSG_OK;
     };
 
@@ -219,6 +237,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
         }
         if (cfg->distance) PSG_RUN(run_block(PSG_BLOCK_DIST, kDist));
         if (cfg->pose) PSG_RUN(run_block(PSG_BLOCK_POSE, kPose));
+        PSG_RUN(end_of_iteration());
         const auto t1 = std::chrono::steady_clock::now();
         const double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
         ms_sum += ms;

@@ -43,6 +43,15 @@ struct SurfView {
     const int* nbr_lin;                 // 3*S linear index of the finite-difference neighbour per axis (or -1)
     const int* nbr_row;                 // 3*S surface row of that neighbour, -1 if it is not a surface voxel
     const unsigned char* pos;           // S   bit a set = forward difference along axis a
+    // Slot-ordered work list of the sweeps.  Slot t holds surface row perm[t]; slots are sorted by keyframe visibility so
+    // that the 32 voxels of a warp see (nearly) the same keyframes (in lin order a warp straddles both sides of the
+    // object and half of its lanes idle).  Each field is one coalesced 128-bit load per lane:
+    const unsigned long long* pvis;     // S   keyframe visibility of the slot
+    float4* rec0;                       // S   {dist, g_hat.xyz}            g_hat = normalised stored gradient
+    float4* rec1;                       // S   {r, g, b, bits(pos)}
+    float4* rec2;                       // S   {fd.xyz, bits(row)}          fd = finite-difference gradient, row = perm[t]
+    float4* rec3;                       // S   {voxel centre in world xyz, bits(lin)}
+    float4* rec4;                       // S   {normalised fd xyz, -}
 };
 
 struct Camera { float fx, fy, cx, cy; int H, W; };

@@ -64,6 +64,7 @@ struct psg_volume {
     long long N = 0;
     float vs = 0.f, shift[3] = {0, 0, 0}, origin[3] = {0, 0, 0}, T = 0.f, invT = 0.f, zmin = 0.f, zmax = 0.f;
     int max_frames = 64, nwords = 1, counter = 0;
+    unsigned long long generation = 1;       // bumped whenever the host or fusion rewrites voxel records
     psg::DevBuf<float> f[8];                 // dist gx gy gz w r g b
     psg::DevBuf<unsigned long long> vis;     // nwords * N
     psg::DevBuf<float> frame;                // packed per-pixel fusion inputs (8 floats / pixel)
@@ -91,6 +92,11 @@ struct psg_optimizer {
     psg::DevBuf<int> lin, nbr_lin, nbr_row, inc;
     psg::DevBuf<unsigned long long> svis;
     psg::DevBuf<unsigned char> pos;
+    psg::DevBuf<float4> rec0, rec1, rec2, rec3, rec4;   // slot-ordered voxel records (SurfView)
+    psg::DevBuf<unsigned long long> pvis, sort_keys, sort_keys2;
+    psg::DevBuf<int> perm, sort_vals;
+    psg::DevBuf<unsigned char> sort_tmp;
+    unsigned long long vol_gen_seen = 0;     // volume generation the records were gathered from
     psg::DevBuf<unsigned int> mask, prefix;  // membership bitmask over the volume + exclusive popcount prefix
     psg::DevBuf<unsigned int> block_counts;
     psg::DevBuf<int> frame_idx_dev;
@@ -98,12 +104,20 @@ struct psg_optimizer {
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
     psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
+    int pcg_mode = 0;                        // 0 = auto (cluster kernel for small surfaces), 2 = always the cooperative-grid kernel
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
     psg::DevBuf<double> pcg_partials;
+    psg::DevBuf<float> pcg_pbuf;             // double-buffered search direction of the cluster PCG
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
     std::vector<float> lastvb, lastvd;
     int last_n = 0, last_block = -1;
+    // pinned host staging: [kMaxFrames*64 + 8] doubles of reduction results, then the per-keyframe table
+    double* host_staging = nullptr;
+    psg::FrameParams* host_frames = nullptr;
+    void ensure_host_staging();
+    double last_energy_sum = 0.0;            // sum of robust losses seen by the last sweep (state before its update)
+    long long last_active = 0;
     cudaStream_t stream = nullptr;
 };
 
@@ -118,6 +132,8 @@ void launch_soa_to_aos(psg_volume* v, float* aos_dev, long long begin, long long
 
 // ---- surface.cu
 void build_surface(psg_optimizer* o, bool reindex_vis);
+void refresh_records(psg_optimizer* o);      // re-gather rec0..2 from the volume (no allocation)
+SurfView surf_view(psg_optimizer* o);        // refreshes the records first if the volume changed under them
 void launch_upsample(psg_optimizer* o);
 
 // ---- sweep.cu

@@ -8,6 +8,8 @@
 // Membership is a bitmask over the volume (1 bit / voxel) plus an exclusive popcount prefix per 32-voxel word
 // (a rank structure, 0.25 B / voxel instead of a 4 B / voxel row map): member(l) is a bit test and
 // row(l) = prefix[l/32] + popc(mask[l/32] below bit l%32), which is also what keeps the list in ascending lin order.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "psg_host.h"
 
 namespace psg {
@@ -211,6 +213,73 @@ __global__ void __launch_bounds__(256) k_upsample(VolView src, VolView dst, floa
     for (int w = 0; w < dst.nwords; ++w) dst.vis[(long long)w * dst.N + lin] = src.vis[(long long)w * src.N + pl];
 }
 
+// Slot-ordered records gathered from the volume planes (slot t -> surface row perm[t]).
+__global__ void __launch_bounds__(256) k_gather_records(VolView v, const int* __restrict__ perm, const int* __restrict__ lin_in,
+                                                       const unsigned long long* __restrict__ vis_in, const int* __restrict__ nbr_lin,
+                                                       const unsigned char* __restrict__ pos, int S, float vs_inv, SurfView out,
+                                                       unsigned long long* __restrict__ pvis) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S) return;
+    const int s = perm[t];
+    const int lin = lin_in[s];
+    int idx[3];
+    line2idx(lin, v.dims, idx);
+    const float d = v.dist[lin];
+    const float g[3] = { v.gx[lin], v.gy[lin], v.gz[lin] };
+    float gh[3], fd[3], nfd[3];
+    normalized3(g, gh);
+    const unsigned char pb = pos[s];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const int nl = nbr_lin[a * S + s];
+        const float p = ((pb >> a) & 1) ? 1.f : -1.f;
+        const float dn = nl >= 0 ? v.dist[nl] : d;
+        fd[a] = (p * (dn - d)) * vs_inv;      // Optimizer::computeDistGrad (Optimizer.cpp:346-351)
+    }
+    normalized3(fd, nfd);
+    out.rec0[t] = make_float4(d, gh[0], gh[1], gh[2]);
+    out.rec1[t] = make_float4(v.r[lin], v.g[lin], v.b[lin], __int_as_float((int)pb));
+    out.rec2[t] = make_float4(fd[0], fd[1], fd[2], __int_as_float(s));
+    out.rec3[t] = make_float4(v.origin[0] + v.vs * (float)idx[0], v.origin[1] + v.vs * (float)idx[1],
+                              v.origin[2] + v.vs * (float)idx[2], __int_as_float(lin));   // VoxelGrid::voxel2world
+    out.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
+    pvis[t] = vis_in[s];
+}
+
+static SurfView raw_view(psg_optimizer* o) {
+    SurfView sv;
+    sv.S = o->S; sv.lin = o->lin.p; sv.vis = o->svis.p; sv.nbr_lin = o->nbr_lin.p; sv.nbr_row = o->nbr_row.p; sv.pos = o->pos.p;
+    sv.pvis = o->pvis.p;
+    sv.rec0 = o->rec0.p; sv.rec1 = o->rec1.p; sv.rec2 = o->rec2.p; sv.rec3 = o->rec3.p; sv.rec4 = o->rec4.p;
+    return sv;
+}
+
+void refresh_records(psg_optimizer* o) {
+    if (o->S > 0) {
+        { Prof pf(o->stream, KID_SURF_NEIGHBORS);
+          k_gather_records<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), o->perm.p, o->lin.p, o->svis.p, o->nbr_lin.p,
+                                                                      o->pos.p, o->S, o->vs_inv, raw_view(o), o->pvis.p); }
+        PSG_LAUNCH_CHECK();
+    }
+    o->vol_gen_seen = o->vol->generation;
+}
+
+SurfView surf_view(psg_optimizer* o) {
+    if (o->vol_gen_seen != o->vol->generation) refresh_records(o);
+    return raw_view(o);
+}
+
+// sort key of a row: (64 - number of visible keyframes) above the visibility word, so that rows with equal masks are
+// adjacent and the rows with most work come first (no heavy blocks left for the tail of the launch)
+__global__ void __launch_bounds__(256) k_sort_keys(const unsigned long long* __restrict__ vis, unsigned long long* __restrict__ keys,
+                                                  int* __restrict__ vals, int n, int F) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long m = vis[i];
+    keys[i] = (F <= 57) ? (((unsigned long long)(64 - __popcll(m)) << F) | m) : m;
+    vals[i] = i;
+}
+
 void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     psg_volume* vol = o->vol;
     const VolView v = vol->view();
@@ -238,6 +307,8 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     o->S = (int)total;
     const size_t S = (size_t)(o->S > 0 ? o->S : 1);
     o->lin.alloc(S); o->svis.alloc(S); o->nbr_lin.alloc(3 * S); o->nbr_row.alloc(3 * S); o->pos.alloc(S); o->inc.alloc(6 * S);
+    o->rec0.alloc(S); o->rec1.alloc(S); o->rec2.alloc(S); o->rec3.alloc(S); o->rec4.alloc(S);
+    o->pvis.alloc(S); o->perm.alloc(S); o->sort_keys.alloc(S); o->sort_vals.alloc(S);
     if (o->S > 0) {
         { Prof pf(o->stream, KID_SURF_SCATTER);
           k_surface_scatter<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->prefix.p, nw, (int)wpb,
@@ -248,6 +319,21 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
                                                                  o->nbr_row.p, o->pos.p, o->inc.p); }
         PSG_LAUNCH_CHECK();
     }
+    if (o->S > 0) {
+        // slot order: stable radix sort of the rows by keyframe-visibility word (set-up time only; CUB library sort)
+        o->sort_keys2.alloc((size_t)o->S);
+        k_sort_keys<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->sort_keys.p, o->sort_vals.p, o->S, o->F);
+        PSG_LAUNCH_CHECK();
+        const int end_bit = o->F <= 57 ? o->F + 7 : 64;
+        size_t tmp_bytes = 0;
+        PSG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p, o->S,
+                                                 0, end_bit, o->stream));
+        o->sort_tmp.alloc(tmp_bytes);
+        PSG_CUDA(cub::DeviceRadixSort::SortPairs(o->sort_tmp.p, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p,
+                                                 o->S, 0, end_bit, o->stream));
+        count_launch(4);
+    }
+    refresh_records(o);
     PSG_CUDA(cudaStreamSynchronize(o->stream));
 }
 
@@ -275,6 +361,7 @@ void launch_upsample(psg_optimizer* o) {
     vol->vs = (float)((double)vol->vs * 0.5);
     for (int a = 0; a < 3; ++a) vol->dims[a] *= 2;
     vol->N = N8;
+    vol->generation++;
     const float half_vs = (float)(0.5 * (double)vol->vs);
     for (int a = 0; a < 3; ++a) vol->origin[a] = (vol->shift[a] - half_vs * (float)vol->dims[a]) - half_vs * 1.f;
     // Optimizer: voxel_size_ *= 0.5; voxel_size_inv_ = 1.0 / voxel_size_ (OptimizerAux.cpp:679-680)

@@ -38,7 +38,8 @@ struct SweepArgs {
     float led[3];
     float damping, reg_n, reg_l;
     int flags;
-    double* red;        // reductions (zeroed by the launcher)
+    double* red;        // per-keyframe reductions (zeroed by the launcher)
+    double* scal;       // 8 scalar results: [0..5] mode specific, [6] sum of robust losses, [7] active pairs
     double* partials;   // [gridDim.x][8] per-block scalar partials, combined in block order by the last block
     unsigned* counter;  // arrival counter for that (self-resetting)
     float* out0;        // mode dependent per-voxel outputs
@@ -154,31 +155,62 @@ __device__ __forceinline__ void warp_accumulate(float* vals, int lane, double* d
     if (lane < V && s != 0.f) atomicAdd(&dst[lane], (double)s);
 }
 
-// Deterministic grid-wide sum of n <= 8 per-block doubles: every block parks its values, the last block to arrive adds
-// them up in block order (fixed association) and writes out[0..n).
-__device__ __forceinline__ void grid_sum_scalars(const double* block_vals, int n, double* partials, unsigned* counter,
-                                                 double* out, bool* s_last) {
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < n; ++i) partials[(size_t)blockIdx.x * 8 + i] = block_vals[i];
-        __threadfence();
-        const unsigned ticket = atomicAdd(counter, 1u);
-        *s_last = (ticket == gridDim.x - 1);
+// Deterministic grid-wide sum of 8 per-block doubles, two levels so that no single block serialises the whole grid:
+// blocks are grouped by kRedGroup; the last block of a group to arrive adds the group's partials (fixed association:
+// thread t takes elements t, t + blockDim, ... -- independent, coalesced loads -- then the threads holding the same slot
+// are combined in thread order) into a group partial; the last group to finish adds the group partials the same way and
+// writes out[0..8).  Counters reset themselves.
+constexpr int kRedGroup = 128;
+
+__device__ __forceinline__ void fixed_order_sum8(const double* src, size_t n /* multiple of 8 */, double* dst, double* s_scratch) {
+    const int t = threadIdx.x;
+    double acc = 0.0;
+    size_t e = t;
+    for (; e + 3 * (size_t)blockDim.x < n; e += 4 * (size_t)blockDim.x) {
+        const double a0 = __ldcg(src + e), a1 = __ldcg(src + e + blockDim.x);
+        const double a2 = __ldcg(src + e + 2 * (size_t)blockDim.x), a3 = __ldcg(src + e + 3 * (size_t)blockDim.x);
+        acc += a0; acc += a1; acc += a2; acc += a3;
     }
+    for (; e < n; e += blockDim.x) acc += __ldcg(src + e);
     __syncthreads();
-    if (*s_last && threadIdx.x < 32) {
-        __threadfence();
-        for (int i = 0; i < n; ++i) {
-            double t = 0.0;
-            for (unsigned b = threadIdx.x; b < gridDim.x; b += 32) t += partials[(size_t)b * 8 + i];
-            t = warp_sum(t);
-            if (threadIdx.x == 0) out[i] = t;
-        }
-        if (threadIdx.x == 0) *counter = 0u;
+    s_scratch[t] = acc;
+    __syncthreads();
+    if (t < 8) {
+        double v = 0.0;
+        for (int j = t; j < (int)blockDim.x; j += 8) v += s_scratch[j];
+        dst[t] = v;
     }
 }
 
+__device__ __forceinline__ void grid_sum_scalars(const double* block_vals, double* partials, unsigned* counter, double* out,
+                                                 bool* s_last, double* s_scratch /* blockDim.x doubles */) {
+    const int t = threadIdx.x;
+    const unsigned ngroups = (gridDim.x + kRedGroup - 1) / kRedGroup;
+    const unsigned group = blockIdx.x / kRedGroup;
+    const unsigned gfirst = group * kRedGroup;
+    const unsigned gsize = min((unsigned)kRedGroup, gridDim.x - gfirst);
+    double* group_partials = partials + (size_t)gridDim.x * 8;   // [ngroups][8] behind the block partials
+    if (t < 8) partials[(size_t)blockIdx.x * 8 + t] = block_vals[t];
+    __threadfence();
+    __syncthreads();
+    if (t == 0) *s_last = (atomicAdd(counter + 1 + group, 1u) == gsize - 1);
+    __syncthreads();
+    if (!*s_last) return;
+    __threadfence();
+    fixed_order_sum8(partials + (size_t)gfirst * 8, (size_t)gsize * 8, group_partials + (size_t)group * 8, s_scratch);
+    if (t == 0) counter[1 + group] = 0u;
+    __threadfence();
+    __syncthreads();
+    if (t == 0) *s_last = (atomicAdd(counter, 1u) == ngroups - 1);
+    __syncthreads();
+    if (!*s_last) return;
+    __threadfence();
+    fixed_order_sum8(group_partials, (size_t)ngroups * 8, out, s_scratch);
+    if (t == 0) *counter = 0u;
+}
+
 template <int MODEL, int MODE>
-__global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
+__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_POSE || MODE == M_LIGHT) ? 2 : 4) k_sweep(SweepArgs A) {
     constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
     constexpr bool LED = (MODEL == PSG_MODEL_LED);
     // per-keyframe reduction width (padded to a power of two / multiple of 32 lanes)
@@ -190,38 +222,35 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
     extern __shared__ float s_dyn[];   // [W][NACC][32]
     __shared__ double s_red[kMaxSplit][8];
     __shared__ double s_tot[8];
+    __shared__ double s_scratch[32 * kMaxSplit];
     __shared__ bool s_last;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int S = A.surf.S;
-    const int s = blockIdx.x * 32 + lane;
-    const bool live = s < S;
+    const int slot = blockIdx.x * 32 + lane;   // position in the visibility-sorted work list
+    const bool live = slot < S;
 
-    // ---- voxel record
-    int lin = 0, idx[3] = {0, 0, 0};
+    // ---- voxel record (five coalesced 128-bit loads; everything per-voxel is precomputed by k_gather_records)
+    int lin = 0, s = 0;
     unsigned long long vis = 0ull;
-    float dist = 0.f, g[3] = {0, 0, 0}, gh[3] = {0, 0, 0}, rho[3] = {0, 0, 0}, q0[3] = {0, 0, 0};
+    float dist = 0.f, gh[3] = {0, 0, 0}, rho[3] = {0, 0, 0}, q0[3] = {0, 0, 0};
     float fd[3] = {0, 0, 0}, posf[3] = {1, 1, 1}, nfd[3] = {0, 0, 0};
     if (live) {
-        lin = A.surf.lin[s];
-        vis = A.surf.vis[s];
-        line2idx(lin, A.vol.dims, idx);
-        dist = A.vol.dist[lin];
-        g[0] = A.vol.gx[lin]; g[1] = A.vol.gy[lin]; g[2] = A.vol.gz[lin];
-        rho[0] = A.vol.r[lin]; rho[1] = A.vol.g[lin]; rho[2] = A.vol.b[lin];
-        normalized3(g, gh);
-#pragma unroll
-        for (int a = 0; a < 3; ++a) q0[a] = (A.vol.origin[a] + A.vol.vs * (float)idx[a]) - dist * gh[a];
-        // Optimizer::computeDistGrad (Optimizer.cpp:287-364)
-        const unsigned char pb = A.surf.pos[s];
+        vis = A.surf.pvis[slot];
+        const float4 r0 = A.surf.rec0[slot], r1 = A.surf.rec1[slot], r2 = A.surf.rec2[slot], r3 = A.surf.rec3[slot],
+                     r4 = A.surf.rec4[slot];
+        dist = r0.x; gh[0] = r0.y; gh[1] = r0.z; gh[2] = r0.w;
+        rho[0] = r1.x; rho[1] = r1.y; rho[2] = r1.z;
+        fd[0] = r2.x; fd[1] = r2.y; fd[2] = r2.z; s = __float_as_int(r2.w);
+        lin = __float_as_int(r3.w);
+        nfd[0] = r4.x; nfd[1] = r4.y; nfd[2] = r4.z;
+        const int pb = __float_as_int(r1.w);
+        const float pw[3] = { r3.x, r3.y, r3.z };
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-            const int nl = A.surf.nbr_lin[a * S + s];
             posf[a] = ((pb >> a) & 1) ? 1.f : -1.f;
-            const float dn = nl >= 0 ? A.vol.dist[nl] : dist;
-            fd[a] = (posf[a] * (dn - dist)) * A.vs_inv;
+            q0[a] = pw[a] - dist * gh[a];
         }
-        normalized3(fd, nfd);
     }
     float sh_n[NB];   // SH basis at the finite-difference normal (shading in the residual)
     float sh_g[NB];   // SH basis at the stored gradient (albedo / light Jacobians)
@@ -239,6 +268,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
     // ---- mode-specific per-voxel state
     double acc_d[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // ENERGY: [0] loss; LED_INIT: I[3], rend[3]; LED light: H[3], b[3]
     long long cnt = 0;
+    double eloss = 0.0;                           // robust loss of the current state (every mode that forms residuals)
+    int accepted = 0;
     float vacc[14];                               // ALBEDO: H[3], b[3]; INIT_ALBEDO: sum[3]; DIST: A(10) + b(4)
 #pragma unroll
     for (int i = 0; i < 14; ++i) vacc[i] = 0.f;
@@ -274,13 +305,20 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
     const float fx = A.cam.fx, fy = A.cam.fy, cx = A.cam.cx, cy = A.cam.cy;
 
     // ---- keyframe loop: ascending, every lane of a warp on the same keyframe; warp w takes every W-th visible keyframe
-    int slot = 0;
+    if (W > 1) {   // keep every W-th set bit, starting with the warp-th (one pass over the bits, outside the hot loop)
+        unsigned long long mine = 0ull, rest = uni;
+        int k = 0;
+        while (rest) {
+            const unsigned long long low = rest & (0ull - rest);
+            if ((k & (W - 1)) == warp) mine |= low;
+            rest ^= low;
+            ++k;
+        }
+        uni = mine;
+    }
     while (uni) {
         const int f = __ffsll((long long)uni) - 1;
         uni &= uni - 1;
-        const bool mine = (slot & (W - 1)) == warp;
-        ++slot;
-        if (!mine) continue;
         FrameParams P;
         {
             const float4* src = reinterpret_cast<const float4*>(A.frames + f);
@@ -292,7 +330,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
 
         bool ok = false;
         float pt[3] = {0, 0, 1}, I[3] = {0, 0, 0}, rend[3] = {0, 0, 0}, r[3] = {0, 0, 0}, w[3] = {0, 0, 0};
-        float m = 0.f, n = 0.f;
+        float m = 0.f, n = 0.f, pair_loss = 0.f;
         Footprint fp; fp.x = 0; fp.y = 0;
         if (act) {
             const float q[3] = { q0[0] - P.t[0], q0[1] - P.t[1], q0[2] - P.t[2] };
@@ -318,12 +356,27 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
                     for (int c = 0; c < 3; ++c) rend[c] = rho[c] * irr;
                 }
 #pragma unroll
-                for (int c = 0; c < 3; ++c) { r[c] = I[c] - rend[c]; w[c] = irls_weight(A.loss, r[c]); }
+                for (int c = 0; c < 3; ++c) r[c] = I[c] - rend[c];
+                if (A.loss.loss == PSG_LOSS_CAUCHY) {
+                    // Cauchy (every shipped config): w = 1 / (1 + (r/lambda)^2), loss = sum_c log(1 + (r_c/lambda)^2).
+                    // One division per channel serves both; the three logarithms are taken as one log of the product
+                    // (|r| <= 1 and lambda > 0 keep it far from overflow), which changes a per-pair loss by ~1 ulp.
+                    float tq[3];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) { const float q = r[c] / A.loss.lambda; tq[c] = 1.f + q * q; w[c] = 1.f / tq[c]; }
+                    if constexpr (MODE != M_PROBE && MODE != M_INIT_ALBEDO && MODE != M_LED_INIT) pair_loss = logf((tq[0] * tq[1]) * tq[2]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) w[c] = irls_weight(A.loss, r[c]);
+                    if constexpr (MODE != M_PROBE && MODE != M_INIT_ALBEDO && MODE != M_LED_INIT) pair_loss = robust_loss3(A.loss, r);
+                }
             }
         }
 
+        if constexpr (MODE != M_PROBE && MODE != M_INIT_ALBEDO && MODE != M_LED_INIT) {
+            if (ok) { eloss += (double)pair_loss; ++cnt; }
+        }
         if constexpr (MODE == M_ENERGY) {
-            if (ok) { acc_d[0] += (double)robust_loss3(A.loss, r); ++cnt; }
         } else if constexpr (MODE == M_INIT_ALBEDO) {
             if (ok) { vacc[0] += I[0]; vacc[1] += I[1]; vacc[2] += I[2]; ++icount; }
         } else if constexpr (MODE == M_LED_INIT) {
@@ -563,33 +616,16 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
             }
         }
     }
-    // (b) scalar sums: warp -> block (warp order) -> grid (block order, last block)
-    if constexpr (MODE == M_ENERGY || MODE == M_LED_INIT || (MODE == M_LIGHT && LED)) {
-        constexpr int ND = (MODE == M_ENERGY) ? 1 : 6;
-#pragma unroll
-        for (int i = 0; i < ND; ++i) { const double v = warp_sum(acc_d[i]); if (lane == 0) s_red[warp][i] = v; }
-        const long long c2 = warp_sum_ll(cnt);
-        if (lane == 0) s_red[warp][7] = (double)c2;
-        __syncthreads();
-        if (tid < 8) {
-            double v = 0.0;
-            if (tid < ND || tid == 7) for (int i = 0; i < W; ++i) v += s_red[i][tid];
-            s_tot[tid] = v;
-        }
-        __syncthreads();
-        grid_sum_scalars(s_tot, 8, A.partials, A.counter, A.red, &s_last);
-    }
     if constexpr (MODE == M_INIT_ALBEDO) {
         if (warp == 0 && live && icount) {
-            A.vol.r[lin] = vacc[0] / (float)icount;
-            A.vol.g[lin] = vacc[1] / (float)icount;
-            A.vol.b[lin] = vacc[2] / (float)icount;
+            const float nr = vacc[0] / (float)icount, ng = vacc[1] / (float)icount, nbl = vacc[2] / (float)icount;
+            A.vol.r[lin] = nr; A.vol.g[lin] = ng; A.vol.b[lin] = nbl;
+            A.surf.rec1[slot] = make_float4(nr, ng, nbl, A.surf.rec1[slot].w);
         }
     }
     if constexpr (MODE == M_ALBEDO) {
         // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
         // Optimizer::updateAlbedo gate (OptimizerAux.cpp:120-147): accept a channel only if it stays strictly in (0, 1)
-        int accepted = 0;
         if (warp == 0 && live) {
             float* chan[3] = { A.vol.r, A.vol.g, A.vol.b };
 #pragma unroll
@@ -599,14 +635,11 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
                 const float inv = (Hd != 0.f) ? 1.f / Hd : 1.f;
                 const float delta = inv * vacc[3 + c];
                 const float nv = rho[c] - delta;
-                if ((double)nv > 0.0 && (double)nv < 1.0) { chan[c][lin] = nv; ++accepted; }
+                if ((double)nv > 0.0 && (double)nv < 1.0) { chan[c][lin] = nv; rho[c] = nv; ++accepted; }
                 if (A.out0) { A.out0[3 * (long long)s + c] = vacc[3 + c]; A.out1[3 * (long long)s + c] = delta; }
             }
+            if (accepted) A.surf.rec1[slot] = make_float4(rho[0], rho[1], rho[2], A.surf.rec1[slot].w);
         }
-        const long long c2 = warp_sum_ll(accepted);
-        if (tid == 0) { for (int i = 0; i < 8; ++i) s_tot[i] = 0.0; s_tot[0] = (double)c2; }
-        __syncthreads();
-        grid_sum_scalars(s_tot, 1, A.partials, A.counter, A.red, &s_last);
     }
     if constexpr (MODE == M_DIST) {
         if (warp == 0 && live) {
@@ -652,6 +685,22 @@ __global__ void __launch_bounds__(32 * kMaxSplit) k_sweep(SweepArgs A) {
             for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
         }
     }
+    // (b) scalar sums: warp -> block (warp order) -> grid (fixed order, last block): [0..5] mode specific, [6] loss, [7] pairs
+    if constexpr (MODE != M_PROBE && MODE != M_INIT_ALBEDO) {
+        double v8[8] = { acc_d[0], acc_d[1], acc_d[2], acc_d[3], acc_d[4], acc_d[5], eloss, (double)cnt };
+        if constexpr (MODE == M_ALBEDO) v8[5] = (double)accepted;
+        __syncthreads();   // s_dyn / s_red reuse
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const double v = warp_sum(v8[i]); if (lane == 0) s_red[warp][i] = v; }
+        __syncthreads();
+        if (tid < 8) {
+            double v = 0.0;
+            for (int i = 0; i < W; ++i) v += s_red[i][tid];
+            s_tot[tid] = v;
+        }
+        __syncthreads();
+        grid_sum_scalars(s_tot, A.partials, A.counter, A.scal, &s_last, s_scratch);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
@@ -660,8 +709,7 @@ static SweepArgs base_args(psg_optimizer* o) {
     SweepArgs A;
     memset(&A, 0, sizeof(A));
     A.vol = o->vol->view();
-    A.surf.S = o->S; A.surf.lin = o->lin.p; A.surf.vis = o->svis.p; A.surf.nbr_lin = o->nbr_lin.p;
-    A.surf.nbr_row = o->nbr_row.p; A.surf.pos = o->pos.p;
+    A.surf = surf_view(o);
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
     A.frames = o->frames.p; A.images = o->images.p; A.F = o->F;
@@ -670,11 +718,13 @@ static SweepArgs base_args(psg_optimizer* o) {
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
     o->red.alloc(kMaxFrames * 64 + 8);
     A.red = o->red.p;
+    A.scal = o->red.p + kMaxFrames * 64;
     const size_t grid = (size_t)(o->S + 31) / 32 + 1;
-    o->sweep_partials.alloc(grid * 8);
-    if (!o->sweep_counter.p) {
-        o->sweep_counter.alloc(4);
-        PSG_CUDA(cudaMemsetAsync(o->sweep_counter.p, 0, 4 * sizeof(unsigned), o->stream));
+    const size_t ngroups = grid / kRedGroup + 2;
+    o->sweep_partials.alloc((grid + ngroups) * 8);
+    if (o->sweep_counter.n < ngroups + 1) {
+        o->sweep_counter.alloc(ngroups + 1);
+        PSG_CUDA(cudaMemsetAsync(o->sweep_counter.p, 0, (ngroups + 1) * sizeof(unsigned), o->stream));
     }
     A.partials = o->sweep_partials.p;
     A.counter = o->sweep_counter.p;
@@ -683,16 +733,16 @@ static SweepArgs base_args(psg_optimizer* o) {
 
 void upload_frames(psg_optimizer* o) {
     if (!o->frames_dirty) return;
-    std::vector<FrameParams> fr((size_t)(o->F > 0 ? o->F : 1));
-    memset(fr.data(), 0, fr.size() * sizeof(FrameParams));
+    o->ensure_host_staging();
+    FrameParams* fr = o->host_frames;   // pinned; every API call ends with a stream sync, so the previous copy has finished
+    memset(fr, 0, sizeof(FrameParams) * kMaxFrames);
     for (int f = 0; f < o->F; ++f) {
         const float* P = o->poses.data() + 16 * f;
         for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
         if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
     }
-    o->frames.alloc(fr.size());
-    PSG_CUDA(cudaMemcpyAsync(o->frames.p, fr.data(), fr.size() * sizeof(FrameParams), cudaMemcpyHostToDevice, o->stream));
-    PSG_CUDA(cudaStreamSynchronize(o->stream));   // fr is a temporary
+    o->frames.alloc(kMaxFrames);
+    PSG_CUDA(cudaMemcpyAsync(o->frames.p, fr, sizeof(FrameParams) * (size_t)(o->F > 0 ? o->F : 1), cudaMemcpyHostToDevice, o->stream));
     o->frames_dirty = false;
 }
 
@@ -701,9 +751,9 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
     if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
     if (o->S == 0) return;
     const int grid = (o->S + 31) / 32;
-    // keyframe split: double W while the launch still has fewer warps than the GPU holds (148 SMs x 48 warps)
+    // keyframe split: double W while the launch stays within ~32 warps per SM (beyond that the replicated prologue costs more than it hides)
     int W = 1;
-    while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 48) W *= 2;
+    while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
     if (o->sweep_split > 0) W = o->sweep_split;
     const int kBlockDim = 32 * W;
     if (W > 1 && dyn_smem < (size_t)W * 14 * 32 * sizeof(float)) dyn_smem = (size_t)W * 14 * 32 * sizeof(float);
@@ -724,18 +774,25 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
     PSG_LAUNCH_CHECK();
 }
 
-static void fetch_red(psg_optimizer* o, double* dst, size_t n) {
-    PSG_CUDA(cudaMemcpyAsync(dst, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+// per-keyframe reductions (n doubles) + the 8 scalars behind them, in one pinned-host round trip
+static const double* fetch_red(psg_optimizer* o, size_t n) {
+    o->ensure_host_staging();
+    double* h = o->host_staging;
+    if (n) PSG_CUDA(cudaMemcpyAsync(h, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaMemcpyAsync(h + kMaxFrames * 64, o->red.p + kMaxFrames * 64, 8 * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
+    o->last_energy_sum = h[kMaxFrames * 64 + 6];
+    o->last_active = (long long)(h[kMaxFrames * 64 + 7] + 0.5);
+    return h;
 }
+static inline const double* scalars(const double* h) { return h + kMaxFrames * 64; }
 
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
     SweepArgs A = base_args(o);
-    launch_sweep<M_ENERGY>(o, A, 8, 0);
-    double r[8];
-    fetch_red(o, r, 8);
-    *E_sum = r[0];
-    *n_active = (long long)(r[7] + 0.5);
+    launch_sweep<M_ENERGY>(o, A, 0, 0);
+    fetch_red(o, 0);
+    *E_sum = o->last_energy_sum;
+    *n_active = o->last_active;
 }
 
 void sweep_init_albedo(psg_optimizer* o) {
@@ -745,10 +802,9 @@ void sweep_init_albedo(psg_optimizer* o) {
 
 void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
     SweepArgs A = base_args(o);
-    launch_sweep<M_LED_INIT>(o, A, 8, 0);
-    double r[8];
-    fetch_red(o, r, 8);
-    for (int i = 0; i < 6; ++i) sums[i] = r[i];
+    launch_sweep<M_LED_INIT>(o, A, 0, 0);
+    const double* sc = scalars(fetch_red(o, 0));
+    for (int i = 0; i < 6; ++i) sums[i] = sc[i];
 }
 
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
@@ -760,10 +816,9 @@ void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float*
 void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b_dev, float* delta_dev) {
     SweepArgs A = base_args(o);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
-    launch_sweep<M_ALBEDO>(o, A, 8, 0);
-    double r[8];
-    fetch_red(o, r, 8);
-    *accepted = (long long)(r[0] + 0.5);
+    launch_sweep<M_ALBEDO>(o, A, 0, 0);
+    const double* sc = scalars(fetch_red(o, 0));
+    *accepted = (long long)(sc[5] + 0.5);
 }
 
 // light / pose: returns per-keyframe lower triangles + rhs as accumulated on the device (doubles).
@@ -771,11 +826,10 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
     SweepArgs A = base_args(o);
     const bool led = o->set.model == PSG_MODEL_LED;
     if (block == PSG_BLOCK_LIGHT && led) {
-        launch_sweep<M_LIGHT>(o, A, 8, 0);
-        double r[8];
-        fetch_red(o, r, 8);
+        launch_sweep<M_LIGHT>(o, A, 0, 0);
+        const double* sc = scalars(fetch_red(o, 0));
         Hout.assign(9, 0.0); bout.assign(3, 0.0);
-        for (int c = 0; c < 3; ++c) { Hout[4 * c] = r[c]; bout[c] = r[3 + c]; }
+        for (int c = 0; c < 3; ++c) { Hout[4 * c] = sc[c]; bout[c] = sc[3 + c]; }
         return;
     }
     const int nbk = block == PSG_BLOCK_POSE ? 6 : o->nb;
@@ -784,12 +838,11 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
     const size_t nred = (size_t)o->F * V;
     if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, 0);
     else launch_sweep<M_LIGHT>(o, A, nred, 0);
-    std::vector<double> r(nred);
-    fetch_red(o, r.data(), nred);
+    const double* r = fetch_red(o, nred);
     Hout.assign((size_t)o->F * nbk * nbk, 0.0);
     bout.assign((size_t)o->F * nbk, 0.0);
     for (int f = 0; f < o->F; ++f) {
-        const double* v = r.data() + (size_t)f * V;
+        const double* v = r + (size_t)f * V;
         int t = 0;
         for (int i = 0; i < nbk; ++i) {
             for (int k = 0; k <= i; ++k) {
@@ -802,12 +855,14 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
     }
 }
 
+// distance: leaves the stencil blocks in o->vecs; the scalars (energy before the update) are fetched with the PCG result
 void sweep_dist(psg_optimizer* o, int flags) {
     SweepArgs A = base_args(o);
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
     launch_sweep<M_DIST>(o, A, 0, 0);
+    fetch_red(o, 0);
 }
 
 // ---- regulariser energies (Optimizer.cpp:86-136) -------------------------------------------------------------
@@ -862,8 +917,7 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
         { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red); }
         PSG_LAUNCH_CHECK();
     }
-    double r[8];
-    fetch_red(o, r, 8);
+    const double* r = fetch_red(o, 8);
     *En = r[0]; *El = r[1]; *Er = r[2];
 }
 
@@ -884,9 +938,9 @@ constexpr int kNoAllocMaxSurface = 1 << 21;   // 2 097 152 surface voxels
 constexpr int kNoAllocMaxDevices = 64;
 struct NoAllocScratch {
     double red[8];
-    unsigned counter[8];
+    unsigned counter[kNoAllocMaxSurface / 32 / kRedGroup + 8];   // [0] top level, [1 + g] per group of blocks
     FrameParams frames[kMaxFrames];
-    double partials[((size_t)kNoAllocMaxSurface / 32 + 1) * 8];
+    double partials[((size_t)kNoAllocMaxSurface / 32 + kNoAllocMaxSurface / 32 / kRedGroup + 8) * 8];   // blocks, then groups
 };
 static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
 // device address of the array per device ordinal (the symbol name itself is only a host-side handle)
@@ -931,19 +985,18 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         SweepArgs A;
         memset(&A, 0, sizeof(A));
         A.vol = o->vol->view();
-        A.surf.S = o->S; A.surf.lin = o->lin.p; A.surf.vis = o->svis.p; A.surf.nbr_lin = o->nbr_lin.p;
-        A.surf.nbr_row = o->nbr_row.p; A.surf.pos = o->pos.p;
+        A.surf = surf_view(o);   // re-gathers the compact records if the volume changed; launches a kernel, allocates nothing
         A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
         A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
         A.frames = sc->frames; A.images = o->images.p; A.F = o->F;
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
-        A.red = sc->red; A.partials = sc->partials; A.counter = sc->counter;
+        A.red = sc->red; A.scal = sc->red; A.partials = sc->partials; A.counter = sc->counter;
 
         const int grid = (o->S + 31) / 32;
         int W = 1;
-        while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 48) W *= 2;
+        while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
         if (o->sweep_split > 0) W = o->sweep_split;
         const size_t smem = W > 1 ? (size_t)W * 14 * 32 * sizeof(float) : 0;
         switch (o->set.model) {
@@ -956,7 +1009,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         double r[8];
         PSG_CUDA(cudaMemcpyAsync(r, sc->red, sizeof(r), cudaMemcpyDeviceToHost, o->stream));
         PSG_CUDA(cudaStreamSynchronize(o->stream));
-        if (E) *E = r[0] / (double)o->S;
+        if (E) *E = r[6] / (double)o->S;
         if (n_active) *n_active = (long long)(r[7] + 0.5);
         return PSG_OK;
     } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }

@@ -157,6 +157,69 @@ def test_out_of_image_projection():
     assert_bit_equal(po[2], pg[2], "in-bounds flags")
 
 
+def test_pcg_kernels_agree():
+    """Cluster-synchronised and cooperative-grid PCG run the same iteration: identical iteration count and solution."""
+    model, G = "SH1", 40
+    sc = scene(model)
+    outs = []
+    for mode in (0, 2):
+        gv, go = make_gpu(model, G, sc)
+        handoff(go, sc); go.init_albedo(); go.set_pcg_mode(mode)
+        info = go.step("dist", damping=1.0, normal_reg=True)
+        outs.append((info["iters"], info["cg_success"], go.last_vectors("dist")[1], gv.download()))
+    assert outs[0][0] == outs[1][0] and outs[0][1] == outs[1][1]
+    assert rel_err(outs[0][2], outs[1][2]) < 1e-6
+    assert rel_err(outs[0][3][:, 0], outs[1][3][:, 0]) < 1e-6
+
+
+def test_step_reports_energy_of_starting_state():
+    model, G = "SH1", 32
+    sc = scene(model)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc); go.init_albedo()
+    for blk in block_order(model):
+        e, a = go.energy()
+        info = go.step(blk, damping=1.0, normal_reg=True)
+        assert info["n_active_before"] == a and abs(info["energy_before"] - e) <= 1e-12 * abs(e), (blk, info, e)
+
+
+def test_outer_loop_matches_reference_log(tmp_path):
+    """psg_opt_alternating_optimize against the reference's own alternatingOptimize: same per-block energies in
+    optimizer_doc.txt (to the 6 digits the reference prints, within 2e-5) and the same verdict."""
+    from oracle import pyref
+    if not pyref.available():
+        pytest.skip("oracle/_ref/libpsgref.so not present")
+    import re
+    from psgradientsdf_b200 import synth
+    import psgradientsdf_b200 as psg
+    model, G = "SH1", 32
+    sc = scene(model)
+    vs, T = synth.grid_for_scene(G)
+    rdir = tmp_path / "ref"; rdir.mkdir(); gdir = tmp_path / "gpu"; gdir.mkdir()
+    rv = pyref.RefVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5)
+    ro = pyref.RefOptimizer(rv, model, vs, sc.K, str(rdir) + "/", reg_n=10.0, max_it=3, conv=5e-3, damping=1.0)
+    for f in range(sc.color.shape[0]):
+        rv.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
+    handoff(ro, sc)
+    ok_ref, _, _ = ro.alternating(True, True, True, True)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc)
+    res = go.alternatingOptimize(True, True, True, True, max_it=3, conv_threshold=5e-3, damping=1.0, save_path=str(gdir) + "/")
+    assert bool(res["converged"]) == ok_ref and res["iterations"] == 3
+    num = re.compile(r"[-+]?\d+\.?\d*(?:[eE][-+]?\d+)?")
+    lr = (rdir / "optimizer_doc.txt").read_text().splitlines()
+    lg = (gdir / "optimizer_doc.txt").read_text().splitlines()
+    assert len(lr) == len(lg), (len(lr), len(lg))
+    for a, b in zip(lr, lg):
+        assert re.sub(num, "#", a) == re.sub(num, "#", b), (a, b)          # same text
+        va, vb = [float(x) for x in num.findall(a)], [float(x) for x in num.findall(b)]
+        for x, y in zip(va, vb):
+            assert abs(x - y) <= 2e-5 * max(abs(x), 1e-3) + 1e-6, (a, b)
+    assert (gdir / "after_iter_3_pointcloud.ply").exists() and (gdir / "after_poses_opt_3.txt").exists()
+    # reg weights were rescaled by E / E_n exactly like the reference's settings
+    assert abs(go.reg()[1] - ro.reg()[1]) <= 2e-5 * abs(ro.reg()[1])
+
+
 def test_upsample_vs_oracle():
     model, G = "SH1", 24
     sc = scene(model)
