@@ -18,8 +18,10 @@ ms_per_step = ms per LM iteration.
 `roofline`   : dominant kernel by device time, timed live with CUDA events on the launching stream (psg_profile_*).
 `cpu_baseline`: the reference's getPSEnergy() on this box's host (1 thread: the reference is single-threaded), on a
                bounded sample of the same workload.
-At N > 1 each rank runs the same workload on its own GPU (replicas, weak scaling; the z-slab partition with halo
-exchange is not in this round) -- see DESIGN.md.
+At N > 1 the SAME workload is sharded over the ranks (strong scaling): every rank holds the volume and the work list, the
+sweeps are split by contiguous ranges of the visibility-sorted work list, and the library combines the results with NCCL
+(all-reduce of energies and of the light / pose normal equations, all-gather of albedo, all-reduce of the distance stencil
+blocks, replicated distance solve) -- see DESIGN.md section 7.
 """
 from __future__ import annotations
 
@@ -232,6 +234,10 @@ def run_ours(a):
         go.init()
         go.init_albedo()
 
+    if world > 1:
+        ids = [psg.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        go.comm_init(ids[0], rank, world)
     handoff()
     S = go.S
     E0, A = go.energy()
@@ -276,7 +282,7 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_max = float(tt.item())
-    value = world * A * sweeps_per_step * a.steps / t_max
+    value = A * sweeps_per_step * a.steps / t_max          # one shared workload: total pairs, not per rank
 
     # ---- e2e leg: host buffers -> C ABI every step
     h2d = images_np.nbytes + poses_np.nbytes
@@ -298,10 +304,12 @@ def run_ours(a):
     tte = torch.tensor([te], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(tte, op=dist.ReduceOp.MAX)
-    e2e_value = world * A * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
+    e2e_value = A * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
 
     if rank != 0:
         if world > 1:
+            dist.barrier()
+            go.comm_destroy()
             dist.destroy_process_group()
         return
 
@@ -317,7 +325,8 @@ def run_ours(a):
     roof = None
     if best:
         n, ms = prof[best]
-        bytes_launch = sweep_bytes(A, S, F, out_block.get(best, 0))
+        # per launch = per rank: a rank sweeps its share of the work list
+        bytes_launch = sweep_bytes(A // world, S // world, F, out_block.get(best, 0))
         ach = bytes_launch / (ms / n * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
@@ -350,22 +359,28 @@ def run_ours(a):
             cpu["port"] = port
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-           "dtype": "f32", "data": "synthetic",
+           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": workload_name(a), "surface_voxels": S, "active_pairs": A, "keyframes": F,
                       "sweeps_per_step": sweeps_per_step, "energy_after_last_step": E[0] if E else None,
                       "l2": "flushed between steps (256 MiB device write); per-step host timing bracketed by device syncs, summed",
-                      "multi_gpu": "replicas (each rank runs the full workload on its own GPU)" if world > 1 else "single GPU"},
+                      "multi_gpu": (f"work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
+                                    if world > 1 else "single GPU")},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": 1e3 * float(tte.item()) / a.steps,
                    "step": "psg_opt_set_keyframes (pinned host images + poses) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},
            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "kernels": table}
     print(json.dumps(out))
     if world > 1:
+        dist.barrier()
+        go.comm_destroy()
         dist.destroy_process_group()
 
 
 def main():
+    # NCCL (and some launchers) set NCCL_DEBUG=VERSION, which prints a banner on stdout; the contract is ONE JSON line
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
     a = parse()
     if a.impl == "reference":
         run_reference(a)

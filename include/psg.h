@@ -192,6 +192,23 @@ int psg_opt_last_vectors(psg_optimizer* opt, float* b, float* delta);
  * updated in place (dims x2, voxel size /2, origin shifted, VoxelGrid.h:143-149) and the surface is re-extracted. */
 int psg_opt_upsample(psg_optimizer* opt);
 
+/* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
+ * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
+ * every rank); the (surface voxel, keyframe) sweeps are split by contiguous ranges of the visibility-sorted work list.
+ * After psg_opt_comm_init, psg_opt_init_albedo / psg_opt_energy / psg_opt_step / psg_opt_alternating_optimize are
+ * collective: all ranks must call them in the same order with the same arguments, and all ranks end in the same state
+ * (small light / pose normal equations and energies: NCCL all-reduce; updated albedo: all-gather; distance stencil blocks:
+ * all-reduce, then every rank runs the same distance solve).  NCCL over NVLink / NVSwitch; the communicator runs on the
+ * optimizer's stream. */
+int psg_comm_unique_id(unsigned char id[128]);                                   /* rank 0; send the bytes to the other ranks */
+int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank, int world);
+int psg_opt_comm_destroy(psg_optimizer* opt);
+/* The range [begin, end) of work-list slots that `rank` of `world` sweeps for a surface of S voxels (multiples of 32). */
+int psg_shard_range(int S, int rank, int world, int* begin, int* end);
+/* Diagnostic: the partial energy sum and pair count over the slots of `rank` of `world`, computed locally without any
+ * communication (the partials of all ranks add up to psg_opt_energy * S). */
+int psg_opt_energy_partial(psg_optimizer* opt, int rank, int world, double* loss_sum, long long* n_active);
+
 /* {Ps,Led}Optimizer::alternatingOptimize(light, albedo, distance, pose) (PsOptimizer.cpp:239-428,
  * LedOptimizer.cpp:279-478) with the settings it reads from OptimizerSettings (max_it, conv_threshold, damping, upsample,
  * OptimizerSettings.h:24-33).  Runs initAlbedo, the regulariser-weight normalisation and the outer loop; writes

@@ -102,6 +102,11 @@ def lib():
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
         L.psg_opt_upsample.argtypes = [vp]
         L.psg_opt_alternating_optimize.argtypes = [vp, C.POINTER(LoopConfig), C.c_char_p, C.POINTER(LoopResult)]
+        L.psg_comm_unique_id.argtypes = [C.c_char_p]
+        L.psg_opt_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+        L.psg_opt_comm_destroy.argtypes = [vp]
+        L.psg_shard_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psg_opt_energy_partial.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_profile_enable.argtypes = [C.c_int]
         L.psg_profile_name.restype = C.c_char_p
         L.psg_profile_name.argtypes = [C.c_int]
@@ -117,6 +122,19 @@ def _check(status: int) -> None:
 
 def kernel_launches() -> int:
     return int(lib().psg_kernel_launches())
+
+
+def comm_unique_id() -> bytes:
+    """NCCL unique id (128 bytes) created on this rank; broadcast it to the other ranks and pass it to comm_init."""
+    buf = C.create_string_buffer(128)
+    _check(lib().psg_comm_unique_id(buf))
+    return buf.raw
+
+
+def shard_range(S: int, rank: int, world: int):
+    b, e = C.c_int(), C.c_int()
+    _check(lib().psg_shard_range(int(S), int(rank), int(world), C.byref(b), C.byref(e)))
+    return b.value, e.value
 
 
 def profile_enable(on: bool = True) -> None:
@@ -309,6 +327,19 @@ class Optimizer:
         na = C.c_longlong()
         _check(lib().psg_opt_energy(self.h, C.byref(e), C.byref(na)))
         return e.value, na.value
+
+    def comm_init(self, unique_id: bytes, rank: int, world: int):
+        """Join the NCCL communicator: from here on init_albedo / energy / step / alternatingOptimize are collective."""
+        _check(lib().psg_opt_comm_init(self.h, C.create_string_buffer(unique_id, 128), int(rank), int(world)))
+
+    def comm_destroy(self):
+        _check(lib().psg_opt_comm_destroy(self.h))
+
+    def energy_partial(self, rank: int, world: int):
+        s = C.c_double()
+        n = C.c_longlong()
+        _check(lib().psg_opt_energy_partial(self.h, int(rank), int(world), C.byref(s), C.byref(n)))
+        return s.value, n.value
 
     def energy_noalloc(self):
         """psg_opt_energy_noalloc: same value as energy(), computed without any device allocation (see include/psg.h)."""

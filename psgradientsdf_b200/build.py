@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libpsg_b200.so")
-SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu"]
+SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu", "comm.cu"]
 HEADERS = ["psg_device.cuh", "psg_host.h", os.path.join("..", "..", "include", "psg.h")]
 
 
@@ -68,7 +68,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, *_ccbin(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
+    cmd = [nvcc, *_ccbin(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs, "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)

@@ -1,0 +1,176 @@
+// Multi-GPU plumbing: one process per GPU, NCCL over NVLink / NVSwitch.
+//
+// The reference is a single process; this is the B200 part of the design.  Every rank keeps the whole
+// volume and work list; the sweeps are split by contiguous slot ranges of the visibility-sorted work list
+// (psg_shard_range).  What has to cross ranks per outer iteration is small:
+//   * energy / counters and the per-keyframe light (4x4 / 9x9) and pose (6x6) normal equations: all-reduce of <= 4104 doubles;
+//   * albedo after initAlbedo / the albedo block: all-gather of the {r, g, b} records (16 B per surface voxel);
+//   * distance: all-reduce of the 14 stencil-block planes (56 B per surface voxel), after which every rank runs the same
+//     deterministic distance solve and applies the same update, so no further exchange is needed.
+// All collectives are enqueued on the optimizer's stream, so they order with the kernels without host synchronisation.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include "psg_host.h"
+
+namespace psg {
+
+// NCCL is bound at first use, not at link time: a process that also imports PyTorch must end up with ONE libnccl.so.2
+// (PyTorch bundles a newer one than the system's, and whichever is loaded first wins the soname).  Order of preference:
+// a copy that is already loaded (RTLD_NOLOAD), then $PSG_NCCL_LIB, then the system library.
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+static NcclApi g_nccl;
+
+static bool nccl_load() {
+    if (g_nccl.ok) return true;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) { const char* env = getenv("PSG_NCCL_LIB"); if (env && *env) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL); }
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) { set_error("NCCL not available: %s", dlerror()); return false; }
+#define PSG_SYM(field, name)                                                                        \
+    g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));                        \
+    if (!g_nccl.field) { set_error("NCCL symbol %s not found", name); return false; }
+    PSG_SYM(GetUniqueId, "ncclGetUniqueId")
+    PSG_SYM(CommInitRank, "ncclCommInitRank")
+    PSG_SYM(CommDestroy, "ncclCommDestroy")
+    PSG_SYM(AllReduce, "ncclAllReduce")
+    PSG_SYM(AllGather, "ncclAllGather")
+    PSG_SYM(GroupStart, "ncclGroupStart")
+    PSG_SYM(GroupEnd, "ncclGroupEnd")
+    PSG_SYM(GetErrorString, "ncclGetErrorString")
+#undef PSG_SYM
+    g_nccl.ok = true;
+    return true;
+}
+
+#define PSG_NCCL(call)                                                                                   \
+    do {                                                                                                 \
+        ncclResult_t r__ = (call);                                                                       \
+        if (r__ != ncclSuccess) {                                                                        \
+            psg::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, g_nccl.GetErrorString(r__)); \
+            throw psg::CudaError{(int)r__};                                                              \
+        }                                                                                                \
+    } while (0)
+
+void shard_range(int S, int rank, int world, int* begin, int* end) {
+    const long long nblocks = ((long long)S + 31) / 32;
+    const long long per = (nblocks + world - 1) / world;
+    long long b = (long long)rank * per * 32;
+    if (b > S) b = S;
+    long long e = b + per * 32;
+    if (e > S) e = S;
+    *begin = (int)b; *end = (int)e;
+}
+
+void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb) {
+    ncclComm_t comm = static_cast<ncclComm_t>(o->comm);
+    PSG_NCCL(g_nccl.GroupStart());
+    if (na) PSG_NCCL(g_nccl.AllReduce(a, a, na, ncclDouble, ncclSum, comm, o->stream));
+    if (nb) PSG_NCCL(g_nccl.AllReduce(b, b, nb, ncclDouble, ncclSum, comm, o->stream));
+    PSG_NCCL(g_nccl.GroupEnd());
+}
+
+void comm_allreduce_floats(psg_optimizer* o, float* a, size_t n) {
+    if (!n) return;
+    PSG_NCCL(g_nccl.AllReduce(a, a, n, ncclFloat, ncclSum, static_cast<ncclComm_t>(o->comm), o->stream));
+}
+
+// rho of slots swept by other ranks -> dense volume planes (own slots were written by the sweep itself)
+__global__ void __launch_bounds__(256) k_scatter_rho(VolView vol, SurfView surf, int own_begin, int own_end) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= surf.S || (t >= own_begin && t < own_end)) return;
+    const float4 r1 = surf.rec1[t];
+    const int lin = __float_as_int(surf.rec3[t].w);
+    vol.r[lin] = r1.x; vol.g[lin] = r1.y; vol.b[lin] = r1.z;
+}
+
+void comm_allgather_rec1(psg_optimizer* o) {
+    if (o->S == 0) return;
+    int b0, e0, b, e;
+    shard_range(o->S, 0, o->world, &b0, &e0);
+    shard_range(o->S, o->rank, o->world, &b, &e);
+    const long long nblocks = ((long long)o->S + 31) / 32;
+    const size_t chunk = (size_t)((nblocks + o->world - 1) / o->world) * 32;   // slots per rank (the last ranks' tails are padding)
+    float4* base = o->rec1.p;
+    PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * chunk, base, chunk * 4, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
+    const SurfView sv = surf_view(o);
+    { Prof pf(o->stream, KID_AOS); k_scatter_rho<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, b, e); }
+    PSG_LAUNCH_CHECK();
+}
+
+}  // namespace psg
+
+using namespace psg;
+
+extern "C" {
+
+int psg_comm_unique_id(unsigned char id[128]) {
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is expected to be 128 bytes");
+    if (!id) { set_error("psg_comm_unique_id: null argument"); return PSG_ERR_INVALID; }
+    if (!nccl_load()) return PSG_ERR_CUDA;
+    ncclUniqueId u;
+    const ncclResult_t r = g_nccl.GetUniqueId(&u);
+    if (r != ncclSuccess) { set_error("ncclGetUniqueId failed: %s", g_nccl.GetErrorString(r)); return PSG_ERR_CUDA; }
+    memcpy(id, &u, 128);
+    return PSG_OK;
+}
+
+int psg_opt_comm_init(psg_optimizer* o, const unsigned char id[128], int rank, int world) {
+    if (!o || !id) { set_error("psg_opt_comm_init: null argument"); return PSG_ERR_INVALID; }
+    if (world < 1 || world > 64 || rank < 0 || rank >= world) { set_error("psg_opt_comm_init: rank %d of %d is not valid (1 <= world <= 64)", rank, world); return PSG_ERR_INVALID; }
+    if (o->comm) { set_error("psg_opt_comm_init: a communicator already exists"); return PSG_ERR_STATE; }
+    if (!nccl_load()) return PSG_ERR_CUDA;
+    try {
+        PSG_CUDA(cudaSetDevice(o->vol->device));
+        ncclUniqueId u;
+        memcpy(&u, id, 128);
+        ncclComm_t comm = nullptr;
+        PSG_NCCL(g_nccl.CommInitRank(&comm, world, u, rank));
+        o->comm = comm; o->rank = rank; o->world = world;
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+int psg_opt_comm_destroy(psg_optimizer* o) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (o->comm) {
+        cudaSetDevice(o->vol->device);
+        cudaStreamSynchronize(o->stream);
+        g_nccl.CommDestroy(static_cast<ncclComm_t>(o->comm));
+        o->comm = nullptr;
+    }
+    o->rank = 0; o->world = 1;
+    return PSG_OK;
+}
+
+int psg_shard_range(int S, int rank, int world, int* begin, int* end) {
+    if (S < 0 || world < 1 || rank < 0 || rank >= world || !begin || !end) { set_error("psg_shard_range: bad argument"); return PSG_ERR_INVALID; }
+    shard_range(S, rank, world, begin, end);
+    return PSG_OK;
+}
+
+int psg_opt_energy_partial(psg_optimizer* o, int rank, int world, double* loss_sum, long long* n_active) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (!o->inited) { set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
+    if (world < 1 || rank < 0 || rank >= world) { set_error("psg_opt_energy_partial: rank %d of %d is not valid", rank, world); return PSG_ERR_INVALID; }
+    try {
+        PSG_CUDA(cudaSetDevice(o->vol->device));
+        double s = 0.0; long long n = 0;
+        sweep_energy_partial(o, rank, world, &s, &n);
+        if (loss_sum) *loss_sum = s;
+        if (n_active) *n_active = n;
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+}  // extern "C"

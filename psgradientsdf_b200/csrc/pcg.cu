@@ -91,31 +91,34 @@ __device__ __forceinline__ double grid_total(const double* partials, int nblocks
     return s_buf[0];
 }
 
-// Cooperative launch, grid.sync() between phases: any surface size (the large-surface path).
-template <int BS>
-__global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A) {
-    auto sync_all = [&]() { cg::this_grid().sync(); };
+// Large surfaces: cooperative launch over the whole GPU, grid.sync() between phases, vectors in global memory.
+// Same three-barrier iteration as the cluster kernel below (the search-direction update is folded into the stencil
+// phase: neighbours' new p is recomputed from the published r, 1/diag and previous p).  A thread walks its rows in
+// groups of RPT and issues the loads of a whole group before using any of them, so a phase costs two dependent memory
+// round trips per group instead of two per row.
+template <int BS, int RPT>
+__global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ pbuf /* 2 x S */) {
+    cg::grid_group grid = cg::this_grid();
     __shared__ double s_buf[BS / 32];
     const int S = A.S;
     const int nb = gridDim.x;
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int gstride = nb * blockDim.x;
+    const int T = nb * BS;
+    const int gtid = blockIdx.x * BS + threadIdx.x;
     double* P0 = A.partials;
     double* P1 = A.partials + nb;
     double* P2 = A.partials + 2 * nb;
 
-    // ---- init: x = 0, residual = rhs, p = precond.solve(residual)
     double a0 = 0.0, a1 = 0.0;
-    for (int s = gtid; s < S; s += gstride) {
+    for (int s = gtid; s < S; s += T) {
         const float b = A.rhs[s];
         const float pv = A.invd[s] * b;
-        A.x[s] = 0.f; A.r[s] = b; A.p[s] = pv;
+        A.x[s] = 0.f; A.r[s] = b; pbuf[s] = pv;
         a0 += (double)b * (double)b;
         a1 += (double)b * (double)pv;
     }
     a0 = block_sum<BS>(a0, s_buf); if (threadIdx.x == 0) P0[blockIdx.x] = a0;
     a1 = block_sum<BS>(a1, s_buf); if (threadIdx.x == 0) P1[blockIdx.x] = a1;
-    sync_all();
+    grid.sync();
     const float rhsNorm2 = (float)grid_total(P0, nb, s_buf);
     float absNew = (float)grid_total(P1, nb, s_buf);
     const float tol = 1.1920929e-07f;   // NumTraits<float>::epsilon(), the default tolerance
@@ -124,68 +127,113 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A) {
     float residualNorm2 = rhsNorm2;
     int it = 0;
     if (rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+        float gamma = 0.f, beta = 1.f;
+        int cur = 0;
         while (it < A.max_iters) {
-            // ---- phase 1: u_t = A_t * p[stencil(t)]
-            for (int t = gtid; t < S; t += gstride) {
-                int col[4]; float px[4];
-                col[0] = t; px[0] = A.p[t];
+            const float* pc = pbuf + (size_t)cur * S;
+            float* pn = pbuf + (size_t)(cur ^ 1) * S;
+            // ---- phase 1: p <- z + beta p, u_t = A_t * p[stencil(t)]
+            for (int base = gtid; base < S; base += T * RPT) {
+                int row[RPT], col[RPT][3];
+                float pj[RPT];
 #pragma unroll
-                for (int a = 0; a < 3; ++a) { col[a + 1] = A.nbr_row[a * S + t]; px[a + 1] = col[a + 1] >= 0 ? A.p[col[a + 1]] : 0.f; }
-                float Ab[10];
+                for (int j = 0; j < RPT; ++j) {
+                    row[j] = base + j * T;
+                    const bool in = row[j] < S;
 #pragma unroll
-                for (int i = 0; i < 10; ++i) Ab[i] = A.blk[(long long)i * S + t];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    float u = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
-                        if (col[k] >= 0) u += aik * px[k];
-                    }
-                    A.U[(long long)i * S + t] = (col[i] >= 0) ? u : 0.f;
+                    for (int a = 0; a < 3; ++a) col[j][a] = in ? A.nbr_row[a * S + row[j]] : -1;
+                    pj[j] = in ? (A.invd[row[j]] * A.r[row[j]]) * gamma + beta * pc[row[j]] : 0.f;
                 }
-            }
-            sync_all();
-            // ---- phase 2: tmp_s = sum of incident u + damping * diag * p_s ; p . tmp
-            double pAp = 0.0;
-            for (int s = gtid; s < S; s += gstride) {
-                float y = A.U[s];
 #pragma unroll
-                for (int h = 0; h < 2; ++h)
+                for (int j = 0; j < RPT; ++j) {
+                    if (row[j] >= S) continue;
+                    pn[row[j]] = pj[j];
+                    float px[4];
+                    px[0] = pj[j];
 #pragma unroll
                     for (int a = 0; a < 3; ++a) {
-                        const int t = A.inc[(h * 3 + a) * S + s];
-                        if (t >= 0) y += A.U[(long long)(a + 1) * S + t];
+                        const int c = col[j][a];
+                        px[a + 1] = c >= 0 ? (A.invd[c] * A.r[c]) * gamma + beta * pc[c] : 0.f;
                     }
-                const float ps = A.p[s];
-                y += A.ddiag[s] * ps;
-                A.tmp[s] = y;
-                pAp += (double)ps * (double)y;
+                    float Ab[10];
+#pragma unroll
+                    for (int i = 0; i < 10; ++i) Ab[i] = A.blk[(long long)i * S + row[j]];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float u = 0.f;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                            if (k == 0 || col[j][k - 1] >= 0) u += aik * px[k];
+                        }
+                        const bool valid = (i == 0) || col[j][i - 1] >= 0;
+                        A.U[(long long)i * S + row[j]] = valid ? u : 0.f;
+                    }
+                }
+            }
+            grid.sync();
+            // ---- phase 2: tmp_s = u_s[0] + incident u + damping * diag * p_s ; p . tmp
+            double pAp = 0.0;
+            for (int base = gtid; base < S; base += T * RPT) {
+                int tn[RPT][6];
+#pragma unroll
+                for (int j = 0; j < RPT; ++j)
+#pragma unroll
+                    for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < S) ? A.inc[h * S + base + j * T] : -1;
+#pragma unroll
+                for (int j = 0; j < RPT; ++j) {
+                    const int s = base + j * T;
+                    if (s >= S) continue;
+                    float y = A.U[s];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) {
+                            const int t = tn[j][h * 3 + a];
+                            if (t >= 0) y += A.U[(long long)(a + 1) * S + t];
+                        }
+                    const float ps = pn[s];
+                    y += A.ddiag[s] * ps;
+                    A.tmp[s] = y;
+                    pAp += (double)ps * (double)y;
+                }
             }
             pAp = block_sum<BS>(pAp, s_buf); if (threadIdx.x == 0) P0[blockIdx.x] = pAp;
-            sync_all();
+            grid.sync();
             const float alpha = absNew / (float)grid_total(P0, nb, s_buf);
             // ---- phase 3: x += alpha p ; residual -= alpha tmp ; norms
             double rn = 0.0, rz = 0.0;
-            for (int s = gtid; s < S; s += gstride) {
-                A.x[s] += alpha * A.p[s];
-                const float rv = A.r[s] - alpha * A.tmp[s];
-                A.r[s] = rv;
-                rn += (double)rv * (double)rv;
-                rz += (double)rv * (double)(A.invd[s] * rv);
+            for (int base = gtid; base < S; base += T * RPT) {
+                float xv[RPT], pv[RPT], rv[RPT], tv[RPT], iv[RPT];
+#pragma unroll
+                for (int j = 0; j < RPT; ++j) {
+                    const int s = base + j * T;
+                    const bool in = s < S;
+                    xv[j] = in ? A.x[s] : 0.f; pv[j] = in ? pn[s] : 0.f; rv[j] = in ? A.r[s] : 0.f;
+                    tv[j] = in ? A.tmp[s] : 0.f; iv[j] = in ? A.invd[s] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < RPT; ++j) {
+                    const int s = base + j * T;
+                    if (s >= S) continue;
+                    A.x[s] = xv[j] + alpha * pv[j];
+                    const float r2 = rv[j] - alpha * tv[j];
+                    A.r[s] = r2;
+                    rn += (double)r2 * (double)r2;
+                    rz += (double)r2 * (double)(iv[j] * r2);
+                }
             }
             rn = block_sum<BS>(rn, s_buf); if (threadIdx.x == 0) P1[blockIdx.x] = rn;
             rz = block_sum<BS>(rz, s_buf); if (threadIdx.x == 0) P2[blockIdx.x] = rz;
-            sync_all();
+            grid.sync();
             residualNorm2 = (float)grid_total(P1, nb, s_buf);
             if (residualNorm2 < threshold) break;
             const float absOld = absNew;
             absNew = (float)grid_total(P2, nb, s_buf);
-            const float beta = absNew / absOld;
-            // ---- phase 4: p = z + beta p
-            for (int s = gtid; s < S; s += gstride) A.p[s] = A.invd[s] * A.r[s] + beta * A.p[s];
+            beta = absNew / absOld;
+            gamma = 1.f;
+            cur ^= 1;
             ++it;
-            sync_all();
         }
     } else if (rhsNorm2 == 0.f) {
         residualNorm2 = 0.f;
@@ -427,17 +475,19 @@ void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float
         int dev = 0, sms = 0, per_sm = 0;
         PSG_CUDA(cudaGetDevice(&dev));
         PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
         if (per_sm < 1) { set_error("PCG kernel does not fit on an SM"); throw CudaError{-1}; }
-        if (per_sm > 2) per_sm = 2;   // enough to hide latency; fewer blocks = cheaper grid.sync
+        if (per_sm > 4) per_sm = 4;
         int grid = sms * per_sm;
-        const int need = (S + kPcgBlock - 1) / kPcgBlock;
+        const int need = (S + kPcgBlock * 4 - 1) / (kPcgBlock * 4);
         if (grid > need) grid = need;
         o->pcg_partials.alloc((size_t)3 * grid);
         A.partials = o->pcg_partials.p;
-        void* args[] = { &A };
+        o->pcg_pbuf.alloc((size_t)2 * S);
+        float* pbuf = o->pcg_pbuf.p;
+        void* args[] = { &A, &pbuf };
         { Prof pf(o->stream, KID_PCG_SOLVE);
-          PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream)); }
+          PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 4>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream)); }
     }
     o->ensure_host_staging();
     float* res = reinterpret_cast<float*>(o->host_staging);   // pinned: a pageable destination makes the copy synchronous and slow

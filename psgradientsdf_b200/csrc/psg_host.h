@@ -104,6 +104,8 @@ struct psg_optimizer {
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
     psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
+    void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
+    int rank = 0, world = 1;
     int pcg_mode = 0;                        // 0 = auto (cluster kernel for small surfaces), 2 = always the cooperative-grid kernel
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
@@ -142,6 +144,11 @@ struct SweepOut {
     long long n_active = 0;
 };
 void upload_frames(psg_optimizer* o);
+void shard_range(int S, int rank, int world, int* begin, int* end);
+void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
+void comm_allreduce_floats(psg_optimizer* o, float* a, size_t n);
+void comm_allgather_rec1(psg_optimizer* o);
+void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active);
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
 void sweep_init_albedo(psg_optimizer* o);
 void sweep_led_light_init(psg_optimizer* o, double sums[6]);

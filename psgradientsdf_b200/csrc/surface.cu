@@ -307,7 +307,8 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     o->S = (int)total;
     const size_t S = (size_t)(o->S > 0 ? o->S : 1);
     o->lin.alloc(S); o->svis.alloc(S); o->nbr_lin.alloc(3 * S); o->nbr_row.alloc(3 * S); o->pos.alloc(S); o->inc.alloc(6 * S);
-    o->rec0.alloc(S); o->rec1.alloc(S); o->rec2.alloc(S); o->rec3.alloc(S); o->rec4.alloc(S);
+    o->rec0.alloc(S); o->rec1.alloc(S + 32 * 65);   // rec1 is all-gathered in equal, 32-aligned chunks (comm.cu)
+    o->rec0.alloc(S); o->rec2.alloc(S); o->rec3.alloc(S); o->rec4.alloc(S);
     o->pvis.alloc(S); o->perm.alloc(S); o->sort_keys.alloc(S); o->sort_vals.alloc(S);
     if (o->S > 0) {
         { Prof pf(o->stream, KID_SURF_SCATTER);

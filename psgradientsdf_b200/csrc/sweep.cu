@@ -34,6 +34,7 @@ struct SweepArgs {
     const FrameParams* frames;
     const float4* images;
     int F;
+    int slot_begin, slot_end;   // this rank's range of the work list
     float vs_inv;
     float led[3];
     float damping, reg_n, reg_l;
@@ -227,8 +228,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int S = A.surf.S;
-    const int slot = blockIdx.x * 32 + lane;   // position in the visibility-sorted work list
-    const bool live = slot < S;
+    const int slot = A.slot_begin + blockIdx.x * 32 + lane;   // position in the visibility-sorted work list
+    const bool live = slot < A.slot_end;
 
     // ---- voxel record (five coalesced 128-bit loads; everything per-voxel is precomputed by k_gather_records)
     int lin = 0, s = 0;
@@ -713,6 +714,7 @@ static SweepArgs base_args(psg_optimizer* o) {
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
     A.frames = o->frames.p; A.images = o->images.p; A.F = o->F;
+    shard_range(o->S, o->rank, o->world, &A.slot_begin, &A.slot_end);
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
@@ -749,8 +751,10 @@ void upload_frames(psg_optimizer* o) {
 template <int MODE>
 static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
     if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
-    if (o->S == 0) return;
-    const int grid = (o->S + 31) / 32;
+    if (o->world > 1 || A.slot_end <= A.slot_begin)   // ranks with an empty range still take part in the all-reduce
+        PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
+    if (o->S == 0 || A.slot_end <= A.slot_begin) return;
+    const int grid = (A.slot_end - A.slot_begin + 31) / 32;
     // keyframe split: double W while the launch stays within ~32 warps per SM (beyond that the replicated prologue costs more than it hides)
     int W = 1;
     while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
@@ -775,9 +779,10 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
 }
 
 // per-keyframe reductions (n doubles) + the 8 scalars behind them, in one pinned-host round trip
-static const double* fetch_red(psg_optimizer* o, size_t n) {
+static const double* fetch_red(psg_optimizer* o, size_t n, bool reduce_over_ranks = true) {
     o->ensure_host_staging();
     double* h = o->host_staging;
+    if (reduce_over_ranks && o->world > 1) comm_allreduce_doubles(o, o->red.p, n, o->red.p + kMaxFrames * 64, 8);
     if (n) PSG_CUDA(cudaMemcpyAsync(h, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaMemcpyAsync(h + kMaxFrames * 64, o->red.p + kMaxFrames * 64, 8 * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -795,9 +800,20 @@ void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
     *n_active = o->last_active;
 }
 
+void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active) {
+    SweepArgs A = base_args(o);
+    shard_range(o->S, rank, world, &A.slot_begin, &A.slot_end);
+    PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));   // an empty range launches nothing
+    launch_sweep<M_ENERGY>(o, A, 0, 0);
+    fetch_red(o, 0, /*reduce_over_ranks=*/false);
+    *sum = o->last_energy_sum;
+    *n_active = o->last_active;
+}
+
 void sweep_init_albedo(psg_optimizer* o) {
     SweepArgs A = base_args(o);
     launch_sweep<M_INIT_ALBEDO>(o, A, 0, 0);
+    if (o->world > 1) comm_allgather_rec1(o);
 }
 
 void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
@@ -810,6 +826,7 @@ void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
     SweepArgs A = base_args(o);
     A.pm = m; A.pn = n; A.pok = ok; A.pI = I3; A.prend = rend3; A.pr = r3; A.pw = w3;
+    A.slot_begin = 0; A.slot_end = o->S;   // diagnostic: every rank probes all pairs
     launch_sweep<M_PROBE>(o, A, 0, 0);
 }
 
@@ -817,6 +834,7 @@ void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b
     SweepArgs A = base_args(o);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
+    if (o->world > 1) comm_allgather_rec1(o);
     const double* sc = scalars(fetch_red(o, 0));
     *accepted = (long long)(sc[5] + 0.5);
 }
@@ -861,7 +879,9 @@ void sweep_dist(psg_optimizer* o, int flags) {
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
+    if (o->world > 1) PSG_CUDA(cudaMemsetAsync(o->vecs.p, 0, (size_t)14 * o->S * sizeof(float), o->stream));   // rows of other ranks
     launch_sweep<M_DIST>(o, A, 0, 0);
+    if (o->world > 1) comm_allreduce_floats(o, o->vecs.p, (size_t)14 * o->S);   // own rows + zeros: exact
     fetch_red(o, 0);
 }
 
@@ -917,7 +937,7 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
         { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red); }
         PSG_LAUNCH_CHECK();
     }
-    const double* r = fetch_red(o, 8);
+    const double* r = fetch_red(o, 8, /*reduce_over_ranks=*/false);   // every rank evaluates all rows
     *En = r[0]; *El = r[1]; *Er = r[2];
 }
 
@@ -989,6 +1009,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
         A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
         A.frames = sc->frames; A.images = o->images.p; A.F = o->F;
+        A.slot_begin = 0; A.slot_end = o->S;   // always the whole work list (no communication on this path)
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;

@@ -172,6 +172,21 @@ def test_pcg_kernels_agree():
     assert rel_err(outs[0][3][:, 0], outs[1][3][:, 0]) < 1e-6
 
 
+def test_sharded_partials_add_up():
+    """Emulated ranks on one GPU: the per-range partial sweeps cover every active pair exactly once."""
+    model, G = "SH1", 40
+    sc = scene(model)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc); go.init_albedo()
+    e, a = go.energy()
+    for world in (2, 3, 8):
+        tot, cnt = 0.0, 0
+        for rank in range(world):
+            s_, n_ = go.energy_partial(rank, world)
+            tot += s_; cnt += n_
+        assert cnt == a and abs(tot / go.S - e) <= 1e-12 * abs(e), (world, tot / go.S, e, cnt, a)
+
+
 def test_step_reports_energy_of_starting_state():
     model, G = "SH1", 32
     sc = scene(model)
