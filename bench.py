@@ -155,7 +155,7 @@ def run_reference(a):
         return
     from oracle import pyref
     if not pyref.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpsgref.so missing (reference sources were not built)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/libpsgref.so missing (reference sources were not built)"})
         return
     sc, vs, T = build_scene(a)
     rv, ro, A, keys = reference_sample(a, sc, vs, T, a.ref_keyframes)
@@ -176,7 +176,7 @@ def run_reference(a):
                             "host_cores": os.cpu_count()},
            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out))
+    emit(out)
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -370,18 +370,32 @@ def run_ours(a):
                    "ms_per_step": 1e3 * float(tte.item()) / a.steps,
                    "step": "psg_opt_set_keyframes (pinned host images + poses) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},
            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "kernels": table}
-    print(json.dumps(out))
+    emit(out)
     if world > 1:
         dist.barrier()
         go.comm_destroy()
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(obj):
+    """The one JSON line goes to the real stdout; everything else written to fd 1 was diverted to stderr in main()."""
+    line = json.dumps(obj) + "\n"
+    if _JSON_OUT is None:
+        sys.stdout.write(line); sys.stdout.flush()
+    else:
+        os.write(_JSON_OUT, line.encode())
+
+
 def main():
-    # NCCL (and some launchers) set NCCL_DEBUG=VERSION, which prints a banner on stdout; the contract is ONE JSON line
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # native libraries (NCCL prints its version banner) write to fd 1 directly; the contract is ONE JSON line on stdout
+    global _JSON_OUT
     a = parse()
+    sys.stdout.flush()
+    _JSON_OUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
