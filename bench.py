@@ -182,14 +182,8 @@ def run_reference(a):
 # ------------------------------------------------------------------------------------------------ our arm
 def lm_iteration(go, model, damping=1.0):
     """One pass of the reference's while-body (PsOptimizer.cpp:303-360 / LedOptimizer.cpp:343-403)."""
-    order = ["light", "albedo", "dist", "pose"] if model == "LED" else ["albedo", "light", "dist", "pose"]
-    energies = []
-    for blk in order:
-        info = go.step(blk, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
-        energies.append(info["energy_before"])      # = the value the reference logs after the previous block
-        if blk == "dist":
-            go.reg_energies()
-    return go.energy()                              # after the last block: the convergence test needs it
+    info = go.iteration(True, True, True, True, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
+    return info["energy_end"], info["n_active_end"]   # the energies the reference logs after each block are in info[...]
 
 
 def sweep_bytes(A, S, F, out_block):

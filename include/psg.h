@@ -144,8 +144,9 @@ int psg_opt_set_reg(psg_optimizer* opt, const float reg3[3]);
  * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
  * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */
 int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
-/* Distance solve: 0 (default) = one thread-block cluster when the surface has at most 65 536 voxels, else a cooperative
- * grid; 2 = always the cooperative-grid kernel.  Both run the same iteration and return the same iterates. */
+/* Distance solve: 0 (default) and 2 = persistent cooperative-grid kernel over all SMs; 1 = one thread-block cluster of at
+ * most 8 CTAs when the surface has at most 65 536 voxels (kept for comparison: slower on B200 once the grid kernel got its
+ * own barrier).  Both run the same iteration and return the same iterates up to the order of the dot-product partials. */
 int psg_opt_set_pcg_mode(psg_optimizer* opt, int mode);
 
 /* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */
@@ -182,6 +183,28 @@ int psg_opt_probe_pairs(psg_optimizer* opt, float* m, float* n, unsigned char* o
 #define PSG_REG_NORMAL 2
 #define PSG_REG_LAPLACIAN 4
 int psg_opt_step(psg_optimizer* opt, int block, float damping, int flags, psg_step_info* info /* may be NULL */);
+/* One pass of the reference's while-body (PsOptimizer.cpp:303-360, LedOptimizer.cpp:343-403): the enabled blocks in the
+ * reference's order (SH: albedo, light, distance, pose; LED: light, albedo, distance, pose), the regulariser energies after
+ * the distance block and the closing getPSEnergy().  Same kernels and host solves as four psg_opt_step calls +
+ * psg_opt_reg_energies + psg_opt_energy, but the host waits for the device only where it has to solve a small system
+ * (light, pose) and for the closing energy: 3 waits instead of 8.  The distance update's CG gate (applied only on Success,
+ * PsOptimizer.cpp:168-170) is evaluated on the device. */
+typedef struct {
+    int light, albedo, distance, pose;   /* alternatingOptimize(bool light, bool albedo, bool distance, bool pose) */
+    float damping;
+    int reg_flags;                       /* PSG_REG_NORMAL | PSG_REG_LAPLACIAN for the distance block */
+    int closing_energy;                  /* evaluate the energy even if no block is enabled */
+} psg_iteration_config;
+typedef struct {
+    int ran[4];                          /* indexed by PSG_BLOCK_* */
+    psg_step_info block[4];
+    double energy_after[4];              /* getPSEnergy() after each executed block */
+    double reg_normal_after_dist, reg_laplacian_after_dist;   /* getNormalEnergy / getLaplacianEnergy after the distance block */
+    double energy_end;                   /* = energy_after of the last executed block */
+    long long n_active_end;
+} psg_iteration_info;
+int psg_opt_iteration(psg_optimizer* opt, const psg_iteration_config* cfg, psg_iteration_info* info /* may be NULL */);
+
 /* Normal equations of the last psg_opt_step for the small dense blocks (diagnostic / parity probe):
  * light: F blocks of nb x nb (+ nb rhs) or LED 3 (+3); pose: F blocks of 6 x 6 (+6).  Row-major, after damping. */
 int psg_opt_last_system(psg_optimizer* opt, double* H_blocks, double* b, double* delta);

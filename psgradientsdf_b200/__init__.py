@@ -39,6 +39,17 @@ class StepInfo(C.Structure):
                 ("n_active_before", C.c_longlong)]
 
 
+class IterationConfig(C.Structure):
+    _fields_ = [("light", C.c_int), ("albedo", C.c_int), ("distance", C.c_int), ("pose", C.c_int), ("damping", C.c_float),
+                ("reg_flags", C.c_int), ("closing_energy", C.c_int)]
+
+
+class IterationInfo(C.Structure):
+    _fields_ = [("ran", C.c_int * 4), ("block", StepInfo * 4), ("energy_after", C.c_double * 4),
+                ("reg_normal_after_dist", C.c_double), ("reg_laplacian_after_dist", C.c_double), ("energy_end", C.c_double),
+                ("n_active_end", C.c_longlong)]
+
+
 class LoopConfig(C.Structure):
     _fields_ = [("light", C.c_int), ("albedo", C.c_int), ("distance", C.c_int), ("pose", C.c_int),
                 ("max_it", C.c_int), ("conv_threshold", C.c_float), ("damping", C.c_float), ("upsample", C.c_int),
@@ -98,6 +109,7 @@ def lib():
         L.psg_opt_residual.argtypes = [vp, f32p, f32p]
         L.psg_opt_probe_pairs.argtypes = [vp, f32p, f32p, vp, f32p, f32p]
         L.psg_opt_step.argtypes = [vp, C.c_int, C.c_float, C.c_int, C.POINTER(StepInfo)]
+        L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
         L.psg_opt_upsample.argtypes = [vp]
@@ -376,6 +388,23 @@ class Optimizer:
         return dict(n=info.n, cg_success=bool(info.cg_success), iters=info.cg_iterations, err=info.cg_error,
                     applied=bool(info.applied), n_accepted=info.n_accepted, energy_before=info.energy_before,
                     n_active_before=info.n_active_before)
+
+    def iteration(self, light=True, albedo=True, distance=True, pose=True, damping=1.0, normal_reg=False, laplacian_reg=False):
+        """One pass of alternatingOptimize's while-body (psg_opt_iteration): dict with per-block step records, the energy
+        after each block, the regulariser energies after the distance block and the closing energy."""
+        cfg = IterationConfig(int(light), int(albedo), int(distance), int(pose), float(damping),
+                              (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0), 0)
+        info = IterationInfo()
+        _check(lib().psg_opt_iteration(self.h, C.byref(cfg), C.byref(info)))
+        out = {"energy_end": info.energy_end, "n_active_end": info.n_active_end,
+               "reg_normal_after_dist": info.reg_normal_after_dist, "reg_laplacian_after_dist": info.reg_laplacian_after_dist}
+        for name, b in BLOCK.items():
+            if info.ran[b]:
+                st = info.block[b]
+                out[name] = dict(n=st.n, cg_success=bool(st.cg_success), iters=st.cg_iterations, err=st.cg_error,
+                                 applied=bool(st.applied), n_accepted=st.n_accepted, energy_before=st.energy_before,
+                                 n_active_before=st.n_active_before, energy_after=info.energy_after[b])
+        return out
 
     def last_system(self, which):
         """(H_blocks, b, delta) of the last light / pose step as float64 arrays."""

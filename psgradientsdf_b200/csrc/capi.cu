@@ -179,10 +179,10 @@ using namespace psg;
 void psg_optimizer::ensure_host_staging() {
     if (host_staging) return;
     void* p = nullptr;
-    const size_t bytes = (kMaxFrames * 64 + 8) * sizeof(double) + kMaxFrames * sizeof(FrameParams);
+    const size_t bytes = (kRedDoubles + kMailDoubles) * sizeof(double) + kMaxFrames * sizeof(FrameParams);
     PSG_CUDA(cudaMallocHost(&p, bytes));
     host_staging = static_cast<double*>(p);
-    host_frames = reinterpret_cast<FrameParams*>(host_staging + kMaxFrames * 64 + 8);
+    host_frames = reinterpret_cast<FrameParams*>(host_staging + kRedDoubles + kMailDoubles);
 }
 
 #define PSG_TRY try {
@@ -533,7 +533,7 @@ int psg_opt_set_sweep_split(psg_optimizer* o, int warps) {
 
 int psg_opt_set_pcg_mode(psg_optimizer* o, int mode) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
-    if (mode != 0 && mode != 2) { set_error("psg_opt_set_pcg_mode: %d is not 0 or 2", mode); return PSG_ERR_INVALID; }
+    if (mode < 0 || mode > 2) { set_error("psg_opt_set_pcg_mode: %d is not 0, 1 or 2", mode); return PSG_ERR_INVALID; }
     o->pcg_mode = mode;
     return PSG_OK;
 }
@@ -606,31 +606,46 @@ int psg_opt_probe_pairs(psg_optimizer* o, float* m, float* n, unsigned char* ok,
     return probe_common(o, m, n, ok, I3, rend3, nullptr, nullptr);
 }
 
-int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step_info* info) {
-    PSG_NEED_INIT(o)
-    if (block < 0 || block > 3) { set_error("psg_opt_step: unknown block %d", block); return PSG_ERR_INVALID; }
-    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO)) {
-        set_error("psg_opt_step: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
-                  "the reference's README asks for reg albedo = 0");
-        return PSG_ERR_UNSUPPORTED;
-    }
-    PSG_TRY
-    PSG_CUDA(cudaSetDevice(o->vol->device));
+// ---- one block = queue (no host wait) + finish (after fetch_mail) ------------------------------------------------
+namespace {
+
+struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; };
+
+// queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
+Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot) {
+    Pending p; p.block = block; p.slot = slot; p.damping = damping;
     const bool led = o->set.model == PSG_MODEL_LED;
-    psg_step_info inf;
-    memset(&inf, 0, sizeof(inf));
     o->last_block = block;
     if (block == PSG_BLOCK_ALBEDO) {
         const size_t n = (size_t)3 * o->S;
         o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
-        float* bdev = o->vecs.p; float* ddev = o->vecs.p + n;
-        long long acc = 0;
-        sweep_albedo(o, damping, &acc, bdev, ddev);
-        inf.n = (int)n; inf.cg_success = 1; inf.cg_iterations = 0; inf.cg_error = 0.f; inf.applied = 1; inf.n_accepted = acc;
+        launch_albedo(o, damping, o->vecs.p, o->vecs.p + n, slot);
+    } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
+        p.nred = launch_small_block(o, block, slot);
+    } else {
+        launch_dist_sweep(o, flags, slot);
+        launch_dist_solve(o, damping);
+        // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242).  The
+        // verdict stays on the device: the update kernels read it, the host learns it with the next round trip.
+        launch_dist_update(o, /*only_on_success=*/!led);
+    }
+    return p;
+}
+
+// host part of a block once fetch_mail has brought its results: the small solves and their updates, the step record
+void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
+    const bool led = o->set.model == PSG_MODEL_LED;
+    const int block = p.block;
+    psg_step_info inf;
+    memset(&inf, 0, sizeof(inf));
+    if (block == PSG_BLOCK_ALBEDO) {
+        const size_t n = (size_t)3 * o->S;
+        inf.n = (int)n; inf.cg_success = 1; inf.cg_iterations = 0; inf.cg_error = 0.f; inf.applied = 1;
+        inf.n_accepted = (long long)(mail_slot(o, p.slot)[5] + 0.5);
         o->last_n = (int)n;
     } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
         std::vector<double> Hd, bd;
-        sweep_small_block(o, block, Hd, bd);
+        unpack_small_block(o, block, p.slot, Hd, bd);
         const int bs = block == PSG_BLOCK_POSE ? 6 : (led ? 3 : o->nb);
         const int nblk = (block == PSG_BLOCK_LIGHT && led) ? 1 : o->F;
         const int n = bs * nblk;
@@ -639,10 +654,10 @@ int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step
         std::vector<float> Hf(Hd.size()), bf(bd.size()), x((size_t)n, 0.f);
         for (size_t i = 0; i < Hd.size(); ++i) Hf[i] = (float)Hd[i];
         for (size_t i = 0; i < bd.size(); ++i) bf[i] = (float)bd[i];
-        if (damp && damping != 0.f)
+        if (damp && p.damping != 0.f)
             for (int i = 0; i < n; ++i) {
                 float& d = Hf[(size_t)(i / bs) * bs * bs + (i % bs) * bs + (i % bs)];
-                d = d + damping * d;
+                d = d + p.damping * d;
             }
         const CgVerdict v = eigen_like_cg(nblk, bs, Hf.data(), bf.data(), x.data());
         inf.n = n; inf.cg_success = v.success; inf.cg_iterations = v.iters; inf.cg_error = v.err;
@@ -660,17 +675,126 @@ int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step
             if (!led || v.success) { update_poses(o, x.data()); inf.applied = 1; }
         }
     } else {
-        sweep_dist(o, flags);
-        int ok = 1, iters = 0; float err = 0.f;
-        solve_dist(o, damping, &ok, &iters, &err);
+        int ok = 1, iters = 0; float err = 0.f; long long acc = 0;
+        read_dist_verdict(o, &ok, &iters, &err, &acc);
         inf.n = o->S; inf.cg_success = ok; inf.cg_iterations = iters; inf.cg_error = err;
+        inf.applied = (led || ok) ? 1 : 0; inf.n_accepted = acc;
         o->last_n = o->S;
-        // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242)
-        if (led || ok) { long long acc = 0; apply_dist_update(o, &acc); inf.applied = 1; inf.n_accepted = acc; }
     }
-    inf.energy_before = o->S > 0 ? o->last_energy_sum / (double)o->S : 0.0;
+    const double* sc = mail_slot(o, p.slot);
+    o->last_energy_sum = sc[6];
+    o->last_active = (long long)(sc[7] + 0.5);
+    inf.energy_before = o->S > 0 ? sc[6] / (double)o->S : 0.0;
     inf.n_active_before = o->last_active;
-    if (info) *info = inf;
+    if (out) *out = inf;
+}
+
+}  // namespace
+
+int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step_info* info) {
+    PSG_NEED_INIT(o)
+    if (block < 0 || block > 3) { set_error("psg_opt_step: unknown block %d", block); return PSG_ERR_INVALID; }
+    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO)) {
+        set_error("psg_opt_step: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
+                  "the reference's README asks for reg albedo = 0");
+        return PSG_ERR_UNSUPPORTED;
+    }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const Pending p = queue_block(o, block, damping, flags, 0);
+    fetch_mail(o, p.nred);
+    finish_block(o, p, info);
+    return PSG_OK;
+    PSG_CATCH
+}
+
+// One pass of the reference's while-body with as few host waits as the data flow allows: a block whose result the host
+// does not need before the next launch (albedo, distance) is queued behind it, and the host waits only where a small
+// system has to be solved (light, pose) and for the closing energy.  SH: albedo+light | distance+pose | energy;
+// LED: light | albedo+distance+pose | energy.
+int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_iteration_info* out) {
+    PSG_NEED_INIT(o)
+    if (!cfg) { set_error("psg_opt_iteration: null configuration"); return PSG_ERR_INVALID; }
+    if (cfg->reg_flags & PSG_REG_ALBEDO) {
+        set_error("psg_opt_iteration: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path");
+        return PSG_ERR_UNSUPPORTED;
+    }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    const bool led = o->set.model == PSG_MODEL_LED;
+    psg_iteration_info R;
+    memset(&R, 0, sizeof(R));
+    int order[4];
+    if (led) { order[0] = PSG_BLOCK_LIGHT; order[1] = PSG_BLOCK_ALBEDO; }
+    else { order[0] = PSG_BLOCK_ALBEDO; order[1] = PSG_BLOCK_LIGHT; }
+    order[2] = PSG_BLOCK_DIST; order[3] = PSG_BLOCK_POSE;
+    const int enabled[4] = { cfg->albedo, cfg->light, cfg->distance, cfg->pose };   // indexed by PSG_BLOCK_*
+    static_assert(PSG_BLOCK_ALBEDO == 0 && PSG_BLOCK_LIGHT == 1 && PSG_BLOCK_DIST == 2 && PSG_BLOCK_POSE == 3, "block ids");
+
+    Pending queued[4];
+    int nq = 0, slot = 0;
+    bool reg_queued = false;
+    int last_run = -1;
+    auto flush = [&](size_t nred) {
+        fetch_mail(o, nred);
+        for (int i = 0; i < nq; ++i) {
+            finish_block(o, queued[i], &R.block[queued[i].block]);
+            R.ran[queued[i].block] = 1;
+        }
+        if (reg_queued) {
+            const double* r = mail_slot(o, kSlotReg);
+            R.reg_normal_after_dist = o->S > 0 ? r[0] / (double)o->S : 0.0;
+            R.reg_laplacian_after_dist = o->S > 0 ? r[1] / (double)o->S : 0.0;
+            reg_queued = false;
+        }
+        nq = 0; slot = 0;
+    };
+    for (int k = 0; k < 4; ++k) {
+        const int block = order[k];
+        if (!enabled[block]) continue;
+        const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) : 0;
+        queued[nq] = queue_block(o, block, cfg->damping, flags, slot);
+        const size_t nred = queued[nq].nred;
+        ++nq; ++slot;
+        last_run = block;
+        if (block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN))) {
+            launch_reg_energies(o, kSlotReg);   // getNormalEnergy / getLaplacianEnergy after the distance update
+            reg_queued = true;
+        }
+        if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) flush(nred);   // the host solves this one now
+    }
+    // closing energy (the convergence test needs it); blocks still queued ride on the same round trip
+    if (last_run >= 0 || cfg->closing_energy) {
+        launch_energy(o, slot);
+        const int eslot = slot;
+        // flush() resets `slot`, read the closing energy first
+        fetch_mail(o, 0);
+        const double* sc = mail_slot(o, eslot);
+        R.energy_end = o->S > 0 ? sc[6] / (double)o->S : 0.0;
+        R.n_active_end = (long long)(sc[7] + 0.5);
+        for (int i = 0; i < nq; ++i) {
+            finish_block(o, queued[i], &R.block[queued[i].block]);
+            R.ran[queued[i].block] = 1;
+        }
+        if (reg_queued) {
+            const double* r = mail_slot(o, kSlotReg);
+            R.reg_normal_after_dist = o->S > 0 ? r[0] / (double)o->S : 0.0;
+            R.reg_laplacian_after_dist = o->S > 0 ? r[1] / (double)o->S : 0.0;
+        }
+        o->last_energy_sum = sc[6];
+        o->last_active = R.n_active_end;
+    }
+    // energy after block k = energy the next executed block started from (or the closing energy)
+    {
+        double next = R.energy_end;
+        for (int k = 3; k >= 0; --k) {
+            const int block = order[k];
+            if (!R.ran[block]) continue;
+            R.energy_after[block] = next;
+            next = R.block[block].energy_before;
+        }
+    }
+    if (out) *out = R;
     return PSG_OK;
     PSG_CATCH
 }

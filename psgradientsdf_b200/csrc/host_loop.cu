@@ -183,42 +183,40 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
     float E_total = total_energy(o, e, file, echo);
     std::vector<float> E_vec(1, E_total);
 
-    const char* kAlbedo = "albedo"; const char* kLight = "light"; const char* kDist = "distance"; const char* kPose = "pose";
     // The reference evaluates getPSEnergy() after every block.  Here every block's own sweep already yields the energy of
-    // the state it started from (psg_step_info::energy_before), so the log line of block k is completed when block k+1 has
-    // run, and only the last enabled block of an iteration needs an explicit energy sweep.
-    const char* pending_label = nullptr;
-    auto finish_pending = [&](float E_now) {
-        if (!pending_label) return;
-        e.E = E_now;
-        if (echo) std::cout << "===> [" << R.iterations << "]: after " << pending_label << " optimization: ";
-        if (file.is_open()) file << "===> [" << R.iterations << "]: after " << pending_label << " optimization: \n";
-        E_total = total_energy(o, e, file, echo);
-        pending_label = nullptr;
-    };
-    auto run_block = [&](int block, const char* label) -> int {
-        int flags = 0;
-        if (block == PSG_BLOCK_ALBEDO && albedo_reg) flags |= PSG_REG_ALBEDO;
-        if (block == PSG_BLOCK_DIST && normal_reg) flags |= PSG_REG_NORMAL;
-        if (block == PSG_BLOCK_DIST && laplacian_reg) flags |= PSG_REG_LAPLACIAN;
-        psg_step_info info;
-        const int st = psg_opt_step(o, block, damping, flags, &info);
+    // the state it started from, and psg_opt_iteration queues the blocks with three host waits per pass; the log lines of an
+    // iteration are written once it has returned, in the reference's order and with the values the reference would print.
+    const char* labels[4];
+    labels[PSG_BLOCK_ALBEDO] = "albedo"; labels[PSG_BLOCK_LIGHT] = "light"; labels[PSG_BLOCK_DIST] = "distance"; labels[PSG_BLOCK_POSE] = "pose";
+    const int order_sh[4] = { PSG_BLOCK_ALBEDO, PSG_BLOCK_LIGHT, PSG_BLOCK_DIST, PSG_BLOCK_POSE };
+    const int order_led[4] = { PSG_BLOCK_LIGHT, PSG_BLOCK_ALBEDO, PSG_BLOCK_DIST, PSG_BLOCK_POSE };
+    const int* order = led ? order_led : order_sh;
+    if (albedo_reg && cfg->albedo) {
+        psg::set_error("psg_opt_alternating_optimize: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
+                       "the reference's README asks for reg albedo = 0");
+        return PSG_ERR_UNSUPPORTED;
+    }
+    auto run_iteration = [&]() -> int {
+        psg_iteration_config ic;
+        memset(&ic, 0, sizeof(ic));
+        ic.light = cfg->light; ic.albedo = cfg->albedo; ic.distance = cfg->distance; ic.pose = cfg->pose;
+        ic.damping = damping;
+        ic.reg_flags = (normal_reg ? PSG_REG_NORMAL : 0) | (laplacian_reg ? PSG_REG_LAPLACIAN : 0);
+        psg_iteration_info info;
+        const int st = psg_opt_iteration(o, &ic, &info);
         if (st != PSG_OK) return st;
-        finish_pending((float)info.energy_before);   // the previous block's line, with the regulariser energies of that time
-        if (block == PSG_BLOCK_ALBEDO && albedo_reg) { psg_opt_reg_energies(o, nullptr, nullptr, &dr); e.Er = (float)dr; }
-        if (block == PSG_BLOCK_DIST) {
-            if (normal_reg) { psg_opt_reg_energies(o, &dn, nullptr, nullptr); e.En = (float)dn; }
-            if (laplacian_reg) { psg_opt_reg_energies(o, nullptr, &dl, nullptr); e.El = (float)dl; }
+        for (int k = 0; k < 4; ++k) {
+            const int block = order[k];
+            if (!info.ran[block]) continue;
+            e.E = (float)info.energy_after[block];
+            if (block == PSG_BLOCK_DIST) {
+                if (normal_reg) e.En = (float)info.reg_normal_after_dist;
+                if (laplacian_reg) e.El = (float)info.reg_laplacian_after_dist;
+            }
+            if (echo) std::cout << "===> [" << R.iterations << "]: after " << labels[block] << " optimization: ";
+            if (file.is_open()) file << "===> [" << R.iterations << "]: after " << labels[block] << " optimization: \n";
+            E_total = total_energy(o, e, file, echo);
         }
-        pending_label = label;
-        return PSG_OK;
-    };
-    auto end_of_iteration = [&]() -> int {
-        if (!pending_label) return PSG_OK;
-        float E_now = 0.f;
-        const int st = ps_energy(o, &E_now);
-        if (st != PSG_OK) return st;
-        finish_pending(E_now);
         return PSG_OK;
     };
 
@@ -228,16 +226,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
     while (iter < cfg->max_it) {
         R.iterations = iter;
         const auto t0 = std::chrono::steady_clock::now();
-        if (led) {
-            if (cfg->light) PSG_RUN(run_block(PSG_BLOCK_LIGHT, kLight));
-            if (cfg->albedo) PSG_RUN(run_block(PSG_BLOCK_ALBEDO, kAlbedo));
-        } else {
-            if (cfg->albedo) PSG_RUN(run_block(PSG_BLOCK_ALBEDO, kAlbedo));
-            if (cfg->light) PSG_RUN(run_block(PSG_BLOCK_LIGHT, kLight));
-        }
-        if (cfg->distance) PSG_RUN(run_block(PSG_BLOCK_DIST, kDist));
-        if (cfg->pose) PSG_RUN(run_block(PSG_BLOCK_POSE, kPose));
-        PSG_RUN(end_of_iteration());
+        PSG_RUN(run_iteration());
         const auto t1 = std::chrono::steady_clock::now();
         const double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
         ms_sum += ms;

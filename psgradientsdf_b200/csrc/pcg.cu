@@ -31,6 +31,7 @@ struct PcgArgs {
     float* rhs; float* invd; float* ddiag;   // assembled rhs, 1 / damped diagonal, damping * diagonal
     float* x; float* r; float* p; float* tmp; float* U;   // U: 4 planes
     double* partials;        // [3][gridDim.x]
+    unsigned long long* barrier;   // grid barrier arrival counter (zeroed by k_dist_assemble)
     float* result;           // [0] iterations, [1] residualNorm2, [2] rhsNorm2, [3] threshold
     float damping;
     int max_iters;
@@ -42,6 +43,7 @@ __device__ __forceinline__ int tri(int i, int k) { return i * (i + 1) / 2 + k; }
 __global__ void __launch_bounds__(kPcgBlock) k_dist_assemble(PcgArgs A) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     const int S = A.S;
+    if (s == 0) *A.barrier = 0ull;
     if (s >= S) return;
     float rhs = A.blk[(long long)10 * S + s];
     float diag = A.blk[(long long)0 * S + s];
@@ -91,15 +93,74 @@ __device__ __forceinline__ double grid_total(const double* partials, int nblocks
     return s_buf[0];
 }
 
-// Large surfaces: cooperative launch over the whole GPU, grid.sync() between phases, vectors in global memory.
-// Same three-barrier iteration as the cluster kernel below (the search-direction update is folded into the stencil
-// phase: neighbours' new p is recomputed from the published r, 1/diag and previous p).  A thread walks its rows in
-// groups of RPT and issues the loads of a whole group before using any of them, so a phase costs two dependent memory
-// round trips per group instead of two per row.
+// two sums at once (one pair of block barriers instead of two)
+template <int BS>
+__device__ __forceinline__ double2 block_sum2(double a, double b, double* s_buf /* 2 * BS / 32 */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b);
+    __syncthreads();
+    if (lane == 0) { s_buf[warp] = a; s_buf[BS / 32 + warp] = b; }
+    __syncthreads();
+    double2 t = make_double2(0.0, 0.0);
+    if (warp == 0) {
+        t.x = lane < (BS / 32) ? s_buf[lane] : 0.0;
+        t.y = lane < (BS / 32) ? s_buf[BS / 32 + lane] : 0.0;
+        t.x = warp_sum(t.x); t.y = warp_sum(t.y);
+    }
+    return t;   // valid in warp 0
+}
+
+// block partials written by other blocks: read through L2 (an SM's L1 may still hold last iteration's line)
+__device__ __forceinline__ double grid_total_cg(const double* partials, int nblocks, double* s_buf) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (warp == 0) {
+        double t = 0.0;
+        for (int i = lane; i < nblocks; i += 32) t += __ldcg(partials + i);
+        t = warp_sum(t);
+        if (lane == 0) s_buf[0] = t;
+    }
+    __syncthreads();
+    return s_buf[0];
+}
+
+__device__ __forceinline__ double2 grid_total2_cg(const double* pa, const double* pb, int nblocks, double* s_buf) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (warp == 0) {
+        double ta = 0.0, tb = 0.0;
+        for (int i = lane; i < nblocks; i += 32) { ta += __ldcg(pa + i); tb += __ldcg(pb + i); }
+        ta = warp_sum(ta); tb = warp_sum(tb);
+        if (lane == 0) { s_buf[0] = ta; s_buf[1] = tb; }
+    }
+    __syncthreads();
+    return make_double2(s_buf[0], s_buf[1]);
+}
+
+// Grid-wide barrier of the cooperative launch (all blocks co-resident): one monotonic arrival counter, zeroed by
+// k_dist_assemble; a block arrives with a gpu-scope release and its thread 0 spins with gpu-scope acquires.  Data that other
+// blocks wrote before the barrier is then read with ld.global.cg (L2), never through this SM's L1.
+__device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned long long& target, unsigned nb) {
+    __syncthreads();
+    target += nb;
+    if (threadIdx.x == 0) {
+        asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(ctr) : "memory");
+        unsigned long long v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+        } while (v < target);
+    }
+    __syncthreads();
+}
+
+// Cooperative launch over the whole GPU, vectors in global memory, three grid barriers per iteration (the search-direction
+// update is folded into the stencil phase: neighbours' new p is recomputed from the published r, 1/diag and previous p).
+// A thread walks its rows in groups of RPT and issues the loads of a whole group before using any of them, so a phase costs
+// two dependent memory round trips per group instead of two per row.  RPT = 1 for small surfaces (one row per thread, every
+// SM busy), 4 for large ones.
 template <int BS, int RPT>
-__global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ pbuf /* 2 x S */) {
-    cg::grid_group grid = cg::this_grid();
-    __shared__ double s_buf[BS / 32];
+__global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* pbuf /* 2 x S */) {
+    __shared__ double s_buf[2 * (BS / 32)];
     const int S = A.S;
     const int nb = gridDim.x;
     const int T = nb * BS;
@@ -107,20 +168,24 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
     double* P0 = A.partials;
     double* P1 = A.partials + nb;
     double* P2 = A.partials + 2 * nb;
+    unsigned long long bar_target = 0;
 
     double a0 = 0.0, a1 = 0.0;
     for (int s = gtid; s < S; s += T) {
-        const float b = A.rhs[s];
-        const float pv = A.invd[s] * b;
+        const float b = __ldg(A.rhs + s);
+        const float pv = __ldg(A.invd + s) * b;
         A.x[s] = 0.f; A.r[s] = b; pbuf[s] = pv;
         a0 += (double)b * (double)b;
         a1 += (double)b * (double)pv;
     }
-    a0 = block_sum<BS>(a0, s_buf); if (threadIdx.x == 0) P0[blockIdx.x] = a0;
-    a1 = block_sum<BS>(a1, s_buf); if (threadIdx.x == 0) P1[blockIdx.x] = a1;
-    grid.sync();
-    const float rhsNorm2 = (float)grid_total(P0, nb, s_buf);
-    float absNew = (float)grid_total(P1, nb, s_buf);
+    {
+        const double2 t = block_sum2<BS>(a0, a1, s_buf);
+        if (threadIdx.x == 0) { P0[blockIdx.x] = t.x; P1[blockIdx.x] = t.y; }
+    }
+    grid_barrier(A.barrier, bar_target, nb);
+    const double2 t01 = grid_total2_cg(P0, P1, nb, s_buf);
+    const float rhsNorm2 = (float)t01.x;
+    float absNew = (float)t01.y;
     const float tol = 1.1920929e-07f;   // NumTraits<float>::epsilon(), the default tolerance
     float threshold = tol * tol * rhsNorm2;
     if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
@@ -141,8 +206,8 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
                     row[j] = base + j * T;
                     const bool in = row[j] < S;
 #pragma unroll
-                    for (int a = 0; a < 3; ++a) col[j][a] = in ? A.nbr_row[a * S + row[j]] : -1;
-                    pj[j] = in ? (A.invd[row[j]] * A.r[row[j]]) * gamma + beta * pc[row[j]] : 0.f;
+                    for (int a = 0; a < 3; ++a) col[j][a] = in ? __ldg(A.nbr_row + a * S + row[j]) : -1;
+                    pj[j] = in ? (__ldg(A.invd + row[j]) * __ldcg(A.r + row[j])) * gamma + beta * __ldcg(pc + row[j]) : 0.f;
                 }
 #pragma unroll
                 for (int j = 0; j < RPT; ++j) {
@@ -153,11 +218,11 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
 #pragma unroll
                     for (int a = 0; a < 3; ++a) {
                         const int c = col[j][a];
-                        px[a + 1] = c >= 0 ? (A.invd[c] * A.r[c]) * gamma + beta * pc[c] : 0.f;
+                        px[a + 1] = c >= 0 ? (__ldg(A.invd + c) * __ldcg(A.r + c)) * gamma + beta * __ldcg(pc + c) : 0.f;
                     }
                     float Ab[10];
 #pragma unroll
-                    for (int i = 0; i < 10; ++i) Ab[i] = A.blk[(long long)i * S + row[j]];
+                    for (int i = 0; i < 10; ++i) Ab[i] = __ldg(A.blk + (long long)i * S + row[j]);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         float u = 0.f;
@@ -171,7 +236,7 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
                     }
                 }
             }
-            grid.sync();
+            grid_barrier(A.barrier, bar_target, nb);
             // ---- phase 2: tmp_s = u_s[0] + incident u + damping * diag * p_s ; p . tmp
             double pAp = 0.0;
             for (int base = gtid; base < S; base += T * RPT) {
@@ -179,29 +244,29 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
 #pragma unroll
                 for (int j = 0; j < RPT; ++j)
 #pragma unroll
-                    for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < S) ? A.inc[h * S + base + j * T] : -1;
+                    for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < S) ? __ldg(A.inc + h * S + base + j * T) : -1;
 #pragma unroll
                 for (int j = 0; j < RPT; ++j) {
                     const int s = base + j * T;
                     if (s >= S) continue;
-                    float y = A.U[s];
+                    float y = __ldcg(A.U + s);
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int a = 0; a < 3; ++a) {
                             const int t = tn[j][h * 3 + a];
-                            if (t >= 0) y += A.U[(long long)(a + 1) * S + t];
+                            if (t >= 0) y += __ldcg(A.U + (long long)(a + 1) * S + t);
                         }
-                    const float ps = pn[s];
-                    y += A.ddiag[s] * ps;
+                    const float ps = __ldcg(pn + s);
+                    y += __ldg(A.ddiag + s) * ps;
                     A.tmp[s] = y;
                     pAp += (double)ps * (double)y;
                 }
             }
             pAp = block_sum<BS>(pAp, s_buf); if (threadIdx.x == 0) P0[blockIdx.x] = pAp;
-            grid.sync();
-            const float alpha = absNew / (float)grid_total(P0, nb, s_buf);
-            // ---- phase 3: x += alpha p ; residual -= alpha tmp ; norms
+            grid_barrier(A.barrier, bar_target, nb);
+            const float alpha = absNew / (float)grid_total_cg(P0, nb, s_buf);
+            // ---- phase 3 (own rows only): x += alpha p ; residual -= alpha tmp ; norms
             double rn = 0.0, rz = 0.0;
             for (int base = gtid; base < S; base += T * RPT) {
                 float xv[RPT], pv[RPT], rv[RPT], tv[RPT], iv[RPT];
@@ -209,8 +274,8 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
                 for (int j = 0; j < RPT; ++j) {
                     const int s = base + j * T;
                     const bool in = s < S;
-                    xv[j] = in ? A.x[s] : 0.f; pv[j] = in ? pn[s] : 0.f; rv[j] = in ? A.r[s] : 0.f;
-                    tv[j] = in ? A.tmp[s] : 0.f; iv[j] = in ? A.invd[s] : 0.f;
+                    xv[j] = in ? __ldcg(A.x + s) : 0.f; pv[j] = in ? __ldcg(pn + s) : 0.f; rv[j] = in ? __ldcg(A.r + s) : 0.f;
+                    tv[j] = in ? __ldcg(A.tmp + s) : 0.f; iv[j] = in ? __ldg(A.invd + s) : 0.f;
                 }
 #pragma unroll
                 for (int j = 0; j < RPT; ++j) {
@@ -223,13 +288,16 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* __restrict__ 
                     rz += (double)r2 * (double)(iv[j] * r2);
                 }
             }
-            rn = block_sum<BS>(rn, s_buf); if (threadIdx.x == 0) P1[blockIdx.x] = rn;
-            rz = block_sum<BS>(rz, s_buf); if (threadIdx.x == 0) P2[blockIdx.x] = rz;
-            grid.sync();
-            residualNorm2 = (float)grid_total(P1, nb, s_buf);
+            {
+                const double2 t = block_sum2<BS>(rn, rz, s_buf);
+                if (threadIdx.x == 0) { P1[blockIdx.x] = t.x; P2[blockIdx.x] = t.y; }
+            }
+            grid_barrier(A.barrier, bar_target, nb);
+            const double2 t12 = grid_total2_cg(P1, P2, nb, s_buf);
+            residualNorm2 = (float)t12.x;
             if (residualNorm2 < threshold) break;
             const float absOld = absNew;
-            absNew = (float)grid_total(P2, nb, s_buf);
+            absNew = (float)t12.y;
             beta = absNew / absOld;
             gamma = 1.f;
             cur ^= 1;
@@ -393,8 +461,16 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
 }
 
 // Optimizer::updateDist (OptimizerAux.cpp:162-188): d -= delta only where |delta| < sqrt(3) * voxel_size (double compare)
+// IterativeSolverBase: info = error <= tolerance ? Success : NoConvergence, error = sqrt(residualNorm2 / rhsNorm2)
+__device__ __forceinline__ bool pcg_success(const float* __restrict__ verdict) {
+    const float err = verdict[2] != 0.f ? sqrtf(verdict[1] / verdict[2]) : 0.f;
+    return err <= 1.1920929e-07f;
+}
+
 __global__ void __launch_bounds__(256) k_dist_update(VolView vol, const int* __restrict__ lin, int S, const float* __restrict__ delta,
-                                                    double thr, unsigned long long* accepted) {
+                                                    double thr, unsigned long long* accepted, const float* __restrict__ verdict,
+                                                    int only_on_success) {
+    if (only_on_success && !pcg_success(verdict)) return;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     int acc = 0;
     if (s < S) {
@@ -407,7 +483,9 @@ __global__ void __launch_bounds__(256) k_dist_update(VolView vol, const int* __r
 
 // Optimizer::updateGrad (OptimizerAux.cpp:152-160): grad <- finite-difference gradient (not normalised); also refreshes
 // the compact per-row records (own distance, new gradient, neighbour distances)
-__global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf, float vs_inv) {
+__global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf, float vs_inv, const float* __restrict__ verdict,
+                                                    int only_on_success) {
+    if (only_on_success && !pcg_success(verdict)) return;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int S = surf.S;
     if (t >= S) return;
@@ -431,9 +509,11 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
 }
 
 // vecs layout (floats, planes of S): 0..13 stencil blocks | 14 rhs | 15 invd | 16 ddiag | 17 x | 18 r | 19 p | 20 tmp | 21..24 U
-void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float* err) {
+// queues the assembly and the solve; the verdict lands in mail slot kSlotPcg
+void launch_dist_solve(psg_optimizer* o, float damping) {
     const int S = o->S;
-    *success = 1; *iters = 0; *err = 0.f;
+    o->red.alloc(kRedDoubles + kMailDoubles);
+    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotPcg, 0, 16 * sizeof(double), o->stream));   // verdict + accepted counter
     if (S == 0) return;
     o->vecs.alloc((size_t)S * 25 + 8);
     float* base = o->vecs.p;
@@ -442,24 +522,43 @@ void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float
     A.rhs = base + (size_t)14 * S; A.invd = base + (size_t)15 * S; A.ddiag = base + (size_t)16 * S;
     A.x = base + (size_t)17 * S; A.r = base + (size_t)18 * S; A.p = base + (size_t)19 * S; A.tmp = base + (size_t)20 * S;
     A.U = base + (size_t)21 * S;
-    A.result = base + (size_t)25 * S;
+    A.result = reinterpret_cast<float*>(mail_dev(o) + 8 * kSlotPcg);
     A.damping = damping;
     A.max_iters = 2 * S;
+
+    constexpr int kClusterMax = 8, kClusterRows = 1 << 16;
+    const bool use_cluster = o->pcg_mode == 1 && S <= kClusterRows;
+    int dev = 0, sms = 0;
+    PSG_CUDA(cudaGetDevice(&dev));
+    PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // grid kernel geometry: one row per thread while that still leaves SMs idle, four rows per thread beyond
+    const int rpt = (S <= sms * kPcgBlock * 2) ? 1 : 4;
+    int grid = 0;
+    if (!use_cluster) {
+        int per_sm = 0;
+        if (rpt == 1) PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
+        else PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
+        if (per_sm < 1) { set_error("PCG kernel does not fit on an SM"); throw CudaError{-1}; }
+        if (per_sm > 4) per_sm = 4;
+        grid = sms * per_sm;
+        const int need = (S + kPcgBlock * rpt - 1) / (kPcgBlock * rpt);
+        if (grid > need) grid = need;
+    }
+    o->pcg_partials.alloc((size_t)3 * (use_cluster ? kClusterMax : grid) + 1);
+    A.partials = o->pcg_partials.p + 1;
+    A.barrier = reinterpret_cast<unsigned long long*>(o->pcg_partials.p);
+    o->pcg_pbuf.alloc((size_t)2 * S);
+    float* pbuf = o->pcg_pbuf.p;
 
     { Prof pf(o->stream, KID_PCG_ASSEMBLE); k_dist_assemble<<<(S + kPcgBlock - 1) / kPcgBlock, kPcgBlock, 0, o->stream>>>(A); }
     PSG_LAUNCH_CHECK();
 
-    constexpr int kClusterMax = 8, kClusterRows = 1 << 16;
-    if (S <= kClusterRows && o->pcg_mode != 2) {
+    if (use_cluster) {
         // one thread-block cluster: as many CTAs as there is work for, at most the portable 8
         int nc = (S + kClusterBlock - 1) / kClusterBlock;
         if (nc > kClusterMax) nc = kClusterMax;
         const int threads = nc * kClusterBlock;
-        const int rpt = (S + threads - 1) / threads;
-        o->pcg_partials.alloc((size_t)3 * nc);
-        A.partials = o->pcg_partials.p;
-        o->pcg_pbuf.alloc((size_t)2 * S);
-        float* pbuf = o->pcg_pbuf.p;
+        const int crpt = (S + threads - 1) / threads;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(nc); cfg.blockDim = dim3(kClusterBlock); cfg.dynamicSmemBytes = 0; cfg.stream = o->stream;
         cudaLaunchAttribute attr[1];
@@ -467,59 +566,45 @@ void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float
         attr[0].val.clusterDim.x = nc; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
         Prof pf(o->stream, KID_PCG_SOLVE);
-        if (rpt <= 1) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<1>, A, pbuf));
-        else if (rpt <= 2) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<2>, A, pbuf));
-        else if (rpt <= 4) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<4>, A, pbuf));
+        if (crpt <= 1) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<1>, A, pbuf));
+        else if (crpt <= 2) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<2>, A, pbuf));
+        else if (crpt <= 4) PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<4>, A, pbuf));
         else PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_pcg_cluster<8>, A, pbuf));
     } else {
-        int dev = 0, sms = 0, per_sm = 0;
-        PSG_CUDA(cudaGetDevice(&dev));
-        PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
-        if (per_sm < 1) { set_error("PCG kernel does not fit on an SM"); throw CudaError{-1}; }
-        if (per_sm > 4) per_sm = 4;
-        int grid = sms * per_sm;
-        const int need = (S + kPcgBlock * 4 - 1) / (kPcgBlock * 4);
-        if (grid > need) grid = need;
-        o->pcg_partials.alloc((size_t)3 * grid);
-        A.partials = o->pcg_partials.p;
-        o->pcg_pbuf.alloc((size_t)2 * S);
-        float* pbuf = o->pcg_pbuf.p;
+        // cooperative launch = the driver guarantees all blocks are co-resident, which the in-kernel barrier relies on
         void* args[] = { &A, &pbuf };
-        { Prof pf(o->stream, KID_PCG_SOLVE);
-          PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 4>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream)); }
+        Prof pf(o->stream, KID_PCG_SOLVE);
+        if (rpt == 1) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 1>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
+        else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 4>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
     }
-    o->ensure_host_staging();
-    float* res = reinterpret_cast<float*>(o->host_staging);   // pinned: a pageable destination makes the copy synchronous and slow
-    PSG_CUDA(cudaMemcpyAsync(res, A.result, 4 * sizeof(float), cudaMemcpyDeviceToHost, o->stream));
-    PSG_CUDA(cudaStreamSynchronize(o->stream));
+}
+
+void launch_dist_update(psg_optimizer* o, bool only_on_success) {
+    const int S = o->S;
+    if (S == 0) return;
+    float* base = o->vecs.p;
+    const float* delta = base + (size_t)17 * S;
+    const float* verdict = reinterpret_cast<const float*>(mail_dev(o) + 8 * kSlotPcg);
+    unsigned long long* cnt = reinterpret_cast<unsigned long long*>(mail_dev(o) + 8 * kSlotCount);
+    const VolView vol = o->vol->view();
+    const SurfView sv = surf_view(o);
+    const double thr = sqrt(3.0) * (double)o->vs;
+    const int gate = only_on_success ? 1 : 0;
+    { Prof pf(o->stream, KID_DIST_UPDATE); k_dist_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, S, delta, thr, cnt, verdict, gate); }
+    PSG_LAUNCH_CHECK();
+    { Prof pf(o->stream, KID_GRAD_UPDATE); k_grad_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, sv, o->vs_inv, verdict, gate); }
+    PSG_LAUNCH_CHECK();
+}
+
+void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted) {
+    *success = 1; *iters = 0; *err = 0.f; *accepted = 0;
+    if (o->S == 0) return;
+    const float* res = reinterpret_cast<const float*>(mail_slot(o, kSlotPcg));
     *iters = (int)res[0];
     const float tol = 1.1920929e-07f;
     *err = res[2] != 0.f ? sqrtf(res[1] / res[2]) : 0.f;
     *success = (*err <= tol) ? 1 : 0;   // IterativeSolverBase: info = error <= tolerance ? Success : NoConvergence
-}
-
-void apply_dist_update(psg_optimizer* o, long long* accepted) {
-    const int S = o->S;
-    *accepted = 0;
-    if (S == 0) return;
-    float* base = o->vecs.p;
-    const float* delta = base + (size_t)17 * S;
-    o->red.alloc(kMaxFrames * 64 + 8);
-    unsigned long long* cnt = reinterpret_cast<unsigned long long*>(o->red.p);
-    PSG_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), o->stream));
-    const VolView vol = o->vol->view();
-    const SurfView sv = surf_view(o);
-    const double thr = sqrt(3.0) * (double)o->vs;
-    { Prof pf(o->stream, KID_DIST_UPDATE); k_dist_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, S, delta, thr, cnt); }
-    PSG_LAUNCH_CHECK();
-    { Prof pf(o->stream, KID_GRAD_UPDATE); k_grad_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, sv, o->vs_inv); }
-    PSG_LAUNCH_CHECK();
-    o->ensure_host_staging();
-    unsigned long long* h = reinterpret_cast<unsigned long long*>(o->host_staging);
-    PSG_CUDA(cudaMemcpyAsync(h, cnt, sizeof(*h), cudaMemcpyDeviceToHost, o->stream));
-    PSG_CUDA(cudaStreamSynchronize(o->stream));
-    *accepted = (long long)*h;
+    *accepted = (long long)*reinterpret_cast<const unsigned long long*>(mail_slot(o, kSlotCount));
 }
 
 }  // namespace psg

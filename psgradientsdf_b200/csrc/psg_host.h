@@ -106,7 +106,7 @@ struct psg_optimizer {
     psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
     void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
     int rank = 0, world = 1;
-    int pcg_mode = 0;                        // 0 = auto (cluster kernel for small surfaces), 2 = always the cooperative-grid kernel
+    int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
     psg::DevBuf<double> pcg_partials;
@@ -114,7 +114,7 @@ struct psg_optimizer {
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
     std::vector<float> lastvb, lastvd;
     int last_n = 0, last_block = -1;
-    // pinned host staging: [kMaxFrames*64 + 8] doubles of reduction results, then the per-keyframe table
+    // pinned host staging: kRedDoubles + kMailDoubles doubles of reduction results, then the per-keyframe table
     double* host_staging = nullptr;
     psg::FrameParams* host_frames = nullptr;
     void ensure_host_staging();
@@ -124,6 +124,14 @@ struct psg_optimizer {
 };
 
 namespace psg {
+
+// o->red: kRedDoubles of per-keyframe sums, then the mailbox (8 slots x 8 doubles) every kernel of an outer iteration reports
+// into: slots 0..4 sweep scalars (one per sweep in flight), then the three below
+constexpr int kRedDoubles = kMaxFrames * 64;
+constexpr int kMailDoubles = 64;
+constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
+constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
+constexpr int kSlotCount = 7;    // unsigned long long: accepted distance updates
 
 // ---- volume.cu
 void launch_fill_volume(psg_volume* v);
@@ -153,13 +161,21 @@ void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
 void sweep_init_albedo(psg_optimizer* o);
 void sweep_led_light_init(psg_optimizer* o, double sums[6]);
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3);
-void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b_dev, float* delta_dev);
-void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& H, std::vector<double>& b);
-void sweep_dist(psg_optimizer* o, int flags);
+// queue-only pieces (no host wait) and the one round trip that collects their results
+double* mail_dev(psg_optimizer* o);
+const double* fetch_mail(psg_optimizer* o, size_t n_red_doubles);
+const double* mail_slot(const psg_optimizer* o, int slot);
+void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot);
+size_t launch_small_block(psg_optimizer* o, int block, int slot);
+void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<double>& H, std::vector<double>& b);
+void launch_dist_sweep(psg_optimizer* o, int flags, int slot);
+void launch_energy(psg_optimizer* o, int slot);
+void launch_reg_energies(psg_optimizer* o, int slot);
 void reg_energies(psg_optimizer* o, double* En, double* El, double* Er);
 
 // ---- pcg.cu
-void solve_dist(psg_optimizer* o, float damping, int* success, int* iters, float* err);
-void apply_dist_update(psg_optimizer* o, long long* accepted);
+void launch_dist_solve(psg_optimizer* o, float damping);              // assemble + PCG; verdict -> mail slot kSlotPcg
+void launch_dist_update(psg_optimizer* o, bool only_on_success);     // gated on the device by the PCG verdict; count -> kSlotCount
+void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted);   // after fetch_mail
 
 }  // namespace psg

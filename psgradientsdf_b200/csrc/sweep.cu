@@ -705,7 +705,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
-static SweepArgs base_args(psg_optimizer* o) {
+static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     upload_frames(o);   // (re)allocates o->frames on first use, so it must precede the pointer capture below
     SweepArgs A;
     memset(&A, 0, sizeof(A));
@@ -718,9 +718,9 @@ static SweepArgs base_args(psg_optimizer* o) {
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
-    o->red.alloc(kMaxFrames * 64 + 8);
+    o->red.alloc(kRedDoubles + kMailDoubles);
     A.red = o->red.p;
-    A.scal = o->red.p + kMaxFrames * 64;
+    A.scal = mail_dev(o) + 8 * slot;
     const size_t grid = (size_t)(o->S + 31) / 32 + 1;
     const size_t ngroups = grid / kRedGroup + 2;
     o->sweep_partials.alloc((grid + ngroups) * 8);
@@ -778,19 +778,35 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
     PSG_LAUNCH_CHECK();
 }
 
-// per-keyframe reductions (n doubles) + the 8 scalars behind them, in one pinned-host round trip
-static const double* fetch_red(psg_optimizer* o, size_t n, bool reduce_over_ranks = true) {
+// Results travel through a small "mailbox" behind the per-keyframe reduction buffer: 8 slots of 8 doubles.  A launch
+// function queues kernels (and, across GPUs, the collectives on their results) without waiting; fetch_mail brings n doubles
+// of per-keyframe sums plus the whole mailbox to pinned host memory in one round trip.  Several blocks of an outer
+// iteration can therefore be in flight before the host waits once (psg_opt_iteration).
+double* mail_dev(psg_optimizer* o) { return o->red.p + kRedDoubles; }
+
+const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
-    if (reduce_over_ranks && o->world > 1) comm_allreduce_doubles(o, o->red.p, n, o->red.p + kMaxFrames * 64, 8);
     if (n) PSG_CUDA(cudaMemcpyAsync(h, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
-    PSG_CUDA(cudaMemcpyAsync(h + kMaxFrames * 64, o->red.p + kMaxFrames * 64, 8 * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaMemcpyAsync(h + kRedDoubles, mail_dev(o), kMailDoubles * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
-    o->last_energy_sum = h[kMaxFrames * 64 + 6];
-    o->last_active = (long long)(h[kMaxFrames * 64 + 7] + 0.5);
     return h;
 }
-static inline const double* scalars(const double* h) { return h + kMaxFrames * 64; }
+const double* mail_slot(const psg_optimizer* o, int slot) { return o->host_staging + kRedDoubles + 8 * slot; }
+
+static void reduce_over_ranks(psg_optimizer* o, size_t n, int slot) {
+    if (o->world > 1) comm_allreduce_doubles(o, o->red.p, n, mail_dev(o) + 8 * slot, 8);
+}
+
+// legacy one-block round trip: slot 0
+static const double* fetch_red(psg_optimizer* o, size_t n, bool over_ranks = true) {
+    if (over_ranks) reduce_over_ranks(o, n, 0);
+    const double* h = fetch_mail(o, n);
+    o->last_energy_sum = mail_slot(o, 0)[6];
+    o->last_active = (long long)(mail_slot(o, 0)[7] + 0.5);
+    return h;
+}
+static inline const double* scalars(const double* h) { return h + kRedDoubles; }
 
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
     SweepArgs A = base_args(o);
@@ -830,22 +846,36 @@ void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float*
     launch_sweep<M_PROBE>(o, A, 0, 0);
 }
 
-void sweep_albedo(psg_optimizer* o, float damping, long long* accepted, float* b_dev, float* delta_dev) {
-    SweepArgs A = base_args(o);
+void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot) {
+    SweepArgs A = base_args(o, slot);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
     if (o->world > 1) comm_allgather_rec1(o);
-    const double* sc = scalars(fetch_red(o, 0));
-    *accepted = (long long)(sc[5] + 0.5);
+    reduce_over_ranks(o, 0, slot);
 }
 
-// light / pose: returns per-keyframe lower triangles + rhs as accumulated on the device (doubles).
-void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, std::vector<double>& bout) {
-    SweepArgs A = base_args(o);
+// light / pose: queues the sweep; returns how many doubles of per-keyframe sums it leaves in o->red (0 for the LED light)
+size_t launch_small_block(psg_optimizer* o, int block, int slot) {
+    SweepArgs A = base_args(o, slot);
     const bool led = o->set.model == PSG_MODEL_LED;
+    size_t nred = 0;
     if (block == PSG_BLOCK_LIGHT && led) {
         launch_sweep<M_LIGHT>(o, A, 0, 0);
-        const double* sc = scalars(fetch_red(o, 0));
+    } else {
+        const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
+        nred = (size_t)o->F * V;
+        if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, 0);
+        else launch_sweep<M_LIGHT>(o, A, nred, 0);
+    }
+    reduce_over_ranks(o, nred, slot);
+    return nred;
+}
+
+// unpacks what fetch_mail brought back: per-keyframe lower triangles + rhs as accumulated on the device (doubles)
+void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<double>& Hout, std::vector<double>& bout) {
+    const bool led = o->set.model == PSG_MODEL_LED;
+    if (block == PSG_BLOCK_LIGHT && led) {
+        const double* sc = mail_slot(o, slot);
         Hout.assign(9, 0.0); bout.assign(3, 0.0);
         for (int c = 0; c < 3; ++c) { Hout[4 * c] = sc[c]; bout[c] = sc[3 + c]; }
         return;
@@ -853,10 +883,7 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
     const int nbk = block == PSG_BLOCK_POSE ? 6 : o->nb;
     const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
     const int NT = nbk * (nbk + 1) / 2;
-    const size_t nred = (size_t)o->F * V;
-    if (block == PSG_BLOCK_POSE) launch_sweep<M_POSE>(o, A, nred, 0);
-    else launch_sweep<M_LIGHT>(o, A, nred, 0);
-    const double* r = fetch_red(o, nred);
+    const double* r = o->host_staging;
     Hout.assign((size_t)o->F * nbk * nbk, 0.0);
     bout.assign((size_t)o->F * nbk, 0.0);
     for (int f = 0; f < o->F; ++f) {
@@ -874,15 +901,21 @@ void sweep_small_block(psg_optimizer* o, int block, std::vector<double>& Hout, s
 }
 
 // distance: leaves the stencil blocks in o->vecs; the scalars (energy before the update) are fetched with the PCG result
-void sweep_dist(psg_optimizer* o, int flags) {
-    SweepArgs A = base_args(o);
+void launch_dist_sweep(psg_optimizer* o, int flags, int slot) {
+    SweepArgs A = base_args(o, slot);
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
     if (o->world > 1) PSG_CUDA(cudaMemsetAsync(o->vecs.p, 0, (size_t)14 * o->S * sizeof(float), o->stream));   // rows of other ranks
     launch_sweep<M_DIST>(o, A, 0, 0);
     if (o->world > 1) comm_allreduce_floats(o, o->vecs.p, (size_t)14 * o->S);   // own rows + zeros: exact
-    fetch_red(o, 0);
+    reduce_over_ranks(o, 0, slot);
+}
+
+void launch_energy(psg_optimizer* o, int slot) {
+    SweepArgs A = base_args(o, slot);
+    launch_sweep<M_ENERGY>(o, A, 0, 0);
+    reduce_over_ranks(o, 0, slot);
 }
 
 // ---- regulariser energies (Optimizer.cpp:86-136) -------------------------------------------------------------
@@ -930,14 +963,19 @@ __global__ void __launch_bounds__(kBlock) k_reg_energy(VolView vol, SurfView sur
     }
 }
 
-void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
-    SweepArgs A = base_args(o);
-    PSG_CUDA(cudaMemsetAsync(A.red, 0, 8 * sizeof(double), o->stream));
+void launch_reg_energies(psg_optimizer* o, int slot) {
+    SweepArgs A = base_args(o, slot);   // every rank evaluates all rows: nothing to combine
+    PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
     if (o->S > 0) {
-        { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.red); }
+        { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.scal); }
         PSG_LAUNCH_CHECK();
     }
-    const double* r = fetch_red(o, 8, /*reduce_over_ranks=*/false);   // every rank evaluates all rows
+}
+
+void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
+    launch_reg_energies(o, kSlotReg);
+    fetch_mail(o, 0);
+    const double* r = mail_slot(o, kSlotReg);
     *En = r[0]; *El = r[1]; *Er = r[2];
 }
 
