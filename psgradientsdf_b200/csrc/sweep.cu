@@ -433,19 +433,23 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
 #pragma unroll
                 for (int i = 0; i < VLIGHT; ++i) vals[i] = 0.f;
                 if (ok) {
+                    // sum_c w_c (rho_c SH_i)(rho_c SH_k) = (sum_c w_c rho_c^2) SH_i SH_k, sum_c w_c (-rho_c SH_i) r_c likewise:
+                    // the channel sums are two scalars per pair.  Contracted arithmetic: these sums are accumulated in fp64
+                    // and compared with the reference's float-serial sums to 2e-5, not bit for bit.
+                    float s2 = 0.f, sr = 0.f;
 #pragma unroll
                     for (int c = 0; c < 3; ++c) {
-                        float J[NB];
+                        const float wr = w[c] * rho[c];
+                        s2 = __fmaf_rn(wr, rho[c], s2);
+                        sr = __fmaf_rn(-wr, r[c], sr);
+                    }
+                    int t = 0;
 #pragma unroll
-                        for (int i = 0; i < NB; ++i) J[i] = (-rho[c]) * sh_g[i];
-                        int t = 0;
+                    for (int i = 0; i < NB; ++i) {
+                        const float si = s2 * sh_g[i];
 #pragma unroll
-                        for (int i = 0; i < NB; ++i) {
-                            const float jw = J[i] * w[c];
-#pragma unroll
-                            for (int k = 0; k <= i; ++k) { vals[t] += jw * J[k]; ++t; }
-                            vals[NT + i] += jw * r[c];
-                        }
+                        for (int k = 0; k <= i; ++k) { vals[t] = si * sh_g[k]; ++t; }
+                        vals[NT + i] = sr * sh_g[i];
                     }
                 }
                 double* dst = A.red + (long long)f * VRED;
@@ -474,10 +478,14 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                     const float z_inv = (float)(1.0 / (double)pt[2]);
                     const float z_inv_sq = z_inv * z_inv;
                     const float pi[6] = { fx * z_inv, 0.f, -fx * pt[0] * z_inv_sq, 0.f, fy * z_inv, -fy * pt[1] * z_inv_sq };
+                    // G = grad I (3x2) * d pi (2x3); pi[1] = pi[3] = 0.  From here on the Jacobian algebra is contracted (FMA):
+                    // it feeds normal equations that are accumulated in fp64 / compared to 2e-5, not the bit-exact residual path.
 #pragma unroll
-                    for (int c = 0; c < 3; ++c)
-#pragma unroll
-                        for (int j = 0; j < 3; ++j) Aim[3 * c + j] = g0[c] * pi[j] + g1[c] * pi[3 + j];
+                    for (int c = 0; c < 3; ++c) {
+                        Aim[3 * c] = g0[c] * pi[0];
+                        Aim[3 * c + 1] = g1[c] * pi[4];
+                        Aim[3 * c + 2] = __fmaf_rn(g0[c], pi[2], g1[c] * pi[5]);
+                    }
                 }
             }
             if constexpr (MODE == M_POSE) {
@@ -488,12 +496,16 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                     const float Sk[9] = { 0.f, -pt[2], pt[1], pt[2], 0.f, -pt[0], -pt[1], pt[0], 0.f };
                     float J[3][6];
 #pragma unroll
-                    for (int c = 0; c < 3; ++c)
+                    for (int c = 0; c < 3; ++c) {
+                        const float a0 = Aim[3 * c], a1 = Aim[3 * c + 1], a2 = Aim[3 * c + 2];
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) {
-                            J[c][j] = sum3((-Aim[3 * c]) * P.R[3 * j], (-Aim[3 * c + 1]) * P.R[3 * j + 1], (-Aim[3 * c + 2]) * P.R[3 * j + 2]);
-                            J[c][3 + j] = sum3(Aim[3 * c] * Sk[j], Aim[3 * c + 1] * Sk[3 + j], Aim[3 * c + 2] * Sk[6 + j]);
-                        }
+                        for (int j = 0; j < 3; ++j)   // -G R^T
+                            J[c][j] = -__fmaf_rn(a0, P.R[3 * j], __fmaf_rn(a1, P.R[3 * j + 1], a2 * P.R[3 * j + 2]));
+                        // G [p]x
+                        J[c][3] = __fmaf_rn(a1, pt[2], -(a2 * pt[1]));
+                        J[c][4] = __fmaf_rn(a2, pt[0], -(a0 * pt[2]));
+                        J[c][5] = __fmaf_rn(a0, pt[1], -(a1 * pt[0]));
+                    }
                     if constexpr (LED) {   // LedOptimizerJa.cpp:63-78
                         const float l3 = (float)cube_d(norm3(pt));
                         const float l5 = (float)pow5_d(norm3(pt));
@@ -518,8 +530,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                         for (int i = 0; i < 6; ++i) {
                             const float jw = J[c][i] * w[c];
 #pragma unroll
-                            for (int k = 0; k <= i; ++k) { vals[t] += jw * J[c][k]; ++t; }
-                            vals[21 + i] += jw * r[c];
+                            for (int k = 0; k <= i; ++k) { vals[t] = __fmaf_rn(jw, J[c][k], vals[t]); ++t; }
+                            vals[21 + i] = __fmaf_rn(jw, r[c], vals[21 + i]);
                         }
                     }
                 }
@@ -531,10 +543,13 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                 for (int c = 0; c < 3; ++c)
 #pragma unroll
                     for (int j = 0; j < 3; ++j)
-                        Mx[3 * c + j] = sum3(Aim[3 * c] * P.R[3 * j], Aim[3 * c + 1] * P.R[3 * j + 1], Aim[3 * c + 2] * P.R[3 * j + 2]);
+                        Mx[3 * c + j] = __fmaf_rn(Aim[3 * c], P.R[3 * j], __fmaf_rn(Aim[3 * c + 1], P.R[3 * j + 1], Aim[3 * c + 2] * P.R[3 * j + 2]));
                 float Jd[4][3];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) mat_vec(Mx, dx[k], Jd[k]);   // dI_k for now
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)   // dI_k for now
+                        Jd[k][c] = __fmaf_rn(Mx[3 * c], dx[k][0], __fmaf_rn(Mx[3 * c + 1], dx[k][1], Mx[3 * c + 2] * dx[k][2]));
                 if constexpr (LED) {   // LedOptimizerJa.cpp:178-207
                     float gR[3], pRt[3];
 #pragma unroll
@@ -557,32 +572,29 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                     }
                 } else if constexpr (NB == 4) {   // PsOptimizerJa.cpp:225-240
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
+                    for (int k = 0; k < 4; ++k) {
+                        const float ld = __fmaf_rn(P.light[1], dn[k][0], __fmaf_rn(P.light[2], dn[k][1], P.light[3] * dn[k][2]));
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            const float d0 = rho[c] * P.light[1], d1 = rho[c] * P.light[2], d2 = rho[c] * P.light[3];
-                            Jd[k][c] = Jd[k][c] - sum3(d0 * dn[k][0], d1 * dn[k][1], d2 * dn[k][2]);
-                        }
+                        for (int c = 0; c < 3; ++c) Jd[k][c] = __fmaf_rn(-rho[c], ld, Jd[k][c]);
+                    }
                 } else {                // PsOptimizerJa.cpp:242-278
                     const float D[27] = { 0, 1, 0, 0, nfd[1], nfd[2], 0, 2 * nfd[0], 2 * nfd[0],
                                           0, 0, 1, 0, nfd[0], 0, nfd[2], -2 * nfd[1], 0,
                                           0, 0, 0, 1, 0, nfd[0], nfd[1], 0, -2 * nfd[2] };
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        float dsh[9];
+                        float ld = 0.f;   // l^T (dSH/dn)^T dn_k, common to the three channels
 #pragma unroll
-                        for (int i = 0; i < 9; ++i) dsh[i] = sum3(D[i] * dn[k][0], D[9 + i] * dn[k][1], D[18 + i] * dn[k][2]);
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            float a[9];
-#pragma unroll
-                            for (int i = 0; i < 9; ++i) a[i] = (rho[c] * P.light[i]) * dsh[i];
-                            const float sdot = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + (a[7] + a[8])));
-                            Jd[k][c] = Jd[k][c] - sdot;
+                        for (int i = 1; i < 9; ++i) {   // column 0 of D is zero
+                            const float dsh = __fmaf_rn(D[i], dn[k][0], __fmaf_rn(D[9 + i], dn[k][1], D[18 + i] * dn[k][2]));
+                            ld = __fmaf_rn(P.light[i], dsh, ld);
                         }
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) Jd[k][c] = __fmaf_rn(-rho[c], ld, Jd[k][c]);
                     }
                 }
                 // stencil normal equations, lower triangle in slot order: (0,0),(1,0),(1,1),(2,0)...(3,3), then b[4]
+                // (entries of neighbours that are not surface voxels are dropped when the block is written out)
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     int t = 0;
@@ -590,8 +602,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                     for (int i = 0; i < 4; ++i) {
                         const float jw = Jd[i][c] * w[c];
 #pragma unroll
-                        for (int k = 0; k <= i; ++k) { if (cols[i] >= 0 && cols[k] >= 0) vacc[t] += jw * Jd[k][c]; ++t; }
-                        if (cols[i] >= 0) vacc[10 + i] += jw * r[c];
+                        for (int k = 0; k <= i; ++k) { vacc[t] = __fmaf_rn(jw, Jd[k][c], vacc[t]); ++t; }
+                        vacc[10 + i] = __fmaf_rn(jw, r[c], vacc[10 + i]);
                     }
                 }
             }
@@ -644,6 +656,16 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
     }
     if constexpr (MODE == M_DIST) {
         if (warp == 0 && live) {
+            // columns of neighbours that are not surface voxels do not exist (PsOptimizerJa.cpp:536-552)
+            {
+                int t = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+#pragma unroll
+                    for (int k = 0; k <= i; ++k) { if (!(cols[i] >= 0 && cols[k] >= 0)) vacc[t] = 0.f; ++t; }
+                    if (cols[i] < 0) vacc[10 + i] = 0.f;
+                }
+            }
             // Eikonal rows (Optimizer.cpp:196-218, 477-537), scaled by reg_weight_n (PsOptimizer.cpp:136-142)
             if (A.flags & PSG_REG_NORMAL) {
                 float nd[3], Jr[4];
