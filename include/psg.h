@@ -217,17 +217,18 @@ int psg_opt_upsample(psg_optimizer* opt);
 
 /* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
  * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
- * every rank); the (surface voxel, keyframe) sweeps are split by contiguous ranges of the visibility-sorted work list.
+ * every rank); the (surface voxel, keyframe) sweeps are split by round-robin 32-slot blocks of the visibility-sorted work list.
  * After psg_opt_comm_init, psg_opt_init_albedo / psg_opt_energy / psg_opt_step / psg_opt_alternating_optimize are
  * collective: all ranks must call them in the same order with the same arguments, and all ranks end in the same state
- * (small light / pose normal equations and energies: NCCL all-reduce; updated albedo: all-gather; distance stencil blocks:
- * all-reduce, then every rank runs the same distance solve).  NCCL over NVLink / NVSwitch; the communicator runs on the
+ * (small light / pose normal equations and energies: NCCL all-reduce; updated albedo and distance stencil blocks:
+ * all-gather, then every rank runs the same distance solve).  NCCL over NVLink / NVSwitch; the communicator runs on the
  * optimizer's stream. */
 int psg_comm_unique_id(unsigned char id[128]);                                   /* rank 0; send the bytes to the other ranks */
 int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank, int world);
 int psg_opt_comm_destroy(psg_optimizer* opt);
-/* The range [begin, end) of work-list slots that `rank` of `world` sweeps for a surface of S voxels (multiples of 32). */
-int psg_shard_range(int S, int rank, int world, int* begin, int* end);
+/* Which 32-slot blocks of the work list `rank` of `world` sweeps for a surface of S voxels: blocks first, first + stride,
+ * ... (count of them); round-robin, so that every rank gets the same mix of the visibility-sorted list. */
+int psg_shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 /* Diagnostic: the partial energy sum and pair count over the slots of `rank` of `world`, computed locally without any
  * communication (the partials of all ranks add up to psg_opt_energy * S). */
 int psg_opt_energy_partial(psg_optimizer* opt, int rank, int world, double* loss_sum, long long* n_active);

@@ -117,7 +117,7 @@ def lib():
         L.psg_comm_unique_id.argtypes = [C.c_char_p]
         L.psg_opt_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
         L.psg_opt_comm_destroy.argtypes = [vp]
-        L.psg_shard_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psg_shard_blocks.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psg_opt_energy_partial.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_profile_enable.argtypes = [C.c_int]
         L.psg_profile_name.restype = C.c_char_p
@@ -143,10 +143,11 @@ def comm_unique_id() -> bytes:
     return buf.raw
 
 
-def shard_range(S: int, rank: int, world: int):
-    b, e = C.c_int(), C.c_int()
-    _check(lib().psg_shard_range(int(S), int(rank), int(world), C.byref(b), C.byref(e)))
-    return b.value, e.value
+def shard_blocks(S: int, rank: int, world: int):
+    """(first, stride, count): the 32-slot blocks of the work list that `rank` of `world` sweeps."""
+    f, st, c = C.c_int(), C.c_int(), C.c_int()
+    _check(lib().psg_shard_blocks(int(S), int(rank), int(world), C.byref(f), C.byref(st), C.byref(c)))
+    return f.value, st.value, c.value
 
 
 def profile_enable(on: bool = True) -> None:

@@ -62,14 +62,19 @@ static bool nccl_load() {
         }                                                                                                \
     } while (0)
 
-void shard_range(int S, int rank, int world, int* begin, int* end) {
-    const long long nblocks = ((long long)S + 31) / 32;
-    const long long per = (nblocks + world - 1) / world;
-    long long b = (long long)rank * per * 32;
-    if (b > S) b = S;
-    long long e = b + per * 32;
-    if (e > S) e = S;
-    *begin = (int)b; *end = (int)e;
+// The work list is cut into blocks of 32 slots; rank r sweeps blocks r, r + world, r + 2 world, ...  The list is sorted by
+// visibility (most keyframes first), so contiguous ranges would give the first ranks the expensive end; round-robin blocks
+// give every rank the same mix.
+void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count) {
+    const int nblocks = (S + 31) / 32;
+    *first = rank; *stride = world;
+    *count = rank < nblocks ? (nblocks - rank + world - 1) / world : 0;
+}
+
+// slots per rank in the packed all-gather layout (the same for every rank: padded to the largest share)
+static size_t chunk_slots(const psg_optimizer* o) {
+    const int nblocks = (o->S + 31) / 32;
+    return (size_t)((nblocks + o->world - 1) / o->world) * 32;
 }
 
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb) {
@@ -80,31 +85,68 @@ void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, s
     PSG_NCCL(g_nccl.GroupEnd());
 }
 
-void comm_allreduce_floats(psg_optimizer* o, float* a, size_t n) {
-    if (!n) return;
-    PSG_NCCL(g_nccl.AllReduce(a, a, n, ncclFloat, ncclSum, static_cast<ncclComm_t>(o->comm), o->stream));
-}
+// packed index (rank r, local j) -> work-list slot
+__device__ __forceinline__ int packed_slot(int r, int j, int world) { return ((j >> 5) * world + r) * 32 + (j & 31); }
 
-// rho of slots swept by other ranks -> dense volume planes (own slots were written by the sweep itself)
-__global__ void __launch_bounds__(256) k_scatter_rho(VolView vol, SurfView surf, int own_begin, int own_end) {
+// albedo of every slot -> rec1 + dense volume planes (own slots were written by the sweep itself)
+__global__ void __launch_bounds__(256) k_scatter_rho(VolView vol, SurfView surf, const float4* __restrict__ buf, int chunk, int world, int own) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= surf.S || (t >= own_begin && t < own_end)) return;
-    const float4 r1 = surf.rec1[t];
-    const int lin = __float_as_int(surf.rec3[t].w);
+    if (t >= chunk * world) return;
+    const int r = t / chunk, j = t - r * chunk;
+    if (r == own) return;
+    const int slot = packed_slot(r, j, world);
+    if (slot >= surf.S) return;
+    const float4 r1 = buf[t];
+    surf.rec1[slot] = r1;
+    const int lin = __float_as_int(surf.rec3[slot].w);
     vol.r[lin] = r1.x; vol.g[lin] = r1.y; vol.b[lin] = r1.z;
 }
 
-void comm_allgather_rec1(psg_optimizer* o) {
+// distance stencil blocks of every slot -> 14 planes indexed by surface row
+__global__ void __launch_bounds__(256) k_scatter_stencil(SurfView surf, const float* __restrict__ buf, float* __restrict__ blocks, int chunk, int world) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= chunk * world) return;
+    const int r = t / chunk, j = t - r * chunk;
+    const int slot = packed_slot(r, j, world);
+    if (slot >= surf.S) return;
+    const int s = __float_as_int(surf.rec2[slot].w);
+    const float* src = buf + (size_t)r * 14 * chunk + j;
+#pragma unroll
+    for (int i = 0; i < 14; ++i) blocks[(size_t)i * surf.S + s] = src[(size_t)i * chunk];
+}
+
+float4* comm_pack_rho(psg_optimizer* o) {
+    const size_t chunk = chunk_slots(o);
+    o->comm_buf.alloc(chunk * o->world * 14);   // sized for the larger user (stencil); 16-byte aligned by cudaMalloc
+    return reinterpret_cast<float4*>(o->comm_buf.p) + (size_t)o->rank * chunk;
+}
+
+void comm_allgather_rho(psg_optimizer* o) {
     if (o->S == 0) return;
-    int b0, e0, b, e;
-    shard_range(o->S, 0, o->world, &b0, &e0);
-    shard_range(o->S, o->rank, o->world, &b, &e);
-    const long long nblocks = ((long long)o->S + 31) / 32;
-    const size_t chunk = (size_t)((nblocks + o->world - 1) / o->world) * 32;   // slots per rank (the last ranks' tails are padding)
-    float4* base = o->rec1.p;
+    const size_t chunk = chunk_slots(o);
+    float4* base = reinterpret_cast<float4*>(o->comm_buf.p);
     PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * chunk, base, chunk * 4, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
     const SurfView sv = surf_view(o);
-    { Prof pf(o->stream, KID_AOS); k_scatter_rho<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, b, e); }
+    const int n = (int)(chunk * o->world);
+    { Prof pf(o->stream, KID_AOS); k_scatter_rho<<<(n + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, base, (int)chunk, o->world, o->rank); }
+    PSG_LAUNCH_CHECK();
+}
+
+float* comm_pack_stencil(psg_optimizer* o, int* stride) {
+    const size_t chunk = chunk_slots(o);
+    o->comm_buf.alloc(chunk * o->world * 14);
+    *stride = (int)chunk;
+    return o->comm_buf.p + (size_t)o->rank * 14 * chunk;
+}
+
+void comm_allgather_stencil(psg_optimizer* o, float* blocks) {
+    if (o->S == 0) return;
+    const size_t chunk = chunk_slots(o);
+    float* base = o->comm_buf.p;
+    PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * 14 * chunk, base, 14 * chunk, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
+    const SurfView sv = surf_view(o);
+    const int n = (int)(chunk * o->world);
+    { Prof pf(o->stream, KID_AOS); k_scatter_stencil<<<(n + 255) / 256, 256, 0, o->stream>>>(sv, base, blocks, (int)chunk, o->world); }
     PSG_LAUNCH_CHECK();
 }
 
@@ -153,9 +195,9 @@ int psg_opt_comm_destroy(psg_optimizer* o) {
     return PSG_OK;
 }
 
-int psg_shard_range(int S, int rank, int world, int* begin, int* end) {
-    if (S < 0 || world < 1 || rank < 0 || rank >= world || !begin || !end) { set_error("psg_shard_range: bad argument"); return PSG_ERR_INVALID; }
-    shard_range(S, rank, world, begin, end);
+int psg_shard_blocks(int S, int rank, int world, int* first, int* stride, int* count) {
+    if (S < 0 || world < 1 || rank < 0 || rank >= world || !first || !stride || !count) { set_error("psg_shard_blocks: bad argument"); return PSG_ERR_INVALID; }
+    shard_blocks(S, rank, world, first, stride, count);
     return PSG_OK;
 }
 

@@ -105,6 +105,7 @@ struct psg_optimizer {
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
     psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
     void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
+    psg::DevBuf<float> comm_buf;             // all-gather staging: world chunks of packed per-slot results
     int rank = 0, world = 1;
     int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
@@ -152,10 +153,12 @@ struct SweepOut {
     long long n_active = 0;
 };
 void upload_frames(psg_optimizer* o);
-void shard_range(int S, int rank, int world, int* begin, int* end);
+void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
-void comm_allreduce_floats(psg_optimizer* o, float* a, size_t n);
-void comm_allgather_rec1(psg_optimizer* o);
+float4* comm_pack_rho(psg_optimizer* o);                         // this rank's send chunk (written by the sweep)
+void comm_allgather_rho(psg_optimizer* o);                       // all-gather + scatter into rec1 / volume planes
+float* comm_pack_stencil(psg_optimizer* o, int* stride);         // this rank's send chunk: 14 planes of `stride` floats
+void comm_allgather_stencil(psg_optimizer* o, float* blocks);    // all-gather + scatter into 14 planes of S rows
 void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active);
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
 void sweep_init_albedo(psg_optimizer* o);

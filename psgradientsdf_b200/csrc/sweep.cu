@@ -34,7 +34,9 @@ struct SweepArgs {
     const FrameParams* frames;
     const float4* images;
     int F;
-    int slot_begin, slot_end;   // this rank's range of the work list
+    // multi-GPU: updated albedo records / distance stencil blocks of this rank's slots, packed by local slot for the all-gather
+    float4* pack_rho; float* pack_out; int pack_stride;
+    int blk_first, blk_stride, blk_count;   // this rank's 32-slot blocks of the work list: blk_first + i * blk_stride, i < blk_count
     float vs_inv;
     float led[3];
     float damping, reg_n, reg_l;
@@ -228,20 +230,22 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int S = A.surf.S;
-    const int slot = A.slot_begin + blockIdx.x * 32 + lane;   // position in the visibility-sorted work list
-    const bool live = slot < A.slot_end;
+    const int slot = (A.blk_first + (int)blockIdx.x * A.blk_stride) * 32 + lane;   // position in the visibility-sorted work list
+    const bool live = slot < S;
 
     // ---- voxel record (five coalesced 128-bit loads; everything per-voxel is precomputed by k_gather_records)
     int lin = 0, s = 0;
     unsigned long long vis = 0ull;
     float dist = 0.f, gh[3] = {0, 0, 0}, rho[3] = {0, 0, 0}, q0[3] = {0, 0, 0};
     float fd[3] = {0, 0, 0}, posf[3] = {1, 1, 1}, nfd[3] = {0, 0, 0};
+    float rec1w = 0.f;
+    const int local = (int)blockIdx.x * 32 + lane;   // index among this rank's slots
     if (live) {
         vis = A.surf.pvis[slot];
         const float4 r0 = A.surf.rec0[slot], r1 = A.surf.rec1[slot], r2 = A.surf.rec2[slot], r3 = A.surf.rec3[slot],
                      r4 = A.surf.rec4[slot];
         dist = r0.x; gh[0] = r0.y; gh[1] = r0.z; gh[2] = r0.w;
-        rho[0] = r1.x; rho[1] = r1.y; rho[2] = r1.z;
+        rho[0] = r1.x; rho[1] = r1.y; rho[2] = r1.z; rec1w = r1.w;
         fd[0] = r2.x; fd[1] = r2.y; fd[2] = r2.z; s = __float_as_int(r2.w);
         lin = __float_as_int(r3.w);
         nfd[0] = r4.x; nfd[1] = r4.y; nfd[2] = r4.z;
@@ -633,8 +637,10 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
         if (warp == 0 && live && icount) {
             const float nr = vacc[0] / (float)icount, ng = vacc[1] / (float)icount, nbl = vacc[2] / (float)icount;
             A.vol.r[lin] = nr; A.vol.g[lin] = ng; A.vol.b[lin] = nbl;
-            A.surf.rec1[slot] = make_float4(nr, ng, nbl, A.surf.rec1[slot].w);
+            A.surf.rec1[slot] = make_float4(nr, ng, nbl, rec1w);
+            rho[0] = nr; rho[1] = ng; rho[2] = nbl;
         }
+        if (A.pack_rho && warp == 0 && live) A.pack_rho[local] = make_float4(rho[0], rho[1], rho[2], rec1w);
     }
     if constexpr (MODE == M_ALBEDO) {
         // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
@@ -651,7 +657,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                 if ((double)nv > 0.0 && (double)nv < 1.0) { chan[c][lin] = nv; rho[c] = nv; ++accepted; }
                 if (A.out0) { A.out0[3 * (long long)s + c] = vacc[3 + c]; A.out1[3 * (long long)s + c] = delta; }
             }
-            if (accepted) A.surf.rec1[slot] = make_float4(rho[0], rho[1], rho[2], A.surf.rec1[slot].w);
+            if (accepted) A.surf.rec1[slot] = make_float4(rho[0], rho[1], rho[2], rec1w);
+            if (A.pack_rho) A.pack_rho[local] = make_float4(rho[0], rho[1], rho[2], rec1w);
         }
     }
     if constexpr (MODE == M_DIST) {
@@ -704,8 +711,13 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
                 vacc[0] += A.reg_l * (jd * jd);
                 vacc[10] += A.reg_l * (jd * lap);
             }
+            if (A.pack_out) {
 #pragma unroll
-            for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
+                for (int i = 0; i < 14; ++i) A.pack_out[(long long)i * A.pack_stride + local] = vacc[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
+            }
         }
     }
     // (b) scalar sums: warp -> block (warp order) -> grid (fixed order, last block): [0..5] mode specific, [6] loss, [7] pairs
@@ -736,7 +748,7 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
     A.frames = o->frames.p; A.images = o->images.p; A.F = o->F;
-    shard_range(o->S, o->rank, o->world, &A.slot_begin, &A.slot_end);
+    shard_blocks(o->S, o->rank, o->world, &A.blk_first, &A.blk_stride, &A.blk_count);
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
@@ -773,10 +785,10 @@ void upload_frames(psg_optimizer* o) {
 template <int MODE>
 static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
     if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
-    if (o->world > 1 || A.slot_end <= A.slot_begin)   // ranks with an empty range still take part in the all-reduce
+    if (o->world > 1 || A.blk_count <= 0)   // ranks without work still take part in the all-reduce
         PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
-    if (o->S == 0 || A.slot_end <= A.slot_begin) return;
-    const int grid = (A.slot_end - A.slot_begin + 31) / 32;
+    if (o->S == 0 || A.blk_count <= 0) return;
+    const int grid = A.blk_count;
     // keyframe split: double W while the launch stays within ~32 warps per SM (beyond that the replicated prologue costs more than it hides)
     int W = 1;
     while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
@@ -840,7 +852,7 @@ void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
 
 void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active) {
     SweepArgs A = base_args(o);
-    shard_range(o->S, rank, world, &A.slot_begin, &A.slot_end);
+    shard_blocks(o->S, rank, world, &A.blk_first, &A.blk_stride, &A.blk_count);
     PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));   // an empty range launches nothing
     launch_sweep<M_ENERGY>(o, A, 0, 0);
     fetch_red(o, 0, /*reduce_over_ranks=*/false);
@@ -850,8 +862,9 @@ void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, lo
 
 void sweep_init_albedo(psg_optimizer* o) {
     SweepArgs A = base_args(o);
+    if (o->world > 1) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_INIT_ALBEDO>(o, A, 0, 0);
-    if (o->world > 1) comm_allgather_rec1(o);
+    if (o->world > 1) comm_allgather_rho(o);
 }
 
 void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
@@ -864,15 +877,16 @@ void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
     SweepArgs A = base_args(o);
     A.pm = m; A.pn = n; A.pok = ok; A.pI = I3; A.prend = rend3; A.pr = r3; A.pw = w3;
-    A.slot_begin = 0; A.slot_end = o->S;   // diagnostic: every rank probes all pairs
+    shard_blocks(o->S, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // diagnostic: every rank probes all pairs
     launch_sweep<M_PROBE>(o, A, 0, 0);
 }
 
 void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot) {
     SweepArgs A = base_args(o, slot);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
+    if (o->world > 1) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
-    if (o->world > 1) comm_allgather_rec1(o);
+    if (o->world > 1) comm_allgather_rho(o);
     reduce_over_ranks(o, 0, slot);
 }
 
@@ -928,9 +942,9 @@ void launch_dist_sweep(psg_optimizer* o, int flags, int slot) {
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
-    if (o->world > 1) PSG_CUDA(cudaMemsetAsync(o->vecs.p, 0, (size_t)14 * o->S * sizeof(float), o->stream));   // rows of other ranks
+    if (o->world > 1) A.pack_out = comm_pack_stencil(o, &A.pack_stride);
     launch_sweep<M_DIST>(o, A, 0, 0);
-    if (o->world > 1) comm_allreduce_floats(o, o->vecs.p, (size_t)14 * o->S);   // own rows + zeros: exact
+    if (o->world > 1) comm_allgather_stencil(o, o->vecs.p);   // every rank ends with all rows
     reduce_over_ranks(o, 0, slot);
 }
 
@@ -1069,7 +1083,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
         A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
         A.frames = sc->frames; A.images = o->images.p; A.F = o->F;
-        A.slot_begin = 0; A.slot_end = o->S;   // always the whole work list (no communication on this path)
+        shard_blocks(o->S, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // always the whole work list (no communication on this path)
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;

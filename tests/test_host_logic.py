@@ -44,19 +44,20 @@ def test_sweep_byte_model():
     assert "128^3" in bench.METRIC
 
 
-def test_shard_ranges_tile_the_work_list():
+def test_shard_blocks_tile_the_work_list():
     import psgradientsdf_b200 as psg
     for S in (0, 1, 31, 32, 33, 1000, 28384, 458398, 2 ** 21 + 5):
+        nblocks = (S + 31) // 32
         for world in (1, 2, 3, 4, 8):
-            pos = 0
+            seen = []
+            counts = []
             for rank in range(world):
-                b, e = psg.shard_range(S, rank, world)
-                assert b == pos and b <= e <= S and (b % 32 == 0 or b == S), (S, world, rank, b, e)
-                pos = e
-            assert pos == S
-            sizes = [psg.shard_range(S, r, world)[1] - psg.shard_range(S, r, world)[0] for r in range(world)]
-            assert max(sizes) - min(s for s in sizes if s > 0 or True) <= max(sizes)      # ranges may be empty at the tail
-            assert max(sizes) <= ((S + 31) // 32 + world - 1) // world * 32
+                first, stride, count = psg.shard_blocks(S, rank, world)
+                assert stride == world and first == rank and count >= 0
+                seen += [first + i * stride for i in range(count)]
+                counts.append(count)
+            assert sorted(seen) == list(range(nblocks)), (S, world)
+            assert max(counts) - min(counts) <= 1
 
 
 _WORKER = r'''
@@ -68,18 +69,15 @@ dist.all_reduce(t, op=dist.ReduceOp.MAX)          # bench.py: max-over-ranks tim
 u = torch.tensor([float(rank + 1)], dtype=torch.float64)
 dist.all_reduce(u, op=dist.ReduceOp.SUM)          # small normal-equation blocks are summed over ranks
 assert t.item() == world and u.item() == world * (world + 1) / 2
-# the slot ranges each rank would sweep tile the work list (library function, no GPU needed)
+# the blocks each rank would sweep tile the work list (library function, no GPU needed)
 sys.path.insert(0, os.environ["PSG_ROOT"])
 import psgradientsdf_b200 as psg
 S = 28384
-b, e = psg.shard_range(S, rank, world)
-rng = torch.tensor([b, e], dtype=torch.int64)
-allr = [torch.zeros(2, dtype=torch.int64) for _ in range(world)]
-dist.all_gather(allr, rng)
-pos = 0
-for r in allr:
-    assert int(r[0]) == pos; pos = int(r[1])
-assert pos == S
+first, stride, count = psg.shard_blocks(S, rank, world)
+mine = torch.zeros((S + 31) // 32, dtype=torch.int64)
+mine[first::stride][:count] += 1
+dist.all_reduce(mine, op=dist.ReduceOp.SUM)       # every block is swept by exactly one rank
+assert bool((mine == 1).all())
 dist.barrier(); dist.destroy_process_group()
 print("rank", rank, "ok")
 '''

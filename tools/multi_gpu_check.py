@@ -47,6 +47,8 @@ for it in range(2):
         info = opt.step(blk, damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
         log.append((info["energy_before"], info["n_active_before"], info["iters"]))
 log.append(opt.energy())
+it_info = opt.iteration(damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))   # the three-wait pass, sharded
+log.append((it_info["energy_end"], it_info["n_active_end"]))
 state = vol.download()
 # all ranks must hold the same state
 h = torch.tensor(np.frombuffer(state.tobytes(), dtype=np.uint8).astype(np.int64).sum(), device=f"cuda:{local}")
@@ -62,6 +64,8 @@ if rank == 0:
             info = opt1.step(blk, damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
             log1.append((info["energy_before"], info["n_active_before"], info["iters"]))
     log1.append(opt1.energy())
+    it1 = opt1.iteration(damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
+    log1.append((it1["energy_end"], it1["n_active_end"]))
     worst = 0.0
     for a, b in zip(log, log1):
         assert a[1] == b[1], (a, b)
