@@ -215,6 +215,31 @@ int psg_opt_last_vectors(psg_optimizer* opt, float* b, float* delta);
  * updated in place (dims x2, voxel size /2, origin shifted, VoxelGrid.h:143-149) and the surface is re-extracted. */
 int psg_opt_upsample(psg_optimizer* opt);
 
+/* ------------------------------------------------------------------ frame front end on the device
+ * cv::NormalEstimator<float> (cpp/include/normals/NormalEstimator.h:125-176; main_ps.cpp:115 builds it with an 11 x 11
+ * window) and the loader's pixel conversions (img_loader/ImageLoader.h:130-146 depth, :166-188 colour), so that
+ * VolumetricGradSdf::update (VolumetricGradSdf.cpp:51-138) can be fed the 16-bit depth and 8-bit colour the loader read
+ * from disk.  Results are OpenCV's bit for bit (tests/golden/normals.npz, OpenCV 4.13). */
+typedef struct psg_normals psg_normals;
+/* NormalEstimator(width, height, K, Size(window, window)): builds the per-pixel tables of cache() (:52-123). */
+int psg_normals_create(psg_normals** out, int width, int height, const float K[9], int window, int device);
+int psg_normals_destroy(psg_normals* ne);
+/* The cached tables, 9 planes of height*width floats: x0_n_sq_inv, y0_n_sq_inv, n_sq_inv, Q11, Q12, Q13, Q22, Q23, Q33
+ * (plane 2 is what update() receives through NEst->n_sq_inv_ptr(), VolumetricGradSdf.cpp:66). */
+int psg_normals_tables(psg_normals* ne, float* planes9);
+/* NormalEstimator::compute(depth, nx, ny, nz) (:148-176): host depth in metres (0 = no measurement) -> host unit normals;
+ * NaN where the whole window is empty, as OpenCV >= 4 produces. */
+int psg_normals_compute(psg_normals* ne, const float* depth, float* nx, float* ny, float* nz);
+/* load_depth + load_color + NEst->compute + update() for one frame in the loader's raw format: depth_u16 (height*width,
+ * metres = value * depth_unit), color_bgr_u8 (height*width*3).  Same result as converting and estimating on the host and
+ * calling psg_volume_integrate; 5 bytes per pixel cross PCIe instead of 32. */
+int psg_volume_integrate_raw(psg_volume* vol, psg_normals* ne, const unsigned char* color_bgr_u8, const unsigned short* depth_u16,
+                             float depth_unit, const float K[9], const float R[9], const float t[3], int increase_counter);
+/* psg_opt_set_keyframes with the keyframe images as the loader read them (8-bit BGR, F*H*W*3 bytes): converted on the
+ * device with load_color's float(src) * (1.0f / 255.0f), so the texels equal those of the float entry point. */
+int psg_opt_set_keyframes_u8(psg_optimizer* opt, int F, const int* frame_idx, const float* poses4x4, const unsigned char* images_bgr_u8,
+                             int H, int W);
+
 /* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
  * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
  * every rank); the (surface voxel, keyframe) sweeps are split by round-robin 32-slot blocks of the visibility-sorted work list.

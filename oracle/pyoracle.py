@@ -24,8 +24,8 @@ BLOCK = {"albedo": 0, "light": 1, "dist": 2, "pose": 3}
 
 
 def build(force: bool = False) -> None:
-    src = os.path.join(_HERE, "psg_oracle.c")
-    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, "psg_oracle.c"), os.path.join(_HERE, "psg_oracle_normals.c")]
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(x) for x in srcs):
         subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
 
 
@@ -78,6 +78,10 @@ def lib():
         L.or_opt_block_H.restype = C.c_longlong
         L.or_opt_block_H.argtypes = [vp, vp, vp, vp]
         L.or_opt_subsampling.argtypes = [vp]
+        L.or_normals_cache.argtypes = [C.c_int, C.c_int, f32p, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p]
+        L.or_normals_compute.argtypes = [C.c_int, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p]
+        L.or_convert_depth_u16.argtypes = [vp, C.c_size_t, C.c_float, f32p]
+        L.or_convert_color_u8.argtypes = [vp, C.c_size_t, f32p]
         _lib = L
     return _lib
 
@@ -258,3 +262,35 @@ class OrOptimizer:
 
     def subsampling(self):
         lib().or_opt_subsampling(self.h)
+
+
+class OrNormalEstimator:
+    """cv::NormalEstimator<float> (NormalEstimator.h:125-176) restated in oracle/psg_oracle_normals.c."""
+
+    def __init__(self, width, height, K, window=11):
+        self.W, self.H, self.window = int(width), int(height), int(window)
+        shp = (self.H, self.W)
+        self.x0, self.y0, self.x0_n, self.y0_n, self.n_sq_inv = (np.zeros(shp, np.float32) for _ in range(5))
+        self.Q = np.zeros((6,) + shp, np.float32)
+        lib().or_normals_cache(self.W, self.H, np.ascontiguousarray(K, np.float32).reshape(-1), self.window, self.x0, self.y0,
+                               self.x0_n, self.y0_n, self.n_sq_inv, self.Q)
+
+    def compute(self, depth):
+        depth = np.ascontiguousarray(depth, np.float32)
+        nx, ny, nz = (np.zeros((self.H, self.W), np.float32) for _ in range(3))
+        lib().or_normals_compute(self.W, self.H, self.window, depth, self.x0_n, self.y0_n, self.n_sq_inv, self.Q, nx, ny, nz)
+        return nx, ny, nz
+
+
+def convert_depth_u16(d16, unit):
+    d16 = np.ascontiguousarray(d16, np.uint16)
+    out = np.zeros(d16.shape, np.float32)
+    lib().or_convert_depth_u16(d16.ctypes.data, d16.size, float(unit), out)
+    return out
+
+
+def convert_color_u8(c8):
+    c8 = np.ascontiguousarray(c8, np.uint8)
+    out = np.zeros(c8.shape, np.float32)
+    lib().or_convert_color_u8(c8.ctypes.data, c8.size, out)
+    return out

@@ -109,6 +109,12 @@ def lib():
         L.psg_opt_residual.argtypes = [vp, f32p, f32p]
         L.psg_opt_probe_pairs.argtypes = [vp, f32p, f32p, vp, f32p, f32p]
         L.psg_opt_step.argtypes = [vp, C.c_int, C.c_float, C.c_int, C.POINTER(StepInfo)]
+        L.psg_normals_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, f32p, C.c_int, C.c_int]
+        L.psg_normals_destroy.argtypes = [vp]
+        L.psg_normals_tables.argtypes = [vp, f32p]
+        L.psg_normals_compute.argtypes = [vp, f32p, f32p, f32p, f32p]
+        L.psg_volume_integrate_raw.argtypes = [vp, vp, vp, vp, C.c_float, f32p, f32p, f32p, C.c_int]
+        L.psg_opt_set_keyframes_u8.argtypes = [vp, C.c_int, i32p, f32p, vp, C.c_int, C.c_int]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -214,6 +220,18 @@ class VolumetricGradSdf:
                                           c(t).reshape(3), int(self._pending_counter)))
         self._pending_counter = False
 
+    def update_raw(self, color_u8, depth_u16, depth_unit, K, R, t, NEst: "NormalEstimator"):
+        """load_color + load_depth + NEst->compute + update() from the loader's raw pixels (psg_volume_integrate_raw)."""
+        self._ensure()
+        color_u8 = np.ascontiguousarray(color_u8, np.uint8)
+        depth_u16 = np.ascontiguousarray(depth_u16, np.uint16)
+        assert depth_u16.shape == (NEst.H, NEst.W) and color_u8.shape == (NEst.H, NEst.W, 3)
+        _check(lib().psg_volume_integrate_raw(self.h, NEst.h, color_u8.ctypes.data, depth_u16.ctypes.data, float(depth_unit),
+                                              np.ascontiguousarray(K, np.float32).reshape(-1),
+                                              np.ascontiguousarray(R, np.float32).reshape(-1),
+                                              np.ascontiguousarray(t, np.float32).reshape(-1), int(self._pending_counter)))
+        self._pending_counter = False
+
     @property
     def N(self):
         dims, _, _ = self.geometry()
@@ -250,6 +268,43 @@ class VolumetricGradSdf:
         _check(lib().psg_volume_upload_vis(self.h, np.ascontiguousarray(words, np.uint64), int(frame_counter)))
 
 
+class NormalEstimator:
+    """cv::NormalEstimator<float> (normals/NormalEstimator.h:125-176) on the device."""
+
+    def __init__(self, width, height, K, window=11, device=0):
+        self.W, self.H, self.window = int(width), int(height), int(window)
+        self.h = C.c_void_p()
+        _check(lib().psg_normals_create(C.byref(self.h), self.W, self.H, np.ascontiguousarray(K, np.float32).reshape(-1),
+                                        self.window, int(device)))
+
+    def close(self):
+        if self.h:
+            lib().psg_normals_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def tables(self):
+        """(9, H, W): x0_n_sq_inv, y0_n_sq_inv, n_sq_inv, Q11, Q12, Q13, Q22, Q23, Q33."""
+        t = np.zeros((9, self.H, self.W), np.float32)
+        _check(lib().psg_normals_tables(self.h, t))
+        return t
+
+    def n_sq_inv(self):
+        return self.tables()[2]
+
+    def compute(self, depth):
+        depth = np.ascontiguousarray(depth, np.float32)
+        assert depth.shape == (self.H, self.W)
+        nx, ny, nz = (np.zeros((self.H, self.W), np.float32) for _ in range(3))
+        _check(lib().psg_normals_compute(self.h, depth, nx, ny, nz))
+        return nx, ny, nz
+
+
 class Optimizer:
     """Look-alike of Optimizer / PsOptimizer / LedOptimizer (Optimizer.h:24-182) over psg_opt_*."""
 
@@ -276,6 +331,14 @@ class Optimizer:
         img = np.ascontiguousarray(images, np.float32)
         _check(lib().psg_opt_set_keyframes(self.h, F, np.ascontiguousarray(frame_idx, np.int32),
                                            np.ascontiguousarray(poses, np.float32).reshape(-1), _ptr(img), H, W))
+
+    def set_keyframes_u8(self, frame_idx, poses, images_u8):
+        """setImages with the 8-bit BGR pixels the loader read (psg_opt_set_keyframes_u8)."""
+        F, H, W, _ = images_u8.shape
+        self._F = F
+        img = np.ascontiguousarray(images_u8, np.uint8)
+        _check(lib().psg_opt_set_keyframes_u8(self.h, F, np.ascontiguousarray(frame_idx, np.int32),
+                                              np.ascontiguousarray(poses, np.float32).reshape(-1), img.ctypes.data, H, W))
 
     def init(self):
         _check(lib().psg_opt_init(self.h))

@@ -26,7 +26,7 @@ static const char* const kKernelNames[KID_COUNT] = {
     "k_fill_volume", "k_pack_frame", "k_integrate", "k_aos_soa", "k_surface_mask", "k_scan_counts", "k_surface_scatter",
     "k_neighbors", "k_upsample", "k_sweep<ENERGY>", "k_sweep<INIT_ALBEDO>", "k_sweep<LED_INIT>", "k_sweep<PROBE>",
     "k_sweep<ALBEDO>", "k_sweep<LIGHT>", "k_sweep<POSE>", "k_sweep<DIST>", "k_reg_energy", "k_dist_assemble", "k_dist_pcg",
-    "k_dist_update", "k_grad_update", "k_pad_images" };
+    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather" };
 static bool g_prof_on = false;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof_recs;
@@ -41,7 +41,7 @@ static cudaEvent_t pool_get() {
     return e;
 }
 Prof::Prof(cudaStream_t stream, int kernel_id) : st(stream), id(kernel_id) {
-    g_launches += 1;
+    if (kernel_id != KID_COMM_ALLREDUCE && kernel_id != KID_COMM_ALLGATHER) g_launches += 1;   // NCCL's kernels are not ours
     if (g_prof_on) {
         e0 = pool_get(); e1 = pool_get();
         cudaEventRecord(e0, st);
@@ -421,6 +421,34 @@ int psg_opt_set_keyframes(psg_optimizer* o, int F, const int* frame_idx, const f
         { Prof pf(o->stream, KID_PAD_IMAGES);
           k_pad_images<<<(unsigned)((per + 255) / 256), 256, 0, o->stream>>>(o->vol->staging.p, o->images.p + (size_t)f * per, per); }
         PSG_LAUNCH_CHECK();
+    }
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    o->frames_dirty = true;
+    o->inited = false;
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_opt_set_keyframes_u8(psg_optimizer* o, int F, const int* frame_idx, const float* poses16, const unsigned char* images_bgr_u8,
+                             int H, int W) {
+    if (!o || (F > 0 && (!frame_idx || !poses16 || !images_bgr_u8)) || F < 0 || H <= 0 || W <= 0) {
+        set_error("psg_opt_set_keyframes_u8: null or empty argument");
+        return PSG_ERR_INVALID;
+    }
+    if (F > kMaxFrames) { set_error("psg_opt_set_keyframes_u8: %d keyframes given, at most %d supported", F, kMaxFrames); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    o->F = F; o->H = H; o->W = W;
+    o->frame_idx.assign(frame_idx, frame_idx + F);
+    o->poses.assign(poses16, poses16 + 16 * (size_t)F);
+    const long long npix = (long long)F * H * W;
+    o->images.alloc((size_t)(npix > 0 ? npix : 1));
+    if (npix > 0) {
+        // the 8-bit pixels of all keyframes in one copy (3 B / pixel instead of 12), converted on the device
+        o->vol->staging.alloc((size_t)(npix * 3 + 3) / 4);
+        unsigned char* raw = reinterpret_cast<unsigned char*>(o->vol->staging.p);
+        PSG_CUDA(cudaMemcpyAsync(raw, images_bgr_u8, (size_t)npix * 3, cudaMemcpyHostToDevice, o->stream));
+        launch_texels_u8(o->stream, raw, o->images.p, npix);
     }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
     o->frames_dirty = true;

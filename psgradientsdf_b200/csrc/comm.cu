@@ -79,6 +79,7 @@ static size_t chunk_slots(const psg_optimizer* o) {
 
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb) {
     ncclComm_t comm = static_cast<ncclComm_t>(o->comm);
+    Prof pf(o->stream, KID_COMM_ALLREDUCE);
     PSG_NCCL(g_nccl.GroupStart());
     if (na) PSG_NCCL(g_nccl.AllReduce(a, a, na, ncclDouble, ncclSum, comm, o->stream));
     if (nb) PSG_NCCL(g_nccl.AllReduce(b, b, nb, ncclDouble, ncclSum, comm, o->stream));
@@ -125,10 +126,11 @@ void comm_allgather_rho(psg_optimizer* o) {
     if (o->S == 0) return;
     const size_t chunk = chunk_slots(o);
     float4* base = reinterpret_cast<float4*>(o->comm_buf.p);
-    PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * chunk, base, chunk * 4, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
+    { Prof pf(o->stream, KID_COMM_ALLGATHER);
+      PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * chunk, base, chunk * 4, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream)); }
     const SurfView sv = surf_view(o);
     const int n = (int)(chunk * o->world);
-    { Prof pf(o->stream, KID_AOS); k_scatter_rho<<<(n + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, base, (int)chunk, o->world, o->rank); }
+    { Prof pf(o->stream, KID_COMM_SCATTER); k_scatter_rho<<<(n + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, base, (int)chunk, o->world, o->rank); }
     PSG_LAUNCH_CHECK();
 }
 
@@ -143,10 +145,11 @@ void comm_allgather_stencil(psg_optimizer* o, float* blocks) {
     if (o->S == 0) return;
     const size_t chunk = chunk_slots(o);
     float* base = o->comm_buf.p;
-    PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * 14 * chunk, base, 14 * chunk, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
+    { Prof pf(o->stream, KID_COMM_ALLGATHER);
+      PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * 14 * chunk, base, 14 * chunk, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream)); }
     const SurfView sv = surf_view(o);
     const int n = (int)(chunk * o->world);
-    { Prof pf(o->stream, KID_AOS); k_scatter_stencil<<<(n + 255) / 256, 256, 0, o->stream>>>(sv, base, blocks, (int)chunk, o->world); }
+    { Prof pf(o->stream, KID_COMM_SCATTER); k_scatter_stencil<<<(n + 255) / 256, 256, 0, o->stream>>>(sv, base, blocks, (int)chunk, o->world); }
     PSG_LAUNCH_CHECK();
 }
 

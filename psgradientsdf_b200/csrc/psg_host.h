@@ -19,7 +19,7 @@ enum KernelId {
     KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
     KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
     KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
-    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_COUNT
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_COUNT
 };
 // Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
 struct Prof {
@@ -107,6 +107,8 @@ struct psg_optimizer {
     void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
     psg::DevBuf<float> comm_buf;             // all-gather staging: world chunks of packed per-slot results
     int rank = 0, world = 1;
+    int reduce_lo = 1 << 30, reduce_hi = -1; // mail slots whose values are still per-rank partial sums
+    size_t reduce_red = 0;                   // ... and how many doubles of o->red
     int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
@@ -140,6 +142,9 @@ void launch_integrate(psg_volume* v, int H, int W, const float* K, const float* 
 void launch_pack_frame(psg_volume* v, const float* planar_dev, int H, int W);
 void launch_aos_to_soa(psg_volume* v, const float* aos_dev, long long begin, long long count);
 void launch_soa_to_aos(psg_volume* v, float* aos_dev, long long begin, long long count);
+
+// ---- normals.cu
+void launch_texels_u8(cudaStream_t st, const unsigned char* bgr8_dev, float4* dst, long long n);
 
 // ---- surface.cu
 void build_surface(psg_optimizer* o, bool reindex_vis);

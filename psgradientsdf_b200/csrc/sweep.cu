@@ -821,6 +821,11 @@ double* mail_dev(psg_optimizer* o) { return o->red.p + kRedDoubles; }
 const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
+    if (o->world > 1 && o->reduce_hi >= o->reduce_lo) {
+        // one all-reduce for everything queued since the last round trip: per-keyframe sums + the scalar slots in flight
+        comm_allreduce_doubles(o, o->red.p, o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
+        o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0;
+    }
     if (n) PSG_CUDA(cudaMemcpyAsync(h, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaMemcpyAsync(h + kRedDoubles, mail_dev(o), kMailDoubles * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -828,8 +833,12 @@ const double* fetch_mail(psg_optimizer* o, size_t n) {
 }
 const double* mail_slot(const psg_optimizer* o, int slot) { return o->host_staging + kRedDoubles + 8 * slot; }
 
+// partial sums of this rank's share: summed over the ranks by the next fetch_mail (slots in flight are contiguous)
 static void reduce_over_ranks(psg_optimizer* o, size_t n, int slot) {
-    if (o->world > 1) comm_allreduce_doubles(o, o->red.p, n, mail_dev(o) + 8 * slot, 8);
+    if (o->world <= 1) return;
+    if (slot < o->reduce_lo) o->reduce_lo = slot;
+    if (slot > o->reduce_hi) o->reduce_hi = slot;
+    if (n > o->reduce_red) o->reduce_red = n;
 }
 
 // legacy one-block round trip: slot 0
