@@ -191,6 +191,22 @@ def sweep_bytes(A, S, F, out_block):
     return 48 * A + 80 * S + out_block * S + 128 * F
 
 
+def ncu_traffic(a, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture
+    (profiles/r1_traffic.json); None when the capture was taken on another workload."""
+    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        with open(p) as f:
+            t = json.load(f)
+    except OSError:
+        return None
+    w = t.get("workload", {})
+    if (w.get("grid"), w.get("frames"), w.get("model"), w.get("height"), w.get("width")) != (a.grid, a.frames, a.model, a.height, a.width):
+        return None
+    k = t.get("kernels", {}).get(kernel)
+    return None if k is None else k["dram_read_bytes"] + k["dram_write_bytes"]
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -353,8 +369,9 @@ def run_ours(a):
         bytes_launch = sweep_bytes(A // world, S // world, F, out_block.get(best, 0))
         ach = bytes_launch / (ms / n * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
-                "avg_launch_ms": ms / n}
+                "traffic": ncu_traffic(a, best) if world == 1 else None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": bytes_launch, "avg_launch_ms": ms / n,
+                "note": "instruction-issue bound, not HBM bound: see DESIGN.md section 3 / profiles/r1_summary.md"}
 
     # ---- CPU baseline (reference, 1 thread) on a bounded sample
     cpu = None

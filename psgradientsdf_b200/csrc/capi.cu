@@ -640,7 +640,7 @@ namespace {
 struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; };
 
 // queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
-Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot) {
+Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot, bool reg_energies_after = false) {
     Pending p; p.block = block; p.slot = slot; p.damping = damping;
     const bool led = o->set.model == PSG_MODEL_LED;
     o->last_block = block;
@@ -652,10 +652,13 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
         p.nred = launch_small_block(o, block, slot);
     } else {
         launch_dist_sweep(o, flags, slot);
-        launch_dist_solve(o, damping);
         // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242).  The
         // verdict stays on the device: the update kernels read it, the host learns it with the next round trip.
-        launch_dist_update(o, /*only_on_success=*/!led);
+        if (!launch_dist_block_small(o, damping, /*only_on_success=*/!led, reg_energies_after ? kSlotReg : -1)) {
+            launch_dist_solve(o, damping);
+            launch_dist_update(o, /*only_on_success=*/!led);
+            if (reg_energies_after) launch_reg_energies(o, kSlotReg);   // getNormalEnergy / getLaplacianEnergy after the update
+        }
     }
     return p;
 }
@@ -781,14 +784,12 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
         const int block = order[k];
         if (!enabled[block]) continue;
         const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) : 0;
-        queued[nq] = queue_block(o, block, cfg->damping, flags, slot);
+        const bool want_reg = block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN));
+        queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg);
         const size_t nred = queued[nq].nred;
         ++nq; ++slot;
         last_run = block;
-        if (block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN))) {
-            launch_reg_energies(o, kSlotReg);   // getNormalEnergy / getLaplacianEnergy after the distance update
-            reg_queued = true;
-        }
+        if (want_reg) reg_queued = true;
         if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) flush(nred);   // the host solves this one now
     }
     // closing energy (the convergence test needs it); blocks still queued ride on the same round trip

@@ -314,6 +314,263 @@ __global__ void __launch_bounds__(BS) k_dist_pcg(PcgArgs A, float* pbuf /* 2 x S
     }
 }
 
+// Barrier and dot-product reduction in one: warp 0 forms the block's partials, publishes them with the arrival, waits for the
+// other blocks and sums all partials (same association as block_sum2 + grid_total2_cg: identical bits); the other warps only
+// pass two block barriers.
+template <int BS>
+__device__ __forceinline__ double2 grid_reduce2(double a, double b, double* Pa, double* Pb, unsigned long long* ctr,
+                                                unsigned long long& target, int nb, double* s_buf /* 2 * BS / 32 + 2 */) {
+    constexpr int NW = BS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; }
+    target += (unsigned)nb;
+    __syncthreads();
+    if (warp == 0) {
+        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0;
+        ta = warp_sum(ta); tb = warp_sum(tb);
+        if (lane == 0) {
+            Pa[blockIdx.x] = ta; Pb[blockIdx.x] = tb;
+            asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(ctr) : "memory");
+            unsigned long long v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+            } while (v < target);
+        }
+        __syncwarp();
+        double xa = 0.0, xb = 0.0;
+        for (int i = lane; i < nb; i += 32) { xa += __ldcg(Pa + i); xb += __ldcg(Pb + i); }
+        xa = warp_sum(xa); xb = warp_sum(xb);
+        if (lane == 0) { s_buf[2 * NW] = xa; s_buf[2 * NW + 1] = xb; }
+    }
+    __syncthreads();
+    const double2 out = make_double2(s_buf[2 * NW], s_buf[2 * NW + 1]);
+    return out;
+}
+
+// ---- surfaces with at most one row per resident thread: assembly, solve, update and regulariser energies in ONE launch
+// Everything a row owns (its stencil block, neighbour / incidence indices, x, r, p, z, 1/diag) stays in registers for the
+// whole solve; only what other rows read crosses L2: z = r / diag and p (for the neighbours' on-the-fly direction update),
+// the stencil products U, and the block partials of the dot products.  The prologue is k_dist_assemble, the epilogue is
+// k_dist_update + k_grad_update (+ k_reg_energy), separated by the same grid barrier -- five kernel launches become one.
+struct SolveSmallArgs {
+    PcgArgs A;
+    VolView vol;
+    SurfView surf;
+    const int* lin;
+    double thr;                      // sqrt(3) * voxel size: Optimizer::updateDist's gate
+    float vs_inv;
+    unsigned long long* accepted;
+    int only_on_success;             // SH: the update is applied only if CG reports Success
+    double* reg_out;                 // {normal, laplacian, albedo} regulariser energy sums after the update, or nullptr
+    float* zbuf;                     // S floats: published z = r / diag
+};
+
+template <int BS>
+__global__ void __launch_bounds__(BS, 4) k_dist_solve_small(SolveSmallArgs G, float* pbuf /* 2 x S */) {
+    const PcgArgs& A = G.A;
+    __shared__ double s_buf[2 * (BS / 32) + 2];
+    __shared__ double s_reg[BS / 32][3];
+    const int S = A.S;
+    const int nb = gridDim.x;
+    const int row = blockIdx.x * BS + threadIdx.x;
+    const bool in = row < S;
+    double* P0 = A.partials;
+    double* P1 = A.partials + nb;
+    double* P2 = A.partials + 2 * nb;
+    double* P3 = A.partials + 3 * nb;   // unused second lane of the p.Ap reduction
+    unsigned long long bar_target = 0;
+
+    // ---- prologue: assemble the row (k_dist_assemble) and keep it
+    int col[3] = { -1, -1, -1 }, tn[6] = { -1, -1, -1, -1, -1, -1 };
+    float Ab[10], invd = 0.f, dd = 0.f, b = 0.f;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) Ab[i] = 0.f;
+    if (in) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) col[a] = __ldg(A.nbr_row + a * S + row);
+#pragma unroll
+        for (int h = 0; h < 6; ++h) tn[h] = __ldg(A.inc + h * S + row);
+#pragma unroll
+        for (int i = 0; i < 10; ++i) Ab[i] = __ldg(A.blk + (long long)i * S + row);
+        float rhs = __ldg(A.blk + (long long)10 * S + row);
+        float diag = Ab[0];
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = tn[h * 3 + a];
+                if (t >= 0) {
+                    rhs += __ldg(A.blk + (long long)(10 + a + 1) * S + t);
+                    diag += __ldg(A.blk + (long long)tri(a + 1, a + 1) * S + t);
+                }
+            }
+        dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
+        const float full = diag + dd;
+        invd = (full != 0.f) ? 1.f / full : 1.f;
+        b = rhs;
+        A.rhs[row] = rhs;          // diagnostics (psg_opt_last_vectors)
+    }
+    float x = 0.f, r = b, z = invd * b, p = z, u0 = 0.f, y = 0.f;
+    if (in) { pbuf[row] = p; G.zbuf[row] = z; }
+    const double2 t01 = grid_reduce2<BS>((double)b * (double)b, (double)b * (double)z, P0, P1, A.barrier, bar_target, nb, s_buf);
+    const float rhsNorm2 = (float)t01.x;
+    float absNew = (float)t01.y;
+    const float tol = 1.1920929e-07f;
+    float threshold = tol * tol * rhsNorm2;
+    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+    float residualNorm2 = rhsNorm2;
+    int it = 0;
+    if (rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+        float gamma = 0.f, beta = 1.f;   // first pass: the published p already is the search direction
+        int cur = 0;
+        while (it < A.max_iters) {
+            const float* pc = pbuf + (size_t)cur * S;
+            float* pn = pbuf + (size_t)(cur ^ 1) * S;
+            // ---- phase 1: p <- z + beta p (own row from registers, neighbours recomputed from the published z and p)
+            if (in) {
+                p = z * gamma + beta * p;
+                pn[row] = p;
+                float px[4];
+                px[0] = p;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const int c = col[a];
+                    px[a + 1] = c >= 0 ? __ldcg(G.zbuf + c) * gamma + beta * __ldcg(pc + c) : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float u = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                        if (k == 0 || col[k - 1] >= 0) u += aik * px[k];
+                    }
+                    const bool valid = (i == 0) || col[i - 1] >= 0;
+                    if (i == 0) u0 = u; else A.U[(long long)i * S + row] = valid ? u : 0.f;
+                }
+            }
+            grid_barrier(A.barrier, bar_target, nb);
+            // ---- phase 2: y = u_s[0] + incident u + damping * diag * p_s ; p . y
+            double pAp = 0.0;
+            if (in) {
+                y = u0;
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int t = tn[h * 3 + a];
+                        if (t >= 0) y += __ldcg(A.U + (long long)(a + 1) * S + t);
+                    }
+                y += dd * p;
+                pAp = (double)p * (double)y;
+            }
+            const float alpha = absNew / (float)grid_reduce2<BS>(pAp, 0.0, P0, P3, A.barrier, bar_target, nb, s_buf).x;
+            // ---- phase 3 (registers only, then publish z)
+            double rn = 0.0, rz = 0.0;
+            if (in) {
+                x += alpha * p;
+                r = r - alpha * y;
+                z = invd * r;
+                G.zbuf[row] = z;
+                rn = (double)r * (double)r;
+                rz = (double)r * (double)z;
+            }
+            const double2 t12 = grid_reduce2<BS>(rn, rz, P1, P2, A.barrier, bar_target, nb, s_buf);
+            residualNorm2 = (float)t12.x;
+            if (residualNorm2 < threshold) break;
+            const float absOld = absNew;
+            absNew = (float)t12.y;
+            beta = absNew / absOld;
+            gamma = 1.f;
+            cur ^= 1;
+            ++it;
+        }
+    } else if (rhsNorm2 == 0.f) {
+        residualNorm2 = 0.f;
+    }
+    if (in) A.x[row] = x;
+    if (row == 0) {
+        A.result[0] = (float)it;
+        A.result[1] = residualNorm2;
+        A.result[2] = rhsNorm2;
+        A.result[3] = threshold;
+    }
+    // ---- epilogue: Optimizer::updateDist (OptimizerAux.cpp:162-188), every block knows the verdict
+    const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
+    const bool apply = !G.only_on_success || err <= tol;
+    if (apply) {
+        int acc = 0;
+        if (in && fabs((double)x) < G.thr) { G.vol.dist[G.lin[row]] -= x; acc = 1; }
+        const unsigned m = __ballot_sync(0xffffffffu, acc);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(G.accepted, (unsigned long long)__popc(m));
+    }
+    if (!apply && !G.reg_out) return;   // uniform over the grid
+    grid_barrier(A.barrier, bar_target, nb);
+    // Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records; any one-to-one thread -> slot map will do
+    if (apply && in) {
+        const int t = row;
+        const int s = __float_as_int(G.surf.rec2[t].w);
+        const int lin = __float_as_int(G.surf.rec3[t].w);
+        const float dist = __ldcg(G.vol.dist + lin);
+        const int pb = __float_as_int(G.surf.rec1[t].w);
+        float fd[3], nfd[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int nl = G.surf.nbr_lin[a * S + s];
+            const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+            const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+            fd[a] = (pp * (dn - dist)) * G.vs_inv;
+        }
+        G.vol.gx[lin] = fd[0]; G.vol.gy[lin] = fd[1]; G.vol.gz[lin] = fd[2];
+        normalized3(fd, nfd);
+        G.surf.rec0[t] = make_float4(dist, nfd[0], nfd[1], nfd[2]);
+        G.surf.rec2[t] = make_float4(fd[0], fd[1], fd[2], __int_as_float(s));
+        G.surf.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
+    }
+    // getNormalEnergy / getLaplacianEnergy / getAlbedoRegEnergy (Optimizer.cpp:86-136) on the updated distances
+    if (G.reg_out) {
+        double en = 0.0, el = 0.0, er = 0.0;
+        if (in) {
+            const int s = row;
+            const int lin = G.lin[s];
+            const float dist = __ldcg(G.vol.dist + lin);
+            const float rho[3] = { G.vol.r[lin], G.vol.g[lin], G.vol.b[lin] };
+            const unsigned char pb = G.surf.pos[s];
+            const long long stride[3] = { 1, G.vol.dims[0], (long long)G.vol.dims[0] * G.vol.dims[1] };
+            float fd[3], d2[3], Gr[9];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = G.surf.nbr_lin[a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * G.vs_inv;
+                const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+                const float d1 = (l1 < G.vol.N) ? __ldcg(G.vol.dist + l1) : dist;
+                const float d0 = (l0 >= 0) ? __ldcg(G.vol.dist + l0) : dist;
+                d2[a] = d1 + d0 - 2 * dist;
+                const float nr = nl >= 0 ? G.vol.r[nl] : rho[0], ng = nl >= 0 ? G.vol.g[nl] : rho[1], nbb = nl >= 0 ? G.vol.b[nl] : rho[2];
+                Gr[a] = (pp * (nr - rho[0])) * G.vs_inv; Gr[3 + a] = (pp * (ng - rho[1])) * G.vs_inv; Gr[6 + a] = (pp * (nbb - rho[2])) * G.vs_inv;
+            }
+            const float e = norm3(fd) - 1;
+            en = (double)(e * e);
+            const float lap = (d2[0] + d2[1] + d2[2]) * G.vs_inv * G.vs_inv;
+            el = (double)(lap * lap);
+            er = (double)((norm3(Gr) + norm3(Gr + 3)) + norm3(Gr + 6));
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        en = warp_sum(en); el = warp_sum(el); er = warp_sum(er);
+        if (lane == 0) { s_reg[warp][0] = en; s_reg[warp][1] = el; s_reg[warp][2] = er; }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < BS / 32; ++i) v += s_reg[i][threadIdx.x];
+            atomicAdd(&G.reg_out[threadIdx.x], v);
+        }
+    }
+}
+
 // ---- small surfaces: the whole solve inside ONE thread-block cluster ------------------------------------------------
 // At 128^3 an iteration touches ~4 MB; the grid-wide kernel above spends its time in grid.sync() and in dependent L2
 // round trips.  Here <= 8 CTAs x 1024 threads form one cluster; a thread owns RPT rows (row = gtid + j * threads), keeps
@@ -577,6 +834,52 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
         if (rpt == 1) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 1>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
         else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 4>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
     }
+}
+
+// Fused path for surfaces with at most one row per resident thread (128^3, 256^3): returns false if it does not apply.
+bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot) {
+    const int S = o->S;
+    if (S == 0 || o->pcg_mode != 0) return false;
+    int dev = 0, sms = 0, per_sm = 0;
+    PSG_CUDA(cudaGetDevice(&dev));
+    PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
+    const int grid = (S + kPcgBlock - 1) / kPcgBlock;
+    if (per_sm < 1 || grid > sms * per_sm) return false;
+
+    o->red.alloc(kRedDoubles + kMailDoubles);
+    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotPcg, 0, 16 * sizeof(double), o->stream));   // verdict + accepted counter
+    if (reg_slot >= 0) PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * reg_slot, 0, 8 * sizeof(double), o->stream));
+    o->vecs.alloc((size_t)S * 25 + 8);
+    float* base = o->vecs.p;
+    SolveSmallArgs G;
+    PcgArgs& A = G.A;
+    A.S = S; A.blk = base; A.nbr_row = o->nbr_row.p; A.inc = o->inc.p;
+    A.rhs = base + (size_t)14 * S; A.invd = base + (size_t)15 * S; A.ddiag = base + (size_t)16 * S;
+    A.x = base + (size_t)17 * S; A.r = base + (size_t)18 * S; A.p = base + (size_t)19 * S; A.tmp = base + (size_t)20 * S;
+    A.U = base + (size_t)21 * S;
+    A.result = reinterpret_cast<float*>(mail_dev(o) + 8 * kSlotPcg);
+    A.damping = damping;
+    A.max_iters = 2 * S;
+    o->pcg_partials.alloc((size_t)4 * grid + 1);
+    A.partials = o->pcg_partials.p + 1;
+    A.barrier = reinterpret_cast<unsigned long long*>(o->pcg_partials.p);
+    PSG_CUDA(cudaMemsetAsync(A.barrier, 0, sizeof(unsigned long long), o->stream));
+    o->pcg_pbuf.alloc((size_t)2 * S);
+    float* pbuf = o->pcg_pbuf.p;
+    G.vol = o->vol->view();
+    G.surf = surf_view(o);
+    G.lin = o->lin.p;
+    G.thr = sqrt(3.0) * (double)o->vs;
+    G.vs_inv = o->vs_inv;
+    G.accepted = reinterpret_cast<unsigned long long*>(mail_dev(o) + 8 * kSlotCount);
+    G.only_on_success = only_on_success ? 1 : 0;
+    G.reg_out = reg_slot >= 0 ? mail_dev(o) + 8 * reg_slot : nullptr;
+    G.zbuf = A.r;   // plane 18 is free on this path (the residual lives in registers)
+    void* args[] = { &G, &pbuf };
+    Prof pf(o->stream, KID_PCG_SOLVE);
+    PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
+    return true;
 }
 
 void launch_dist_update(psg_optimizer* o, bool only_on_success) {

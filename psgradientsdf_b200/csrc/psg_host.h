@@ -182,6 +182,7 @@ void launch_reg_energies(psg_optimizer* o, int slot);
 void reg_energies(psg_optimizer* o, double* En, double* El, double* Er);
 
 // ---- pcg.cu
+bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot);   // fused assemble + PCG + update (+ reg energies)
 void launch_dist_solve(psg_optimizer* o, float damping);              // assemble + PCG; verdict -> mail slot kSlotPcg
 void launch_dist_update(psg_optimizer* o, bool only_on_success);     // gated on the device by the PCG verdict; count -> kSlotCount
 void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted);   // after fetch_mail

@@ -158,18 +158,22 @@ def test_out_of_image_projection():
 
 
 def test_pcg_kernels_agree():
-    """Cluster-synchronised and cooperative-grid PCG run the same iteration: identical iteration count and solution."""
+    """The three distance-solve kernels run the same iteration: fused small-surface kernel (0, the default), thread-block
+    cluster (1), general cooperative grid (2).  0 and 2 share the row -> thread map, hence the dot-product partials and every bit."""
     model, G = "SH1", 40
     sc = scene(model)
     outs = []
-    for mode in (1, 2):
+    for mode in (0, 1, 2):
         gv, go = make_gpu(model, G, sc)
         handoff(go, sc); go.init_albedo(); go.set_pcg_mode(mode)
         info = go.step("dist", damping=1.0, normal_reg=True)
-        outs.append((info["iters"], info["cg_success"], go.last_vectors("dist")[1], gv.download()))
-    assert outs[0][0] == outs[1][0] and outs[0][1] == outs[1][1]
-    assert rel_err(outs[0][2], outs[1][2]) < 1e-6
-    assert rel_err(outs[0][3][:, 0], outs[1][3][:, 0]) < 1e-6
+        outs.append((info["iters"], info["cg_success"], go.last_vectors("dist")[1], gv.download(), info["n_accepted"], go.energy()))
+    for o in outs[1:]:
+        assert outs[0][0] == o[0] and outs[0][1] == o[1] and outs[0][4] == o[4]
+        assert rel_err(outs[0][2], o[2]) < 1e-6
+        assert rel_err(outs[0][3][:, 0], o[3][:, 0]) < 1e-6
+    assert np.array_equal(outs[0][2], outs[2][2]) and np.array_equal(outs[0][3].view(np.uint32), outs[2][3].view(np.uint32))
+    assert outs[0][5] == outs[2][5]
 
 
 def test_sharded_partials_add_up():
