@@ -389,7 +389,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     if (!o) return PSG_OK;
     cudaSetDevice(o->vol->device);
     psg_opt_comm_destroy(o);
-    o->images.release(); o->frames.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
+    o->images.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);

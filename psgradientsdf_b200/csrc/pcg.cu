@@ -848,8 +848,8 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
     o->red.alloc(kRedDoubles + kMailDoubles);
-    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotPcg, 0, 16 * sizeof(double), o->stream));   // verdict + accepted counter
-    if (reg_slot >= 0) PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * reg_slot, 0, 8 * sizeof(double), o->stream));
+    static_assert(kSlotReg + 1 == kSlotPcg && kSlotPcg + 1 == kSlotCount, "slots 5..7 are cleared with one memset");
+    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotReg, 0, 24 * sizeof(double), o->stream));   // reg energies, verdict, counter + barrier
     o->vecs.alloc((size_t)S * 25 + 8);
     float* base = o->vecs.p;
     SolveSmallArgs G;
@@ -863,8 +863,7 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     A.max_iters = 2 * S;
     o->pcg_partials.alloc((size_t)4 * grid + 1);
     A.partials = o->pcg_partials.p + 1;
-    A.barrier = reinterpret_cast<unsigned long long*>(o->pcg_partials.p);
-    PSG_CUDA(cudaMemsetAsync(A.barrier, 0, sizeof(unsigned long long), o->stream));
+    A.barrier = reinterpret_cast<unsigned long long*>(mail_dev(o) + 8 * kSlotCount + 1);
     o->pcg_pbuf.alloc((size_t)2 * S);
     float* pbuf = o->pcg_pbuf.p;
     G.vol = o->vol->view();

@@ -35,6 +35,8 @@ struct __align__(16) FrameParams {
     float light[9];   // SH coefficients of this keyframe (4 or 9 used); unused for LED
     float pad[3];
 };
+// all keyframes' parameters travel as a kernel parameter (constant bank, indexed by the warp-uniform keyframe)
+struct FrameTable { FrameParams f[kMaxFrames]; };
 
 struct SurfView {
     int S;                              // number of surface voxels

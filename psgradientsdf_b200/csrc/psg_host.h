@@ -84,7 +84,7 @@ struct psg_optimizer {
     std::vector<float> poses;                // F x 16 (host copy, authoritative)
     std::vector<float> light;                // F x nb or 3
     psg::DevBuf<float4> images;              // F x H x W texels (b, g, r, 0)
-    psg::DevBuf<psg::FrameParams> frames;    // F
+    psg::FrameTable frame_table;             // per-keyframe R, t, light (host copy; passed to the sweeps as a kernel parameter)
     bool frames_dirty = true;
     bool inited = false;
     // surface work list
@@ -134,7 +134,7 @@ constexpr int kRedDoubles = kMaxFrames * 64;
 constexpr int kMailDoubles = 64;
 constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
 constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
-constexpr int kSlotCount = 7;    // unsigned long long: accepted distance updates
+constexpr int kSlotCount = 7;    // [0] unsigned long long: accepted distance updates, [1] arrival counter of the PCG's grid barrier
 
 // ---- volume.cu
 void launch_fill_volume(psg_volume* v);
@@ -157,7 +157,7 @@ struct SweepOut {
     double E = 0.0;
     long long n_active = 0;
 };
-void upload_frames(psg_optimizer* o);
+void refresh_frame_table(psg_optimizer* o);
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
 float4* comm_pack_rho(psg_optimizer* o);                         // this rank's send chunk (written by the sweep)
@@ -171,6 +171,8 @@ void sweep_led_light_init(psg_optimizer* o, double sums[6]);
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3);
 // queue-only pieces (no host wait) and the one round trip that collects their results
 double* mail_dev(psg_optimizer* o);
+double* red_dev(psg_optimizer* o);
+const double* red_host(const psg_optimizer* o);
 const double* fetch_mail(psg_optimizer* o, size_t n_red_doubles);
 const double* mail_slot(const psg_optimizer* o, int slot);
 void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot);

@@ -31,7 +31,6 @@ struct SweepArgs {
     SurfView surf;
     Camera cam;
     LossParams loss;
-    const FrameParams* frames;
     const float4* images;
     int F;
     // multi-GPU: updated albedo records / distance stencil blocks of this rank's slots, packed by local slot for the all-gather
@@ -213,7 +212,7 @@ __device__ __forceinline__ void grid_sum_scalars(const double* block_vals, doubl
 }
 
 template <int MODEL, int MODE>
-__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_POSE || MODE == M_LIGHT) ? 2 : 4) k_sweep(SweepArgs A) {
+__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_POSE || MODE == M_LIGHT) ? 2 : 4) k_sweep(const __grid_constant__ SweepArgs A, const __grid_constant__ FrameTable T) {
     constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
     constexpr bool LED = (MODEL == PSG_MODEL_LED);
     // per-keyframe reduction width (padded to a power of two / multiple of 32 lanes)
@@ -324,13 +323,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
     while (uni) {
         const int f = __ffsll((long long)uni) - 1;
         uni &= uni - 1;
-        FrameParams P;
-        {
-            const float4* src = reinterpret_cast<const float4*>(A.frames + f);
-            float4* dst = reinterpret_cast<float4*>(&P);
-#pragma unroll
-            for (int i = 0; i < (int)(sizeof(FrameParams) / 16); ++i) dst[i] = __ldg(src + i);
-        }
+        const FrameParams& P = T.f[f];   // kernel parameter space: no global load at the head of the iteration
         const bool act = live && ((vis >> f) & 1ull);
 
         bool ok = false;
@@ -740,20 +733,20 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_P
 
 // ------------------------------------------------------------------------------------------------ launchers
 static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
-    upload_frames(o);   // (re)allocates o->frames on first use, so it must precede the pointer capture below
+    refresh_frame_table(o);
     SweepArgs A;
     memset(&A, 0, sizeof(A));
     A.vol = o->vol->view();
     A.surf = surf_view(o);
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
-    A.frames = o->frames.p; A.images = o->images.p; A.F = o->F;
+    A.images = o->images.p; A.F = o->F;
     shard_blocks(o->S, o->rank, o->world, &A.blk_first, &A.blk_stride, &A.blk_count);
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
     o->red.alloc(kRedDoubles + kMailDoubles);
-    A.red = o->red.p;
+    A.red = red_dev(o);
     A.scal = mail_dev(o) + 8 * slot;
     const size_t grid = (size_t)(o->S + 31) / 32 + 1;
     const size_t ngroups = grid / kRedGroup + 2;
@@ -767,18 +760,16 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     return A;
 }
 
-void upload_frames(psg_optimizer* o) {
+// per-keyframe R, t, light -> the table that every sweep launch passes by value
+void refresh_frame_table(psg_optimizer* o) {
     if (!o->frames_dirty) return;
-    o->ensure_host_staging();
-    FrameParams* fr = o->host_frames;   // pinned; every API call ends with a stream sync, so the previous copy has finished
+    FrameParams* fr = o->frame_table.f;
     memset(fr, 0, sizeof(FrameParams) * kMaxFrames);
     for (int f = 0; f < o->F; ++f) {
         const float* P = o->poses.data() + 16 * f;
         for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
         if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
     }
-    o->frames.alloc(kMaxFrames);
-    PSG_CUDA(cudaMemcpyAsync(o->frames.p, fr, sizeof(FrameParams) * (size_t)(o->F > 0 ? o->F : 1), cudaMemcpyHostToDevice, o->stream));
     o->frames_dirty = false;
 }
 
@@ -800,7 +791,7 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
         if (dyn_smem > 48 * 1024)                                                                                      \
             PSG_CUDA(cudaFuncSetAttribute(k_sweep<MODEL, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem)); \
         Prof pf(o->stream, KID_SWEEP_ENERGY + MODE);                                                                   \
-        k_sweep<MODEL, MODE><<<grid, kBlockDim, dyn_smem, o->stream>>>(A);                                                \
+        k_sweep<MODEL, MODE><<<grid, kBlockDim, dyn_smem, o->stream>>>(A, o->frame_table);                                                \
     } break;
     switch (o->set.model) {
         PSG_SWEEP_CASE(PSG_MODEL_SH1)
@@ -816,22 +807,24 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
 // function queues kernels (and, across GPUs, the collectives on their results) without waiting; fetch_mail brings n doubles
 // of per-keyframe sums plus the whole mailbox to pinned host memory in one round trip.  Several blocks of an outer
 // iteration can therefore be in flight before the host waits once (psg_opt_iteration).
-double* mail_dev(psg_optimizer* o) { return o->red.p + kRedDoubles; }
+// device / pinned-host layout: mailbox first, per-keyframe sums behind it, so that one copy brings both
+double* mail_dev(psg_optimizer* o) { return o->red.p; }
+double* red_dev(psg_optimizer* o) { return o->red.p + kMailDoubles; }
 
 const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
     if (o->world > 1 && o->reduce_hi >= o->reduce_lo) {
         // one all-reduce for everything queued since the last round trip: per-keyframe sums + the scalar slots in flight
-        comm_allreduce_doubles(o, o->red.p, o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
+        comm_allreduce_doubles(o, red_dev(o), o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
         o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0;
     }
-    if (n) PSG_CUDA(cudaMemcpyAsync(h, o->red.p, n * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
-    PSG_CUDA(cudaMemcpyAsync(h + kRedDoubles, mail_dev(o), kMailDoubles * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaMemcpyAsync(h, o->red.p, (kMailDoubles + n) * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
     return h;
 }
-const double* mail_slot(const psg_optimizer* o, int slot) { return o->host_staging + kRedDoubles + 8 * slot; }
+const double* mail_slot(const psg_optimizer* o, int slot) { return o->host_staging + 8 * slot; }
+const double* red_host(const psg_optimizer* o) { return o->host_staging + kMailDoubles; }
 
 // partial sums of this rank's share: summed over the ranks by the next fetch_mail (slots in flight are contiguous)
 static void reduce_over_ranks(psg_optimizer* o, size_t n, int slot) {
@@ -849,7 +842,7 @@ static const double* fetch_red(psg_optimizer* o, size_t n, bool over_ranks = tru
     o->last_active = (long long)(mail_slot(o, 0)[7] + 0.5);
     return h;
 }
-static inline const double* scalars(const double* h) { return h + kRedDoubles; }
+static inline const double* scalars(const double* h) { return h; }   // slot 0
 
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
     SweepArgs A = base_args(o);
@@ -928,7 +921,7 @@ void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<doubl
     const int nbk = block == PSG_BLOCK_POSE ? 6 : o->nb;
     const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
     const int NT = nbk * (nbk + 1) / 2;
-    const double* r = o->host_staging;
+    const double* r = red_host(o);
     Hout.assign((size_t)o->F * nbk * nbk, 0.0);
     bout.assign((size_t)o->F * nbk, 0.0);
     for (int f = 0; f < o->F; ++f) {
@@ -1034,7 +1027,7 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
 // grow on demand); this variant runs the same kernel with all of its scratch in one array that is part of the loaded
 // module, so the only device memory it touches beyond the caller's volume / keyframes is that array.
 //
-// Layout of the array: 8 doubles of results | arrival counter | per-keyframe parameters (64 entries) | per-block
+// Layout of the array: 8 doubles of results | arrival counter | per-block
 // partial sums for up to kNoAllocMaxSurface / 32 blocks.  About 4.2 MB, held by every GPU that loads the library until
 // the process exits.
 constexpr int kNoAllocMaxSurface = 1 << 21;   // 2 097 152 surface voxels
@@ -1042,7 +1035,6 @@ constexpr int kNoAllocMaxDevices = 64;
 struct NoAllocScratch {
     double red[8];
     unsigned counter[kNoAllocMaxSurface / 32 / kRedGroup + 8];   // [0] top level, [1 + g] per group of blocks
-    FrameParams frames[kMaxFrames];
     double partials[((size_t)kNoAllocMaxSurface / 32 + kNoAllocMaxSurface / 32 / kRedGroup + 8) * 8];   // blocks, then groups
 };
 static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
@@ -1073,15 +1065,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         NoAllocScratch* sc = g_noalloc_dev[dev];
         if (o->S == 0) { const double zero = 0.0; if (E) *E = zero / zero; if (n_active) *n_active = 0; return PSG_OK; }   // E / S with S = 0, as psg_opt_energy
 
-        // per-keyframe parameters, built on the stack and copied into the array
-        FrameParams fr[kMaxFrames];
-        memset(fr, 0, sizeof(fr));
-        for (int f = 0; f < o->F; ++f) {
-            const float* P = o->poses.data() + 16 * f;
-            for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
-            if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
-        }
-        PSG_CUDA(cudaMemcpyAsync(sc->frames, fr, sizeof(FrameParams) * (size_t)(o->F > 0 ? o->F : 1), cudaMemcpyHostToDevice, o->stream));
+        refresh_frame_table(o);   // per-keyframe parameters travel as a kernel parameter, not through device memory
         // the array keeps whatever the previous call left: results and the arrival counter must start at zero
         PSG_CUDA(cudaMemsetAsync(sc, 0, sizeof(sc->red) + sizeof(sc->counter), o->stream));
 
@@ -1091,7 +1075,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.surf = surf_view(o);   // re-gathers the compact records if the volume changed; launches a kernel, allocates nothing
         A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
         A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
-        A.frames = sc->frames; A.images = o->images.p; A.F = o->F;
+        A.images = o->images.p; A.F = o->F;
         shard_blocks(o->S, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // always the whole work list (no communication on this path)
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
@@ -1104,9 +1088,9 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         if (o->sweep_split > 0) W = o->sweep_split;
         const size_t smem = W > 1 ? (size_t)W * 14 * 32 * sizeof(float) : 0;
         switch (o->set.model) {
-            case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
-            case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
-            default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+            case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
+            case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
+            default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
         }
         count_launch();
         PSG_LAUNCH_CHECK();
