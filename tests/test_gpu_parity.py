@@ -367,3 +367,16 @@ def test_iteration_matches_block_steps(model):
     assert rel_err(gv1.download(), gv2.download()) < 1e-7
     assert rel_err(g1.poses(), g2.poses()) < 1e-7
     assert rel_err(g1.light(), g2.light()) < 1e-6
+
+
+def test_fusion_256():
+    """Fusion at 256^3 (BASELINE configs[2] grid) against the C restatement: volume and visibility bit-identical."""
+    model, G = "SH1", 256
+    sc = scene(model)
+    ov, oo = make_oracle(model, G, sc)
+    gv, go = make_gpu(model, G, sc)
+    a, b = ov.download(), gv.download()
+    assert np.count_nonzero(a[:, 4]) > 100000
+    assert_bit_equal(a, b, "fused 256^3 volume")
+    wo, lo = ov.vis()
+    assert np.array_equal(wo, gv.vis())
