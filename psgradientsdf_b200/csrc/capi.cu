@@ -227,8 +227,9 @@ int psg_device_count(int* count) {
 int psg_volume_create(psg_volume** out, const int dims[3], float voxel_size, const float shift[3], float T, float zmin,
                       float zmax, int max_frames, int device) {
     if (!out || !dims || !shift) { set_error("psg_volume_create: null argument"); return PSG_ERR_INVALID; }
-    if (dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 || (long long)dims[0] * dims[1] * dims[2] > (1ll << 31) - 64) {
-        set_error("psg_volume_create: grid %d x %d x %d not supported (needs 0 < W*H*D < 2^31)", dims[0], dims[1], dims[2]);
+    if (dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 || (long long)dims[0] * dims[1] * dims[2] > (1ll << 31) - 64 ||
+        dims[1] > 65535 || dims[2] > 65535) {   // H and D are CUDA grid dimensions of the fusion launch
+        set_error("psg_volume_create: grid %d x %d x %d not supported (needs 0 < W*H*D < 2^31, H and D <= 65535)", dims[0], dims[1], dims[2]);
         return PSG_ERR_INVALID;
     }
     if (max_frames < 1) { set_error("psg_volume_create: max_frames must be >= 1"); return PSG_ERR_INVALID; }

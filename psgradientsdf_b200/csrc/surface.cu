@@ -191,10 +191,11 @@ __global__ void __launch_bounds__(256) k_upsample(VolView src, VolView dst, floa
     const long long lin = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (lin >= dst.N) return;
     const int W0 = dst.dims[0], W1 = dst.dims[1];
-    const int i = (int)(lin % W0);
-    const long long rest = lin / W0;
-    const int j = (int)(rest % W1);
-    const int k = (int)(rest / W1);
+    const unsigned ul = (unsigned)lin;               // N < 2^31: 32-bit divisions
+    const int i = (int)(ul % (unsigned)W0);
+    const unsigned rest = ul / (unsigned)W0;
+    const int j = (int)(rest % (unsigned)W1);
+    const int k = (int)(rest / (unsigned)W1);
     const long long pl = (long long)(i >> 1) + (long long)src.dims[0] * (j >> 1) + (long long)src.dims[0] * src.dims[1] * (k >> 1);
     const float pd = src.dist[pl];
     if (pd == src.T) {   // never-fused parents are skipped; children keep the fill value (dist = T, rgb = 0.5)

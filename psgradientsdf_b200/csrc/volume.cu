@@ -42,14 +42,14 @@ struct FuseParams {
 
 // One thread per voxel, x fastest (coalesced plane accesses).  Gates in the reference's order
 // (VolumetricGradSdf.cpp:84-116); voxels that fail a gate touch no volume memory.
+// 3-D launch: (x-run, j, k) come from the block / thread indices -- a linear index would cost two 64-bit divisions per voxel,
+// more than the projection itself (the kernel is instruction bound: most voxels are rejected before they touch memory).
 __global__ void __launch_bounds__(256) k_integrate(VolView v, const float* __restrict__ frame, FuseParams P) {
-    const long long lin = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (lin >= v.N) return;
     const int W0 = v.dims[0], W1 = v.dims[1];
-    const int i = (int)(lin % W0);
-    const long long rest = lin / W0;
-    const int j = (int)(rest % W1);
-    const int k = (int)(rest / W1);
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    if (i >= W0) return;
+    const int j = (int)blockIdx.y, k = (int)blockIdx.z;
+    const long long lin = (long long)i + (long long)W0 * ((long long)j + (long long)W1 * k);
 
     const float p[3] = { v.origin[0] + v.vs * (float)i, v.origin[1] + v.vs * (float)j, v.origin[2] + v.vs * (float)k };
     const float q[3] = { p[0] - P.t[0], p[1] - P.t[1], p[2] - P.t[2] };
@@ -134,7 +134,10 @@ void launch_integrate(psg_volume* v, int H, int W, const float* K, const float* 
     for (int a = 0; a < 3; ++a) P.t[a] = t[a];
     P.H = H; P.W = W; P.counter = counter;
     const VolView view = v->view();
-    { Prof pf(v->stream, KID_FUSE); k_integrate<<<blocks_for(v->N, 256), 256, 0, v->stream>>>(view, v->frame.p, P); }
+    int bx = (v->dims[0] + 31) / 32 * 32;
+    if (bx > 256) bx = 256;
+    const dim3 grid((unsigned)((v->dims[0] + bx - 1) / bx), (unsigned)v->dims[1], (unsigned)v->dims[2]);
+    { Prof pf(v->stream, KID_FUSE); k_integrate<<<grid, bx, 0, v->stream>>>(view, v->frame.p, P); }
     PSG_LAUNCH_CHECK();
 }
 
