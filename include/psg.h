@@ -240,6 +240,19 @@ int psg_volume_integrate_raw(psg_volume* vol, psg_normals* ne, const unsigned ch
 int psg_opt_set_keyframes_u8(psg_optimizer* opt, int F, const int* frame_idx, const float* poses4x4, const unsigned char* images_bgr_u8,
                              int H, int W);
 
+/* ------------------------------------------------------------------ rigid depth-to-SDF tracking
+ * The per-pixel part of RigidPointOptimizer::optimize_sampled (cpp/include/sdf_tracker/RigidPointOptimizer.cpp:38-62) with
+ * Sdf::weights / Sdf::tsdf of the gradient-SDF volume (VolumetricGradSdf.h:76-93).  The host keeps the reference's 6 x 6
+ * solve and pose update (:67-75, Eigen LLT + Sophus SE3::exp) and calls psg_tracker_system once per Gauss-Newton iteration. */
+/* the frame to track: depth in metres (H*W floats, host), or as the loader read it (16-bit, metres = value * unit) */
+int psg_tracker_set_depth(psg_volume* vol, const float* depth, int H, int W);
+int psg_tracker_set_depth_u16(psg_volume* vol, const unsigned short* depth_u16, float depth_unit, int H, int W);
+/* at pose (R, t) (camera to world, SE3::rotationMatrix / translation): E = sum phi^2 (the reference divides by count
+ * afterwards), g = sum phi J, H = sum J J^T (row-major 6 x 6), count = pixels that hit a fused voxel; zmin / zmax are the
+ * volume's.  Sums are formed in double; which pixels count is decided bit-identically to the reference. */
+int psg_tracker_system(psg_volume* vol, const float K[9], const float R[9], const float t[3], int sampling, double* E_sum,
+                       double g6[6], double H36[36], long long* count);
+
 /* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
  * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
  * every rank); the (surface voxel, keyframe) sweeps are split by round-robin 32-slot blocks of the visibility-sorted work list.

@@ -1196,3 +1196,58 @@ void or_opt_subsampling(or_opt* o) {
     o->vs_inv = (float)(1.0 / (double)o->vs);
     select_surface(o, 0);
 }
+
+/* ---- rigid depth-to-SDF tracker: one pass of RigidPointOptimizer::optimize_sampled's inner loop
+ * (sdf_tracker/RigidPointOptimizer.cpp:38-62) at pose (R, t), with Sdf::weights / Sdf::tsdf of the gradient-SDF volume
+ * (VolumetricGradSdf.h:76-93) and VoxelGrid::nearest_index / world2voxel / voxel2world (VoxelGrid.cpp:57-72,
+ * VoxelGrid.h:38-66).  Sums in one serial float each, in pixel order, like the reference. */
+static int nearest_index(const or_volume* v, const float* p) {
+    const float i = (p[0] - v->origin[0]) / v->vs, j = (p[1] - v->origin[1]) / v->vs, k = (p[2] - v->origin[2]) / v->vs;
+    if (i <= 0 || j <= 0 || k <= 0 || i >= (v->dims[0] - 1) || j >= (v->dims[1] - 1) || k >= (v->dims[2] - 1)) return -1;
+    const int im = (int)((double)i + 0.5), jm = (int)((double)j + 0.5), km = (int)((double)k + 0.5);
+    return im + jm * v->dims[0] + km * v->dims[0] * v->dims[1];
+}
+
+void or_tracker_system(const or_volume* v, const float* depth, int H, int W, const float K[9], const float R[9],
+                       const float t[3], int sampling, float* E_out, float g6[6], float H36[36], long long* count) {
+    const float fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+    const float fx_inv = 1.f / fx, fy_inv = 1.f / fy;
+    float E = 0.f, g[6] = {0, 0, 0, 0, 0, 0}, Hm[36];
+    long long counter = 0;
+    for (int i = 0; i < 36; ++i) Hm[i] = 0.f;
+    for (int y = 0; y < H; y += sampling)
+        for (int x = 0; x < W; x += sampling) {
+            const float z = depth[y * W + x];
+            if (z <= v->zmin || z >= v->zmax) continue;
+            const float x0 = ((float)x - cx) * fx_inv;
+            const float y0 = ((float)y - cy) * fy_inv;
+            const float pc[3] = { x0 * z, y0 * z, z };
+            float Rp[3], point[3];
+            mat_vec(R, pc, Rp);
+            for (int a = 0; a < 3; ++a) point[a] = Rp[a] + t[a];
+            const int I = nearest_index(v, point);
+            if (I < 0 || !(v->w[I] > 0)) continue;
+            const float grad[3] = { v->gx[I], v->gy[I], v->gz[I] };
+            float gn[3];
+            normalized3(grad, gn);
+            /* voxel2world(world2voxel(point)) - point: world2voxel adds a FLOAT 0.5 and truncates */
+            float d[3];
+            for (int a = 0; a < 3; ++a) {
+                const float fi = (point[a] - v->origin[a]) / v->vs + 0.5f;
+                const int idx = (int)fi;
+                d[a] = (v->origin[a] + v->vs * (float)idx) - point[a];
+            }
+            const float phi0 = v->dist[I] + dot3(gn, d);
+            E += phi0 * phi0;
+            const float gx[6] = { gn[0], gn[1], gn[2], point[1] * gn[2] - point[2] * gn[1], point[2] * gn[0] - point[0] * gn[2],
+                                  point[0] * gn[1] - point[1] * gn[0] };
+            for (int a = 0; a < 6; ++a) g[a] += phi0 * gx[a];
+            for (int a = 0; a < 6; ++a)
+                for (int b = 0; b < 6; ++b) Hm[6 * a + b] += gx[a] * gx[b];
+            ++counter;
+        }
+    *E_out = E;
+    for (int a = 0; a < 6; ++a) g6[a] = g[a];
+    for (int a = 0; a < 36; ++a) H36[a] = Hm[a];
+    *count = counter;
+}

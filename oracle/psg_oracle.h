@@ -84,4 +84,8 @@ void or_opt_subsampling(or_opt*);                                   /* Optimizer
 #ifdef __cplusplus
 }
 #endif
+/* RigidPointOptimizer::optimize_sampled's inner loop (sdf_tracker/RigidPointOptimizer.cpp:38-62) at pose (R, t) */
+void or_tracker_system(const or_volume*, const float* depth, int H, int W, const float K[9], const float R[9],
+                       const float t[3], int sampling, float* E, float g6[6], float H36[36], long long* count);
+
 #endif

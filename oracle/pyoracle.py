@@ -78,6 +78,8 @@ def lib():
         L.or_opt_block_H.restype = C.c_longlong
         L.or_opt_block_H.argtypes = [vp, vp, vp, vp]
         L.or_opt_subsampling.argtypes = [vp]
+        L.or_tracker_system.argtypes = [vp, f32p, C.c_int, C.c_int, f32p, f32p, f32p, C.c_int, C.POINTER(C.c_float), f32p, f32p,
+                                        C.POINTER(C.c_longlong)]
         L.or_normals_cache.argtypes = [C.c_int, C.c_int, f32p, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p]
         L.or_normals_compute.argtypes = [C.c_int, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p]
         L.or_convert_depth_u16.argtypes = [vp, C.c_size_t, C.c_float, f32p]
@@ -112,6 +114,16 @@ class OrVolume:
         c = lambda a: np.ascontiguousarray(a, np.float32)
         lib().or_volume_integrate(self.h, c(color), c(depth), c(nx), c(ny), c(nz), c(n_sq_inv), H, W,
                                   c(K).reshape(9), c(R).reshape(9), c(t).reshape(3), int(increase_counter))
+
+    def tracker_system(self, depth, K, R, t, sampling=1):
+        """(E, g[6], H[6,6], count) of one RigidPointOptimizer::optimize_sampled pass at pose (R, t)."""
+        depth = np.ascontiguousarray(depth, np.float32)
+        E, cnt = C.c_float(), C.c_longlong()
+        g, Hm = np.zeros(6, np.float32), np.zeros((6, 6), np.float32)
+        c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+        lib().or_tracker_system(self.h, depth, depth.shape[0], depth.shape[1], c(K), c(R), c(t), int(sampling), C.byref(E), g, Hm,
+                                C.byref(cnt))
+        return E.value, g, Hm, cnt.value
 
     def download(self):
         a = np.zeros((self.N, 8), np.float32)

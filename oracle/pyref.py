@@ -32,6 +32,11 @@ def lib():
         L.ref_vol_create.argtypes = [i32p, C.c_float, f32p, C.c_float, C.c_float, C.c_float]
         L.ref_vol_destroy.argtypes = [C.c_void_p]
         L.ref_se3_from_matrix.argtypes = [f32p, f32p, f32p]
+        L.ref_tracker_system.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, f32p, f32p, C.c_int, C.POINTER(C.c_float), f32p, f32p,
+                                         C.POINTER(C.c_longlong)]
+        L.ref_tracker_update.restype = C.c_float
+        L.ref_tracker_update.argtypes = [f32p, f32p, C.c_float, f32p, f32p, f32p]
+        L.ref_tracker_optimize.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, f32p, f32p, C.c_int, C.c_float, C.c_float, f32p]
         L.ref_vol_integrate.argtypes = [C.c_void_p, f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, C.c_int]
         L.ref_vol_num_voxels.restype = C.c_longlong
         L.ref_vol_num_voxels.argtypes = [C.c_void_p]
@@ -95,6 +100,15 @@ def se3_from_matrix(pose: np.ndarray):
     return R.reshape(3, 3), t
 
 
+def tracker_update(g, H, damping, pose):
+    """xi = damping * H.llt().solve(g); pose <- SE3::exp(-xi) * pose (RigidPointOptimizer.cpp:67-75): (new pose, xi, |xi|^2)."""
+    out = np.zeros(16, np.float32)
+    xi = np.zeros(6, np.float32)
+    c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+    n2 = lib().ref_tracker_update(c(g), c(H), float(damping), c(pose), out, xi)
+    return out.reshape(4, 4), xi, float(n2)
+
+
 class RefVolume:
     def __init__(self, dims, voxel_size, shift, T, zmin=0.5, zmax=3.5):
         self.dims = np.asarray(dims, np.int32)
@@ -121,6 +135,25 @@ class RefVolume:
         c = lambda a: np.ascontiguousarray(a, np.float32)
         lib().ref_vol_integrate(self.h, c(color), c(depth), c(nx), c(ny), c(nz), c(n_sq_inv), H, W,
                                 c(K).reshape(9), c(pose).reshape(16), int(increase_counter))
+
+    def tracker_system(self, depth, K, pose, sampling=1):
+        """One pass of RigidPointOptimizer::optimize_sampled's inner loop at `pose`, by the reference's own Sdf lookups."""
+        depth = np.ascontiguousarray(depth, np.float32)
+        E, cnt = C.c_float(), C.c_longlong()
+        g, Hm = np.zeros(6, np.float32), np.zeros((6, 6), np.float32)
+        c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+        lib().ref_tracker_system(self.h, depth, depth.shape[0], depth.shape[1], c(K), c(pose), int(sampling), C.byref(E), g, Hm,
+                                 C.byref(cnt))
+        return E.value, g, Hm, cnt.value
+
+    def tracker_optimize(self, depth, K, pose, num_iterations=50, conv_threshold=1e-3, damping=1.0):
+        """RigidPointOptimizer(num_iterations, conv_threshold, damping, tSDF).optimize(depth, K) from `pose`: (converged, pose)."""
+        depth = np.ascontiguousarray(depth, np.float32)
+        out = np.zeros(16, np.float32)
+        c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+        conv = lib().ref_tracker_optimize(self.h, depth, depth.shape[0], depth.shape[1], c(K), c(pose), int(num_iterations),
+                                          float(conv_threshold), float(damping), out)
+        return bool(conv), out.reshape(4, 4)
 
     def download(self):
         a = np.zeros((self.N, 8), np.float32)

@@ -50,6 +50,7 @@
 #include "ps_optimizer/Optimizer.h"
 #include "ps_optimizer/PsOptimizer.h"
 #include "ps_optimizer/LedOptimizer.h"
+#include "sdf_tracker/RigidPointOptimizer.h"
 #undef class
 #undef private
 #undef protected
@@ -537,5 +538,79 @@ static std::string g_last_out;
 const char* ref_last_stdout() { g_last_out = g_sink.str(); return g_last_out.c_str(); }
 
 void ref_opt_subsampling(void* h) { Quiet q; static_cast<RefOpt*>(h)->opt->subsampling(); }
+
+
+// ---- rigid depth-to-SDF tracker (sdf_tracker/RigidPointOptimizer.cpp:11-78), SURVEY.md 8f next-2 ---------------------
+// One evaluation of optimize_sampled's inner loop (:38-62) at a given pose, re-played statement by statement against the
+// reference's own Sdf::weights / Sdf::tsdf (VolumetricGradSdf.h:76-93): cost, gradient, approximate Hessian, pixel count.
+void ref_tracker_system(void* h, const float* depth, int H, int W, const float* K9, const float* pose16, int sampling,
+                        float* E_out, float* g6, float* H36, long long* count) {
+    RefVol* v = static_cast<RefVol*>(h);
+    Sdf* tSDF_ = v->sdf;
+    SE3 pose_(M4_from(pose16));
+    const float z_min = tSDF_->z_min_, z_max = tSDF_->z_max_;
+    const float fx = K9[0], fy = K9[4], cx = K9[2], cy = K9[5];
+    const float fx_inv = 1.f / fx;
+    const float fy_inv = 1.f / fy;
+    Mat3f R = pose_.rotationMatrix();
+    Vec3f t = pose_.translation();
+    float E = 0;
+    Vec6f g = Vec6f::Zero();
+    Mat6f Hm = Mat6f::Zero();
+    size_t counter = 0;
+    for (int y = 0; y < H; y += sampling) for (int x = 0; x < W; x += sampling) {
+        const float z = depth[y * W + x];
+        if (z <= z_min || z >= z_max) continue;
+        const float x0 = (float(x) - cx) * fx_inv;
+        const float y0 = (float(y) - cy) * fy_inv;
+        Vec3f point(x0 * z, y0 * z, z);
+        point = R * point + t;
+        float w0 = tSDF_->weights(point);
+        if (w0 > 0) {
+            Vec3f grad_curr;
+            float phi0 = tSDF_->tsdf(point, &grad_curr);
+            E += phi0 * phi0;
+            Vec6f grad_xi;
+            grad_xi << grad_curr, point.cross(grad_curr);
+            g += phi0 * grad_xi;
+            Hm += grad_xi * grad_xi.transpose();
+            ++counter;
+        }
+    }
+    *E_out = E;
+    for (int i = 0; i < 6; ++i) g6[i] = g[i];
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) H36[6 * i + j] = Hm(i, j);
+    *count = (long long)counter;
+}
+
+// xi = damping * H.llt().solve(g); pose <- SE3::exp(-xi) * pose (RigidPointOptimizer.cpp:67-75); returns |xi|^2
+float ref_tracker_update(const float* g6, const float* H36, float damping, const float* pose_in16, float* pose_out16, float* xi6) {
+    Vec6f g; Mat6f Hm;
+    for (int i = 0; i < 6; ++i) g[i] = g6[i];
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) Hm(i, j) = H36[6 * i + j];
+    Vec6f xi = damping * Hm.llt().solve(g);
+    SE3 pose_(M4_from(pose_in16));
+    pose_ = SE3::exp(-xi) * pose_;
+    const Mat4f M = pose_.matrix();
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) pose_out16[4 * r + c] = M(r, c);
+    if (xi6) for (int i = 0; i < 6; ++i) xi6[i] = xi[i];
+    return xi.squaredNorm();
+}
+
+// The reference's own RigidPointOptimizer::optimize (main_ps.cpp:236-243 path) from a given start pose
+int ref_tracker_optimize(void* h, const float* depth, int H, int W, const float* K9, const float* pose_in16, int num_iterations,
+                         float conv_threshold, float damping, float* pose_out16) {
+    Quiet q;
+    RefVol* v = static_cast<RefVol*>(h);
+    RigidPointOptimizer opt(num_iterations, conv_threshold, damping, v->sdf);
+    opt.set_pose(SE3(M4_from(pose_in16)));
+    cv::Mat dep = cv::Mat::wrap(H, W, CV_32FC1, const_cast<float*>(depth));
+    Mat3f K;
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) K(r, c) = K9[3 * r + c];
+    const bool conv = opt.optimize(dep, K);
+    const Mat4f M = opt.pose().matrix();
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) pose_out16[4 * r + c] = M(r, c);
+    return conv ? 1 : 0;
+}
 
 }  // extern "C"

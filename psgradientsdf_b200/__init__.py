@@ -115,6 +115,9 @@ def lib():
         L.psg_normals_compute.argtypes = [vp, f32p, f32p, f32p, f32p]
         L.psg_volume_integrate_raw.argtypes = [vp, vp, vp, vp, C.c_float, f32p, f32p, f32p, C.c_int]
         L.psg_opt_set_keyframes_u8.argtypes = [vp, C.c_int, i32p, f32p, vp, C.c_int, C.c_int]
+        L.psg_tracker_set_depth.argtypes = [vp, f32p, C.c_int, C.c_int]
+        L.psg_tracker_set_depth_u16.argtypes = [vp, vp, C.c_float, C.c_int, C.c_int]
+        L.psg_tracker_system.argtypes = [vp, f32p, f32p, f32p, C.c_int, C.POINTER(C.c_double), vp, vp, C.POINTER(C.c_longlong)]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -219,6 +222,24 @@ class VolumetricGradSdf:
         _check(lib().psg_volume_integrate(self.h, *[_ptr(a) for a in arrs], H, W, c(K).reshape(9), c(R).reshape(9),
                                           c(t).reshape(3), int(self._pending_counter)))
         self._pending_counter = False
+
+    def tracker_set_depth(self, depth=None, depth_u16=None, depth_unit=None):
+        """The frame RigidPointOptimizer::optimize tracks: float depth in metres, or 16-bit depth + unit."""
+        self._ensure()
+        if depth_u16 is not None:
+            d = np.ascontiguousarray(depth_u16, np.uint16)
+            _check(lib().psg_tracker_set_depth_u16(self.h, d.ctypes.data, float(depth_unit), d.shape[0], d.shape[1]))
+        else:
+            d = np.ascontiguousarray(depth, np.float32)
+            _check(lib().psg_tracker_set_depth(self.h, d, d.shape[0], d.shape[1]))
+
+    def tracker_system(self, K, R, t, sampling=1):
+        """One pass of optimize_sampled's inner loop at pose (R, t): (E_sum, g[6], H[6,6], count), sums in float64."""
+        E, cnt = C.c_double(), C.c_longlong()
+        g, Hm = np.zeros(6), np.zeros((6, 6))
+        c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+        _check(lib().psg_tracker_system(self.h, c(K), c(R), c(t), int(sampling), C.byref(E), g.ctypes.data, Hm.ctypes.data, C.byref(cnt)))
+        return E.value, g, Hm, cnt.value
 
     def update_raw(self, color_u8, depth_u16, depth_unit, K, R, t, NEst: "NormalEstimator"):
         """load_color + load_depth + NEst->compute + update() from the loader's raw pixels (psg_volume_integrate_raw)."""

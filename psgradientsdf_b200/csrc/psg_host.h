@@ -19,7 +19,7 @@ enum KernelId {
     KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
     KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
     KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
-    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_COUNT
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_COUNT
 };
 // Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
 struct Prof {
@@ -69,6 +69,9 @@ struct psg_volume {
     psg::DevBuf<unsigned long long> vis;     // nwords * N
     psg::DevBuf<float> frame;                // packed per-pixel fusion inputs (8 floats / pixel)
     psg::DevBuf<float> staging;              // H2D staging for planar inputs / AoS transfers
+    psg::DevBuf<float> track_depth;          // rigid tracker: current frame's depth in metres
+    psg::DevBuf<double> track_partials;
+    int track_H = 0, track_W = 0;
     cudaStream_t stream = nullptr;
     psg::VolView view() const;
 };

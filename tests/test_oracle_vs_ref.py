@@ -4,7 +4,7 @@ Skipped where the reference build is absent."""
 import numpy as np
 import pytest
 
-from tests.common import MODELS, assert_bit_equal, block_order, handoff, make_oracle, make_ref, rel_err, scene
+from tests.common import MODELS, assert_bit_equal, block_order, handoff, make_oracle, make_ref, rel_err, scene, se3
 
 
 def _need_ref():
@@ -90,3 +90,22 @@ def test_subsampling_vs_reference():
     assert ro.voxel_size() == oo.voxel_size()
     er, eo = ro.energy(), oo.energy()
     assert er[0] == eo[0] and er[2] == eo[2]
+
+
+def test_tracker_system_vs_reference():
+    """One pass of RigidPointOptimizer::optimize_sampled's inner loop: the C restatement against the reference's own
+    Sdf::weights / Sdf::tsdf lookups, bit for bit (serial float sums in pixel order on both sides)."""
+    _need_ref()
+    model, G = "SH1", 48
+    sc = scene(model)
+    rv, ro = make_ref(model, G, sc)
+    ov, oo = make_oracle(model, G, sc)
+    for f, pose in ((2, sc.poses_init[2]), (0, sc.poses_gt[0]), (4, sc.poses_init[5])):
+        R, t = se3(pose)
+        for sampling in (1, 2, 3):
+            a = rv.tracker_system(sc.depth[f], sc.K, pose, sampling)
+            b = ov.tracker_system(sc.depth[f], sc.K, R, t, sampling)
+            assert a[3] == b[3] and a[3] > 100, (f, sampling, a[3], b[3])
+            assert a[0] == b[0]
+            assert_bit_equal(a[1], b[1], "tracker gradient")
+            assert_bit_equal(a[2], b[2], "tracker Hessian")

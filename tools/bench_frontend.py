@@ -79,6 +79,30 @@ def main():
 
     raw_ms, raw_k, touched = run(True)
     flt_ms, flt_k, _ = run(False)
+    # rigid tracker: one Gauss-Newton pass over the full-resolution depth image (next-2)
+    vt = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(64, F)); vt.set_zmin(0.5); vt.set_zmax(3.5)
+    for f in range(F):
+        if f:
+            vt.increase_counter()
+        vt.update_raw(c8[f], d16[f], unit, sc.K, Rs[f], ts[f], gn)
+    vt.tracker_set_depth(depth_u16=d16[1], depth_unit=unit)
+    vt.tracker_system(sc.K, Rs[1], ts[1], 1)
+    torch.cuda.synchronize()
+    psg.profile_reset(); psg.profile_enable(True)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        Et, gt, Ht, ct = vt.tracker_system(sc.K, Rs[1], ts[1], 1)
+    trk_ms = 1e3 * (time.perf_counter() - t0) / 20
+    tabt = psg.profile_table(); psg.profile_enable(False)
+    trk_cpu = None
+    if G <= 256:   # the CPU restatement needs the whole volume on the host
+        ov = pyoracle.OrVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5, max(64, F))
+        ov.upload(vt.download())
+        t0 = time.perf_counter()
+        Eo, go_, Ho, co = ov.tracker_system(host[1][1], sc.K, Rs[1], ts[1], 1)
+        trk_cpu = 1e3 * (time.perf_counter() - t0)
+        assert co == ct
+    vt.close()
     peak = 6555.8
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -91,6 +115,8 @@ def main():
            "ms_per_frame_host_float_planes": round(flt_ms, 3), "cpu_front_end_ms_per_frame": round(cpu_ms, 2),
            "h2d_bytes_per_frame_raw": int(H * W * 5), "h2d_bytes_per_frame_float": int(H * W * 32),
            "kernel_us_raw": raw_k, "kernel_us_float": flt_k, "voxels": N, "voxels_touched_by_any_frame": touched,
+           "tracker_pass_ms": round(trk_ms, 4), "tracker_kernel_us": {k: round(1e3 * t / n, 2) for k, (n, t) in tabt.items()},
+           "tracker_pixels_hit": int(ct), "tracker_cpu_pass_ms": None if trk_cpu is None else round(trk_cpu, 2),
            "k_integrate": {"algorithmic_bytes_upper_bound": 72 * touched, "achieved_GBps": round(72 * touched / (fuse_us * 1e-6) / 1e9, 1) if fuse_us else None,
                            "peak_GBps": peak}}
     print(json.dumps(out))
