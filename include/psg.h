@@ -130,6 +130,10 @@ int psg_opt_init(psg_optimizer* opt);
 int psg_opt_num_surface(const psg_optimizer* opt, int* S);
 /* surface_points_ (Optimizer.h:44), ascending lin indices, and the keyframe-indexed visibility of each. */
 int psg_opt_get_surface(psg_optimizer* opt, int* lin, uint64_t* vis_keyframes /* may be NULL */);
+/* The SdfVoxel records (8 floats: dist, grad[3], weight, r, g, b -- Sdfvoxel.h:6-13) of the surface voxels, in the order
+ * of psg_opt_get_surface: what Optimizer::save_pointcloud / extract_pc read through tsdf_[surface_points_[i]]
+ * (OptimizerAux.cpp:456-511) without downloading the whole volume. */
+int psg_opt_get_surface_voxels(psg_optimizer* opt, float* aos8 /* S x 8 */);
 
 int psg_opt_light_len(const psg_optimizer* opt, int* n);  /* SH: F*4 or F*9 ; LED: 3 */
 int psg_opt_get_light(psg_optimizer* opt, float* light);

@@ -118,6 +118,7 @@ def lib():
         L.psg_tracker_set_depth.argtypes = [vp, f32p, C.c_int, C.c_int]
         L.psg_tracker_set_depth_u16.argtypes = [vp, vp, C.c_float, C.c_int, C.c_int]
         L.psg_tracker_system.argtypes = [vp, f32p, f32p, f32p, C.c_int, C.POINTER(C.c_double), vp, vp, C.POINTER(C.c_longlong)]
+        L.psg_opt_get_surface_voxels.argtypes = [vp, f32p]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -378,6 +379,12 @@ class Optimizer:
         s = np.zeros(self.S, np.int32)
         _check(lib().psg_opt_get_surface(self.h, _ptr(s), None))
         return s
+
+    def surface_voxels(self):
+        """(S, 8) SdfVoxel records of the surface voxels, in surface-list order (psg_opt_get_surface_voxels)."""
+        a = np.zeros((self.S, 8), np.float32)
+        _check(lib().psg_opt_get_surface_voxels(self.h, a))
+        return a
 
     def vis_keyframes(self):
         v = np.zeros(self.S, np.uint64)

@@ -512,6 +512,20 @@ int psg_opt_get_surface(psg_optimizer* o, int* lin, uint64_t* vis) {
     PSG_CATCH
 }
 
+int psg_opt_get_surface_voxels(psg_optimizer* o, float* aos8) {
+    PSG_NEED_INIT(o)
+    if (!aos8) { set_error("psg_opt_get_surface_voxels: null argument"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (o->S > 0) {
+        o->vol->staging.alloc((size_t)o->S * 8);
+        launch_gather_voxels(o, o->vol->staging.p);
+        copy_sync(aos8, o->vol->staging.p, (size_t)o->S * 8 * sizeof(float), cudaMemcpyDeviceToHost, o->stream);
+    }
+    return PSG_OK;
+    PSG_CATCH
+}
+
 int psg_opt_light_len(const psg_optimizer* o, int* n) {
     if (!o || !n) { set_error("null argument"); return PSG_ERR_INVALID; }
     *n = o->set.model == PSG_MODEL_LED ? 3 : o->F * o->nb;

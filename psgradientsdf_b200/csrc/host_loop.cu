@@ -83,8 +83,9 @@ bool save_poses(psg_optimizer* o, const std::string& path, const std::vector<std
 // Optimizer::save_pointcloud (OptimizerAux.cpp:456-511): grid-relative position vs * idx - d * g_hat, normal, colour
 bool save_pointcloud(psg_optimizer* o, const std::string& path) {
     psg_volume* v = o->vol;
-    std::vector<float> aos((size_t)v->N * 8);
-    if (psg_volume_download(v, aos.data()) != PSG_OK) return false;
+    // only the surface voxels leave the device (S x 32 B), not the volume (N x 32 B: 4 GiB at 512^3)
+    std::vector<float> rec((size_t)(o->S > 0 ? o->S : 1) * 8);
+    if (psg_opt_get_surface_voxels(o, rec.data()) != PSG_OK) return false;
     std::vector<int> lin((size_t)(o->S > 0 ? o->S : 1));
     if (psg_opt_get_surface(o, lin.data(), nullptr) != PSG_OK) return false;
     const double thr = std::sqrt(3.0) * (double)o->vs;
@@ -92,7 +93,7 @@ bool save_pointcloud(psg_optimizer* o, const std::string& path) {
     size_t count = 0;
     const int W0 = v->dims[0], WH = v->dims[0] * v->dims[1];
     for (int s = 0; s < o->S; ++s) {
-        const float* r = aos.data() + (size_t)lin[s] * 8;
+        const float* r = rec.data() + (size_t)s * 8;
         if (!(std::fabs((double)r[0]) < thr)) continue;
         int rest = lin[s];
         const int k = rest / WH; rest -= k * WH;

@@ -154,6 +154,7 @@ void build_surface(psg_optimizer* o, bool reindex_vis);
 void refresh_records(psg_optimizer* o);      // re-gather rec0..2 from the volume (no allocation)
 SurfView surf_view(psg_optimizer* o);        // refreshes the records first if the volume changed under them
 void launch_upsample(psg_optimizer* o);
+void launch_gather_voxels(psg_optimizer* o, float* out_dev);   // S x 8 floats (SdfVoxel layout) in surface-list order
 
 // ---- sweep.cu
 struct SweepOut {

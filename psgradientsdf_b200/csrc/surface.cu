@@ -372,4 +372,20 @@ void launch_upsample(psg_optimizer* o) {
     (void)nv_store;
 }
 
+// the eight floats of every surface voxel (SdfVoxel layout: dist, grad, weight, r, g, b) in surface-list order, so that the
+// writers (save_pointcloud, extract_pc) need S records from the device instead of the whole volume
+__global__ void __launch_bounds__(256) k_gather_voxels(VolView vol, const int* __restrict__ lin, int S, float* __restrict__ out) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const int l = lin[s];
+    reinterpret_cast<float4*>(out)[2 * (long long)s] = make_float4(vol.dist[l], vol.gx[l], vol.gy[l], vol.gz[l]);
+    reinterpret_cast<float4*>(out)[2 * (long long)s + 1] = make_float4(vol.w[l], vol.r[l], vol.g[l], vol.b[l]);
+}
+
+void launch_gather_voxels(psg_optimizer* o, float* out_dev) {
+    if (o->S == 0) return;
+    { Prof pf(o->stream, KID_AOS); k_gather_voxels<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), o->lin.p, o->S, out_dev); }
+    PSG_LAUNCH_CHECK();
+}
+
 }  // namespace psg

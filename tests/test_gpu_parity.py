@@ -380,3 +380,12 @@ def test_fusion_256():
     assert_bit_equal(a, b, "fused 256^3 volume")
     wo, lo = ov.vis()
     assert np.array_equal(wo, gv.vis())
+
+
+def test_surface_voxels_gather():
+    model, G = "SH1", 40
+    sc = scene(model)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc); go.init_albedo()
+    go.iteration(damping=1.0, normal_reg=True)
+    assert_bit_equal(go.surface_voxels(), gv.download()[go.surface()], "surface voxel records")
