@@ -54,7 +54,8 @@ def parse():
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--ref-keyframes", type=int, default=4, help="keyframes in the reference-arm sample")
+    ap.add_argument("--ref-keyframes", type=int, default=30,
+                    help="keyframes in the reference-arm sample (the reference is O(S^2 F): 30 keyframes at 128^3 = ~3 s per sweep)")
     return ap.parse_args()
 
 
@@ -141,6 +142,9 @@ def reference_sample(a, sc, vs, T, nkey):
     ro = pyref.RefOptimizer(rv, a.model, vs, sc.K, "/tmp/", reg_n=10.0, reg_l=reg_l)
     for f in range(a.frames):
         rv.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
+    # the reference's membership test is a linear scan: a sweep costs ~3 s x (G/128)^4 x nkey/30 on one core;
+    # keep the sample around 20 s on larger grids
+    nkey = max(1, min(nkey, a.frames, int(200.0 / (G / 128.0) ** 4)))
     keys = np.unique(np.linspace(0, a.frames - 1, nkey).round().astype(np.int32))
     ro.set_keyframes(keys, sc.poses_init[keys], sc.color[keys])
     ro.init()

@@ -179,10 +179,9 @@ using namespace psg;
 void psg_optimizer::ensure_host_staging() {
     if (host_staging) return;
     void* p = nullptr;
-    const size_t bytes = (kRedDoubles + kMailDoubles) * sizeof(double) + kMaxFrames * sizeof(FrameParams);
+    const size_t bytes = (kRedDoubles + kMailDoubles) * sizeof(double);
     PSG_CUDA(cudaMallocHost(&p, bytes));
     host_staging = static_cast<double*>(p);
-    host_frames = reinterpret_cast<FrameParams*>(host_staging + kRedDoubles + kMailDoubles);
 }
 
 #define PSG_TRY try {

@@ -120,9 +120,8 @@ struct psg_optimizer {
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
     std::vector<float> lastvb, lastvd;
     int last_n = 0, last_block = -1;
-    // pinned host staging: kRedDoubles + kMailDoubles doubles of reduction results, then the per-keyframe table
+    // pinned host staging: the mailbox (kMailDoubles) followed by kRedDoubles of per-keyframe sums
     double* host_staging = nullptr;
-    psg::FrameParams* host_frames = nullptr;
     void ensure_host_staging();
     double last_energy_sum = 0.0;            // sum of robust losses seen by the last sweep (state before its update)
     long long last_active = 0;
