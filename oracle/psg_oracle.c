@@ -174,6 +174,7 @@ typedef struct { int i, j; float v; } trip;
 
 struct or_opt {
     or_volume* vol;
+    int accum64;   /* diagnostic: carry the long per-keyframe sums of the light / pose blocks in double (or_opt_set_accum64) */
     int model, order, nb, loss;
     float vs, vs_inv, K[9], lambda, lambda_sq, reg_rho, reg_n, reg_l;
     int F, H, W;
@@ -940,6 +941,8 @@ static void update_pose(or_opt* o, const float* d) {
     }
 }
 
+void or_opt_set_accum64(or_opt* o, int on) { o->accum64 = on; }
+
 /* ------------------------------------------------------------------ block step */
 static void H_push(or_opt* o, int i, int j, float v) {
     if (o->Hn >= o->Hcap) { o->Hcap = o->Hcap ? 2 * o->Hcap : 1024; o->Ht = realloc(o->Ht, sizeof(trip) * (size_t)o->Hcap); }
@@ -956,6 +959,10 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
     else n = 6 * F;
     rowacc* H = ra_new(n, which == OR_DIST ? 48 : (which == OR_ALBEDO ? (albedo_reg ? 48 : 2) : (which == OR_LIGHT ? (nb > 6 ? nb : 6) : 6)));
     float* b = calloc(n > 0 ? n : 1, sizeof(float));
+    /* accum64: the same products, summed in double, replace the float sums of the light / pose blocks afterwards */
+    const int bs64 = which == OR_POSE ? 6 : (which == OR_LIGHT ? (o->model == OR_LED ? 1 : nb) : 0);
+    double* H64 = (o->accum64 && bs64) ? calloc((size_t)n * bs64, sizeof(double)) : NULL;
+    double* b64 = (o->accum64 && bs64) ? calloc((size_t)n, sizeof(double)) : NULL;
 
     /* J^T W J and J^T W r accumulated in the reference's row order: frame-major, then surface row, then channel */
     for (int f = 0; f < F; ++f) {
@@ -1004,6 +1011,7 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
                         const float j = refl * x.rho[c];
                         *ra_at(H, c, c) += (j * w[c]) * j;
                         b[c] += (j * w[c]) * r[c];
+                        if (H64) { H64[c] += (double)((j * w[c]) * j); b64[c] += (double)((j * w[c]) * r[c]); }
                     }
                 } else { /* PsOptimizerJa.cpp:132-143 */
                     float sh[9];
@@ -1015,6 +1023,10 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
                             const float jw = J[i] * w[c];
                             for (int k = 0; k < nb; ++k) *ra_at(H, nb * f + i, nb * f + k) += jw * J[k];
                             b[nb * f + i] += jw * r[c];
+                            if (H64) {
+                                for (int k = 0; k < nb; ++k) H64[(size_t)(nb * f + i) * nb + k] += (double)(jw * J[k]);
+                                b64[nb * f + i] += (double)(jw * r[c]);
+                            }
                         }
                     }
                 }
@@ -1025,6 +1037,10 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
                     const float jw = J[6 * c + i] * w[c];
                     for (int k = 0; k < 6; ++k) *ra_at(H, 6 * f + i, 6 * f + k) += jw * J[6 * c + k];
                     b[6 * f + i] += jw * r[c];
+                    if (H64) {
+                        for (int k = 0; k < 6; ++k) H64[(size_t)(6 * f + i) * 6 + k] += (double)(jw * J[6 * c + k]);
+                        b64[6 * f + i] += (double)(jw * r[c]);
+                    }
                 }
             } else {
                 float Jd[4][3], pos[3]; long long nl[3];
@@ -1112,6 +1128,17 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
             b[i] += o->reg_rho * bb[i];
         }
         ra_free(M); free(bb);
+    }
+    if (H64) {
+        for (int i = 0; i < n; ++i) {
+            const int blk0 = (i / bs64) * bs64;
+            for (int k = 0; k < bs64; ++k) {
+                const double hv = H64[(size_t)i * bs64 + k];
+                if (hv != 0.0 || ra_get(H, i, blk0 + k) != 0.f) *ra_at(H, i, blk0 + k) = (float)hv;
+            }
+            b[i] = (float)b64[i];
+        }
+        free(H64); free(b64);
     }
     /* H.diagonal() += damping * H.diagonal(); the SH light block has none (PsOptimizer.cpp:175-203) */
     const int damp = !(which == OR_LIGHT && o->model != OR_LED);

@@ -75,6 +75,9 @@ void or_opt_dist_grad(or_opt*, float* out6 /* S x 6: grad, pos */);
 /* One block step (PsOptimizer.cpp:85-234 / LedOptimizer.cpp:134-275).  Returns system size n.
  * Afterwards: or_opt_block_result() gives b, delta, CG verdict; or_opt_block_H() the matrix as COO triplets
  * (full symmetric pattern). */
+/* Diagnostic switch (not reference behaviour): sum the per-keyframe light / pose normal equations in double instead of
+ * the reference's serial float, to separate summation-order noise from real differences. */
+void or_opt_set_accum64(or_opt*, int on);
 int or_opt_block(or_opt*, int which, int apply, float damping, int albedo_reg, int normal_reg, int laplacian_reg);
 void or_opt_block_result(const or_opt*, float* b, float* delta, int* success, int* iters, float* err);
 long long or_opt_block_H(const or_opt*, int* rows, int* cols, float* vals); /* returns nnz; pass NULLs to query */

@@ -78,6 +78,7 @@ def lib():
         L.or_opt_block_H.restype = C.c_longlong
         L.or_opt_block_H.argtypes = [vp, vp, vp, vp]
         L.or_opt_subsampling.argtypes = [vp]
+        L.or_opt_set_accum64.argtypes = [vp, C.c_int]
         L.or_tracker_system.argtypes = [vp, f32p, C.c_int, C.c_int, f32p, f32p, f32p, C.c_int, C.POINTER(C.c_float), f32p, f32p,
                                         C.POINTER(C.c_longlong)]
         L.or_normals_cache.argtypes = [C.c_int, C.c_int, f32p, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p]
@@ -271,6 +272,10 @@ class OrOptimizer:
         H = sp.coo_matrix((vals, (rows, cols)), shape=(n, n)).tocsc()
         # info follows Eigen's ComputationInfo: 0 = Success
         return dict(H=H, b=b, delta=d, info=0 if ok.value else 2, iters=iters.value, err=err.value)
+
+    def set_accum64(self, on=True):
+        """Diagnostic: light / pose normal equations summed in double (not what the reference does)."""
+        lib().or_opt_set_accum64(self.h, int(on))
 
     def subsampling(self):
         lib().or_opt_subsampling(self.h)

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_ref", "libpsgref.so")
+LIB_PATH = os.environ.get("PSG_REF_LIB") or os.path.join(_HERE, "_ref", "libpsgref.so")   # PSG_REF_LIB: an alternative build (e.g. -DNDEBUG)
 
 _lib = None
 
