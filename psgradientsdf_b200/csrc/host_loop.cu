@@ -147,7 +147,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
     if (!o->inited) { psg::set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
     const bool led = o->set.model == PSG_MODEL_LED;
     const std::string out = save_path ? save_path : "";
-    const bool files = cfg->write_artifacts != 0 && save_path != nullptr;
+    const bool files = cfg->write_artifacts != 0 && save_path != nullptr && o->rank == 0;   // several GPUs: rank 0 writes
     const bool echo = cfg->verbose != 0;
     psg_loop_result R;
     memset(&R, 0, sizeof(R));
