@@ -212,7 +212,7 @@ __device__ __forceinline__ void grid_sum_scalars(const double* block_vals, doubl
 }
 
 template <int MODEL, int MODE>
-__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST || MODE == M_POSE || MODE == M_LIGHT) ? 2 : 4) k_sweep(const __grid_constant__ SweepArgs A, const __grid_constant__ FrameTable T) {
+__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE == M_POSE) ? 3 : 4)) k_sweep(const __grid_constant__ SweepArgs A, const __grid_constant__ FrameTable T) {
     constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
     constexpr bool LED = (MODEL == PSG_MODEL_LED);
     // per-keyframe reduction width (padded to a power of two / multiple of 32 lanes)
