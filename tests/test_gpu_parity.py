@@ -389,3 +389,29 @@ def test_surface_voxels_gather():
     handoff(go, sc); go.init_albedo()
     go.iteration(damping=1.0, normal_reg=True)
     assert_bit_equal(go.surface_voxels(), gv.download()[go.surface()], "surface voxel records")
+
+
+def test_sixty_four_keyframes():
+    """The largest keyframe set (all 64 bits of the visibility word in use; the sort key then is the mask alone) and the
+    65th keyframe being refused."""
+    import psgradientsdf_b200 as psg
+    model, G = "SH1", 32
+    sc = scene(model, F=64, H=60, W=80)
+    ov, oo = make_oracle(model, G, sc)
+    gv, go = make_gpu(model, G, sc)
+    assert_bit_equal(ov.download(), gv.download(), "fused volume")
+    handoff(oo, sc); handoff(go, sc)
+    assert go.F == 64
+    assert_bit_equal(oo.surface(), go.surface(), "surface list")
+    vk = go.vis_keyframes()
+    assert_bit_equal(oo.vis_keyframes(), vk, "keyframe visibility")
+    assert (vk >> np.uint64(63)).any()                     # the top bit is really used
+    oo.init_albedo(); go.init_albedo()
+    for blk in block_order(model):
+        oo.block(blk, apply=True, damping=1.0, normal_reg=True)
+        go.step(blk, damping=1.0, normal_reg=True)
+        eo, eg = oo.energy(), go.energy()
+        assert eo[2] == eg[1], blk
+        assert abs(eo[1] - eg[0]) <= 1e-5 * abs(eo[1]), (blk, eo[1], eg[0])
+    with pytest.raises(psg.PsgError):
+        go.set_keyframes(np.arange(65, dtype=np.int32), np.tile(sc.poses_init[:1], (65, 1, 1)), np.tile(sc.color[:1], (65, 1, 1, 1)))
