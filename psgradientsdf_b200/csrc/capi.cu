@@ -654,14 +654,17 @@ namespace {
 struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; };
 
 // queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
-Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot, bool reg_energies_after = false) {
+Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot, bool reg_energies_after = false,
+                    bool keep_vectors = true) {
     Pending p; p.block = block; p.slot = slot; p.damping = damping;
     const bool led = o->set.model == PSG_MODEL_LED;
     o->last_block = block;
     if (block == PSG_BLOCK_ALBEDO) {
         const size_t n = (size_t)3 * o->S;
         o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
-        launch_albedo(o, damping, o->vecs.p, o->vecs.p + n, slot);
+        // rhs / delta per voxel are only kept for psg_opt_last_vectors (scattered 12-byte writes): the outer loop skips them
+        launch_albedo(o, damping, keep_vectors ? o->vecs.p : nullptr, keep_vectors ? o->vecs.p + n : nullptr, slot);
+        if (!keep_vectors) o->last_block = -1;
     } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
         p.nred = launch_small_block(o, block, slot);
     } else {
@@ -799,7 +802,7 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
         if (!enabled[block]) continue;
         const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) : 0;
         const bool want_reg = block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN));
-        queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg);
+        queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg, /*keep_vectors=*/false);
         const size_t nred = queued[nq].nred;
         ++nq; ++slot;
         last_run = block;
