@@ -409,8 +409,11 @@ def run_ours(a):
            "config": {"workload": workload_name(a), "surface_voxels": S, "active_pairs": A, "keyframes": F,
                       "sweeps_per_step": sweeps_per_step, "energy_after_last_step": E[0] if E else None,
                       "l2": "flushed between steps (256 MiB device write); per-step host timing bracketed by device syncs, summed",
-                      "multi_gpu": (f"work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
-                                    if world > 1 else "single GPU")},
+                      "multi_gpu": ("single GPU" if world == 1 else
+                                    (f"work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
+                                     if go.is_sharded()[0] else
+                                     f"{world} ranks, sweeps replicated (below the sharding threshold of 2e6 visible pairs per rank), "
+                                     "rank 0's sums broadcast"))},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": 1e3 * float(tte.item()) / a.steps,
                    "step": "psg_opt_set_keyframes (pinned host images + poses) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},

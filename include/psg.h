@@ -268,6 +268,12 @@ int psg_tracker_system(psg_volume* vol, const float K[9], const float R[9], cons
 int psg_comm_unique_id(unsigned char id[128]);                                   /* rank 0; send the bytes to the other ranks */
 int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank, int world);
 int psg_opt_comm_destroy(psg_optimizer* opt);
+/* Sharding policy.  Splitting the sweeps adds ~7 collectives per outer iteration; it pays from about two million visible
+ * (voxel, keyframe) pairs per rank (measured on B200: 512^3 x 30 keyframes on 2 GPUs breaks even, 1024^3 x 64 gains up to 8).
+ * 0 (default): shard when the work list has at least that much work per rank, otherwise every rank sweeps everything and
+ * only rank 0's reduced sums are broadcast (same results, no slower than one GPU); 1: always shard; 2: never. */
+int psg_opt_set_shard_policy(psg_optimizer* opt, int policy);
+int psg_opt_is_sharded(const psg_optimizer* opt, int* sharded, long long* visible_pairs);
 /* Which 32-slot blocks of the work list `rank` of `world` sweeps for a surface of S voxels: blocks first, first + stride,
  * ... (count of them); round-robin, so that every rank gets the same mix of the visibility-sorted list. */
 int psg_shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);

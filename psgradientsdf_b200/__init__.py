@@ -119,6 +119,8 @@ def lib():
         L.psg_tracker_set_depth_u16.argtypes = [vp, vp, C.c_float, C.c_int, C.c_int]
         L.psg_tracker_system.argtypes = [vp, f32p, f32p, f32p, C.c_int, C.POINTER(C.c_double), vp, vp, C.POINTER(C.c_longlong)]
         L.psg_opt_get_surface_voxels.argtypes = [vp, f32p]
+        L.psg_opt_set_shard_policy.argtypes = [vp, C.c_int]
+        L.psg_opt_is_sharded.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -435,6 +437,15 @@ class Optimizer:
     def comm_init(self, unique_id: bytes, rank: int, world: int):
         """Join the NCCL communicator: from here on init_albedo / energy / step / alternatingOptimize are collective."""
         _check(lib().psg_opt_comm_init(self.h, C.create_string_buffer(unique_id, 128), int(rank), int(world)))
+
+    def set_shard_policy(self, policy: int):
+        """0 = shard the sweeps when there is enough work per rank, 1 = always, 2 = never (psg_opt_set_shard_policy)."""
+        _check(lib().psg_opt_set_shard_policy(self.h, int(policy)))
+
+    def is_sharded(self):
+        sh, vp_ = C.c_int(), C.c_longlong()
+        _check(lib().psg_opt_is_sharded(self.h, C.byref(sh), C.byref(vp_)))
+        return bool(sh.value), vp_.value
 
     def comm_destroy(self):
         _check(lib().psg_opt_comm_destroy(self.h))

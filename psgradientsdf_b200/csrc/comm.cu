@@ -24,6 +24,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -41,6 +42,7 @@ static bool nccl_load() {
     g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));                        \
     if (!g_nccl.field) { set_error("NCCL symbol %s not found", name); return false; }
     PSG_SYM(GetUniqueId, "ncclGetUniqueId")
+    PSG_SYM(Broadcast, "ncclBroadcast")
     PSG_SYM(CommInitRank, "ncclCommInitRank")
     PSG_SYM(CommDestroy, "ncclCommDestroy")
     PSG_SYM(AllReduce, "ncclAllReduce")
@@ -84,6 +86,24 @@ void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, s
     if (na) PSG_NCCL(g_nccl.AllReduce(a, a, na, ncclDouble, ncclSum, comm, o->stream));
     if (nb) PSG_NCCL(g_nccl.AllReduce(b, b, nb, ncclDouble, ncclSum, comm, o->stream));
     PSG_NCCL(g_nccl.GroupEnd());
+}
+
+void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n) {
+    if (!n) return;
+    Prof pf(o->stream, KID_COMM_ALLREDUCE);
+    PSG_NCCL(g_nccl.Broadcast(a, a, n, ncclDouble, 0, static_cast<ncclComm_t>(o->comm), o->stream));
+}
+
+// Sharding pays only when a rank's share of the sweeps outweighs the collectives it adds (~7 per outer iteration, 20-400 us
+// each): measured on B200 x 2..8, the break-even is around two million visible pairs per rank (512^3 x 30 keyframes on two
+// GPUs).  Below it every rank sweeps the whole list and only rank 0's reduced sums are broadcast, so that all ranks still
+// solve identical small systems and stay in the same state bit for bit.
+constexpr long long kShardMinPairsPerRank = 2000000;
+void update_shard_policy(psg_optimizer* o) {
+    if (o->world <= 1 || !o->comm) { o->sharded = false; return; }
+    if (o->shard_policy == 1) o->sharded = true;
+    else if (o->shard_policy == 2) o->sharded = false;
+    else o->sharded = o->vis_pairs / o->world >= kShardMinPairsPerRank;
 }
 
 // packed index (rank r, local j) -> work-list slot
@@ -182,6 +202,7 @@ int psg_opt_comm_init(psg_optimizer* o, const unsigned char id[128], int rank, i
         ncclComm_t comm = nullptr;
         PSG_NCCL(g_nccl.CommInitRank(&comm, world, u, rank));
         o->comm = comm; o->rank = rank; o->world = world;
+        update_shard_policy(o);
         return PSG_OK;
     } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
 }
@@ -194,7 +215,22 @@ int psg_opt_comm_destroy(psg_optimizer* o) {
         g_nccl.CommDestroy(static_cast<ncclComm_t>(o->comm));
         o->comm = nullptr;
     }
-    o->rank = 0; o->world = 1;
+    o->rank = 0; o->world = 1; o->sharded = false;
+    return PSG_OK;
+}
+
+int psg_opt_set_shard_policy(psg_optimizer* o, int policy) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (policy < 0 || policy > 2) { set_error("psg_opt_set_shard_policy: %d is not 0 (by work), 1 (always) or 2 (never)", policy); return PSG_ERR_INVALID; }
+    o->shard_policy = policy;
+    update_shard_policy(o);
+    return PSG_OK;
+}
+
+int psg_opt_is_sharded(const psg_optimizer* o, int* sharded, long long* visible_pairs) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (sharded) *sharded = o->sharded ? 1 : 0;
+    if (visible_pairs) *visible_pairs = o->vis_pairs;
     return PSG_OK;
 }
 

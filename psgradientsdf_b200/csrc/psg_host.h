@@ -110,6 +110,9 @@ struct psg_optimizer {
     void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
     psg::DevBuf<float> comm_buf;             // all-gather staging: world chunks of packed per-slot results
     int rank = 0, world = 1;
+    bool sharded = false;                    // the sweeps are split over the ranks (else every rank sweeps everything)
+    int shard_policy = 0;                    // 0 = by work per rank, 1 = always, 2 = never
+    long long vis_pairs = 0;                 // visible (surface voxel, keyframe) pairs of the current work list
     int reduce_lo = 1 << 30, reduce_hi = -1; // mail slots whose values are still per-rank partial sums
     size_t reduce_red = 0;                   // ... and how many doubles of o->red
     int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
@@ -163,6 +166,8 @@ struct SweepOut {
 void refresh_frame_table(psg_optimizer* o);
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
+void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n);   // rank 0's values to every rank
+void update_shard_policy(psg_optimizer* o);
 float4* comm_pack_rho(psg_optimizer* o);                         // this rank's send chunk (written by the sweep)
 void comm_allgather_rho(psg_optimizer* o);                       // all-gather + scatter into rec1 / volume planes
 float* comm_pack_stencil(psg_optimizer* o, int* stride);         // this rank's send chunk: 14 planes of `stride` floats

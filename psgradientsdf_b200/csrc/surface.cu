@@ -281,6 +281,15 @@ __global__ void __launch_bounds__(256) k_sort_keys(const unsigned long long* __r
     vals[i] = i;
 }
 
+// number of visible (surface voxel, keyframe) pairs: the size of a sweep, used to decide whether sharding it pays
+__global__ void __launch_bounds__(256) k_count_pairs(const unsigned long long* __restrict__ vis, int n, unsigned long long* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int c = i < n ? __popcll(vis[i]) : 0;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
 void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     psg_volume* vol = o->vol;
     const VolView v = vol->view();
@@ -336,7 +345,20 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
         count_launch(4);
     }
     refresh_records(o);
+    o->vis_pairs = 0;
+    if (o->S > 0) {
+        unsigned long long* cnt = reinterpret_cast<unsigned long long*>(o->sort_keys.p);   // free again after the sort
+        PSG_CUDA(cudaMemsetAsync(cnt, 0, sizeof(*cnt), o->stream));
+        k_count_pairs<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->S, cnt);
+        PSG_LAUNCH_CHECK();
+        count_launch(1);
+        unsigned long long h = 0;
+        PSG_CUDA(cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, o->stream));
+        PSG_CUDA(cudaStreamSynchronize(o->stream));
+        o->vis_pairs = (long long)h;
+    }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
+    update_shard_policy(o);
 }
 
 void launch_upsample(psg_optimizer* o) {

@@ -741,7 +741,7 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
     A.images = o->images.p; A.F = o->F;
-    shard_blocks(o->S, o->rank, o->world, &A.blk_first, &A.blk_stride, &A.blk_count);
+    shard_blocks(o->S, o->sharded ? o->rank : 0, o->sharded ? o->world : 1, &A.blk_first, &A.blk_stride, &A.blk_count);
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
@@ -776,7 +776,7 @@ void refresh_frame_table(psg_optimizer* o) {
 template <int MODE>
 static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
     if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
-    if (o->world > 1 || A.blk_count <= 0)   // ranks without work still take part in the all-reduce
+    if (o->sharded || A.blk_count <= 0)   // ranks without work still take part in the all-reduce
         PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
     if (o->S == 0 || A.blk_count <= 0) return;
     const int grid = A.blk_count;
@@ -815,8 +815,14 @@ const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
     if (o->world > 1 && o->reduce_hi >= o->reduce_lo) {
-        // one all-reduce for everything queued since the last round trip: per-keyframe sums + the scalar slots in flight
-        comm_allreduce_doubles(o, red_dev(o), o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
+        if (o->sharded) {
+            // one all-reduce for everything queued since the last round trip: per-keyframe sums + the scalar slots in flight
+            comm_allreduce_doubles(o, red_dev(o), o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
+        } else {
+            // replicated sweeps: every rank holds complete sums, equal up to the order of the fp64 atomics; rank 0's copy
+            // becomes everybody's, so that the host solves that follow are identical on all ranks
+            comm_broadcast_doubles(o, o->red.p, kMailDoubles + o->reduce_red);
+        }
         o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0;
     }
     PSG_CUDA(cudaMemcpyAsync(h, o->red.p, (kMailDoubles + n) * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
@@ -864,9 +870,9 @@ void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, lo
 
 void sweep_init_albedo(psg_optimizer* o) {
     SweepArgs A = base_args(o);
-    if (o->world > 1) A.pack_rho = comm_pack_rho(o);
+    if (o->sharded) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_INIT_ALBEDO>(o, A, 0, 0);
-    if (o->world > 1) comm_allgather_rho(o);
+    if (o->sharded) comm_allgather_rho(o);
 }
 
 void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
@@ -886,9 +892,9 @@ void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float*
 void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot) {
     SweepArgs A = base_args(o, slot);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
-    if (o->world > 1) A.pack_rho = comm_pack_rho(o);
+    if (o->sharded) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
-    if (o->world > 1) comm_allgather_rho(o);
+    if (o->sharded) comm_allgather_rho(o);
     reduce_over_ranks(o, 0, slot);
 }
 
@@ -944,9 +950,9 @@ void launch_dist_sweep(psg_optimizer* o, int flags, int slot) {
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
-    if (o->world > 1) A.pack_out = comm_pack_stencil(o, &A.pack_stride);
+    if (o->sharded) A.pack_out = comm_pack_stencil(o, &A.pack_stride);
     launch_sweep<M_DIST>(o, A, 0, 0);
-    if (o->world > 1) comm_allgather_stencil(o, o->vecs.p);   // every rank ends with all rows
+    if (o->sharded) comm_allgather_stencil(o, o->vecs.p);   // every rank ends with all rows
     reduce_over_ranks(o, 0, slot);
 }
 

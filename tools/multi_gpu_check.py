@@ -40,6 +40,7 @@ vol, opt = build(local)
 ids = [psg.comm_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(ids, src=0)
 opt.comm_init(ids[0], rank, world)
+opt.set_shard_policy(int(sys.argv[3]) if len(sys.argv) > 3 else 1)   # default: force sharding (the test scene is tiny)
 opt.init_albedo()
 log = [opt.energy()]
 for it in range(2):
