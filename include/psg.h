@@ -144,6 +144,11 @@ int psg_opt_set_poses(psg_optimizer* opt, const float* poses16);
 int psg_opt_get_reg(const psg_optimizer* opt, float reg3[3]);
 int psg_opt_set_reg(psg_optimizer* opt, const float reg3[3]);
 
+/* Overlapped keyframe upload (no counterpart in the reference, whose setImages deep-copies on the host): with on != 0,
+ * psg_opt_set_keyframes(_u8) only queues the copy + conversion on a second stream and returns; psg_opt_init builds the work
+ * list meanwhile and waits for the images before it returns.  The image buffer handed to set_keyframes must stay valid and
+ * unmodified until psg_opt_init has returned (use pinned memory, otherwise the driver stages the copy synchronously). */
+int psg_opt_set_upload_overlap(psg_optimizer* opt, int on);
 /* Tuning knob without a counterpart in the reference: how many warps share the keyframes of one group of 32 surface
  * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
  * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */

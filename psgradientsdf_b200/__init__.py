@@ -121,6 +121,7 @@ def lib():
         L.psg_opt_get_surface_voxels.argtypes = [vp, f32p]
         L.psg_opt_set_shard_policy.argtypes = [vp, C.c_int]
         L.psg_opt_is_sharded.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
+        L.psg_opt_set_upload_overlap.argtypes = [vp, C.c_int]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -355,6 +356,7 @@ class Optimizer:
         img = np.ascontiguousarray(images, np.float32)
         _check(lib().psg_opt_set_keyframes(self.h, F, np.ascontiguousarray(frame_idx, np.int32),
                                            np.ascontiguousarray(poses, np.float32).reshape(-1), _ptr(img), H, W))
+        self._pending_images = img      # with set_upload_overlap the copy may still be running: keep the buffer until init()
 
     def set_keyframes_u8(self, frame_idx, poses, images_u8):
         """setImages with the 8-bit BGR pixels the loader read (psg_opt_set_keyframes_u8)."""
@@ -363,9 +365,11 @@ class Optimizer:
         img = np.ascontiguousarray(images_u8, np.uint8)
         _check(lib().psg_opt_set_keyframes_u8(self.h, F, np.ascontiguousarray(frame_idx, np.int32),
                                               np.ascontiguousarray(poses, np.float32).reshape(-1), img.ctypes.data, H, W))
+        self._pending_images = img
 
     def init(self):
         _check(lib().psg_opt_init(self.h))
+        self._pending_images = None
 
     @property
     def S(self):
@@ -421,6 +425,12 @@ class Optimizer:
 
     def init_albedo(self):
         _check(lib().psg_opt_init_albedo(self.h))
+
+    def set_upload_overlap(self, on: bool):
+        """Queue keyframe uploads behind psg_opt_init's work-list build; the arrays given to set_keyframes* must then stay alive
+        (and pinned, to actually overlap) until init() has returned."""
+        _check(lib().psg_opt_set_upload_overlap(self.h, int(on)))
+        self._overlap = bool(on)
 
     def set_pcg_mode(self, mode: int):
         _check(lib().psg_opt_set_pcg_mode(self.h, int(mode)))

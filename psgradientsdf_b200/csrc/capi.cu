@@ -176,6 +176,18 @@ __global__ void __launch_bounds__(256) k_pad_images(const float* __restrict__ sr
 
 using namespace psg;
 
+static void ensure_upload_stream(psg_optimizer* o) {
+    if (!o->upload_stream) PSG_CUDA(cudaStreamCreateWithFlags(&o->upload_stream, cudaStreamNonBlocking));
+    if (!o->upload_done) PSG_CUDA(cudaEventCreateWithFlags(&o->upload_done, cudaEventDisableTiming));
+}
+// the keyframe texels are complete on the device and the caller's buffer is free again
+static void finish_upload(psg_optimizer* o) {
+    if (!o->upload_pending) return;
+    PSG_CUDA(cudaStreamWaitEvent(o->stream, o->upload_done, 0));
+    PSG_CUDA(cudaEventSynchronize(o->upload_done));
+    o->upload_pending = false;
+}
+
 void psg_optimizer::ensure_host_staging() {
     if (host_staging) return;
     void* p = nullptr;
@@ -389,6 +401,9 @@ int psg_opt_destroy(psg_optimizer* o) {
     if (!o) return PSG_OK;
     cudaSetDevice(o->vol->device);
     psg_opt_comm_destroy(o);
+    if (o->upload_stream) { cudaStreamSynchronize(o->upload_stream); cudaStreamDestroy(o->upload_stream); }
+    if (o->upload_done) cudaEventDestroy(o->upload_done);
+    o->upload_staging.release();
     o->images.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
@@ -412,6 +427,21 @@ int psg_opt_set_keyframes(psg_optimizer* o, int F, const int* frame_idx, const f
     o->poses.assign(poses16, poses16 + 16 * (size_t)F);
     const long long npix = (long long)F * H * W;
     o->images.alloc((size_t)(npix > 0 ? npix : 1));
+    if (o->upload_overlap && npix > 0) {
+        // all keyframes in one copy + one conversion on the upload stream; psg_opt_init waits for it after it has built the
+        // work list (which does not need the images)
+        ensure_upload_stream(o);
+        o->upload_staging.alloc((size_t)npix * 3);
+        PSG_CUDA(cudaMemcpyAsync(o->upload_staging.p, images, (size_t)npix * 3 * sizeof(float), cudaMemcpyHostToDevice, o->upload_stream));
+        { Prof pf(o->upload_stream, KID_PAD_IMAGES);
+          k_pad_images<<<(unsigned)((npix + 255) / 256), 256, 0, o->upload_stream>>>(o->upload_staging.p, o->images.p, npix); }
+        PSG_LAUNCH_CHECK();
+        PSG_CUDA(cudaEventRecord(o->upload_done, o->upload_stream));
+        o->upload_pending = true;
+        o->frames_dirty = true;
+        o->inited = false;
+        return PSG_OK;
+    }
     // stage one keyframe at a time through the volume's staging buffer
     const long long per = (long long)H * W;
     o->vol->staging.alloc((size_t)per * 3);
@@ -443,6 +473,18 @@ int psg_opt_set_keyframes_u8(psg_optimizer* o, int F, const int* frame_idx, cons
     o->poses.assign(poses16, poses16 + 16 * (size_t)F);
     const long long npix = (long long)F * H * W;
     o->images.alloc((size_t)(npix > 0 ? npix : 1));
+    if (o->upload_overlap && npix > 0) {
+        ensure_upload_stream(o);
+        o->upload_staging.alloc((size_t)(npix * 3 + 3) / 4);
+        unsigned char* raw = reinterpret_cast<unsigned char*>(o->upload_staging.p);
+        PSG_CUDA(cudaMemcpyAsync(raw, images_bgr_u8, (size_t)npix * 3, cudaMemcpyHostToDevice, o->upload_stream));
+        launch_texels_u8(o->upload_stream, raw, o->images.p, npix);
+        PSG_CUDA(cudaEventRecord(o->upload_done, o->upload_stream));
+        o->upload_pending = true;
+        o->frames_dirty = true;
+        o->inited = false;
+        return PSG_OK;
+    }
     if (npix > 0) {
         // the 8-bit pixels of all keyframes in one copy (3 B / pixel instead of 12), converted on the device
         o->vol->staging.alloc((size_t)(npix * 3 + 3) / 4);
@@ -478,6 +520,7 @@ int psg_opt_init(psg_optimizer* o) {
     }
     o->frames_dirty = true;
     build_surface(o, true);
+    finish_upload(o);   // overlapped keyframe upload: the images are needed from here on
     o->inited = true;
     if (led && o->S > 0) {
         // LedOptimizer::computeLightIntensive (LedOptimizer.cpp:76-112)
@@ -570,6 +613,12 @@ int psg_opt_set_sweep_split(psg_optimizer* o, int warps) {
         return PSG_ERR_INVALID;
     }
     o->sweep_split = warps;
+    return PSG_OK;
+}
+
+int psg_opt_set_upload_overlap(psg_optimizer* o, int on) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    o->upload_overlap = on != 0;
     return PSG_OK;
 }
 

@@ -89,6 +89,12 @@ struct psg_optimizer {
     psg::DevBuf<float4> images;              // F x H x W texels (b, g, r, 0)
     psg::FrameTable frame_table;             // per-keyframe R, t, light (host copy; passed to the sweeps as a kernel parameter)
     bool frames_dirty = true;
+    // overlapped keyframe upload (psg_opt_set_upload_overlap): copy + conversion on their own stream while psg_opt_init
+    // builds the work list; the caller's image buffer must then stay valid until psg_opt_init returns
+    bool upload_overlap = false, upload_pending = false;
+    cudaStream_t upload_stream = nullptr;
+    cudaEvent_t upload_done = nullptr;
+    psg::DevBuf<float> upload_staging;
     bool inited = false;
     // surface work list
     int S = 0;

@@ -89,3 +89,23 @@ def test_u8_keyframes_equal_float_keyframes():
         out.append((go.energy(), gv.download()))
     assert out[0][0] == out[1][0]
     assert np.array_equal(out[0][1].view(np.uint32), out[1][1].view(np.uint32))
+
+
+def test_overlapped_upload_gives_the_same_state():
+    """psg_opt_set_upload_overlap: keyframes copied on a second stream while init builds the work list."""
+    sc = scene("LED")            # the LED init sweeps the images inside psg_opt_init: the wait must come before it
+    c8 = np.round(sc.color * 255.0).astype(np.uint8)
+    out = []
+    for overlap in (False, True):
+        for use_u8 in (False, True):
+            gv, go = make_gpu("LED", 40, sc)
+            go.set_upload_overlap(overlap)
+            fi = np.arange(sc.color.shape[0], dtype=np.int32)
+            if use_u8:
+                go.set_keyframes_u8(fi, sc.poses_init, c8)
+            else:
+                go.set_keyframes(fi, sc.poses_init, (c8.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32))
+            go.init(); go.init_albedo()
+            out.append((go.energy(), go.light().copy()))
+    for o in out[1:]:
+        assert o[0] == out[0][0] and np.array_equal(o[1], out[0][1])
