@@ -69,6 +69,8 @@ struct psg_volume {
     psg::DevBuf<unsigned long long> vis;     // nwords * N
     psg::DevBuf<float> frame;                // packed per-pixel fusion inputs (8 floats / pixel)
     psg::DevBuf<float> staging;              // H2D staging for planar inputs / AoS transfers
+    psg::DevBuf<int> brick_list;             // fusion: bricks of the current frame that survive the cull, then their count
+    psg::DevBuf<float> tiles;                // fusion: largest valid depth per 8 x 8 pixel tile of the current frame
     psg::DevBuf<float> track_depth;          // rigid tracker: current frame's depth in metres
     psg::DevBuf<double> track_partials;
     int track_H = 0, track_W = 0;

@@ -72,3 +72,40 @@ def test_demo_frames_fuse_and_optimize_like_the_restatement():
         assert eo[2] == eg[1], blk
         assert abs(eo[1] - eg[0]) <= 5e-6 * abs(eo[1]), (blk, eo[1], eg[0])
         assert abs(ef[1] - eg[0]) <= 1e-3 * abs(ef[1]), (blk, ef[1], eg[0])
+
+
+def test_demo_frames_fuse_identically_through_the_brick_cull():
+    """256^3 (voxel size 0.002) switches fusion to the culled path: tiles of valid depth, brick test, brick list."""
+    if not os.path.exists(os.path.join(DATA, "depth000001.png")):
+        pytest.skip("demo data not staged (tools/run_sokrates.py --stage)")
+    cv2 = pytest.importorskip("cv2")
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import run_sokrates as rs
+
+    import psgradientsdf_b200 as psg
+    from oracle import pyoracle
+    F, G = 3, 256
+    K = np.loadtxt(os.path.join(DATA, "intrinsics.txt"), dtype=np.float32)[:3, :3].copy()
+    poses = rs.load_poses(os.path.join(DATA, "pose.txt"))
+    unit, vs = np.float32(1.0 / 1000), np.float32(0.002)
+    T = np.float32(5.0) * vs
+    d16 = [cv2.imread(os.path.join(DATA, f"depth{i:06d}.png"), cv2.IMREAD_ANYDEPTH | cv2.IMREAD_ANYCOLOR) for i in (1, 12, 23)]
+    c8 = [cv2.imread(os.path.join(DATA, f"color{i:06d}.png")) for i in (1, 12, 23)]
+    pp = [poses[0], poses[11], poses[22]]
+    H, W = d16[0].shape
+    centroid = rs.compute_centroid(K, (d16[0].astype(np.float32) * unit).astype(np.float32), pp[0])
+    gn, on = psg.NormalEstimator(W, H, K, 11), pyoracle.OrNormalEstimator(W, H, K, 11)
+    gv = psg.VolumetricGradSdf([G] * 3, vs, centroid, T, 64); gv.set_zmin(0.5); gv.set_zmax(3.5)
+    ov = pyoracle.OrVolume([G] * 3, vs, centroid, T, 0.5, 3.5, 64)
+    for f in range(F):
+        R, t = rs.se3_parts(pp[f])
+        depth = pyoracle.convert_depth_u16(d16[f], unit)
+        nx, ny, nz = on.compute(depth)
+        if f:
+            gv.increase_counter()
+        gv.update_raw(c8[f], d16[f], unit, K, R, t, gn)
+        ov.integrate(pyoracle.convert_color_u8(c8[f]), depth, nx, ny, nz, on.n_sq_inv, K, R, t, f > 0)
+    a, b = ov.download(), gv.download()
+    assert np.count_nonzero(a[:, 4]) > 1000000
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), "fused volume"
+    assert np.array_equal(ov.vis()[0], gv.vis())
