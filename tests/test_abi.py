@@ -61,3 +61,29 @@ def test_product_does_not_import_the_oracle():
                 if re.search(r"(from|import)\s+oracle|oracle/|psg_oracle|libpsgref|pyref|pyoracle", src):
                     offenders.append(os.path.join(dirpath, fn))
     assert not offenders, f"product sources reference the oracle: {offenders}"
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/psg.h is the drop-in boundary for a C / C++ host: it must compile as C99 without any CUDA or C++ header, and
+    a C program must link against the library."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        import pytest
+        pytest.skip("no gcc")
+    src = tmp_path / "t.c"
+    src.write_text('#include "psg.h"\n#include <stdio.h>\n'
+                   'int main(void) { psg_iteration_config c; psg_settings s; int n = -1; (void)c; (void)s;\n'
+                   '  if (psg_shard_blocks(100, 1, 2, &n, &n, &n) != 0) return 2;\n'
+                   '  if (psg_volume_create(0, 0, 0.f, 0, 0.f, 0.f, 0.f, 1, 0) == 0) return 3;   /* null arguments are refused */\n'
+                   '  printf("%s\\n", psg_last_error()); return 0; }\n')
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    inc = os.path.join(ROOT, "include")
+    subprocess.check_call([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", str(src)])
+    libdir = os.path.join(ROOT, "psgradientsdf_b200")
+    exe = tmp_path / "t"
+    subprocess.check_call([gcc, "-std=c99", "-I", inc, str(src), "-o", str(exe), "-L", libdir, "-lpsg_b200", f"-Wl,-rpath,{libdir}"])
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "null" in r.stdout
