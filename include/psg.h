@@ -262,6 +262,15 @@ int psg_tracker_set_depth_u16(psg_volume* vol, const unsigned short* depth_u16, 
 int psg_tracker_system(psg_volume* vol, const float K[9], const float R[9], const float t[3], int sampling, double* E_sum,
                        double g6[6], double H36[36], long long* count);
 
+/* RigidPointOptimizer(num_iterations, conv_threshold, damping, tSDF)::optimize_sampled(depth, K, sampling) from pose_in
+ * (row-major 4 x 4, camera to world) on the frame given to psg_tracker_set_depth: Gauss-Newton with the device sums above,
+ * xi = damping * H.llt().solve(g), converged when |xi|^2 < conv_threshold^2, else pose <- SE3::exp(-xi) * pose
+ * (RigidPointOptimizer.cpp:26-77).  The 6 x 6 solve and the SE(3) update are float host code written after Eigen's LLT and
+ * Sophus' SE3::exp; against the reference they agree to rounding, not bit for bit. */
+typedef struct { int num_iterations; float conv_threshold; float damping; int sampling; } psg_tracker_config;
+int psg_tracker_optimize(psg_volume* vol, const float K[9], const float pose_in[16], const psg_tracker_config* cfg,
+                         float pose_out[16], int* converged, int* iterations);
+
 /* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
  * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
  * every rank); the (surface voxel, keyframe) sweeps are split by round-robin 32-slot blocks of the visibility-sorted work list.

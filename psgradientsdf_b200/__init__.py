@@ -50,6 +50,10 @@ class IterationInfo(C.Structure):
                 ("n_active_end", C.c_longlong)]
 
 
+class TrackerConfig(C.Structure):
+    _fields_ = [("num_iterations", C.c_int), ("conv_threshold", C.c_float), ("damping", C.c_float), ("sampling", C.c_int)]
+
+
 class LoopConfig(C.Structure):
     _fields_ = [("light", C.c_int), ("albedo", C.c_int), ("distance", C.c_int), ("pose", C.c_int),
                 ("max_it", C.c_int), ("conv_threshold", C.c_float), ("damping", C.c_float), ("upsample", C.c_int),
@@ -122,6 +126,7 @@ def lib():
         L.psg_opt_set_shard_policy.argtypes = [vp, C.c_int]
         L.psg_opt_is_sharded.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
         L.psg_opt_set_upload_overlap.argtypes = [vp, C.c_int]
+        L.psg_tracker_optimize.argtypes = [vp, f32p, f32p, C.POINTER(TrackerConfig), f32p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -244,6 +249,15 @@ class VolumetricGradSdf:
         c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
         _check(lib().psg_tracker_system(self.h, c(K), c(R), c(t), int(sampling), C.byref(E), g.ctypes.data, Hm.ctypes.data, C.byref(cnt)))
         return E.value, g, Hm, cnt.value
+
+    def tracker_optimize(self, K, pose, num_iterations=50, conv_threshold=1e-3, damping=1.0, sampling=1):
+        """RigidPointOptimizer::optimize on the frame given to tracker_set_depth: (converged, iterations, pose 4x4)."""
+        cfg = TrackerConfig(int(num_iterations), float(conv_threshold), float(damping), int(sampling))
+        out = np.zeros(16, np.float32)
+        conv, it = C.c_int(), C.c_int()
+        c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
+        _check(lib().psg_tracker_optimize(self.h, c(K), c(pose), C.byref(cfg), out, C.byref(conv), C.byref(it)))
+        return bool(conv.value), it.value, out.reshape(4, 4)
 
     def update_raw(self, color_u8, depth_u16, depth_unit, K, R, t, NEst: "NormalEstimator"):
         """load_color + load_depth + NEst->compute + update() from the loader's raw pixels (psg_volume_integrate_raw)."""

@@ -10,6 +10,8 @@
 // Per-pixel arithmetic is the reference's float arithmetic operation by operation, so which pixels count (voxel index,
 // weight test) is decided identically; the sums are formed in double (the reference: one serial float each), reduced
 // warp -> block -> grid in a fixed order, hence reproducible.
+#include <cmath>
+
 #include "psg_host.h"
 
 namespace psg {
@@ -172,6 +174,169 @@ int psg_tracker_system(psg_volume* v, const float K[9], const float R[9], const 
         if (count) *count = (long long)(h[28] + 0.5);
         return PSG_OK;
     } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+
+// ---- host side of RigidPointOptimizer::optimize_sampled (RigidPointOptimizer.cpp:26-77): float 6 x 6 Cholesky solve and the
+// SE(3) update pose <- exp(-xi) * pose, written after Eigen's LLT and Sophus' SE3 / SO3 (third/Sophus/sophus/se3.hpp:761-782,
+// so3.hpp:325-339, 583-619).  The pose is carried as unit quaternion + translation like Sophus does.
+namespace {
+
+struct Se3f { float q[4]; /* x y z w */ float t[3]; };
+
+// Eigen::Quaternion<float>(Matrix3f)
+void quat_from_rot(const float* R /* row-major */, float q[4]) {
+    auto m = [&](int r, int c) { return R[3 * r + c]; };
+    float tr = m(0, 0) + m(1, 1) + m(2, 2);
+    if (tr > 0.f) {
+        tr = std::sqrt(tr + 1.f);
+        q[3] = 0.5f * tr;
+        tr = 0.5f / tr;
+        q[0] = (m(2, 1) - m(1, 2)) * tr; q[1] = (m(0, 2) - m(2, 0)) * tr; q[2] = (m(1, 0) - m(0, 1)) * tr;
+    } else {
+        int i = 0;
+        if (m(1, 1) > m(0, 0)) i = 1;
+        if (m(2, 2) > m(i, i)) i = 2;
+        const int j = (i + 1) % 3, k = (j + 1) % 3;
+        tr = std::sqrt(m(i, i) - m(j, j) - m(k, k) + 1.f);
+        q[i] = 0.5f * tr;
+        tr = 0.5f / tr;
+        q[3] = (m(k, j) - m(j, k)) * tr; q[j] = (m(j, i) + m(i, j)) * tr; q[k] = (m(k, i) + m(i, k)) * tr;
+    }
+}
+
+// Eigen::QuaternionBase::toRotationMatrix
+void rot_from_quat(const float q[4], float* R /* row-major */) {
+    const float tx = 2.f * q[0], ty = 2.f * q[1], tz = 2.f * q[2];
+    const float twx = tx * q[3], twy = ty * q[3], twz = tz * q[3], txx = tx * q[0], txy = ty * q[0], txz = tz * q[0];
+    const float tyy = ty * q[1], tyz = tz * q[1], tzz = tz * q[2];
+    R[0] = 1.f - (tyy + tzz); R[1] = txy - twz; R[2] = txz + twy;
+    R[3] = txy + twz; R[4] = 1.f - (txx + tzz); R[5] = tyz - twx;
+    R[6] = txz - twy; R[7] = tyz + twx; R[8] = 1.f - (txx + tyy);
+}
+
+inline float sum3h(float a, float b, float c) { return a + (b + c); }
+
+// xi = H.llt().solve(g) for a 6 x 6 float system; false if H is not positive definite
+bool llt_solve6(const float* H /* row-major, symmetric */, const float* g, float* x) {
+    float L[36];
+    for (int i = 0; i < 36; ++i) L[i] = H[i];
+    for (int k = 0; k < 6; ++k) {
+        float d = L[6 * k + k];
+        for (int j = 0; j < k; ++j) d -= L[6 * k + j] * L[6 * k + j];
+        if (!(d > 0.f)) return false;
+        d = std::sqrt(d);
+        L[6 * k + k] = d;
+        for (int i = k + 1; i < 6; ++i) {
+            float v = L[6 * i + k];
+            for (int j = 0; j < k; ++j) v -= L[6 * i + j] * L[6 * k + j];
+            L[6 * i + k] = v / d;
+        }
+    }
+    float y[6];
+    for (int i = 0; i < 6; ++i) {
+        float v = g[i];
+        for (int j = 0; j < i; ++j) v -= L[6 * i + j] * y[j];
+        y[i] = v / L[6 * i + i];
+    }
+    for (int i = 5; i >= 0; --i) {
+        float v = y[i];
+        for (int j = i + 1; j < 6; ++j) v -= L[6 * j + i] * x[j];
+        x[i] = v / L[6 * i + i];
+    }
+    return true;
+}
+
+// pose <- SE3::exp(a) * pose
+void se3_exp_left(const float a[6], Se3f& P) {
+    const float w[3] = { a[3], a[4], a[5] };
+    const float theta_sq = sum3h(w[0] * w[0], w[1] * w[1], w[2] * w[2]);
+    const float eps = 1e-10f;   // Sophus::Constants<float>::epsilon()
+    float theta, imag, real;
+    if (theta_sq < eps * eps) {
+        theta = 0.f;
+        const float t4 = theta_sq * theta_sq;
+        imag = 0.5f - (float)(1.0 / 48.0) * theta_sq + (float)(1.0 / 3840.0) * t4;
+        real = 1.f - (float)(1.0 / 8.0) * theta_sq + (float)(1.0 / 384.0) * t4;
+    } else {
+        theta = std::sqrt(theta_sq);
+        const float half = 0.5f * theta;
+        imag = std::sin(half) / theta;
+        real = std::cos(half);
+    }
+    const float qe[4] = { imag * w[0], imag * w[1], imag * w[2], real };
+    // V (se3.hpp:768-780)
+    const float Om[9] = { 0.f, -w[2], w[1], w[2], 0.f, -w[0], -w[1], w[0], 0.f };
+    float V[9];
+    if (theta < eps) {
+        rot_from_quat(qe, V);
+    } else {
+        float Om2[9];
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) Om2[3 * r + c] = sum3h(Om[3 * r] * Om[c], Om[3 * r + 1] * Om[3 + c], Om[3 * r + 2] * Om[6 + c]);
+        const float th2 = theta * theta;
+        const float c1 = (1.f - std::cos(theta)) / th2, c2 = (theta - std::sin(theta)) / (th2 * theta);
+        for (int i = 0; i < 9; ++i) V[i] = ((i % 4 == 0 ? 1.f : 0.f) + c1 * Om[i]) + c2 * Om2[i];
+    }
+    const float te[3] = { sum3h(V[0] * a[0], V[1] * a[1], V[2] * a[2]), sum3h(V[3] * a[0], V[4] * a[1], V[5] * a[2]),
+                          sum3h(V[6] * a[0], V[7] * a[1], V[8] * a[2]) };
+    // translation: te + qe * t (Eigen's _transformVector)
+    {
+        const float* v = P.t;
+        float uv[3] = { qe[1] * v[2] - qe[2] * v[1], qe[2] * v[0] - qe[0] * v[2], qe[0] * v[1] - qe[1] * v[0] };
+        for (int i = 0; i < 3; ++i) uv[i] += uv[i];
+        const float c[3] = { qe[1] * uv[2] - qe[2] * uv[1], qe[2] * uv[0] - qe[0] * uv[2], qe[0] * uv[1] - qe[1] * uv[0] };
+        float rt[3];
+        for (int i = 0; i < 3; ++i) rt[i] = v[i] + qe[3] * uv[i] + c[i];
+        for (int i = 0; i < 3; ++i) P.t[i] = te[i] + rt[i];
+    }
+    // rotation: quaternion product (so3.hpp:334-338), then SO3(quaternion) normalises
+    const float* b = P.q;
+    float r[4];
+    r[3] = qe[3] * b[3] - qe[0] * b[0] - qe[1] * b[1] - qe[2] * b[2];
+    r[0] = qe[3] * b[0] + qe[0] * b[3] + qe[1] * b[2] - qe[2] * b[1];
+    r[1] = qe[3] * b[1] + qe[1] * b[3] + qe[2] * b[0] - qe[0] * b[2];
+    r[2] = qe[3] * b[2] + qe[2] * b[3] + qe[0] * b[1] - qe[1] * b[0];
+    const float len = std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2] + r[3] * r[3]);
+    for (int i = 0; i < 4; ++i) P.q[i] = r[i] / len;
+}
+
+}  // namespace
+
+int psg_tracker_optimize(psg_volume* v, const float K[9], const float pose_in[16], const psg_tracker_config* cfg, float pose_out[16],
+                         int* converged, int* iterations) {
+    if (!v || !K || !pose_in || !cfg || !pose_out) { set_error("psg_tracker_optimize: null argument"); return PSG_ERR_INVALID; }
+    if (cfg->num_iterations < 0 || cfg->sampling < 1) { set_error("psg_tracker_optimize: bad configuration"); return PSG_ERR_INVALID; }
+    Se3f P;
+    float R[9];
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) R[3 * r + c] = pose_in[4 * r + c]; P.t[r] = pose_in[4 * r + 3]; }
+    quat_from_rot(R, P.q);
+    int conv = 0, it = 0;
+    const float thr_sq = cfg->conv_threshold * cfg->conv_threshold;
+    for (; it < cfg->num_iterations; ++it) {
+        rot_from_quat(P.q, R);
+        double E = 0.0, g6[6], H36[36];
+        long long count = 0;
+        const int st = psg_tracker_system(v, K, R, P.t, cfg->sampling, &E, g6, H36, &count);
+        if (st != PSG_OK) return st;
+        if (count == 0) break;                                   // "return false" (RigidPointOptimizer.cpp:64-66)
+        float Hf[36], gf[6], xi[6];
+        for (int i = 0; i < 36; ++i) Hf[i] = (float)H36[i];
+        for (int i = 0; i < 6; ++i) gf[i] = (float)g6[i];
+        if (!llt_solve6(Hf, gf, xi)) break;
+        float n2 = 0.f;
+        for (int i = 0; i < 6; ++i) { xi[i] = cfg->damping * xi[i]; }
+        for (int i = 0; i < 6; ++i) n2 += xi[i] * xi[i];
+        if (n2 < thr_sq) { conv = 1; break; }
+        float neg[6];
+        for (int i = 0; i < 6; ++i) neg[i] = -xi[i];
+        se3_exp_left(neg, P);
+    }
+    rot_from_quat(P.q, R);
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) pose_out[4 * r + c] = R[3 * r + c]; pose_out[4 * r + 3] = P.t[r]; }
+    pose_out[12] = 0.f; pose_out[13] = 0.f; pose_out[14] = 0.f; pose_out[15] = 1.f;
+    if (converged) *converged = conv;
+    if (iterations) *iterations = it;
+    return PSG_OK;
 }
 
 }  // extern "C"

@@ -53,3 +53,24 @@ def test_tracker_iterations_vs_reference():
         P, xi, n2 = pyref.tracker_update(g.astype(np.float32), H.astype(np.float32), 1.0, P)
     assert not conv
     assert np.abs(P - P_ref).max() < 2e-5, np.abs(P - P_ref).max()
+
+
+def test_tracker_optimize_vs_reference():
+    """The whole Gauss-Newton loop (device sums + this library's float LLT / SE(3) update) against the reference's optimize()."""
+    from oracle import pyref
+    if not pyref.available():
+        pytest.skip("oracle/_ref not built")
+    model, G = "SH1", 48
+    sc = scene(model)
+    rv, ro = make_ref(model, G, sc)
+    gv, go = make_gpu(model, G, sc)
+    for f, iters in ((2, 1), (2, 3), (4, 2)):
+        gv.tracker_set_depth(sc.depth[f])
+        conv_r, P_ref = rv.tracker_optimize(sc.depth[f], sc.K, sc.poses_init[f], num_iterations=iters, conv_threshold=1e-12, damping=1.0)
+        conv_g, it_g, P = gv.tracker_optimize(sc.K, sc.poses_init[f], num_iterations=iters, conv_threshold=1e-12, damping=1.0)
+        assert conv_g == conv_r and it_g == iters
+        assert np.abs(P - P_ref).max() < 3e-5 * iters, (f, iters, np.abs(P - P_ref).max())
+    # a converged call: start at the fixed point of a previous run with a loose threshold
+    conv_r, P_ref = rv.tracker_optimize(sc.depth[4], sc.K, sc.poses_gt[4], num_iterations=5, conv_threshold=10.0, damping=1.0)
+    conv_g, it_g, P = gv.tracker_optimize(sc.K, sc.poses_gt[4], num_iterations=5, conv_threshold=10.0, damping=1.0)
+    assert conv_r and conv_g and it_g == 0 and np.abs(P - P_ref).max() < 1e-6
