@@ -249,6 +249,20 @@ int psg_volume_integrate_raw(psg_volume* vol, psg_normals* ne, const unsigned ch
 int psg_opt_set_keyframes_u8(psg_optimizer* opt, int F, const int* frame_idx, const float* poses4x4, const unsigned char* images_bgr_u8,
                              int H, int W);
 
+/* ------------------------------------------------------------------ keyframe gate and volume placement
+ * sharpDetector's measure, modifiedLaplacian(img) (cpp/include/ps_optimizer/SharpDetector.h:12-37): mean over the blue channel
+ * of |G_col(M_row(x))| + |M_col(G_row(x))|, M = (-1, 2, -1), G = (0.25, 0.5, 0.25), reflect-101 border -- what
+ * cv::sepFilter2D + cv::mean(FM).val[0] return for the CV_32FC3 colour image (bit-equal to OpenCV 4.13 in the fixture).
+ * The image has the size the estimator was created with; the caller compares with its sharpness threshold. */
+int psg_normals_sharpness(psg_normals* ne, const float* color_bgr, float* measure);
+int psg_normals_sharpness_u8(psg_normals* ne, const unsigned char* color_bgr_u8, float* measure);
+/* compute_centroid(K, depth, Trans) (voxel_ps/src/main_ps.cpp:346-375): where main() centres the volume.  Host code: the
+ * serial float sum is part of the result. */
+int psg_compute_centroid(const float K[9], const float* depth, int H, int W, const float pose4x4[16], float centroid[3]);
+/* sampleKeyFrame(..., max_num) (main_ps.cpp:392-421, called with 40): positions of the keyframes that are kept (kept must
+ * hold max(n, max_num) ints). */
+int psg_sample_keyframes(int n, int max_num, int* kept, int* n_kept);
+
 /* ------------------------------------------------------------------ rigid depth-to-SDF tracking
  * The per-pixel part of RigidPointOptimizer::optimize_sampled (cpp/include/sdf_tracker/RigidPointOptimizer.cpp:38-62) with
  * Sdf::weights / Sdf::tsdf of the gradient-SDF volume (VolumetricGradSdf.h:76-93).  The host keeps the reference's 6 x 6

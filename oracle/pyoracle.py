@@ -85,6 +85,10 @@ def lib():
         L.or_normals_compute.argtypes = [C.c_int, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p]
         L.or_convert_depth_u16.argtypes = [vp, C.c_size_t, C.c_float, f32p]
         L.or_convert_color_u8.argtypes = [vp, C.c_size_t, f32p]
+        L.or_modified_laplacian.restype = C.c_float
+        L.or_modified_laplacian.argtypes = [f32p, C.c_int, C.c_int]
+        L.or_compute_centroid.argtypes = [f32p, f32p, C.c_int, C.c_int, f32p, f32p]
+        L.or_sample_keyframes.argtypes = [C.c_int, C.c_int, i32p]
         _lib = L
     return _lib
 
@@ -311,3 +315,25 @@ def convert_color_u8(c8):
     out = np.zeros(c8.shape, np.float32)
     lib().or_convert_color_u8(c8.ctypes.data, c8.size, out)
     return out
+
+
+def modified_laplacian(color_bgr):
+    """SharpDetector.h:22-37 on a float BGR image."""
+    c = np.ascontiguousarray(color_bgr, np.float32)
+    return float(lib().or_modified_laplacian(c, c.shape[0], c.shape[1]))
+
+
+def compute_centroid(K, depth, pose):
+    """main_ps.cpp:346-375."""
+    d = np.ascontiguousarray(depth, np.float32)
+    out = np.zeros(3, np.float32)
+    lib().or_compute_centroid(np.ascontiguousarray(K, np.float32).reshape(-1), d, d.shape[0], d.shape[1],
+                              np.ascontiguousarray(pose, np.float32).reshape(-1), out)
+    return out
+
+
+def sample_keyframes(n, max_num):
+    """main_ps.cpp:392-421: indices of the keyframes that are kept."""
+    idx = np.zeros(max(n, max_num) + 1, np.int32)
+    m = lib().or_sample_keyframes(int(n), int(max_num), idx)
+    return idx[:m].copy()

@@ -32,6 +32,7 @@ def lib():
         L.ref_vol_create.argtypes = [i32p, C.c_float, f32p, C.c_float, C.c_float, C.c_float]
         L.ref_vol_destroy.argtypes = [C.c_void_p]
         L.ref_se3_from_matrix.argtypes = [f32p, f32p, f32p]
+        L.ref_compute_centroid.argtypes = [f32p, f32p, C.c_int, C.c_int, f32p, f32p]
         L.ref_tracker_system.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, f32p, f32p, C.c_int, C.POINTER(C.c_float), f32p, f32p,
                                          C.POINTER(C.c_longlong)]
         L.ref_tracker_update.restype = C.c_float
@@ -98,6 +99,15 @@ def se3_from_matrix(pose: np.ndarray):
     t = np.zeros(3, np.float32)
     lib().ref_se3_from_matrix(np.ascontiguousarray(pose, np.float32).reshape(16), R, t)
     return R.reshape(3, 3), t
+
+
+def compute_centroid(K, depth, pose):
+    """main_ps.cpp:346-375 re-played with the reference's Eigen types."""
+    d = np.ascontiguousarray(depth, np.float32)
+    out = np.zeros(3, np.float32)
+    lib().ref_compute_centroid(np.ascontiguousarray(K, np.float32).reshape(-1), d, d.shape[0], d.shape[1],
+                               np.ascontiguousarray(pose, np.float32).reshape(-1), out)
+    return out
 
 
 def tracker_update(g, H, damping, pose):

@@ -613,4 +613,34 @@ int ref_tracker_optimize(void* h, const float* depth, int H, int W, const float*
     return conv ? 1 : 0;
 }
 
+
+// compute_centroid (voxel_ps/src/main_ps.cpp:346-375) lives in the driver translation unit, which cannot be built here
+// (imread etc.); its statements are re-played with the same Eigen types.
+void ref_compute_centroid(const float* K9, const float* depth_ptr, int h, int w, const float* pose16, float* out3) {
+    Mat3f K;
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) K(r, c) = K9[3 * r + c];
+    const Mat4f Trans = M4_from(pose16);
+    Vec3f centroid(0., 0., 0.);
+    int counter = 0;
+    Mat3f R = Trans.topLeftCorner(3, 3);
+    Vec3f t = Trans.topRightCorner(3, 1);
+    float fx = K(0, 0);
+    float fy = K(1, 1);
+    float cx = K(0, 2);
+    float cy = K(1, 2);
+    float fx_inv = 1.f / fx;
+    float fy_inv = 1.f / fy;
+    for (int y = 0; y < h; ++y) for (int x = 0; x < w; ++x) {
+        float z = depth_ptr[y * w + x];
+        if (z > 0.0) {
+            float x0 = (float(x) - cx) * fx_inv;
+            float y0 = (float(y) - cy) * fy_inv;
+            centroid += R * Vec3f(x0 * z, y0 * z, z) + t;
+            ++counter;
+        }
+    }
+    const Vec3f c = centroid / float(counter);
+    for (int a = 0; a < 3; ++a) out3[a] = c[a];
+}
+
 }  // extern "C"

@@ -127,6 +127,10 @@ def lib():
         L.psg_opt_is_sharded.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
         L.psg_opt_set_upload_overlap.argtypes = [vp, C.c_int]
         L.psg_tracker_optimize.argtypes = [vp, f32p, f32p, C.POINTER(TrackerConfig), f32p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psg_normals_sharpness.argtypes = [vp, f32p, C.POINTER(C.c_float)]
+        L.psg_normals_sharpness_u8.argtypes = [vp, vp, C.POINTER(C.c_float)]
+        L.psg_compute_centroid.argtypes = [f32p, f32p, C.c_int, C.c_int, f32p, f32p]
+        L.psg_sample_keyframes.argtypes = [C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
@@ -166,6 +170,23 @@ def shard_blocks(S: int, rank: int, world: int):
     f, st, c = C.c_int(), C.c_int(), C.c_int()
     _check(lib().psg_shard_blocks(int(S), int(rank), int(world), C.byref(f), C.byref(st), C.byref(c)))
     return f.value, st.value, c.value
+
+
+def compute_centroid(K, depth, pose):
+    """compute_centroid (main_ps.cpp:346-375): host code, no GPU needed."""
+    d = np.ascontiguousarray(depth, np.float32)
+    out = np.zeros(3, np.float32)
+    _check(lib().psg_compute_centroid(np.ascontiguousarray(K, np.float32).reshape(-1), d, d.shape[0], d.shape[1],
+                                      np.ascontiguousarray(pose, np.float32).reshape(-1), out))
+    return out
+
+
+def sample_keyframes(n: int, max_num: int = 40):
+    """sampleKeyFrame (main_ps.cpp:392-421): positions of the keyframes that are kept."""
+    kept = np.zeros(max(n, max_num) + 1, np.int32)
+    m = C.c_int()
+    _check(lib().psg_sample_keyframes(int(n), int(max_num), kept, C.byref(m)))
+    return kept[:m.value].copy()
 
 
 def profile_enable(on: bool = True) -> None:
@@ -335,6 +356,19 @@ class NormalEstimator:
 
     def n_sq_inv(self):
         return self.tables()[2]
+
+    def sharpness(self, color):
+        """modifiedLaplacian (SharpDetector.h:22-37) of a float BGR image, or of the 8-bit image the loader read."""
+        m = C.c_float()
+        if color.dtype == np.uint8:
+            c = np.ascontiguousarray(color)
+            assert c.shape == (self.H, self.W, 3)
+            _check(lib().psg_normals_sharpness_u8(self.h, c.ctypes.data, C.byref(m)))
+        else:
+            c = np.ascontiguousarray(color, np.float32)
+            assert c.shape == (self.H, self.W, 3)
+            _check(lib().psg_normals_sharpness(self.h, c, C.byref(m)))
+        return m.value
 
     def compute(self, depth):
         depth = np.ascontiguousarray(depth, np.float32)

@@ -25,7 +25,8 @@ struct psg_normals {
     psg::DevBuf<double> rows;             // 3 planes of horizontal sums
     psg::DevBuf<float> depth;             // depth in metres
     psg::DevBuf<float> out;               // 3 planes nx ny nz (psg_normals_compute)
-    psg::DevBuf<unsigned char> raw;       // H2D staging of one raw frame: depth u16 then colour u8
+    psg::DevBuf<unsigned char> raw;       // H2D staging of one raw frame: depth u16 then colour u8 (or a float colour image)
+    psg::DevBuf<double> partials;         // block partials of the sharpness sum
     cudaStream_t stream = nullptr;
 };
 
@@ -171,6 +172,49 @@ __global__ void __launch_bounds__(256) k_texels_u8(const unsigned char* __restri
     dst[i] = make_float4((float)bgr8[3 * i] * a, (float)bgr8[3 * i + 1] * a, (float)bgr8[3 * i + 2] * a, 0.f);
 }
 
+// modifiedLaplacian (ps_optimizer/SharpDetector.h:22-37) of the blue channel: FM = |G_col(M_row(x))| + |M_col(G_row(x))| with
+// M = (-1, 2, -1), G = (0.25, 0.5, 0.25), reflect-101 border, OpenCV's (left + right) * k1 + centre * k0 form; sum in double.
+// U8 = true reads the 8-bit BGR image the loader saw and converts like load_color.
+__device__ __forceinline__ float tap3(float l, float c, float r, float k1, float k0) { return (l + r) * k1 + c * k0; }
+template <bool U8>
+__global__ void __launch_bounds__(256) k_sharpness(const void* __restrict__ img, int H, int W, double* __restrict__ out) {
+    __shared__ double s_w[8];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double fm = 0.0;
+    if (i < H * W) {
+        const int y = i / W, x = i - y * W;
+        const int xl = reflect101(x - 1, W), xr = reflect101(x + 1, W);
+        float tm[3], tg[3];
+#pragma unroll
+        for (int d = -1; d <= 1; ++d) {
+            const long long row = (long long)reflect101(y + d, H) * W;
+            float l, c, r;
+            if constexpr (U8) {
+                const unsigned char* p = static_cast<const unsigned char*>(img);
+                const float a = 1.0f / 255.0f;
+                l = (float)p[3 * (row + xl)] * a; c = (float)p[3 * (row + x)] * a; r = (float)p[3 * (row + xr)] * a;
+            } else {
+                const float* p = static_cast<const float*>(img);
+                l = p[3 * (row + xl)]; c = p[3 * (row + x)]; r = p[3 * (row + xr)];
+            }
+            tm[d + 1] = tap3(l, c, r, -1.f, 2.f);
+            tg[d + 1] = tap3(l, c, r, 0.25f, 0.5f);
+        }
+        const float Lx = tap3(tm[0], tm[1], tm[2], 0.25f, 0.5f);
+        const float Ly = tap3(tg[0], tg[1], tg[2], -1.f, 2.f);
+        fm = (double)(fabsf(Lx) + fabsf(Ly));
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) fm += __shfl_xor_sync(0xffffffffu, fm, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = fm;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += s_w[w];
+        out[blockIdx.x] = t;          // block partials, added on the host in block order: reproducible
+    }
+}
+
 static void run_normals(psg_normals* ne, cudaStream_t st, bool packed, const unsigned char* bgr8_dev, float* out) {
     const int n = ne->H * ne->W, r = ne->window / 2;
     ne->rows.alloc((size_t)3 * n);
@@ -280,6 +324,75 @@ int psg_volume_integrate_raw(psg_volume* v, psg_normals* ne, const unsigned char
         PSG_CUDA(cudaStreamSynchronize(v->stream));
         return PSG_OK;
     } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+
+static int sharpness_impl(psg_normals* ne, const void* host_img, bool u8, float* measure) {
+    if (!ne || !host_img || !measure) { set_error("psg_normals_sharpness: null argument"); return PSG_ERR_INVALID; }
+    try {
+        PSG_CUDA(cudaSetDevice(ne->device));
+        const size_t n = (size_t)ne->H * ne->W;
+        const size_t bytes = n * 3 * (u8 ? 1 : 4);
+        ne->raw.alloc(n * 12);
+        const int nblocks = (int)((n + 255) / 256);
+        ne->partials.alloc((size_t)nblocks);
+        PSG_CUDA(cudaMemcpyAsync(ne->raw.p, host_img, bytes, cudaMemcpyHostToDevice, ne->stream));
+        { Prof pf(ne->stream, KID_NORMALS);
+          if (u8) k_sharpness<true><<<nblocks, 256, 0, ne->stream>>>(ne->raw.p, ne->H, ne->W, ne->partials.p);
+          else k_sharpness<false><<<nblocks, 256, 0, ne->stream>>>(ne->raw.p, ne->H, ne->W, ne->partials.p); }
+        PSG_LAUNCH_CHECK();
+        std::vector<double> h((size_t)nblocks);
+        PSG_CUDA(cudaMemcpyAsync(h.data(), ne->partials.p, sizeof(double) * (size_t)nblocks, cudaMemcpyDeviceToHost, ne->stream));
+        PSG_CUDA(cudaStreamSynchronize(ne->stream));
+        double acc = 0.0;
+        for (int b = 0; b < nblocks; ++b) acc += h[(size_t)b];
+        *measure = (float)(acc / ((double)ne->H * (double)ne->W));
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+int psg_normals_sharpness(psg_normals* ne, const float* color_bgr, float* measure) { return sharpness_impl(ne, color_bgr, false, measure); }
+int psg_normals_sharpness_u8(psg_normals* ne, const unsigned char* color_bgr_u8, float* measure) { return sharpness_impl(ne, color_bgr_u8, true, measure); }
+
+// compute_centroid (voxel_ps/src/main_ps.cpp:346-375).  One serial float accumulator per component over the pixels in row
+// order: the rounding of that sum fixes the volume origin for everything downstream, so it is kept serial (host, ~1 ms).
+int psg_compute_centroid(const float K[9], const float* depth, int H, int W, const float pose16[16], float centroid[3]) {
+    if (!K || !depth || !pose16 || !centroid || H <= 0 || W <= 0) { set_error("psg_compute_centroid: null or empty argument"); return PSG_ERR_INVALID; }
+    float c[3] = { 0.f, 0.f, 0.f };
+    int counter = 0;
+    const float fx_inv = 1.f / K[0], fy_inv = 1.f / K[4], cx = K[2], cy = K[5];
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            const float z = depth[(size_t)y * W + x];
+            if (z > 0.0) {
+                const float x0 = ((float)x - cx) * fx_inv, y0 = ((float)y - cy) * fy_inv;
+                const float p[3] = { x0 * z, y0 * z, z };
+                for (int a = 0; a < 3; ++a) {
+                    const float rp = pose16[4 * a] * p[0] + (pose16[4 * a + 1] * p[1] + pose16[4 * a + 2] * p[2]);
+                    c[a] += rp + pose16[4 * a + 3];
+                }
+                ++counter;
+            }
+        }
+    for (int a = 0; a < 3; ++a) centroid[a] = c[a] / (float)counter;
+    return PSG_OK;
+}
+
+// sampleKeyFrame (main_ps.cpp:392-421): positions (into the keyframe list) of the keyframes that are kept
+int psg_sample_keyframes(int n, int max_num, int* kept, int* n_kept) {
+    if (n < 0 || max_num < 2 || !kept || !n_kept) { set_error("psg_sample_keyframes: bad argument"); return PSG_ERR_INVALID; }
+    int m = 0;
+    if (n < max_num) {
+        for (int i = 0; i < n; ++i) kept[m++] = i;
+    } else {
+        const int cnt = max_num - 1;
+        const float step = (float)n / (float)cnt;
+        float idx = 0;
+        for (int k = 0; k < cnt; ++k) { kept[m++] = (int)idx; idx += step; }
+        kept[m++] = n - 1;
+    }
+    *n_kept = m;
+    return PSG_OK;
 }
 
 }  // extern "C"

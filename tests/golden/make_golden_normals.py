@@ -89,11 +89,21 @@ def main():
     assert np.array_equal(depth, cv2.multiply(d16.astype(np.float32), np.full((H, W), unit, np.float32)))
     color8 = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
     color = (color8.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)   # ImageLoader::load_color (:166-188)
+    # SharpDetector.h:22-37 modifiedLaplacian on the colour image (CV_32FC3): cv::mean(FM).val[0] is the blue channel's mean
+    Mk = np.array([-1, 2, -1], np.float32).reshape(3, 1)
+    Gk = cv2.getGaussianKernel(3, -1, cv2.CV_32F)
+    sharp = []
+    for img in (color, np.ascontiguousarray(color[::-1, ::-1]), cv2.GaussianBlur(color, (5, 5), 0)):
+        Lx = cv2.sepFilter2D(img, cv2.CV_32F, Mk, Gk)
+        Ly = cv2.sepFilter2D(img, cv2.CV_32F, Gk, Mk)
+        FM = cv2.add(np.abs(Lx), np.abs(Ly))
+        sharp.append(np.float32(cv2.mean(FM)[0]))
+    blurred = cv2.GaussianBlur(color, (5, 5), 0)
     c = cache(W, H, K, win)
     nx, ny, nz, b1, b2, b3 = compute(c, depth, win)
     np.savez_compressed(os.path.join(HERE, "normals.npz"), cv2_version=cv2.__version__, H=H, W=W, window=win, K=K, depth_u16=d16,
                         depth_unit=unit, color_u8=color8, depth=depth, color=color, x0=c["x0"], y0=c["y0"], x0_n=c["x0_n"],
-                        y0_n=c["y0_n"], n_sq_inv=c["n_sq_inv"], Q=c["Q"], nx=nx, ny=ny, nz=nz, b1=b1, b2=b2, b3=b3)
+                        y0_n=c["y0_n"], n_sq_inv=c["n_sq_inv"], Q=c["Q"], nx=nx, ny=ny, nz=nz, b1=b1, b2=b2, b3=b3, sharpness=np.array(sharp, np.float32), blurred=blurred)
     print("wrote normals.npz", cv2.__version__, "NaN normals:", int(np.isnan(nx).sum()))
 
 

@@ -109,3 +109,21 @@ def test_overlapped_upload_gives_the_same_state():
             out.append((go.energy(), go.light().copy()))
     for o in out[1:]:
         assert o[0] == out[0][0] and np.array_equal(o[1], out[0][1])
+
+
+def test_sharpness_matches_opencv_fixture_and_oracle():
+    import psgradientsdf_b200 as psg
+    from oracle import pyoracle
+    g = np.load(GOLD)
+    ne = psg.NormalEstimator(int(g["W"]), int(g["H"]), g["K"], int(g["window"]))
+    c = g["color"]
+    for img, want in zip((c, np.ascontiguousarray(c[::-1, ::-1]), g["blurred"]), g["sharpness"]):
+        assert np.float32(ne.sharpness(img)) == want
+    assert np.float32(ne.sharpness(g["color_u8"])) == g["sharpness"][0]          # the 8-bit entry converts like load_color
+    rng = np.random.default_rng(5)
+    for (H, W) in ((2, 2), (3, 7), (480, 640), (1709, 1139)):
+        img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        n2 = psg.NormalEstimator(W, H, g["K"], 3)
+        f = (img.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)
+        want = np.float32(pyoracle.modified_laplacian(f))
+        assert np.float32(n2.sharpness(img)) == want and np.float32(n2.sharpness(f)) == want

@@ -40,3 +40,33 @@ def test_window_sizes_and_tiny_images():
         nx, ny, nz = ne.compute(depth)
         ok = np.isfinite(nx)
         assert np.allclose((nx * nx + ny * ny + nz * nz)[ok], 1.0, atol=1e-5)
+
+
+def test_sharpness_matches_opencv():
+    """modifiedLaplacian (SharpDetector.h:22-37) restated against cv2.sepFilter2D + cv2.mean on three images."""
+    g = np.load(GOLD)
+    c = g["color"]
+    got = [pyoracle.modified_laplacian(x) for x in (c, np.ascontiguousarray(c[::-1, ::-1]), g["blurred"])]
+    assert [np.float32(v) for v in got] == list(g["sharpness"])
+    assert got[2] < 0.2 * got[0]                     # the blurred image is what the gate is meant to reject
+
+
+def test_centroid_and_keyframe_sampling_vs_reference_and_library():
+    """compute_centroid and sampleKeyFrame are host code in the library (no GPU): restatement, library and -- where the
+    reference build is present -- the re-played reference statements agree bit for bit."""
+    import psgradientsdf_b200 as psg
+    from oracle import pyref
+    g = np.load(GOLD)
+    P = np.eye(4, dtype=np.float32)
+    P[:3, :3] = np.array([[0.936, 0.18, 0.302], [-0.1, 0.96, -0.262], [-0.337, 0.215, 0.917]], np.float32)
+    P[:3, 3] = [0.1, -0.2, 0.3]
+    a = pyoracle.compute_centroid(g["K"], g["depth"], P)
+    b = psg.compute_centroid(g["K"], g["depth"], P)
+    assert np.array_equal(a, b)
+    if pyref.available():
+        assert np.array_equal(a, pyref.compute_centroid(g["K"], g["depth"], P))
+    for n in (0, 1, 5, 39, 40, 41, 64, 100, 1000):
+        o = pyoracle.sample_keyframes(n, 40)
+        l = psg.sample_keyframes(n, 40)
+        assert np.array_equal(o, l), n
+        assert len(l) == (n if n < 40 else 40) and (n == 0 or l[-1] == n - 1) and np.all(np.diff(l) >= 0)
