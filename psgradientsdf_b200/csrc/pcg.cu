@@ -765,6 +765,23 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
     surf.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
 }
 
+// launch geometry of the cooperative kernels, queried once per device (the queries cost microseconds each, the solve runs
+// every outer iteration)
+struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_1 = 0, per_sm_4 = 0; };
+static const PcgGeometry& pcg_geometry() {
+    static PcgGeometry g[64];
+    int dev = 0;
+    PSG_CUDA(cudaGetDevice(&dev));
+    PcgGeometry& e = g[dev & 63];
+    if (e.sms == 0) {
+        PSG_CUDA(cudaDeviceGetAttribute(&e.sms, cudaDevAttrMultiProcessorCount, dev));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_1, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
+    }
+    return e;
+}
+
 // vecs layout (floats, planes of S): 0..13 stencil blocks | 14 rhs | 15 invd | 16 ddiag | 17 x | 18 r | 19 p | 20 tmp | 21..24 U
 // queues the assembly and the solve; the verdict lands in mail slot kSlotPcg
 void launch_dist_solve(psg_optimizer* o, float damping) {
@@ -785,16 +802,13 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 
     constexpr int kClusterMax = 8, kClusterRows = 1 << 16;
     const bool use_cluster = o->pcg_mode == 1 && S <= kClusterRows;
-    int dev = 0, sms = 0;
-    PSG_CUDA(cudaGetDevice(&dev));
-    PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const PcgGeometry& geo = pcg_geometry();
+    const int sms = geo.sms;
     // grid kernel geometry: one row per thread while that still leaves SMs idle, four rows per thread beyond
     const int rpt = (S <= sms * kPcgBlock * 2) ? 1 : 4;
     int grid = 0;
     if (!use_cluster) {
-        int per_sm = 0;
-        if (rpt == 1) PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
-        else PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
+        int per_sm = rpt == 1 ? geo.per_sm_1 : geo.per_sm_4;
         if (per_sm < 1) { set_error("PCG kernel does not fit on an SM"); throw CudaError{-1}; }
         if (per_sm > 4) per_sm = 4;
         grid = sms * per_sm;
@@ -840,10 +854,8 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot) {
     const int S = o->S;
     if (S == 0 || o->pcg_mode != 0) return false;
-    int dev = 0, sms = 0, per_sm = 0;
-    PSG_CUDA(cudaGetDevice(&dev));
-    PSG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
+    const PcgGeometry& geo = pcg_geometry();
+    const int sms = geo.sms, per_sm = geo.per_sm_small;
     const int grid = (S + kPcgBlock - 1) / kPcgBlock;
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
