@@ -110,7 +110,6 @@ struct psg_optimizer {
     unsigned long long vol_gen_seen = 0;     // volume generation the records were gathered from
     psg::DevBuf<unsigned int> mask, prefix;  // membership bitmask over the volume + exclusive popcount prefix
     psg::DevBuf<unsigned int> block_counts;
-    psg::DevBuf<int> frame_idx_dev;
     // reductions / systems
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
@@ -129,7 +128,6 @@ struct psg_optimizer {
     psg::DevBuf<double> pcg_partials;
     psg::DevBuf<float> pcg_pbuf;             // double-buffered search direction of the cluster PCG
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
-    std::vector<float> lastvb, lastvd;
     int last_n = 0, last_block = -1;
     // pinned host staging: the mailbox (kMailDoubles) followed by kRedDoubles of per-keyframe sums
     double* host_staging = nullptr;
@@ -167,10 +165,6 @@ void launch_upsample(psg_optimizer* o);
 void launch_gather_voxels(psg_optimizer* o, float* out_dev);   // S x 8 floats (SdfVoxel layout) in surface-list order
 
 // ---- sweep.cu
-struct SweepOut {
-    double E = 0.0;
-    long long n_active = 0;
-};
 void refresh_frame_table(psg_optimizer* o);
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
