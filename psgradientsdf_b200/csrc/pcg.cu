@@ -786,7 +786,7 @@ static const PcgGeometry& pcg_geometry() {
 // queues the assembly and the solve; the verdict lands in mail slot kSlotPcg
 void launch_dist_solve(psg_optimizer* o, float damping) {
     const int S = o->S;
-    o->red.alloc(kRedDoubles + kMailDoubles);
+    o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
     PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotPcg, 0, 16 * sizeof(double), o->stream));   // verdict + accepted counter
     if (S == 0) return;
     o->vecs.alloc((size_t)S * 25 + 8);
@@ -859,7 +859,7 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     const int grid = (S + kPcgBlock - 1) / kPcgBlock;
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
-    o->red.alloc(kRedDoubles + kMailDoubles);
+    o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
     static_assert(kSlotReg + 1 == kSlotPcg && kSlotPcg + 1 == kSlotCount, "slots 5..7 are cleared with one memset");
     PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotReg, 0, 24 * sizeof(double), o->stream));   // reg energies, verdict, counter + barrier
     o->vecs.alloc((size_t)S * 25 + 8);

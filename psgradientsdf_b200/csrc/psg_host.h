@@ -139,9 +139,10 @@ struct psg_optimizer {
 
 namespace psg {
 
-// o->red: kRedDoubles of per-keyframe sums, then the mailbox (8 slots x 8 doubles) every kernel of an outer iteration reports
+// o->red: the mailbox, then kRedCopies x kRedDoubles of per-keyframe sums (copy 0 holds the result); the mailbox (8 slots x 8 doubles) every kernel of an outer iteration reports
 // into: slots 0..4 sweep scalars (one per sweep in flight), then the three below
 constexpr int kRedDoubles = kMaxFrames * 64;
+constexpr int kRedCopies = 8;     // private copies of the per-keyframe sums on large grids (same-address fp64 atomics serialise in L2)
 constexpr int kMailDoubles = 64;
 constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
 constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold

@@ -41,6 +41,7 @@ struct SweepArgs {
     float damping, reg_n, reg_l;
     int flags;
     double* red;        // per-keyframe reductions (zeroed by the launcher)
+    int red_copies;     // blocks spread their atomics over this many copies of `red` (kRedDoubles apart), combined afterwards
     double* scal;       // 8 scalar results: [0..5] mode specific, [6] sum of robust losses, [7] active pairs
     double* partials;   // [gridDim.x][8] per-block scalar partials, combined in block order by the last block
     unsigned* counter;  // arrival counter for that (self-resetting)
@@ -449,7 +450,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                         vals[NT + i] = sr * sh_g[i];
                     }
                 }
-                double* dst = A.red + (long long)f * VRED;
+                double* dst = A.red + (size_t)(blockIdx.x % (unsigned)A.red_copies) * kRedDoubles + (long long)f * VRED;
                 if constexpr (VLIGHT == 16) {
                     warp_accumulate<16>(vals, lane, dst);
                 } else {
@@ -532,7 +533,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                         }
                     }
                 }
-                warp_accumulate<32>(vals, lane, A.red + (long long)f * VRED);
+                warp_accumulate<32>(vals, lane, A.red + (size_t)(blockIdx.x % (unsigned)A.red_copies) * kRedDoubles + (long long)f * VRED);
             } else if (okj) {   // M_DIST
                 // M = A * R^T, dI_k = M * dx_k
                 float Mx[9];
@@ -731,6 +732,15 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     }
 }
 
+// copy 0 += copies 1.. of the per-keyframe sums, in copy order
+__global__ void __launch_bounds__(256) k_combine_red(double* __restrict__ red, int n, int copies) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double t = red[i];
+    for (int c = 1; c < copies; ++c) t += red[(size_t)c * kRedDoubles + i];
+    red[i] = t;
+}
+
 // ------------------------------------------------------------------------------------------------ launchers
 static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     refresh_frame_table(o);
@@ -745,8 +755,9 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
-    o->red.alloc(kRedDoubles + kMailDoubles);
+    o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
     A.red = red_dev(o);
+    A.red_copies = 1;
     A.scal = mail_dev(o) + 8 * slot;
     const size_t grid = (size_t)(o->S + 31) / 32 + 1;
     const size_t ngroups = grid / kRedGroup + 2;
@@ -775,7 +786,10 @@ void refresh_frame_table(psg_optimizer* o) {
 
 template <int MODE>
 static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, size_t dyn_smem) {
-    if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, red_doubles * sizeof(double), o->stream));
+    // many blocks adding into the same few hundred doubles serialise in L2: from a few thousand blocks on, spread them over
+    // private copies and add the copies up afterwards (k_combine_red)
+    if (red_doubles && A.blk_count >= 2048) A.red_copies = kRedCopies;
+    if (red_doubles) PSG_CUDA(cudaMemsetAsync(A.red, 0, ((size_t)(A.red_copies - 1) * kRedDoubles + red_doubles) * sizeof(double), o->stream));
     if (o->sharded || A.blk_count <= 0)   // ranks without work still take part in the all-reduce
         PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
     if (o->S == 0 || A.blk_count <= 0) return;
@@ -801,6 +815,11 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
     }
 #undef PSG_SWEEP_CASE
     PSG_LAUNCH_CHECK();
+    if (red_doubles && A.red_copies > 1) {
+        k_combine_red<<<(unsigned)((red_doubles + 255) / 256), 256, 0, o->stream>>>(A.red, (int)red_doubles, A.red_copies);
+        count_launch(1);
+        PSG_LAUNCH_CHECK();
+    }
 }
 
 // Results travel through a small "mailbox" behind the per-keyframe reduction buffer: 8 slots of 8 doubles.  A launch
@@ -1086,7 +1105,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
-        A.red = sc->red; A.scal = sc->red; A.partials = sc->partials; A.counter = sc->counter;
+        A.red = sc->red; A.red_copies = 1; A.scal = sc->red; A.partials = sc->partials; A.counter = sc->counter;
 
         const int grid = (o->S + 31) / 32;
         int W = 1;
