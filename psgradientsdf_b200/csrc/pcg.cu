@@ -734,8 +734,8 @@ __global__ void __launch_bounds__(256) k_dist_update(VolView vol, const int* __r
         const float d = delta[s];
         if (fabs((double)d) < thr) { vol.dist[lin[s]] -= d; acc = 1; }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, acc);
-    if ((threadIdx.x & 31) == 0 && m) atomicAdd(accepted, (unsigned long long)__popc(m));
+    const int n = __syncthreads_count(acc);       // one atomic per block: tens of thousands on one address serialise in L2
+    if (threadIdx.x == 0 && n) atomicAdd(accepted, (unsigned long long)n);
 }
 
 // Optimizer::updateGrad (OptimizerAux.cpp:152-160): grad <- finite-difference gradient (not normalised); also refreshes

@@ -284,10 +284,17 @@ __global__ void __launch_bounds__(256) k_sort_keys(const unsigned long long* __r
 // number of visible (surface voxel, keyframe) pairs: the size of a sweep, used to decide whether sharding it pays
 __global__ void __launch_bounds__(256) k_count_pairs(const unsigned long long* __restrict__ vis, int n, unsigned long long* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ int s_c[8];
     int c = i < n ? __popcll(vis[i]) : 0;
 #pragma unroll
     for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; ++w) t += s_c[w];
+        if (t) atomicAdd(out, (unsigned long long)t);
+    }
 }
 
 void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
