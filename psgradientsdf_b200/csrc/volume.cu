@@ -133,7 +133,8 @@ constexpr int kBrick = 8;
 __global__ void __launch_bounds__(128) k_cull_bricks(VolView v, FuseParams P, const float* __restrict__ tile_max, int tx, int nbx, int nby,
                                                     int nbricks, int* __restrict__ list, int* __restrict__ count) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= nbricks) return;
+    bool skip = true;
+    if (b < nbricks) {
     const int bx = b % nbx, by = (b / nbx) % nby, bz = b / (nbx * nby);
     const int i0 = bx * kBrick, j0 = by * kBrick, k0 = bz * kBrick;
     float zlo = 3.4e38f, zhi = -3.4e38f, nlo = 3.4e38f, nhi = -3.4e38f, mlo = 3.4e38f, mhi = -3.4e38f;
@@ -152,7 +153,7 @@ __global__ void __launch_bounds__(128) k_cull_bricks(VolView v, FuseParams P, co
         zlo = fminf(zlo, pt[2]); zhi = fmaxf(zhi, pt[2]);
         nlo = fminf(nlo, n); nhi = fmaxf(nhi, n); mlo = fminf(mlo, m); mhi = fmaxf(mhi, m);
     }
-    bool skip = false;
+    skip = false;
     const float eps = 1e-4f * fmaxf(1.f, fabsf(zhi)) + v.vs * 1e-3f;
     if (zhi < -eps) {
         skip = true;                                    // the whole brick is behind the camera (gate pt.z < 0)
@@ -172,7 +173,17 @@ __global__ void __launch_bounds__(128) k_cull_bricks(VolView v, FuseParams P, co
             }
         }
     }
-    if (!skip) list[atomicAdd(count, 1)] = b;
+    }
+    // warp-aggregated append: one atomic per warp (every survivor adding to the same counter would serialise in L2)
+    const unsigned keep = __ballot_sync(0xffffffffu, !skip);
+    if (!skip) {
+        const int lane = threadIdx.x & 31;
+        const int leader = __ffs(keep) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(count, __popc(keep));
+        base = __shfl_sync(keep, base, leader);
+        list[base + __popc(keep & ((1u << lane) - 1u))] = b;
+    }
 }
 
 __global__ void __launch_bounds__(256) k_integrate_list(VolView v, const float* __restrict__ frame, FuseParams P, const int* __restrict__ list,
