@@ -129,6 +129,10 @@ def test_empty_cases():
     for blk in block_order("SH1"):
         info = go.step(blk, normal_reg=True)
         assert info["n"] in (0, 8, 12)
+    it = go.iteration(normal_reg=True)              # the three-wait pass on an empty work list: no-ops as well
+    assert it["n_active_end"] == 0 and it["dist"]["n"] == 0 and it["pose"]["n"] == 12
+    res = go.alternatingOptimize(max_it=2)
+    assert res["iterations"] >= 1
     # frames fused, but the keyframe indices point past them
     gv2, go2 = make_gpu("SH1", G, sc)
     go2.set_keyframes(np.array([40, 41], np.int32), sc.poses_init[:2], sc.color[:2]); go2.init()
