@@ -24,7 +24,7 @@ BLOCK = {"albedo": 0, "light": 1, "dist": 2, "pose": 3}
 
 
 def build(force: bool = False) -> None:
-    srcs = [os.path.join(_HERE, "psg_oracle.c"), os.path.join(_HERE, "psg_oracle_normals.c")]
+    srcs = [os.path.join(_HERE, n) for n in ("psg_oracle.c", "psg_oracle_normals.c", "psg_oracle_mesh.c")]
     if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(x) for x in srcs):
         subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
 
@@ -89,6 +89,14 @@ def lib():
         L.or_modified_laplacian.argtypes = [f32p, C.c_int, C.c_int]
         L.or_compute_centroid.argtypes = [f32p, f32p, C.c_int, C.c_int, f32p, f32p]
         L.or_sample_keyframes.argtypes = [C.c_int, C.c_int, i32p]
+        L.or_mesh_bbox.argtypes = [f32p, i32p, C.c_float, i32p, i32p]
+        L.or_marching_cubes.restype = C.c_longlong
+        L.or_marching_cubes.argtypes = [i32p, f32p, f32p, f32p, f32p, u8p, u8p, u8p, C.c_float, vp, vp]
+        L.or_extract_mesh.restype = C.c_longlong
+        L.or_extract_mesh.argtypes = [f32p, i32p, C.c_float, C.c_int, vp, vp, vp, vp]
+        L.or_write_mesh_ply.argtypes = [C.c_char_p, C.c_longlong, f32p, u8p]
+        L.or_write_sdf.argtypes = [C.c_char_p, f32p, i32p, C.c_float]
+        L.or_write_volume_pc.argtypes = [C.c_char_p, f32p, u8p, i32p, C.c_float]
         _lib = L
     return _lib
 
@@ -337,3 +345,50 @@ def sample_keyframes(n, max_num):
     idx = np.zeros(max(n, max_num) + 1, np.int32)
     m = lib().or_sample_keyframes(int(n), int(max_num), idx)
     return idx[:m].copy()
+
+
+# ---- surface extraction (psg_oracle_mesh.c) --------------------------------------------------------------------------------
+def mesh_bbox(aos, dims, vs):
+    """Crop box of extract_mesh / saveSDF: (lo[3], hi[3]) or None when no voxel lies within sqrt(3) * vs of the surface."""
+    lo, hi = np.zeros(3, np.int32), np.zeros(3, np.int32)
+    any_ = lib().or_mesh_bbox(np.ascontiguousarray(aos, np.float32), np.asarray(dims, np.int32), float(vs), lo, hi)
+    return (lo, hi) if any_ else None
+
+
+def marching_cubes(dims, size, origin, tsdf, weights, red, green, blue, iso=0.0):
+    """MarchingCubes::computeIsoSurface on cropped arrays: (vertices 3T x 3 float32, colours 3T x 3 uint8)."""
+    a = (np.asarray(dims, np.int32), np.asarray(size, np.float32), np.asarray(origin, np.float32),
+         np.ascontiguousarray(tsdf, np.float32).reshape(-1), np.ascontiguousarray(weights, np.float32).reshape(-1),
+         np.ascontiguousarray(red, np.uint8).reshape(-1), np.ascontiguousarray(green, np.uint8).reshape(-1),
+         np.ascontiguousarray(blue, np.uint8).reshape(-1), float(iso))
+    nt = lib().or_marching_cubes(*a, None, None)
+    v, c = np.zeros((max(3 * nt, 1), 3), np.float32), np.zeros((max(3 * nt, 1), 3), np.uint8)
+    lib().or_marching_cubes(*a, v.ctypes.data, c.ctypes.data)
+    return v[:3 * nt], c[:3 * nt]
+
+
+def extract_mesh(aos, dims, vs, white=False):
+    """Optimizer::extract_mesh / save_white_mesh on an N x 8 voxel array: (vertices, colours) or None (empty crop box)."""
+    aos = np.ascontiguousarray(aos, np.float32)
+    dims = np.asarray(dims, np.int32)
+    nt = lib().or_extract_mesh(aos, dims, float(vs), int(white), None, None, None, None)
+    if nt < 0:
+        return None
+    v, c = np.zeros((max(3 * nt, 1), 3), np.float32), np.zeros((max(3 * nt, 1), 3), np.uint8)
+    lib().or_extract_mesh(aos, dims, float(vs), int(white), None, None, v.ctypes.data, c.ctypes.data)
+    return v[:3 * nt], c[:3 * nt]
+
+
+def write_mesh_ply(path, vertices, colors):
+    v, c = np.ascontiguousarray(vertices, np.float32), np.ascontiguousarray(colors, np.uint8)
+    return bool(lib().or_write_mesh_ply(path.encode(), len(v) // 3, v.reshape(-1) if len(v) else np.zeros(1, np.float32),
+                                        c.reshape(-1) if len(c) else np.zeros(1, np.uint8)))
+
+
+def write_sdf(path, aos, dims, vs):
+    return bool(lib().or_write_sdf(path.encode(), np.ascontiguousarray(aos, np.float32), np.asarray(dims, np.int32), float(vs)))
+
+
+def write_volume_pc(path, aos, seen, dims, vs):
+    return bool(lib().or_write_volume_pc(path.encode(), np.ascontiguousarray(aos, np.float32), np.ascontiguousarray(seen, np.uint8),
+                                         np.asarray(dims, np.int32), float(vs)))

@@ -85,6 +85,11 @@ def lib():
         L.ref_last_stdout.restype = C.c_char_p
         L.ref_opt_subsampling.argtypes = [C.c_void_p]
         L.ref_set_quiet.argtypes = [C.c_int]
+        L.ref_marching_cubes.argtypes = [i32p, f32p, f32p, f32p, f32p, u8p, u8p, u8p, C.c_float, C.POINTER(C.c_longlong),
+                                         C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p, C.c_void_p]
+        for n in ("ref_vol_extract_mesh", "ref_vol_extract_pc", "ref_vol_save_sdf", "ref_opt_extract_mesh", "ref_opt_save_white_mesh",
+                  "ref_opt_save_pointcloud", "ref_opt_save_sdf"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_char_p]
         _lib = L
     return _lib
 
@@ -117,6 +122,19 @@ def tracker_update(g, H, damping, pose):
     c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
     n2 = lib().ref_tracker_update(c(g), c(H), float(damping), c(pose), out, xi)
     return out.reshape(4, 4), xi, float(n2)
+
+
+def marching_cubes(dims, size, origin, tsdf, weights, red, green, blue, iso=0.0):
+    """third/mesh/MarchingCubes.cpp, unmodified: (vertices T*3 x 3 float32, colours T*3 x 3 uint8, faces T x 3 int32)."""
+    dims = np.asarray(dims, np.int32)
+    a = (dims, np.asarray(size, np.float32), np.asarray(origin, np.float32), np.ascontiguousarray(tsdf, np.float32).reshape(-1),
+         np.ascontiguousarray(weights, np.float32).reshape(-1), np.ascontiguousarray(red, np.uint8).reshape(-1),
+         np.ascontiguousarray(green, np.uint8).reshape(-1), np.ascontiguousarray(blue, np.uint8).reshape(-1), float(iso))
+    nv, nf = C.c_longlong(), C.c_longlong()
+    lib().ref_marching_cubes(*a, C.byref(nv), C.byref(nf), None, None, None)
+    v = np.zeros((max(nv.value, 1), 3), np.float32); c = np.zeros((max(nv.value, 1), 3), np.uint8); f = np.zeros((max(nf.value, 1), 3), np.int32)
+    lib().ref_marching_cubes(*a, C.byref(nv), C.byref(nf), v.ctypes.data, c.ctypes.data, f.ctypes.data)
+    return v[:nv.value], c[:nv.value], f[:nf.value]
 
 
 class RefVolume:
@@ -164,6 +182,16 @@ class RefVolume:
         conv = lib().ref_tracker_optimize(self.h, depth, depth.shape[0], depth.shape[1], c(K), c(pose), int(num_iterations),
                                           float(conv_threshold), float(damping), out)
         return bool(conv), out.reshape(4, 4)
+
+    def extract_mesh(self, filename):
+        """VolumetricGradSdf::extract_mesh (VolumetricGradSdf.cpp:234-318), the file it writes."""
+        return bool(lib().ref_vol_extract_mesh(self.h, filename.encode()))
+
+    def extract_pc(self, filename):
+        return bool(lib().ref_vol_extract_pc(self.h, filename.encode()))
+
+    def save_sdf(self, filename):
+        return bool(lib().ref_vol_save_sdf(self.h, filename.encode()))
 
     def download(self):
         a = np.zeros((self.N, 8), np.float32)
@@ -334,3 +362,16 @@ class RefOptimizer:
 
     def subsampling(self):
         lib().ref_opt_subsampling(self.h)
+
+    # the reference's writers: <save_path><name>_mesh.ply, _obj.ply, _pointcloud.ply, <save_path><name>
+    def extract_mesh(self, name):
+        return bool(lib().ref_opt_extract_mesh(self.h, name.encode()))
+
+    def save_white_mesh(self, name):
+        return bool(lib().ref_opt_save_white_mesh(self.h, name.encode()))
+
+    def save_pointcloud(self, name):
+        return bool(lib().ref_opt_save_pointcloud(self.h, name.encode()))
+
+    def save_sdf(self, name):
+        return bool(lib().ref_opt_save_sdf(self.h, name.encode()))

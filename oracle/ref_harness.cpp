@@ -51,6 +51,7 @@
 #include "ps_optimizer/PsOptimizer.h"
 #include "ps_optimizer/LedOptimizer.h"
 #include "sdf_tracker/RigidPointOptimizer.h"
+#include "mesh/MarchingCubes.h"
 #undef class
 #undef private
 #undef protected
@@ -642,5 +643,30 @@ void ref_compute_centroid(const float* K9, const float* depth_ptr, int h, int w,
     const Vec3f c = centroid / float(counter);
     for (int a = 0; a < 3; ++a) out3[a] = c[a];
 }
+
+// ---- surface extraction ------------------------------------------------------------------------------
+// third/mesh/MarchingCubes.cpp:314-699, unmodified, on caller-supplied arrays.  Query with null outputs for the counts.
+// vertices: 3 floats each, colors: 3 bytes each, faces: 3 ints each.
+int ref_marching_cubes(const int* dims, const float* size3, const float* origin3, const float* tsdf, const float* weights,
+                       const unsigned char* red, const unsigned char* green, const unsigned char* blue, float iso,
+                       long long* n_vertices, long long* n_faces, float* vertices, unsigned char* colors, int* faces) {
+    MarchingCubes mc(Vec3i(dims[0], dims[1], dims[2]), Vec3f(size3[0], size3[1], size3[2]), Vec3f(origin3[0], origin3[1], origin3[2]));
+    const bool ok = mc.computeIsoSurface(tsdf, weights, red, green, blue, iso);
+    if (n_vertices) *n_vertices = (long long)mc.vertices_.size();
+    if (n_faces) *n_faces = (long long)mc.faces_.size();
+    if (vertices) for (size_t i = 0; i < mc.vertices_.size(); ++i) for (int a = 0; a < 3; ++a) vertices[3 * i + a] = mc.vertices_[i][a];
+    if (colors) for (size_t i = 0; i < mc.colors_.size(); ++i) for (int a = 0; a < 3; ++a) colors[3 * i + a] = mc.colors_[i][a];
+    if (faces) for (size_t i = 0; i < mc.faces_.size(); ++i) for (int a = 0; a < 3; ++a) faces[3 * i + a] = mc.faces_[i][a];
+    return ok ? 1 : 0;
+}
+// the reference's own writers, unmodified: the files they produce are what the tests compare byte by byte
+int ref_vol_extract_mesh(void* h, const char* filename) { Quiet q; return static_cast<RefVol*>(h)->sdf->extract_mesh(filename) ? 1 : 0; }
+int ref_vol_extract_pc(void* h, const char* filename) { Quiet q; return static_cast<RefVol*>(h)->sdf->extract_pc(filename) ? 1 : 0; }
+int ref_vol_save_sdf(void* h, const char* filename) { Quiet q; return static_cast<RefVol*>(h)->sdf->saveSDF(filename) ? 1 : 0; }
+// these write <save_path><name>_mesh.ply / _obj.ply / _pointcloud.ply / <save_path><name>
+int ref_opt_extract_mesh(void* h, const char* name) { Quiet q; return static_cast<RefOpt*>(h)->opt->extract_mesh(name) ? 1 : 0; }
+int ref_opt_save_white_mesh(void* h, const char* name) { Quiet q; return static_cast<RefOpt*>(h)->opt->save_white_mesh(name) ? 1 : 0; }
+int ref_opt_save_pointcloud(void* h, const char* name) { Quiet q; return static_cast<RefOpt*>(h)->opt->save_pointcloud(name) ? 1 : 0; }
+int ref_opt_save_sdf(void* h, const char* name) { Quiet q; return static_cast<RefOpt*>(h)->opt->saveSDF(name) ? 1 : 0; }
 
 }  // extern "C"
