@@ -192,6 +192,33 @@ int psg_opt_probe_pairs(psg_optimizer* opt, float* m, float* n, unsigned char* o
 #define PSG_REG_NORMAL 2
 #define PSG_REG_LAPLACIAN 4
 int psg_opt_step(psg_optimizer* opt, int block, float damping, int flags, psg_step_info* info /* may be NULL */);
+/* ---- surface extraction ---------------------------------------------------------------------------------
+ * Marching cubes on the device with the reference's exact output: the crop box of voxels with |dist| <= sqrt(3) * voxel_size
+ * (OptimizerAux.cpp:278-308), MarchingCubes::computeIsoSurface over the (box - 2)^3 cells of it with size = voxel_size * box and
+ * origin = -voxel_size * box_min (OptimizerAux.cpp:344-345, third/mesh/MarchingCubes.cpp:314-541): three new vertices per
+ * triangle, cells in x, y, z order, triangles in table order, degenerate triangles dropped; vertices and 8-bit colours are
+ * bit-identical to the reference's vertices_ / colors_ and face t is (3t, 3t+1, 3t+2).  voxel_size <= 0 means the volume's own. */
+int psg_volume_mesh_box(psg_volume* vol, float voxel_size, int lo[3], int hi[3], int* any /* 0: no voxel near the surface */);
+/* white != 0: save_white_mesh (OptimizerAux.cpp:365-453), every colour 255.  The triangles stay on the device until the next
+ * extraction; *n_triangles = 0 also when the crop box is empty. */
+int psg_volume_mesh_extract(psg_volume* vol, float voxel_size, int white, long long* n_triangles);
+int psg_volume_mesh_download(psg_volume* vol, float* vertices /* n_triangles x 9, may be NULL */,
+                             unsigned char* colors /* n_triangles x 9 (r, g, b per vertex), may be NULL */);
+/* VolumetricGradSdf::extract_mesh (VolumetricGradSdf.cpp:234-318) + MarchingCubes::savePly (MarchingCubes.cpp:653-699): the
+ * ASCII PLY the reference writes, byte for byte.  No file is written when there is no triangle (savePly returns false then);
+ * *n_triangles (may be NULL) tells.  PSG_ERR_INVALID when the file cannot be opened. */
+int psg_volume_extract_mesh(psg_volume* vol, const char* filename, int white, long long* n_triangles);
+/* VolumetricGradSdf::extract_pc (VolumetricGradSdf.cpp:320-376): voxels within sqrt(3) * voxel_size of the surface seen by at
+ * least one frame, in lin order: grid-relative position, unit gradient, colour. */
+int psg_volume_extract_pc(psg_volume* vol, const char* filename, long long* n_points /* may be NULL */);
+/* VolumetricGradSdf::saveSDF (VolumetricGradSdf.cpp:379-460): crop box dimensions, lower corner, voxel size, -dist values. */
+int psg_volume_save_sdf(psg_volume* vol, const char* filename);
+/* Optimizer::extract_mesh / save_white_mesh / saveSDF / save_pointcloud (OptimizerAux.cpp:278-577) with the full file name
+ * instead of save_path_ + name + suffix; they read Optimizer::voxel_size_ where the volume's own writers read theirs. */
+int psg_opt_extract_mesh(psg_optimizer* opt, const char* filename, int white, long long* n_triangles /* may be NULL */);
+int psg_opt_save_sdf(psg_optimizer* opt, const char* filename);
+int psg_opt_save_pointcloud(psg_optimizer* opt, const char* filename);
+
 /* One pass of the reference's while-body (PsOptimizer.cpp:303-360, LedOptimizer.cpp:343-403): the enabled blocks in the
  * reference's order (SH: albedo, light, distance, pose; LED: light, albedo, distance, pose), the regulariser energies after
  * the distance block and the closing getPSEnergy().  Same kernels and host solves as four psg_opt_step calls +
@@ -314,7 +341,8 @@ int psg_opt_energy_partial(psg_optimizer* opt, int rank, int world, double* loss
  * OptimizerSettings.h:24-33).  Runs initAlbedo, the regulariser-weight normalisation and the outer loop; writes
  * <save_path>optimizer_doc.txt, after_poses_opt_<it>.txt, after_iter_<it>_pointcloud.ply, upsample_after_5_pointcloud.ply,
  * final_refined_pointcloud.ply (LED: refined_sdf.sdf) when write_artifacts != 0 (save_path must exist and end in '/',
- * as in the reference).  Mesh files are not written (marching cubes is outside this path). */
+ * as in the reference), and beside every point cloud the mesh the reference extracts there (extract_mesh, PsOptimizer.cpp:373,380,
+ * 398,422): after_iter_<it>_mesh.ply, upsample_after_5_mesh.ply, final_refined_mesh.ply. */
 typedef struct {
     int light, albedo, distance, pose;   /* the --light/--albedo/--distance/--pose switches (main_ps.cpp:79-82) */
     int max_it;

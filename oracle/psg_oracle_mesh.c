@@ -224,3 +224,31 @@ int or_write_volume_pc(const char* path, const float* aos, const unsigned char* 
     fclose(f);
     return 1;
 }
+
+/* Optimizer::save_pointcloud (OptimizerAux.cpp:456-511): the surface list's voxels with |dist| < sqrt(3) * vs (strictly, std::abs
+ * in float against a double product), same record as extract_pc. */
+int or_write_surface_pc(const char* path, const float* aos, const int* lin, int S, const int* dims, float vs) {
+    const double thr = sqrt(3.0) * (double)vs;
+    FILE* f = fopen(path, "w");
+    if (!f) return 0;
+    long long count = 0;
+    for (int s = 0; s < S; ++s) if ((double)fabsf(aos[8 * (size_t)lin[s]]) < thr) ++count;
+    fprintf(f, "ply\nformat ascii 1.0\nelement vertex %lld\nproperty float x\nproperty float y\nproperty float z\n", count);
+    fprintf(f, "property float nx\nproperty float ny\nproperty float nz\nproperty uchar red\nproperty uchar green\nproperty uchar blue\nend_header\n");
+    for (int s = 0; s < S; ++s) {
+        const float* v = aos + 8 * (size_t)lin[s];
+        if (!((double)fabsf(v[0]) < thr)) continue;
+        int rest = lin[s];
+        const int k = rest / (dims[0] * dims[1]); rest -= k * dims[0] * dims[1];
+        const int j = rest / dims[0], i = rest - j * dims[0];
+        float g[3] = { v[1], v[2], v[3] };
+        const float z = g[0] * g[0] + (g[1] * g[1] + g[2] * g[2]);
+        if (z > 0.f) { const float sq = sqrtf(z); g[0] /= sq; g[1] /= sq; g[2] /= sq; }
+        const float idx[3] = { (float)i, (float)j, (float)k };
+        float p[3];
+        for (int a = 0; a < 3; ++a) p[a] = vs * idx[a] - v[0] * g[a];
+        fprintf(f, "%g %g %g %g %g %g %d %d %d\n", p[0], p[1], p[2], g[0], g[1], g[2], (int)(255 * v[5]), (int)(255 * v[6]), (int)(255 * v[7]));
+    }
+    fclose(f);
+    return 1;
+}

@@ -97,6 +97,7 @@ def lib():
         L.or_write_mesh_ply.argtypes = [C.c_char_p, C.c_longlong, f32p, u8p]
         L.or_write_sdf.argtypes = [C.c_char_p, f32p, i32p, C.c_float]
         L.or_write_volume_pc.argtypes = [C.c_char_p, f32p, u8p, i32p, C.c_float]
+        L.or_write_surface_pc.argtypes = [C.c_char_p, f32p, i32p, C.c_int, i32p, C.c_float]
         _lib = L
     return _lib
 
@@ -392,3 +393,10 @@ def write_sdf(path, aos, dims, vs):
 def write_volume_pc(path, aos, seen, dims, vs):
     return bool(lib().or_write_volume_pc(path.encode(), np.ascontiguousarray(aos, np.float32), np.ascontiguousarray(seen, np.uint8),
                                          np.asarray(dims, np.int32), float(vs)))
+
+
+def write_surface_pc(path, aos, lin, dims, vs):
+    """Optimizer::save_pointcloud over the surface list `lin`."""
+    lin = np.ascontiguousarray(lin, np.int32)
+    return bool(lib().or_write_surface_pc(path.encode(), np.ascontiguousarray(aos, np.float32), lin if len(lin) else np.zeros(1, np.int32),
+                                          len(lin), np.asarray(dims, np.int32), float(vs)))

@@ -132,6 +132,16 @@ def lib():
         L.psg_compute_centroid.argtypes = [f32p, f32p, C.c_int, C.c_int, f32p, f32p]
         L.psg_sample_keyframes.argtypes = [C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
         L.psg_opt_iteration.argtypes = [vp, C.POINTER(IterationConfig), C.POINTER(IterationInfo)]
+        LL = C.POINTER(C.c_longlong)
+        L.psg_volume_mesh_box.argtypes = [vp, C.c_float, i32p, i32p, C.POINTER(C.c_int)]
+        L.psg_volume_mesh_extract.argtypes = [vp, C.c_float, C.c_int, LL]
+        L.psg_volume_mesh_download.argtypes = [vp, vp, vp]
+        L.psg_volume_extract_mesh.argtypes = [vp, C.c_char_p, C.c_int, LL]
+        L.psg_volume_extract_pc.argtypes = [vp, C.c_char_p, LL]
+        L.psg_volume_save_sdf.argtypes = [vp, C.c_char_p]
+        L.psg_opt_extract_mesh.argtypes = [vp, C.c_char_p, C.c_int, LL]
+        L.psg_opt_save_sdf.argtypes = [vp, C.c_char_p]
+        L.psg_opt_save_pointcloud.argtypes = [vp, C.c_char_p]
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
         L.psg_opt_upsample.argtypes = [vp]
@@ -279,6 +289,42 @@ class VolumetricGradSdf:
         c = lambda a: np.ascontiguousarray(a, np.float32).reshape(-1)
         _check(lib().psg_tracker_optimize(self.h, c(K), c(pose), C.byref(cfg), out, C.byref(conv), C.byref(it)))
         return bool(conv.value), it.value, out.reshape(4, 4)
+
+    # ---- surface extraction
+    def mesh_box(self, voxel_size=0.0):
+        """Crop box of extract_mesh / saveSDF: (lo[3], hi[3]) or None when no voxel lies within sqrt(3) * vs of the surface."""
+        self._ensure()
+        lo, hi, any_ = np.zeros(3, np.int32), np.zeros(3, np.int32), C.c_int()
+        _check(lib().psg_volume_mesh_box(self.h, float(voxel_size), lo, hi, C.byref(any_)))
+        return (lo, hi) if any_.value else None
+
+    def mesh(self, white=False, voxel_size=0.0):
+        """Marching cubes on the device: (vertices 3T x 3 float32, colours 3T x 3 uint8); face t is (3t, 3t+1, 3t+2)."""
+        self._ensure()
+        nt = C.c_longlong()
+        _check(lib().psg_volume_mesh_extract(self.h, float(voxel_size), int(white), C.byref(nt)))
+        v, c = np.zeros((3 * nt.value, 3), np.float32), np.zeros((3 * nt.value, 3), np.uint8)
+        if nt.value:
+            _check(lib().psg_volume_mesh_download(self.h, v.ctypes.data, c.ctypes.data))
+        return v, c
+
+    def extract_mesh(self, filename="mesh.ply", white=False):
+        """VolumetricGradSdf::extract_mesh: the reference's PLY file; False (and no file) when there is no triangle."""
+        self._ensure()
+        nt = C.c_longlong()
+        _check(lib().psg_volume_extract_mesh(self.h, str(filename).encode(), int(white), C.byref(nt)))
+        return nt.value > 0
+
+    def extract_pc(self, filename="cloud.ply"):
+        self._ensure()
+        n = C.c_longlong()
+        _check(lib().psg_volume_extract_pc(self.h, str(filename).encode(), C.byref(n)))
+        return True
+
+    def saveSDF(self, filename="sdf.sdf"):
+        self._ensure()
+        _check(lib().psg_volume_save_sdf(self.h, str(filename).encode()))
+        return True
 
     def update_raw(self, color_u8, depth_u16, depth_unit, K, R, t, NEst: "NormalEstimator"):
         """load_color + load_depth + NEst->compute + update() from the loader's raw pixels (psg_volume_integrate_raw)."""
@@ -439,6 +485,24 @@ class Optimizer:
         a = np.zeros((self.S, 8), np.float32)
         _check(lib().psg_opt_get_surface_voxels(self.h, a))
         return a
+
+    # Optimizer::extract_mesh / save_white_mesh / save_pointcloud / saveSDF (OptimizerAux.cpp:278-577); the reference prefixes
+    # save_path_ and appends _mesh.ply / _obj.ply / _pointcloud.ply itself, here the caller passes the whole file name
+    def extract_mesh(self, filename, white=False):
+        nt = C.c_longlong()
+        _check(lib().psg_opt_extract_mesh(self.h, str(filename).encode(), int(white), C.byref(nt)))
+        return nt.value > 0
+
+    def save_white_mesh(self, filename):
+        return self.extract_mesh(filename, white=True)
+
+    def save_pointcloud(self, filename):
+        _check(lib().psg_opt_save_pointcloud(self.h, str(filename).encode()))
+        return True
+
+    def saveSDF(self, filename):
+        _check(lib().psg_opt_save_sdf(self.h, str(filename).encode()))
+        return True
 
     def vis_keyframes(self):
         v = np.zeros(self.S, np.uint64)

@@ -5,8 +5,8 @@
 // LedOptimizer::alternatingOptimize (LedOptimizer.cpp:279-478): block order (SH: albedo, light, distance, pose;
 // LED: light, albedo, distance, pose), one-off rescaling of the regulariser weights by E / E_reg, convergence and
 // divergence tests on the total energy after the last enabled block, upsampling at iteration 5, optimizer_doc.txt,
-// and the every-third-iteration dumps (Optimizer::savePoses / save_pointcloud, OptimizerAux.cpp:456-511, 580-599).
-// Meshes (marching cubes) are not written.
+// and the every-third-iteration dumps (Optimizer::savePoses / save_pointcloud / extract_mesh, OptimizerAux.cpp:278-362, 456-511,
+// 580-599; the meshes come from mesh.cu).
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -116,30 +116,26 @@ bool save_pointcloud(psg_optimizer* o, const std::string& path) {
     return true;
 }
 
-// Optimizer::saveSDF (OptimizerAux.cpp:513-577): cropped box of -dist values
+// Optimizer::saveSDF (OptimizerAux.cpp:513-577): cropped box of -dist values; only the box leaves the device (mesh.cu)
 bool save_sdf(psg_optimizer* o, const std::string& path) {
-    psg_volume* v = o->vol;
-    std::vector<float> aos((size_t)v->N * 8);
-    if (psg_volume_download(v, aos.data()) != PSG_OK) return false;
-    const double thr = std::sqrt(3.0) * (double)o->vs;
-    int lo[3] = { 1 << 30, 1 << 30, 1 << 30 }, hi[3] = { -(1 << 30), -(1 << 30), -(1 << 30) };
-    size_t l = 0;
-    for (int k = 0; k < v->dims[2]; ++k) for (int j = 0; j < v->dims[1]; ++j) for (int i = 0; i < v->dims[0]; ++i, ++l) {
-        if (std::fabs((double)aos[l * 8]) > thr) continue;
-        const int idx[3] = { i, j, k };
-        for (int a = 0; a < 3; ++a) { if (idx[a] < lo[a]) lo[a] = idx[a]; if (idx[a] > hi[a]) hi[a] = idx[a]; }
-    }
-    std::ofstream f(path.c_str());
-    if (!f.is_open()) return false;
-    f << hi[0] - lo[0] + 1 << " " << hi[1] - lo[1] + 1 << " " << hi[2] - lo[2] + 1 << "\n";
-    f << (float)lo[0] * o->vs << " " << (float)lo[1] * o->vs << " " << (float)lo[2] * o->vs << "\n";
-    f << o->vs << "\n";
-    for (int k = lo[2]; k <= hi[2]; ++k) for (int j = lo[1]; j <= hi[1]; ++j) for (int i = lo[0]; i <= hi[0]; ++i)
-        f << -aos[((size_t)i + (size_t)v->dims[0] * j + (size_t)v->dims[0] * v->dims[1] * k) * 8] << "\n";
-    return true;
+    try { bool any = false; return psg::write_sdf_file(o->vol, o->vs, path.c_str(), &any) && any; }
+    catch (const psg::CudaError&) { return false; }
+}
+
+// Optimizer::extract_mesh (OptimizerAux.cpp:278-362): <name>_mesh.ply, marching cubes on the device
+bool save_mesh(psg_optimizer* o, const std::string& path) {
+    try { long long nt = 0; return psg::write_mesh_file(o->vol, o->vs, path.c_str(), 0, &nt) && nt > 0; }
+    catch (const psg::CudaError&) { return false; }
 }
 
 }  // namespace
+
+extern "C" int psg_opt_save_pointcloud(psg_optimizer* o, const char* filename) {
+    if (!o || !filename) { psg::set_error("psg_opt_save_pointcloud: null argument"); return PSG_ERR_INVALID; }
+    if (!o->inited) { psg::set_error("psg_opt_save_pointcloud: psg_opt_init has not run"); return PSG_ERR_STATE; }
+    if (!save_pointcloud(o, filename)) { psg::set_error("psg_opt_save_pointcloud: cannot write %s", filename); return PSG_ERR_INVALID; }
+    return PSG_OK;
+}
 
 extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_config* cfg, const char* save_path,
                                             psg_loop_result* res) {
@@ -250,6 +246,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
         if (verdict) {
             if (files) {
                 save_pointcloud(o, out + "final_refined_pointcloud.ply");
+                save_mesh(o, out + "final_refined_mesh.ply");
                 if (led) save_sdf(o, out + "refined_sdf.sdf");
             }
             ++iter;
@@ -262,7 +259,10 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
             psg_opt_set_reg(o, reg);
             laplacian_reg = true;
             PSG_RUN(psg_opt_upsample(o));
-            if (files) save_pointcloud(o, out + "upsample_after_" + std::to_string(iter) + "_pointcloud.ply");
+            if (files) {
+                save_pointcloud(o, out + "upsample_after_" + std::to_string(iter) + "_pointcloud.ply");
+                save_mesh(o, out + "upsample_after_" + std::to_string(iter) + "_mesh.ply");
+            }
             if (file.is_open()) file << "===> [" << iter << "]: after pose optimization: \n";
             PSG_RUN(psg_opt_reg_energies(o, nullptr, &dl, nullptr));
             e.El = (float)dl;
@@ -282,6 +282,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
         if (iter % 3 == 0 && files) {
             save_poses(o, out + "after_poses_opt_" + std::to_string(iter) + ".txt", {});
             save_pointcloud(o, out + "after_iter_" + std::to_string(iter) + "_pointcloud.ply");
+            save_mesh(o, out + "after_iter_" + std::to_string(iter) + "_mesh.ply");
         }
     }
 #undef PSG_RUN

@@ -19,7 +19,7 @@ enum KernelId {
     KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
     KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
     KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
-    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_COUNT
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_MESH, KID_COUNT
 };
 // Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
 struct Prof {
@@ -74,6 +74,12 @@ struct psg_volume {
     psg::DevBuf<float> track_depth;          // rigid tracker: current frame's depth in metres
     psg::DevBuf<double> track_partials;
     int track_H = 0, track_W = 0;
+    // surface extraction (mesh.cu): per-block counts / offsets, crop box, and the triangles of the last extraction
+    psg::DevBuf<unsigned> mesh_counts;
+    psg::DevBuf<int> mesh_box;
+    psg::DevBuf<float> mesh_vertices;        // 9 floats per triangle
+    psg::DevBuf<unsigned char> mesh_colors;  // 9 bytes per triangle
+    long long mesh_triangles = -1;           // -1: nothing extracted yet
     cudaStream_t stream = nullptr;
     psg::VolView view() const;
 };
@@ -193,6 +199,10 @@ void launch_dist_sweep(psg_optimizer* o, int flags, int slot);
 void launch_energy(psg_optimizer* o, int slot);
 void launch_reg_energies(psg_optimizer* o, int slot);
 void reg_energies(psg_optimizer* o, double* En, double* El, double* Er);
+
+// ---- mesh.cu
+bool write_mesh_file(psg_volume* v, float vs, const char* path, int white, long long* n_triangles);   // false: file not opened
+bool write_sdf_file(psg_volume* v, float vs, const char* path, bool* any);
 
 // ---- pcg.cu
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot);   // fused assemble + PCG + update (+ reg energies)

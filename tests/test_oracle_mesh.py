@@ -86,7 +86,7 @@ def test_writers_vs_reference_files(model, tmp_path):
     dims = [G, G, G]
     words, lengths = rv.vis(1)
     seen = (words.reshape(-1) != 0).astype(np.uint8)
-    assert ro.extract_mesh("a") and ro.save_white_mesh("a") and ro.save_sdf("a.sdf")
+    assert ro.extract_mesh("a") and ro.save_white_mesh("a") and ro.save_sdf("a.sdf") and ro.save_pointcloud("a")
     assert rv.extract_mesh(str(tmp_path / "v_mesh.ply")) and rv.extract_pc(str(tmp_path / "v_pc.ply"))
     v, c = pyoracle.extract_mesh(aos, dims, vs)
     vw, cw = pyoracle.extract_mesh(aos, dims, vs, white=True)
@@ -95,7 +95,9 @@ def test_writers_vs_reference_files(model, tmp_path):
     assert pyoracle.write_mesh_ply(str(tmp_path / "o_obj.ply"), vw, cw)
     assert pyoracle.write_sdf(str(tmp_path / "o.sdf"), aos, dims, vs)
     assert pyoracle.write_volume_pc(str(tmp_path / "o_pc.ply"), aos, seen, dims, vs)
+    assert pyoracle.write_surface_pc(str(tmp_path / "o_spc.ply"), aos, ro.surface(), dims, vs)
     rd = lambda n: open(tmp_path / n, "rb").read()
+    assert rd("a_pointcloud.ply") == rd("o_spc.ply")
     assert rd("a_mesh.ply") == rd("o_mesh.ply")
     assert rd("a_obj.ply") == rd("o_obj.ply")
     assert rd("v_mesh.ply") == rd("o_mesh.ply")

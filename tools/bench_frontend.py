@@ -6,6 +6,7 @@
 Prints one JSON line: ms per frame for (a) psg_volume_integrate_raw -- 16-bit depth + 8-bit colour from pinned host memory,
 conversions + FALS normals + fusion on the device, (b) psg_volume_integrate fed with float planes computed on the host,
 the device time of the kernels involved (launch profiler), algorithmic bytes and the fraction of the measured HBM peak, and
+the device marching cubes of the fused volume (next-4) with the CPU restatement's time beside it, and
 the CPU restatement's time for the normal estimation alone (oracle/psg_oracle_normals.c, 1 thread -- what the reference
 spends in OpenCV per frame before it can call update()).
 """
@@ -102,6 +103,27 @@ def main():
         Eo, go_, Ho, co = ov.tracker_system(host[1][1], sc.K, Rs[1], ts[1], 1)
         trk_cpu = 1e3 * (time.perf_counter() - t0)
         assert co == ct
+    # surface extraction (next-4): crop box + marching cubes on the device, triangles to the host; the CPU restatement beside it
+    torch.cuda.synchronize()
+    vt.mesh()                                    # warm-up (allocations)
+    psg.profile_reset(); psg.profile_enable(True)
+    t0 = time.perf_counter()
+    for _ in range(10):
+        mv, mc_ = vt.mesh()
+    mesh_ms = 1e3 * (time.perf_counter() - t0) / 10
+    tabm = psg.profile_table(); psg.profile_enable(False)
+    box = vt.mesh_box()
+    box_voxels = int(np.prod(box[1] - box[0] + 1)) if box is not None else 0
+    t0 = time.perf_counter()
+    vt.extract_mesh("/tmp/psg_bench_mesh.ply")
+    mesh_file_ms = 1e3 * (time.perf_counter() - t0)
+    mesh_cpu = None
+    if G <= 256:
+        aos = vt.download()
+        t0 = time.perf_counter()
+        mo = pyoracle.extract_mesh(aos, [G, G, G], vs)
+        mesh_cpu = 1e3 * (time.perf_counter() - t0)
+        assert np.array_equal(mo[0], mv) and np.array_equal(mo[1], mc_)
     vt.close()
     peak = 6555.8
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -117,6 +139,11 @@ def main():
            "kernel_us_raw": raw_k, "kernel_us_float": flt_k, "voxels": N, "voxels_touched_by_any_frame": touched,
            "tracker_pass_ms": round(trk_ms, 4), "tracker_kernel_us": {k: round(1e3 * t / n, 2) for k, (n, t) in tabt.items()},
            "tracker_pixels_hit": int(ct), "tracker_cpu_pass_ms": None if trk_cpu is None else round(trk_cpu, 2),
+           "mesh": {"triangles": int(len(mv) // 3), "crop_box_voxels": box_voxels, "ms_device_to_host_arrays": round(mesh_ms, 3),
+                    "kernel_us_per_extraction": round(1e3 * sum(t for _, t in tabm.values()) / 10, 1),
+                    "ms_with_ascii_ply_file": round(mesh_file_ms, 1), "cpu_marching_cubes_ms": None if mesh_cpu is None else round(mesh_cpu, 1),
+                    # both passes read dist + weight of every cell corner once (8 B per voxel of the crop box, neighbours from L1 / L2)
+                    "algorithmic_bytes": 2 * 8 * box_voxels + 45 * int(len(mv) // 3)},
            "k_integrate": {"algorithmic_bytes_upper_bound": 72 * touched, "achieved_GBps": round(72 * touched / (fuse_us * 1e-6) / 1e9, 1) if fuse_us else None,
                            "peak_GBps": peak}}
     print(json.dumps(out))
