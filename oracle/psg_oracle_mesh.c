@@ -26,7 +26,7 @@ static const int kEdgeV[12][6] = {
     {1, 1, 0, 1, 0, 0}, {1, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 1, 0}, {0, 1, 0, 1, 1, 0},
     {1, 1, 1, 1, 0, 1}, {1, 0, 1, 0, 0, 1}, {0, 0, 1, 0, 1, 1}, {0, 1, 1, 1, 1, 1},
     {1, 1, 0, 1, 1, 1}, {1, 0, 0, 1, 0, 1}, {0, 0, 0, 0, 0, 1}, {0, 1, 0, 0, 1, 1}};
-/* ... and to getColor: edges 2, 3, 5, 6, 7 pass their two corners the other way round (:374,386,410,422,434) */
+/* ... and to getColor: edges 2, 3, 6, 7 pass their two corners the other way round (:374,386,422,434) */
 static const int kEdgeC[12][6] = {
     {1, 1, 0, 1, 0, 0}, {1, 0, 0, 0, 0, 0}, {0, 1, 0, 0, 0, 0}, {1, 1, 0, 0, 1, 0},
     {1, 1, 1, 1, 0, 1}, {1, 0, 1, 0, 0, 1}, {0, 1, 1, 0, 0, 1}, {1, 1, 1, 0, 1, 1},

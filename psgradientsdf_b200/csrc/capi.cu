@@ -26,7 +26,7 @@ static const char* const kKernelNames[KID_COUNT] = {
     "k_fill_volume", "k_pack_frame", "k_integrate", "k_aos_soa", "k_surface_mask", "k_scan_counts", "k_surface_scatter",
     "k_neighbors", "k_upsample", "k_sweep<ENERGY>", "k_sweep<INIT_ALBEDO>", "k_sweep<LED_INIT>", "k_sweep<PROBE>",
     "k_sweep<ALBEDO>", "k_sweep<LIGHT>", "k_sweep<POSE>", "k_sweep<DIST>", "k_reg_energy", "k_dist_assemble", "k_dist_pcg",
-    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather", "k_track", "k_mesh" };
+    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather", "k_track", "k_mesh_bbox", "k_mesh_cells<count>", "k_mesh_scan", "k_mesh_cells<emit>", "k_mesh_misc" };
 static bool g_prof_on = false;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof_recs;
@@ -278,7 +278,7 @@ int psg_volume_destroy(psg_volume* v) {
     for (int a = 0; a < 8; ++a) v->f[a].release();
     v->vis.release(); v->frame.release(); v->staging.release();
     v->brick_list.release(); v->tiles.release(); v->track_depth.release(); v->track_partials.release();
-    v->mesh_counts.release(); v->mesh_box.release(); v->mesh_vertices.release(); v->mesh_colors.release();
+    v->mesh_counts.release(); v->mesh_crossed.release(); v->mesh_box.release(); v->mesh_vertices.release(); v->mesh_colors.release();
     if (v->stream) cudaStreamDestroy(v->stream);
     delete v;
     return PSG_OK;

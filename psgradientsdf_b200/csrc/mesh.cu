@@ -35,7 +35,8 @@ constexpr int kCellsPerBlock = 1024;   // four rounds of 256 threads; one count 
 
 struct MeshView {
     const float* dist; const float* w; const float* r; const float* g; const float* b;
-    int W; long long WH;       // volume strides
+    int W, WH;                 // volume strides (every voxel index fits an int: psg_volume_create keeps N below 2^31)
+    int lin0;                  // voxel index of the crop box's lower corner
     int lo[3];                 // lower corner of the crop box in the volume
     int bd[3];                 // crop box dimensions
     int cd[3];                 // cells per axis: bd - 2 (the reference's loops stop at dim - 2, MarchingCubes.cpp:333-337)
@@ -45,8 +46,9 @@ struct MeshView {
 };
 
 // ---- crop box ------------------------------------------------------------------------------------------------------------------
-// One warp per x-row of the volume; box[0..2] = lower corner (atomicMin), box[3..5] = upper corner (atomicMax).
-__global__ void __launch_bounds__(256) k_mesh_bbox(const float* __restrict__ dist, int W, int H, int D, double thr, int* __restrict__ box) {
+// One warp per x-row of the volume; box[0..2] = lower corner (atomicMin), box[3..5] = upper corner (atomicMax).  thr is the
+// largest float <= sqrt(3) * vs: for a float x, x > thr decides exactly like the reference's double comparison x > sqrt(3) * vs.
+__global__ void __launch_bounds__(256) k_mesh_bbox(const float* __restrict__ dist, int W, int H, int D, float thr, int* __restrict__ box) {
     const int lane = threadIdx.x & 31;
     const long long rows = (long long)H * D;
     int ilo = INT_MAX, ihi = INT_MIN, jlo = INT_MAX, jhi = INT_MIN, klo = INT_MAX, khi = INT_MIN;
@@ -54,15 +56,33 @@ __global__ void __launch_bounds__(256) k_mesh_bbox(const float* __restrict__ dis
         const int j = (int)(row % H), k = (int)(row / H);
         const float* p = dist + row * W;
         bool any = false;
-        for (int i = lane; i < W; i += 32) {
-            if (!(fabs((double)p[i]) > thr)) { any = true; ilo = min(ilo, i); ihi = max(ihi, i); }
+        if ((W & 3) == 0) {                      // rows are 16-byte aligned: four voxels per load
+            const float4* p4 = reinterpret_cast<const float4*>(p);
+#pragma unroll 4
+            for (int q = lane; q < (W >> 2); q += 32) {
+                const float4 d = p4[q];
+                const float dv[4] = { d.x, d.y, d.z, d.w };
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (!(fabsf(dv[c]) > thr)) { any = true; ilo = min(ilo, 4 * q + c); ihi = max(ihi, 4 * q + c); }
+            }
+        } else {
+            for (int i = lane; i < W; i += 32) {
+                if (!(fabsf(p[i]) > thr)) { any = true; ilo = min(ilo, i); ihi = max(ihi, i); }
+            }
         }
         if (__any_sync(0xffffffffu, any)) { jlo = min(jlo, j); jhi = max(jhi, j); klo = min(klo, k); khi = max(khi, k); }
     }
     ilo = __reduce_min_sync(0xffffffffu, ilo); ihi = __reduce_max_sync(0xffffffffu, ihi);
     if (lane == 0 && ihi >= ilo) {
-        atomicMin(box + 0, ilo); atomicMin(box + 1, jlo); atomicMin(box + 2, klo);
-        atomicMax(box + 3, ihi); atomicMax(box + 4, jhi); atomicMax(box + 5, khi);
+        // the box only grows: an atomic is needed only where this warp would still move a face (a stale read errs on the safe side)
+        const volatile int* cur = box;
+        if (ilo < cur[0]) atomicMin(box + 0, ilo);
+        if (jlo < cur[1]) atomicMin(box + 1, jlo);
+        if (klo < cur[2]) atomicMin(box + 2, klo);
+        if (ihi > cur[3]) atomicMax(box + 3, ihi);
+        if (jhi > cur[4]) atomicMax(box + 4, jhi);
+        if (khi > cur[5]) atomicMax(box + 5, khi);
     }
 }
 
@@ -74,13 +94,13 @@ __global__ void k_mesh_box_init(int* box) {
 // ---- marching cubes ------------------------------------------------------------------------------------------------------------
 // corner b of a cell at (x, y, z): bit 0 (x+1, y+1, z), 1 (x+1, y, z), 2 (x, y, z), 3 (x, y+1, z), 4..7 the same at z+1
 // (MarchingCubes::computeLutIndex, :549-585); edge e joins corners kEdgeA[e] -> kEdgeB[e] in the order getVertex receives them
-// (:342-506); getColor receives edges 2, 3, 5, 6, 7 the other way round.
+// (:342-506); getColor receives edges 2, 3, 6, 7 the other way round.
 __device__ __forceinline__ int corner_dx(int b) { return (0x33 >> b) & 1; }
 __device__ __forceinline__ int corner_dy(int b) { return (0x99 >> b) & 1; }
 __device__ __forceinline__ int corner_dz(int b) { return b >> 2; }
 __device__ __forceinline__ int edge_first(int e) { return e < 8 ? e : e - 8; }
 __device__ __forceinline__ int edge_second(int e) { return e < 4 ? ((e + 1) & 3) : e < 8 ? 4 + ((e + 1) & 3) : e - 4; }
-constexpr unsigned kColorSwapped = 0x0EC;   // edges 2, 3, 5, 6, 7
+constexpr unsigned kColorSwapped = 0x0CC;   // edges 2, 3, 6, 7 (MarchingCubes.cpp:374,386,422,434)
 
 // MarchingCubes::interpolate (:589-609) with isoValue = 0.0f (every caller's default)
 __device__ __forceinline__ void mc_interp(float t0, float t1, const float v0[3], const float v1[3], float out[3]) {
@@ -95,146 +115,205 @@ __device__ __forceinline__ void mc_interp(float t0, float t1, const float v0[3],
 }
 
 // the 8-bit colour the crop copy would hold: int(255 * c) stored to an unsigned char (OptimizerAux.cpp:335-337)
-__device__ __forceinline__ float crop_color(const float* __restrict__ plane, long long lin, int white) {
+__device__ __forceinline__ float crop_color(const float* __restrict__ plane, int lin, int white) {
     return white ? 255.0f : (float)(unsigned char)(int)__fmul_rn(255.0f, plane[lin]);
 }
 
-// volume index of entry (idx + k) of the cropped array, idx the crop index of box cell corner (x, y, z), k = 0..2
-__device__ __forceinline__ long long crop_shift(const MeshView& m, int x, int y, int z, int k) {
+// volume index of entry (idx + k) of the cropped array, idx the crop index of box voxel (x, y, z), k = 0..2
+__device__ __forceinline__ int crop_shift(const MeshView& m, int x, int y, int z, int k) {
     x += k;
     if (x >= m.bd[0]) { x -= m.bd[0]; ++y; }   // corners have y <= bd[1] - 2: no second wrap
-    return (long long)(m.lo[0] + x) + (long long)m.W * (m.lo[1] + y) + m.WH * (m.lo[2] + z);
+    return m.lin0 + x + m.W * y + m.WH * z;
 }
 
-struct CellTris {
-    int n;                    // triangles kept
-    float p[5][3][3];
-    unsigned char c[5][3][3];
-};
+// offset of corner b from a cell's (x, y, z) voxel
+__device__ __forceinline__ int corner_off(const MeshView& m, int b) { return corner_dx(b) + m.W * corner_dy(b) + m.WH * corner_dz(b); }
 
-// One cell: cube case, edge vertices (and colours when EMIT), the non-degenerate triangles (computeTriangles, :613-641).
-template <bool EMIT>
-__device__ int mesh_cell(const MeshView& m, int x, int y, int z, CellTris* out) {
-    const long long base = (long long)(m.lo[0] + x) + (long long)m.W * (m.lo[1] + y) + m.WH * (m.lo[2] + z);
-    float t[8];
+// MarchingCubes::computeLutIndex (:549-585): 0 when any corner was never fused (weight 0), else bit b = tsdf > 0 at corner b.
+// All sixteen loads are issued before the first test (the reference's short-circuit has no side effect to preserve).
+__device__ __forceinline__ int cell_case(const MeshView& m, int base) {
+    const float* __restrict__ wp = m.w + base;
+    const float* __restrict__ dp = m.dist + base;
+    float w[8], d[8];
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        const long long l = base + corner_dx(b) + (long long)m.W * corner_dy(b) + m.WH * corner_dz(b);
-        if (m.w[l] == 0.0f) return 0;
-    }
+    for (int b = 0; b < 8; ++b) { const int o = corner_off(m, b); w[b] = wp[o]; d[b] = dp[o]; }
     int ci = 0;
+    bool seen = true;
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        const long long l = base + corner_dx(b) + (long long)m.W * corner_dy(b) + m.WH * corner_dz(b);
-        t[b] = -m.dist[l];
-        if (t[b] > 0.0f) ci |= 1 << b;
-    }
-    if (ci == 0 || ci == 255) return 0;
-    const unsigned long long tri = d_tri[ci];
-    unsigned need = 0;
-    for (unsigned long long q = tri; (q & 0xF) != 0xF; q >>= 4) need |= 1u << (q & 0xF);
-    float ep[12][3];
-    unsigned char ec[12][3];
-    for (int e = 0; e < 12; ++e) {
-        if (!(need >> e & 1)) continue;
-        const int a = edge_first(e), b = edge_second(e);
-        const int ax = x + corner_dx(a), ay = y + corner_dy(a), az = z + corner_dz(a);
-        const int bx = x + corner_dx(b), by = y + corner_dy(b), bz = z + corner_dz(b);
-        const float pa[3] = { __fsub_rn(__fmul_rn((float)ax, m.vsz[0]), m.org[0]), __fsub_rn(__fmul_rn((float)ay, m.vsz[1]), m.org[1]),
-                              __fsub_rn(__fmul_rn((float)az, m.vsz[2]), m.org[2]) };
-        const float pb[3] = { __fsub_rn(__fmul_rn((float)bx, m.vsz[0]), m.org[0]), __fsub_rn(__fmul_rn((float)by, m.vsz[1]), m.org[1]),
-                              __fsub_rn(__fmul_rn((float)bz, m.vsz[2]), m.org[2]) };
-        mc_interp(t[a], t[b], pa, pb, ep[e]);
-        if (EMIT) {
-            const bool sw = (kColorSwapped >> e) & 1;
-            const int c1 = sw ? b : a, c2 = sw ? a : b;
-            const int x1 = x + corner_dx(c1), y1 = y + corner_dy(c1), z1 = z + corner_dz(c1);
-            const int x2 = x + corner_dx(c2), y2 = y + corner_dy(c2), z2 = z + corner_dz(c2);
-            const float k1[3] = { __fdiv_rn(crop_color(m.r, crop_shift(m, x1, y1, z1, 0), m.white), 255.0f),
-                                  __fdiv_rn(crop_color(m.g, crop_shift(m, x1, y1, z1, 1), m.white), 255.0f),
-                                  __fdiv_rn(crop_color(m.b, crop_shift(m, x1, y1, z1, 2), m.white), 255.0f) };
-            const float k2[3] = { __fdiv_rn(crop_color(m.r, crop_shift(m, x2, y2, z2, 0), m.white), 255.0f),
-                                  __fdiv_rn(crop_color(m.g, crop_shift(m, x2, y2, z2, 1), m.white), 255.0f),
-                                  __fdiv_rn(crop_color(m.b, crop_shift(m, x2, y2, z2, 2), m.white), 255.0f) };
-            float cv[3];
-            mc_interp(t[c1], t[c2], k1, k2, cv);
-#pragma unroll
-            for (int a3 = 0; a3 < 3; ++a3) ec[e][a3] = (unsigned char)(int)__fmul_rn(cv[a3], 255.0f);
-        }
-    }
-    int n = 0;
-    for (unsigned long long q = tri; (q & 0xF) != 0xF; q >>= 12) {
-        const int e0 = (int)(q & 0xF), e1 = (int)((q >> 4) & 0xF), e2 = (int)((q >> 8) & 0xF);
-        const float *p1 = ep[e0], *p2 = ep[e1], *p3 = ep[e2];
-        const bool ne12 = p1[0] != p2[0] || p1[1] != p2[1] || p1[2] != p2[2];
-        const bool ne13 = p1[0] != p3[0] || p1[1] != p3[1] || p1[2] != p3[2];
-        const bool ne23 = p2[0] != p3[0] || p2[1] != p3[1] || p2[2] != p3[2];
-        if (!(ne12 && ne13 && ne23)) continue;
-        if (EMIT) {
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                out->p[n][0][a] = p1[a]; out->p[n][1][a] = p2[a]; out->p[n][2][a] = p3[a];
-                out->c[n][0][a] = ec[e0][a]; out->c[n][1][a] = ec[e1][a]; out->c[n][2][a] = ec[e2][a];
-            }
-        }
-        ++n;
-    }
-    return n;
+    for (int b = 0; b < 8; ++b) { seen = seen && !(w[b] == 0.0f); if (d[b] < 0.0f) ci |= 1 << b; }   // -d > 0.0f
+    return seen ? ci : 0;
+}
+
+constexpr int kChunk = 64;   // active cells whose edges sit in shared memory at a time
+
+// cell o (< kCellsPerBlock) after the block's first cell (x0, y0, z0), in x, y, z order; 32-bit arithmetic only
+__device__ __forceinline__ void cell_xyz(const MeshView& m, int x0, int y0, int z0, unsigned o, int& x, int& y, int& z) {
+    const unsigned xo = (unsigned)x0 + o, cy = xo / (unsigned)m.cd[0];
+    x = (int)(xo - cy * (unsigned)m.cd[0]);
+    const unsigned yo = (unsigned)y0 + cy, cz = yo / (unsigned)m.cd[1];
+    y = (int)(yo - cz * (unsigned)m.cd[1]);
+    z = z0 + (int)cz;
+}
+// the cell 256 further on
+__device__ __forceinline__ void cell_advance(const MeshView& m, int& x, int& y, int& z) {
+    x += 256;
+    if (x < m.cd[0]) return;
+    if (m.cd[0] >= 128) { do { x -= m.cd[0]; ++y; } while (x >= m.cd[0]); }
+    else { const unsigned q = (unsigned)x / (unsigned)m.cd[0]; x -= (int)q * m.cd[0]; y += (int)q; }
+    if (y >= m.cd[1]) { const unsigned q = (unsigned)y / (unsigned)m.cd[1]; y -= (int)q * m.cd[1]; z += (int)q; }
 }
 
 // Count pass (EMIT = false): triangles per block of kCellsPerBlock cells -> counts[blockIdx.x].
 // Emit pass (EMIT = true): counts[] holds the exclusive scan; every triangle is written at its serial position.
+//
+// A block first classifies its 1024 cells (one cell per thread, four rounds) and compacts the ones the surface crosses, in cell
+// order, into shared memory -- a few dozen out of 1024.  Those are then worked on by the whole block: one thread per (cell, edge)
+// interpolates the vertex (and its colour when emitting) into shared memory, one thread per cell drops the degenerate triangles
+// (computeTriangles, :613-641) and takes part in the scan that gives the cell its output position, one thread per
+// (cell, triangle, vertex) writes.  The serial reference order -- cells in x, y, z order, triangles in table order -- is the order
+// of the compaction and of the scans.
 template <bool EMIT>
-__global__ void __launch_bounds__(256) k_mesh_cells(MeshView m, unsigned* __restrict__ counts, float* __restrict__ vertices,
-                                                    unsigned char* __restrict__ colors) {
-    __shared__ unsigned s_warp[8];
+__global__ void __launch_bounds__(256) k_mesh_cells(MeshView m, unsigned* __restrict__ counts, unsigned* __restrict__ crossed,
+                                                    float* __restrict__ vertices, unsigned char* __restrict__ colors) {
+    __shared__ unsigned long long s_list[kCellsPerBlock]; // x | y << 16 | z << 32 | case << 48 of the crossed cells, in cell order
+    __shared__ unsigned s_cnt[4 * 8 + 1];                 // active cells per (round, warp), then their exclusive scan
+    __shared__ float s_ep[kChunk][12][3];
+    __shared__ unsigned char s_ec[kChunk][12][3];
+    __shared__ unsigned s_keep[kChunk], s_off[kChunk], s_wsum[2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long c0 = (long long)blockIdx.x * kCellsPerBlock;
-    unsigned running = 0, mine = 0;
+    unsigned running = 0;
     if (EMIT) {
         running = counts[blockIdx.x];
         if (counts[blockIdx.x + 1] == running) return;      // nothing in this block (the common case away from the surface)
     }
     const long long cxy = (long long)m.cd[0] * m.cd[1];
-    for (int round = 0; round < kCellsPerBlock / 256; ++round) {
-        const long long c = c0 + round * 256 + threadIdx.x;
-        int n = 0;
-        CellTris tris;
-        if (c < m.ncells) {
-            const int z = (int)(c / cxy);
-            const long long rem = c - (long long)z * cxy;
-            const int y = (int)(rem / m.cd[0]), x = (int)(rem - (long long)y * m.cd[0]);
-            n = mesh_cell<EMIT>(m, x, y, z, &tris);
-        }
-        if (!EMIT) { mine += n; continue; }
-        unsigned inc = n;
+    const int z0 = (int)(c0 / cxy);
+    const int y0 = (int)((c0 - (long long)z0 * cxy) / m.cd[0]), x0 = (int)(c0 - (long long)z0 * cxy - (long long)y0 * m.cd[0]);
+    // ---- classify and compact
+    int my_case[4]; unsigned my_rank[4];
+    int cx, cy, cz;
+    cell_xyz(m, x0, y0, z0, threadIdx.x, cx, cy, cz);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-        if (lane == 31) s_warp[warp] = inc;
+    for (int round = 0; round < 4; ++round) {
+        int ci = 0;
+        // the count pass leaves one bit per cell ("the surface crosses it"); the emit pass classifies those cells only
+        const size_t word = (size_t)blockIdx.x * 32 + round * 8 + warp;
+        const bool look = EMIT ? ((crossed[word] >> lane) & 1u) != 0u : c0 + round * 256 + threadIdx.x < m.ncells;
+        if (look) {
+            ci = cell_case(m, m.lin0 + cx + m.W * cy + m.WH * cz);
+            if (ci == 255) ci = 0;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, ci != 0);
+        if (!EMIT && lane == 0) crossed[word] = bal;
+        my_case[round] = ci;
+        my_rank[round] = __popc(bal & ((1u << lane) - 1u));
+        if (lane == 0) s_cnt[round * 8 + warp] = __popc(bal);
+        if (round < 3) cell_advance(m, cx, cy, cz);
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned x = s_cnt[lane];
+        unsigned inc = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+        s_cnt[lane] = inc - x;
+        if (lane == 31) s_cnt[32] = inc;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int round = 0; round < 4; ++round)
+        if (my_case[round]) {
+            int x, y, z;
+            cell_xyz(m, x0, y0, z0, (unsigned)(round * 256 + threadIdx.x), x, y, z);
+            s_list[s_cnt[round * 8 + warp] + my_rank[round]] = (unsigned long long)x | ((unsigned long long)y << 16) | ((unsigned long long)z << 32) |
+                                                                ((unsigned long long)my_case[round] << 48);
+        }
+    const int n_active = (int)s_cnt[32];
+    __syncthreads();
+    // ---- the active cells, kChunk at a time
+    unsigned block_total = 0;
+    for (int j0 = 0; j0 < n_active; j0 += kChunk) {
+        const int nj = min(kChunk, n_active - j0);
+        // one thread per (cell, edge)
+        for (int q = threadIdx.x; q < nj * 12; q += 256) {
+            const int j = q / 12, e = q - 12 * j;
+            const unsigned long long ent = s_list[j0 + j];
+            const int ci = (int)(ent >> 48);
+            const int a = edge_first(e), b = edge_second(e);
+            if (!(((ci >> a) ^ (ci >> b)) & 1)) continue;           // the surface does not cross this edge
+            const int x = (int)(ent & 0xFFFF), y = (int)((ent >> 16) & 0xFFFF), z = (int)((ent >> 32) & 0xFFFF);
+            const int base = m.lin0 + x + m.W * y + m.WH * z;
+            const float ta = -m.dist[base + corner_off(m, a)], tb = -m.dist[base + corner_off(m, b)];
+            const int ax = x + corner_dx(a), ay = y + corner_dy(a), az = z + corner_dz(a);
+            const int bx = x + corner_dx(b), by = y + corner_dy(b), bz = z + corner_dz(b);
+            // MarchingCubes::voxelToWorld (:646-650)
+            const float pa[3] = { __fsub_rn(__fmul_rn((float)ax, m.vsz[0]), m.org[0]), __fsub_rn(__fmul_rn((float)ay, m.vsz[1]), m.org[1]),
+                                  __fsub_rn(__fmul_rn((float)az, m.vsz[2]), m.org[2]) };
+            const float pb[3] = { __fsub_rn(__fmul_rn((float)bx, m.vsz[0]), m.org[0]), __fsub_rn(__fmul_rn((float)by, m.vsz[1]), m.org[1]),
+                                  __fsub_rn(__fmul_rn((float)bz, m.vsz[2]), m.org[2]) };
+            float p[3];
+            mc_interp(ta, tb, pa, pb, p);
+            s_ep[j][e][0] = p[0]; s_ep[j][e][1] = p[1]; s_ep[j][e][2] = p[2];
+            if (EMIT) {
+                // MarchingCubes::getColor (:622-640)
+                const bool sw = (kColorSwapped >> e) & 1;
+                const int x1 = sw ? bx : ax, y1 = sw ? by : ay, z1 = sw ? bz : az;
+                const int x2 = sw ? ax : bx, y2 = sw ? ay : by, z2 = sw ? az : bz;
+                const float k1[3] = { __fdiv_rn(crop_color(m.r, crop_shift(m, x1, y1, z1, 0), m.white), 255.0f),
+                                      __fdiv_rn(crop_color(m.g, crop_shift(m, x1, y1, z1, 1), m.white), 255.0f),
+                                      __fdiv_rn(crop_color(m.b, crop_shift(m, x1, y1, z1, 2), m.white), 255.0f) };
+                const float k2[3] = { __fdiv_rn(crop_color(m.r, crop_shift(m, x2, y2, z2, 0), m.white), 255.0f),
+                                      __fdiv_rn(crop_color(m.g, crop_shift(m, x2, y2, z2, 1), m.white), 255.0f),
+                                      __fdiv_rn(crop_color(m.b, crop_shift(m, x2, y2, z2, 2), m.white), 255.0f) };
+                float cv[3];
+                mc_interp(sw ? tb : ta, sw ? ta : tb, k1, k2, cv);
+#pragma unroll
+                for (int a3 = 0; a3 < 3; ++a3) s_ec[j][e][a3] = (unsigned char)(int)__fmul_rn(cv[a3], 255.0f);
+            }
+        }
         __syncthreads();
-        unsigned warp_off = 0, total = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { if (i < warp) warp_off += s_warp[i]; total += s_warp[i]; }
-        const unsigned first = running + warp_off + inc - n;
-        for (int k = 0; k < n; ++k) {
-            float* vp = vertices + (size_t)(first + k) * 9;
-            unsigned char* cp = colors + (size_t)(first + k) * 9;
-#pragma unroll
-            for (int q = 0; q < 9; ++q) { vp[q] = tris.p[k][q / 3][q % 3]; cp[q] = tris.c[k][q / 3][q % 3]; }
+        // one thread per cell: which triangles survive (p1 != p2 && p1 != p3 && p2 != p3), and the cell's place in the output
+        unsigned keep = 0, n = 0;
+        if (threadIdx.x < nj) {
+            const unsigned long long tri = d_tri[s_list[j0 + threadIdx.x] >> 48];
+            int k = 0;
+            for (unsigned long long q = tri; (q & 0xF) != 0xF; q >>= 12, ++k) {
+                const float *p1 = s_ep[threadIdx.x][q & 0xF], *p2 = s_ep[threadIdx.x][(q >> 4) & 0xF], *p3 = s_ep[threadIdx.x][(q >> 8) & 0xF];
+                const bool ne12 = p1[0] != p2[0] || p1[1] != p2[1] || p1[2] != p2[2];
+                const bool ne13 = p1[0] != p3[0] || p1[1] != p3[1] || p1[2] != p3[2];
+                const bool ne23 = p2[0] != p3[0] || p2[1] != p3[1] || p2[2] != p3[2];
+                if (ne12 && ne13 && ne23) { keep |= 1u << k; ++n; }
+            }
         }
-        running += total;
+        if (threadIdx.x < kChunk) {                                   // warps 0 and 1
+            unsigned inc = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+            if (lane == 31) s_wsum[warp] = inc;
+            s_keep[threadIdx.x] = keep;
+            s_off[threadIdx.x] = inc - n;                             // within the warp; the second warp adds s_wsum[0] below
+        }
+        __syncthreads();
+        const unsigned chunk_total = s_wsum[0] + s_wsum[1];
+        if (EMIT) {
+            // one thread per (cell, triangle slot, vertex)
+            for (int q = threadIdx.x; q < nj * 15; q += 256) {
+                const int j = q / 15, r = q - 15 * j, k = r / 3, vtx = r - 3 * k;
+                const unsigned kp = s_keep[j];
+                if (!(kp >> k & 1)) continue;
+                const unsigned ord = running + block_total + s_off[j] + (j >= 32 ? s_wsum[0] : 0u) + __popc(kp & ((1u << k) - 1u));
+                const int e = (int)((d_tri[s_list[j0 + j] >> 48] >> (4 * r)) & 0xF);
+                float* vp = vertices + (size_t)ord * 9 + 3 * vtx;
+                unsigned char* cp = colors + (size_t)ord * 9 + 3 * vtx;
+                vp[0] = s_ep[j][e][0]; vp[1] = s_ep[j][e][1]; vp[2] = s_ep[j][e][2];
+                cp[0] = s_ec[j][e][0]; cp[1] = s_ec[j][e][1]; cp[2] = s_ec[j][e][2];
+            }
+        }
+        block_total += chunk_total;
         __syncthreads();
     }
-    if (!EMIT) {
-        mine = __reduce_add_sync(0xffffffffu, mine);
-        if (lane == 0) s_warp[warp] = mine;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned tsum = 0;
-            for (int i = 0; i < 8; ++i) tsum += s_warp[i];
-            counts[blockIdx.x] = tsum;
-        }
-    }
+    if (!EMIT && threadIdx.x == 0) counts[blockIdx.x] = block_total;
 }
 
 // Exclusive scan of n per-block counts in place (single block, chunked with a carry); the total lands in counts[n].
@@ -281,7 +360,7 @@ __global__ void __launch_bounds__(256) k_crop_neg_dist(MeshView m, float* __rest
     const int z = (int)(i / bxy);
     const long long rem = i - (long long)z * bxy;
     const int y = (int)(rem / m.bd[0]), x = (int)(rem - (long long)y * m.bd[0]);
-    out[i] = -m.dist[(long long)(m.lo[0] + x) + (long long)m.W * (m.lo[1] + y) + m.WH * (m.lo[2] + z)];
+    out[i] = -m.dist[m.lin0 + x + m.W * y + m.WH * z];
 }
 
 // ---- volume point cloud (VolumetricGradSdf::extract_pc, VolumetricGradSdf.cpp:320-346) -----------------------------------------
@@ -353,11 +432,13 @@ struct Box { int lo[3], hi[3]; bool any; };
 Box crop_box(psg_volume* v, float vs) {
     PSG_CUDA(cudaSetDevice(v->device));
     v->mesh_box.alloc(8);
-    const double thr = std::sqrt(3.0) * (double)vs;
+    const double thr64 = std::sqrt(3.0) * (double)vs;
+    float thr = (float)thr64;
+    if ((double)thr > thr64) thr = std::nextafterf(thr, -INFINITY);   // round down: see k_mesh_bbox
     const long long rows = (long long)v->dims[1] * v->dims[2];
     const unsigned nb = (unsigned)std::min<long long>((rows + 7) / 8, 148 * 8);
-    { Prof pf(v->stream, KID_MESH); k_mesh_box_init<<<1, 32, 0, v->stream>>>(v->mesh_box.p); }
-    { Prof pf(v->stream, KID_MESH); k_mesh_bbox<<<nb, 256, 0, v->stream>>>(v->f[0].p, v->dims[0], v->dims[1], v->dims[2], thr, v->mesh_box.p); }
+    { Prof pf(v->stream, KID_MESH_MISC); k_mesh_box_init<<<1, 32, 0, v->stream>>>(v->mesh_box.p); }
+    { Prof pf(v->stream, KID_MESH_BOX); k_mesh_bbox<<<nb, 256, 0, v->stream>>>(v->f[0].p, v->dims[0], v->dims[1], v->dims[2], thr, v->mesh_box.p); }
     PSG_LAUNCH_CHECK();
     int h[6];
     PSG_CUDA(cudaMemcpyAsync(h, v->mesh_box.p, sizeof h, cudaMemcpyDeviceToHost, v->stream));
@@ -371,7 +452,8 @@ Box crop_box(psg_volume* v, float vs) {
 MeshView mesh_view(psg_volume* v, float vs, const Box& b, int white) {
     MeshView m{};
     m.dist = v->f[0].p; m.w = v->f[4].p; m.r = v->f[5].p; m.g = v->f[6].p; m.b = v->f[7].p;
-    m.W = v->dims[0]; m.WH = (long long)v->dims[0] * v->dims[1];
+    m.W = v->dims[0]; m.WH = v->dims[0] * v->dims[1];
+    m.lin0 = b.lo[0] + m.W * b.lo[1] + m.WH * b.lo[2];
     m.ncells = 1;
     for (int a = 0; a < 3; ++a) {
         m.lo[a] = b.lo[a];
@@ -397,8 +479,9 @@ long long run_marching_cubes(psg_volume* v, float vs, int white, Box* box_out) {
     if (m.ncells == 0) return 0;
     const long long nblocks = (m.ncells + kCellsPerBlock - 1) / kCellsPerBlock;
     v->mesh_counts.alloc((size_t)nblocks + 1);
-    { Prof pf(v->stream, KID_MESH); k_mesh_cells<false><<<(unsigned)nblocks, 256, 0, v->stream>>>(m, v->mesh_counts.p, nullptr, nullptr); }
-    { Prof pf(v->stream, KID_MESH); k_mesh_scan<<<1, 1024, 0, v->stream>>>(v->mesh_counts.p, nblocks); }
+    v->mesh_crossed.alloc((size_t)nblocks * 32);      // one bit per cell
+    { Prof pf(v->stream, KID_MESH_COUNT); k_mesh_cells<false><<<(unsigned)nblocks, 256, 0, v->stream>>>(m, v->mesh_counts.p, v->mesh_crossed.p, nullptr, nullptr); }
+    { Prof pf(v->stream, KID_MESH_SCAN); k_mesh_scan<<<1, 1024, 0, v->stream>>>(v->mesh_counts.p, nblocks); }
     PSG_LAUNCH_CHECK();
     unsigned total = 0;
     PSG_CUDA(cudaMemcpyAsync(&total, v->mesh_counts.p + nblocks, sizeof total, cudaMemcpyDeviceToHost, v->stream));
@@ -406,7 +489,7 @@ long long run_marching_cubes(psg_volume* v, float vs, int white, Box* box_out) {
     if (total > 0) {
         v->mesh_vertices.alloc((size_t)total * 9);
         v->mesh_colors.alloc((size_t)total * 9);
-        { Prof pf(v->stream, KID_MESH); k_mesh_cells<true><<<(unsigned)nblocks, 256, 0, v->stream>>>(m, v->mesh_counts.p, v->mesh_vertices.p, v->mesh_colors.p); }
+        { Prof pf(v->stream, KID_MESH_EMIT); k_mesh_cells<true><<<(unsigned)nblocks, 256, 0, v->stream>>>(m, v->mesh_counts.p, v->mesh_crossed.p, v->mesh_vertices.p, v->mesh_colors.p); }
         PSG_LAUNCH_CHECK();
     }
     v->mesh_triangles = total;
@@ -480,7 +563,7 @@ bool write_sdf_file(psg_volume* v, float vs, const char* path, bool* any) {
     const MeshView m = mesh_view(v, vs, b, 0);
     const long long n = (long long)m.bd[0] * m.bd[1] * m.bd[2];
     v->staging.alloc((size_t)n);
-    { Prof pf(v->stream, KID_MESH); k_crop_neg_dist<<<(unsigned)((n + 255) / 256), 256, 0, v->stream>>>(m, v->staging.p, n); }
+    { Prof pf(v->stream, KID_MESH_MISC); k_crop_neg_dist<<<(unsigned)((n + 255) / 256), 256, 0, v->stream>>>(m, v->staging.p, n); }
     PSG_LAUNCH_CHECK();
     std::vector<float> host((size_t)n);
     PSG_CUDA(cudaMemcpyAsync(host.data(), v->staging.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, v->stream));
@@ -559,8 +642,8 @@ int psg_volume_extract_pc(psg_volume* v, const char* filename, long long* n_poin
     const double thr = std::sqrt(3.0) * (double)v->vs;
     const long long nblocks = (v->N + kCellsPerBlock - 1) / kCellsPerBlock;
     v->mesh_counts.alloc((size_t)nblocks + 1);
-    { Prof pf(v->stream, KID_MESH); k_volume_points<false><<<(unsigned)nblocks, 256, 0, v->stream>>>(v->view(), thr, v->mesh_counts.p, nullptr); }
-    { Prof pf(v->stream, KID_MESH); k_mesh_scan<<<1, 1024, 0, v->stream>>>(v->mesh_counts.p, nblocks); }
+    { Prof pf(v->stream, KID_MESH_MISC); k_volume_points<false><<<(unsigned)nblocks, 256, 0, v->stream>>>(v->view(), thr, v->mesh_counts.p, nullptr); }
+    { Prof pf(v->stream, KID_MESH_SCAN); k_mesh_scan<<<1, 1024, 0, v->stream>>>(v->mesh_counts.p, nblocks); }
     PSG_LAUNCH_CHECK();
     unsigned total = 0;
     PSG_CUDA(cudaMemcpyAsync(&total, v->mesh_counts.p + nblocks, sizeof total, cudaMemcpyDeviceToHost, v->stream));
@@ -569,7 +652,7 @@ int psg_volume_extract_pc(psg_volume* v, const char* filename, long long* n_poin
     std::vector<float> host((size_t)total * 9 + 1);
     if (total) {
         v->staging.alloc((size_t)total * 9);
-        { Prof pf(v->stream, KID_MESH); k_volume_points<true><<<(unsigned)nblocks, 256, 0, v->stream>>>(v->view(), thr, v->mesh_counts.p, v->staging.p); }
+        { Prof pf(v->stream, KID_MESH_MISC); k_volume_points<true><<<(unsigned)nblocks, 256, 0, v->stream>>>(v->view(), thr, v->mesh_counts.p, v->staging.p); }
         PSG_LAUNCH_CHECK();
         PSG_CUDA(cudaMemcpyAsync(host.data(), v->staging.p, (size_t)total * 9 * sizeof(float), cudaMemcpyDeviceToHost, v->stream));
         PSG_CUDA(cudaStreamSynchronize(v->stream));

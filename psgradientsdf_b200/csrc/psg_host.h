@@ -19,7 +19,7 @@ enum KernelId {
     KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
     KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
     KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
-    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_MESH, KID_COUNT
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_MESH_BOX, KID_MESH_COUNT, KID_MESH_SCAN, KID_MESH_EMIT, KID_MESH_MISC, KID_COUNT
 };
 // Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
 struct Prof {
@@ -75,7 +75,7 @@ struct psg_volume {
     psg::DevBuf<double> track_partials;
     int track_H = 0, track_W = 0;
     // surface extraction (mesh.cu): per-block counts / offsets, crop box, and the triangles of the last extraction
-    psg::DevBuf<unsigned> mesh_counts;
+    psg::DevBuf<unsigned> mesh_counts, mesh_crossed;
     psg::DevBuf<int> mesh_box;
     psg::DevBuf<float> mesh_vertices;        // 9 floats per triangle
     psg::DevBuf<unsigned char> mesh_colors;  // 9 bytes per triangle

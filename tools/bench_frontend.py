@@ -141,6 +141,7 @@ def main():
            "tracker_pixels_hit": int(ct), "tracker_cpu_pass_ms": None if trk_cpu is None else round(trk_cpu, 2),
            "mesh": {"triangles": int(len(mv) // 3), "crop_box_voxels": box_voxels, "ms_device_to_host_arrays": round(mesh_ms, 3),
                     "kernel_us_per_extraction": round(1e3 * sum(t for _, t in tabm.values()) / 10, 1),
+                    "kernel_us": {k: round(1e3 * t / 10, 1) for k, (n, t) in tabm.items()},
                     "ms_with_ascii_ply_file": round(mesh_file_ms, 1), "cpu_marching_cubes_ms": None if mesh_cpu is None else round(mesh_cpu, 1),
                     # both passes read dist + weight of every cell corner once (8 B per voxel of the crop box, neighbours from L1 / L2)
                     "algorithmic_bytes": 2 * 8 * box_voxels + 45 * int(len(mv) // 3)},
