@@ -18,10 +18,13 @@ ms_per_step = ms per LM iteration.
 `roofline`   : dominant kernel by device time, timed live with CUDA events on the launching stream (psg_profile_*).
 `cpu_baseline`: the reference's getPSEnergy() on this box's host (1 thread: the reference is single-threaded), on a
                bounded sample of the same workload.
-At N > 1 the SAME workload is sharded over the ranks (strong scaling): every rank holds the volume and the work list, the
-sweeps are split by contiguous ranges of the visibility-sorted work list, and the library combines the results with NCCL
-(all-reduce of energies and of the light / pose normal equations, all-gather of albedo, all-reduce of the distance stencil
-blocks, replicated distance solve) -- see DESIGN.md section 7.
+At N > 1 (--multi): "shard" splits ONE workload over the ranks (strong scaling): every rank holds the volume and the work list,
+the sweeps are split round-robin over 32-slot blocks of the visibility-sorted work list, and the library combines the results
+with NCCL (all-reduce of energies and of the light / pose normal equations, all-gather of albedo and of the distance stencil
+blocks, replicated distance solve) -- see DESIGN.md section 7.  "replicas" gives every rank its own keyframe set (weak scaling,
+no data-path collective; value = pairs of all ranks / slowest rank's time).  "auto" (default) applies the library's own rule:
+sharding one workload pays from 2e6 visible pairs per rank; the default 128^3 x 30 workload has 0.26e6 in total, so N GPUs
+serve N keyframe sets, while --grid 1024 --frames 64 is sharded.
 """
 from __future__ import annotations
 
@@ -54,6 +57,9 @@ def parse():
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--multi", default="auto", choices=["auto", "shard", "replicas"],
+                    help="N > 1: shard ONE workload over the ranks (strong scaling), run one independent keyframe set per rank "
+                         "(weak scaling), or choose by the library's sharding threshold (2e6 visible pairs per rank)")
     ap.add_argument("--ref-keyframes", type=int, default=30,
                     help="keyframes in the reference-arm sample (the reference is O(S^2 F): 30 keyframes at 128^3 = ~3 s per sweep)")
     return ap.parse_args()
@@ -116,9 +122,9 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def build_scene(a):
+def build_scene(a, seed=1234):
     from psgradientsdf_b200 import synth
-    sc = synth.make_scene(F=a.frames, H=a.height, W=a.width, model=a.model)
+    sc = synth.make_scene(F=a.frames, H=a.height, W=a.width, model=a.model, seed=seed)
     vs, T = synth.grid_for_scene(a.grid)
     return sc, vs, T
 
@@ -226,21 +232,43 @@ def run_ours(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    sc, vs, T = build_scene(a)
     G, F = a.grid, a.frames
     reg_l = 5.0 if a.model == "LED" else 0.0
-    gv = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(64, F), device=local)
-    gv.set_zmin(0.5); gv.set_zmax(3.5)
-    go = psg.Optimizer(gv, vs, sc.K, model=a.model, reg_n=10.0, reg_l=reg_l)
-    for f in range(F):
-        R, t = se3_parts(sc.poses_gt[f])
-        if f > 0:
-            gv.increase_counter()
-        gv.update(sc.color[f], sc.depth[f], sc.K, R, t, sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv)
     fi = np.arange(F, dtype=np.int32)
-    # pinned host copies of the per-step inputs (e2e leg)
-    img_pin = torch.from_numpy(np.ascontiguousarray(sc.color)).pin_memory()
-    pose_pin = torch.from_numpy(np.ascontiguousarray(sc.poses_init)).pin_memory()
+    SHARD_MIN_PAIRS = 2_000_000       # kShardMinPairsPerRank (psgradientsdf_b200/csrc/comm.cu)
+
+    def make_job(seed):
+        """One keyframe set fused into its volume, optimizer created, per-step inputs in pinned host memory."""
+        sc, vs, T = build_scene(a, seed)
+        gv = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(64, F), device=local)
+        gv.set_zmin(0.5); gv.set_zmax(3.5)
+        go = psg.Optimizer(gv, vs, sc.K, model=a.model, reg_n=10.0, reg_l=reg_l)
+        for f in range(F):
+            R, t = se3_parts(sc.poses_gt[f])
+            if f > 0:
+                gv.increase_counter()
+            gv.update(sc.color[f], sc.depth[f], sc.K, R, t, sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv)
+        img_pin = torch.from_numpy(np.ascontiguousarray(sc.color)).pin_memory()
+        pose_pin = torch.from_numpy(np.ascontiguousarray(sc.poses_init)).pin_memory()
+        return sc, vs, T, gv, go, img_pin, pose_pin
+
+    # N > 1: one workload sharded over the ranks, or one independent keyframe set per rank.  "auto" asks the library's own rule:
+    # sharding pays from 2e6 visible (surface voxel, keyframe) pairs per rank (DESIGN.md section 7); rank 0 builds the standard
+    # workload, counts, and tells the others, which then build the standard workload (shard) or their own (replicas).
+    mode = "single" if world == 1 else a.multi
+    job = None
+    if world > 1 and mode == "auto":
+        verdict = [None]
+        if rank == 0:
+            job = make_job(1234)
+            job[4].set_keyframes(fi, job[6].numpy(), job[5].numpy()); job[4].init()
+            verdict[0] = "shard" if job[4].is_sharded()[1] // world >= SHARD_MIN_PAIRS else "replicas"
+        dist.broadcast_object_list(verdict, src=0)
+        mode = verdict[0]
+    seed = 1234 + (17 * rank if mode == "replicas" else 0)
+    if job is None:
+        job = make_job(seed)
+    sc, vs, T, gv, go, img_pin, pose_pin = job
     images_np, poses_np = img_pin.numpy(), pose_pin.numpy()
 
     def handoff():
@@ -248,13 +276,21 @@ def run_ours(a):
         go.init()
         go.init_albedo()
 
-    if world > 1:
+    if mode == "shard":
         ids = [psg.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         go.comm_init(ids[0], rank, world)
+        go.set_shard_policy(1)
     handoff()
     S = go.S
     E0, A = go.energy()
+    # units of one step over the whole job: the shared work list when sharded, the sum of the ranks' own lists otherwise
+    A_job, S_job = A, S
+    vis_pairs = go.is_sharded()[1]
+    if mode == "replicas":
+        tot = torch.tensor([A, S], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(tot)
+        A_job, S_job = int(tot[0].item()), int(tot[1].item())
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")   # > 126 MB L2
 
     def barrier():
@@ -296,7 +332,7 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_max = float(tt.item())
-    value = A * sweeps_per_step * a.steps / t_max          # one shared workload: total pairs, not per rank
+    value = A_job * sweeps_per_step * a.steps / t_max      # whole job: the shared list once, or the sum of the ranks' own lists
 
     # ---- e2e leg: host buffers -> C ABI every step (keyframe upload overlapped with the work-list build: the pinned image
     # buffers stay valid until psg_opt_init returns, as psg_opt_set_upload_overlap requires)
@@ -320,7 +356,7 @@ def run_ours(a):
     tte = torch.tensor([te], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(tte, op=dist.ReduceOp.MAX)
-    e2e_value = A * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
+    e2e_value = A_job * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
 
     # same hand-off with the keyframes as the loader read them (8-bit BGR, psg_opt_set_keyframes_u8): reported beside e2e
     c8_pin = torch.from_numpy(np.ascontiguousarray(np.round(sc.color * 255.0).astype(np.uint8))).pin_memory()
@@ -347,7 +383,7 @@ def run_ours(a):
     tte8 = torch.tensor([te8], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(tte8, op=dist.ReduceOp.MAX)
-    e2e_u8 = {"value": A * (sweeps_per_step + 1) * a.steps / float(tte8.item()), "unit": UNIT,
+    e2e_u8 = {"value": A_job * (sweeps_per_step + 1) * a.steps / float(tte8.item()), "unit": UNIT,
               "h2d_bytes_per_step": int(c8_np.nbytes + poses_np.nbytes), "d2h_bytes_per_step": int(d2h),
               "ms_per_step": 1e3 * float(tte8.item()) / a.steps,
               "step": "as e2e, keyframes handed over as 8-bit BGR (psg_opt_set_keyframes_u8) and converted on the device"}
@@ -355,7 +391,8 @@ def run_ours(a):
     if rank != 0:
         if world > 1:
             dist.barrier()
-            go.comm_destroy()
+            if mode == "shard":
+                go.comm_destroy()
             dist.destroy_process_group()
         return
 
@@ -372,7 +409,8 @@ def run_ours(a):
     if best:
         n, ms = prof[best]
         # per launch = per rank: a rank sweeps its share of the work list
-        bytes_launch = sweep_bytes(A // world, S // world, F, out_block.get(best, 0))
+        shards = world if mode == "shard" else 1
+        bytes_launch = sweep_bytes(A // shards, S // shards, F, out_block.get(best, 0))
         ach = bytes_launch / (ms / n * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": ncu_traffic(a, best) if world == 1 else None, "peak_source": peak_src,
@@ -406,16 +444,19 @@ def run_ours(a):
             cpu["port"] = port
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "strong" if mode == "shard" else "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": workload_name(a), "surface_voxels": S, "active_pairs": A, "keyframes": F,
+           "config": {"workload": workload_name(a), "surface_voxels": S_job, "active_pairs": A_job, "keyframes": F,
                       "sweeps_per_step": sweeps_per_step, "energy_after_last_step": E[0] if E else None,
                       "l2": "flushed between steps (256 MiB device write); per-step host timing bracketed by device syncs, summed",
                       "multi_gpu": ("single GPU" if world == 1 else
-                                    (f"work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
-                                     if go.is_sharded()[0] else
-                                     f"{world} ranks, sweeps replicated (below the sharding threshold of 2e6 visible pairs per rank), "
-                                     "rank 0's sums broadcast"))},
+                                    f"ONE workload, work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
+                                    if mode == "shard" else
+                                    f"{world} independent keyframe sets, one per GPU (same geometry and camera orbit, lights and pose "
+                                    f"perturbations seeded per rank), no data-path collective; surface_voxels / active_pairs are sums "
+                                    f"over the ranks.  One such set has {vis_pairs} visible pairs, "
+                                    f"below the {SHARD_MIN_PAIRS} per rank from which sharding one set pays "
+                                    f"(DESIGN.md section 7; --multi shard forces it)")},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": 1e3 * float(tte.item()) / a.steps,
                    "step": "psg_opt_set_keyframes (pinned host images + poses, upload overlapped with the work-list build) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},
@@ -424,7 +465,8 @@ def run_ours(a):
     emit(out)
     if world > 1:
         dist.barrier()
-        go.comm_destroy()
+        if mode == "shard":
+            go.comm_destroy()
         dist.destroy_process_group()
 
 
