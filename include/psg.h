@@ -361,6 +361,13 @@ typedef struct {
     double ms_per_iteration;             /* host wall clock over the loop body, file dumps excluded */
     float iteration_ms[64];
 } psg_loop_result;
+/* Diagnostic: microseconds the calling thread spent inside psg_opt_iteration since the last reset, split into
+ * us[0] queuing kernels, us[1] waiting for the device's results, us[2] host solves (light / pose CG, pose update) and bookkeeping. */
+int psg_debug_host_times(double us[3], long long* iterations, int reset);
+/* Diagnostic, host only: the Jacobi-preconditioned CG the light and pose blocks are solved with (Eigen::ConjugateGradient<
+ * SparseMatrix<float>, Lower, DiagonalPreconditioner>, PsOptimizer.cpp:184-191,217-227) on nblocks dense bs x bs blocks (row
+ * major, lower triangle read). */
+int psg_debug_small_cg(int nblocks, int bs, const float* H, const float* b, float* x, int* success, int* iterations, float* error);
 int psg_opt_alternating_optimize(psg_optimizer* opt, const psg_loop_config* cfg, const char* save_path,
                                  psg_loop_result* result /* may be NULL */);
 

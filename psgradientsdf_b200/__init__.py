@@ -199,6 +199,31 @@ def sample_keyframes(n: int, max_num: int = 40):
     return kept[:m.value].copy()
 
 
+def host_times(reset: bool = True) -> dict:
+    """Where the host thread's time went inside psg_opt_iteration (microseconds per iteration since the last reset)."""
+    us = (C.c_double * 3)()
+    it = C.c_longlong()
+    lib().psg_debug_host_times.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.c_int]
+    _check(lib().psg_debug_host_times(us, C.byref(it), int(reset)))
+    n = max(it.value, 1)
+    return {"iterations": it.value, "queue_us": us[0] / n, "wait_us": us[1] / n, "host_solve_us": us[2] / n}
+
+
+def small_cg(H_blocks, b):
+    """The host solve of the light / pose blocks (psg_debug_small_cg) on (nblocks, bs, bs) dense symmetric blocks: host code only,
+    no device needed.  Returns (x, success, iterations, error)."""
+    Hb = np.ascontiguousarray(H_blocks, np.float32)
+    bb = np.ascontiguousarray(b, np.float32).reshape(-1)
+    nblocks, bs = Hb.shape[0], Hb.shape[1]
+    assert Hb.shape == (nblocks, bs, bs) and bb.size == nblocks * bs
+    x = np.zeros(bb.size, np.float32)
+    ok, it, err = C.c_int(), C.c_int(), C.c_float()
+    L = lib()
+    L.psg_debug_small_cg.argtypes = [C.c_int, C.c_int, f32p, f32p, f32p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_float)]
+    _check(L.psg_debug_small_cg(nblocks, bs, Hb.reshape(-1), bb, x, C.byref(ok), C.byref(it), C.byref(err)))
+    return x, bool(ok.value), it.value, err.value
+
+
 def profile_enable(on: bool = True) -> None:
     lib().psg_profile_enable(int(on))
 
@@ -630,6 +655,16 @@ class Optimizer:
                                  applied=bool(st.applied), n_accepted=st.n_accepted, energy_before=st.energy_before,
                                  n_active_before=st.n_active_before, energy_after=info.energy_after[b])
         return out
+
+    def iteration_config(self, light=True, albedo=True, distance=True, pose=True, damping=1.0, normal_reg=False, laplacian_reg=False):
+        """(psg_iteration_config, psg_iteration_info) to reuse with iteration_raw."""
+        return (IterationConfig(int(light), int(albedo), int(distance), int(pose), float(damping),
+                                (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0), 0), IterationInfo())
+
+    def iteration_raw(self, cfg, info):
+        """psg_opt_iteration on caller-held structs: what a C / C++ host's loop does per pass, without building Python dicts."""
+        _check(lib().psg_opt_iteration(self.h, C.byref(cfg), C.byref(info)))
+        return info
 
     def last_system(self, which):
         """(H_blocks, b, delta) of the last light / pose step as float64 arrays."""

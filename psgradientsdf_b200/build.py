@@ -15,8 +15,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libpsg_b200.so")
-SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu", "comm.cu", "normals.cu", "tracker.cu", "mesh.cu"]
-HEADERS = ["psg_device.cuh", "psg_host.h", "mc_table.h", os.path.join("..", "..", "include", "psg.h")]
+SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu", "comm.cu", "normals.cu", "tracker.cu", "mesh.cu", "host_solve.cpp"]
+HEADERS = ["psg_device.cuh", "psg_host.h", "mc_table.h", "host_solve.h", os.path.join("..", "..", "include", "psg.h")]
 
 
 def _nvcc() -> str:
@@ -51,7 +51,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     hdr_t = max(os.path.getmtime(os.path.join(CSRC, h)) for h in HEADERS)
 
     def compile_one(src: str) -> str:
-        obj = os.path.join(OBJ, src.replace(".cu", ".o"))
+        obj = os.path.join(OBJ, os.path.splitext(src)[0] + ".o")
         spath = os.path.join(CSRC, src)
         if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(spath), hdr_t):
             return obj

@@ -2,10 +2,12 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 
 #include <atomic>
 
+#include "host_solve.h"
 #include "psg_host.h"
 
 namespace psg {
@@ -59,58 +61,6 @@ static void prof_collect() {
         g_event_pool.push_back(r.e0); g_event_pool.push_back(r.e1);
     }
     g_prof_recs.clear();
-}
-
-// Eigen::ConjugateGradient<SparseMatrix<float>, Lower, DiagonalPreconditioner<float>> on a small dense symmetric system
-// (the light and pose blocks: F independent 4x4 / 9x9 / 6x6 blocks solved jointly, exactly as the reference does,
-// PsOptimizer.cpp:184-191, 217-227).  Only the lower triangle is read.  Returns Eigen's verdict.
-struct CgVerdict { int success; int iters; float err; };
-static CgVerdict eigen_like_cg(int nblocks, int bs, const float* H /* nblocks * bs * bs */, const float* b, float* x) {
-    const int n = nblocks * bs;
-    std::vector<float> res(b, b + n), p(n), z(n), tmp(n), invd(n);
-    for (int i = 0; i < n; ++i) {
-        x[i] = 0.f;
-        const float d = H[(size_t)(i / bs) * bs * bs + (i % bs) * bs + (i % bs)];
-        invd[i] = d != 0.f ? 1.f / d : 1.f;
-    }
-    const float tol = 1.1920929e-07f;
-    const int maxIters = 2 * n;
-    float rhsNorm2 = 0.f;
-    for (int i = 0; i < n; ++i) rhsNorm2 += b[i] * b[i];
-    if (rhsNorm2 == 0.f) return {1, 0, 0.f};
-    float threshold = tol * tol * rhsNorm2;
-    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
-    float residualNorm2 = rhsNorm2;
-    if (residualNorm2 < threshold) return {1, 0, std::sqrt(residualNorm2 / rhsNorm2)};
-    float absNew = 0.f;
-    for (int i = 0; i < n; ++i) { p[i] = invd[i] * res[i]; absNew += res[i] * p[i]; }
-    int it = 0;
-    while (it < maxIters) {
-        for (int blk = 0; blk < nblocks; ++blk) {
-            const float* Hb = H + (size_t)blk * bs * bs;
-            float* t = tmp.data() + blk * bs;
-            const float* pp = p.data() + blk * bs;
-            for (int i = 0; i < bs; ++i) t[i] = 0.f;
-            for (int i = 0; i < bs; ++i) {
-                t[i] += Hb[i * bs + i] * pp[i];
-                for (int k = 0; k < i; ++k) { t[i] += Hb[i * bs + k] * pp[k]; t[k] += Hb[i * bs + k] * pp[i]; }
-            }
-        }
-        float pt = 0.f;
-        for (int i = 0; i < n; ++i) pt += p[i] * tmp[i];
-        const float alpha = absNew / pt;
-        residualNorm2 = 0.f;
-        for (int i = 0; i < n; ++i) { x[i] += alpha * p[i]; res[i] -= alpha * tmp[i]; residualNorm2 += res[i] * res[i]; }
-        if (residualNorm2 < threshold) break;
-        const float absOld = absNew;
-        absNew = 0.f;
-        for (int i = 0; i < n; ++i) { z[i] = invd[i] * res[i]; absNew += res[i] * z[i]; }
-        const float beta = absNew / absOld;
-        for (int i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
-        ++it;
-    }
-    const float err = std::sqrt(residualNorm2 / rhsNorm2);
-    return {err <= tol ? 1 : 0, it, err};
 }
 
 // Sophus SO3::exp (third/Sophus/sophus/so3.hpp:583-619) followed by Eigen's Quaternion::toRotationMatrix
@@ -702,6 +652,15 @@ int psg_opt_probe_pairs(psg_optimizer* o, float* m, float* n, unsigned char* ok,
 // ---- one block = queue (no host wait) + finish (after fetch_mail) ------------------------------------------------
 namespace {
 
+// where the host thread's time goes inside psg_opt_iteration (psg_debug_host_times): launching, waiting for the device, solving
+double g_host_us[3] = {0.0, 0.0, 0.0};
+long long g_host_iterations = 0;
+struct HostClock {
+    int slot; std::chrono::steady_clock::time_point t0;
+    explicit HostClock(int s) : slot(s), t0(std::chrono::steady_clock::now()) {}
+    ~HostClock() { g_host_us[slot] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
 struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; };
 
 // queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
@@ -743,21 +702,24 @@ void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
         inf.n_accepted = (long long)(mail_slot(o, p.slot)[5] + 0.5);
         o->last_n = (int)n;
     } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
-        std::vector<double> Hd, bd;
+        // scratch kept across calls: the solve runs three times per outer iteration and must not pay for allocations
+        thread_local static std::vector<double> Hd, bd;
+        thread_local static std::vector<float> Hf, bf, x;
         unpack_small_block(o, block, p.slot, Hd, bd);
         const int bs = block == PSG_BLOCK_POSE ? 6 : (led ? 3 : o->nb);
         const int nblk = (block == PSG_BLOCK_LIGHT && led) ? 1 : o->F;
         const int n = bs * nblk;
         // H.diagonal() += damping * H.diagonal(): every block but the SH light block (PsOptimizer.cpp:175-203)
         const bool damp = !(block == PSG_BLOCK_LIGHT && !led);
-        std::vector<float> Hf(Hd.size()), bf(bd.size()), x((size_t)n, 0.f);
+        Hf.resize(Hd.size()); bf.resize(bd.size()); x.assign((size_t)n, 0.f);
         for (size_t i = 0; i < Hd.size(); ++i) Hf[i] = (float)Hd[i];
         for (size_t i = 0; i < bd.size(); ++i) bf[i] = (float)bd[i];
         if (damp && p.damping != 0.f)
-            for (int i = 0; i < n; ++i) {
-                float& d = Hf[(size_t)(i / bs) * bs * bs + (i % bs) * bs + (i % bs)];
-                d = d + p.damping * d;
-            }
+            for (int blk = 0; blk < nblk; ++blk)
+                for (int k = 0; k < bs; ++k) {
+                    float& d = Hf[(size_t)blk * bs * bs + k * bs + k];
+                    d = d + p.damping * d;
+                }
         const CgVerdict v = eigen_like_cg(nblk, bs, Hf.data(), bf.data(), x.data());
         inf.n = n; inf.cg_success = v.success; inf.cg_iterations = v.iters; inf.cg_error = v.err;
         o->lastH.assign(Hf.begin(), Hf.end());
@@ -835,7 +797,8 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
     bool reg_queued = false;
     int last_run = -1;
     auto flush = [&](size_t nred) {
-        fetch_mail(o, nred);
+        { HostClock hc(1); fetch_mail(o, nred); }
+        HostClock hc(2);
         for (int i = 0; i < nq; ++i) {
             finish_block(o, queued[i], &R.block[queued[i].block]);
             R.ran[queued[i].block] = 1;
@@ -853,7 +816,7 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
         if (!enabled[block]) continue;
         const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) : 0;
         const bool want_reg = block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN));
-        queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg, /*keep_vectors=*/false);
+        { HostClock hc(0); queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg, /*keep_vectors=*/false); }
         const size_t nred = queued[nq].nred;
         ++nq; ++slot;
         last_run = block;
@@ -862,10 +825,10 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
     }
     // closing energy (the convergence test needs it); blocks still queued ride on the same round trip
     if (last_run >= 0 || cfg->closing_energy) {
-        launch_energy(o, slot);
+        { HostClock hc(0); launch_energy(o, slot); }
         const int eslot = slot;
         // flush() resets `slot`, read the closing energy first
-        fetch_mail(o, 0);
+        { HostClock hc(1); fetch_mail(o, 0); }
         const double* sc = mail_slot(o, eslot);
         R.energy_end = o->S > 0 ? sc[6] / (double)o->S : 0.0;
         R.n_active_end = (long long)(sc[7] + 0.5);
@@ -891,9 +854,27 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
             next = R.block[block].energy_before;
         }
     }
+    ++g_host_iterations;
     if (out) *out = R;
     return PSG_OK;
     PSG_CATCH
+}
+
+// The host's small solve on caller-supplied blocks (no device involved): what finish_block runs for the light and pose blocks.
+int psg_debug_small_cg(int nblocks, int bs, const float* H, const float* b, float* x, int* success, int* iterations, float* error) {
+    if (nblocks < 1 || bs < 1 || !H || !b || !x) { set_error("psg_debug_small_cg: bad argument"); return PSG_ERR_INVALID; }
+    const CgVerdict v = eigen_like_cg(nblocks, bs, H, b, x);
+    if (success) *success = v.success;
+    if (iterations) *iterations = v.iters;
+    if (error) *error = v.err;
+    return PSG_OK;
+}
+
+int psg_debug_host_times(double us[3], long long* iterations, int reset) {
+    if (us) for (int i = 0; i < 3; ++i) us[i] = g_host_us[i];
+    if (iterations) *iterations = g_host_iterations;
+    if (reset) { g_host_us[0] = g_host_us[1] = g_host_us[2] = 0.0; g_host_iterations = 0; }
+    return PSG_OK;
 }
 
 int psg_opt_last_system(psg_optimizer* o, double* H, double* b, double* delta) {

@@ -5,6 +5,7 @@ import subprocess
 import sys
 
 import numpy as np
+import pytest
 
 from psgradientsdf_b200 import synth
 
@@ -91,3 +92,22 @@ def test_two_rank_gloo_plumbing(tmp_path):
                         "127.0.0.1", "--master-port", "29611", str(script)], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stderr[-2000:]
     assert r.stdout.count("ok") == 2
+
+
+@pytest.mark.parametrize("model", ["SH1", "SH2", "LED"])
+def test_small_solve_is_the_reference_cg(model):
+    """The host solve of the light and pose blocks (host_solve.cpp, no device involved) against the reference's own
+    Eigen::ConjugateGradient on the committed golden systems: same iterates bit for bit, same iteration count and verdict --
+    including the 9 x 9 SH2 light systems, whose verdict depends on the summation order of the inner products."""
+    import psgradientsdf_b200 as psg
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"ref_{model}.npz"))
+    for name in ("light", "pose"):
+        bs = 6 if name == "pose" else (3 if model == "LED" else (9 if model == "SH2" else 4))
+        H = np.asarray(g[name + "_H"], np.float32)
+        b = np.asarray(g[name + "_b"], np.float32)
+        F = b.size // bs
+        assert H.shape == (F * bs, F * bs)
+        blocks = np.stack([H[f * bs:(f + 1) * bs, f * bs:(f + 1) * bs] for f in range(F)])
+        x, ok, it, err = psg.small_cg(blocks, b)
+        assert it == int(g[name + "_iters"]) and ok == (int(g[name + "_info"]) == 0), (model, name, it, ok)
+        assert np.array_equal(x.view(np.uint32), np.asarray(g[name + "_delta"], np.float32).view(np.uint32)), (model, name)
