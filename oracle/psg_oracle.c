@@ -7,7 +7,9 @@
  *     unrolled as  a0 + (a1 + a2)   (third/eigen/Eigen/src/Core/Redux.h:100-116);
  *   - dynamic VectorXf inner products of length 4 / 9 use the SSE packet order
  *     (Redux.h:236-281, arch/SSE/PacketMath.h:978-988);
- *   - cv::Vec3f * double scales in double and rounds to float per channel.
+ *   - cv::Vec3f * double scales in double and rounds to float per channel;
+ *   - the block solves follow Eigen operation by operation (eigen_dot, eigen_like_cg, rowsum2 below): against the reference
+ *     build, two complete outer iterations are bit-identical for SH1, SH2 and LED (tests/test_oracle_vs_ref.py).
  * Build with -ffp-contract=off (oracle/Makefile).
  */
 #include "psg_oracle.h"
@@ -805,6 +807,26 @@ static int dist_jacobian(const or_opt* o, const voxel* x, int f, const float* R,
     return 1;
 }
 
+/* b += s * (J^T * r) as Eigen evaluates it: the scalar goes into the matrix, (s * J^T) * r, and the product of a row-major
+ * sparse expression with a dense vector sums every row with two accumulators, entries alternating between them in ascending
+ * column order, res[i] += alpha * (tmp_a + tmp_b) with alpha = 1 (SparseCore/SparseDenseProduct.h:66-80).  Entries must
+ * arrive in ascending J-row order per column. */
+typedef struct { float* a; float* b; unsigned char* odd; int n; } rowsum2;
+static rowsum2 rs2_new(int n) {
+    rowsum2 r; r.n = n;
+    r.a = calloc(n > 0 ? n : 1, sizeof(float)); r.b = calloc(n > 0 ? n : 1, sizeof(float)); r.odd = calloc(n > 0 ? n : 1, 1);
+    return r;
+}
+static void rs2_add(rowsum2* r, int col, float scaled_j, float res) {
+    const float t = scaled_j * res;
+    if (r->odd[col]) r->b[col] += t; else r->a[col] += t;
+    r->odd[col] ^= 1;
+}
+static void rs2_finish(rowsum2* r, float* b) {
+    for (int i = 0; i < r->n; ++i) b[i] += r->a[i] + r->b[i];
+    free(r->a); free(r->b); free(r->odd);
+}
+
 /* ------------------------------------------------------------------ sparse accumulator + CG */
 typedef struct { int n; int* cnt; int* col; float* val; int cap; } rowacc;
 static rowacc* ra_new(int n, int cap) {
@@ -827,46 +849,97 @@ static float ra_get(const rowacc* a, int i, int j) {
     return 0.f;
 }
 
-/* Eigen::ConjugateGradient<SparseMatrix<float>, Lower, DiagonalPreconditioner> (ConjugateGradient.h:28-93,
- * IterativeSolverBase.h, BasicPreconditioners.h:67-82): only the lower triangle is read; tol = epsilon; maxIters = 2n. */
+/* sum_i a[i] * b[i] in the order Eigen's vectorised reduction adds them on the reference's x86-64 build (SSE2 packets of 4
+ * floats, no FMA): two packet accumulators over strides of 8, their sum, one more packet if the length allows, the horizontal
+ * sum (l0 + l2) + (l1 + l3), then the tail element by element (third/eigen/Eigen/src/Core/Redux.h:236-281, predux in
+ * arch/SSE/PacketMath.h).  Vectors shorter than one packet are summed serially. */
+static float eigen_dot(const float* a, const float* b, int n) {
+    if (n <= 0) return 0.f;
+    if (n < 4) {
+        float r = a[0] * b[0];
+        for (int i = 1; i < n; ++i) r += a[i] * b[i];
+        return r;
+    }
+    const int aligned = n & ~3, aligned2 = n & ~7;
+    float p0[4], p1[4];
+    for (int l = 0; l < 4; ++l) p0[l] = a[l] * b[l];
+    if (aligned > 4) {
+        for (int l = 0; l < 4; ++l) p1[l] = a[4 + l] * b[4 + l];
+        for (int i = 8; i < aligned2; i += 8) {
+            for (int l = 0; l < 4; ++l) p0[l] += a[i + l] * b[i + l];
+            for (int l = 0; l < 4; ++l) p1[l] += a[i + 4 + l] * b[i + 4 + l];
+        }
+        for (int l = 0; l < 4; ++l) p0[l] += p1[l];
+        if (aligned > aligned2) for (int l = 0; l < 4; ++l) p0[l] += a[aligned2 + l] * b[aligned2 + l];
+    }
+    float r = (p0[0] + p0[2]) + (p0[1] + p0[3]);
+    for (int i = aligned; i < n; ++i) r += a[i] * b[i];
+    return r;
+}
+
+/* Eigen::ConjugateGradient<SparseMatrix<float>, Lower, DiagonalPreconditioner> statement by statement (ConjugateGradient.h:
+ * 29-98, IterativeSolverBase.h, BasicPreconditioners.h:67-93): tol = epsilon, maxIters = 2n, only the lower triangle is read.
+ * The product with the lower selfadjoint view walks the columns of the column-major matrix: diagonal term into res[j], then for
+ * the rows i > j below it (ascending) res_j += l * p[i] and res[i] += l * p[j], then res[j] += res_j
+ * (SparseCore/SparseSelfAdjointView.h:299-331); the inner products follow eigen_dot. */
 static void eigen_like_cg(const rowacc* H, const float* b, float* x, int* success, int* iters_out, float* err_out) {
     const int n = H->n;
     float *res = malloc(4 * (size_t)(n + 1)), *p = malloc(4 * (size_t)(n + 1)), *z = malloc(4 * (size_t)(n + 1)),
-          *tmp = malloc(4 * (size_t)(n + 1)), *invd = malloc(4 * (size_t)(n + 1));
-    for (int i = 0; i < n; ++i) { x[i] = 0.f; res[i] = b[i]; float d = ra_get(H, i, i); invd[i] = d != 0.f ? 1.f / d : 1.f; }
+          *tmp = malloc(4 * (size_t)(n + 1)), *invd = malloc(4 * (size_t)(n + 1)), *diag = malloc(4 * (size_t)(n + 1));
+    unsigned char* has_diag = calloc((size_t)n + 1, 1);
+    /* lower triangle by columns, rows ascending within a column (row i's entries (i, j < i) are appended to column j as i grows) */
+    int* colptr = calloc((size_t)n + 2, sizeof(int));
+    for (int i = 0; i < n; ++i) {
+        const int* c = H->col + (size_t)i * H->cap;
+        for (int k = 0; k < H->cnt[i]; ++k) if (c[k] < i) ++colptr[c[k] + 1];
+    }
+    for (int j = 0; j < n; ++j) colptr[j + 1] += colptr[j];
+    const int nnz = colptr[n];
+    int* rowidx = malloc(sizeof(int) * (size_t)(nnz + 1));
+    float* lval = malloc(sizeof(float) * (size_t)(nnz + 1));
+    int* fill = malloc(sizeof(int) * (size_t)(n + 1));
+    for (int j = 0; j < n; ++j) fill[j] = colptr[j];
+    for (int i = 0; i < n; ++i) {
+        const int* c = H->col + (size_t)i * H->cap; const float* v = H->val + (size_t)i * H->cap;
+        diag[i] = 0.f;
+        for (int k = 0; k < H->cnt[i]; ++k) {
+            if (c[k] == i) { diag[i] = v[k]; has_diag[i] = 1; }
+            else if (c[k] < i) { rowidx[fill[c[k]]] = i; lval[fill[c[k]]++] = v[k]; }
+        }
+    }
+    for (int i = 0; i < n; ++i) { x[i] = 0.f; res[i] = b[i]; invd[i] = (has_diag[i] && diag[i] != 0.f) ? 1.f / diag[i] : 1.f; }
     const float tol = 1.1920929e-07f;
     const int maxIters = 2 * n;
-    float rhsNorm2 = 0.f;
-    for (int i = 0; i < n; ++i) rhsNorm2 += b[i] * b[i];
+    const float rhsNorm2 = eigen_dot(b, b, n);
     int it = 0; float residualNorm2 = 0.f;
     if (rhsNorm2 == 0.f) { *success = 1; *iters_out = 0; *err_out = 0.f; goto done; }
     {
         float threshold = tol * tol * rhsNorm2;
         if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
-        residualNorm2 = rhsNorm2;
+        residualNorm2 = eigen_dot(res, res, n);
         if (residualNorm2 < threshold) { *iters_out = 0; *err_out = sqrtf(residualNorm2 / rhsNorm2); *success = 1; goto done; }
-        float absNew = 0.f;
-        for (int i = 0; i < n; ++i) { p[i] = invd[i] * res[i]; absNew += res[i] * p[i]; }
+        for (int i = 0; i < n; ++i) p[i] = invd[i] * res[i];
+        float absNew = eigen_dot(res, p, n);
         while (it < maxIters) {
             /* tmp = selfadjointView<Lower>(H) * p */
             for (int i = 0; i < n; ++i) tmp[i] = 0.f;
-            for (int i = 0; i < n; ++i) {
-                const int* c = H->col + (size_t)i * H->cap; const float* v = H->val + (size_t)i * H->cap;
-                for (int k = 0; k < H->cnt[i]; ++k) {
-                    const int j = c[k];
-                    if (j == i) tmp[i] += v[k] * p[i];
-                    else if (j < i) { tmp[i] += v[k] * p[j]; tmp[j] += v[k] * p[i]; }
+            for (int j = 0; j < n; ++j) {
+                if (has_diag[j]) tmp[j] += diag[j] * p[j];
+                const float rhs_j = p[j];
+                float res_j = 0.f;
+                for (int k = colptr[j]; k < colptr[j + 1]; ++k) {
+                    res_j += lval[k] * p[rowidx[k]];
+                    tmp[rowidx[k]] += lval[k] * rhs_j;
                 }
+                tmp[j] += res_j;
             }
-            float pt = 0.f;
-            for (int i = 0; i < n; ++i) pt += p[i] * tmp[i];
-            const float alpha = absNew / pt;
-            residualNorm2 = 0.f;
-            for (int i = 0; i < n; ++i) { x[i] += alpha * p[i]; res[i] -= alpha * tmp[i]; residualNorm2 += res[i] * res[i]; }
+            const float alpha = absNew / eigen_dot(p, tmp, n);
+            for (int i = 0; i < n; ++i) { x[i] += alpha * p[i]; res[i] -= alpha * tmp[i]; }
+            residualNorm2 = eigen_dot(res, res, n);
             if (residualNorm2 < threshold) break;
+            for (int i = 0; i < n; ++i) z[i] = invd[i] * res[i];
             const float absOld = absNew;
-            absNew = 0.f;
-            for (int i = 0; i < n; ++i) { z[i] = invd[i] * res[i]; absNew += res[i] * z[i]; }
+            absNew = eigen_dot(res, z, n);
             const float beta = absNew / absOld;
             for (int i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
             ++it;
@@ -876,7 +949,7 @@ static void eigen_like_cg(const rowacc* H, const float* b, float* x, int* succes
         *success = (*err_out <= tol) ? 1 : 0; /* IterativeSolverBase: m_info = m_error <= m_tolerance ? Success : NoConvergence */
     }
 done:
-    free(res); free(p); free(z); free(tmp); free(invd);
+    free(res); free(p); free(z); free(tmp); free(invd); free(diag); free(has_diag); free(colptr); free(rowidx); free(lval); free(fill);
 }
 
 /* ------------------------------------------------------------------ updates */
@@ -1060,7 +1133,7 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
     /* regularisers */
     if (which == OR_DIST && normal_reg) { /* Optimizer.cpp:196-218, 477-537; PsOptimizer.cpp:136-142 */
         rowacc* M = ra_new(n, 48);
-        float* bb = calloc(n > 0 ? n : 1, sizeof(float));
+        rowsum2 bb = rs2_new(n);
         for (int s = 0; s < S; ++s) {
             voxel x = load_voxel(o, (size_t)o->surf[s]);
             float g[3], pos[3]; long long nl[3];
@@ -1077,15 +1150,14 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
             for (int i = 0; i < 4; ++i) {
                 if (cols[i] < 0) continue;
                 for (int k = 0; k < 4; ++k) if (cols[k] >= 0) *ra_at(M, cols[i], cols[k]) += Jr[i] * Jr[k];
-                bb[cols[i]] += Jr[i] * rr;
+                rs2_add(&bb, cols[i], o->reg_n * Jr[i], rr);
             }
         }
-        for (int i = 0; i < n; ++i) {
+        for (int i = 0; i < n; ++i)
             for (int k = 0; k < M->cnt[i]; ++k)
                 *ra_at(H, i, M->col[(size_t)i * M->cap + k]) += o->reg_n * M->val[(size_t)i * M->cap + k];
-            b[i] += o->reg_n * bb[i];
-        }
-        ra_free(M); free(bb);
+        rs2_finish(&bb, b);
+        ra_free(M);
     }
     if (which == OR_DIST && laplacian_reg) { /* Optimizer.cpp:540-590 (diagonal only); PsOptimizer.cpp:144-150 */
         const float vi2 = o->vs_inv * o->vs_inv;
@@ -1094,12 +1166,12 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
             voxel x = load_voxel(o, (size_t)o->surf[s]);
             const float rr = dist_laplacian(o, &x);
             *ra_at(H, s, s) += o->reg_l * (jd * jd);
-            b[s] += o->reg_l * (jd * rr);
+            b[s] += (o->reg_l * jd) * rr + 0.f;   /* (reg_l * J^T) * r, one entry per row: tmp_a + tmp_b with tmp_b = 0 */
         }
     }
     if (which == OR_ALBEDO && albedo_reg) { /* Optimizer.cpp:221-245, 593-647 (incl. the blue-channel column quirk at :618) */
         rowacc* M = ra_new(n, 48);
-        float* bb = calloc(n > 0 ? n : 1, sizeof(float));
+        rowsum2 bb = rs2_new(n);
         /* J rows: 3*s+c ; gather J first, then J^T J in row order */
         for (int s = 0; s < S; ++s) {
             voxel x = load_voxel(o, (size_t)o->surf[s]);
@@ -1118,16 +1190,15 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
                 for (int k = 0; k < 3; ++k) if (ncol[k] >= 0) { cols[m] = 3 * ncol[k] + c; vals[m++] = Jr[k + 1][c]; }
                 for (int i = 0; i < m; ++i) {
                     for (int k = 0; k < m; ++k) *ra_at(M, cols[i], cols[k]) += vals[i] * vals[k];
-                    bb[cols[i]] += vals[i] * gnorm[c];
+                    rs2_add(&bb, cols[i], o->reg_rho * vals[i], gnorm[c]);
                 }
             }
         }
-        for (int i = 0; i < n; ++i) {
+        for (int i = 0; i < n; ++i)
             for (int k = 0; k < M->cnt[i]; ++k)
                 *ra_at(H, i, M->col[(size_t)i * M->cap + k]) += o->reg_rho * M->val[(size_t)i * M->cap + k];
-            b[i] += o->reg_rho * bb[i];
-        }
-        ra_free(M); free(bb);
+        rs2_finish(&bb, b);
+        ra_free(M);
     }
     if (H64) {
         for (int i = 0; i < n; ++i) {

@@ -106,6 +106,14 @@ def replay(model, make_volume, make_optimizer, integrate, *, gpu: bool, exact_or
             res = opt.block(blk, apply=True, **kw)
             b, delta, success = res["b"], res["delta"], res["info"] == 0
             H = res["H"].toarray() if blk in ("light", "pose") else None
+        if not gpu:
+            # the CPU restatement follows the reference's Eigen arithmetic operation by operation: the committed reference
+            # outputs are reproduced bit for bit (right-hand side, matrix, solution, CG iteration count and verdict)
+            assert res["info"] == int(ref[f"{blk}_info"]) and res["iters"] == int(ref[f"{blk}_iters"]), (blk, res["info"], res["iters"])
+            assert_bit_equal(np.asarray(b, np.float32), np.asarray(ref[f"{blk}_b"], np.float32), f"{blk} rhs")
+            assert_bit_equal(np.asarray(delta, np.float32), np.asarray(ref[f"{blk}_delta"], np.float32), f"{blk} solution")
+            if H is not None:
+                assert_bit_equal(np.asarray(H, np.float32), np.asarray(ref[f"{blk}_H"], np.float32), f"{blk} matrix")
         if blk != "light":   # the light update is unconditional; SH2's 9x9 systems sit at the edge of float convergence
             assert success == (int(ref[f"{blk}_info"]) == 0), f"{blk}: CG verdict"
         tol_b = 2e-4 if model == "SH2" else 2e-5   # SH2: everything after the ill-conditioned 9x9 light solve inherits its spread
@@ -127,6 +135,10 @@ def replay(model, make_volume, make_optimizer, integrate, *, gpu: bool, exact_or
     d_rms = float(np.sqrt(np.mean((final[:, 0].astype(np.float64) - ref["final_rows"][:, 0]) ** 2))) / vs
     a_rms = float(np.sqrt(np.mean((final[:, 5:8].astype(np.float64) - ref["final_rows"][:, 5:8]) ** 2)))
     assert d_rms <= 1e-4 and a_rms <= 1e-4, ("final RMS (distance in voxel units, albedo)", d_rms, a_rms)
+    if not gpu:
+        assert_bit_equal(final, np.asarray(ref["final_rows"], np.float32), "surface voxel records after the iteration")
+        assert_bit_equal(np.asarray(opt.light(), np.float32).reshape(-1), np.asarray(ref["final_light"], np.float32).reshape(-1), "light after the iteration")
+        assert_bit_equal(np.asarray(opt.poses(), np.float32).reshape(-1), np.asarray(ref["final_poses"], np.float32).reshape(-1), "poses after the iteration")
 
     # upsampling: membership and index contracts are exact; values follow from dist (within the RMS above)
     up = opt.upsample if gpu else opt.subsampling
@@ -139,4 +151,7 @@ def replay(model, make_volume, make_optimizer, integrate, *, gpu: bool, exact_or
     # flip a child's membership, so compare the lists as sets with a tiny budget
     diff = np.setxor1d(s2, ref["up_surface"]).size
     assert diff <= max(2, int(2e-4 * ref["up_surface"].size)), ("surface list after upsampling", diff)
+    if not gpu:   # bit-identical state before the upsampling: identical list and voxel records after it
+        assert_bit_equal(s2, ref["up_surface"], "surface list after upsampling")
+        assert_bit_equal(vol.download()[s2], np.asarray(ref["up_rows"], np.float32), "voxel records after upsampling")
     return opt, vol
