@@ -72,6 +72,10 @@ def test_demo_frames_fuse_and_optimize_like_the_restatement():
         assert eo[2] == eg[1], blk
         assert abs(eo[1] - eg[0]) <= 5e-6 * abs(eo[1]), (blk, eo[1], eg[0])
         assert abs(ef[1] - eg[0]) <= 1e-3 * abs(ef[1]), (blk, ef[1], eg[0])
+    # the mesh the reference would dump from this state (real colours, holes where no frame saw the surface)
+    mv, mc = gv.mesh()
+    mo = pyoracle.extract_mesh(gv.download(), [128] * 3, vs)
+    assert len(mv) > 30000 and np.array_equal(mv.view(np.uint32), mo[0].view(np.uint32)) and np.array_equal(mc, mo[1])
 
 
 def test_demo_frames_fuse_identically_through_the_brick_cull():
