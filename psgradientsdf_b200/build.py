@@ -39,7 +39,9 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__), os.path.join(HERE, "..", "examples", "voxelps_host.cpp")]
+    if not os.path.exists(os.path.join(HERE, "voxelps_host")):
+        return True
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -72,7 +74,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+    build_host_example()
     return LIB
+
+
+HOST_EXAMPLE = os.path.join(HERE, "voxelps_host")
+
+
+def build_host_example() -> str:
+    """examples/voxelps_host.cpp: a plain C++ host over the C ABI (no Python, no torch), built next to the library."""
+    src = os.path.join(HERE, "..", "examples", "voxelps_host.cpp")
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [cxx, "-std=c++17", "-O2", "-I" + os.path.join(HERE, "..", "include"), src, "-L" + HERE, "-lpsg_b200",
+           "-Wl,-rpath,$ORIGIN", "-o", HOST_EXAMPLE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("host example failed to build:\n" + r.stdout + r.stderr)
+    return HOST_EXAMPLE
 
 
 if __name__ == "__main__":
