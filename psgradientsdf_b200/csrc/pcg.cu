@@ -367,7 +367,7 @@ struct SolveSmallArgs {
 };
 
 template <int BS>
-__global__ void __launch_bounds__(BS, 4) k_dist_solve_small(SolveSmallArgs G, float* pbuf /* 2 x S */) {
+__global__ void __launch_bounds__(BS, (BS >= 512) ? 2 : 4) k_dist_solve_small(SolveSmallArgs G, float* pbuf /* 2 x S */) {
     const PcgArgs& A = G.A;
     __shared__ double s_buf[2 * (BS / 32) + 2];
     __shared__ double s_reg[BS / 32][3];
@@ -767,7 +767,7 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
 
 // launch geometry of the cooperative kernels, queried once per device (the queries cost microseconds each, the solve runs
 // every outer iteration)
-struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_1 = 0, per_sm_4 = 0; };
+struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_1 = 0, per_sm_4 = 0; };
 static const PcgGeometry& pcg_geometry() {
     static PcgGeometry g[64];
     int dev = 0;
@@ -776,6 +776,7 @@ static const PcgGeometry& pcg_geometry() {
     if (e.sms == 0) {
         PSG_CUDA(cudaDeviceGetAttribute(&e.sms, cudaDevAttrMultiProcessorCount, dev));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small512, k_dist_solve_small<512>, 512, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_1, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
     }
@@ -853,10 +854,11 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 // Fused path for surfaces with at most one row per resident thread (128^3, 256^3): returns false if it does not apply.
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot) {
     const int S = o->S;
-    if (S == 0 || o->pcg_mode != 0) return false;
+    if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3)) return false;
     const PcgGeometry& geo = pcg_geometry();
-    const int sms = geo.sms, per_sm = geo.per_sm_small;
-    const int grid = (S + kPcgBlock - 1) / kPcgBlock;
+    const int bsz = o->pcg_mode == 3 ? 512 : kPcgBlock;   // mode 3: half as many, twice as large blocks at the grid barrier
+    const int sms = geo.sms, per_sm = o->pcg_mode == 3 ? geo.per_sm_small512 : geo.per_sm_small;
+    const int grid = (S + bsz - 1) / bsz;
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
     o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
@@ -889,7 +891,8 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     G.zbuf = A.r;   // plane 18 is free on this path (the residual lives in registers)
     void* args[] = { &G, &pbuf };
     Prof pf(o->stream, KID_PCG_SOLVE);
-    PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
+    if (bsz == 512) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<512>, dim3(grid), dim3(512), args, 0, o->stream));
+    else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
     return true;
 }
 
