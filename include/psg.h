@@ -153,9 +153,12 @@ int psg_opt_set_upload_overlap(psg_optimizer* opt, int on);
  * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
  * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */
 int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
-/* Distance solve: 0 (default) and 2 = persistent cooperative-grid kernel over all SMs; 1 = one thread-block cluster of at
- * most 8 CTAs when the surface has at most 65 536 voxels (kept for comparison: slower on B200 once the grid kernel got its
- * own barrier).  Both run the same iteration and return the same iterates up to the order of the dot-product partials. */
+/* Distance solve: 0 (default) = the fused small-surface kernel where the surface fits one row per resident thread (block size
+ * chosen from the row count: fewer, larger blocks make the grid barriers cheaper), else the general persistent
+ * cooperative-grid kernel; 2 = always the general kernel; 1 = one thread-block cluster of at most 8 CTAs when the surface has
+ * at most 65 536 voxels (kept for comparison: slower on B200 once the grid kernel got its own barrier); 3 / 4 = the fused
+ * kernel with 512 / 1024 threads per block.  All run the same iteration and return the same iterates up to the order of the
+ * dot-product partials. */
 int psg_opt_set_pcg_mode(psg_optimizer* opt, int mode);
 
 /* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */

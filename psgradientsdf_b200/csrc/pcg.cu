@@ -367,7 +367,7 @@ struct SolveSmallArgs {
 };
 
 template <int BS>
-__global__ void __launch_bounds__(BS, (BS >= 512) ? 2 : 4) k_dist_solve_small(SolveSmallArgs G, float* pbuf /* 2 x S */) {
+__global__ void __launch_bounds__(BS, (BS >= 1024) ? 1 : (BS >= 512) ? 2 : 4) k_dist_solve_small(SolveSmallArgs G, float* pbuf /* 2 x S */) {
     const PcgArgs& A = G.A;
     __shared__ double s_buf[2 * (BS / 32) + 2];
     __shared__ double s_reg[BS / 32][3];
@@ -767,7 +767,7 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
 
 // launch geometry of the cooperative kernels, queried once per device (the queries cost microseconds each, the solve runs
 // every outer iteration)
-struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_1 = 0, per_sm_4 = 0; };
+struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_small1024 = 0, per_sm_1 = 0, per_sm_4 = 0; };
 static const PcgGeometry& pcg_geometry() {
     static PcgGeometry g[64];
     int dev = 0;
@@ -777,6 +777,7 @@ static const PcgGeometry& pcg_geometry() {
         PSG_CUDA(cudaDeviceGetAttribute(&e.sms, cudaDevAttrMultiProcessorCount, dev));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small512, k_dist_solve_small<512>, 512, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small1024, k_dist_solve_small<1024>, 1024, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_1, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
     }
@@ -854,10 +855,25 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 // Fused path for surfaces with at most one row per resident thread (128^3, 256^3): returns false if it does not apply.
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot) {
     const int S = o->S;
-    if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3)) return false;
+    if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3 && o->pcg_mode != 4)) return false;
     const PcgGeometry& geo = pcg_geometry();
-    const int bsz = o->pcg_mode == 3 ? 512 : kPcgBlock;   // mode 3: half as many, twice as large blocks at the grid barrier
-    const int sms = geo.sms, per_sm = o->pcg_mode == 3 ? geo.per_sm_small512 : geo.per_sm_small;
+    // Block size: the solve is a chain of grid barriers (three per iteration), and a barrier costs more the more blocks take
+    // part, while a row's arithmetic is negligible.  Measured (profiles/r1_summary.md section 8c): 128^3 (28 k rows) 125 / 114 /
+    // 120 us with 256 / 512 / 1024 threads per block, 256^3 (113 k rows) 216 / 164 / 152 us.  So: the smallest block that
+    // keeps the grid at or below 64 blocks, else the largest that fits.  Modes 3 / 4 force 512 / 1024.
+    int bsz = kPcgBlock;
+    if (o->pcg_mode == 3) bsz = 512;
+    else if (o->pcg_mode == 4) bsz = 1024;
+    else {
+        while (bsz < 1024 && (S + bsz - 1) / bsz > 64) bsz *= 2;
+    }
+    const int sms = geo.sms;
+    auto fits = [&](int b) {
+        const int per = b == 1024 ? geo.per_sm_small1024 : b == 512 ? geo.per_sm_small512 : geo.per_sm_small;
+        return per >= 1 && (S + b - 1) / b <= sms * per;
+    };
+    while (bsz > kPcgBlock && !fits(bsz)) bsz /= 2;
+    const int per_sm = bsz == 1024 ? geo.per_sm_small1024 : bsz == 512 ? geo.per_sm_small512 : geo.per_sm_small;
     const int grid = (S + bsz - 1) / bsz;
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
@@ -891,7 +907,8 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     G.zbuf = A.r;   // plane 18 is free on this path (the residual lives in registers)
     void* args[] = { &G, &pbuf };
     Prof pf(o->stream, KID_PCG_SOLVE);
-    if (bsz == 512) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<512>, dim3(grid), dim3(512), args, 0, o->stream));
+    if (bsz == 1024) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<1024>, dim3(grid), dim3(1024), args, 0, o->stream));
+    else if (bsz == 512) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<512>, dim3(grid), dim3(512), args, 0, o->stream));
     else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
     return true;
 }

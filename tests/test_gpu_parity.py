@@ -167,7 +167,7 @@ def test_pcg_kernels_agree():
     model, G = "SH1", 40
     sc = scene(model)
     outs = []
-    for mode in (0, 1, 2):
+    for mode in (0, 1, 2, 3, 4):   # 3, 4: the fused kernel with 512- / 1024-thread blocks
         gv, go = make_gpu(model, G, sc)
         handoff(go, sc); go.init_albedo(); go.set_pcg_mode(mode)
         info = go.step("dist", damping=1.0, normal_reg=True)
