@@ -57,7 +57,7 @@ def parse():
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--pcg-mode", type=int, default=0, choices=[0, 1, 2, 3, 4], help="psg_opt_set_pcg_mode (0 = default)")
+    ap.add_argument("--pcg-mode", type=int, default=0, choices=[0, 1, 2, 3, 4, 5], help="psg_opt_set_pcg_mode (0 = default)")
     ap.add_argument("--multi", default="auto", choices=["auto", "shard", "replicas"],
                     help="N > 1: shard ONE workload over the ranks (strong scaling), run one independent keyframe set per rank "
                          "(weak scaling), or choose by the library's sharding threshold (2e6 visible pairs per rank)")

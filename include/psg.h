@@ -157,7 +157,8 @@ int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
  * chosen from the row count: fewer, larger blocks make the grid barriers cheaper), else the general persistent
  * cooperative-grid kernel; 2 = always the general kernel; 1 = one thread-block cluster of at most 8 CTAs when the surface has
  * at most 65 536 voxels (kept for comparison: slower on B200 once the grid kernel got its own barrier); 3 / 4 = the fused
- * kernel with 512 / 1024 threads per block.  All run the same iteration and return the same iterates up to the order of the
+ * kernel with 512 / 1024 threads per block; 5 = the general kernel with 256-thread blocks on large surfaces (default there:
+ * 1024).  All run the same iteration and return the same iterates up to the order of the
  * dot-product partials. */
 int psg_opt_set_pcg_mode(psg_optimizer* opt, int mode);
 

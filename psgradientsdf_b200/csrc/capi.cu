@@ -576,7 +576,7 @@ int psg_opt_set_upload_overlap(psg_optimizer* o, int on) {
 
 int psg_opt_set_pcg_mode(psg_optimizer* o, int mode) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
-    if (mode < 0 || mode > 4) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 4", mode); return PSG_ERR_INVALID; }
+    if (mode < 0 || mode > 5) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 5", mode); return PSG_ERR_INVALID; }
     o->pcg_mode = mode;
     return PSG_OK;
 }

@@ -767,7 +767,7 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
 
 // launch geometry of the cooperative kernels, queried once per device (the queries cost microseconds each, the solve runs
 // every outer iteration)
-struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_small1024 = 0, per_sm_1 = 0, per_sm_4 = 0; };
+struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_small1024 = 0, per_sm_4_1024 = 0, per_sm_1 = 0, per_sm_4 = 0; };
 static const PcgGeometry& pcg_geometry() {
     static PcgGeometry g[64];
     int dev = 0;
@@ -780,6 +780,7 @@ static const PcgGeometry& pcg_geometry() {
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small1024, k_dist_solve_small<1024>, 1024, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_1, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4_1024, k_dist_pcg<1024, 4>, 1024, 0));
     }
     return e;
 }
@@ -809,12 +810,14 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
     // grid kernel geometry: one row per thread while that still leaves SMs idle, four rows per thread beyond
     const int rpt = (S <= sms * kPcgBlock * 2) ? 1 : 4;
     int grid = 0;
+    // large surfaces: 1024-thread blocks, a quarter of the blocks at every grid barrier (mode 5 keeps 256 for comparison)
+    const int bsz = (rpt == 4 && o->pcg_mode != 5 && geo.per_sm_4_1024 >= 1) ? 1024 : kPcgBlock;
     if (!use_cluster) {
-        int per_sm = rpt == 1 ? geo.per_sm_1 : geo.per_sm_4;
+        int per_sm = bsz == 1024 ? geo.per_sm_4_1024 : (rpt == 1 ? geo.per_sm_1 : geo.per_sm_4);
         if (per_sm < 1) { set_error("PCG kernel does not fit on an SM"); throw CudaError{-1}; }
         if (per_sm > 4) per_sm = 4;
         grid = sms * per_sm;
-        const int need = (S + kPcgBlock * rpt - 1) / (kPcgBlock * rpt);
+        const int need = (S + bsz * rpt - 1) / (bsz * rpt);
         if (grid > need) grid = need;
     }
     o->pcg_partials.alloc((size_t)3 * (use_cluster ? kClusterMax : grid) + 1);
@@ -848,6 +851,7 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
         void* args[] = { &A, &pbuf };
         Prof pf(o->stream, KID_PCG_SOLVE);
         if (rpt == 1) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 1>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
+        else if (bsz == 1024) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<1024, 4>, dim3(grid), dim3(1024), args, 0, o->stream));
         else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_pcg<kPcgBlock, 4>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
     }
 }
