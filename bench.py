@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep-split", type=int, default=0, choices=[0, 1, 2, 4, 8], help="psg_opt_set_sweep_split (0 = chosen per launch)")
     ap.add_argument("--pcg-mode", type=int, default=0, choices=[0, 1, 2, 3, 4, 5], help="psg_opt_set_pcg_mode (0 = default)")
     ap.add_argument("--multi", default="auto", choices=["auto", "shard", "replicas"],
                     help="N > 1: shard ONE workload over the ranks (strong scaling), run one independent keyframe set per rank "
@@ -280,6 +281,8 @@ def run_ours(a):
     sc, vs, T, gv, go, img_pin, pose_pin = job
     if a.pcg_mode:
         go.set_pcg_mode(a.pcg_mode)
+    if a.sweep_split:
+        go.set_sweep_split(a.sweep_split)
     images_np, poses_np = img_pin.numpy(), pose_pin.numpy()
 
     def handoff():
