@@ -123,11 +123,13 @@ def main():
     H, W = d16s[0].shape
     t_load = time.perf_counter() - t0
     depth0 = (d16s[0].astype(np.float32) * unit).astype(np.float32)
-    centroid = compute_centroid(K, depth0, poses[0])
 
     import torch
 
     import psgradientsdf_b200 as psg
+
+    centroid = psg.compute_centroid(K, depth0, poses[0])            # psg_compute_centroid: host code of the library
+    assert np.array_equal(centroid, compute_centroid(K, depth0, poses[0])), "library centroid differs from the numpy restatement"
 
     t0 = time.perf_counter()
     nest = psg.NormalEstimator(W, H, K, 11)
