@@ -3,6 +3,9 @@
 #include <cmath>
 #include <cstddef>
 #include <vector>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include "host_solve.h"
 
@@ -12,6 +15,31 @@ namespace psg {
 // packet, no FMA): two packet accumulators over strides of 8, their sum, one more packet if the length allows, the horizontal sum
 // (l0 + l2) + (l1 + l3), then the tail element by element (third/eigen/Eigen/src/Core/Redux.h:236-281, arch/SSE/PacketMath.h
 // predux).  Besides matching the reference's rounding it keeps eight independent accumulation chains in flight.
+#if defined(__SSE2__)
+// the same packet operations Eigen issues (pmul, padd, predux of arch/SSE/PacketMath.h)
+static inline float eigen_dot(const float* a, const float* b, int n) {
+    if (n < 4) {
+        float r = a[0] * b[0];
+        for (int i = 1; i < n; ++i) r += a[i] * b[i];
+        return r;
+    }
+    const int aligned = n & ~3, aligned2 = n & ~7;
+    __m128 p0 = _mm_mul_ps(_mm_loadu_ps(a), _mm_loadu_ps(b));
+    if (aligned > 4) {
+        __m128 p1 = _mm_mul_ps(_mm_loadu_ps(a + 4), _mm_loadu_ps(b + 4));
+        for (int i = 8; i < aligned2; i += 8) {
+            p0 = _mm_add_ps(p0, _mm_mul_ps(_mm_loadu_ps(a + i), _mm_loadu_ps(b + i)));
+            p1 = _mm_add_ps(p1, _mm_mul_ps(_mm_loadu_ps(a + i + 4), _mm_loadu_ps(b + i + 4)));
+        }
+        p0 = _mm_add_ps(p0, p1);
+        if (aligned > aligned2) p0 = _mm_add_ps(p0, _mm_mul_ps(_mm_loadu_ps(a + aligned2), _mm_loadu_ps(b + aligned2)));
+    }
+    const __m128 t = _mm_add_ps(p0, _mm_movehl_ps(p0, p0));
+    float r = _mm_cvtss_f32(_mm_add_ss(t, _mm_shuffle_ps(t, t, 1)));
+    for (int i = aligned; i < n; ++i) r += a[i] * b[i];
+    return r;
+}
+#else
 static inline float eigen_dot(const float* a, const float* b, int n) {
     if (n < 4) {
         float r = a[0] * b[0];
@@ -34,6 +62,7 @@ static inline float eigen_dot(const float* a, const float* b, int n) {
     for (int i = aligned; i < n; ++i) r += a[i] * b[i];
     return r;
 }
+#endif
 
 // tmp = H.selfadjointView<Lower>() * p for block-diagonal H: Eigen walks column j, adds the diagonal term to res[j], scatters
 // l * p[j] into res[i] for the rows i > j below it while gathering res_j += l * p[i], and adds res_j to res[j] last
