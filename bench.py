@@ -6,25 +6,25 @@
 
 A *step* is one outer ("LM") iteration of the alternating optimizer over the whole keyframe set
 (PsOptimizer.cpp:303-360): albedo, light, distance and pose blocks, each followed by the energy evaluation the
-reference logs.  The reference spends 8 sweeps over all active (surface voxel, keyframe) pairs on that; here every
-block's sweep also returns the energy of the state it started from, so 5 sweeps give the same 4 updates and 4 logged
-energies, plus the distance PCG and the small host solves.  metric = active pair evaluations per second (pairs x sweeps executed / time);
-ms_per_step = ms per LM iteration.
+reference logs.  The reference spends 8 sweeps over all active (surface voxel, keyframe) pairs on that (computeResidual
+inside every optimize*All + getPSEnergy after it); here every block's sweep also returns the energy of the state it
+started from, so 5 sweeps give the same 4 updates and 4 logged energies, plus the distance PCG and the small solves.
+metric = active pair evaluations per second (pairs x sweeps executed / time); ms_per_step = ms per LM iteration.
 
-`value`      : inputs resident in HBM when the timed region starts (volume fused, keyframes uploaded, surface list built).
+`value`      : inputs resident in HBM when the timed region starts (volume fused, keyframes uploaded, surface list built);
+               timed with CUDA events on the library's stream (psg_debug_timer_*), L2 flushed between steps.
 `e2e`        : the same iteration driven from HOST buffers through the C ABI: every step re-sends the keyframe images and
                poses from pinned host memory (psg_opt_set_keyframes), rebuilds the surface list (psg_opt_init), runs
                initAlbedo + one LM iteration and reads energies, poses and light back.
-`roofline`   : dominant kernel by device time, timed live with CUDA events on the launching stream (psg_profile_*).
-`cpu_baseline`: the reference's getPSEnergy() on this box's host (1 thread: the reference is single-threaded), on a
-               bounded sample of the same workload.
-At N > 1 (--multi): "shard" splits ONE workload over the ranks (strong scaling): every rank holds the volume and the work list,
-the sweeps are split round-robin over 32-slot blocks of the visibility-sorted work list, and the library combines the results
-with NCCL (all-reduce of energies and of the light / pose normal equations, all-gather of albedo and of the distance stencil
-blocks, replicated distance solve) -- see DESIGN.md section 7.  "replicas" gives every rank its own keyframe set (weak scaling,
-no data-path collective; value = pairs of all ranks / slowest rank's time).  "auto" (default) applies the library's own rule:
-sharding one workload pays from 2e6 visible pairs per rank; the default 128^3 x 30 workload has 0.26e6 in total, so N GPUs
-serve N keyframe sets, while --grid 1024 --frames 64 is sharded.
+`roofline`   : the dominant kernel of the step BY DEVICE TIME over all kernels (sweeps and the distance solve alike), timed live
+               with CUDA events on the launching stream (psg_profile_*); `kernels` has every kernel's bytes and fraction.
+`config.grids`: the same step on the larger BASELINE grids (256^3 LED, 512^3 SH1), a few steps each, with per-kernel fractions.
+`cpu_baseline`: the reference's own optimizer (oracle/_ref, 1 thread: the reference is single-threaded) on this box's host:
+               one getPSEnergy() sweep and one full LM iteration (4 optimize*All + 4 getPSEnergy) of the same workload, plus
+               the O(1)-membership C port (oracle/psg_oracle.c) for the non-pathological comparison.
+`--impl reference`: a step is one full LM iteration of the reference on a bounded keyframe subset of the same fused volume.
+At N > 1 every rank joins ONE communicator; the headline workload follows --multi and
+`config.strong_512` reports one 512^3 x 30 job sharded over the N ranks (z-slab row ranges, distributed distance solve).
 """
 from __future__ import annotations
 
@@ -43,6 +43,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "active voxel-frame residual+Jacobian evaluations per second (128^3 SH1 LM iteration)"
 UNIT = "evals/s"
+SWEEPS_PER_STEP = 5        # ours: 4 block sweeps (each also yields the energy of the state it starts from) + 1 energy sweep
+REF_SWEEPS_PER_STEP = 8    # reference: computeResidual inside each optimize*All + getPSEnergy after it
 
 
 def parse():
@@ -57,19 +59,22 @@ def parse():
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-grids", action="store_true", help="skip the 256^3 LED / 512^3 SH1 legs (config.grids, config.strong_512)")
     ap.add_argument("--sweep-split", type=int, default=0, choices=[0, 1, 2, 4, 8], help="psg_opt_set_sweep_split (0 = chosen per launch)")
-    ap.add_argument("--pcg-mode", type=int, default=0, choices=[0, 1, 2, 3, 4, 5], help="psg_opt_set_pcg_mode (0 = default)")
+    ap.add_argument("--pcg-mode", type=int, default=0, help="psg_opt_set_pcg_mode (0 = default)")
     ap.add_argument("--multi", default="auto", choices=["auto", "shard", "replicas"],
-                    help="N > 1: shard ONE workload over the ranks (strong scaling), run one independent keyframe set per rank "
-                         "(weak scaling), or choose by the library's sharding threshold (2e6 visible pairs per rank)")
-    ap.add_argument("--ref-keyframes", type=int, default=30,
-                    help="keyframes in the reference-arm sample (the reference is O(S^2 F): 30 keyframes at 128^3 = ~3 s per sweep)")
+                    help="N > 1 headline workload: shard ONE workload over the ranks (strong scaling), run one independent keyframe "
+                         "set per rank (weak scaling), or choose by the library's sharding threshold")
+    ap.add_argument("--ref-keyframes", type=int, default=4,
+                    help="keyframes in a step of the reference arm (one reference LM iteration costs ~2 s per keyframe at 128^3)")
+    ap.add_argument("--cpu-iteration-keyframes", type=int, default=30,
+                    help="keyframes in cpu_baseline's single reference LM iteration (30 = the full workload, ~40-60 s once)")
     return ap.parse_args()
 
 
-def workload_name(a):
-    return (f"synthetic TUM-style RGB-D orbit, {a.model}, {a.grid}^3 grid, {a.frames} keyframes {a.width}x{a.height}, "
-            f"light+albedo+distance+pose")
+def workload_name(a, grid=None, model=None, frames=None):
+    return (f"synthetic TUM-style RGB-D orbit, {model or a.model}, {grid or a.grid}^3 grid, {frames or a.frames} keyframes "
+            f"{a.width}x{a.height}, light+albedo+distance+pose")
 
 
 def peaks():
@@ -124,41 +129,57 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def build_scene(a, seed=1234):
+def build_scene(a, seed=1234, model=None):
     from psgradientsdf_b200 import synth
-    sc = synth.make_scene(F=a.frames, H=a.height, W=a.width, model=a.model, seed=seed)
-    vs, T = synth.grid_for_scene(a.grid)
-    return sc, vs, T
+    return synth.make_scene(F=a.frames, H=a.height, W=a.width, model=model or a.model, seed=seed)
 
 
-def se3_parts(pose):
-    """R, t the reference's SE3(pose) hands to update(); orthonormal input poses make this the identity up to rounding,
-    and the same R, t go to every implementation."""
-    from oracle import pyref
-    if pyref.available():
-        return pyref.se3_from_matrix(pose)
-    return pose[:3, :3].copy(), pose[:3, 3].copy()
+def pose_parts(pose):
+    """R, t of a camera-to-world 4x4 for the fusion call.  The synthetic poses are orthonormal by construction, so this is what
+    the reference's SE3(pose) hands to update() up to rounding; no implementation is consulted to prepare the inputs."""
+    return np.ascontiguousarray(pose[:3, :3], np.float32), np.ascontiguousarray(pose[:3, 3], np.float32)
+
+
+def reg_for(model):
+    """(reg_n, reg_l, damping): config_skorates.json for SH, config_basket_LED.json for LED."""
+    return (0.1, 5.0, 3.0) if model == "LED" else (10.0, 0.0, 1.0)
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
-def reference_sample(a, sc, vs, T, nkey):
-    """The reference's own optimizer on the same fused volume with `nkey` of the keyframes."""
+def reference_job(a, sc, nkey):
+    """The reference's own optimizer (oracle/_ref) on the same fused volume with `nkey` of the keyframes, after init + initAlbedo."""
     from oracle import pyref
+    from psgradientsdf_b200 import synth
     G = a.grid
+    vs, T = synth.grid_for_scene(G)
+    reg_n, reg_l, damping = reg_for(a.model)
     rv = pyref.RefVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5)
-    reg_l = 5.0 if a.model == "LED" else 0.0
-    ro = pyref.RefOptimizer(rv, a.model, vs, sc.K, "/tmp/", reg_n=10.0, reg_l=reg_l)
+    ro = pyref.RefOptimizer(rv, a.model, vs, sc.K, "/tmp/", reg_n=reg_n, reg_l=reg_l)
     for f in range(a.frames):
         rv.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
-    # the reference's membership test is a linear scan (SURVEY F5): a sweep costs ~3 s x (G/128)^4 x nkey/30 on one core;
-    # keep the sample around 20 s on larger grids
-    nkey = max(1, min(nkey, a.frames, int(200.0 / (G / 128.0) ** 4)))
+    nkey = max(1, min(nkey, a.frames))
     keys = np.unique(np.linspace(0, a.frames - 1, nkey).round().astype(np.int32))
     ro.set_keyframes(keys, sc.poses_init[keys], sc.color[keys])
     ro.init()
     ro.init_albedo()
     _, _, A = ro.energy()
     return rv, ro, int(A), keys
+
+
+def reference_iteration(ro, model):
+    """One pass of the reference's while-body through its own optimize*All + getPSEnergy (PsOptimizer.cpp:303-360,
+    LedOptimizer.cpp:343-403); returns per-block wall seconds the way the reference's Timer would log them."""
+    reg_n, reg_l, damping = reg_for(model)
+    order = ["light", "albedo", "dist", "pose"] if model == "LED" else ["albedo", "light", "dist", "pose"]
+    times = {}
+    for blk in order:
+        t0 = time.perf_counter()
+        ro.block_reference(blk, damping, False, reg_n != 0.0, reg_l != 0.0)
+        t1 = time.perf_counter()
+        ro.ps_energy()
+        t2 = time.perf_counter()
+        times[blk] = round(t1 - t0, 3); times[blk + "_energy"] = round(t2 - t1, 3)
+    return times
 
 
 def run_reference(a):
@@ -169,21 +190,26 @@ def run_reference(a):
     if not pyref.available():
         emit({"impl": "reference", "unavailable": "oracle/_ref/libpsgref.so missing (reference sources were not built)"})
         return
-    sc, vs, T = build_scene(a)
-    rv, ro, A, keys = reference_sample(a, sc, vs, T, a.ref_keyframes)
+    sc = build_scene(a)
+    # the reference's membership test is a linear scan: an LM iteration costs ~2 s x (G/128)^4 per keyframe on one
+    # core; keep a step around 5-10 s
+    nkey = max(1, min(a.ref_keyframes, int(round(a.ref_keyframes / (a.grid / 128.0) ** 4)) or 1))
+    rv, ro, A, keys = reference_job(a, sc, nkey)
     for _ in range(a.warmup):
-        ro.ps_energy()
+        reference_iteration(ro, a.model)
     t0 = time.perf_counter()
+    last = None
     for _ in range(a.steps):
-        ro.ps_energy()
+        last = reference_iteration(ro, a.model)
     dt = time.perf_counter() - t0
-    val = A * a.steps / dt
-    sample = (f"getPSEnergy() (PsOptimizer.cpp:47-78) over the full fused {a.grid}^3 volume with {len(keys)} of the "
-              f"{a.frames} keyframes: S={ro.S} surface voxels, {A} active pairs per step")
+    val = A * REF_SWEEPS_PER_STEP * a.steps / dt
+    sample = (f"one LM iteration per step (optimizeAlbedoAll/LightAll/DistAll/PosesAll + getPSEnergy after each, "
+              f"PsOptimizer.cpp:303-360) on the full fused {a.grid}^3 volume with {len(keys)} of the {a.frames} keyframes: "
+              f"S={ro.S} surface voxels, {A} active pairs x {REF_SWEEPS_PER_STEP} sweeps per step")
     out = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
            "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic", "impl": "reference",
-           "config": {"workload": workload_name(a), "sample": sample},
+           "config": {"workload": workload_name(a), "sample": sample, "block_seconds_last_step": last},
            "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": "reference", "sample": sample,
                             "host_cores": os.cpu_count()},
            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -192,39 +218,132 @@ def run_reference(a):
 
 
 # ------------------------------------------------------------------------------------------------ our arm
-_ITER = {}
-
-
-def lm_iteration(go, model, damping=1.0):
-    """One pass of the reference's while-body (PsOptimizer.cpp:303-360 / LedOptimizer.cpp:343-403): psg_opt_iteration on structs
-    that are built once, as a C++ host's loop holds them."""
-    key = (id(go), model, damping)
-    if key not in _ITER:
-        _ITER[key] = go.iteration_config(True, True, True, True, damping=damping, normal_reg=True, laplacian_reg=(model == "LED"))
-    cfg, info = _ITER[key]
-    go.iteration_raw(cfg, info)
-    return info.energy_end, info.n_active_end   # the energies the reference logs after each block are in info.block[...]
-
-
 def sweep_bytes(A, S, F, out_block):
     """Algorithmic bytes of one sweep (SURVEY.md 8d / BASELINE.md): 48 A + 80 S + out_block S + 128 F."""
     return 48 * A + 80 * S + out_block * S + 128 * F
 
 
+def kernel_bytes(name, A, S, F, pcg_iters):
+    """Algorithmic bytes per launch; None for kernels without a byte model."""
+    out_block = {"k_sweep<ALBEDO>": 24, "k_sweep<DIST>": 56}
+    if name.startswith("k_sweep<"):
+        return sweep_bytes(A, S, F, out_block.get(name, 0))
+    if name == "k_dist_pcg":       # 76 S per CG iteration (+1 for the start-up pass) + 56 S to read the stencil blocks once
+        return 76 * S * (pcg_iters + 1) + 56 * S
+    if name in ("k_dist_assemble",):
+        return 56 * S + 12 * S
+    if name in ("k_dist_update", "k_grad_update", "k_reg_energy"):
+        return 64 * S
+    return None
+
+
 def ncu_traffic(a, kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture
-    (profiles/r1_traffic.json); None when the capture was taken on another workload."""
-    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
-    try:
-        with open(p) as f:
-            t = json.load(f)
-    except OSError:
-        return None
-    w = t.get("workload", {})
-    if (w.get("grid"), w.get("frames"), w.get("model"), w.get("height"), w.get("width")) != (a.grid, a.frames, a.model, a.height, a.width):
-        return None
-    k = t.get("kernels", {}).get(kernel)
-    return None if k is None else k["dram_read_bytes"] + k["dram_write_bytes"]
+    (profiles/*_traffic.json, newest round first); None when the capture was taken on another workload."""
+    for fn in ("r2_traffic.json", "r1_traffic.json"):
+        p = os.path.join(ROOT, "profiles", fn)
+        try:
+            with open(p) as f:
+                t = json.load(f)
+        except OSError:
+            continue
+        w = t.get("workload", {})
+        if (w.get("grid"), w.get("frames"), w.get("model"), w.get("height"), w.get("width")) != (a.grid, a.frames, a.model, a.height, a.width):
+            continue
+        k = t.get("kernels", {}).get(kernel)
+        if k is not None:
+            return k["dram_read_bytes"] + k["dram_write_bytes"]
+    return None
+
+
+class Job:
+    """One keyframe set fused into its volume, optimizer created, per-step inputs in pinned host memory."""
+
+    def __init__(self, a, local, sc, G, model, max_frames=64):
+        import torch
+
+        import psgradientsdf_b200 as psg
+        from psgradientsdf_b200 import synth
+        self.a, self.model, self.G = a, model, G
+        self.F = F = sc.color.shape[0]
+        vs, T = synth.grid_for_scene(G)
+        reg_n, reg_l, self.damping = reg_for(model)
+        self.reg_n, self.reg_l = reg_n, reg_l
+        self.gv = gv = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(max_frames, F), device=local)
+        gv.set_zmin(0.5); gv.set_zmax(3.5)
+        self.go = psg.Optimizer(gv, vs, sc.K, model=model, reg_n=reg_n, reg_l=reg_l)
+        for f in range(F):
+            R, t = pose_parts(sc.poses_gt[f])
+            if f > 0:
+                gv.increase_counter()
+            gv.update(sc.color[f], sc.depth[f], sc.K, R, t, sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv)
+        self.img_pin = torch.from_numpy(np.ascontiguousarray(sc.color)).pin_memory()
+        self.pose_pin = torch.from_numpy(np.ascontiguousarray(sc.poses_init)).pin_memory()
+        self.images_np, self.poses_np = self.img_pin.numpy(), self.pose_pin.numpy()
+        self.fi = np.arange(F, dtype=np.int32)
+        self.cfg = None
+
+    def handoff(self):
+        self.go.set_keyframes(self.fi, self.poses_np, self.images_np)
+        self.go.init()
+        self.go.init_albedo()
+
+    def iteration(self):
+        """One pass of the reference's while-body: psg_opt_iteration on structs built once, as a C++ host's loop holds them."""
+        if self.cfg is None:
+            self.cfg = self.go.iteration_config(True, True, True, True, damping=self.damping, normal_reg=self.reg_n != 0.0,
+                                                laplacian_reg=self.reg_l != 0.0)
+        cfg, info = self.cfg
+        self.go.iteration_raw(cfg, info)
+        return info
+
+    def close(self):
+        self.go.close(); self.gv.close()
+
+
+def timed_steps(job, steps, flush, sync, barrier=None):
+    """K iterations, each bracketed by CUDA events on the library's stream (L2 flushed in between); returns
+    (device seconds, host wall seconds, last info)."""
+    dev_ms, wall = 0.0, 0.0
+    info = None
+    for _ in range(steps):
+        flush.zero_()
+        sync()
+        if barrier is not None:
+            barrier()
+        t0 = time.perf_counter()
+        job.go.timer_begin()
+        info = job.iteration()
+        dev_ms += job.go.timer_end()
+        wall += time.perf_counter() - t0
+    return dev_ms * 1e-3, wall, info
+
+
+def kernel_table(prof, A, S, F, pcg_iters, peak):
+    table = {}
+    for name, (n, ms) in prof.items():
+        row = {"launches": n, "ms_total": round(ms, 4), "ms_avg": round(ms / n, 5)}
+        kb = kernel_bytes(name, A, S, F, pcg_iters)
+        if kb is not None:
+            row["algorithmic_bytes"] = int(kb)
+            row["frac"] = round(kb / (ms / n * 1e-3) / 1e9 / peak, 4)
+        table[name] = row
+    return table
+
+
+def profiled_steps(job, steps, flush, sync, peak):
+    """The same steps once more with the library's CUDA-event launch timer on (kept out of the timed region: two event
+    records per launch would be charged to the step).  Returns the per-kernel table."""
+    import psgradientsdf_b200 as psg
+    psg.profile_reset(); psg.profile_enable(True)
+    info = None
+    for _ in range(steps):
+        flush.zero_(); sync()
+        info = job.iteration()
+    sync()
+    prof = psg.profile_table()
+    psg.profile_enable(False)
+    return prof, info
 
 
 def run_ours(a):
@@ -239,73 +358,16 @@ def run_ours(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback")
     torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     G, F = a.grid, a.frames
-    reg_l = 5.0 if a.model == "LED" else 0.0
-    fi = np.arange(F, dtype=np.int32)
+    peak, peak_src = peaks()
     SHARD_MIN_PAIRS = 2_000_000       # kShardMinPairsPerRank (psgradientsdf_b200/csrc/comm.cu)
 
-    def make_job(seed):
-        """One keyframe set fused into its volume, optimizer created, per-step inputs in pinned host memory."""
-        sc, vs, T = build_scene(a, seed)
-        gv = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, max(64, F), device=local)
-        gv.set_zmin(0.5); gv.set_zmax(3.5)
-        go = psg.Optimizer(gv, vs, sc.K, model=a.model, reg_n=10.0, reg_l=reg_l)
-        for f in range(F):
-            R, t = se3_parts(sc.poses_gt[f])
-            if f > 0:
-                gv.increase_counter()
-            gv.update(sc.color[f], sc.depth[f], sc.K, R, t, sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv)
-        img_pin = torch.from_numpy(np.ascontiguousarray(sc.color)).pin_memory()
-        pose_pin = torch.from_numpy(np.ascontiguousarray(sc.poses_init)).pin_memory()
-        return sc, vs, T, gv, go, img_pin, pose_pin
-
-    # N > 1: one workload sharded over the ranks, or one independent keyframe set per rank.  "auto" asks the library's own rule:
-    # sharding pays from 2e6 visible (surface voxel, keyframe) pairs per rank (DESIGN.md section 7); rank 0 builds the standard
-    # workload, counts, and tells the others, which then build the standard workload (shard) or their own (replicas).
-    mode = "single" if world == 1 else a.multi
-    job = None
-    if world > 1 and mode == "auto":
-        verdict = [None]
-        if rank == 0:
-            job = make_job(1234)
-            job[4].set_keyframes(fi, job[6].numpy(), job[5].numpy()); job[4].init()
-            verdict[0] = "shard" if job[4].is_sharded()[1] // world >= SHARD_MIN_PAIRS else "replicas"
-        dist.broadcast_object_list(verdict, src=0)
-        mode = verdict[0]
-    seed = 1234 + (17 * rank if mode == "replicas" else 0)
-    if job is None:
-        job = make_job(seed)
-    sc, vs, T, gv, go, img_pin, pose_pin = job
-    if a.pcg_mode:
-        go.set_pcg_mode(a.pcg_mode)
-    if a.sweep_split:
-        go.set_sweep_split(a.sweep_split)
-    images_np, poses_np = img_pin.numpy(), pose_pin.numpy()
-
-    def handoff():
-        go.set_keyframes(fi, poses_np, images_np)
-        go.init()
-        go.init_albedo()
-
-    if mode == "shard":
-        ids = [psg.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(ids, src=0)
-        go.comm_init(ids[0], rank, world)
-        go.set_shard_policy(1)
-    handoff()
-    S = go.S
-    E0, A = go.energy()
-    # units of one step over the whole job: the shared work list when sharded, the sum of the ranks' own lists otherwise
-    A_job, S_job = A, S
-    vis_pairs = go.is_sharded()[1]
-    if mode == "replicas":
-        tot = torch.tensor([A, S], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(tot)
-        A_job, S_job = int(tot[0].item()), int(tot[1].item())
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")   # > 126 MB L2
+    def sync():
+        torch.cuda.synchronize()
 
     def barrier():
         torch.cuda.synchronize()
@@ -313,168 +375,247 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    sweeps_per_step = 5   # 4 block sweeps (each also yields the energy of the state it starts from) + 1 energy sweep
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # N > 1: one workload sharded over the ranks, or one independent keyframe set per rank.  "auto" asks the library's own rule
+    # (DESIGN.md section 7); rank 0 builds the standard workload, counts, and tells the others.
+    mode = "single" if world == 1 else a.multi
+    job = None
+    if world > 1 and mode == "auto":
+        verdict = [None]
+        if rank == 0:
+            job = Job(a, local, build_scene(a, 1234), G, a.model)
+            job.go.set_keyframes(job.fi, job.poses_np, job.images_np); job.go.init()
+            verdict[0] = "shard" if job.go.is_sharded()[1] // world >= SHARD_MIN_PAIRS else "replicas"
+        dist.broadcast_object_list(verdict, src=0)
+        mode = verdict[0]
+    seed = 1234 + (17 * rank if mode == "replicas" else 0)
+    if job is None:
+        job = Job(a, local, build_scene(a, seed), G, a.model)
+    go = job.go
+    if a.pcg_mode:
+        go.set_pcg_mode(a.pcg_mode)
+    if a.sweep_split:
+        go.set_sweep_split(a.sweep_split)
+
+    def join_comm(g):
+        ids = [psg.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        g.comm_init(ids[0], rank, world)
+        g.set_shard_policy(1)
+
+    if mode == "shard":
+        join_comm(go)
+    job.handoff()
+    S = go.S
+    E0, A = go.energy()
+    # units of one step over the whole job: the shared work list when sharded, the sum of the ranks' own lists otherwise
+    A_job, S_job = A, S
+    vis_pairs = go.is_sharded()[1]
+    if mode == "replicas":
+        tot = torch.tensor([A, S], dtype=torch.float64, device=dev)
+        dist.all_reduce(tot)
+        A_job, S_job = int(tot[0].item()), int(tot[1].item())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
     # ---- device-resident leg
     for _ in range(a.warmup):
-        lm_iteration(go, a.model)
+        job.iteration()
     sampler = ClockSampler(local); sampler.start()
     launches0 = psg.kernel_launches()
     barrier()
     psg.host_times(reset=True)
-    t_total = 0.0
-    E = None
-    for _ in range(a.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        E = lm_iteration(go, a.model)
-        torch.cuda.synchronize()
-        t_total += time.perf_counter() - t0
+    t_dev, t_wall, info = timed_steps(job, a.steps, flush, sync, barrier if mode == "shard" else None)
     host_us = psg.host_times(reset=True)
     barrier()
     launches = psg.kernel_launches() - launches0
     clocks = sampler.stop()
-    # same K steps once more with the library's CUDA-event launch timer on (kept out of the timed region above: two event
-    # records per launch would be charged to the step)
-    psg.profile_reset(); psg.profile_enable(True)
-    for _ in range(a.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        lm_iteration(go, a.model)
-    torch.cuda.synchronize()
-    prof = psg.profile_table()
-    psg.profile_enable(False)
-    tt = torch.tensor([t_total], dtype=torch.float64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    t_max = float(tt.item())
-    value = A_job * sweeps_per_step * a.steps / t_max      # whole job: the shared list once, or the sum of the ranks' own lists
+    prof, pinfo = profiled_steps(job, a.steps, flush, sync, peak)
+    pcg_iters = int(pinfo.block[2].cg_iterations)
+    t_max = allmax(t_dev)
+    t_wall_max = allmax(t_wall)
+    value = A_job * SWEEPS_PER_STEP * a.steps / t_max      # whole job: the shared list once, or the sum of the ranks' own lists
 
     # ---- e2e leg: host buffers -> C ABI every step (keyframe upload overlapped with the work-list build: the pinned image
     # buffers stay valid until psg_opt_init returns, as psg_opt_set_upload_overlap requires)
     go.set_upload_overlap(True)
-    h2d = images_np.nbytes + poses_np.nbytes
-    d2h = poses_np.nbytes + 4 * go.light().size + 8 * 6
-    for _ in range(min(a.warmup, 2)):
-        handoff(); lm_iteration(go, a.model)
-    barrier()
-    te = 0.0
-    for _ in range(a.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        handoff()
-        lm_iteration(go, a.model)
-        go.poses(); go.light()
-        torch.cuda.synchronize()
-        te += time.perf_counter() - t0
-    barrier()
-    tte = torch.tensor([te], dtype=torch.float64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(tte, op=dist.ReduceOp.MAX)
-    e2e_value = A_job * (sweeps_per_step + 1) * a.steps / float(tte.item())   # + the initAlbedo sweep
+    h2d = job.images_np.nbytes + job.poses_np.nbytes
+    d2h = job.poses_np.nbytes + 4 * go.light().size + 8 * 6
+
+    def e2e_leg(handoff):
+        for _ in range(min(a.warmup, 2)):
+            handoff(); job.iteration()
+        barrier()
+        te = 0.0
+        for _ in range(a.steps):
+            flush.zero_()
+            sync()
+            t0 = time.perf_counter()
+            handoff()
+            job.iteration()
+            go.poses(); go.light()
+            sync()
+            te += time.perf_counter() - t0
+        barrier()
+        return allmax(te)
+
+    te = e2e_leg(job.handoff)
+    e2e_value = A_job * (SWEEPS_PER_STEP + 1) * a.steps / te   # + the initAlbedo sweep
 
     # same hand-off with the keyframes as the loader read them (8-bit BGR, psg_opt_set_keyframes_u8): reported beside e2e
-    c8_pin = torch.from_numpy(np.ascontiguousarray(np.round(sc.color * 255.0).astype(np.uint8))).pin_memory()
+    c8_pin = torch.from_numpy(np.ascontiguousarray(np.round(job.images_np * 255.0).astype(np.uint8))).pin_memory()
     c8_np = c8_pin.numpy()
 
     def handoff_u8():
-        go.set_keyframes_u8(fi, poses_np, c8_np)
+        go.set_keyframes_u8(job.fi, job.poses_np, c8_np)
         go.init()
         go.init_albedo()
 
-    handoff_u8(); lm_iteration(go, a.model)
-    barrier()
-    te8 = 0.0
-    for _ in range(a.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        handoff_u8()
-        lm_iteration(go, a.model)
-        go.poses(); go.light()
-        torch.cuda.synchronize()
-        te8 += time.perf_counter() - t0
-    barrier()
-    tte8 = torch.tensor([te8], dtype=torch.float64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(tte8, op=dist.ReduceOp.MAX)
-    e2e_u8 = {"value": A_job * (sweeps_per_step + 1) * a.steps / float(tte8.item()), "unit": UNIT,
-              "h2d_bytes_per_step": int(c8_np.nbytes + poses_np.nbytes), "d2h_bytes_per_step": int(d2h),
-              "ms_per_step": 1e3 * float(tte8.item()) / a.steps,
+    te8 = e2e_leg(handoff_u8)
+    e2e_u8 = {"value": A_job * (SWEEPS_PER_STEP + 1) * a.steps / te8, "unit": UNIT,
+              "h2d_bytes_per_step": int(c8_np.nbytes + job.poses_np.nbytes), "d2h_bytes_per_step": int(d2h),
+              "ms_per_step": 1e3 * te8 / a.steps,
               "step": "as e2e, keyframes handed over as 8-bit BGR (psg_opt_set_keyframes_u8) and converted on the device"}
+    go.set_upload_overlap(False)
+    energy_end = float(info.energy_end) if info is not None else None
+    if mode == "shard":
+        go.comm_destroy()
+    job.close()
+    del job
+
+    # ---- the larger BASELINE grids: a few steps each, per-kernel fractions (N = 1), and ONE 512^3 job sharded over the ranks (N > 1)
+    grids, strong = None, None
+    if not a.no_grids:
+        sc_big = {}
+
+        def big_job(model, Gb):
+            if model not in sc_big:
+                sc_big[model] = build_scene(a, 1234, model=model)
+            return Job(a, local, sc_big[model], Gb, model)
+
+        def run_grid(model, Gb, nsteps=3, shard=False):
+            j = big_job(model, Gb)
+            if shard:
+                join_comm(j.go)
+            j.handoff()
+            Eb, Ab = j.go.energy()
+            for _ in range(2):
+                j.iteration()
+            barrier()
+            td, tw, inf = timed_steps(j, nsteps, flush, sync, barrier if shard else None)
+            td = allmax(td)
+            prof_b, pinf = profiled_steps(j, nsteps, flush, sync, peak)
+            tab = kernel_table(prof_b, Ab // (world if shard else 1), j.go.S // (world if shard else 1), j.F,
+                               int(pinf.block[2].cg_iterations), peak)
+            out = {"workload": workload_name(a, Gb, model, j.F), "surface_voxels": int(j.go.S), "active_pairs": int(Ab),
+                   "ms_per_step": round(1e3 * td / nsteps, 4), "steps": nsteps, "pcg_iterations": int(pinf.block[2].cg_iterations),
+                   "evals_per_s": Ab * SWEEPS_PER_STEP * nsteps / td, "kernels": tab}
+            if shard:
+                out["mode"] = f"one job sharded over {world} ranks"
+                j.go.comm_destroy()
+            j.close()
+            return out
+
+        if world == 1:
+            grids = {"256^3 LED": run_grid("LED", 256), "512^3 SH1": run_grid("SH1", 512)}
+        else:
+            strong = run_grid("SH1", 512, shard=True)
 
     if rank != 0:
         if world > 1:
             dist.barrier()
-            if mode == "shard":
-                go.comm_destroy()
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel
-    peak, peak_src = peaks()
-    out_block = {"k_sweep<ALBEDO>": 24, "k_sweep<DIST>": 56}
-    best = None
-    table = {}
-    for name, (n, ms) in prof.items():
-        table[name] = {"launches": n, "ms_total": round(ms, 4), "ms_avg": round(ms / n, 5)}
-        if name.startswith("k_sweep<") and (best is None or ms > prof[best][1]):
-            best = name
+    # ---- roofline of the dominant kernel: over ALL kernels of the step by device time
+    shards = world if mode == "shard" else 1
+    table = kernel_table(prof, A // shards, S // shards, F, pcg_iters, peak)
+    best = max(prof, key=lambda k: prof[k][1]) if prof else None
     roof = None
     if best:
         n, ms = prof[best]
-        # per launch = per rank: a rank sweeps its share of the work list
-        shards = world if mode == "shard" else 1
-        bytes_launch = sweep_bytes(A // shards, S // shards, F, out_block.get(best, 0))
-        ach = bytes_launch / (ms / n * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+        row = table[best]
+        kb = row.get("algorithmic_bytes")
+        ach = (kb / (ms / n * 1e-3) / 1e9) if kb else None
+        roof = {"bound": "hbm", "kernel": best, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None,
                 "traffic": ncu_traffic(a, best) if world == 1 else None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": bytes_launch, "avg_launch_ms": ms / n,
-                "note": "instruction-issue bound, not HBM bound: see DESIGN.md section 3 / profiles/r1_summary.md"}
+                "algorithmic_bytes_per_launch": kb, "avg_launch_ms": ms / n,
+                "share_of_kernel_time": round(ms / sum(v[1] for v in prof.values()), 3),
+                "note": ("the distance solve is a chain of grid-wide barriers, the sweeps are instruction-issue bound: neither is "
+                         "HBM bound at this size (DESIGN.md section 3, profiles/r2_summary.md); config.grids has the 512^3 fractions")}
 
-    # ---- CPU baseline (reference, 1 thread) on a bounded sample
+    # ---- CPU baseline (reference sources, 1 thread): one energy sweep + one full LM iteration; and the O(1)-membership port
     cpu = None
-    if not a.no_cpu_baseline:
+    if not a.no_cpu_baseline and world == 1:
         from oracle import pyoracle, pyref
+        from psgradientsdf_b200 import synth
+        sc = build_scene(a)
+        vs, T = synth.grid_for_scene(G)
+        reg_n, reg_l, damping = reg_for(a.model)
         if pyref.available():
-            rv, ro, A_s, keys = reference_sample(a, sc, vs, T, a.ref_keyframes)
+            rv, ro, A_s, keys = reference_job(a, sc, a.cpu_iteration_keyframes)
             t0 = time.perf_counter(); ro.ps_energy(); dt = time.perf_counter() - t0
+            t0 = time.perf_counter(); blk_s = reference_iteration(ro, a.model); dti = time.perf_counter() - t0
             cpu = {"value": A_s / dt, "unit": UNIT, "cores": 1, "kind": "reference", "host_cores": os.cpu_count(),
                    "sample": f"one getPSEnergy() sweep, reference sources, {len(keys)} of {F} keyframes on the full fused "
-                             f"{G}^3 volume: S={ro.S}, {A_s} active pairs, {dt:.2f} s"}
+                             f"{G}^3 volume: S={ro.S}, {A_s} active pairs, {dt:.2f} s",
+                   "lm_iteration_ms": round(1e3 * dti, 1),
+                   "lm_iteration_evals_per_s": A_s * REF_SWEEPS_PER_STEP / dti,
+                   "lm_iteration_block_seconds": blk_s,
+                   "lm_iteration_sample": f"one pass of the while-body (PsOptimizer.cpp:303-360) through the reference's own "
+                                          f"optimize*All + getPSEnergy, {len(keys)} of {F} keyframes (BASELINE.md CPU-A)"}
             ro.close(); rv.close()
         # the O(1)-membership C port on the full workload, for the non-pathological comparison (BASELINE.md CPU-B)
         ov = pyoracle.OrVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5, max(64, F))
-        oo = pyoracle.OrOptimizer(ov, a.model, vs, sc.K, reg_n=10.0, reg_l=reg_l)
+        oo = pyoracle.OrOptimizer(ov, a.model, vs, sc.K, reg_n=reg_n, reg_l=reg_l)
         for f in range(F):
-            R, t = se3_parts(sc.poses_gt[f])
+            R, t = pose_parts(sc.poses_gt[f])
             ov.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, R, t, f > 0)
+        fi = np.arange(F, dtype=np.int32)
         oo.set_keyframes(fi, sc.poses_init, sc.color); oo.init(); oo.init_albedo()
         t0 = time.perf_counter(); _, _, A_o = oo.energy(); dt = time.perf_counter() - t0
+        order = ["light", "albedo", "dist", "pose"] if a.model == "LED" else ["albedo", "light", "dist", "pose"]
+        t0 = time.perf_counter()
+        for blk in order:
+            oo.block(blk, apply=True, damping=damping, normal_reg=reg_n != 0.0, laplacian_reg=reg_l != 0.0)
+            oo.energy()
+        dti = time.perf_counter() - t0
         port = {"value": A_o / dt, "unit": UNIT, "cores": 1, "kind": "port",
-                "sample": f"one energy sweep of oracle/psg_oracle.c (dense row map) on the full workload: {A_o} pairs, {dt:.2f} s"}
+                "sample": f"one energy sweep of oracle/psg_oracle.c (dense row map) on the full workload: {A_o} pairs, {dt:.2f} s",
+                "lm_iteration_ms": round(1e3 * dti, 1), "lm_iteration_evals_per_s": A_o * REF_SWEEPS_PER_STEP / dti,
+                "lm_iteration_sample": "the same pass through the C port's block solves + energies, all keyframes (BASELINE.md CPU-B)"}
         if cpu is None:
             cpu = port
         else:
             cpu["port"] = port
 
+    config = {"workload": workload_name(a), "surface_voxels": S_job, "active_pairs": A_job, "keyframes": F,
+              "sweeps_per_step": SWEEPS_PER_STEP, "pcg_iterations": pcg_iters, "energy_after_last_step": energy_end,
+              "timing": "CUDA events on the library's stream around each step (psg_debug_timer_*), max over ranks; host wall "
+                        "clock per step in host_ms_per_step",
+              "l2": "flushed between steps (256 MiB device write)",
+              "multi_gpu": ("single GPU" if world == 1 else
+                            f"ONE workload sharded over {world} ranks (DESIGN.md section 7)"
+                            if mode == "shard" else
+                            f"{world} independent keyframe sets, one per GPU (same geometry and camera orbit, lights and pose "
+                            f"perturbations seeded per rank), no data-path collective; surface_voxels / active_pairs are sums "
+                            f"over the ranks.  One such set has {vis_pairs} visible pairs, "
+                            f"below the {SHARD_MIN_PAIRS} per rank from which sharding one set pays "
+                            f"(DESIGN.md section 7; --multi shard forces it); config.strong_512 is the sharded job")}
+    if grids is not None:
+        config["grids"] = grids
+    if strong is not None:
+        config["strong_512"] = strong
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-           "ms_per_step": 1e3 * t_max / a.steps, "higher_is_better": True, "scaling": "strong" if mode == "shard" else "weak",
-           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": workload_name(a), "surface_voxels": S_job, "active_pairs": A_job, "keyframes": F,
-                      "sweeps_per_step": sweeps_per_step, "energy_after_last_step": E[0] if E else None,
-                      "l2": "flushed between steps (256 MiB device write); per-step host timing bracketed by device syncs, summed",
-                      "multi_gpu": ("single GPU" if world == 1 else
-                                    f"ONE workload, work list sharded over {world} ranks, NCCL all-reduce / all-gather, replicated distance solve"
-                                    if mode == "shard" else
-                                    f"{world} independent keyframe sets, one per GPU (same geometry and camera orbit, lights and pose "
-                                    f"perturbations seeded per rank), no data-path collective; surface_voxels / active_pairs are sums "
-                                    f"over the ranks.  One such set has {vis_pairs} visible pairs, "
-                                    f"below the {SHARD_MIN_PAIRS} per rank from which sharding one set pays "
-                                    f"(DESIGN.md section 7; --multi shard forces it)")},
+           "ms_per_step": 1e3 * t_max / a.steps, "host_ms_per_step": 1e3 * t_wall_max / a.steps, "higher_is_better": True,
+           "scaling": "strong" if mode == "shard" else "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                   "ms_per_step": 1e3 * float(tte.item()) / a.steps,
+                   "ms_per_step": 1e3 * te / a.steps,
                    "step": "psg_opt_set_keyframes (pinned host images + poses, upload overlapped with the work-list build) + psg_opt_init + psg_opt_init_albedo + one LM iteration + read-back"},
            "e2e_u8": e2e_u8,
            "host_thread_us_per_step": {k: round(v, 1) for k, v in host_us.items() if k != "iterations"},
@@ -482,8 +623,6 @@ def run_ours(a):
     emit(out)
     if world > 1:
         dist.barrier()
-        if mode == "shard":
-            go.comm_destroy()
         dist.destroy_process_group()
 
 

@@ -123,6 +123,12 @@ int psg_opt_destroy(psg_optimizer* opt);
  * frame_idx[k] = input-frame ordinal of keyframe k, poses F x 16, images F x H x W x 3 float BGR. */
 int psg_opt_set_keyframes(psg_optimizer* opt, int F, const int* frame_idx, const float* poses16,
                           const float* images_bgr, int H, int W);
+/* setKeytimestamps (Optimizer.h:151-154, called at main_ps.cpp:325): one NUL-terminated string per keyframe, copied.
+ * Optimizer::savePoses (OptimizerAux.cpp:580-599) prints key_stamps_[i] as the first column of
+ * after_poses_opt_<it>.txt.  F must equal the keyframe count of the last psg_opt_set_keyframes call; the strings survive
+ * later psg_opt_set_keyframes calls with the same F and are dropped when F changes.  Where the reference would index an
+ * unset key_stamps_ (undefined behaviour), this path prints the keyframe's frame_idx. */
+int psg_opt_set_keytimestamps(psg_optimizer* opt, int F, const char* const* stamps);
 
 /* {Ps,Led}Optimizer::init() (PsOptimizer.cpp:25-42, LedOptimizer.cpp:25-36): initial light, select_vis()
  * (Optimizer.cpp:30-47), getSurfaceVoxel() (OptimizerAux.cpp:237-257), LED computeLightIntensive(). */
@@ -170,11 +176,13 @@ int psg_opt_init_albedo(psg_optimizer* opt);
 int psg_opt_energy(psg_optimizer* opt, double* E, long long* n_active);
 /* Same result as psg_opt_energy, for hosts that must not trigger device allocations once they are running (all GPU
  * memory already committed to another owner, or a loop that cannot absorb the stall of an allocation).  It has no
- * counterpart in the reference.  The kernel's scratch (results, per-block partial sums, arrival counter, per-keyframe
- * table) lives in one ~4.2 MB array inside the loaded module, present on every GPU that loads the library until exit;
- * nothing is allocated or freed.  Limits and rules:
+ * counterpart in the reference.  The kernel's scratch (results, per-block partial sums, arrival counters) lives in one
+ * ~4.2 MB array inside the loaded module, present on every GPU that loads the library until exit; the per-keyframe
+ * poses and light travel as a kernel parameter.  Nothing is allocated or freed.  Limits and rules:
  *   - at most 2 097 152 surface voxels and device ordinals below 64; larger inputs are rejected with PSG_ERR_INVALID;
- *   - the first call on a device looks up the array's device address; make that first call before any stream capture;
+ *   - the first call on a device looks up the array's device address, and the driver may load the kernel's code then
+ *     (a driver-side, one-time cost); make that first call before any stream capture and before the phase in which
+ *     allocations must not happen;
  *   - all calls on a device share the array (it keeps the previous call's contents, the parts that must be zero are
  *     cleared at the start of every call), so two calls that overlap on the GPU race -- serialise them. */
 int psg_opt_energy_noalloc(psg_optimizer* opt, double* E, long long* n_active);
@@ -188,6 +196,12 @@ int psg_opt_residual(psg_optimizer* opt, float* r3, float* w3);
 /* Per pair: getIntensity's projected pixel (col m, row n) and in-bounds flag (OptimizerAux.cpp:207-231),
  * sampled RGB and rendered RGB.  S x F (x 3).  Diagnostic / parity probe. */
 int psg_opt_probe_pairs(psg_optimizer* opt, float* m, float* n, unsigned char* ok, float* I3, float* rend3);
+/* Diagnostic: interpolateImage(row, col) and computeImageGradient(row, col, img, 0 | 1) (Auxilary.h:41-123) of keyframe `frame`
+ * at n positions inside the image, evaluated by the device functions the sweeps use: rgb3, g0 (along columns), g1 (along
+ * rows), 3 floats each per position.  In the bottom-right corner cell the reference reads one element past the image; this
+ * path uses the centre texel there. */
+int psg_debug_image_probe(psg_optimizer* opt, int frame, int n, const float* rows, const float* cols, float* rgb3, float* g0,
+                          float* g1);
 
 /* optimizeAlbedoAll / optimizeLightAll / optimizeDistAll / optimizePosesAll
  * (PsOptimizer.cpp:85-234, LedOptimizer.cpp:134-275).  flags: PSG_REG_* bits select the regularisers
@@ -368,6 +382,11 @@ typedef struct {
 /* Diagnostic: microseconds the calling thread spent inside psg_opt_iteration since the last reset, split into
  * us[0] queuing kernels, us[1] waiting for the device's results, us[2] host solves (light / pose CG, pose update) and bookkeeping. */
 int psg_debug_host_times(double us[3], long long* iterations, int reset);
+/* Diagnostic: CUDA events on the optimizer's own stream (events of another library see only their own stream).  begin
+ * records an event; end records a second one, waits for it and returns the device time between the two in milliseconds:
+ * the device-side duration of whatever was called in between (idle gaps while the host works included). */
+int psg_debug_timer_begin(psg_optimizer* opt);
+int psg_debug_timer_end(psg_optimizer* opt, float* ms);
 /* Diagnostic, host only: the Jacobi-preconditioned CG the light and pose blocks are solved with (Eigen::ConjugateGradient<
  * SparseMatrix<float>, Lower, DiagonalPreconditioner>, PsOptimizer.cpp:184-191,217-227) on nblocks dense bs x bs blocks (row
  * major, lower triangle read). */

@@ -397,6 +397,15 @@ static void image_gradient(const or_opt* o, int f, float rowf, float colf, int d
     else for (int c = 0; c < 3; ++c) out[c] = v0[2 - c];
 }
 
+/* test probe: interpolateImage + computeImageGradient of keyframe f at n given (row, col) positions inside the image */
+void or_opt_image_probe(const or_opt* o, int f, int n, const float* rows, const float* cols, float* rgb3, float* g0, float* g1) {
+    for (int i = 0; i < n; ++i) {
+        if (rgb3) interp_image(o, f, rows[i], cols[i], rgb3 + 3 * i);
+        image_gradient(o, f, rows[i], cols[i], 0, g0 + 3 * i);
+        image_gradient(o, f, rows[i], cols[i], 1, g1 + 3 * i);
+    }
+}
+
 /* Optimizer::getIntensity (OptimizerAux.cpp:207-231) */
 static int get_intensity(const or_opt* o, const voxel* x, int f, const float* R, const float* t, float* rgb,
                          float* m_out, float* n_out) {
@@ -1188,15 +1197,18 @@ int or_opt_block(or_opt* o, int which, int apply, float damping, int albedo_reg,
                 int cols[4]; float vals[4]; int m = 0;
                 cols[m] = (c == 2) ? 3 * s + 1 : 3 * s + c; vals[m++] = Jr[0][c];
                 for (int k = 0; k < 3; ++k) if (ncol[k] >= 0) { cols[m] = 3 * ncol[k] + c; vals[m++] = Jr[k + 1][c]; }
+                /* H += reg * Jr^T * Jr parses as (reg * Jr^T) * Jr (PsOptimizer.cpp:99; the distance block writes reg * (J^T J)):
+                 * the scaled transpose is evaluated first, so every term is (reg * J(k,i)) * J(k,j) */
                 for (int i = 0; i < m; ++i) {
-                    for (int k = 0; k < m; ++k) *ra_at(M, cols[i], cols[k]) += vals[i] * vals[k];
-                    rs2_add(&bb, cols[i], o->reg_rho * vals[i], gnorm[c]);
+                    const float sv = o->reg_rho * vals[i];
+                    for (int k = 0; k < m; ++k) *ra_at(M, cols[i], cols[k]) += sv * vals[k];
+                    rs2_add(&bb, cols[i], sv, gnorm[c]);
                 }
             }
         }
         for (int i = 0; i < n; ++i)
             for (int k = 0; k < M->cnt[i]; ++k)
-                *ra_at(H, i, M->col[(size_t)i * M->cap + k]) += o->reg_rho * M->val[(size_t)i * M->cap + k];
+                *ra_at(H, i, M->col[(size_t)i * M->cap + k]) += M->val[(size_t)i * M->cap + k];
         rs2_finish(&bb, b);
         ra_free(M);
     }

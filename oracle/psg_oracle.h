@@ -71,6 +71,8 @@ float or_opt_albedo_reg_energy(or_opt*, double* E64);               /* Optimizer
 void or_opt_probe_pairs(or_opt*, float* m, float* n, unsigned char* ok, float* I3, float* rend3);
 void or_opt_residual(or_opt*, float* r3 /* S x F x 3 */, float* w3);
 void or_opt_dist_grad(or_opt*, float* out6 /* S x 6: grad, pos */);
+/* interpolateImage + computeImageGradient (Auxilary.h:41-123) of keyframe f at n (row, col) positions; rgb3 may be NULL */
+void or_opt_image_probe(const or_opt*, int f, int n, const float* rows, const float* cols, float* rgb3, float* g0, float* g1);
 
 /* One block step (PsOptimizer.cpp:85-234 / LedOptimizer.cpp:134-275).  Returns system size n.
  * Afterwards: or_opt_block_result() gives b, delta, CG verdict; or_opt_block_H() the matrix as COO triplets

@@ -264,6 +264,15 @@ class OrOptimizer:
         lib().or_opt_residual(self.h, r, w)
         return r, w
 
+    def image_probe(self, frame, rows, cols):
+        rows = np.ascontiguousarray(rows, np.float32); cols = np.ascontiguousarray(cols, np.float32)
+        n = rows.size
+        rgb = np.zeros((n, 3), np.float32); g0 = np.zeros((n, 3), np.float32); g1 = np.zeros((n, 3), np.float32)
+        L = lib()
+        L.or_opt_image_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p]
+        L.or_opt_image_probe(self.h, int(frame), n, rows, cols, rgb.reshape(-1), g0.reshape(-1), g1.reshape(-1))
+        return rgb, g0, g1
+
     def dist_grad(self):
         g = np.zeros((self.S, 6), np.float32)
         lib().or_opt_dist_grad(self.h, g)

@@ -53,6 +53,7 @@ def lib():
         L.ref_opt_destroy.argtypes = [C.c_void_p]
         L.ref_opt_set_keyframes.argtypes = [C.c_void_p, C.c_int, i32p, f32p, f32p, C.c_int, C.c_int]
         L.ref_opt_init.argtypes = [C.c_void_p]
+        L.ref_opt_set_keytimestamps.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p)]
         L.ref_opt_num_surface.argtypes = [C.c_void_p]
         L.ref_opt_surface.argtypes = [C.c_void_p, i32p]
         L.ref_opt_num_frames.argtypes = [C.c_void_p]
@@ -232,6 +233,10 @@ class RefOptimizer:
                                     np.ascontiguousarray(poses, np.float32).reshape(-1),
                                     np.ascontiguousarray(images, np.float32).reshape(-1), H, W)
 
+    def set_keytimestamps(self, stamps):
+        arr = (C.c_char_p * len(stamps))(*[str(x).encode() for x in stamps])
+        lib().ref_opt_set_keytimestamps(self.h, len(stamps), arr)
+
     def init(self):
         lib().ref_opt_init(self.h)
 
@@ -315,6 +320,15 @@ class RefOptimizer:
         # -> (S, F, 3)
         return (r.reshape(self.F, self.S, 3).transpose(1, 0, 2).copy(),
                 w.reshape(self.F, self.S, 3).transpose(1, 0, 2).copy())
+
+    def image_probe(self, frame, rows, cols):
+        rows = np.ascontiguousarray(rows, np.float32); cols = np.ascontiguousarray(cols, np.float32)
+        n = rows.size
+        rgb = np.zeros((n, 3), np.float32); g0 = np.zeros((n, 3), np.float32); g1 = np.zeros((n, 3), np.float32)
+        L = lib()
+        L.ref_opt_image_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p]
+        L.ref_opt_image_probe(self.h, int(frame), n, rows, cols, rgb.reshape(-1), g0.reshape(-1), g1.reshape(-1))
+        return rgb, g0, g1
 
     def dist_grad(self):
         g = np.zeros((self.S, 6), np.float32)

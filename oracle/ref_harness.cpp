@@ -55,6 +55,7 @@
 #undef class
 #undef private
 #undef protected
+#include "ps_optimizer/Auxilary.h"   // interpolateImage, computeImageGradient (static free functions)
 
 namespace {
 
@@ -252,6 +253,23 @@ void ref_opt_set_keyframes(void* h, int F, const int* frame_idx, const float* po
     o->opt->setKeyframes(kf);
     o->opt->setKeytimestamps(stamps);
     o->opt->setPoses(poses);
+}
+// main_ps.cpp:325 with caller-chosen strings (ref_opt_set_keyframes installs the frame ordinals)
+void ref_opt_set_keytimestamps(void* h, int F, const char* const* stamps) {
+    std::vector<std::string> st(stamps, stamps + F);
+    static_cast<RefOpt*>(h)->opt->setKeytimestamps(st);
+}
+// Auxilary.h:41-123 on keyframe f at n (row, col) positions: interpolateImage(row, col) and computeImageGradient(row, col, img, 0 | 1),
+// the way getIntensity / poseJacobian / distJacobian call them.  The corner cell (last row AND last column) reads past the image in the
+// reference and must not be probed.
+void ref_opt_image_probe(void* h, int f, int n, const float* rows, const float* cols, float* rgb3, float* g0, float* g1) {
+    RefOpt* o = static_cast<RefOpt*>(h);
+    const cv::Mat& img = *o->images[f];
+    for (int i = 0; i < n; ++i) {
+        if (rgb3) { const Vec3f c = interpolateImage(rows[i], cols[i], img); rgb3[3 * i] = c[0]; rgb3[3 * i + 1] = c[1]; rgb3[3 * i + 2] = c[2]; }
+        const Vec3f a = computeImageGradient(rows[i], cols[i], img, 0), b = computeImageGradient(rows[i], cols[i], img, 1);
+        for (int c = 0; c < 3; ++c) { g0[3 * i + c] = a[c]; g1[3 * i + c] = b[c]; }
+    }
 }
 void ref_opt_init(void* h) { Quiet q; static_cast<RefOpt*>(h)->opt->init(); }
 

@@ -94,6 +94,7 @@ def lib():
         L.psg_opt_create.argtypes = [C.POINTER(vp), vp, C.c_float, f32p, C.POINTER(Settings)]
         L.psg_opt_destroy.argtypes = [vp]
         L.psg_opt_set_keyframes.argtypes = [vp, C.c_int, i32p, f32p, vp, C.c_int, C.c_int]
+        L.psg_opt_set_keytimestamps.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p)]
         L.psg_opt_init.argtypes = [vp]
         L.psg_opt_num_surface.argtypes = [vp, C.POINTER(C.c_int)]
         L.psg_opt_get_surface.argtypes = [vp, vp, vp]
@@ -145,6 +146,8 @@ def lib():
         L.psg_opt_last_system.argtypes = [vp, vp, vp, vp]
         L.psg_opt_last_vectors.argtypes = [vp, vp, vp]
         L.psg_opt_upsample.argtypes = [vp]
+        L.psg_debug_timer_begin.argtypes = [vp]
+        L.psg_debug_timer_end.argtypes = [vp, C.POINTER(C.c_float)]
         L.psg_opt_alternating_optimize.argtypes = [vp, C.POINTER(LoopConfig), C.c_char_p, C.POINTER(LoopResult)]
         L.psg_comm_unique_id.argtypes = [C.c_char_p]
         L.psg_opt_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
@@ -486,6 +489,11 @@ class Optimizer:
                                               np.ascontiguousarray(poses, np.float32).reshape(-1), img.ctypes.data, H, W))
         self._pending_images = img
 
+    # setKeytimestamps (main_ps.cpp:325): the strings savePoses prints in front of every pose
+    def set_keytimestamps(self, stamps):
+        arr = (C.c_char_p * len(stamps))(*[str(s).encode() for s in stamps])
+        _check(lib().psg_opt_set_keytimestamps(self.h, len(stamps), arr))
+
     def init(self):
         _check(lib().psg_opt_init(self.h))
         self._pending_images = None
@@ -631,6 +639,16 @@ class Optimizer:
         _check(lib().psg_opt_probe_pairs(self.h, m, n, _ptr(ok), I, rend))
         return m, n, ok, I, rend
 
+    def image_probe(self, frame, rows, cols):
+        """(rgb, g0, g1) of interpolateImage / computeImageGradient at the given positions of keyframe `frame` (psg_debug_image_probe)."""
+        rows = np.ascontiguousarray(rows, np.float32); cols = np.ascontiguousarray(cols, np.float32)
+        n = rows.size
+        rgb = np.zeros((n, 3), np.float32); g0 = np.zeros((n, 3), np.float32); g1 = np.zeros((n, 3), np.float32)
+        L = lib()
+        L.psg_debug_image_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, f32p]
+        _check(L.psg_debug_image_probe(self.h, int(frame), n, rows, cols, rgb.reshape(-1), g0.reshape(-1), g1.reshape(-1)))
+        return rgb, g0, g1
+
     def step(self, which, damping=1.0, albedo_reg=False, normal_reg=False, laplacian_reg=False):
         flags = (REG_ALBEDO if albedo_reg else 0) | (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0)
         info = StepInfo()
@@ -686,6 +704,16 @@ class Optimizer:
 
     def upsample(self):
         _check(lib().psg_opt_upsample(self.h))
+
+    def timer_begin(self):
+        """CUDA event on the optimizer's stream (psg_debug_timer_begin)."""
+        _check(lib().psg_debug_timer_begin(self.h))
+
+    def timer_end(self) -> float:
+        """Second event, wait, device milliseconds since timer_begin."""
+        ms = C.c_float()
+        _check(lib().psg_debug_timer_end(self.h, C.byref(ms)))
+        return ms.value
 
     def alternatingOptimize(self, light=True, albedo=True, distance=True, pose=True, max_it=100, conv_threshold=1e-4,
                             damping=1.0, upsample=False, save_path=None, verbose=False):

@@ -355,6 +355,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     psg_opt_comm_destroy(o);
     if (o->upload_stream) { cudaStreamSynchronize(o->upload_stream); cudaStreamDestroy(o->upload_stream); }
     if (o->upload_done) cudaEventDestroy(o->upload_done);
+    if (o->timer0) { cudaEventDestroy(o->timer0); cudaEventDestroy(o->timer1); }
     o->upload_staging.release();
     o->images.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
@@ -374,6 +375,7 @@ int psg_opt_set_keyframes(psg_optimizer* o, int F, const int* frame_idx, const f
     if (F > kMaxFrames) { set_error("psg_opt_set_keyframes: %d keyframes given, at most %d supported", F, kMaxFrames); return PSG_ERR_INVALID; }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (F != o->F) o->key_stamps.clear();
     o->F = F; o->H = H; o->W = W;
     o->frame_idx.assign(frame_idx, frame_idx + F);
     o->poses.assign(poses16, poses16 + 16 * (size_t)F);
@@ -420,6 +422,7 @@ int psg_opt_set_keyframes_u8(psg_optimizer* o, int F, const int* frame_idx, cons
     if (F > kMaxFrames) { set_error("psg_opt_set_keyframes_u8: %d keyframes given, at most %d supported", F, kMaxFrames); return PSG_ERR_INVALID; }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (F != o->F) o->key_stamps.clear();
     o->F = F; o->H = H; o->W = W;
     o->frame_idx.assign(frame_idx, frame_idx + F);
     o->poses.assign(poses16, poses16 + 16 * (size_t)F);
@@ -449,6 +452,15 @@ int psg_opt_set_keyframes_u8(psg_optimizer* o, int F, const int* frame_idx, cons
     o->inited = false;
     return PSG_OK;
     PSG_CATCH
+}
+
+int psg_opt_set_keytimestamps(psg_optimizer* o, int F, const char* const* stamps) {
+    if (!o || F < 0 || (F > 0 && !stamps)) { set_error("psg_opt_set_keytimestamps: null or empty argument"); return PSG_ERR_INVALID; }
+    if (F != o->F) { set_error("psg_opt_set_keytimestamps: %d stamps for %d keyframes", F, o->F); return PSG_ERR_INVALID; }
+    for (int i = 0; i < F; ++i)
+        if (!stamps[i]) { set_error("psg_opt_set_keytimestamps: stamp %d is null", i); return PSG_ERR_INVALID; }
+    o->key_stamps.assign(stamps, stamps + F);
+    return PSG_OK;
 }
 
 int psg_opt_init(psg_optimizer* o) {
@@ -490,6 +502,7 @@ int psg_opt_init(psg_optimizer* o) {
 
 int psg_opt_num_surface(const psg_optimizer* o, int* S) {
     PSG_NEED_INIT(o)
+    if (!S) { set_error("psg_opt_num_surface: null argument"); return PSG_ERR_INVALID; }
     *S = o->S;
     return PSG_OK;
 }
@@ -527,11 +540,13 @@ int psg_opt_light_len(const psg_optimizer* o, int* n) {
 }
 int psg_opt_get_light(psg_optimizer* o, float* light) {
     PSG_NEED_INIT(o)
+    if (!light) { set_error("psg_opt_get_light: null argument"); return PSG_ERR_INVALID; }
     memcpy(light, o->light.data(), o->light.size() * sizeof(float));
     return PSG_OK;
 }
 int psg_opt_set_light(psg_optimizer* o, const float* light) {
     PSG_NEED_INIT(o)
+    if (!light) { set_error("psg_opt_set_light: null argument"); return PSG_ERR_INVALID; }
     memcpy(o->light.data(), light, o->light.size() * sizeof(float));
     o->frames_dirty = true;
     return PSG_OK;
@@ -636,6 +651,31 @@ static int probe_common(psg_optimizer* o, float* m, float* n, unsigned char* ok,
     if (r3) copy_sync(r3, dres, SF * 12, cudaMemcpyDeviceToHost, o->stream);
     if (w3) copy_sync(w3, dw, SF * 12, cudaMemcpyDeviceToHost, o->stream);
     buf.release(); okb.release();
+    return PSG_OK;
+    PSG_CATCH
+}
+
+int psg_debug_image_probe(psg_optimizer* o, int frame, int n, const float* rows, const float* cols, float* rgb3, float* g0, float* g1) {
+    PSG_NEED_INIT(o)
+    if (frame < 0 || frame >= o->F || n < 0 || !rows || !cols || !rgb3 || !g0 || !g1) { set_error("psg_debug_image_probe: bad argument"); return PSG_ERR_INVALID; }
+    for (int i = 0; i < n; ++i)
+        if (!(rows[i] >= 0.f && rows[i] < (float)o->H && cols[i] >= 0.f && cols[i] < (float)o->W)) {
+            set_error("psg_debug_image_probe: position %d (%g, %g) is outside the %d x %d image", i, rows[i], cols[i], o->H, o->W);
+            return PSG_ERR_INVALID;
+        }
+    if (n == 0) return PSG_OK;
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    DevBuf<float> buf;
+    buf.alloc((size_t)n * 11);
+    float* d = buf.p;
+    PSG_CUDA(cudaMemcpyAsync(d, rows, (size_t)n * 4, cudaMemcpyHostToDevice, o->stream));
+    PSG_CUDA(cudaMemcpyAsync(d + n, cols, (size_t)n * 4, cudaMemcpyHostToDevice, o->stream));
+    image_probe(o, frame, n, d, d + n, d + 2 * (size_t)n, d + 5 * (size_t)n, d + 8 * (size_t)n);
+    copy_sync(rgb3, d + 2 * (size_t)n, (size_t)n * 12, cudaMemcpyDeviceToHost, o->stream);
+    copy_sync(g0, d + 5 * (size_t)n, (size_t)n * 12, cudaMemcpyDeviceToHost, o->stream);
+    copy_sync(g1, d + 8 * (size_t)n, (size_t)n * 12, cudaMemcpyDeviceToHost, o->stream);
+    buf.release();
     return PSG_OK;
     PSG_CATCH
 }
@@ -875,6 +915,27 @@ int psg_debug_host_times(double us[3], long long* iterations, int reset) {
     if (iterations) *iterations = g_host_iterations;
     if (reset) { g_host_us[0] = g_host_us[1] = g_host_us[2] = 0.0; g_host_iterations = 0; }
     return PSG_OK;
+}
+
+int psg_debug_timer_begin(psg_optimizer* o) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (!o->timer0) { PSG_CUDA(cudaEventCreate(&o->timer0)); PSG_CUDA(cudaEventCreate(&o->timer1)); }
+    PSG_CUDA(cudaEventRecord(o->timer0, o->stream));
+    return PSG_OK;
+    PSG_CATCH
+}
+int psg_debug_timer_end(psg_optimizer* o, float* ms) {
+    if (!o || !ms) { set_error("null argument"); return PSG_ERR_INVALID; }
+    if (!o->timer0) { set_error("psg_debug_timer_end without psg_debug_timer_begin"); return PSG_ERR_STATE; }
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    PSG_CUDA(cudaEventRecord(o->timer1, o->stream));
+    PSG_CUDA(cudaEventSynchronize(o->timer1));
+    PSG_CUDA(cudaEventElapsedTime(ms, o->timer0, o->timer1));
+    return PSG_OK;
+    PSG_CATCH
 }
 
 int psg_opt_last_system(psg_optimizer* o, double* H, double* b, double* delta) {

@@ -67,7 +67,8 @@ void quat_from_matrix(const float* P /* 4x4 row-major */, float q[4] /* x y z w 
 }
 
 // Optimizer::savePoses (OptimizerAux.cpp:580-599)
-bool save_poses(psg_optimizer* o, const std::string& path, const std::vector<std::string>& stamps) {
+bool save_poses(psg_optimizer* o, const std::string& path) {
+    const std::vector<std::string>& stamps = o->key_stamps;
     std::ofstream f(path.c_str());
     if (!f.is_open()) return false;
     for (int i = 0; i < o->F; ++i) {
@@ -280,7 +281,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
         }
         ++iter;
         if (iter % 3 == 0 && files) {
-            save_poses(o, out + "after_poses_opt_" + std::to_string(iter) + ".txt", {});
+            save_poses(o, out + "after_poses_opt_" + std::to_string(iter) + ".txt");
             save_pointcloud(o, out + "after_iter_" + std::to_string(iter) + "_pointcloud.ply");
             save_mesh(o, out + "after_iter_" + std::to_string(iter) + "_mesh.ply");
         }

@@ -92,6 +92,7 @@ struct psg_optimizer {
     float K[9] = {0};
     int F = 0, H = 0, W = 0;
     std::vector<int> frame_idx;
+    std::vector<std::string> key_stamps;     // Optimizer::key_stamps_ (first column of savePoses); empty = print frame_idx
     std::vector<float> poses;                // F x 16 (host copy, authoritative)
     std::vector<float> light;                // F x nb or 3
     psg::DevBuf<float4> images;              // F x H x W texels (b, g, r, 0)
@@ -141,6 +142,7 @@ struct psg_optimizer {
     double last_energy_sum = 0.0;            // sum of robust losses seen by the last sweep (state before its update)
     long long last_active = 0;
     cudaStream_t stream = nullptr;
+    cudaEvent_t timer0 = nullptr, timer1 = nullptr;   // psg_debug_timer_begin / _end
 };
 
 namespace psg {
@@ -150,6 +152,7 @@ namespace psg {
 constexpr int kRedDoubles = kMaxFrames * 64;
 constexpr int kRedCopies = 8;     // private copies of the per-keyframe sums on large grids (same-address fp64 atomics serialise in L2)
 constexpr int kMailDoubles = 64;
+constexpr int kPcgMaxBlocks = 1024;   // most blocks a cooperative distance-solve launch uses (4 per SM, <= 256 SMs)
 constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
 constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
 constexpr int kSlotCount = 7;    // [0] unsigned long long: accepted distance updates, [1] arrival counter of the PCG's grid barrier
@@ -185,6 +188,7 @@ void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, lo
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
 void sweep_init_albedo(psg_optimizer* o);
 void sweep_led_light_init(psg_optimizer* o, double sums[6]);
+void image_probe(psg_optimizer* o, int f, int n, const float* rows_dev, const float* cols_dev, float* rgb3, float* g0, float* g1);
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3);
 // queue-only pieces (no host wait) and the one round trip that collects their results
 double* mail_dev(psg_optimizer* o);

@@ -364,6 +364,21 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
         PSG_CUDA(cudaStreamSynchronize(o->stream));
         o->vis_pairs = (long long)h;
     }
+    // everything the blocks of an outer iteration use is sized here, once per work list, so that the iteration path itself
+    // never allocates (DevBuf::alloc is a no-op once sized; growing it frees and reallocates, which synchronises the device)
+    {
+        const size_t Sr = (size_t)(o->S > 0 ? o->S : 1);
+        o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
+        o->vecs.alloc(Sr * 25 + 8);
+        o->pcg_pbuf.alloc(2 * Sr);
+        o->pcg_partials.alloc((size_t)4 * kPcgMaxBlocks + 1);
+        const size_t grid = (Sr + 31) / 32 + 1, ngroups = grid / 128 + 2;
+        o->sweep_partials.alloc((grid + ngroups) * 8);
+        if (o->sweep_counter.n < ngroups + 1) {
+            o->sweep_counter.alloc(ngroups + 1);
+            PSG_CUDA(cudaMemsetAsync(o->sweep_counter.p, 0, (ngroups + 1) * sizeof(unsigned), o->stream));
+        }
+    }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
     update_shard_policy(o);
 }

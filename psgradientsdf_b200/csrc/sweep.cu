@@ -1042,6 +1042,26 @@ void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
     *En = r[0]; *El = r[1]; *Er = r[2];
 }
 
+// ---- diagnostic: interpolateImage + computeImageGradient at caller-chosen positions (the sweeps' own device functions)
+__global__ void __launch_bounds__(128) k_image_probe(SweepArgs A, int f, int n, const float* __restrict__ rows, const float* __restrict__ cols,
+                                                    float* __restrict__ rgb3, float* __restrict__ g0o, float* __restrict__ g1o) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Footprint fp;
+    float rgb[3], g0[3], g1[3];
+    sample_image(A, f, rows[i], cols[i], fp, rgb);
+    image_gradient(A, f, rows[i], cols[i], fp, g0, g1);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { rgb3[3 * i + c] = rgb[c]; g0o[3 * i + c] = g0[c]; g1o[3 * i + c] = g1[c]; }
+}
+
+void image_probe(psg_optimizer* o, int f, int n, const float* rows_dev, const float* cols_dev, float* rgb3, float* g0, float* g1) {
+    SweepArgs A = base_args(o);
+    k_image_probe<<<(n + 127) / 128, 128, 0, o->stream>>>(A, f, n, rows_dev, cols_dev, rgb3, g0, g1);
+    count_launch();
+    PSG_LAUNCH_CHECK();
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // Energy evaluation that performs no device allocation.
 //

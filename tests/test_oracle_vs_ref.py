@@ -134,3 +134,73 @@ def test_demo_data_blocks_bit_identical(tmp_path):
     for st in r["steps"]:
         assert st["rhs_bit_equal"] and st["solution_bit_equal"] and st["volume_bit_equal"] and st["light_bit_equal"], st
         assert st["poses_bit_equal"] and st["energy_equal"] and st["cg_iterations"][0] == st["cg_iterations"][1], st
+
+
+def border_positions(H, W, seed=3):
+    """(row, col) positions that reach every branch of computeImageGradient (Auxilary.h:64-123): interior cells, the last row
+    (x + 1 >= rows), the last column (y + 1 >= cols), integer and fractional coordinates.  The corner cell (last row AND last
+    column) is left out: the reference reads past the image there."""
+    rng = np.random.default_rng(seed)
+    rows = [rng.uniform(0, H - 1, 64), np.full(32, H - 1) + rng.uniform(0, 0.999, 32), rng.uniform(0, H - 1, 32),
+            np.array([0.0, 1.0, H - 2.0, H - 1.0, 0.5]), np.array([H - 1.0, 3.25])]
+    cols = [rng.uniform(0, W - 1, 64), rng.uniform(0, W - 1, 32), np.full(32, W - 1) + rng.uniform(0, 0.999, 32),
+            np.array([0.0, W - 2.0, 1.0, 0.0, 0.25]), np.array([5.0, W - 1.0])]
+    return np.concatenate(rows).astype(np.float32), np.concatenate(cols).astype(np.float32)
+
+
+def test_image_gradient_borders_vs_reference():
+    """interpolateImage / computeImageGradient of the restatement against the reference's own functions, border branches included."""
+    _need_ref()
+    model, G = "SH1", 24
+    sc = scene(model)
+    rv, ro = make_ref(model, G, sc)
+    ov, oo = make_oracle(model, G, sc)
+    handoff(ro, sc); handoff(oo, sc)
+    H, W = sc.color.shape[1:3]
+    rows, cols = border_positions(H, W)
+    for f in (0, 3):
+        a, b = ro.image_probe(f, rows, cols), oo.image_probe(f, rows, cols)
+        for nm, x, y in zip(["interpolated colour", "gradient along columns", "gradient along rows"], a, b):
+            assert_bit_equal(x, y, f"{nm}, keyframe {f}")
+    assert np.abs(a[1]).max() > 0 and np.abs(a[2]).max() > 0
+
+
+@pytest.mark.parametrize("model", ["SH1", "LED"])
+def test_albedo_regulariser_vs_reference(model):
+    """reg albedo != 0: albedoRegJacobian (Optimizer.cpp:221-245, 593-647, with its column index for the blue channel) inside
+    optimizeAlbedoAll -- restatement against the reference's own block, bit for bit, and the energy term."""
+    _need_ref()
+    from oracle import pyoracle, pyref
+    from psgradientsdf_b200 import synth
+    G = 24
+    sc = scene(model)
+    vs, T = synth.grid_for_scene(G)
+    rv = pyref.RefVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5)
+    ro = pyref.RefOptimizer(rv, model, vs, sc.K, "/tmp/", reg_rho=0.05, reg_n=10.0)
+    ov = pyoracle.OrVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5, 64)
+    oo = pyoracle.OrOptimizer(ov, model, vs, sc.K, reg_rho=0.05, reg_n=10.0)
+    for f in range(sc.color.shape[0]):
+        R, t = se3(sc.poses_gt[f])
+        rv.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
+        ov.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, R, t, f > 0)
+    handoff(ro, sc); handoff(oo, sc)
+    ro.init_albedo(); oo.init_albedo()
+    assert ro.albedo_reg_energy() == oo.albedo_reg_energy()
+    for it in range(2):
+        r1 = ro.block("albedo", apply=True, damping=1.0, albedo_reg=True)
+        r2 = oo.block("albedo", apply=True, damping=1.0, albedo_reg=True)
+        assert r1["info"] == r2["info"] and r1["iters"] == r2["iters"] and r1["iters"] > 1, (r1["info"], r2["info"], r1["iters"], r2["iters"])
+        assert_bit_equal(r1["b"], r2["b"], "albedo rhs with the regulariser")
+        assert abs(r1["H"] - r2["H"]).max() == 0
+        assert_bit_equal(r1["delta"], r2["delta"], "albedo solution with the regulariser")
+        assert_bit_equal(rv.download(), ov.download(), "volume after the regularised albedo block")
+        assert ro.albedo_reg_energy() == oo.albedo_reg_energy()
+    # and the reference's own optimizeAlbedoAll leaves the same state as the re-played block
+    rv2 = pyref.RefVolume([G, G, G], vs, [0, 0, 0], T, 0.5, 3.5)
+    ro2 = pyref.RefOptimizer(rv2, model, vs, sc.K, "/tmp/", reg_rho=0.05, reg_n=10.0)
+    for f in range(sc.color.shape[0]):
+        rv2.integrate(sc.color[f], sc.depth[f], sc.nx[f], sc.ny[f], sc.nz[f], sc.n_sq_inv, sc.K, sc.poses_gt[f], f > 0)
+    handoff(ro2, sc); ro2.init_albedo()
+    for it in range(2):
+        ro2.block_reference("albedo", 1.0, True, False, False)
+    assert_bit_equal(rv2.download(), ov.download(), "optimizeAlbedoAll(albedo_reg = true) vs the restatement")
