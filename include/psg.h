@@ -246,7 +246,7 @@ int psg_opt_save_pointcloud(psg_optimizer* opt, const char* filename);
 typedef struct {
     int light, albedo, distance, pose;   /* alternatingOptimize(bool light, bool albedo, bool distance, bool pose) */
     float damping;
-    int reg_flags;                       /* PSG_REG_NORMAL | PSG_REG_LAPLACIAN for the distance block */
+    int reg_flags;                       /* PSG_REG_NORMAL | PSG_REG_LAPLACIAN for the distance block, PSG_REG_ALBEDO for the albedo block */
     int closing_energy;                  /* evaluate the energy even if no block is enabled */
 } psg_iteration_config;
 typedef struct {
@@ -256,6 +256,7 @@ typedef struct {
     double reg_normal_after_dist, reg_laplacian_after_dist;   /* getNormalEnergy / getLaplacianEnergy after the distance block */
     double energy_end;                   /* = energy_after of the last executed block */
     long long n_active_end;
+    double reg_albedo_after_albedo;      /* getAlbedoRegEnergy after the albedo block (reg_flags has PSG_REG_ALBEDO) */
 } psg_iteration_info;
 int psg_opt_iteration(psg_optimizer* opt, const psg_iteration_config* cfg, psg_iteration_info* info /* may be NULL */);
 

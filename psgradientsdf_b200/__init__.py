@@ -47,7 +47,7 @@ class IterationConfig(C.Structure):
 class IterationInfo(C.Structure):
     _fields_ = [("ran", C.c_int * 4), ("block", StepInfo * 4), ("energy_after", C.c_double * 4),
                 ("reg_normal_after_dist", C.c_double), ("reg_laplacian_after_dist", C.c_double), ("energy_end", C.c_double),
-                ("n_active_end", C.c_longlong)]
+                ("n_active_end", C.c_longlong), ("reg_albedo_after_albedo", C.c_double)]
 
 
 class TrackerConfig(C.Structure):
@@ -657,15 +657,18 @@ class Optimizer:
                     applied=bool(info.applied), n_accepted=info.n_accepted, energy_before=info.energy_before,
                     n_active_before=info.n_active_before)
 
-    def iteration(self, light=True, albedo=True, distance=True, pose=True, damping=1.0, normal_reg=False, laplacian_reg=False):
+    def iteration(self, light=True, albedo=True, distance=True, pose=True, damping=1.0, normal_reg=False, laplacian_reg=False,
+                  albedo_reg=False):
         """One pass of alternatingOptimize's while-body (psg_opt_iteration): dict with per-block step records, the energy
         after each block, the regulariser energies after the distance block and the closing energy."""
         cfg = IterationConfig(int(light), int(albedo), int(distance), int(pose), float(damping),
-                              (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0), 0)
+                              (REG_NORMAL if normal_reg else 0) | (REG_LAPLACIAN if laplacian_reg else 0) |
+                              (REG_ALBEDO if albedo_reg else 0), 0)
         info = IterationInfo()
         _check(lib().psg_opt_iteration(self.h, C.byref(cfg), C.byref(info)))
         out = {"energy_end": info.energy_end, "n_active_end": info.n_active_end,
-               "reg_normal_after_dist": info.reg_normal_after_dist, "reg_laplacian_after_dist": info.reg_laplacian_after_dist}
+               "reg_normal_after_dist": info.reg_normal_after_dist, "reg_laplacian_after_dist": info.reg_laplacian_after_dist,
+               "reg_albedo_after_albedo": info.reg_albedo_after_albedo}
         for name, b in BLOCK.items():
             if info.ran[b]:
                 st = info.block[b]

@@ -361,6 +361,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);
+    o->areg.release();
     o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
     delete o;
     return PSG_OK;
@@ -701,7 +702,7 @@ struct HostClock {
     ~HostClock() { g_host_us[slot] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(); }
 };
 
-struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; };
+struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; bool albedo_reg = false; };
 
 // queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
 Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot, bool reg_energies_after = false,
@@ -709,7 +710,16 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
     Pending p; p.block = block; p.slot = slot; p.damping = damping;
     const bool led = o->set.model == PSG_MODEL_LED;
     o->last_block = block;
-    if (block == PSG_BLOCK_ALBEDO) {
+    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO)) {
+        // reg albedo != 0: the sweep hands over J^T W J / J^T W r, the regularised 3S x 3S system is solved by its own PCG;
+        // SH applies the update only on Success (PsOptimizer.cpp:118), LED unconditionally (LedOptimizer.cpp:195)
+        const size_t n = (size_t)3 * o->S;
+        o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
+        launch_albedo(o, damping, o->vecs.p, o->vecs.p + n, slot, /*regularised=*/true);
+        launch_albedo_reg_solve(o, damping, /*only_on_success=*/!led);
+        if (reg_energies_after) launch_reg_energies(o, kSlotReg);   // getAlbedoRegEnergy after the update
+        p.albedo_reg = true;
+    } else if (block == PSG_BLOCK_ALBEDO) {
         const size_t n = (size_t)3 * o->S;
         o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
         // rhs / delta per voxel are only kept for psg_opt_last_vectors (scattered 12-byte writes): the outer loop skips them
@@ -736,7 +746,13 @@ void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
     const int block = p.block;
     psg_step_info inf;
     memset(&inf, 0, sizeof(inf));
-    if (block == PSG_BLOCK_ALBEDO) {
+    if (block == PSG_BLOCK_ALBEDO && p.albedo_reg) {
+        int ok = 1, iters = 0; float err = 0.f; long long acc = 0;
+        read_albedo_reg_verdict(o, &ok, &iters, &err, &acc);
+        inf.n = 3 * o->S; inf.cg_success = ok; inf.cg_iterations = iters; inf.cg_error = err;
+        inf.applied = (led || ok) ? 1 : 0; inf.n_accepted = acc;
+        o->last_n = 3 * o->S;
+    } else if (block == PSG_BLOCK_ALBEDO) {
         const size_t n = (size_t)3 * o->S;
         inf.n = (int)n; inf.cg_success = 1; inf.cg_iterations = 0; inf.cg_error = 0.f; inf.applied = 1;
         inf.n_accepted = (long long)(mail_slot(o, p.slot)[5] + 0.5);
@@ -795,14 +811,15 @@ void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
 int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step_info* info) {
     PSG_NEED_INIT(o)
     if (block < 0 || block > 3) { set_error("psg_opt_step: unknown block %d", block); return PSG_ERR_INVALID; }
-    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO)) {
-        set_error("psg_opt_step: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
-                  "the reference's README asks for reg albedo = 0");
+    if (block == PSG_BLOCK_ALBEDO && (flags & PSG_REG_ALBEDO) && o->sharded) {
+        set_error("psg_opt_step: the albedo-gradient regulariser (reg albedo != 0) is not provided on a work list sharded over "
+                  "several GPUs; use psg_opt_set_shard_policy(opt, 2)");
         return PSG_ERR_UNSUPPORTED;
     }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(o->vol->device));
     const Pending p = queue_block(o, block, damping, flags, 0);
+    o->last_albedo_reg = p.albedo_reg;
     fetch_mail(o, p.nred);
     finish_block(o, p, info);
     return PSG_OK;
@@ -816,8 +833,9 @@ int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step
 int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_iteration_info* out) {
     PSG_NEED_INIT(o)
     if (!cfg) { set_error("psg_opt_iteration: null configuration"); return PSG_ERR_INVALID; }
-    if (cfg->reg_flags & PSG_REG_ALBEDO) {
-        set_error("psg_opt_iteration: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path");
+    if ((cfg->reg_flags & PSG_REG_ALBEDO) && cfg->albedo && o->sharded) {
+        set_error("psg_opt_iteration: the albedo-gradient regulariser (reg albedo != 0) is not provided on a work list sharded "
+                  "over several GPUs; use psg_opt_set_shard_policy(opt, 2)");
         return PSG_ERR_UNSUPPORTED;
     }
     PSG_TRY
@@ -847,6 +865,7 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
             const double* r = mail_slot(o, kSlotReg);
             R.reg_normal_after_dist = o->S > 0 ? r[0] / (double)o->S : 0.0;
             R.reg_laplacian_after_dist = o->S > 0 ? r[1] / (double)o->S : 0.0;
+            R.reg_albedo_after_albedo = o->S > 0 ? r[2] / (double)o->S : 0.0;
             reg_queued = false;
         }
         nq = 0; slot = 0;
@@ -854,8 +873,13 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
     for (int k = 0; k < 4; ++k) {
         const int block = order[k];
         if (!enabled[block]) continue;
-        const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) : 0;
-        const bool want_reg = block == PSG_BLOCK_DIST && (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN));
+        const bool areg = (cfg->reg_flags & PSG_REG_ALBEDO) != 0;
+        const int flags = block == PSG_BLOCK_DIST ? (cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN))
+                                                  : (block == PSG_BLOCK_ALBEDO ? (cfg->reg_flags & PSG_REG_ALBEDO) : 0);
+        // regulariser energies after the block that changes them (the albedo term does not depend on the distance, so a
+        // later distance block in the same flush recomputes the same value into the same slot)
+        const bool want_reg = (block == PSG_BLOCK_DIST && ((cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) || areg)) ||
+                              (block == PSG_BLOCK_ALBEDO && areg);
         { HostClock hc(0); queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg, /*keep_vectors=*/false); }
         const size_t nred = queued[nq].nred;
         ++nq; ++slot;
@@ -880,6 +904,7 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
             const double* r = mail_slot(o, kSlotReg);
             R.reg_normal_after_dist = o->S > 0 ? r[0] / (double)o->S : 0.0;
             R.reg_laplacian_after_dist = o->S > 0 ? r[1] / (double)o->S : 0.0;
+            R.reg_albedo_after_albedo = o->S > 0 ? r[2] / (double)o->S : 0.0;
         }
         o->last_energy_sum = sc[6];
         o->last_active = R.n_active_end;
@@ -953,8 +978,9 @@ int psg_opt_last_vectors(psg_optimizer* o, float* b, float* delta) {
     PSG_CUDA(cudaSetDevice(o->vol->device));
     const size_t S = (size_t)o->S;
     if (o->last_block == PSG_BLOCK_ALBEDO) {
-        if (b) copy_sync(b, o->vecs.p, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
-        if (delta) copy_sync(delta, o->vecs.p + 3 * S, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
+        const size_t off = o->last_albedo_reg ? 6 * S : 0;   // the regularised solve keeps its rhs / solution behind the sweep's
+        if (b) copy_sync(b, o->vecs.p + off, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
+        if (delta) copy_sync(delta, o->vecs.p + off + 3 * S, 3 * S * 4, cudaMemcpyDeviceToHost, o->stream);
     } else if (o->last_block == PSG_BLOCK_DIST) {
         if (b) copy_sync(b, o->vecs.p + 14 * S, S * 4, cudaMemcpyDeviceToHost, o->stream);
         if (delta) copy_sync(delta, o->vecs.p + 17 * S, S * 4, cudaMemcpyDeviceToHost, o->stream);

@@ -189,17 +189,12 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
     const int order_sh[4] = { PSG_BLOCK_ALBEDO, PSG_BLOCK_LIGHT, PSG_BLOCK_DIST, PSG_BLOCK_POSE };
     const int order_led[4] = { PSG_BLOCK_LIGHT, PSG_BLOCK_ALBEDO, PSG_BLOCK_DIST, PSG_BLOCK_POSE };
     const int* order = led ? order_led : order_sh;
-    if (albedo_reg && cfg->albedo) {
-        psg::set_error("psg_opt_alternating_optimize: the albedo-gradient regulariser (reg albedo != 0) is not provided on this path; "
-                       "the reference's README asks for reg albedo = 0");
-        return PSG_ERR_UNSUPPORTED;
-    }
     auto run_iteration = [&]() -> int {
         psg_iteration_config ic;
         memset(&ic, 0, sizeof(ic));
         ic.light = cfg->light; ic.albedo = cfg->albedo; ic.distance = cfg->distance; ic.pose = cfg->pose;
         ic.damping = damping;
-        ic.reg_flags = (normal_reg ? PSG_REG_NORMAL : 0) | (laplacian_reg ? PSG_REG_LAPLACIAN : 0);
+        ic.reg_flags = (normal_reg ? PSG_REG_NORMAL : 0) | (laplacian_reg ? PSG_REG_LAPLACIAN : 0) | (albedo_reg ? PSG_REG_ALBEDO : 0);
         psg_iteration_info info;
         const int st = psg_opt_iteration(o, &ic, &info);
         if (st != PSG_OK) return st;
@@ -211,6 +206,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
                 if (normal_reg) e.En = (float)info.reg_normal_after_dist;
                 if (laplacian_reg) e.El = (float)info.reg_laplacian_after_dist;
             }
+            if (block == PSG_BLOCK_ALBEDO && albedo_reg) e.Er = (float)info.reg_albedo_after_albedo;   // PsOptimizer.cpp:311
             if (echo) std::cout << "===> [" << R.iterations << "]: after " << labels[block] << " optimization: ";
             if (file.is_open()) file << "===> [" << R.iterations << "]: after " << labels[block] << " optimization: \n";
             E_total = total_energy(o, e, file, echo);

@@ -717,6 +717,242 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
     }
 }
 
+// ---- regularised albedo block (reg albedo != 0) ------------------------------------------------------------------------
+// {Ps,Led}Optimizer::optimizeAlbedoAll with albedo_reg (PsOptimizer.cpp:85-121, LedOptimizer.cpp:162-196):
+//   H = J^T W J + (reg * Jr^T) * Jr,  b = J^T W r + (reg * Jr^T) * r_r,  H.diagonal() += damping * H.diagonal(),
+//   Jacobi-preconditioned CG on the 3S x 3S system, Optimizer::updateAlbedo (OptimizerAux.cpp:120-150).
+// Jr (Optimizer::albedoRegJacobian, Optimizer.cpp:221-245, 593-647) has one row per surface voxel t and channel c with <= 4
+// entries: a0 = (grad rho_c . (-pos / vs)) / |grad rho_c| in the voxel's own column and a_k = grad rho_c[k] * pos[k] / vs / |grad
+// rho_c| in the column of its finite-difference neighbour along axis k (only if that neighbour is a surface voxel); the
+// residual is |grad rho_c| (Optimizer::computeAlbedoGrad, Optimizer.cpp:396-460).  The reference writes the BLUE row's own
+// entry into the GREEN column (3 * row + 1, Optimizer.cpp:618): reproduced, so the blue channel of a voxel is regularised
+// only through its neighbours' rows and the green unknown is coupled to the blue rows.
+// The matrix is never formed: u = Jr p per row (phase 1), y = D p + reg * Jr^T u gathered per unknown through the same
+// incidence lists the distance solve uses (phase 2).  One persistent cooperative launch, grid barriers between phases.
+struct AregArgs {
+    int S;
+    VolView vol;
+    const int* lin; const int* nbr_lin; const int* nbr_row; const int* inc; const unsigned char* pos;
+    const float* bd; const float* Hd;     // [3 s + c]: J^T W r and the diagonal of J^T W J from the albedo sweep
+    float* w;                             // 39 planes of S floats (layout below)
+    float* b_out; float* delta_out;       // [3 s + c] diagnostics (psg_opt_last_vectors), may alias bd / Hd
+    float reg, damping, vs_inv;
+    int max_iters, only_on_success;
+    double* partials;                     // [3][gridDim.x]
+    unsigned long long* barrier;
+    float* result;                        // iterations, residualNorm2, rhsNorm2, threshold
+    unsigned long long* accepted;
+};
+// planes: 0..11 coefficient a_k of channel c at 3 k + c | 12..14 rhs | 15..17 1 / damped diagonal | 18..20 damping * diagonal |
+//         21..23 x | 24..26 r | 27..29 p | 30..32 y = H p | 33..35 u = Jr p
+
+template <int BS>
+__global__ void __launch_bounds__(BS) k_albedo_reg_solve(AregArgs A) {
+    __shared__ double s_buf[2 * (BS / 32)];
+    const int S = A.S, nb = gridDim.x, T = nb * BS, gtid = blockIdx.x * BS + threadIdx.x;
+    double* P0 = A.partials; double* P1 = A.partials + nb; double* P2 = A.partials + 2 * nb;
+    unsigned long long bar_target = 0;
+    float* W = A.w;
+    auto pl = [&](int plane, int s) -> float* { return W + (size_t)plane * S + s; };
+
+    // ---- set-up A: albedo gradient, its row norms and the Jacobian coefficients of every row
+    for (int s = gtid; s < S; s += T) {
+        const int lin = A.lin[s];
+        const float rho[3] = { A.vol.r[lin], A.vol.g[lin], A.vol.b[lin] };
+        const unsigned char pb = A.pos[s];
+        float G[9], posf[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int nl = A.nbr_lin[a * S + s];
+            posf[a] = ((pb >> a) & 1) ? 1.f : -1.f;
+            const float nr = nl >= 0 ? A.vol.r[nl] : rho[0], ng = nl >= 0 ? A.vol.g[nl] : rho[1], nbb = nl >= 0 ? A.vol.b[nl] : rho[2];
+            G[a] = (posf[a] * (nr - rho[0])) * A.vs_inv; G[3 + a] = (posf[a] * (ng - rho[1])) * A.vs_inv; G[6 + a] = (posf[a] * (nbb - rho[2])) * A.vs_inv;
+        }
+        float rd[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) rd[a] = -A.vs_inv * posf[a];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float gn = norm3(G + 3 * c);
+            float a0 = dot3(G + 3 * c, rd);
+            float ak[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) ak[a] = G[3 * c + a] * (0.f + A.vs_inv * posf[a]);
+            if (gn != 0.f) { a0 /= gn; ak[0] /= gn; ak[1] /= gn; ak[2] /= gn; }
+            *pl(c, s) = a0; *pl(3 + c, s) = ak[0]; *pl(6 + c, s) = ak[1]; *pl(9 + c, s) = ak[2];
+            *pl(33 + c, s) = gn;   // residual of the row, parked in the u planes until set-up B has used it
+        }
+    }
+    grid_barrier(A.barrier, bar_target, nb);
+    // ---- set-up B: right-hand side, diagonal (preconditioner, damping), start vectors
+    double a0s = 0.0, a1s = 0.0;
+    for (int s = gtid; s < S; s += T) {
+        int tn[6];
+#pragma unroll
+        for (int h = 0; h < 6; ++h) tn[h] = __ldg(A.inc + h * S + s);
+        float rhs[3], diag[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { rhs[c] = A.bd[3 * (long long)s + c]; diag[c] = A.Hd[3 * (long long)s + c]; }
+        // own rows: red -> column 0, green -> column 1, blue -> column 1 (the reference's index)
+        {
+            const float ar = __ldcg(pl(0, s)), ag = __ldcg(pl(1, s)), ab = __ldcg(pl(2, s));
+            const float sr = A.reg * ar, sg = A.reg * ag, sb = A.reg * ab;
+            rhs[0] += sr * __ldcg(pl(33, s)); diag[0] += sr * ar;
+            rhs[1] += sg * __ldcg(pl(34, s)); diag[1] += sg * ag;
+            rhs[1] += sb * __ldcg(pl(35, s)); diag[1] += sb * ab;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = tn[h * 3 + a];
+                if (t < 0) continue;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float ak = __ldcg(pl(3 * (a + 1) + c, t));
+                    const float sk = A.reg * ak;
+                    rhs[c] += sk * __ldcg(pl(33 + c, t)); diag[c] += sk * ak;
+                }
+            }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float dd = (A.damping != 0.f) ? A.damping * diag[c] : 0.f;
+            const float full = diag[c] + dd;
+            const float invd = (full != 0.f) ? 1.f / full : 1.f;
+            const float pv = invd * rhs[c];
+            *pl(12 + c, s) = rhs[c]; *pl(15 + c, s) = invd; *pl(18 + c, s) = dd;
+            *pl(21 + c, s) = 0.f; *pl(24 + c, s) = rhs[c]; *pl(27 + c, s) = pv;
+            a0s += (double)rhs[c] * (double)rhs[c]; a1s += (double)rhs[c] * (double)pv;
+            if (A.b_out) A.b_out[3 * (long long)s + c] = rhs[c];
+        }
+    }
+    {
+        const double2 t = block_sum2<BS>(a0s, a1s, s_buf);
+        if (threadIdx.x == 0) { P0[blockIdx.x] = t.x; P1[blockIdx.x] = t.y; }
+    }
+    grid_barrier(A.barrier, bar_target, nb);
+    const double2 t01 = grid_total2_cg(P0, P1, nb, s_buf);
+    const float rhsNorm2 = (float)t01.x;
+    float absNew = (float)t01.y;
+    const float tol = 1.1920929e-07f;
+    float threshold = tol * tol * rhsNorm2;
+    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+    float residualNorm2 = rhsNorm2;
+    int it = 0;
+    if (rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+        while (it < A.max_iters) {
+            // ---- phase 1: u = Jr p, one value per row (voxel, channel)
+            for (int s = gtid; s < S; s += T) {
+                int col[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) col[a] = __ldg(A.nbr_row + a * S + s);
+                const float pg = __ldcg(pl(28, s));
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float u = __ldg(pl(c, s)) * (c == 2 ? pg : __ldcg(pl(27 + c, s)));
+#pragma unroll
+                    for (int a = 0; a < 3; ++a)
+                        if (col[a] >= 0) u += __ldg(pl(3 * (a + 1) + c, s)) * __ldcg(pl(27 + c, col[a]));
+                    *pl(33 + c, s) = u;
+                }
+            }
+            grid_barrier(A.barrier, bar_target, nb);
+            // ---- phase 2: y = D p + reg * Jr^T u + damping * diag * p ; p . y
+            double pAp = 0.0;
+            for (int s = gtid; s < S; s += T) {
+                int tn[6];
+#pragma unroll
+                for (int h = 0; h < 6; ++h) tn[h] = __ldg(A.inc + h * S + s);
+                float acc[3];
+                acc[0] = (A.reg * __ldg(pl(0, s))) * __ldcg(pl(33, s));
+                acc[1] = (A.reg * __ldg(pl(1, s))) * __ldcg(pl(34, s)) + (A.reg * __ldg(pl(2, s))) * __ldcg(pl(35, s));
+                acc[2] = 0.f;
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int t = tn[h * 3 + a];
+                        if (t < 0) continue;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) acc[c] += (A.reg * __ldg(pl(3 * (a + 1) + c, t))) * __ldcg(pl(33 + c, t));
+                    }
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float ps = __ldcg(pl(27 + c, s));
+                    const float y = A.Hd[3 * (long long)s + c] * ps + acc[c] + __ldg(pl(18 + c, s)) * ps;
+                    *pl(30 + c, s) = y;
+                    pAp += (double)ps * (double)y;
+                }
+            }
+            pAp = block_sum<BS>(pAp, s_buf); if (threadIdx.x == 0) P0[blockIdx.x] = pAp;
+            grid_barrier(A.barrier, bar_target, nb);
+            const float alpha = absNew / (float)grid_total_cg(P0, nb, s_buf);
+            // ---- phase 3 (own unknowns): x += alpha p ; r -= alpha y ; norms
+            double rn = 0.0, rz = 0.0;
+            for (int s = gtid; s < S; s += T) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float ps = __ldcg(pl(27 + c, s));
+                    *pl(21 + c, s) = __ldcg(pl(21 + c, s)) + alpha * ps;
+                    const float r2 = __ldcg(pl(24 + c, s)) - alpha * __ldcg(pl(30 + c, s));
+                    *pl(24 + c, s) = r2;
+                    rn += (double)r2 * (double)r2;
+                    rz += (double)r2 * (double)(__ldg(pl(15 + c, s)) * r2);
+                }
+            }
+            {
+                const double2 t = block_sum2<BS>(rn, rz, s_buf);
+                if (threadIdx.x == 0) { P1[blockIdx.x] = t.x; P2[blockIdx.x] = t.y; }
+            }
+            grid_barrier(A.barrier, bar_target, nb);
+            const double2 t12 = grid_total2_cg(P1, P2, nb, s_buf);
+            residualNorm2 = (float)t12.x;
+            if (residualNorm2 < threshold) break;
+            const float absOld = absNew;
+            absNew = (float)t12.y;
+            const float beta = absNew / absOld;
+            // ---- phase 4 (own unknowns): p <- z + beta p
+            for (int s = gtid; s < S; s += T) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    *pl(27 + c, s) = __ldg(pl(15 + c, s)) * __ldcg(pl(24 + c, s)) + beta * __ldcg(pl(27 + c, s));
+            }
+            grid_barrier(A.barrier, bar_target, nb);
+            ++it;
+        }
+    } else if (rhsNorm2 == 0.f) {
+        residualNorm2 = 0.f;
+    }
+    if (gtid == 0) {
+        A.result[0] = (float)it; A.result[1] = residualNorm2; A.result[2] = rhsNorm2; A.result[3] = threshold;
+    }
+    // ---- Optimizer::updateAlbedo (OptimizerAux.cpp:120-150): a channel is accepted only if it stays strictly inside (0, 1)
+    const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
+    const bool apply = !A.only_on_success || err <= tol;
+    int acc = 0;
+    for (int s = gtid; s < S; s += T) {
+        const int lin = A.lin[s];
+        float* chan[3] = { A.vol.r, A.vol.g, A.vol.b };
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float d = __ldcg(pl(21 + c, s));
+            if (A.delta_out) A.delta_out[3 * (long long)s + c] = d;
+            if (!apply) continue;
+            const float nv = chan[c][lin] - d;
+            if ((double)nv > 0.0 && (double)nv < 1.0) { chan[c][lin] = nv; ++acc; }
+        }
+    }
+    {
+        // one atomic per block
+        __shared__ int s_acc;
+        if (threadIdx.x == 0) s_acc = 0;
+        __syncthreads();
+        if (acc) atomicAdd(&s_acc, acc);
+        __syncthreads();
+        if (threadIdx.x == 0 && s_acc) atomicAdd(A.accepted, (unsigned long long)s_acc);
+    }
+}
+
 // Optimizer::updateDist (OptimizerAux.cpp:162-188): d -= delta only where |delta| < sqrt(3) * voxel_size (double compare)
 // IterativeSolverBase: info = error <= tolerance ? Success : NoConvergence, error = sqrt(residualNorm2 / rhsNorm2)
 __device__ __forceinline__ bool pcg_success(const float* __restrict__ verdict) {
@@ -932,6 +1168,52 @@ void launch_dist_update(psg_optimizer* o, bool only_on_success) {
     PSG_LAUNCH_CHECK();
     { Prof pf(o->stream, KID_GRAD_UPDATE); k_grad_update<<<(S + 255) / 256, 256, 0, o->stream>>>(vol, sv, o->vs_inv, verdict, gate); }
     PSG_LAUNCH_CHECK();
+}
+
+// regularised albedo block: the sweep left b = J^T W r in vecs[0 .. 3S) and the diagonal of J^T W J in vecs[3S .. 6S)
+void launch_albedo_reg_solve(psg_optimizer* o, float damping, bool only_on_success) {
+    const int S = o->S;
+    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotAreg, 0, 8 * sizeof(double), o->stream));   // verdict, accepted count, barrier
+    if (S == 0) return;
+    o->areg.alloc((size_t)S * 39 + 8);
+    o->vecs.alloc((size_t)S * 25 + 8);
+    const PcgGeometry& geo = pcg_geometry();
+    static int per_sm = 0;
+    if (!per_sm) PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_albedo_reg_solve<kPcgBlock>, kPcgBlock, 0));
+    if (per_sm < 1) { set_error("regularised albedo solve does not fit on an SM"); throw CudaError{-1}; }
+    int grid = geo.sms * (per_sm > 2 ? 2 : per_sm);
+    const int need = (S + kPcgBlock - 1) / kPcgBlock;
+    if (grid > need) grid = need;
+    if (grid > kPcgMaxBlocks) grid = kPcgMaxBlocks;
+    o->pcg_partials.alloc((size_t)4 * kPcgMaxBlocks + 1);
+    AregArgs A;
+    A.S = S; A.vol = o->vol->view();
+    A.lin = o->lin.p; A.nbr_lin = o->nbr_lin.p; A.nbr_row = o->nbr_row.p; A.inc = o->inc.p; A.pos = o->pos.p;
+    A.bd = o->vecs.p; A.Hd = o->vecs.p + (size_t)3 * S;
+    A.w = o->areg.p;
+    A.b_out = o->vecs.p + (size_t)6 * S; A.delta_out = o->vecs.p + (size_t)9 * S;
+    A.reg = o->set.reg_weight_rho; A.damping = damping; A.vs_inv = o->vs_inv;
+    A.max_iters = 2 * 3 * S; A.only_on_success = only_on_success ? 1 : 0;
+    A.partials = o->pcg_partials.p + 1;
+    double* slot = mail_dev(o) + 8 * kSlotAreg;
+    A.result = reinterpret_cast<float*>(slot);
+    A.accepted = reinterpret_cast<unsigned long long*>(slot + 5);
+    A.barrier = reinterpret_cast<unsigned long long*>(slot + 6);
+    void* args[] = { &A };
+    { Prof pf(o->stream, KID_PCG_SOLVE);
+      PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_albedo_reg_solve<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream)); }
+    o->vol->generation++;   // the albedo planes changed under the slot records: re-gathered before the next sweep
+}
+
+void read_albedo_reg_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted) {
+    *success = 1; *iters = 0; *err = 0.f; *accepted = 0;
+    if (o->S == 0) return;
+    const double* slot = mail_slot(o, kSlotAreg);
+    const float* res = reinterpret_cast<const float*>(slot);
+    *iters = (int)res[0];
+    *err = res[2] != 0.f ? sqrtf(res[1] / res[2]) : 0.f;
+    *success = (*err <= 1.1920929e-07f) ? 1 : 0;
+    *accepted = (long long)*reinterpret_cast<const unsigned long long*>(slot + 5);
 }
 
 void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted) {

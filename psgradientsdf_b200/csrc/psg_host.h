@@ -134,8 +134,10 @@ struct psg_optimizer {
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
     psg::DevBuf<double> pcg_partials;
     psg::DevBuf<float> pcg_pbuf;             // double-buffered search direction of the cluster PCG
+    psg::DevBuf<float> areg;                 // workspace of the regularised albedo solve (reg albedo != 0), 39 planes of S
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
     int last_n = 0, last_block = -1;
+    bool last_albedo_reg = false;            // the last albedo step went through the regularised solve
     // pinned host staging: the mailbox (kMailDoubles) followed by kRedDoubles of per-keyframe sums
     double* host_staging = nullptr;
     void ensure_host_staging();
@@ -153,6 +155,7 @@ constexpr int kRedDoubles = kMaxFrames * 64;
 constexpr int kRedCopies = 8;     // private copies of the per-keyframe sums on large grids (same-address fp64 atomics serialise in L2)
 constexpr int kMailDoubles = 64;
 constexpr int kPcgMaxBlocks = 1024;   // most blocks a cooperative distance-solve launch uses (4 per SM, <= 256 SMs)
+constexpr int kSlotAreg = 4;     // regularised albedo solve: 4 floats verdict (as kSlotPcg), [5] accepted updates, [6] grid-barrier counter
 constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
 constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
 constexpr int kSlotCount = 7;    // [0] unsigned long long: accepted distance updates, [1] arrival counter of the PCG's grid barrier
@@ -196,7 +199,7 @@ double* red_dev(psg_optimizer* o);
 const double* red_host(const psg_optimizer* o);
 const double* fetch_mail(psg_optimizer* o, size_t n_red_doubles);
 const double* mail_slot(const psg_optimizer* o, int slot);
-void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot);
+void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot, bool regularised = false);
 size_t launch_small_block(psg_optimizer* o, int block, int slot);
 void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<double>& H, std::vector<double>& b);
 void launch_dist_sweep(psg_optimizer* o, int flags, int slot);
@@ -213,5 +216,7 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
 void launch_dist_solve(psg_optimizer* o, float damping);              // assemble + PCG; verdict -> mail slot kSlotPcg
 void launch_dist_update(psg_optimizer* o, bool only_on_success);     // gated on the device by the PCG verdict; count -> kSlotCount
 void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted);   // after fetch_mail
+void launch_albedo_reg_solve(psg_optimizer* o, float damping, bool only_on_success);   // after launch_albedo(..., regularised = true)
+void read_albedo_reg_verdict(const psg_optimizer* o, int* success, int* iters, float* err, long long* accepted);
 
 }  // namespace psg

@@ -639,7 +639,11 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     if constexpr (MODE == M_ALBEDO) {
         // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
         // Optimizer::updateAlbedo gate (OptimizerAux.cpp:120-147): accept a channel only if it stays strictly in (0, 1)
-        if (warp == 0 && live) {
+        if (warp == 0 && live && (A.flags & PSG_REG_ALBEDO)) {
+            // reg albedo != 0: the system is no longer diagonal; hand J^T W J and J^T W r to the regularised solve (pcg.cu)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { A.out0[3 * (long long)s + c] = vacc[3 + c]; A.out1[3 * (long long)s + c] = vacc[c]; }
+        } else if (warp == 0 && live) {
             float* chan[3] = { A.vol.r, A.vol.g, A.vol.b };
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
@@ -908,9 +912,10 @@ void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float*
     launch_sweep<M_PROBE>(o, A, 0, 0);
 }
 
-void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot) {
+void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot, bool regularised) {
     SweepArgs A = base_args(o, slot);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
+    if (regularised) A.flags = PSG_REG_ALBEDO;   // out0 = J^T W r, out1 = diagonal of J^T W J, no update
     if (o->sharded) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
     if (o->sharded) comm_allgather_rho(o);
