@@ -534,6 +534,8 @@ def test_albedo_regulariser_vs_oracle(model):
             oo.block(blk, apply=True, damping=1.0, normal_reg=True); go.step(blk, damping=1.0, normal_reg=True)
     # the queued iteration takes the same path and reports the regulariser's energy after the albedo block
     info = go.iteration(damping=1.0, normal_reg=True, albedo_reg=True)
+    if model == "LED":   # LedOptimizer's order: the light block comes first
+        oo.block("light", apply=True, damping=1.0)
     oo.block("albedo", apply=True, damping=1.0, albedo_reg=True)
     ero = oo._reg_energy("or_opt_albedo_reg_energy")[1]
     assert abs(info["reg_albedo_after_albedo"] - ero) <= 1e-4 * abs(ero), (info["reg_albedo_after_albedo"], ero)
