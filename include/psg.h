@@ -331,28 +331,53 @@ typedef struct { int num_iterations; float conv_threshold; float damping; int sa
 int psg_tracker_optimize(psg_volume* vol, const float K[9], const float pose_in[16], const psg_tracker_config* cfg,
                          float pose_out[16], int* converged, int* iterations);
 
-/* ------------------------------------------------------------------ multi-GPU (no counterpart in the reference: it is one process)
- * One process per GPU.  Every rank holds the whole volume, keyframes and surface list (build them with the same calls on
- * every rank); the (surface voxel, keyframe) sweeps are split by round-robin 32-slot blocks of the visibility-sorted work list.
- * After psg_opt_comm_init, psg_opt_init_albedo / psg_opt_energy / psg_opt_step / psg_opt_alternating_optimize are
- * collective: all ranks must call them in the same order with the same arguments, and all ranks end in the same state
- * (small light / pose normal equations and energies: NCCL all-reduce; updated albedo and distance stencil blocks:
- * all-gather, then every rank runs the same distance solve).  NCCL over NVLink / NVSwitch; the communicator runs on the
- * optimizer's stream. */
+/* ---- several GPUs (no counterpart in the reference, which is one CPU process; BASELINE.json north_star) --------------------
+ * One rank per GPU.  Every rank creates its volume, fuses the same frames and hands over the same keyframes; after
+ * psg_opt_comm_init the calls psg_opt_init / init_albedo / energy / step / iteration / alternating_optimize / upsample /
+ * reg_energies / sync_volume / get_surface_voxels / set_shard_policy / comm_destroy are COLLECTIVE: all ranks call them in the
+ * same order with the same arguments.
+ *
+ * Sharded mode: the surface list is in ascending voxel order, so a contiguous ROW RANGE of it is a z-slab
+ * of the volume; rank g owns one range (equal numbers of visible pairs per rank) and does all per-row work on it -- sweeps,
+ * distance stencil blocks, the CG of the distance block, the gated updates, the regulariser energies.  Across ranks go: the
+ * energies and the per-keyframe light / pose normal equations (one NCCL all-reduce per host round trip), and, inside the
+ * persistent distance-solve kernel, the one-voxel halo of the CG vectors plus two scalars per reduction, written straight into
+ * the peers' memory over NVLink (CUDA IPC mappings) with a flag barrier.  Energies, light, poses and CG verdicts are identical on
+ * all ranks; of the VOLUME a rank keeps only its own rows (and the distance of its halo) current until psg_opt_sync_volume.
+ * Diagnostics that return per-row data (psg_opt_probe_pairs, psg_opt_residual, psg_opt_last_vectors) cover the rank's own rows.
+ * reg albedo != 0 is not provided in this mode.
+ * Replicated mode: every rank sweeps everything and rank 0's reduced sums are broadcast before the small solves, so that all
+ * ranks stay in the same state bit for bit; nothing is gained, nothing lost -- the fallback for work lists too small to split. */
 int psg_comm_unique_id(unsigned char id[128]);                                   /* rank 0; send the bytes to the other ranks */
-int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank, int world);
+int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank, int world);   /* one process per GPU, NCCL */
+/* The ranks of a job as THREADS of one process whose optimizers share a device: opts[q] becomes rank q.  Same code path as
+ * above with the peers' pointers taken directly and the collectives done by whichever thread arrives last; every collective
+ * call must then be made by `world` threads concurrently, one per optimizer.  For testing the multi-rank logic on one GPU:
+ * the distributed distance solve runs as one cooperative launch whose blocks play all ranks. */
+int psg_opt_comm_init_local(psg_optimizer* const* opts, int world);
 int psg_opt_comm_destroy(psg_optimizer* opt);
-/* Sharding policy.  Splitting the sweeps adds ~7 collectives per outer iteration; it pays from about two million visible
- * (voxel, keyframe) pairs per rank (measured on B200: 512^3 x 30 keyframes on 2 GPUs breaks even, 1024^3 x 64 gains up to 8).
- * 0 (default): shard when the work list has at least that much work per rank, otherwise every rank sweeps everything and
- * only rank 0's reduced sums are broadcast (same results, no slower than one GPU); 1: always shard; 2: never. */
+/* Sharding policy.  0 (default): shard when the work list has at least 150 000 visible (voxel, keyframe) pairs per rank
+ * (below that the exchange costs more than the split saves: 128^3 x 30 keyframes stays replicated, 512^3 x 30 is sharded on 8
+ * GPUs), 1: always shard, 2: never.  Switching re-partitions at the next call that touches the work list. */
 int psg_opt_set_shard_policy(psg_optimizer* opt, int policy);
 int psg_opt_is_sharded(const psg_optimizer* opt, int* sharded, long long* visible_pairs);
-/* Which 32-slot blocks of the work list `rank` of `world` sweeps for a surface of S voxels: blocks first, first + stride,
- * ... (count of them); round-robin, so that every rank gets the same mix of the visibility-sorted list. */
+/* The rows [row_lo, row_hi) of the surface list this rank owns and the rows [halo_lo, row_lo) + [row_hi, halo_hi) it receives
+ * from its neighbours (all rows / no halo unless sharded); any pointer may be NULL. */
+int psg_opt_row_range(psg_optimizer* opt, int* row_lo, int* row_hi, int* halo_lo, int* halo_hi);
+/* Sharded mode: every rank receives the other ranks' rows of the volume planes (distance, gradient, albedo), so that
+ * psg_volume_download, the mesh / point-cloud / .sdf writers and psg_opt_upsample see the whole reconstruction.  Called by
+ * psg_opt_alternating_optimize before every dump and at the end, by psg_opt_upsample, psg_opt_get_surface_voxels and
+ * psg_opt_comm_destroy.  A no-op when nothing changed or the job is not sharded. */
+int psg_opt_sync_volume(psg_optimizer* opt);
+/* The partition rule on host arrays (no device involved): cut points bounds[world + 1] over a surface list lin[S] (ascending)
+ * with keyframe visibility vis[S], equal visible-pair counts per range, and per rank the first / one-past-last row of its halo
+ * for a z-plane of `plane` = W * H voxels. */
+int psg_partition_rows(int S, const int* lin, const uint64_t* vis, long long plane, int world, int* bounds, int* halo_lo, int* halo_hi);
+/* Which 32-slot blocks of a slot list `rank` of `world` takes in a round-robin split (blocks first, first + stride, ...):
+ * used by psg_opt_energy_partial to emulate ranks on one list. */
 int psg_shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
-/* Diagnostic: the partial energy sum and pair count over the slots of `rank` of `world`, computed locally without any
- * communication (the partials of all ranks add up to psg_opt_energy * S). */
+/* Diagnostic: the partial energy sum and pair count over every world-th block of this rank's slot list, computed locally
+ * without any communication (the partials of all `world` emulated ranks add up to the list's energy sum). */
 int psg_opt_energy_partial(psg_optimizer* opt, int rank, int world, double* loss_sum, long long* n_active);
 
 /* {Ps,Led}Optimizer::alternatingOptimize(light, albedo, distance, pose) (PsOptimizer.cpp:239-428,

@@ -152,6 +152,10 @@ def lib():
         L.psg_comm_unique_id.argtypes = [C.c_char_p]
         L.psg_opt_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
         L.psg_opt_comm_destroy.argtypes = [vp]
+        L.psg_opt_comm_init_local.argtypes = [C.POINTER(vp), C.c_int]
+        L.psg_opt_row_range.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psg_opt_sync_volume.argtypes = [vp]
+        L.psg_partition_rows.argtypes = [C.c_int, i32p, u64p, C.c_longlong, C.c_int, i32p, i32p, i32p]
         L.psg_shard_blocks.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psg_opt_energy_partial.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
         L.psg_profile_enable.argtypes = [C.c_int]
@@ -176,6 +180,43 @@ def comm_unique_id() -> bytes:
     buf = C.create_string_buffer(128)
     _check(lib().psg_comm_unique_id(buf))
     return buf.raw
+
+
+def comm_init_local(opts):
+    """The given optimizers (one device) become ranks 0 .. n-1 of one job whose collectives are met by n threads, one per optimizer
+    (psg_opt_comm_init_local)."""
+    arr = (C.c_void_p * len(opts))(*[o.h for o in opts])
+    _check(lib().psg_opt_comm_init_local(arr, len(opts)))
+
+
+def partition_rows(lin, vis, plane: int, world: int):
+    """(bounds[world + 1], halo_lo[world], halo_hi[world]) of psg_partition_rows."""
+    lin = np.ascontiguousarray(lin, np.int32); vis = np.ascontiguousarray(vis, np.uint64)
+    b = np.zeros(world + 1, np.int32); lo = np.zeros(world, np.int32); hi = np.zeros(world, np.int32)
+    _check(lib().psg_partition_rows(int(lin.size), lin, vis, int(plane), int(world), b, lo, hi))
+    return b, lo, hi
+
+
+def run_ranks(fn, n: int):
+    """fn(rank) on n threads at once (the collective calls of a local rank group must be made concurrently); re-raises the first
+    exception; returns the list of results."""
+    import threading
+    out, err = [None] * n, [None] * n
+
+    def work(r):
+        try:
+            out[r] = fn(r)
+        except BaseException as e:   # noqa: BLE001
+            err[r] = e
+    th = [threading.Thread(target=work, args=(r,)) for r in range(n)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for e in err:
+        if e is not None:
+            raise e
+    return out
 
 
 def shard_blocks(S: int, rank: int, world: int):
@@ -601,6 +642,15 @@ class Optimizer:
         sh, vp_ = C.c_int(), C.c_longlong()
         _check(lib().psg_opt_is_sharded(self.h, C.byref(sh), C.byref(vp_)))
         return bool(sh.value), vp_.value
+
+    def row_range(self):
+        """(row_lo, row_hi, halo_lo, halo_hi) of this rank (psg_opt_row_range)."""
+        a, b, c, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _check(lib().psg_opt_row_range(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return a.value, b.value, c.value, d.value
+
+    def sync_volume(self):
+        _check(lib().psg_opt_sync_volume(self.h))
 
     def comm_destroy(self):
         _check(lib().psg_opt_comm_destroy(self.h))

@@ -352,7 +352,8 @@ int psg_opt_create(psg_optimizer** out, psg_volume* vol, float voxel_size, const
 int psg_opt_destroy(psg_optimizer* o) {
     if (!o) return PSG_OK;
     cudaSetDevice(o->vol->device);
-    psg_opt_comm_destroy(o);
+    psg::comm_destroy(o, /*collective=*/false);
+    o->xstate.release(); o->comm_buf.release();
     if (o->upload_stream) { cudaStreamSynchronize(o->upload_stream); cudaStreamDestroy(o->upload_stream); }
     if (o->upload_done) cudaEventDestroy(o->upload_done);
     if (o->timer0) { cudaEventDestroy(o->timer0); cudaEventDestroy(o->timer1); }
@@ -361,7 +362,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);
-    o->areg.release();
+    o->areg.release(); o->mg_args.release();
     o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
     delete o;
     return PSG_OK;
@@ -525,6 +526,7 @@ int psg_opt_get_surface_voxels(psg_optimizer* o, float* aos8) {
     if (!aos8) { set_error("psg_opt_get_surface_voxels: null argument"); return PSG_ERR_INVALID; }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(o->vol->device));
+    sync_volume(o);   // sharded: collective
     if (o->S > 0) {
         o->vol->staging.alloc((size_t)o->S * 8);
         launch_gather_voxels(o, o->vol->staging.p);
@@ -731,7 +733,9 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
         launch_dist_sweep(o, flags, slot);
         // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242).  The
         // verdict stays on the device: the update kernels read it, the host learns it with the next round trip.
-        if (!launch_dist_block_small(o, damping, /*only_on_success=*/!led, reg_energies_after ? kSlotReg : -1)) {
+        if (o->sharded) {
+            launch_dist_block_mg(o, damping, /*only_on_success=*/!led, reg_energies_after);
+        } else if (!launch_dist_block_small(o, damping, /*only_on_success=*/!led, reg_energies_after ? kSlotReg : -1)) {
             launch_dist_solve(o, damping);
             launch_dist_update(o, /*only_on_success=*/!led);
             if (reg_energies_after) launch_reg_energies(o, kSlotReg);   // getNormalEnergy / getLaplacianEnergy after the update
@@ -994,6 +998,7 @@ int psg_opt_upsample(psg_optimizer* o) {
     if (8 * o->vol->N > (1ll << 31) - 64) { set_error("psg_opt_upsample: upsampled grid exceeds 2^31 voxels"); return PSG_ERR_INVALID; }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(o->vol->device));
+    if (o->sharded) { sync_volume(o); release_peers(o); }   // children are made from the whole volume; its planes are reallocated
     launch_upsample(o);
     build_surface(o, false);
     return PSG_OK;

@@ -1,15 +1,36 @@
-// Multi-GPU plumbing: one process per GPU, NCCL over NVLink / NVSwitch.
+// Multi-GPU plumbing: one rank per GPU, NCCL over NVLink / NVSwitch for the small reductions, peer-mapped memory for the
+// distributed distance solve.
 //
-// The reference is a single process; this is the B200 part of the design.  Every rank keeps the whole
-// volume and work list; the sweeps are split by contiguous slot ranges of the visibility-sorted work list
-// (psg_shard_range).  What has to cross ranks per outer iteration is small:
-//   * energy / counters and the per-keyframe light (4x4 / 9x9) and pose (6x6) normal equations: all-reduce of <= 4104 doubles;
-//   * albedo after initAlbedo / the albedo block: all-gather of the {r, g, b} records (16 B per surface voxel);
-//   * distance: all-reduce of the 14 stencil-block planes (56 B per surface voxel), after which every rank runs the same
-//     deterministic distance solve and applies the same update, so no further exchange is needed.
-// All collectives are enqueued on the optimizer's stream, so they order with the kernels without host synchronisation.
+// The reference is a single process; this is the B200 part of the design (BASELINE.json north_star: "the volume
+// is partitioned across the 8 x B200 box in z-slabs with one-voxel halos exchanged over NVLink for the stencils, and the small
+// light / pose JtJ blocks are NCCL-allreduced each iteration").
+//
+// Partition.  The surface list is in ascending lin = i + W j + W H k order, so a contiguous ROW RANGE of it is a z-slab of the
+// volume (with ragged first / last planes).  Rank g owns rows [row_bounds[g], row_bounds[g + 1]), cut so that every rank gets
+// the same number of visible (voxel, keyframe) pairs.  Everything per row is produced and consumed by its owner: the sweeps
+// walk the owner's rows only, the distance stencil blocks stay where the sweep wrote them, the PCG, the gated update, the
+// gradient refresh and the regulariser energies run on the owner's rows.  What crosses ranks:
+//   * energy / counters and the per-keyframe light (4x4 / 9x9) and pose (6x6) normal equations: one NCCL all-reduce of <= 4104
+//     doubles per host round trip (fetch_mail);
+//   * the one-voxel halo: entries of z, p and the stencil products of the rows within one z-plane (W H voxels) of a cut, pushed by
+//     their owner into the neighbour's copy of the vector with plain stores over NVLink inside the persistent solve kernel
+//     (pcg.cu, k_dist_block_mg), and the updated distances of those rows after the solve;
+//   * two scalars per CG reduction, exchanged through the peers' XState mailboxes by the same kernel (a flag barrier over
+//     NVLink, no NCCL call inside the solve).
+// Every rank still holds the whole (fused) volume; only the rows it owns stay current between psg_opt_sync_volume calls, plus
+// the distance plane of its halo.
+//
+// Ranks are either processes (one per GPU; NCCL communicator + CUDA IPC mappings of the peers' buffers) or threads of one
+// process that share a device (psg_opt_comm_init_local: the same code path with the peers' pointers taken directly and the
+// collectives done by a leader thread -- used to test the multi-rank logic on a single GPU, where the distributed solve runs
+// as ONE cooperative launch whose blocks play all ranks).
 #include <dlfcn.h>
 #include <nccl.h>
+
+#include <algorithm>
+#include <condition_variable>
+#include <cstring>
+#include <mutex>
 
 #include "psg_host.h"
 
@@ -64,113 +85,364 @@ static bool nccl_load() {
         }                                                                                                \
     } while (0)
 
-// The work list is cut into blocks of 32 slots; rank r sweeps blocks r, r + world, r + 2 world, ...  The list is sorted by
-// visibility (most keyframes first), so contiguous ranges would give the first ranks the expensive end; round-robin blocks
-// give every rank the same mix.
+// ---- ranks as threads of one process ---------------------------------------------------------------------------------
+// A collective is a rendezvous of the member threads: every member records an event on its stream and publishes what the
+// operation needs; the last one to arrive (the leader) makes its stream wait for all events, runs the operation for everybody
+// on its own stream, records a completion event and wakes the others, whose streams then wait for that event.
+struct LocalGroup {
+    int world = 0;
+    psg_optimizer* member[kMaxRanks] = { nullptr };
+    cudaEvent_t ev[kMaxRanks] = { nullptr };
+    cudaEvent_t done[2] = { nullptr, nullptr };
+    std::mutex m;
+    std::condition_variable cv;
+    int arrived = 0;
+    long long generation = 0;
+    void* arg[kMaxRanks] = { nullptr };   // per-member argument of the collective in flight
+    PeerView views[kMaxRanks];            // filled by the leader of exchange_peers
+    int failed = 0;
+};
+
+template <typename F>
+static void group_collective(psg_optimizer* o, void* my_arg, F&& leader_fn) {
+    LocalGroup* g = static_cast<LocalGroup*>(o->group);
+    PSG_CUDA(cudaEventRecord(g->ev[o->rank], o->stream));
+    std::unique_lock<std::mutex> lk(g->m);
+    g->arg[o->rank] = my_arg;
+    const long long gen = g->generation;
+    cudaEvent_t done = g->done[gen & 1];
+    if (++g->arrived == g->world) {
+        int fail = 0;
+        try {
+            for (int q = 0; q < g->world; ++q) PSG_CUDA(cudaStreamWaitEvent(o->stream, g->ev[q], 0));
+            leader_fn(g);
+            PSG_CUDA(cudaEventRecord(done, o->stream));
+        } catch (const CudaError&) { fail = 1; }
+        g->failed = fail;
+        g->arrived = 0;
+        ++g->generation;
+        g->cv.notify_all();
+    } else {
+        g->cv.wait(lk, [&] { return g->generation != gen; });
+    }
+    const int fail = g->failed;
+    lk.unlock();
+    if (fail) { set_error("a collective of the local rank group failed"); throw CudaError{-1}; }
+    PSG_CUDA(cudaStreamWaitEvent(o->stream, done, 0));
+}
+
+// the same rendezvous for code outside this file: `leader` runs once, on the last member's thread and stream, with every
+// member's argument
+void group_run(psg_optimizer* o, void* my_arg, void (*leader)(psg_optimizer* on, void* const* args, int world, void* user), void* user) {
+    group_collective(o, my_arg, [&](LocalGroup* g) { leader(o, g->arg, g->world, user); });
+}
+
+// out[q][i] = sum over members of in[q'][i], same association (member order) for everybody
+__global__ void __launch_bounds__(256) k_group_allreduce(double* const* bufs /* world pointers */, int world, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double t = 0.0;
+    for (int q = 0; q < world; ++q) t += bufs[q][i];
+    for (int q = 0; q < world; ++q) bufs[q][i] = t;
+}
+__global__ void __launch_bounds__(256) k_group_broadcast(double* const* bufs, int world, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double t = bufs[0][i];
+    for (int q = 1; q < world; ++q) bufs[q][i] = t;
+}
+
+struct PtrTable { DevBuf<double*> dev; };
+static PtrTable& ptr_table() { static thread_local PtrTable t; return t; }
+
+struct ReduceArg { double* ptr[3]; size_t cnt[3]; int n; };
+
+void comm_allreduce_doubles(psg_optimizer* o, double* const* ptr, const size_t* count, int n) {
+    if (n <= 0) return;
+    if (o->group) {
+        ReduceArg mine; mine.n = n;
+        for (int k = 0; k < n; ++k) { mine.ptr[k] = ptr[k]; mine.cnt[k] = count[k]; }
+        group_collective(o, &mine, [&](LocalGroup* g) {
+            PtrTable& t = ptr_table();
+            t.dev.alloc((size_t)kMaxRanks * 3);
+            double* host[kMaxRanks * 3];
+            for (int k = 0; k < n; ++k)
+                for (int q = 0; q < g->world; ++q) host[k * kMaxRanks + q] = static_cast<ReduceArg*>(g->arg[q])->ptr[k];
+            PSG_CUDA(cudaMemcpyAsync(t.dev.p, host, sizeof(host), cudaMemcpyHostToDevice, o->stream));
+            for (int k = 0; k < n; ++k) {
+                k_group_allreduce<<<(unsigned)((count[k] + 255) / 256), 256, 0, o->stream>>>(t.dev.p + k * kMaxRanks, g->world, count[k]);
+                PSG_LAUNCH_CHECK();
+            }
+            PSG_CUDA(cudaStreamSynchronize(o->stream));   // `host` lives on this frame
+        });
+        return;
+    }
+    ncclComm_t comm = static_cast<ncclComm_t>(o->comm);
+    Prof pf(o->stream, KID_COMM_ALLREDUCE);
+    PSG_NCCL(g_nccl.GroupStart());
+    for (int k = 0; k < n; ++k)
+        if (count[k]) PSG_NCCL(g_nccl.AllReduce(ptr[k], ptr[k], count[k], ncclDouble, ncclSum, comm, o->stream));
+    PSG_NCCL(g_nccl.GroupEnd());
+}
+
+void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n) {
+    if (!n) return;
+    if (o->group) {
+        ReduceArg mine; mine.n = 1; mine.ptr[0] = a; mine.cnt[0] = n;
+        group_collective(o, &mine, [&](LocalGroup* g) {
+            PtrTable& t = ptr_table();
+            t.dev.alloc((size_t)kMaxRanks * 3);
+            double* host[kMaxRanks * 3] = { nullptr };
+            for (int q = 0; q < g->world; ++q) host[q] = static_cast<ReduceArg*>(g->arg[q])->ptr[0];
+            PSG_CUDA(cudaMemcpyAsync(t.dev.p, host, sizeof(host), cudaMemcpyHostToDevice, o->stream));
+            k_group_broadcast<<<(unsigned)((n + 255) / 256), 256, 0, o->stream>>>(t.dev.p, g->world, n);
+            PSG_LAUNCH_CHECK();
+            PSG_CUDA(cudaStreamSynchronize(o->stream));
+        });
+        return;
+    }
+    Prof pf(o->stream, KID_COMM_ALLREDUCE);
+    PSG_NCCL(g_nccl.Broadcast(a, a, n, ncclDouble, 0, static_cast<ncclComm_t>(o->comm), o->stream));
+}
+
+// host-side barrier of the ranks (with the streams drained): a one-double all-reduce
+static void comm_barrier(psg_optimizer* o) {
+    if (o->world <= 1) return;
+    o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
+    double* p[1] = { o->red.p + kMailDoubles - 1 };   // last double of the mailbox: slot 7, never summed otherwise
+    const size_t c[1] = { 1 };
+    PSG_CUDA(cudaMemsetAsync(p[0], 0, sizeof(double), o->stream));
+    comm_allreduce_doubles(o, p, c, 1);
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+}
+
+// The 32-slot blocks of a slot list that `rank` of `world` would take in a round-robin split: only used to emulate ranks on one
+// rank's list (psg_opt_energy_partial); a sharded job splits ROWS (partition_rows).
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count) {
     const int nblocks = (S + 31) / 32;
     *first = rank; *stride = world;
     *count = rank < nblocks ? (nblocks - rank + world - 1) / world : 0;
 }
 
-// slots per rank in the packed all-gather layout (the same for every rank: padded to the largest share)
-static size_t chunk_slots(const psg_optimizer* o) {
-    const int nblocks = (o->S + 31) / 32;
-    return (size_t)((nblocks + o->world - 1) / o->world) * 32;
-}
-
-void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb) {
-    ncclComm_t comm = static_cast<ncclComm_t>(o->comm);
-    Prof pf(o->stream, KID_COMM_ALLREDUCE);
-    PSG_NCCL(g_nccl.GroupStart());
-    if (na) PSG_NCCL(g_nccl.AllReduce(a, a, na, ncclDouble, ncclSum, comm, o->stream));
-    if (nb) PSG_NCCL(g_nccl.AllReduce(b, b, nb, ncclDouble, ncclSum, comm, o->stream));
-    PSG_NCCL(g_nccl.GroupEnd());
-}
-
-void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n) {
-    if (!n) return;
-    Prof pf(o->stream, KID_COMM_ALLREDUCE);
-    PSG_NCCL(g_nccl.Broadcast(a, a, n, ncclDouble, 0, static_cast<ncclComm_t>(o->comm), o->stream));
-}
-
-// Sharding pays only when a rank's share of the sweeps outweighs the collectives it adds (~7 per outer iteration, 20-400 us
-// each): measured on B200 x 2..8, the break-even is around two million visible pairs per rank (512^3 x 30 keyframes on two
-// GPUs).  Below it every rank sweeps the whole list and only rank 0's reduced sums are broadcast, so that all ranks still
-// solve identical small systems and stay in the same state bit for bit.
-constexpr long long kShardMinPairsPerRank = 2000000;
+// Sharding pays only when a rank's share of the work outweighs what the exchange adds (one small NCCL all-reduce per host
+// round trip, ~3 NVLink flag barriers per CG iteration): measured on B200 x 2..8 (profiles/r2_summary.md) the break-even is
+// around 150 000 visible pairs per rank.  Below it every rank sweeps the whole list and only rank 0's reduced sums are
+// broadcast, so that all ranks still solve identical small systems and stay in the same state bit for bit.
+constexpr long long kShardMinPairsPerRank = 150000;
 void update_shard_policy(psg_optimizer* o) {
-    if (o->world <= 1 || !o->comm) { o->sharded = false; return; }
-    if (o->shard_policy == 1) o->sharded = true;
-    else if (o->shard_policy == 2) o->sharded = false;
-    else o->sharded = o->vis_pairs / o->world >= kShardMinPairsPerRank;
+    bool want = false;
+    if (o->world > 1 && (o->comm || o->group)) {
+        if (o->shard_policy == 1) want = true;
+        else if (o->shard_policy == 2) want = false;
+        else want = o->vis_pairs / o->world >= kShardMinPairsPerRank;
+    }
+    if (want != o->sharded) { o->sharded = want; o->layout_dirty = true; }
 }
 
-// packed index (rank r, local j) -> work-list slot
-__device__ __forceinline__ int packed_slot(int r, int j, int world) { return ((j >> 5) * world + r) * 32 + (j & 31); }
-
-// albedo of every slot -> rec1 + dense volume planes (own slots were written by the sweep itself)
-__global__ void __launch_bounds__(256) k_scatter_rho(VolView vol, SurfView surf, const float4* __restrict__ buf, int chunk, int world, int own) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= chunk * world) return;
-    const int r = t / chunk, j = t - r * chunk;
-    if (r == own) return;
-    const int slot = packed_slot(r, j, world);
-    if (slot >= surf.S) return;
-    const float4 r1 = buf[t];
-    surf.rec1[slot] = r1;
-    const int lin = __float_as_int(surf.rec3[slot].w);
-    vol.r[lin] = r1.x; vol.g[lin] = r1.y; vol.b[lin] = r1.z;
+// ---- row partition ----------------------------------------------------------------------------------------------------
+// Pure host arithmetic on the (replicated) surface list, exported for the CPU tests as psg_partition_rows.
+// bounds[world + 1]: cut points with equal visible-pair counts per range (every row weighs popcount(vis) + 1, so rows without
+// pairs still spread); halo_lo / halo_hi[world]: rank q needs the rows [halo_lo[q], bounds[q]) below and [bounds[q + 1],
+// halo_hi[q]) above its range -- all rows of other ranks whose voxel lies within `plane` (= W * H) linear indices of the
+// range's first / last voxel: that covers the finite-difference neighbours (+-1, +-W, +-W H), the stencils that contain a
+// row, and the 6-point Laplacian.
+static void partition_rows_host(int S, const int* lin, const unsigned long long* vis, long long plane, int world, int* bounds,
+                                int* halo_lo, int* halo_hi) {
+    std::vector<long long> pre((size_t)S + 1, 0);
+    for (int s = 0; s < S; ++s) pre[s + 1] = pre[s] + __builtin_popcountll(vis[s]) + 1;
+    bounds[0] = 0;
+    for (int g = 1; g < world; ++g) {
+        const long long target = pre[S] * g / world;
+        int b = (int)(std::lower_bound(pre.begin(), pre.end(), target) - pre.begin());
+        if (b < bounds[g - 1]) b = bounds[g - 1];
+        if (b > S) b = S;
+        bounds[g] = b;
+    }
+    bounds[world] = S;
+    for (int q = 0; q < world; ++q) {
+        const int lo = bounds[q], hi = bounds[q + 1];
+        if (hi <= lo) { halo_lo[q] = lo; halo_hi[q] = hi; continue; }   // owns nothing, needs nothing
+        const long long first = lin[lo], last = lin[hi - 1];
+        halo_lo[q] = (int)(std::lower_bound(lin, lin + lo, (int)std::max<long long>(first - plane, 0)) - lin);
+        const long long top = std::min<long long>(last + plane, 0x7fffffffll);
+        halo_hi[q] = (int)(std::upper_bound(lin + hi, lin + S, (int)top) - lin);
+    }
 }
 
-// distance stencil blocks of every slot -> 14 planes indexed by surface row
-__global__ void __launch_bounds__(256) k_scatter_stencil(SurfView surf, const float* __restrict__ buf, float* __restrict__ blocks, int chunk, int world) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= chunk * world) return;
-    const int r = t / chunk, j = t - r * chunk;
-    const int slot = packed_slot(r, j, world);
-    if (slot >= surf.S) return;
-    const int s = __float_as_int(surf.rec2[slot].w);
-    const float* src = buf + (size_t)r * 14 * chunk + j;
-#pragma unroll
-    for (int i = 0; i < 14; ++i) blocks[(size_t)i * surf.S + s] = src[(size_t)i * chunk];
+void partition_rows(psg_optimizer* o) {
+    const int S = o->S, world = o->sharded ? o->world : 1;
+    o->row_bounds.assign(world + 1, 0); o->halo_lo.assign(world, 0); o->halo_hi.assign(world, 0);
+    if (!o->sharded) {
+        o->row_bounds[1] = S; o->halo_hi[0] = S;
+        o->row_lo = 0; o->row_hi = S; o->n_slots = S;
+        return;
+    }
+    std::vector<int> lin((size_t)(S > 0 ? S : 1));
+    std::vector<unsigned long long> vis((size_t)(S > 0 ? S : 1));
+    if (S > 0) {
+        PSG_CUDA(cudaMemcpyAsync(lin.data(), o->lin.p, (size_t)S * sizeof(int), cudaMemcpyDeviceToHost, o->stream));
+        PSG_CUDA(cudaMemcpyAsync(vis.data(), o->svis.p, (size_t)S * sizeof(unsigned long long), cudaMemcpyDeviceToHost, o->stream));
+        PSG_CUDA(cudaStreamSynchronize(o->stream));
+    }
+    const long long plane = (long long)o->vol->dims[0] * o->vol->dims[1];
+    partition_rows_host(S, lin.data(), vis.data(), plane, world, o->row_bounds.data(), o->halo_lo.data(), o->halo_hi.data());
+    o->row_lo = o->row_bounds[o->rank]; o->row_hi = o->row_bounds[o->rank + 1];
+    o->n_slots = o->row_hi - o->row_lo;
 }
 
-float4* comm_pack_rho(psg_optimizer* o) {
-    const size_t chunk = chunk_slots(o);
-    o->comm_buf.alloc(chunk * o->world * 14);   // sized for the larger user (stencil); 16-byte aligned by cudaMalloc
-    return reinterpret_cast<float4*>(o->comm_buf.p) + (size_t)o->rank * chunk;
+// ---- peers' views of each other's buffers ----------------------------------------------------------------------------------
+struct IpcRecord { cudaIpcMemHandle_t h; unsigned long long offset; };
+struct IpcPacket { IpcRecord vecs, pbuf, dist, xs; };
+
+typedef int (*cuMemGetAddressRange_t)(unsigned long long*, size_t*, unsigned long long);
+static cuMemGetAddressRange_t address_range_fn() {
+    static cuMemGetAddressRange_t fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        PSG_CUDA(cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &qr));
+        if (!p || qr != cudaDriverEntryPointSuccess) { set_error("cuMemGetAddressRange not available"); throw CudaError{-1}; }
+        fn = reinterpret_cast<cuMemGetAddressRange_t>(p);
+    }
+    return fn;
 }
 
-void comm_allgather_rho(psg_optimizer* o) {
+// an IPC handle always names a whole allocation; small cudaMalloc blocks are carved out of larger ones, so the offset travels too
+static IpcRecord ipc_export(const void* ptr) {
+    IpcRecord r;
+    memset(&r, 0, sizeof(r));
+    unsigned long long base = 0; size_t size = 0;
+    const int st = address_range_fn()(&base, &size, (unsigned long long)(uintptr_t)ptr);
+    if (st != 0) { set_error("cuMemGetAddressRange failed (%d)", st); throw CudaError{st}; }
+    PSG_CUDA(cudaIpcGetMemHandle(&r.h, reinterpret_cast<void*>((uintptr_t)base)));
+    r.offset = (unsigned long long)(uintptr_t)ptr - base;
+    return r;
+}
+
+struct IpcCache { std::vector<std::pair<cudaIpcMemHandle_t, void*>> open; };
+
+static void* ipc_import(psg_optimizer* o, IpcCache& cache, const IpcRecord& r) {
+    for (auto& e : cache.open)
+        if (memcmp(&e.first, &r.h, sizeof(r.h)) == 0) return static_cast<char*>(e.second) + r.offset;
+    void* base = nullptr;
+    PSG_CUDA(cudaIpcOpenMemHandle(&base, r.h, cudaIpcMemLazyEnablePeerAccess));
+    cache.open.push_back({r.h, base});
+    o->ipc_opened.push_back(base);
+    return static_cast<char*>(base) + r.offset;
+}
+
+void release_peers(psg_optimizer* o) {
+    bool had = false;
+    for (int q = 0; q < kMaxRanks; ++q) { if (o->peer[q].vecs && q != o->rank) had = true; o->peer[q] = PeerView(); }
+    if (!o->ipc_opened.empty()) {
+        PSG_CUDA(cudaStreamSynchronize(o->stream));
+        for (void* b : o->ipc_opened) cudaIpcCloseMemHandle(b);
+        o->ipc_opened.clear();
+    }
+    // nobody may free or reallocate a buffer before every peer has let go of it
+    if (had && o->world > 1 && (o->comm || o->group)) comm_barrier(o);
+}
+
+void exchange_peers(psg_optimizer* o) {
+    for (int q = 0; q < kMaxRanks; ++q) o->peer[q] = PeerView();
+    if (!o->sharded) return;
+    if (o->world > kMaxRanks) { set_error("a sharded job has at most %d ranks (%d given)", kMaxRanks, o->world); throw CudaError{-1}; }
+    if (!o->xstate.p) {
+        o->xstate.alloc(sizeof(XState));
+        PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, sizeof(XState), o->stream));
+        PSG_CUDA(cudaStreamSynchronize(o->stream));
+    }
+    PeerView mine;
+    mine.vecs = o->vecs.p; mine.pbuf = o->pcg_pbuf.p; mine.dist = o->vol->f[0].p; mine.xs = reinterpret_cast<XState*>(o->xstate.p);
+    if (o->group) {
+        // same address space: take the members' pointers (the rendezvous doubles as the barrier after allocation)
+        group_collective(o, &mine, [&](LocalGroup* g) { for (int q = 0; q < g->world; ++q) g->views[q] = *static_cast<PeerView*>(g->arg[q]); });
+        LocalGroup* g = static_cast<LocalGroup*>(o->group);
+        for (int q = 0; q < o->world; ++q) o->peer[q] = g->views[q];
+        group_collective(o, nullptr, [&](LocalGroup*) {});   // everybody has copied before the table is reused
+        return;
+    }
+    // processes: all-gather the IPC handles through NCCL, then map
+    IpcPacket pk;
+    pk.vecs = ipc_export(mine.vecs); pk.pbuf = ipc_export(mine.pbuf); pk.dist = ipc_export(mine.dist); pk.xs = ipc_export(mine.xs);
+    DevBuf<unsigned char> buf;
+    buf.alloc(sizeof(IpcPacket) * (size_t)o->world);
+    PSG_CUDA(cudaMemcpyAsync(buf.p + sizeof(IpcPacket) * (size_t)o->rank, &pk, sizeof(pk), cudaMemcpyHostToDevice, o->stream));
+    PSG_NCCL(g_nccl.AllGather(buf.p + sizeof(IpcPacket) * (size_t)o->rank, buf.p, sizeof(IpcPacket), ncclChar,
+                              static_cast<ncclComm_t>(o->comm), o->stream));
+    std::vector<IpcPacket> all((size_t)o->world);
+    PSG_CUDA(cudaMemcpyAsync(all.data(), buf.p, sizeof(IpcPacket) * (size_t)o->world, cudaMemcpyDeviceToHost, o->stream));
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    buf.release();
+    IpcCache cache;
+    for (int q = 0; q < o->world; ++q) {
+        if (q == o->rank) { o->peer[q] = mine; continue; }
+        o->peer[q].vecs = static_cast<float*>(ipc_import(o, cache, all[q].vecs));
+        o->peer[q].pbuf = static_cast<float*>(ipc_import(o, cache, all[q].pbuf));
+        o->peer[q].dist = static_cast<float*>(ipc_import(o, cache, all[q].dist));
+        o->peer[q].xs = static_cast<XState*>(ipc_import(o, cache, all[q].xs));
+    }
+    comm_barrier(o);   // every rank has mapped everything before anyone launches a kernel that writes to a peer
+}
+
+// ---- psg_opt_sync_volume: the rows every rank owns -> everybody ---------------------------------------------------------------
+// packed per rank: 7 planes {dist, gx, gy, gz, r, g, b} of `chunk` rows (chunk = the largest range, so that equal-sized
+// messages can be all-gathered)
+__global__ void __launch_bounds__(256) k_pack_rows(VolView vol, const int* __restrict__ lin, int row0, int n, int chunk, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int l = lin[row0 + i];
+    out[i] = vol.dist[l]; out[chunk + i] = vol.gx[l]; out[2 * (size_t)chunk + i] = vol.gy[l]; out[3 * (size_t)chunk + i] = vol.gz[l];
+    out[4 * (size_t)chunk + i] = vol.r[l]; out[5 * (size_t)chunk + i] = vol.g[l]; out[6 * (size_t)chunk + i] = vol.b[l];
+}
+__global__ void __launch_bounds__(256) k_unpack_rows(VolView vol, const int* __restrict__ lin, int row0, int n, int chunk, const float* __restrict__ in) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int l = lin[row0 + i];
+    vol.dist[l] = in[i]; vol.gx[l] = in[chunk + i]; vol.gy[l] = in[2 * (size_t)chunk + i]; vol.gz[l] = in[3 * (size_t)chunk + i];
+    vol.r[l] = in[4 * (size_t)chunk + i]; vol.g[l] = in[5 * (size_t)chunk + i]; vol.b[l] = in[6 * (size_t)chunk + i];
+}
+
+struct GatherArg { float* buf; };
+
+void sync_volume(psg_optimizer* o) {
+    if (!o->sharded || !o->vol_unsynced) return;
+    o->vol_unsynced = false;
     if (o->S == 0) return;
-    const size_t chunk = chunk_slots(o);
-    float4* base = reinterpret_cast<float4*>(o->comm_buf.p);
-    { Prof pf(o->stream, KID_COMM_ALLGATHER);
-      PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * chunk, base, chunk * 4, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream)); }
-    const SurfView sv = surf_view(o);
-    const int n = (int)(chunk * o->world);
-    { Prof pf(o->stream, KID_COMM_SCATTER); k_scatter_rho<<<(n + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), sv, base, (int)chunk, o->world, o->rank); }
-    PSG_LAUNCH_CHECK();
-}
-
-float* comm_pack_stencil(psg_optimizer* o, int* stride) {
-    const size_t chunk = chunk_slots(o);
-    o->comm_buf.alloc(chunk * o->world * 14);
-    *stride = (int)chunk;
-    return o->comm_buf.p + (size_t)o->rank * 14 * chunk;
-}
-
-void comm_allgather_stencil(psg_optimizer* o, float* blocks) {
-    if (o->S == 0) return;
-    const size_t chunk = chunk_slots(o);
-    float* base = o->comm_buf.p;
-    { Prof pf(o->stream, KID_COMM_ALLGATHER);
-      PSG_NCCL(g_nccl.AllGather(base + (size_t)o->rank * 14 * chunk, base, 14 * chunk, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream)); }
-    const SurfView sv = surf_view(o);
-    const int n = (int)(chunk * o->world);
-    { Prof pf(o->stream, KID_COMM_SCATTER); k_scatter_stencil<<<(n + 255) / 256, 256, 0, o->stream>>>(sv, base, blocks, (int)chunk, o->world); }
-    PSG_LAUNCH_CHECK();
+    const int world = o->world;
+    int chunk = 1;
+    for (int q = 0; q < world; ++q) chunk = std::max(chunk, o->row_bounds[q + 1] - o->row_bounds[q]);
+    o->comm_buf.alloc((size_t)chunk * 7 * world);
+    const VolView vol = o->vol->view();
+    float* mine = o->comm_buf.p + (size_t)o->rank * 7 * chunk;
+    if (o->n_slots > 0) {
+        k_pack_rows<<<(o->n_slots + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, o->row_lo, o->n_slots, chunk, mine);
+        count_launch(); PSG_LAUNCH_CHECK();
+    }
+    if (o->group) {
+        GatherArg ga; ga.buf = o->comm_buf.p;
+        group_collective(o, &ga, [&](LocalGroup* g) {
+            for (int q = 0; q < world; ++q)
+                for (int p = 0; p < world; ++p) {
+                    if (p == q) continue;
+                    float* src = static_cast<GatherArg*>(g->arg[p])->buf + (size_t)p * 7 * chunk;
+                    float* dst = static_cast<GatherArg*>(g->arg[q])->buf + (size_t)p * 7 * chunk;
+                    PSG_CUDA(cudaMemcpyAsync(dst, src, (size_t)7 * chunk * sizeof(float), cudaMemcpyDeviceToDevice, o->stream));
+                }
+        });
+    } else {
+        Prof pf(o->stream, KID_COMM_ALLGATHER);
+        PSG_NCCL(g_nccl.AllGather(mine, o->comm_buf.p, (size_t)7 * chunk, ncclFloat, static_cast<ncclComm_t>(o->comm), o->stream));
+    }
+    for (int q = 0; q < world; ++q) {
+        const int n = o->row_bounds[q + 1] - o->row_bounds[q];
+        if (q == o->rank || n <= 0) continue;
+        { Prof pf(o->stream, KID_COMM_SCATTER);
+          k_unpack_rows<<<(n + 255) / 256, 256, 0, o->stream>>>(vol, o->lin.p, o->row_bounds[q], n, chunk, o->comm_buf.p + (size_t)q * 7 * chunk); }
+        PSG_LAUNCH_CHECK();
+    }
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    // the slot records cover own rows only and those did not change
 }
 
 }  // namespace psg
@@ -193,7 +465,7 @@ int psg_comm_unique_id(unsigned char id[128]) {
 int psg_opt_comm_init(psg_optimizer* o, const unsigned char id[128], int rank, int world) {
     if (!o || !id) { set_error("psg_opt_comm_init: null argument"); return PSG_ERR_INVALID; }
     if (world < 1 || world > 64 || rank < 0 || rank >= world) { set_error("psg_opt_comm_init: rank %d of %d is not valid (1 <= world <= 64)", rank, world); return PSG_ERR_INVALID; }
-    if (o->comm) { set_error("psg_opt_comm_init: a communicator already exists"); return PSG_ERR_STATE; }
+    if (o->comm || o->group) { set_error("psg_opt_comm_init: a communicator already exists"); return PSG_ERR_STATE; }
     if (!nccl_load()) return PSG_ERR_CUDA;
     try {
         PSG_CUDA(cudaSetDevice(o->vol->device));
@@ -207,30 +479,123 @@ int psg_opt_comm_init(psg_optimizer* o, const unsigned char id[128], int rank, i
     } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
 }
 
-int psg_opt_comm_destroy(psg_optimizer* o) {
-    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
-    if (o->comm) {
-        cudaSetDevice(o->vol->device);
-        cudaStreamSynchronize(o->stream);
-        g_nccl.CommDestroy(static_cast<ncclComm_t>(o->comm));
-        o->comm = nullptr;
+int psg_opt_comm_init_local(psg_optimizer* const* opts, int world) {
+    if (!opts || world < 1 || world > kMaxRanks) { set_error("psg_opt_comm_init_local: 1 <= world <= %d optimizers expected", kMaxRanks); return PSG_ERR_INVALID; }
+    for (int q = 0; q < world; ++q) {
+        if (!opts[q]) { set_error("psg_opt_comm_init_local: optimizer %d is null", q); return PSG_ERR_INVALID; }
+        if (opts[q]->comm || opts[q]->group) { set_error("psg_opt_comm_init_local: optimizer %d already has a communicator", q); return PSG_ERR_STATE; }
+        if (opts[q]->vol->device != opts[0]->vol->device) { set_error("psg_opt_comm_init_local: all members must live on one device"); return PSG_ERR_INVALID; }
     }
-    o->rank = 0; o->world = 1; o->sharded = false;
+    try {
+        PSG_CUDA(cudaSetDevice(opts[0]->vol->device));
+        LocalGroup* g = new LocalGroup;
+        g->world = world;
+        for (int q = 0; q < world; ++q) { g->member[q] = opts[q]; PSG_CUDA(cudaEventCreateWithFlags(&g->ev[q], cudaEventDisableTiming)); }
+        for (int k = 0; k < 2; ++k) PSG_CUDA(cudaEventCreateWithFlags(&g->done[k], cudaEventDisableTiming));
+        for (int q = 0; q < world; ++q) {
+            opts[q]->group = g; opts[q]->rank = q; opts[q]->world = world;
+            update_shard_policy(opts[q]);
+        }
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+}  // extern "C"
+
+// collective = every rank is inside this call (psg_opt_comm_destroy); psg_opt_destroy on a handle that still has a communicator
+// only lets go of the local resources
+int psg::comm_destroy(psg_optimizer* o, bool collective) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    try {
+        if (o->comm || o->group) {
+            cudaSetDevice(o->vol->device);
+            cudaStreamSynchronize(o->stream);
+            if (collective) {
+                if (o->sharded) sync_volume(o);
+                release_peers(o);
+            } else {
+                for (void* b : o->ipc_opened) cudaIpcCloseMemHandle(b);
+                o->ipc_opened.clear();
+                for (int q = 0; q < kMaxRanks; ++q) o->peer[q] = PeerView();
+            }
+        }
+        if (o->comm) {
+            g_nccl.CommDestroy(static_cast<ncclComm_t>(o->comm));
+            o->comm = nullptr;
+        }
+        if (o->group) {
+            LocalGroup* g = static_cast<LocalGroup*>(o->group);
+            bool last = false;
+            {
+                std::lock_guard<std::mutex> lk(g->m);
+                g->member[o->rank] = nullptr;
+                last = true;
+                for (int q = 0; q < g->world; ++q) if (g->member[q]) last = false;
+            }
+            o->group = nullptr;
+            if (last) {
+                for (int q = 0; q < g->world; ++q) if (g->ev[q]) cudaEventDestroy(g->ev[q]);
+                for (int k = 0; k < 2; ++k) if (g->done[k]) cudaEventDestroy(g->done[k]);
+                delete g;
+            }
+        }
+    } catch (const psg::CudaError&) { o->comm = nullptr; o->group = nullptr; o->rank = 0; o->world = 1; o->sharded = false; o->layout_dirty = true; return PSG_ERR_CUDA; }
+    o->rank = 0; o->world = 1;
+    if (o->sharded) { o->sharded = false; o->layout_dirty = true; }
     return PSG_OK;
 }
+
+extern "C" {
+
+int psg_opt_comm_destroy(psg_optimizer* o) { return psg::comm_destroy(o, true); }
 
 int psg_opt_set_shard_policy(psg_optimizer* o, int policy) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
     if (policy < 0 || policy > 2) { set_error("psg_opt_set_shard_policy: %d is not 0 (by work), 1 (always) or 2 (never)", policy); return PSG_ERR_INVALID; }
-    o->shard_policy = policy;
-    update_shard_policy(o);
-    return PSG_OK;
+    try {
+        PSG_CUDA(cudaSetDevice(o->vol->device));
+        if (o->sharded && policy == 2) sync_volume(o);   // leaving the sharded mode: every rank gets the whole state back
+        o->shard_policy = policy;
+        update_shard_policy(o);
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
 }
 
 int psg_opt_is_sharded(const psg_optimizer* o, int* sharded, long long* visible_pairs) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
     if (sharded) *sharded = o->sharded ? 1 : 0;
     if (visible_pairs) *visible_pairs = o->vis_pairs;
+    return PSG_OK;
+}
+
+int psg_opt_row_range(psg_optimizer* o, int* row_lo, int* row_hi, int* halo_lo, int* halo_hi) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (!o->inited) { set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
+    try {
+        PSG_CUDA(cudaSetDevice(o->vol->device));
+        if (o->layout_dirty) build_layout(o);
+        if (row_lo) *row_lo = o->row_lo;
+        if (row_hi) *row_hi = o->row_hi;
+        if (halo_lo) *halo_lo = o->halo_lo[o->sharded ? o->rank : 0];
+        if (halo_hi) *halo_hi = o->halo_hi[o->sharded ? o->rank : 0];
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+int psg_opt_sync_volume(psg_optimizer* o) {
+    if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
+    if (!o->inited) { set_error("psg_opt_init must be called first"); return PSG_ERR_STATE; }
+    try {
+        PSG_CUDA(cudaSetDevice(o->vol->device));
+        if (o->layout_dirty) build_layout(o);
+        sync_volume(o);
+        return PSG_OK;
+    } catch (const psg::CudaError&) { return PSG_ERR_CUDA; }
+}
+
+int psg_partition_rows(int S, const int* lin, const uint64_t* vis, long long plane, int world, int* bounds, int* halo_lo, int* halo_hi) {
+    if (S < 0 || world < 1 || (S > 0 && (!lin || !vis)) || plane < 1 || !bounds || !halo_lo || !halo_hi) { set_error("psg_partition_rows: bad argument"); return PSG_ERR_INVALID; }
+    partition_rows_host(S, lin, reinterpret_cast<const unsigned long long*>(vis), plane, world, bounds, halo_lo, halo_hi);
     return PSG_OK;
 }
 

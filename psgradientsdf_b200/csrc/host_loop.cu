@@ -241,6 +241,7 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
             verdict = 2;
         }
         if (verdict) {
+            PSG_RUN(psg_opt_sync_volume(o));   // several GPUs, sharded: every rank ends with the whole reconstruction
             if (files) {
                 save_pointcloud(o, out + "final_refined_pointcloud.ply");
                 save_mesh(o, out + "final_refined_mesh.ply");
@@ -276,12 +277,14 @@ extern "C" int psg_opt_alternating_optimize(psg_optimizer* o, const psg_loop_con
             psg_opt_set_reg(o, reg);
         }
         ++iter;
+        if (iter % 3 == 0 && cfg->write_artifacts != 0 && save_path != nullptr) PSG_RUN(psg_opt_sync_volume(o));   // collective: all ranks, not only the writer
         if (iter % 3 == 0 && files) {
             save_poses(o, out + "after_poses_opt_" + std::to_string(iter) + ".txt");
             save_pointcloud(o, out + "after_iter_" + std::to_string(iter) + "_pointcloud.ply");
             save_mesh(o, out + "after_iter_" + std::to_string(iter) + "_mesh.ply");
         }
     }
+    PSG_RUN(psg_opt_sync_volume(o));
 #undef PSG_RUN
     R.iterations = iter;
     R.converged = verdict == 1;

@@ -15,6 +15,9 @@
 // reproducible run to run.  One persistent cooperative kernel runs the whole solve (grid.sync between phases).
 #include <cooperative_groups.h>
 
+#include <algorithm>
+#include <cstring>
+
 #include "psg_host.h"
 
 namespace cg = cooperative_groups;
@@ -717,6 +720,372 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
     }
 }
 
+// ---- the distance block of a sharded job: one persistent kernel per rank, halo and reductions over peer memory ----------------
+// Rank g owns rows [lo, hi) of the surface list (a z-slab).  Its kernel runs k_dist_assemble, the CG, Optimizer::updateDist,
+// updateGrad and the regulariser energies on those rows.  Every vector is a full-length array on every rank; a rank computes
+// its own rows and reads the rows of its halo (other ranks' rows within one z-plane of its range) from ITS OWN copy, into which
+// the owners push them: whoever writes a row that a peer needs also stores it through the peer's mapped pointer (plain st.global
+// over NVLink).  A cross-rank barrier (xbar) separates the phases: the rank's blocks arrive on a local counter after a
+// system-scope fence; the rank's leader block then adds the local partial sums, writes them into every peer's XState mailbox
+// followed by a release store of the barrier number to the peer's flag word, waits until all peers' flags carry that number,
+// adds the partials in rank order (every rank forms the same sum bit for bit, hence takes the same branches) and releases its
+// own blocks.  Mailboxes are double-buffered by barrier parity; all counters are monotonic, nothing is reset while a peer might
+// still write.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers) instead of hanging.
+// On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative launch: block b belongs
+// to rank b / nb.
+struct MgSeg { int peer, b, e; };   // own rows [b, e) are in the halo of rank `peer`
+struct MgRank {
+    int rank, lo, hi;
+    int nseg;
+    MgSeg seg[2 * (kMaxRanks - 1)];
+    int inner_lo, inner_hi;         // rows in [inner_lo, inner_hi) are in nobody's halo
+    float* vecs; float* pbuf; XState* xs;
+    const int* nbr_row; const int* inc; const int* lin;
+    VolView vol; SurfView surf;
+    double* partials;               // [2][nb]
+    float* result;                  // iterations, residualNorm2, rhsNorm2, threshold, abort flag
+    double* regslot;                // {normal, laplacian, albedo energy sums, accepted updates}: partial sums over the own rows
+};
+struct MgArgs {
+    int S, world, nb, nplayed;      // nb blocks per rank; this launch plays `nplayed` ranks (1, or all on a single device)
+    PeerView peer[kMaxRanks];       // every rank's buffers as addressable from this launch
+    MgRank loc[kMaxRanks];          // the ranks played, in block order
+    float damping, vs_inv;
+    double thr;
+    int max_iters, only_on_success, want_reg;
+    unsigned long long timeout_ns;
+};
+
+constexpr int kMgBlock = 512;
+
+__device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+template <bool SYS>
+__device__ __forceinline__ bool wait_ge(const unsigned long long* p, unsigned long long target, XState* xs, unsigned long long limit_ns) {
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
+    for (;;) {
+        unsigned long long v;
+        if (SYS) asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+        else asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+        if (v >= target) return true;
+        if ((++spins & 255u) == 0) {
+            unsigned long long ab;
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(ab) : "l"(&xs->abort) : "memory");
+            if (ab) return false;
+            const unsigned long long now = global_ns();
+            if (!t0) t0 = now;
+            else if (now - t0 > limit_ns) {
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&xs->abort), "l"(1ull) : "memory");
+                return false;
+            }
+        }
+    }
+}
+
+struct MgCtx {
+    const MgArgs* A; const MgRank* R;
+    int lb, nb;                      // block index within the rank, blocks per rank
+    unsigned long long base;         // barriers completed by earlier launches
+    unsigned k;                      // barriers completed by this launch
+    bool ok;
+};
+
+// cross-rank barrier with a two-scalar all-reduce; returns the totals (identical bits on every rank and block)
+__device__ __forceinline__ double2 xbar(MgCtx& c, double a, double b, double* s_buf /* 2 * NW + 2 */) {
+    constexpr int NW = kMgBlock / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const MgArgs& A = *c.A; const MgRank& R = *c.R;
+    XState* xs = R.xs;
+    double* P0 = R.partials; double* P1 = R.partials + c.nb;
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; }
+    __syncthreads();
+    ++c.k;
+    const unsigned long long e = c.base + c.k;
+    const int par = (int)(e & 1ull);
+    if (warp == 0) {
+        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0;
+        ta = warp_sum(ta); tb = warp_sum(tb);
+        if (lane == 0) {
+            P0[c.lb] = ta; P1[c.lb] = tb;
+            __threadfence_system();   // this block's stores, local and through the peers' mappings, before the arrival
+            asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
+        }
+        if (c.lb == 0) {
+            bool ok = true;
+            if (lane == 0) ok = wait_ge<false>(&xs->arrive, (unsigned long long)c.k * (unsigned long long)c.nb, xs, A.timeout_ns);
+            ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+            double xa = 0.0, xb = 0.0;
+            for (int i = lane; i < c.nb; i += 32) { xa += __ldcg(P0 + i); xb += __ldcg(P1 + i); }
+            xa = warp_sum(xa); xb = warp_sum(xb);
+            if (lane < A.world) {
+                XState* px = A.peer[lane].xs;
+                if (!ok) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&px->abort), "l"(1ull) : "memory");
+                asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&px->box[par][R.rank][0]), "d"(xa) : "memory");
+                asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&px->box[par][R.rank][1]), "d"(xb) : "memory");
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&px->flag[R.rank]), "l"(e) : "memory");
+                if (!wait_ge<true>(&xs->flag[lane], e, xs, A.timeout_ns)) ok = false;
+            }
+            ok = __all_sync(0xffffffffu, ok);
+            if (lane == 0) {
+                double sa = 0.0, sb = 0.0;
+                for (int q = 0; q < A.world; ++q) {
+                    double va, vb;
+                    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(va) : "l"(&xs->box[par][q][0]) : "memory");
+                    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(vb) : "l"(&xs->box[par][q][1]) : "memory");
+                    sa += va; sb += vb;
+                }
+                xs->bcast[par][0] = sa; xs->bcast[par][1] = sb;
+                if (!ok) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&xs->abort), "l"(1ull) : "memory");
+                __threadfence();
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(&xs->release), "l"(e) : "memory");
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (!wait_ge<false>(&xs->release, e, xs, A.timeout_ns)) c.ok = false;
+        s_buf[2 * NW] = __ldcg(&xs->bcast[par][0]);
+        s_buf[2 * NW + 1] = __ldcg(&xs->bcast[par][1]);
+        unsigned long long ab;
+        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(ab) : "l"(&xs->abort) : "memory");
+        s_buf[2 * NW + 2] = ab ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    if (s_buf[2 * NW + 2] != 0.0) c.ok = false;
+    const double2 out = make_double2(s_buf[2 * NW], s_buf[2 * NW + 1]);
+    __syncthreads();   // s_buf is reused by the next call
+    return out;
+}
+
+// store to the own copy and to the copy of every rank that has the row in its halo
+__device__ __forceinline__ void put_vec(const MgArgs& A, const MgRank& R, size_t plane_off, int s, float v) {
+    R.vecs[plane_off + s] = v;
+    if (s >= R.inner_lo && s < R.inner_hi) return;
+    for (int i = 0; i < R.nseg; ++i)
+        if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].vecs[plane_off + s] = v;
+}
+__device__ __forceinline__ void put_p(const MgArgs& A, const MgRank& R, size_t off, int s, float v) {
+    R.pbuf[off + s] = v;
+    if (s >= R.inner_lo && s < R.inner_hi) return;
+    for (int i = 0; i < R.nseg; ++i)
+        if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].pbuf[off + s] = v;
+}
+
+__global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
+    __shared__ double s_buf[2 * (kMgBlock / 32) + 4];
+    __shared__ double s_reg[kMgBlock / 32][4];
+    const MgArgs& A = *Ap;
+    const int nb = A.nb;
+    const MgRank& R = A.loc[blockIdx.x / nb];
+    MgCtx c;
+    c.A = &A; c.R = &R; c.lb = blockIdx.x % nb; c.nb = nb; c.k = 0; c.ok = true;
+    c.base = __ldcg(&R.xs->epoch);
+    const int S = A.S, lo = R.lo, hi = R.hi;
+    const int T = nb * kMgBlock, ltid = c.lb * kMgBlock + threadIdx.x;
+    const size_t PS = (size_t)S;
+    float* V = R.vecs;
+    const float tol = 1.1920929e-07f;
+
+    // ---- the stencil planes the neighbours' assembly reads: rhs of slots 1..3 and the diagonal entries (a+1, a+1)
+    for (int s = lo + ltid; s < hi; s += T) {
+        if (s >= R.inner_lo && s < R.inner_hi) continue;
+        const int planes[6] = { 2, 5, 9, 11, 12, 13 };
+#pragma unroll
+        for (int i = 0; i < 6; ++i) put_vec(A, R, planes[i] * PS, s, V[planes[i] * PS + s]);
+    }
+    xbar(c, 0.0, 0.0, s_buf);
+    // ---- k_dist_assemble on the own rows; x = 0, r = b, z = b / diag, p = z
+    double a0 = 0.0, a1 = 0.0;
+    for (int s = lo + ltid; s < hi; s += T) {
+        float rhs = V[10 * PS + s], diag = V[s];
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
+                if (t >= 0) { rhs += __ldcg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldcg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
+            }
+        const float dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
+        const float full = diag + dd;
+        const float invd = (full != 0.f) ? 1.f / full : 1.f;
+        const float z = invd * rhs;
+        V[14 * PS + s] = rhs; V[15 * PS + s] = invd; V[16 * PS + s] = dd; V[17 * PS + s] = 0.f; V[19 * PS + s] = rhs;
+        put_vec(A, R, 18 * PS, s, z);
+        put_p(A, R, 0, s, z);
+        a0 += (double)rhs * (double)rhs; a1 += (double)rhs * (double)z;
+    }
+    const double2 t01 = xbar(c, a0, a1, s_buf);
+    const float rhsNorm2 = (float)t01.x;
+    float absNew = (float)t01.y;
+    float threshold = tol * tol * rhsNorm2;
+    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+    float residualNorm2 = rhsNorm2;
+    int it = 0;
+    if (c.ok && rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+        float gamma = 0.f, beta = 1.f;   // first pass: the published p already is the search direction
+        int cur = 0;
+        while (it < A.max_iters) {
+            const float* pc = R.pbuf + (size_t)cur * PS;
+            const size_t pn_off = (size_t)(cur ^ 1) * PS;
+            // ---- phase 1: p <- z + beta p (neighbours recomputed from the published z and p), u_t = A_t * p[stencil(t)]
+            for (int s = lo + ltid; s < hi; s += T) {
+                int col[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) col[a] = __ldg(R.nbr_row + (size_t)a * S + s);
+                float px[4];
+                px[0] = __ldcg(V + 18 * PS + s) * gamma + beta * __ldcg(pc + s);
+#pragma unroll
+                for (int a = 0; a < 3; ++a) px[a + 1] = col[a] >= 0 ? __ldcg(V + 18 * PS + col[a]) * gamma + beta * __ldcg(pc + col[a]) : 0.f;
+                put_p(A, R, pn_off, s, px[0]);
+                float Ab[10];
+#pragma unroll
+                for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float u = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                        if (k == 0 || col[k - 1] >= 0) u += aik * px[k];
+                    }
+                    const bool valid = (i == 0) || col[i - 1] >= 0;
+                    if (i == 0) V[21 * PS + s] = u; else put_vec(A, R, (size_t)(21 + i) * PS, s, valid ? u : 0.f);
+                }
+            }
+            xbar(c, 0.0, 0.0, s_buf);
+            if (!c.ok) break;
+            // ---- phase 2: y = u_s[0] + incident u + damping * diag * p_s ; p . y
+            const float* pn = R.pbuf + pn_off;
+            double pAp = 0.0;
+            for (int s = lo + ltid; s < hi; s += T) {
+                float y = V[21 * PS + s];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
+                        if (t >= 0) y += __ldcg(V + (size_t)(22 + a) * PS + t);
+                    }
+                const float ps = __ldcg(pn + s);
+                y += V[16 * PS + s] * ps;
+                V[20 * PS + s] = y;
+                pAp += (double)ps * (double)y;
+            }
+            const float alpha = absNew / (float)xbar(c, pAp, 0.0, s_buf).x;
+            if (!c.ok) break;
+            // ---- phase 3 (own rows): x += alpha p ; r -= alpha y ; z = r / diag, published ; norms
+            double rn = 0.0, rz = 0.0;
+            for (int s = lo + ltid; s < hi; s += T) {
+                const float ps = __ldcg(pn + s);
+                V[17 * PS + s] = V[17 * PS + s] + alpha * ps;
+                const float r2 = V[19 * PS + s] - alpha * V[20 * PS + s];
+                V[19 * PS + s] = r2;
+                const float z = V[15 * PS + s] * r2;
+                put_vec(A, R, 18 * PS, s, z);
+                rn += (double)r2 * (double)r2; rz += (double)r2 * (double)z;
+            }
+            const double2 t12 = xbar(c, rn, rz, s_buf);
+            if (!c.ok) break;
+            residualNorm2 = (float)t12.x;
+            if (residualNorm2 < threshold) break;
+            const float absOld = absNew;
+            absNew = (float)t12.y;
+            beta = absNew / absOld;
+            gamma = 1.f;
+            cur ^= 1;
+            ++it;
+        }
+    } else if (rhsNorm2 == 0.f) {
+        residualNorm2 = 0.f;
+    }
+    if (ltid == 0) {
+        R.result[0] = (float)it; R.result[1] = residualNorm2; R.result[2] = rhsNorm2; R.result[3] = threshold;
+        R.result[4] = c.ok ? 0.f : 1.f;
+    }
+    // ---- Optimizer::updateDist (OptimizerAux.cpp:162-188) on the own rows; the new distances of the halo rows go to the peers
+    const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
+    const bool apply = c.ok && (!A.only_on_success || err <= tol);
+    double acc = 0.0;
+    for (int s = lo + ltid; s < hi; s += T) {
+        const int lin = R.lin[s];
+        float d = R.vol.dist[lin];
+        if (apply) {
+            const float x = V[17 * PS + s];
+            if (fabs((double)x) < A.thr) { d -= x; R.vol.dist[lin] = d; acc += 1.0; }
+        }
+        if (s >= R.inner_lo && s < R.inner_hi) continue;
+        for (int i = 0; i < R.nseg; ++i)
+            if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].dist[lin] = d;
+    }
+    xbar(c, 0.0, 0.0, s_buf);
+    // ---- Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records of the own slots
+    if (apply) {
+        for (int t = ltid; t < R.surf.nslots; t += T) {
+            const int s = __float_as_int(R.surf.rec2[t].w);
+            const int lin = __float_as_int(R.surf.rec3[t].w);
+            const float dist = __ldcg(R.vol.dist + lin);
+            const int pb = __float_as_int(R.surf.rec1[t].w);
+            float fd[3], nfd[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = R.surf.nbr_lin[(size_t)a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(R.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * A.vs_inv;
+            }
+            R.vol.gx[lin] = fd[0]; R.vol.gy[lin] = fd[1]; R.vol.gz[lin] = fd[2];
+            normalized3(fd, nfd);
+            R.surf.rec0[t] = make_float4(dist, nfd[0], nfd[1], nfd[2]);
+            R.surf.rec2[t] = make_float4(fd[0], fd[1], fd[2], __int_as_float(s));
+            R.surf.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
+        }
+    }
+    // ---- getNormalEnergy / getLaplacianEnergy (Optimizer.cpp:86-119) over the own rows, and the accepted-update count
+    double en = 0.0, el = 0.0;
+    if (A.want_reg) {
+        for (int s = lo + ltid; s < hi; s += T) {
+            const int lin = R.lin[s];
+            const float dist = __ldcg(R.vol.dist + lin);
+            const unsigned char pb = R.surf.pos[s];
+            const long long stride[3] = { 1, R.vol.dims[0], (long long)R.vol.dims[0] * R.vol.dims[1] };
+            float fd[3], d2[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = R.surf.nbr_lin[(size_t)a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(R.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * A.vs_inv;
+                const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+                const float d1 = (l1 < R.vol.N) ? __ldcg(R.vol.dist + l1) : dist;
+                const float d0 = (l0 >= 0) ? __ldcg(R.vol.dist + l0) : dist;
+                d2[a] = d1 + d0 - 2 * dist;
+            }
+            const float e = norm3(fd) - 1;
+            en += (double)(e * e);
+            const float lap = (d2[0] + d2[1] + d2[2]) * A.vs_inv * A.vs_inv;
+            el += (double)(lap * lap);
+        }
+    }
+    {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        en = warp_sum(en); el = warp_sum(el); acc = warp_sum(acc);
+        if (lane == 0) { s_reg[warp][0] = en; s_reg[warp][1] = el; s_reg[warp][3] = acc; }
+        __syncthreads();
+        if (threadIdx.x < 4 && threadIdx.x != 2) {
+            double v = 0.0;
+            for (int i = 0; i < kMgBlock / 32; ++i) v += s_reg[i][threadIdx.x];
+            if (v != 0.0) atomicAdd(&R.regslot[threadIdx.x], v);
+        }
+    }
+    // ---- bookkeeping for the next launch (every block has left its last barrier: nothing reads these any more)
+    if (c.lb == 0 && threadIdx.x == 0) {
+        R.xs->arrive = 0ull;
+        R.xs->epoch = c.base + c.k;
+    }
+}
+
 // ---- regularised albedo block (reg albedo != 0) ------------------------------------------------------------------------
 // {Ps,Led}Optimizer::optimizeAlbedoAll with albedo_reg (PsOptimizer.cpp:85-121, LedOptimizer.cpp:162-196):
 //   H = J^T W J + (reg * Jr^T) * Jr,  b = J^T W r + (reg * Jr^T) * r_r,  H.diagonal() += damping * H.diagonal(),
@@ -1170,6 +1539,83 @@ void launch_dist_update(psg_optimizer* o, bool only_on_success) {
     PSG_LAUNCH_CHECK();
 }
 
+// ---- sharded job: the distance block after the sweep -------------------------------------------------------------------------
+static void fill_mg_rank(psg_optimizer* o, MgRank* R) {
+    memset(R, 0, sizeof(*R));
+    R->rank = o->rank; R->lo = o->row_lo; R->hi = o->row_hi;
+    int inner_lo = R->lo, inner_hi = R->hi, n = 0;
+    for (int q = 0; q < o->world; ++q) {
+        if (q == o->rank) continue;
+        // rows of mine below rank q's range that q needs (q's lower halo), and rows of mine above it (q's upper halo)
+        const int b0 = std::max(R->lo, o->halo_lo[q]), e0 = std::min(R->hi, o->row_bounds[q]);
+        if (e0 > b0) { R->seg[n].peer = q; R->seg[n].b = b0; R->seg[n].e = e0; ++n; if (q > o->rank) inner_hi = std::min(inner_hi, b0); else inner_lo = std::max(inner_lo, e0); }
+        const int b1 = std::max(R->lo, o->row_bounds[q + 1]), e1 = std::min(R->hi, o->halo_hi[q]);
+        if (e1 > b1) { R->seg[n].peer = q; R->seg[n].b = b1; R->seg[n].e = e1; ++n; if (q < o->rank) inner_lo = std::max(inner_lo, e1); else inner_hi = std::min(inner_hi, b1); }
+    }
+    R->nseg = n;
+    if (inner_lo > inner_hi) { inner_lo = R->lo; inner_hi = R->lo; }
+    R->inner_lo = inner_lo; R->inner_hi = inner_hi;
+    R->vecs = o->vecs.p; R->pbuf = o->pcg_pbuf.p; R->xs = reinterpret_cast<XState*>(o->xstate.p);
+    R->nbr_row = o->nbr_row.p; R->inc = o->inc.p; R->lin = o->lin.p;
+    R->vol = o->vol->view(); R->surf = surf_view(o);
+    R->partials = o->pcg_partials.p + 1;
+    R->result = reinterpret_cast<float*>(mail_dev(o) + 8 * kSlotPcg);
+    R->regslot = mail_dev(o) + 8 * kSlotReg;
+}
+
+struct MgLaunch { float damping; int only_on_success, want_reg; };
+
+static int mg_blocks_cap() {
+    static int cap = 0;
+    if (!cap) {
+        int per_sm = 0;
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_block_mg, kMgBlock, 0));
+        if (per_sm < 1) { set_error("distributed distance solve does not fit on an SM"); throw CudaError{-1}; }
+        cap = pcg_geometry().sms;   // one block per SM: the barriers cost more with more blocks than the rows gain
+    }
+    return cap;
+}
+
+static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const MgLaunch& L) {
+    MgArgs A;
+    memset(&A, 0, sizeof(A));
+    A.S = on->S; A.world = on->world; A.nplayed = nplayed;
+    for (int q = 0; q < on->world; ++q) A.peer[q] = on->peer[q];
+    int need = 1;
+    for (int i = 0; i < nplayed; ++i) { A.loc[i] = ranks[i]; need = std::max(need, (ranks[i].hi - ranks[i].lo + kMgBlock - 1) / kMgBlock); }
+    const int cap = std::max(1, mg_blocks_cap() / nplayed);
+    A.nb = std::min(need, cap);
+    if (A.nb > kPcgMaxBlocks / 2) A.nb = kPcgMaxBlocks / 2;
+    A.damping = L.damping; A.vs_inv = on->vs_inv; A.thr = sqrt(3.0) * (double)on->vs;
+    A.max_iters = 2 * on->S; A.only_on_success = L.only_on_success; A.want_reg = L.want_reg;
+    A.timeout_ns = 10ull * 1000ull * 1000ull * 1000ull;
+    on->mg_args.alloc(sizeof(MgArgs));
+    PSG_CUDA(cudaMemcpyAsync(on->mg_args.p, &A, sizeof(A), cudaMemcpyHostToDevice, on->stream));
+    const MgArgs* dev = reinterpret_cast<const MgArgs*>(on->mg_args.p);
+    void* args[] = { (void*)&dev };
+    Prof pf(on->stream, KID_PCG_SOLVE);
+    PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
+}
+
+static void mg_leader(psg_optimizer* on, void* const* args, int world, void* user) {
+    MgRank ranks[kMaxRanks];
+    for (int q = 0; q < world; ++q) ranks[q] = *static_cast<const MgRank*>(args[q]);
+    launch_mg(on, ranks, world, *static_cast<const MgLaunch*>(user));
+}
+
+void launch_dist_block_mg(psg_optimizer* o, float damping, bool only_on_success, bool want_reg) {
+    // verdict (identical on every rank), then the slot whose entries are partial sums over the rank's rows
+    PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotReg, 0, 24 * sizeof(double), o->stream));
+    o->reduce_reg = true;
+    if (o->S == 0) return;
+    MgRank R;
+    fill_mg_rank(o, &R);
+    MgLaunch L; L.damping = damping; L.only_on_success = only_on_success ? 1 : 0; L.want_reg = want_reg ? 1 : 0;
+    if (o->group) group_run(o, &R, mg_leader, &L);
+    else launch_mg(o, &R, 1, L);
+    o->vol_unsynced = true;
+}
+
 // regularised albedo block: the sweep left b = J^T W r in vecs[0 .. 3S) and the diagonal of J^T W J in vecs[3S .. 6S)
 void launch_albedo_reg_solve(psg_optimizer* o, float damping, bool only_on_success) {
     const int S = o->S;
@@ -1224,7 +1670,12 @@ void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* 
     const float tol = 1.1920929e-07f;
     *err = res[2] != 0.f ? sqrtf(res[1] / res[2]) : 0.f;
     *success = (*err <= tol) ? 1 : 0;   // IterativeSolverBase: info = error <= tolerance ? Success : NoConvergence
-    *accepted = (long long)*reinterpret_cast<const unsigned long long*>(mail_slot(o, kSlotCount));
+    if (o->sharded) {
+        if (res[4] != 0.f) { set_error("the distributed distance solve gave up waiting for a peer (10 s limit)"); throw CudaError{-1}; }
+        *accepted = (long long)(mail_slot(o, kSlotReg)[3] + 0.5);   // summed over the ranks by the flush
+    } else {
+        *accepted = (long long)*reinterpret_cast<const unsigned long long*>(mail_slot(o, kSlotCount));
+    }
 }
 
 }  // namespace psg

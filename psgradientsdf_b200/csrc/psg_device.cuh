@@ -39,7 +39,8 @@ struct __align__(16) FrameParams {
 struct FrameTable { FrameParams f[kMaxFrames]; };
 
 struct SurfView {
-    int S;                              // number of surface voxels
+    int S;                              // number of surface voxels (rows)
+    int nslots;                         // slots of this rank's sweep work list: S, or the rows it owns when the list is sharded
     const int* lin;                     // S   linear voxel index, ascending (Optimizer::surface_points_)
     const unsigned long long* vis;      // S   keyframe-indexed visibility (Optimizer::select_vis)
     const int* nbr_lin;                 // 3*S linear index of the finite-difference neighbour per axis (or -1)

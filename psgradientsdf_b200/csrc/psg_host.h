@@ -58,6 +58,31 @@ struct DevBuf {
 
 }  // namespace psg
 
+namespace psg {
+constexpr int kMaxRanks = 8;     // ranks of one sharded job (one 8-GPU NVSwitch box)
+
+// Per-rank synchronisation block of the distributed distance solve, in memory the peers can write (CUDA IPC mapping, or the
+// same address space when the ranks of a job live in one process).  Zeroed once when it is allocated; every counter is monotonic
+// across launches, so nothing is reset while a peer may still be writing.
+struct XState {
+    unsigned long long epoch;              // cross-rank barriers completed by earlier launches (written by the owner at the end of a launch)
+    unsigned long long arrive;             // arrivals of the owner's blocks at the current barrier (reset by the owner's leader block)
+    unsigned long long release;            // last barrier the owner's leader block has released to its own blocks
+    unsigned long long abort;              // sticky: a wait ran into its time limit
+    unsigned long long flag[kMaxRanks];    // flag[q]: last barrier rank q has signalled to the owner        (written by rank q)
+    double box[2][kMaxRanks][2];           // [barrier parity][sender]: the sender's two partial sums         (written by rank q)
+    double bcast[2][2];                    // totals of the current barrier, for the owner's other blocks
+};
+
+// what a rank exposes to its peers
+struct PeerView {
+    float* vecs = nullptr;      // normal-equation planes + PCG vectors, 25 planes of S rows (psg_optimizer::vecs)
+    float* pbuf = nullptr;      // double-buffered search direction, 2 x S
+    float* dist = nullptr;      // the volume's distance plane, N voxels
+    XState* xs = nullptr;
+};
+}  // namespace psg
+
 struct psg_volume {
     int device = 0;
     int dims[3] = {0, 0, 0};
@@ -121,19 +146,32 @@ struct psg_optimizer {
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps
     psg::DevBuf<unsigned> sweep_counter;     // arrival counter of the last-block reduction
-    void* comm = nullptr;                    // ncclComm_t when sharded over several GPUs
-    psg::DevBuf<float> comm_buf;             // all-gather staging: world chunks of packed per-slot results
+    void* comm = nullptr;                    // ncclComm_t: one process per GPU
+    void* group = nullptr;                   // psg::LocalGroup*: the ranks of the job live in this process (threads), see comm.cu
+    psg::DevBuf<float> comm_buf;             // staging of psg_opt_sync_volume: world chunks of packed rows
     int rank = 0, world = 1;
-    bool sharded = false;                    // the sweeps are split over the ranks (else every rank sweeps everything)
+    bool sharded = false;                    // every rank owns a contiguous row range of the surface list (a z-slab); else replicated
+    // row-range sharding (comm.cu): own rows [row_lo, row_hi) = the slots of this rank's sweeps; halo = rows of other ranks within
+    // one z-plane (W * H voxels) of the range, whose vector entries the peers push into this rank's copies
+    int row_lo = 0, row_hi = 0, n_slots = 0;
+    std::vector<int> row_bounds;             // world + 1 cut points (identical on every rank)
+    std::vector<int> halo_lo, halo_hi;       // per rank q: its halo rows are [halo_lo[q], row_bounds[q]) and [row_bounds[q+1], halo_hi[q])
+    bool layout_dirty = true;                // slot list / peer tables must be rebuilt (mode switch, new surface)
+    bool vol_unsynced = false;               // sharded: other ranks' rows of the volume planes are stale (psg_opt_sync_volume)
+    psg::DevBuf<unsigned char> xstate;       // psg::XState of this rank
+    psg::PeerView peer[psg::kMaxRanks];      // peer[q]: rank q's buffers as addressable from this process (peer[rank] = own)
+    std::vector<void*> ipc_opened;           // base pointers of the imported allocations (closed before anything is freed)
     int shard_policy = 0;                    // 0 = by work per rank, 1 = always, 2 = never
     long long vis_pairs = 0;                 // visible (surface voxel, keyframe) pairs of the current work list
     int reduce_lo = 1 << 30, reduce_hi = -1; // mail slots whose values are still per-rank partial sums
     size_t reduce_red = 0;                   // ... and how many doubles of o->red
+    bool reduce_reg = false;                 // ... and the regulariser / accepted-count slot (kSlotReg)
     int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors
     psg::DevBuf<double> pcg_partials;
     psg::DevBuf<float> pcg_pbuf;             // double-buffered search direction of the cluster PCG
+    psg::DevBuf<unsigned char> mg_args;      // argument block of the distributed distance solve (pcg.cu)
     psg::DevBuf<float> areg;                 // workspace of the regularised albedo solve (reg albedo != 0), 39 planes of S
     std::vector<double> lastH, lastb, lastdelta;   // small dense systems of the last step
     int last_n = 0, last_block = -1;
@@ -180,13 +218,18 @@ void launch_gather_voxels(psg_optimizer* o, float* out_dev);   // S x 8 floats (
 // ---- sweep.cu
 void refresh_frame_table(psg_optimizer* o);
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
-void comm_allreduce_doubles(psg_optimizer* o, double* a, size_t na, double* b, size_t nb);
+void comm_allreduce_doubles(psg_optimizer* o, double* const* ptr, const size_t* count, int n);   // in place, n <= 3 arrays in one step
 void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n);   // rank 0's values to every rank
 void update_shard_policy(psg_optimizer* o);
-float4* comm_pack_rho(psg_optimizer* o);                         // this rank's send chunk (written by the sweep)
-void comm_allgather_rho(psg_optimizer* o);                       // all-gather + scatter into rec1 / volume planes
-float* comm_pack_stencil(psg_optimizer* o, int* stride);         // this rank's send chunk: 14 planes of `stride` floats
-void comm_allgather_stencil(psg_optimizer* o, float* blocks);    // all-gather + scatter into 14 planes of S rows
+int comm_destroy(psg_optimizer* o, bool collective);
+// ranks as threads of one process: rendezvous of the members; `leader` runs once with every member's argument, on the last
+// arriver's stream, ordered after everything the members had queued; the members' streams continue after it
+void group_run(psg_optimizer* o, void* my_arg, void (*leader)(psg_optimizer* on, void* const* args, int world, void* user), void* user);
+void partition_rows(psg_optimizer* o);       // row_lo / row_hi / n_slots and the halo ranges of every rank
+void exchange_peers(psg_optimizer* o);       // sharded: fill o->peer[] (CUDA IPC between processes, plain pointers inside one); collective
+void build_layout(psg_optimizer* o);          // row ranges, slot list, records and (sharded) the peer tables; collective when sharded
+void release_peers(psg_optimizer* o);         // close the imported peer buffers before anything they map is freed; collective
+void sync_volume(psg_optimizer* o);           // sharded: every rank receives the other ranks' rows of the volume planes; collective
 void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active);
 void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active);
 void sweep_init_albedo(psg_optimizer* o);
@@ -212,6 +255,7 @@ bool write_mesh_file(psg_volume* v, float vs, const char* path, int white, long 
 bool write_sdf_file(psg_volume* v, float vs, const char* path, bool* any);
 
 // ---- pcg.cu
+void launch_dist_block_mg(psg_optimizer* o, float damping, bool only_on_success, bool want_reg);   // sharded: the whole distance block after the sweep, one kernel
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot);   // fused assemble + PCG + update (+ reg energies)
 void launch_dist_solve(psg_optimizer* o, float damping);              // assemble + PCG; verdict -> mail slot kSlotPcg
 void launch_dist_update(psg_optimizer* o, bool only_on_success);     // gated on the device by the PCG verdict; count -> kSlotCount

@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(256) k_gather_records(VolView v, const int* __
                                                        const unsigned char* __restrict__ pos, int S, float vs_inv, SurfView out,
                                                        unsigned long long* __restrict__ pvis) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S) return;
+    if (t >= out.nslots) return;
     const int s = perm[t];
     const int lin = lin_in[s];
     int idx[3];
@@ -249,16 +249,16 @@ __global__ void __launch_bounds__(256) k_gather_records(VolView v, const int* __
 
 static SurfView raw_view(psg_optimizer* o) {
     SurfView sv;
-    sv.S = o->S; sv.lin = o->lin.p; sv.vis = o->svis.p; sv.nbr_lin = o->nbr_lin.p; sv.nbr_row = o->nbr_row.p; sv.pos = o->pos.p;
+    sv.S = o->S; sv.nslots = o->n_slots; sv.lin = o->lin.p; sv.vis = o->svis.p; sv.nbr_lin = o->nbr_lin.p; sv.nbr_row = o->nbr_row.p; sv.pos = o->pos.p;
     sv.pvis = o->pvis.p;
     sv.rec0 = o->rec0.p; sv.rec1 = o->rec1.p; sv.rec2 = o->rec2.p; sv.rec3 = o->rec3.p; sv.rec4 = o->rec4.p;
     return sv;
 }
 
 void refresh_records(psg_optimizer* o) {
-    if (o->S > 0) {
+    if (o->n_slots > 0) {
         { Prof pf(o->stream, KID_SURF_NEIGHBORS);
-          k_gather_records<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), o->perm.p, o->lin.p, o->svis.p, o->nbr_lin.p,
+          k_gather_records<<<(o->n_slots + 255) / 256, 256, 0, o->stream>>>(o->vol->view(), o->perm.p, o->lin.p, o->svis.p, o->nbr_lin.p,
                                                                       o->pos.p, o->S, o->vs_inv, raw_view(o), o->pvis.p); }
         PSG_LAUNCH_CHECK();
     }
@@ -266,6 +266,7 @@ void refresh_records(psg_optimizer* o) {
 }
 
 SurfView surf_view(psg_optimizer* o) {
+    if (o->layout_dirty) build_layout(o);
     if (o->vol_gen_seen != o->vol->generation) refresh_records(o);
     return raw_view(o);
 }
@@ -273,12 +274,12 @@ SurfView surf_view(psg_optimizer* o) {
 // sort key of a row: (64 - number of visible keyframes) above the visibility word, so that rows with equal masks are
 // adjacent and the rows with most work come first (no heavy blocks left for the tail of the launch)
 __global__ void __launch_bounds__(256) k_sort_keys(const unsigned long long* __restrict__ vis, unsigned long long* __restrict__ keys,
-                                                  int* __restrict__ vals, int n, int F) {
+                                                  int* __restrict__ vals, int row0, int n, int F) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const unsigned long long m = vis[i];
+    const unsigned long long m = vis[row0 + i];
     keys[i] = (F <= 57) ? (((unsigned long long)(64 - __popcll(m)) << F) | m) : m;
-    vals[i] = i;
+    vals[i] = row0 + i;
 }
 
 // number of visible (surface voxel, keyframe) pairs: the size of a sweep, used to decide whether sharding it pays
@@ -337,21 +338,6 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
                                                                  o->nbr_row.p, o->pos.p, o->inc.p); }
         PSG_LAUNCH_CHECK();
     }
-    if (o->S > 0) {
-        // slot order: stable radix sort of the rows by keyframe-visibility word (set-up time only; CUB library sort)
-        o->sort_keys2.alloc((size_t)o->S);
-        k_sort_keys<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->sort_keys.p, o->sort_vals.p, o->S, o->F);
-        PSG_LAUNCH_CHECK();
-        const int end_bit = o->F <= 57 ? o->F + 7 : 64;
-        size_t tmp_bytes = 0;
-        PSG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p, o->S,
-                                                 0, end_bit, o->stream));
-        o->sort_tmp.alloc(tmp_bytes);
-        PSG_CUDA(cub::DeviceRadixSort::SortPairs(o->sort_tmp.p, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p,
-                                                 o->S, 0, end_bit, o->stream));
-        count_launch(4);
-    }
-    refresh_records(o);
     o->vis_pairs = 0;
     if (o->S > 0) {
         unsigned long long* cnt = reinterpret_cast<unsigned long long*>(o->sort_keys.p);   // free again after the sort
@@ -364,6 +350,35 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
         PSG_CUDA(cudaStreamSynchronize(o->stream));
         o->vis_pairs = (long long)h;
     }
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
+    update_shard_policy(o);
+    o->layout_dirty = true;
+    build_layout(o);
+}
+
+// Everything that depends on how the rows are divided among the ranks: the row range this rank owns (all rows unless the
+// work list is sharded), its slot list = its rows in sweep order (stable radix sort by keyframe visibility), the slot records,
+// the buffers an outer iteration uses, and -- sharded -- the peers' views of each other's buffers.  Collective when sharded.
+void build_layout(psg_optimizer* o) {
+    o->layout_dirty = false;
+    release_peers(o);                 // nothing below may reallocate a buffer a peer still maps
+    partition_rows(o);                // row_lo / row_hi / n_slots, halo ranges (comm.cu); whole list when not sharded
+    if (o->n_slots > 0) {
+        // slot order: stable radix sort of the rows by keyframe-visibility word (set-up time only; CUB library sort)
+        const int n = o->n_slots;
+        o->sort_keys2.alloc((size_t)n);
+        k_sort_keys<<<(n + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->sort_keys.p, o->sort_vals.p, o->row_lo, n, o->F);
+        PSG_LAUNCH_CHECK();
+        const int end_bit = o->F <= 57 ? o->F + 7 : 64;
+        size_t tmp_bytes = 0;
+        PSG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p, n,
+                                                 0, end_bit, o->stream));
+        o->sort_tmp.alloc(tmp_bytes);
+        PSG_CUDA(cub::DeviceRadixSort::SortPairs(o->sort_tmp.p, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p,
+                                                 n, 0, end_bit, o->stream));
+        count_launch(4);
+    }
+    refresh_records(o);
     // everything the blocks of an outer iteration use is sized here, once per work list, so that the iteration path itself
     // never allocates (DevBuf::alloc is a no-op once sized; growing it frees and reallocates, which synchronises the device)
     {
@@ -380,7 +395,7 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
         }
     }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
-    update_shard_policy(o);
+    exchange_peers(o);                // sharded: map the peers' buffers (CUDA IPC), or take their pointers inside one process
 }
 
 void launch_upsample(psg_optimizer* o) {

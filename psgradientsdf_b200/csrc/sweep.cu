@@ -33,9 +33,7 @@ struct SweepArgs {
     LossParams loss;
     const float4* images;
     int F;
-    // multi-GPU: updated albedo records / distance stencil blocks of this rank's slots, packed by local slot for the all-gather
-    float4* pack_rho; float* pack_out; int pack_stride;
-    int blk_first, blk_stride, blk_count;   // this rank's 32-slot blocks of the work list: blk_first + i * blk_stride, i < blk_count
+    int blk_first, blk_stride, blk_count;   // 32-slot blocks of the work list this launch walks: blk_first + i * blk_stride, i < blk_count
     float vs_inv;
     float led[3];
     float damping, reg_n, reg_l;
@@ -231,7 +229,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int S = A.surf.S;
     const int slot = (A.blk_first + (int)blockIdx.x * A.blk_stride) * 32 + lane;   // position in the visibility-sorted work list
-    const bool live = slot < S;
+    const bool live = slot < A.surf.nslots;
 
     // ---- voxel record (five coalesced 128-bit loads; everything per-voxel is precomputed by k_gather_records)
     int lin = 0, s = 0;
@@ -239,7 +237,6 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     float dist = 0.f, gh[3] = {0, 0, 0}, rho[3] = {0, 0, 0}, q0[3] = {0, 0, 0};
     float fd[3] = {0, 0, 0}, posf[3] = {1, 1, 1}, nfd[3] = {0, 0, 0};
     float rec1w = 0.f;
-    const int local = (int)blockIdx.x * 32 + lane;   // index among this rank's slots
     if (live) {
         vis = A.surf.pvis[slot];
         const float4 r0 = A.surf.rec0[slot], r1 = A.surf.rec1[slot], r2 = A.surf.rec2[slot], r3 = A.surf.rec3[slot],
@@ -634,7 +631,6 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
             A.surf.rec1[slot] = make_float4(nr, ng, nbl, rec1w);
             rho[0] = nr; rho[1] = ng; rho[2] = nbl;
         }
-        if (A.pack_rho && warp == 0 && live) A.pack_rho[local] = make_float4(rho[0], rho[1], rho[2], rec1w);
     }
     if constexpr (MODE == M_ALBEDO) {
         // H.diagonal() += damping * H.diagonal(); Jacobi-preconditioned CG on a diagonal system = b * (1 / H);
@@ -656,7 +652,6 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                 if (A.out0) { A.out0[3 * (long long)s + c] = vacc[3 + c]; A.out1[3 * (long long)s + c] = delta; }
             }
             if (accepted) A.surf.rec1[slot] = make_float4(rho[0], rho[1], rho[2], rec1w);
-            if (A.pack_rho) A.pack_rho[local] = make_float4(rho[0], rho[1], rho[2], rec1w);
         }
     }
     if constexpr (MODE == M_DIST) {
@@ -709,13 +704,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                 vacc[0] += A.reg_l * (jd * jd);
                 vacc[10] += A.reg_l * (jd * lap);
             }
-            if (A.pack_out) {
 #pragma unroll
-                for (int i = 0; i < 14; ++i) A.pack_out[(long long)i * A.pack_stride + local] = vacc[i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
-            }
+            for (int i = 0; i < 14; ++i) A.out0[(long long)i * S + s] = vacc[i];
         }
     }
     // (b) scalar sums: warp -> block (warp order) -> grid (fixed order, last block): [0..5] mode specific, [6] loss, [7] pairs
@@ -755,7 +745,7 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
     A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
     A.images = o->images.p; A.F = o->F;
-    shard_blocks(o->S, o->sharded ? o->rank : 0, o->sharded ? o->world : 1, &A.blk_first, &A.blk_stride, &A.blk_count);
+    shard_blocks(A.surf.nslots, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // a sharded rank's slot list holds its own rows only
     A.vs_inv = o->vs_inv;
     if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
@@ -837,16 +827,21 @@ double* red_dev(psg_optimizer* o) { return o->red.p + kMailDoubles; }
 const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
-    if (o->world > 1 && o->reduce_hi >= o->reduce_lo) {
+    if (o->world > 1 && (o->reduce_hi >= o->reduce_lo || o->reduce_reg)) {
         if (o->sharded) {
-            // one all-reduce for everything queued since the last round trip: per-keyframe sums + the scalar slots in flight
-            comm_allreduce_doubles(o, red_dev(o), o->reduce_red, mail_dev(o) + 8 * o->reduce_lo, (size_t)8 * (o->reduce_hi - o->reduce_lo + 1));
+            // one all-reduce for everything queued since the last round trip: per-keyframe sums, the scalar slots in flight and
+            // the regulariser energies / accepted-update count of the distance block (partial sums over each rank's rows)
+            double* ptr[3]; size_t cnt[3]; int k = 0;
+            if (o->reduce_red) { ptr[k] = red_dev(o); cnt[k++] = o->reduce_red; }
+            if (o->reduce_hi >= o->reduce_lo) { ptr[k] = mail_dev(o) + 8 * o->reduce_lo; cnt[k++] = (size_t)8 * (o->reduce_hi - o->reduce_lo + 1); }
+            if (o->reduce_reg) { ptr[k] = mail_dev(o) + 8 * kSlotReg; cnt[k++] = 8; }
+            comm_allreduce_doubles(o, ptr, cnt, k);
         } else {
             // replicated sweeps: every rank holds complete sums, equal up to the order of the fp64 atomics; rank 0's copy
             // becomes everybody's, so that the host solves that follow are identical on all ranks
             comm_broadcast_doubles(o, o->red.p, kMailDoubles + o->reduce_red);
         }
-        o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0;
+        o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0; o->reduce_reg = false;
     }
     PSG_CUDA(cudaMemcpyAsync(h, o->red.p, (kMailDoubles + n) * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -883,7 +878,7 @@ void sweep_energy(psg_optimizer* o, double* E_sum, long long* n_active) {
 
 void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, long long* n_active) {
     SweepArgs A = base_args(o);
-    shard_blocks(o->S, rank, world, &A.blk_first, &A.blk_stride, &A.blk_count);
+    shard_blocks(A.surf.nslots, rank, world, &A.blk_first, &A.blk_stride, &A.blk_count);
     PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));   // an empty range launches nothing
     launch_sweep<M_ENERGY>(o, A, 0, 0);
     fetch_red(o, 0, /*reduce_over_ranks=*/false);
@@ -893,9 +888,8 @@ void sweep_energy_partial(psg_optimizer* o, int rank, int world, double* sum, lo
 
 void sweep_init_albedo(psg_optimizer* o) {
     SweepArgs A = base_args(o);
-    if (o->sharded) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_INIT_ALBEDO>(o, A, 0, 0);
-    if (o->sharded) comm_allgather_rho(o);
+    if (o->sharded) o->vol_unsynced = true;   // other ranks' rows of the albedo planes are theirs to write
 }
 
 void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
@@ -908,17 +902,15 @@ void sweep_led_light_init(psg_optimizer* o, double sums[6]) {
 void sweep_probe(psg_optimizer* o, float* m, float* n, unsigned char* ok, float* I3, float* rend3, float* r3, float* w3) {
     SweepArgs A = base_args(o);
     A.pm = m; A.pn = n; A.pok = ok; A.pI = I3; A.prend = rend3; A.pr = r3; A.pw = w3;
-    shard_blocks(o->S, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // diagnostic: every rank probes all pairs
-    launch_sweep<M_PROBE>(o, A, 0, 0);
+    launch_sweep<M_PROBE>(o, A, 0, 0);   // a sharded rank probes the pairs of its own rows
 }
 
 void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot, bool regularised) {
     SweepArgs A = base_args(o, slot);
     A.damping = damping; A.out0 = b_dev; A.out1 = delta_dev;
     if (regularised) A.flags = PSG_REG_ALBEDO;   // out0 = J^T W r, out1 = diagonal of J^T W J, no update
-    if (o->sharded) A.pack_rho = comm_pack_rho(o);
     launch_sweep<M_ALBEDO>(o, A, 0, 0);
-    if (o->sharded) comm_allgather_rho(o);
+    if (o->sharded) o->vol_unsynced = true;
     reduce_over_ranks(o, 0, slot);
 }
 
@@ -974,9 +966,7 @@ void launch_dist_sweep(psg_optimizer* o, int flags, int slot) {
     A.flags = flags;
     o->vecs.alloc((size_t)(o->S > 0 ? o->S : 1) * 25 + 8);
     A.out0 = o->vecs.p;   // planes 0..13: stencil normal equations
-    if (o->sharded) A.pack_out = comm_pack_stencil(o, &A.pack_stride);
-    launch_sweep<M_DIST>(o, A, 0, 0);
-    if (o->sharded) comm_allgather_stencil(o, o->vecs.p);   // every rank ends with all rows
+    launch_sweep<M_DIST>(o, A, 0, 0);   // sharded: the stencil blocks of the rows this rank owns, consumed where they are produced
     reduce_over_ranks(o, 0, slot);
 }
 
@@ -987,13 +977,13 @@ void launch_energy(psg_optimizer* o, int slot) {
 }
 
 // ---- regulariser energies (Optimizer.cpp:86-136) -------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_reg_energy(VolView vol, SurfView surf, float vs_inv, double* red) {
+__global__ void __launch_bounds__(kBlock) k_reg_energy(VolView vol, SurfView surf, float vs_inv, double* red, int row0, int row1) {
     __shared__ double s_red[kWarps][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = surf.S;
-    const int s = blockIdx.x * kBlock + tid;
+    const int s = row0 + blockIdx.x * kBlock + tid;
     double en = 0.0, el = 0.0, er = 0.0;
-    if (s < S) {
+    if (s < row1) {
         const int lin = surf.lin[s];
         const float dist = vol.dist[lin];
         const float rho[3] = { vol.r[lin], vol.g[lin], vol.b[lin] };
@@ -1032,16 +1022,19 @@ __global__ void __launch_bounds__(kBlock) k_reg_energy(VolView vol, SurfView sur
 }
 
 void launch_reg_energies(psg_optimizer* o, int slot) {
-    SweepArgs A = base_args(o, slot);   // every rank evaluates all rows: nothing to combine
+    SweepArgs A = base_args(o, slot);   // replicated: every rank evaluates all rows; sharded: its own rows, summed with the next flush
     PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
-    if (o->S > 0) {
-        { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(o->S + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.scal); }
+    const int r0 = o->sharded ? o->row_lo : 0, r1 = o->sharded ? o->row_hi : o->S;
+    if (r1 > r0) {
+        { Prof pf(o->stream, KID_REG_ENERGY); k_reg_energy<<<(r1 - r0 + kBlock - 1) / kBlock, kBlock, 0, o->stream>>>(A.vol, A.surf, o->vs_inv, A.scal, r0, r1); }
         PSG_LAUNCH_CHECK();
     }
+    if (o->sharded) o->reduce_reg = true;
 }
 
 void reg_energies(psg_optimizer* o, double* En, double* El, double* Er) {
     launch_reg_energies(o, kSlotReg);
+    if (o->world > 1 && !o->sharded) reduce_over_ranks(o, 0, kSlotReg);   // replicated: rank 0's sums become everybody's
     fetch_mail(o, 0);
     const double* r = mail_slot(o, kSlotReg);
     *En = r[0]; *El = r[1]; *Er = r[2];
@@ -1126,18 +1119,18 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.cam.fx = o->K[0]; A.cam.fy = o->K[4]; A.cam.cx = o->K[2]; A.cam.cy = o->K[5]; A.cam.H = o->H; A.cam.W = o->W;
         A.loss.loss = o->set.loss; A.loss.lambda = o->set.lambda; A.loss.lambda_sq = o->set.lambda * o->set.lambda;
         A.images = o->images.p; A.F = o->F;
-        shard_blocks(o->S, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // always the whole work list (no communication on this path)
+        shard_blocks(A.surf.nslots, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // this rank's whole slot list (no communication on this path)
         A.vs_inv = o->vs_inv;
         if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
         A.red = sc->red; A.red_copies = 1; A.scal = sc->red; A.partials = sc->partials; A.counter = sc->counter;
 
-        const int grid = (o->S + 31) / 32;
+        const int grid = A.blk_count;
         int W = 1;
         while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
         if (o->sweep_split > 0) W = o->sweep_split;
         const size_t smem = W > 1 ? (size_t)W * 14 * 32 * sizeof(float) : 0;
-        switch (o->set.model) {
+        if (grid > 0) switch (o->set.model) {
             case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
             case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
             default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;

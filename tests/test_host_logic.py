@@ -61,6 +61,47 @@ def test_shard_blocks_tile_the_work_list():
             assert max(counts) - min(counts) <= 1
 
 
+def test_row_partition_covers_balances_and_haloes():
+    """psg_partition_rows (the z-slab split of a sharded job): the ranges tile the surface list, carry equal visible-pair counts,
+    and a rank's halo contains every row of another rank that its stencils can touch: the finite-difference neighbours (+-1, +-W,
+    +-W*H), the rows whose stencil contains one of its rows, and the 6-point Laplacian."""
+    import psgradientsdf_b200 as psg
+    rng = np.random.default_rng(5)
+    for G, S in ((16, 700), (32, 5000), (48, 20000)):
+        W = H = G
+        plane = W * H
+        # a shell-like surface: voxels near a sphere, so that slabs have ragged first / last planes
+        idx = np.arange(G ** 3)
+        i, j, k = idx % W, (idx // W) % H, idx // plane
+        r = np.sqrt((i - G / 2) ** 2 + (j - G / 2) ** 2 + (k - G / 2) ** 2)
+        cand = np.flatnonzero(np.abs(r - 0.35 * G) < 1.5)
+        lin = np.sort(rng.choice(cand, min(S, cand.size), replace=False)).astype(np.int32)
+        vis = rng.integers(1, 2 ** 30, lin.size).astype(np.uint64)
+        rowmap = -np.ones(G ** 3, np.int64); rowmap[lin] = np.arange(lin.size)
+        w = np.array([bin(int(v)).count("1") + 1 for v in vis], np.int64)
+        for world in (1, 2, 3, 8):
+            b, lo, hi = psg.partition_rows(lin, vis, plane, world)
+            assert b[0] == 0 and b[-1] == lin.size and np.all(np.diff(b) >= 0)
+            loads = np.array([w[b[q]:b[q + 1]].sum() for q in range(world)])
+            assert loads.max() - loads.min() <= 2 * w.max() + 1, (world, loads)
+            for q in range(world):
+                own = np.arange(b[q], b[q + 1])
+                assert lo[q] <= b[q] and hi[q] >= b[q + 1]
+                if own.size == 0:
+                    continue
+                for off in (1, -1, W, -W, plane, -plane):
+                    nl = lin[own].astype(np.int64) + off
+                    ok = (nl >= 0) & (nl < G ** 3)
+                    rows = rowmap[nl[ok]]
+                    rows = rows[rows >= 0]
+                    assert np.all((rows >= lo[q]) & (rows < hi[q])), (G, world, q, off)
+    # degenerate inputs: empty list, more ranks than rows
+    b, lo, hi = psg.partition_rows(np.zeros(0, np.int32), np.zeros(0, np.uint64), 64, 4)
+    assert list(b) == [0, 0, 0, 0, 0]
+    b, lo, hi = psg.partition_rows(np.array([3, 9], np.int32), np.array([1, 1], np.uint64), 64, 4)
+    assert b[0] == 0 and b[-1] == 2 and np.all(np.diff(b) >= 0)
+
+
 _WORKER = r'''
 import os, sys, torch, torch.distributed as dist
 dist.init_process_group("gloo")

@@ -1,4 +1,5 @@
-"""Run under torchrun with N >= 2 GPUs: the sharded optimizer (NCCL) against the single-GPU one on rank 0.
+"""Run under torchrun with N >= 2 GPUs: the multi-GPU optimizer (row-range sharding with the distributed distance solve over
+CUDA IPC peer memory + NCCL, or the replicated policy) against the single-GPU one on rank 0.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29600 tools/multi_gpu_check.py
 """
@@ -50,6 +51,8 @@ for it in range(2):
 log.append(opt.energy())
 it_info = opt.iteration(damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))   # the three-wait pass, sharded
 log.append((it_info["energy_end"], it_info["n_active_end"]))
+regs = (it_info["reg_normal_after_dist"], it_info["reg_laplacian_after_dist"])
+opt.sync_volume()        # sharded: every rank receives the others' rows
 state = vol.download()
 # all ranks must hold the same state
 h = torch.tensor(np.frombuffer(state.tobytes(), dtype=np.uint8).astype(np.int64).sum(), device=f"cuda:{local}")
@@ -71,11 +74,16 @@ if rank == 0:
     for a, b in zip(log, log1):
         assert a[1] == b[1], (a, b)
         worst = max(worst, abs(a[0] - b[0]) / abs(b[0]))
+        if len(a) == 3:
+            assert abs(a[2] - b[2]) <= 1, ("CG iterations", a, b)
+    for x, y in zip(regs, (it1["reg_normal_after_dist"], it1["reg_laplacian_after_dist"])):
+        assert abs(x - y) <= 1e-6 * abs(y) + 1e-12, (regs, it1)
     s1 = vol1.download()
     surf = opt1.surface()
     d_rms = float(np.sqrt(np.mean((state[surf, 0].astype(np.float64) - s1[surf, 0]) ** 2))) / vs
     a_rms = float(np.sqrt(np.mean((state[surf, 5:8].astype(np.float64) - s1[surf, 5:8]) ** 2)))
-    print(f"multi-gpu check: world={world} model={model} G={G} S={opt1.S} worst relative energy difference {worst:.3e}, "
+    print(f"multi-gpu check: world={world} model={model} G={G} S={opt1.S} sharded={opt.is_sharded()[0]} rows={opt.row_range()} "
+          f"worst relative energy difference {worst:.3e}, "
           f"final RMS distance {d_rms:.3e} voxels, albedo {a_rms:.3e}")
     assert worst < 5e-6 and d_rms < 1e-4 and a_rms < 1e-4
 dist.barrier()
