@@ -436,6 +436,8 @@ def run_ours(a):
     clocks = sampler.stop()
     prof, pinfo = profiled_steps(job, a.steps, flush, sync, peak)
     pcg_iters = int(pinfo.block[2].cg_iterations)
+    pcg_kernel = {0: "general cooperative grid", 1: "8-CTA cluster", 2: "fused grid kernel", 3: "16-CTA cluster, vectors in distributed shared memory",
+                  4: "distributed (sharded job)"}.get(go.last_pcg_kernel(), "?")
     t_max = allmax(t_dev)
     t_wall_max = allmax(t_wall)
     value = A_job * SWEEPS_PER_STEP * a.steps / t_max      # whole job: the shared list once, or the sum of the ranks' own lists
@@ -594,7 +596,7 @@ def run_ours(a):
             cpu["port"] = port
 
     config = {"workload": workload_name(a), "surface_voxels": S_job, "active_pairs": A_job, "keyframes": F,
-              "sweeps_per_step": SWEEPS_PER_STEP, "pcg_iterations": pcg_iters, "energy_after_last_step": energy_end,
+              "sweeps_per_step": SWEEPS_PER_STEP, "pcg_iterations": pcg_iters, "distance_solve_kernel": pcg_kernel, "energy_after_last_step": energy_end,
               "timing": "CUDA events on the library's stream around each step (psg_debug_timer_*), max over ranks; host wall "
                         "clock per step in host_ms_per_step",
               "l2": "flushed between steps (256 MiB device write)",

@@ -758,6 +758,12 @@ class Optimizer:
     def upsample(self):
         _check(lib().psg_opt_upsample(self.h))
 
+    def last_pcg_kernel(self) -> int:
+        k = C.c_int()
+        lib().psg_debug_last_pcg_kernel.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        _check(lib().psg_debug_last_pcg_kernel(self.h, C.byref(k)))
+        return k.value
+
     def timer_begin(self):
         """CUDA event on the optimizer's stream (psg_debug_timer_begin)."""
         _check(lib().psg_debug_timer_begin(self.h))

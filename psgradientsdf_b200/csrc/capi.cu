@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include <atomic>
+#include <mutex>
 
 #include "host_solve.h"
 #include "psg_host.h"
@@ -35,6 +36,7 @@ static std::vector<ProfRec> g_prof_recs;
 static long long g_prof_count[KID_COUNT] = {0};
 static double g_prof_ms[KID_COUNT] = {0};
 
+static std::mutex g_prof_mutex;                 // ranks as threads of one process (comm.cu) launch concurrently
 static std::vector<cudaEvent_t> g_event_pool;   // events are recycled: creating two per launch costs more than the launch
 static cudaEvent_t pool_get() {
     if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
@@ -45,14 +47,15 @@ static cudaEvent_t pool_get() {
 Prof::Prof(cudaStream_t stream, int kernel_id) : st(stream), id(kernel_id) {
     if (kernel_id != KID_COMM_ALLREDUCE && kernel_id != KID_COMM_ALLGATHER) g_launches += 1;   // NCCL's kernels are not ours
     if (g_prof_on) {
-        e0 = pool_get(); e1 = pool_get();
+        { std::lock_guard<std::mutex> lk(g_prof_mutex); e0 = pool_get(); e1 = pool_get(); }
         cudaEventRecord(e0, st);
     }
 }
 Prof::~Prof() {
-    if (e0) { cudaEventRecord(e1, st); g_prof_recs.push_back({id, e0, e1}); }
+    if (e0) { cudaEventRecord(e1, st); std::lock_guard<std::mutex> lk(g_prof_mutex); g_prof_recs.push_back({id, e0, e1}); }
 }
 static void prof_collect() {
+    std::lock_guard<std::mutex> lk(g_prof_mutex);
     for (const ProfRec& r : g_prof_recs) {
         float ms = 0.f;
         if (cudaEventSynchronize(r.e1) == cudaSuccess && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
@@ -594,7 +597,7 @@ int psg_opt_set_upload_overlap(psg_optimizer* o, int on) {
 
 int psg_opt_set_pcg_mode(psg_optimizer* o, int mode) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
-    if (mode < 0 || mode > 5) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 5", mode); return PSG_ERR_INVALID; }
+    if (mode < 0 || mode > 7) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 7", mode); return PSG_ERR_INVALID; }
     o->pcg_mode = mode;
     return PSG_OK;
 }
@@ -943,6 +946,12 @@ int psg_debug_host_times(double us[3], long long* iterations, int reset) {
     if (us) for (int i = 0; i < 3; ++i) us[i] = g_host_us[i];
     if (iterations) *iterations = g_host_iterations;
     if (reset) { g_host_us[0] = g_host_us[1] = g_host_us[2] = 0.0; g_host_iterations = 0; }
+    return PSG_OK;
+}
+
+int psg_debug_last_pcg_kernel(const psg_optimizer* o, int* kernel) {
+    if (!o || !kernel) { set_error("null argument"); return PSG_ERR_INVALID; }
+    *kernel = o->last_pcg_kernel;
     return PSG_OK;
 }
 

@@ -13,10 +13,11 @@
 //   * energy / counters and the per-keyframe light (4x4 / 9x9) and pose (6x6) normal equations: one NCCL all-reduce of <= 4104
 //     doubles per host round trip (fetch_mail);
 //   * the one-voxel halo: entries of z, p and the stencil products of the rows within one z-plane (W H voxels) of a cut, pushed by
-//     their owner into the neighbour's copy of the vector with plain stores over NVLink inside the persistent solve kernel
-//     (pcg.cu, k_dist_block_mg), and the updated distances of those rows after the solve;
-//   * two scalars per CG reduction, exchanged through the peers' XState mailboxes by the same kernel (a flag barrier over
-//     NVLink, no NCCL call inside the solve).
+//     their owner into the neighbour's halo buffer over NVLink inside the persistent solve kernel (pcg.cu, k_dist_block_mg) as
+//     8-byte (value, tag) packets -- the reader spins on the tag, so no fence and no barrier is needed for them -- and the
+//     updated distances of those rows after the solve;
+//   * two scalars per CG reduction, exchanged as tagged packets through the peers' XState mailboxes by the same kernel (no NCCL
+//     call inside the solve).
 // Every rank still holds the whole (fused) volume; only the rows it owns stay current between psg_opt_sync_volume calls, plus
 // the distance plane of its halo.
 //
@@ -292,7 +293,7 @@ void partition_rows(psg_optimizer* o) {
 
 // ---- peers' views of each other's buffers ----------------------------------------------------------------------------------
 struct IpcRecord { cudaIpcMemHandle_t h; unsigned long long offset; };
-struct IpcPacket { IpcRecord vecs, pbuf, dist, xs; };
+struct IpcPacket { IpcRecord halo, xs; };
 
 typedef int (*cuMemGetAddressRange_t)(unsigned long long*, size_t*, unsigned long long);
 static cuMemGetAddressRange_t address_range_fn() {
@@ -333,7 +334,7 @@ static void* ipc_import(psg_optimizer* o, IpcCache& cache, const IpcRecord& r) {
 
 void release_peers(psg_optimizer* o) {
     bool had = false;
-    for (int q = 0; q < kMaxRanks; ++q) { if (o->peer[q].vecs && q != o->rank) had = true; o->peer[q] = PeerView(); }
+    for (int q = 0; q < kMaxRanks; ++q) { if (o->peer[q].xs && q != o->rank) had = true; o->peer[q] = PeerView(); }
     if (!o->ipc_opened.empty()) {
         PSG_CUDA(cudaStreamSynchronize(o->stream));
         for (void* b : o->ipc_opened) cudaIpcCloseMemHandle(b);
@@ -352,8 +353,14 @@ void exchange_peers(psg_optimizer* o) {
         PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, sizeof(XState), o->stream));
         PSG_CUDA(cudaStreamSynchronize(o->stream));
     }
+    // halo packets of this rank: one per halo row and kind, tags start at zero (= never written)
+    const int nh = (o->row_lo - o->halo_lo[o->rank]) + (o->halo_hi[o->rank] - o->row_hi);
+    const size_t hcount = (size_t)kHaloKinds * (size_t)(nh > 0 ? nh : 1);
+    if (o->halo.n < hcount) o->halo.alloc(hcount);
+    PSG_CUDA(cudaMemsetAsync(o->halo.p, 0, o->halo.n * sizeof(unsigned long long), o->stream));
+    PSG_CUDA(cudaStreamSynchronize(o->stream));
     PeerView mine;
-    mine.vecs = o->vecs.p; mine.pbuf = o->pcg_pbuf.p; mine.dist = o->vol->f[0].p; mine.xs = reinterpret_cast<XState*>(o->xstate.p);
+    mine.halo = o->halo.p; mine.xs = reinterpret_cast<XState*>(o->xstate.p);
     if (o->group) {
         // same address space: take the members' pointers (the rendezvous doubles as the barrier after allocation)
         group_collective(o, &mine, [&](LocalGroup* g) { for (int q = 0; q < g->world; ++q) g->views[q] = *static_cast<PeerView*>(g->arg[q]); });
@@ -364,7 +371,7 @@ void exchange_peers(psg_optimizer* o) {
     }
     // processes: all-gather the IPC handles through NCCL, then map
     IpcPacket pk;
-    pk.vecs = ipc_export(mine.vecs); pk.pbuf = ipc_export(mine.pbuf); pk.dist = ipc_export(mine.dist); pk.xs = ipc_export(mine.xs);
+    pk.halo = ipc_export(mine.halo); pk.xs = ipc_export(mine.xs);
     DevBuf<unsigned char> buf;
     buf.alloc(sizeof(IpcPacket) * (size_t)o->world);
     PSG_CUDA(cudaMemcpyAsync(buf.p + sizeof(IpcPacket) * (size_t)o->rank, &pk, sizeof(pk), cudaMemcpyHostToDevice, o->stream));
@@ -377,9 +384,7 @@ void exchange_peers(psg_optimizer* o) {
     IpcCache cache;
     for (int q = 0; q < o->world; ++q) {
         if (q == o->rank) { o->peer[q] = mine; continue; }
-        o->peer[q].vecs = static_cast<float*>(ipc_import(o, cache, all[q].vecs));
-        o->peer[q].pbuf = static_cast<float*>(ipc_import(o, cache, all[q].pbuf));
-        o->peer[q].dist = static_cast<float*>(ipc_import(o, cache, all[q].dist));
+        o->peer[q].halo = static_cast<unsigned long long*>(ipc_import(o, cache, all[q].halo));
         o->peer[q].xs = static_cast<XState*>(ipc_import(o, cache, all[q].xs));
     }
     comm_barrier(o);   // every rank has mapped everything before anyone launches a kernel that writes to a peer

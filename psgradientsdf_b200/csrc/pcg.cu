@@ -574,6 +574,319 @@ __global__ void __launch_bounds__(BS, (BS >= 1024) ? 1 : (BS >= 512) ? 2 : 4) k_
     }
 }
 
+// ---- surfaces of at most 32 768 rows: the whole distance block inside ONE 16-CTA cluster, vectors in distributed shared memory --
+// The fused grid kernel above is a chain of grid barriers (~2 us each through L2, three per CG iteration) around a few hundred
+// nanoseconds of arithmetic.  A thread-block cluster has a hardware barrier (barrier.cluster, ~0.2 us) and can read its peers'
+// shared memory directly, so here: 16 CTAs x 1024 threads on 16 SMs of one GPC (non-portable cluster size), RPT <= 2 rows per
+// thread (row = cta * RPC + j * 1024 + tid, RPC = 1024 RPT).  Everything the solve re-reads lives on chip: a row's stencil block
+// and incidence addresses in its CTA's shared memory, x / r / p / z / 1/diag in registers, and what OTHER rows read -- z, p
+// (double-buffered) and the stencil products U1..U3 -- in shared-memory planes that neighbours gather with ld.shared::cluster
+// (a neighbour row's CTA and offset are fixed for the whole solve: mapped once, kept as 32-bit cluster addresses).  Dot products:
+// every CTA writes its two partial sums into a slot of EVERY CTA's shared memory before the phase's barrier and adds the 16
+// slots in slot order after it, so all CTAs hold the same bits and take the same branches.  Assembly (k_dist_assemble) is the
+// prologue; Optimizer::updateDist, updateGrad, the record refresh and the regulariser energies are the epilogue, as in
+// k_dist_solve_small.  Global memory is touched only by prologue and epilogue.
+constexpr int kClNC = 16, kClBS = 1024;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned mapa_u32(unsigned addr, unsigned cta) {
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ float ld_dsmem(unsigned addr) {
+    float v;
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_dsmem_f64(unsigned addr, double v) { asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory"); }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// per-CTA partials -> every CTA, then (after the caller's cluster barrier) the totals in slot order
+template <int RPT>
+struct ClSmem {
+    static constexpr int RPC = 1024 * RPT;
+    float Ab[10][RPC];          // stencil block of the CTA's rows
+    unsigned taddr[6][RPC];     // cluster address of plane U1's entry of each incident row (0 = none)
+    float z[RPC];               // published z = r / diag
+    float p[2][RPC];            // search direction, double-buffered
+    float U[3][RPC];            // stencil products of slots 1..3
+    double slot[2][kClNC][2];   // [parity][sender CTA][value]
+    double red[2 * 32];
+};
+
+template <int RPT>
+__device__ __forceinline__ void cl_post(ClSmem<RPT>& sm, int par, unsigned cta, double a, double b) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
+    __syncthreads();
+    if (warp == 0) {
+        double ta = sm.red[lane], tb = sm.red[32 + lane];
+        ta = warp_sum(ta); tb = warp_sum(tb);
+        if (lane < kClNC) {
+            const unsigned dst = mapa_u32(smem_u32(&sm.slot[par][cta][0]), (unsigned)lane);
+            st_dsmem_f64(dst, ta); st_dsmem_f64(dst + 8, tb);
+        }
+    }
+}
+template <int RPT>
+__device__ __forceinline__ double2 cl_total(const ClSmem<RPT>& sm, int par) {
+    double a = 0.0, b = 0.0;
+#pragma unroll
+    for (int q = 0; q < kClNC; ++q) { a += sm.slot[par][q][0]; b += sm.slot[par][q][1]; }
+    return make_double2(a, b);
+}
+
+template <int RPT>
+__global__ void __launch_bounds__(kClBS, 1) k_dist_solve_cluster16(SolveSmallArgs G) {
+    extern __shared__ __align__(16) unsigned char cl_raw[];
+    ClSmem<RPT>& sm = *reinterpret_cast<ClSmem<RPT>*>(cl_raw);
+    constexpr int RPC = ClSmem<RPT>::RPC;
+    constexpr int LOG_RPC = (RPT == 1) ? 10 : 11;
+    const PcgArgs& A = G.A;
+    const int S = A.S, tid = threadIdx.x;
+    unsigned cta;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
+    const unsigned z0 = smem_u32(&sm.z[0]);
+    constexpr unsigned kP0 = (unsigned)(sizeof(float) * RPC);              // z -> p[0]
+    constexpr unsigned kU = (unsigned)(sizeof(float) * RPC * 3);           // z -> U[0]
+
+    // ---- prologue: assemble the rows (k_dist_assemble), stage what the solve re-reads
+    int row[RPT]; bool in[RPT];
+    unsigned naddr[RPT][3];      // cluster address of z of the finite-difference neighbour per axis (0 = not a surface voxel)
+    float invd[RPT], dd[RPT], x[RPT], r[RPT], z[RPT], p[RPT], u0[RPT], y[RPT];
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < RPT; ++j) {
+        const int li = j * kClBS + tid;
+        row[j] = (int)cta * RPC + li;
+        in[j] = row[j] < S;
+        invd[j] = 0.f; dd[j] = 0.f; x[j] = 0.f; r[j] = 0.f; z[j] = 0.f; p[j] = 0.f; u0[j] = 0.f; y[j] = 0.f;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) naddr[j][a] = 0u;
+#pragma unroll
+        for (int h = 0; h < 6; ++h) sm.taddr[h][li] = 0u;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) sm.Ab[i][li] = 0.f;
+        sm.z[li] = 0.f; sm.p[0][li] = 0.f; sm.p[1][li] = 0.f; sm.U[0][li] = 0.f; sm.U[1][li] = 0.f; sm.U[2][li] = 0.f;
+        if (!in[j]) continue;
+        const int s = row[j];
+        float rhs = __ldg(A.blk + (long long)10 * S + s);
+        float diag = 0.f;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) { const float v = __ldg(A.blk + (long long)i * S + s); sm.Ab[i][li] = v; if (i == 0) diag = v; }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int c = __ldg(A.nbr_row + a * S + s);
+            if (c >= 0) naddr[j][a] = mapa_u32(z0 + 4u * (unsigned)(c & (RPC - 1)), (unsigned)(c >> LOG_RPC));
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = __ldg(A.inc + (h * 3 + a) * S + s);
+                if (t >= 0) {
+                    rhs += __ldg(A.blk + (long long)(10 + a + 1) * S + t);
+                    diag += __ldg(A.blk + (long long)tri(a + 1, a + 1) * S + t);
+                    // U plane a of row t: where phase 2 gathers the product of t's slot a + 1
+                    sm.taddr[h * 3 + a][li] = mapa_u32(z0 + kU + (unsigned)(sizeof(float) * RPC) * (unsigned)a + 4u * (unsigned)(t & (RPC - 1)), (unsigned)(t >> LOG_RPC));
+                }
+            }
+        dd[j] = (A.damping != 0.f) ? A.damping * diag : 0.f;
+        const float full = diag + dd[j];
+        invd[j] = (full != 0.f) ? 1.f / full : 1.f;
+        A.rhs[s] = rhs;          // diagnostics (psg_opt_last_vectors)
+        r[j] = rhs; z[j] = invd[j] * rhs; p[j] = z[j];
+        sm.z[li] = z[j]; sm.p[0][li] = p[j];
+        s0 += (double)rhs * (double)rhs; s1 += (double)rhs * (double)z[j];
+    }
+    int par = 0;
+    cl_post<RPT>(sm, par, cta, s0, s1);
+    cluster_sync_all();
+    const double2 t01 = cl_total<RPT>(sm, par);
+    const float rhsNorm2 = (float)t01.x;
+    float absNew = (float)t01.y;
+    const float tol = 1.1920929e-07f;
+    float threshold = tol * tol * rhsNorm2;
+    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+    float residualNorm2 = rhsNorm2;
+    int it = 0;
+    if (rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+        float gamma = 0.f, beta = 1.f;   // first pass: the published p already is the search direction
+        int cur = 0;
+        while (it < A.max_iters) {
+            const unsigned pc_off = kP0 + (unsigned)cur * (unsigned)(sizeof(float) * RPC);
+            // ---- phase 1: p <- z + beta p (neighbours recomputed from the published z and p), u = A_t * p[stencil]
+#pragma unroll
+            for (int j = 0; j < RPT; ++j) {
+                if (!in[j]) continue;
+                const int li = j * kClBS + tid;
+                p[j] = z[j] * gamma + beta * p[j];
+                sm.p[cur ^ 1][li] = p[j];
+                float px[4];
+                px[0] = p[j];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const unsigned na = naddr[j][a];
+                    px[a + 1] = na ? ld_dsmem(na) * gamma + beta * ld_dsmem(na + pc_off) : 0.f;
+                }
+                float Ab[10];
+#pragma unroll
+                for (int i = 0; i < 10; ++i) Ab[i] = sm.Ab[i][li];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float u = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                        if (k == 0 || naddr[j][k - 1]) u += aik * px[k];
+                    }
+                    const bool valid = (i == 0) || naddr[j][i - 1];
+                    if (i == 0) u0[j] = u; else sm.U[i - 1][li] = valid ? u : 0.f;
+                }
+            }
+            cluster_sync_all();
+            // ---- phase 2: y = u_s[0] + incident u + damping * diag * p_s ; p . y
+            double pAp = 0.0;
+#pragma unroll
+            for (int j = 0; j < RPT; ++j) {
+                if (!in[j]) continue;
+                const int li = j * kClBS + tid;
+                float yy = u0[j];
+#pragma unroll
+                for (int h = 0; h < 6; ++h) {
+                    const unsigned ta = sm.taddr[h][li];
+                    if (ta) yy += ld_dsmem(ta);
+                }
+                yy += dd[j] * p[j];
+                y[j] = yy;
+                pAp += (double)p[j] * (double)yy;
+            }
+            par ^= 1;
+            cl_post<RPT>(sm, par, cta, pAp, 0.0);
+            cluster_sync_all();
+            const float alpha = absNew / (float)cl_total<RPT>(sm, par).x;
+            // ---- phase 3 (registers, then publish z)
+            double rn = 0.0, rz = 0.0;
+#pragma unroll
+            for (int j = 0; j < RPT; ++j) {
+                if (!in[j]) continue;
+                x[j] += alpha * p[j];
+                r[j] = r[j] - alpha * y[j];
+                z[j] = invd[j] * r[j];
+                sm.z[j * kClBS + tid] = z[j];
+                rn += (double)r[j] * (double)r[j];
+                rz += (double)r[j] * (double)z[j];
+            }
+            par ^= 1;
+            cl_post<RPT>(sm, par, cta, rn, rz);
+            cluster_sync_all();
+            const double2 t12 = cl_total<RPT>(sm, par);
+            residualNorm2 = (float)t12.x;
+            if (residualNorm2 < threshold) break;
+            const float absOld = absNew;
+            absNew = (float)t12.y;
+            beta = absNew / absOld;
+            gamma = 1.f;
+            cur ^= 1;
+            ++it;
+        }
+    } else if (rhsNorm2 == 0.f) {
+        residualNorm2 = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < RPT; ++j) if (in[j]) A.x[row[j]] = x[j];
+    if (cta == 0 && tid == 0) {
+        A.result[0] = (float)it; A.result[1] = residualNorm2; A.result[2] = rhsNorm2; A.result[3] = threshold;
+    }
+    // ---- epilogue: Optimizer::updateDist (OptimizerAux.cpp:162-188); every CTA knows the verdict
+    const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
+    const bool apply = !G.only_on_success || err <= tol;
+    if (apply) {
+        int acc = 0;
+#pragma unroll
+        for (int j = 0; j < RPT; ++j)
+            if (in[j] && fabs((double)x[j]) < G.thr) { G.vol.dist[G.lin[row[j]]] -= x[j]; ++acc; }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 16); acc += __shfl_xor_sync(0xffffffffu, acc, 8); acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2); acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if ((tid & 31) == 0 && acc) atomicAdd(G.accepted, (unsigned long long)acc);
+    }
+    if (!apply && !G.reg_out) return;   // uniform over the cluster
+    __threadfence();
+    cluster_sync_all();
+    // Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records; any one-to-one thread -> slot map will do
+    double en = 0.0, el = 0.0, er = 0.0;
+#pragma unroll
+    for (int j = 0; j < RPT; ++j) {
+        if (!in[j]) continue;
+        if (apply) {
+            const int t = row[j];
+            const int s = __float_as_int(G.surf.rec2[t].w);
+            const int lin = __float_as_int(G.surf.rec3[t].w);
+            const float dist = __ldcg(G.vol.dist + lin);
+            const int pb = __float_as_int(G.surf.rec1[t].w);
+            float fd[3], nfd[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = G.surf.nbr_lin[a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * G.vs_inv;
+            }
+            G.vol.gx[lin] = fd[0]; G.vol.gy[lin] = fd[1]; G.vol.gz[lin] = fd[2];
+            normalized3(fd, nfd);
+            G.surf.rec0[t] = make_float4(dist, nfd[0], nfd[1], nfd[2]);
+            G.surf.rec2[t] = make_float4(fd[0], fd[1], fd[2], __int_as_float(s));
+            G.surf.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
+        }
+        // getNormalEnergy / getLaplacianEnergy / getAlbedoRegEnergy (Optimizer.cpp:86-136) on the updated distances
+        if (G.reg_out) {
+            const int s = row[j];
+            const int lin = G.lin[s];
+            const float dist = __ldcg(G.vol.dist + lin);
+            const float rho[3] = { G.vol.r[lin], G.vol.g[lin], G.vol.b[lin] };
+            const unsigned char pb = G.surf.pos[s];
+            const long long stride[3] = { 1, G.vol.dims[0], (long long)G.vol.dims[0] * G.vol.dims[1] };
+            float fd[3], d2[3], Gr[9];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = G.surf.nbr_lin[a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * G.vs_inv;
+                const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+                const float d1 = (l1 < G.vol.N) ? __ldcg(G.vol.dist + l1) : dist;
+                const float d0 = (l0 >= 0) ? __ldcg(G.vol.dist + l0) : dist;
+                d2[a] = d1 + d0 - 2 * dist;
+                const float nr = nl >= 0 ? G.vol.r[nl] : rho[0], ng = nl >= 0 ? G.vol.g[nl] : rho[1], nbb = nl >= 0 ? G.vol.b[nl] : rho[2];
+                Gr[a] = (pp * (nr - rho[0])) * G.vs_inv; Gr[3 + a] = (pp * (ng - rho[1])) * G.vs_inv; Gr[6 + a] = (pp * (nbb - rho[2])) * G.vs_inv;
+            }
+            const float e = norm3(fd) - 1;
+            en += (double)(e * e);
+            const float lap = (d2[0] + d2[1] + d2[2]) * G.vs_inv * G.vs_inv;
+            el += (double)(lap * lap);
+            er += (double)((norm3(Gr) + norm3(Gr + 3)) + norm3(Gr + 6));
+        }
+    }
+    if (G.reg_out) {
+        const int lane = tid & 31, warp = tid >> 5;
+        en = warp_sum(en); el = warp_sum(el); er = warp_sum(er);
+        __syncthreads();
+        if (lane == 0) { sm.red[warp] = en; sm.red[32 + warp] = el; }
+        __shared__ double s_er[32];
+        if (lane == 0) s_er[warp] = er;
+        __syncthreads();
+        if (tid < 3) {
+            double v = 0.0;
+            for (int i = 0; i < 32; ++i) v += (tid == 0) ? sm.red[i] : (tid == 1) ? sm.red[32 + i] : s_er[i];
+            atomicAdd(&G.reg_out[tid], v);
+        }
+    }
+}
+
 // ---- small surfaces: the whole solve inside ONE thread-block cluster ------------------------------------------------
 // At 128^3 an iteration touches ~4 MB; the grid-wide kernel above spends its time in grid.sync() and in dependent L2
 // round trips.  Here <= 8 CTAs x 1024 threads form one cluster; a thread owns RPT rows (row = gtid + j * threads), keeps
@@ -722,24 +1035,31 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
 
 // ---- the distance block of a sharded job: one persistent kernel per rank, halo and reductions over peer memory ----------------
 // Rank g owns rows [lo, hi) of the surface list (a z-slab).  Its kernel runs k_dist_assemble, the CG, Optimizer::updateDist,
-// updateGrad and the regulariser energies on those rows.  Every vector is a full-length array on every rank; a rank computes
-// its own rows and reads the rows of its halo (other ranks' rows within one z-plane of its range) from ITS OWN copy, into which
-// the owners push them: whoever writes a row that a peer needs also stores it through the peer's mapped pointer (plain st.global
-// over NVLink).  A cross-rank barrier (xbar) separates the phases: the rank's blocks arrive on a local counter after a
-// system-scope fence; the rank's leader block then adds the local partial sums, writes them into every peer's XState mailbox
-// followed by a release store of the barrier number to the peer's flag word, waits until all peers' flags carry that number,
-// adds the partials in rank order (every rank forms the same sum bit for bit, hence takes the same branches) and releases its
-// own blocks.  Mailboxes are double-buffered by barrier parity; all counters are monotonic, nothing is reset while a peer might
-// still write.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers) instead of hanging.
-// On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative launch: block b belongs
-// to rank b / nb.
-struct MgSeg { int peer, b, e; };   // own rows [b, e) are in the halo of rank `peer`
+// updateGrad and the regulariser energies on those rows.  What it needs from other ranks are the entries of a few vectors at its
+// HALO rows (other ranks' rows within one z-plane of its range).  Their owners push them: whoever computes a row that lies in a
+// peer's halo also stores it, through the peer's mapped pointer (NVLink), into the peer's halo buffer as ONE 8-byte packet
+// (tag << 32 | float bits).  An 8-byte store is indivisible, so the reader needs no fence and no barrier for halo data: it
+// polls the packet until it carries the tag of the phase that produced the value (tag = number of barriers the job has passed
+// when the value is produced, + 1 -- every rank counts the same barriers, launches included, so tags never repeat).  A packet is
+// overwritten only after a cross-rank reduction both sides took part in, i.e. after its reader has consumed it.
+// Barriers between phases are LOCAL (the rank's blocks; arrival counter + release word at gpu scope, as in the single-GPU
+// kernels); where the CG needs a dot product the rank's leader block adds the local partials, sends them to every rank as four
+// tagged packets (XState::ll, double-buffered by barrier parity), collects everybody's, adds them in rank order -- every rank
+// forms the same sum bit for bit, hence takes the same branches -- and releases its blocks with the totals.  No system-scope
+// fence anywhere.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers) instead of
+// hanging.  On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative launch: block
+// b belongs to rank b / nb.
+enum HaloKind { HK_B2 = 0, HK_B5, HK_B9, HK_B11, HK_B12, HK_B13, HK_Z, HK_P0, HK_P1, HK_U1, HK_U2, HK_U3, HK_D };
+static_assert(HK_D + 1 == kHaloKinds, "halo kinds");
+
+struct MgSeg { int peer, b, e, hbase, nh; };   // own rows [b, e) are halo rows hbase + row of rank `peer`, whose halo has nh rows
 struct MgRank {
     int rank, lo, hi;
+    int halo_lo, halo_hi, nh;       // halo rows [halo_lo, lo) and [hi, halo_hi); nh of them
     int nseg;
     MgSeg seg[2 * (kMaxRanks - 1)];
     int inner_lo, inner_hi;         // rows in [inner_lo, inner_hi) are in nobody's halo
-    float* vecs; float* pbuf; XState* xs;
+    float* vecs; float* pbuf; XState* xs; unsigned long long* halo;
     const int* nbr_row; const int* inc; const int* lin;
     VolView vol; SurfView surf;
     double* partials;               // [2][nb]
@@ -748,37 +1068,39 @@ struct MgRank {
 };
 struct MgArgs {
     int S, world, nb, nplayed;      // nb blocks per rank; this launch plays `nplayed` ranks (1, or all on a single device)
-    PeerView peer[kMaxRanks];       // every rank's buffers as addressable from this launch
+    PeerView peer[kMaxRanks];       // every rank's halo buffer and mailbox as addressable from this launch
     MgRank loc[kMaxRanks];          // the ranks played, in block order
     float damping, vs_inv;
     double thr;
     int max_iters, only_on_success, want_reg;
+    int flags;
     unsigned long long timeout_ns;
 };
 
 constexpr int kMgBlock = 512;
+constexpr int kMgRows = 4;      // rows per thread and batch in the gather phases
 
 __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_vol64(unsigned long long* p, unsigned long long v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
-template <bool SYS>
-__device__ __forceinline__ bool wait_ge(const unsigned long long* p, unsigned long long target, XState* xs, unsigned long long limit_ns) {
+// spin until pred(value) holds; false after the time limit or once the abort flag is up
+template <typename Load, typename Pred>
+__device__ __forceinline__ bool spin_until(Load load, Pred pred, XState* xs, unsigned long long limit_ns, unsigned long long* out) {
     unsigned spins = 0;
     unsigned long long t0 = 0;
     for (;;) {
-        unsigned long long v;
-        if (SYS) asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-        else asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-        if (v >= target) return true;
+        const unsigned long long v = load();
+        if (pred(v)) { *out = v; return true; }
         if ((++spins & 255u) == 0) {
-            unsigned long long ab;
-            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(ab) : "l"(&xs->abort) : "memory");
-            if (ab) return false;
+            if (ld_vol64(&xs->abort)) { *out = v; return false; }
             const unsigned long long now = global_ns();
             if (!t0) t0 = now;
-            else if (now - t0 > limit_ns) {
-                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&xs->abort), "l"(1ull) : "memory");
-                return false;
-            }
+            else if (now - t0 > limit_ns) { st_vol64(&xs->abort, 1ull); *out = v; return false; }
         }
     }
 }
@@ -787,90 +1109,123 @@ struct MgCtx {
     const MgArgs* A; const MgRank* R;
     int lb, nb;                      // block index within the rank, blocks per rank
     unsigned long long base;         // barriers completed by earlier launches
-    unsigned k;                      // barriers completed by this launch
+    unsigned long long base_r;       // ... of which reductions
+    unsigned k, kr;                  // barriers / reductions completed by this launch
     bool ok;
+    __device__ __forceinline__ unsigned tag_now() const { return (unsigned)(base + k) + 1u; }   // tag of values produced in the current phase
+    __device__ __forceinline__ unsigned tag_prev() const { return (unsigned)(base + k); }       // ... in the phase before the last barrier
 };
 
-// cross-rank barrier with a two-scalar all-reduce; returns the totals (identical bits on every rank and block)
-__device__ __forceinline__ double2 xbar(MgCtx& c, double a, double b, double* s_buf /* 2 * NW + 2 */) {
+// push one value of an own row to every rank that has the row in its halo
+__device__ __forceinline__ void halo_push(const MgCtx& c, int kind, int s, float v) {
+    const MgRank& R = *c.R;
+    if (s >= R.inner_lo && s < R.inner_hi) return;
+    const unsigned long long pkt = ((unsigned long long)c.tag_now() << 32) | (unsigned long long)__float_as_uint(v);
+    for (int i = 0; i < R.nseg; ++i)
+        if (s >= R.seg[i].b && s < R.seg[i].e)
+            st_vol64(c.A->peer[R.seg[i].peer].halo + (size_t)kind * R.seg[i].nh + (R.seg[i].hbase + s), pkt);
+}
+// a halo row's value of `kind` carrying `tag`
+__device__ __forceinline__ float halo_get(MgCtx& c, int kind, int row, unsigned tag) {
+    const MgRank& R = *c.R;
+    const int h = row < R.lo ? row - R.halo_lo : (R.lo - R.halo_lo) + (row - R.hi);
+    const unsigned long long* p = R.halo + (size_t)kind * R.nh + h;
+    unsigned long long v;
+    if (!spin_until([&] { return ld_vol64(p); }, [&](unsigned long long x) { return (unsigned)(x >> 32) == tag; }, R.xs, c.A->timeout_ns, &v)) c.ok = false;
+    return __uint_as_float((unsigned)v);
+}
+
+// Barrier of the rank's blocks (REDUCE = false): every block arrives on the rank's counter and polls it, as grid_barrier does.
+// REDUCE = true adds the two-scalar all-reduce over all ranks: blocks publish their partial sums and arrive; the rank's leader
+// block waits for the arrivals, adds the partials and sends the rank's sums to every rank (its own included) as four tagged
+// packets; EVERY block then polls its rank's mailbox until the packets of all ranks carry this barrier's tag and adds them in
+// rank order -- identical bits in every block of every rank.  The own rank's packet doubles as the local release: it is sent
+// only after all local blocks have arrived.
+template <bool REDUCE>
+__device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, double* s_buf /* 2 * NW + 3 */) {
     constexpr int NW = kMgBlock / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const MgArgs& A = *c.A; const MgRank& R = *c.R;
     XState* xs = R.xs;
     double* P0 = R.partials; double* P1 = R.partials + c.nb;
-    a = warp_sum(a); b = warp_sum(b);
-    if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; }
+    if (REDUCE) {
+        a = warp_sum(a); b = warp_sum(b);
+        if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; }
+    }
     __syncthreads();
     ++c.k;
-    const unsigned long long e = c.base + c.k;
-    const int par = (int)(e & 1ull);
+    const unsigned long long target = (unsigned long long)c.k * (unsigned long long)c.nb;
+    auto load_arrive = [&] { unsigned long long x; asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(x) : "l"(&xs->arrive) : "memory"); return x; };
+    if (!REDUCE) {
+        if (threadIdx.x == 0) {
+            asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
+            unsigned long long v;
+            if (!spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v)) c.ok = false;
+            s_buf[2 * NW + 2] = c.ok ? 0.0 : 1.0;
+        }
+        __syncthreads();
+        if (s_buf[2 * NW + 2] != 0.0) c.ok = false;
+        __syncthreads();
+        return make_double2(0.0, 0.0);
+    }
+    // mailbox parity and packet tag count REDUCTIONS: a peer can be at most one reduction ahead, so two buffers suffice
+    ++c.kr;
+    const unsigned long long er = c.base_r + c.kr;
+    const int par = (int)(er & 1ull);
+    const unsigned tag = (unsigned)er;
     if (warp == 0) {
         double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0;
         ta = warp_sum(ta); tb = warp_sum(tb);
+        bool ok = true;
         if (lane == 0) {
             P0[c.lb] = ta; P1[c.lb] = tb;
-            __threadfence_system();   // this block's stores, local and through the peers' mappings, before the arrival
             asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
         }
         if (c.lb == 0) {
-            bool ok = true;
-            if (lane == 0) ok = wait_ge<false>(&xs->arrive, (unsigned long long)c.k * (unsigned long long)c.nb, xs, A.timeout_ns);
+            if (lane == 0) {
+                unsigned long long v;
+                ok = spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v);
+            }
             ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
             double xa = 0.0, xb = 0.0;
             for (int i = lane; i < c.nb; i += 32) { xa += __ldcg(P0 + i); xb += __ldcg(P1 + i); }
             xa = warp_sum(xa); xb = warp_sum(xb);
+            __threadfence();   // what the arrivals made visible to this block, before the packet that releases the others
             if (lane < A.world) {
-                XState* px = A.peer[lane].xs;
-                if (!ok) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&px->abort), "l"(1ull) : "memory");
-                asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&px->box[par][R.rank][0]), "d"(xa) : "memory");
-                asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&px->box[par][R.rank][1]), "d"(xb) : "memory");
-                __threadfence_system();
-                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&px->flag[R.rank]), "l"(e) : "memory");
-                if (!wait_ge<true>(&xs->flag[lane], e, xs, A.timeout_ns)) ok = false;
-            }
-            ok = __all_sync(0xffffffffu, ok);
-            if (lane == 0) {
-                double sa = 0.0, sb = 0.0;
-                for (int q = 0; q < A.world; ++q) {
-                    double va, vb;
-                    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(va) : "l"(&xs->box[par][q][0]) : "memory");
-                    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(vb) : "l"(&xs->box[par][q][1]) : "memory");
-                    sa += va; sb += vb;
-                }
-                xs->bcast[par][0] = sa; xs->bcast[par][1] = sb;
-                if (!ok) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&xs->abort), "l"(1ull) : "memory");
-                __threadfence();
-                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(&xs->release), "l"(e) : "memory");
+                unsigned long long* dst = &A.peer[lane].xs->ll[par][R.rank][0];
+                const unsigned long long ua = (unsigned long long)__double_as_longlong(xa), ub = (unsigned long long)__double_as_longlong(xb);
+                const unsigned long long th = (unsigned long long)tag << 32;
+                if (!ok) st_vol64(&A.peer[lane].xs->abort, 1ull);
+                st_vol64(dst + 0, th | (ua & 0xffffffffull)); st_vol64(dst + 1, th | (ua >> 32));
+                st_vol64(dst + 2, th | (ub & 0xffffffffull)); st_vol64(dst + 3, th | (ub >> 32));
             }
         }
-    }
-    if (threadIdx.x == 0) {
-        if (!wait_ge<false>(&xs->release, e, xs, A.timeout_ns)) c.ok = false;
-        s_buf[2 * NW] = __ldcg(&xs->bcast[par][0]);
-        s_buf[2 * NW + 1] = __ldcg(&xs->bcast[par][1]);
-        unsigned long long ab;
-        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(ab) : "l"(&xs->abort) : "memory");
-        s_buf[2 * NW + 2] = ab ? 1.0 : 0.0;
+        // every block: the sums of all ranks from the own mailbox
+        double xa = 0.0, xb = 0.0;
+        if (lane < A.world) {
+            const unsigned long long* src = &xs->ll[par][lane][0];
+            unsigned long long w[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (!spin_until([&] { return ld_vol64(src + i); }, [&](unsigned long long x) { return (unsigned)(x >> 32) == tag; }, xs, A.timeout_ns, &w[i])) ok = false;
+            xa = __longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[1] << 32)));
+            xb = __longlong_as_double((long long)((w[2] & 0xffffffffull) | (w[3] << 32)));
+        }
+        ok = __all_sync(0xffffffffu, ok);
+        double sa = 0.0, sb = 0.0;
+        for (int q = 0; q < A.world; ++q) { sa += __shfl_sync(0xffffffffu, xa, q); sb += __shfl_sync(0xffffffffu, xb, q); }   // rank order
+        __threadfence();   // the packet was a relaxed load: order the other blocks' data behind it
+        if (lane == 0) {
+            s_buf[2 * NW] = sa; s_buf[2 * NW + 1] = sb;
+            if (!ok) st_vol64(&xs->abort, 1ull);
+            s_buf[2 * NW + 2] = ok ? 0.0 : 1.0;
+        }
     }
     __syncthreads();
     if (s_buf[2 * NW + 2] != 0.0) c.ok = false;
     const double2 out = make_double2(s_buf[2 * NW], s_buf[2 * NW + 1]);
     __syncthreads();   // s_buf is reused by the next call
     return out;
-}
-
-// store to the own copy and to the copy of every rank that has the row in its halo
-__device__ __forceinline__ void put_vec(const MgArgs& A, const MgRank& R, size_t plane_off, int s, float v) {
-    R.vecs[plane_off + s] = v;
-    if (s >= R.inner_lo && s < R.inner_hi) return;
-    for (int i = 0; i < R.nseg; ++i)
-        if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].vecs[plane_off + s] = v;
-}
-__device__ __forceinline__ void put_p(const MgArgs& A, const MgRank& R, size_t off, int s, float v) {
-    R.pbuf[off + s] = v;
-    if (s >= R.inner_lo && s < R.inner_hi) return;
-    for (int i = 0; i < R.nseg; ++i)
-        if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].pbuf[off + s] = v;
 }
 
 __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
@@ -880,43 +1235,50 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     const int nb = A.nb;
     const MgRank& R = A.loc[blockIdx.x / nb];
     MgCtx c;
-    c.A = &A; c.R = &R; c.lb = blockIdx.x % nb; c.nb = nb; c.k = 0; c.ok = true;
-    c.base = __ldcg(&R.xs->epoch);
+    c.A = &A; c.R = &R; c.lb = blockIdx.x % nb; c.nb = nb; c.k = 0; c.kr = 0; c.ok = true;
+    c.base = __ldcg(&R.xs->epoch); c.base_r = __ldcg(&R.xs->epoch_r);
     const int S = A.S, lo = R.lo, hi = R.hi;
     const int T = nb * kMgBlock, ltid = c.lb * kMgBlock + threadIdx.x;
     const size_t PS = (size_t)S;
     float* V = R.vecs;
     const float tol = 1.1920929e-07f;
+    auto own = [&](int row) { return row >= lo && row < hi; };
 
     // ---- the stencil planes the neighbours' assembly reads: rhs of slots 1..3 and the diagonal entries (a+1, a+1)
     for (int s = lo + ltid; s < hi; s += T) {
         if (s >= R.inner_lo && s < R.inner_hi) continue;
         const int planes[6] = { 2, 5, 9, 11, 12, 13 };
 #pragma unroll
-        for (int i = 0; i < 6; ++i) put_vec(A, R, planes[i] * PS, s, V[planes[i] * PS + s]);
+        for (int i = 0; i < 6; ++i) halo_push(c, HK_B2 + i, s, V[planes[i] * PS + s]);
     }
-    xbar(c, 0.0, 0.0, s_buf);
+    mg_barrier<false>(c, 0.0, 0.0, s_buf);
     // ---- k_dist_assemble on the own rows; x = 0, r = b, z = b / diag, p = z
     double a0 = 0.0, a1 = 0.0;
-    for (int s = lo + ltid; s < hi; s += T) {
-        float rhs = V[10 * PS + s], diag = V[s];
+    {
+        const unsigned tg = c.tag_prev();
+        for (int s = lo + ltid; s < hi; s += T) {
+            float rhs = V[10 * PS + s], diag = V[s];
 #pragma unroll
-        for (int h = 0; h < 2; ++h)
+            for (int h = 0; h < 2; ++h)
 #pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
-                if (t >= 0) { rhs += __ldcg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldcg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
-            }
-        const float dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
-        const float full = diag + dd;
-        const float invd = (full != 0.f) ? 1.f / full : 1.f;
-        const float z = invd * rhs;
-        V[14 * PS + s] = rhs; V[15 * PS + s] = invd; V[16 * PS + s] = dd; V[17 * PS + s] = 0.f; V[19 * PS + s] = rhs;
-        put_vec(A, R, 18 * PS, s, z);
-        put_p(A, R, 0, s, z);
-        a0 += (double)rhs * (double)rhs; a1 += (double)rhs * (double)z;
+                for (int a = 0; a < 3; ++a) {
+                    const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
+                    if (t < 0) continue;
+                    if (own(t)) { rhs += __ldcg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldcg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
+                    else { rhs += halo_get(c, HK_B11 + a, t, tg); diag += halo_get(c, HK_B2 + a, t, tg); }
+                }
+            const float dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
+            const float full = diag + dd;
+            const float invd = (full != 0.f) ? 1.f / full : 1.f;
+            const float z = invd * rhs;
+            V[14 * PS + s] = rhs; V[15 * PS + s] = invd; V[16 * PS + s] = dd; V[17 * PS + s] = 0.f; V[19 * PS + s] = rhs;
+            V[18 * PS + s] = z; R.pbuf[s] = z;
+            halo_push(c, HK_Z, s, z); halo_push(c, HK_P0, s, z);
+            a0 += (double)rhs * (double)rhs; a1 += (double)rhs * (double)z;
+        }
     }
-    const double2 t01 = xbar(c, a0, a1, s_buf);
+    unsigned tag_pc = c.tag_now();   // tag of the packets of the current search direction
+    const double2 t01 = mg_barrier<true>(c, a0, a1, s_buf);
     const float rhsNorm2 = (float)t01.x;
     float absNew = (float)t01.y;
     float threshold = tol * tol * rhsNorm2;
@@ -928,65 +1290,124 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
         int cur = 0;
         while (it < A.max_iters) {
             const float* pc = R.pbuf + (size_t)cur * PS;
-            const size_t pn_off = (size_t)(cur ^ 1) * PS;
+            float* pn = R.pbuf + (size_t)(cur ^ 1) * PS;
             // ---- phase 1: p <- z + beta p (neighbours recomputed from the published z and p), u_t = A_t * p[stencil(t)]
-            for (int s = lo + ltid; s < hi; s += T) {
-                int col[3];
+            // rows in batches of kMgRows: all loads of a batch are issued before any is used; halo neighbours (rare) afterwards
+            {
+                const unsigned tz = c.tag_prev();
+                for (int base = lo + ltid; base < hi; base += T * kMgRows) {
+                    int col[kMgRows][3];
+                    float zc[kMgRows][4], pv[kMgRows][4];
 #pragma unroll
-                for (int a = 0; a < 3; ++a) col[a] = __ldg(R.nbr_row + (size_t)a * S + s);
-                float px[4];
-                px[0] = __ldcg(V + 18 * PS + s) * gamma + beta * __ldcg(pc + s);
+                    for (int j = 0; j < kMgRows; ++j) {
+                        const int s = base + j * T;
+                        const bool in = s < hi;
 #pragma unroll
-                for (int a = 0; a < 3; ++a) px[a + 1] = col[a] >= 0 ? __ldcg(V + 18 * PS + col[a]) * gamma + beta * __ldcg(pc + col[a]) : 0.f;
-                put_p(A, R, pn_off, s, px[0]);
-                float Ab[10];
-#pragma unroll
-                for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    float u = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
-                        if (k == 0 || col[k - 1] >= 0) u += aik * px[k];
+                        for (int a = 0; a < 3; ++a) col[j][a] = in ? __ldg(R.nbr_row + (size_t)a * S + s) : -1;
                     }
-                    const bool valid = (i == 0) || col[i - 1] >= 0;
-                    if (i == 0) V[21 * PS + s] = u; else put_vec(A, R, (size_t)(21 + i) * PS, s, valid ? u : 0.f);
+#pragma unroll
+                    for (int j = 0; j < kMgRows; ++j) {
+                        const int s = base + j * T;
+                        const int s0 = s < hi ? s : lo;
+                        zc[j][0] = __ldcg(V + 18 * PS + s0); pv[j][0] = __ldcg(pc + s0);
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) {
+                            const int cc = col[j][a];
+                            const int ci = (cc >= 0 && own(cc)) ? cc : s0;
+                            zc[j][a + 1] = __ldcg(V + 18 * PS + ci); pv[j][a + 1] = __ldcg(pc + ci);
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < kMgRows; ++j) {
+                        const int s = base + j * T;
+                        if (s >= hi) continue;
+                        float px[4];
+                        px[0] = zc[j][0] * gamma + beta * pv[j][0];
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) {
+                            const int cc = col[j][a];
+                            if (cc < 0) px[a + 1] = 0.f;
+                            else if (own(cc)) px[a + 1] = zc[j][a + 1] * gamma + beta * pv[j][a + 1];
+                            else px[a + 1] = halo_get(c, HK_Z, cc, tz) * gamma + beta * halo_get(c, HK_P0 + cur, cc, tag_pc);
+                        }
+                        pn[s] = px[0];
+                        halo_push(c, HK_P0 + (cur ^ 1), s, px[0]);
+                        float Ab[10];
+#pragma unroll
+                        for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            float u = 0.f;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                                if (k == 0 || col[j][k - 1] >= 0) u += aik * px[k];
+                            }
+                            const bool valid = (i == 0) || col[j][i - 1] >= 0;
+                            const float uv = valid ? u : 0.f;
+                            V[(size_t)(21 + i) * PS + s] = uv;
+                            if (i > 0) halo_push(c, HK_U1 + i - 1, s, uv);
+                        }
+                    }
                 }
             }
-            xbar(c, 0.0, 0.0, s_buf);
+            const unsigned tag_pn = c.tag_now();
+            mg_barrier<false>(c, 0.0, 0.0, s_buf);
             if (!c.ok) break;
             // ---- phase 2: y = u_s[0] + incident u + damping * diag * p_s ; p . y
-            const float* pn = R.pbuf + pn_off;
             double pAp = 0.0;
-            for (int s = lo + ltid; s < hi; s += T) {
-                float y = V[21 * PS + s];
+            {
+                const unsigned tu = c.tag_prev();
+                for (int base = lo + ltid; base < hi; base += T * kMgRows) {
+                    int tn[kMgRows][6];
 #pragma unroll
-                for (int h = 0; h < 2; ++h)
+                    for (int j = 0; j < kMgRows; ++j)
 #pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
-                        if (t >= 0) y += __ldcg(V + (size_t)(22 + a) * PS + t);
+                        for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < hi) ? __ldg(R.inc + (size_t)h * S + base + j * T) : -1;
+                    float uu[kMgRows][7], ps[kMgRows], dg[kMgRows];
+#pragma unroll
+                    for (int j = 0; j < kMgRows; ++j) {
+                        const int s = base + j * T;
+                        const int s0 = s < hi ? s : lo;
+                        uu[j][0] = V[21 * PS + s0]; ps[j] = pn[s0]; dg[j] = V[16 * PS + s0];
+#pragma unroll
+                        for (int h = 0; h < 6; ++h) {
+                            const int t = tn[j][h];
+                            uu[j][h + 1] = (t >= 0 && own(t)) ? __ldcg(V + (size_t)(22 + h % 3) * PS + t) : 0.f;
+                        }
                     }
-                const float ps = __ldcg(pn + s);
-                y += V[16 * PS + s] * ps;
-                V[20 * PS + s] = y;
-                pAp += (double)ps * (double)y;
+#pragma unroll
+                    for (int j = 0; j < kMgRows; ++j) {
+                        const int s = base + j * T;
+                        if (s >= hi) continue;
+                        float y = uu[j][0];
+#pragma unroll
+                        for (int h = 0; h < 6; ++h) {
+                            const int t = tn[j][h];
+                            if (t < 0) continue;
+                            y += own(t) ? uu[j][h + 1] : halo_get(c, HK_U1 + h % 3, t, tu);
+                        }
+                        y += dg[j] * ps[j];
+                        V[20 * PS + s] = y;
+                        pAp += (double)ps[j] * (double)y;
+                    }
+                }
             }
-            const float alpha = absNew / (float)xbar(c, pAp, 0.0, s_buf).x;
+            const float alpha = absNew / (float)mg_barrier<true>(c, pAp, 0.0, s_buf).x;
             if (!c.ok) break;
             // ---- phase 3 (own rows): x += alpha p ; r -= alpha y ; z = r / diag, published ; norms
             double rn = 0.0, rz = 0.0;
             for (int s = lo + ltid; s < hi; s += T) {
-                const float ps = __ldcg(pn + s);
+                const float ps = pn[s];
                 V[17 * PS + s] = V[17 * PS + s] + alpha * ps;
                 const float r2 = V[19 * PS + s] - alpha * V[20 * PS + s];
                 V[19 * PS + s] = r2;
                 const float z = V[15 * PS + s] * r2;
-                put_vec(A, R, 18 * PS, s, z);
+                V[18 * PS + s] = z;
+                halo_push(c, HK_Z, s, z);
                 rn += (double)r2 * (double)r2; rz += (double)r2 * (double)z;
             }
-            const double2 t12 = xbar(c, rn, rz, s_buf);
+            const double2 t12 = mg_barrier<true>(c, rn, rz, s_buf);
             if (!c.ok) break;
             residualNorm2 = (float)t12.x;
             if (residualNorm2 < threshold) break;
@@ -995,6 +1416,7 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             beta = absNew / absOld;
             gamma = 1.f;
             cur ^= 1;
+            tag_pc = tag_pn;
             ++it;
         }
     } else if (rhsNorm2 == 0.f) {
@@ -1002,9 +1424,8 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     }
     if (ltid == 0) {
         R.result[0] = (float)it; R.result[1] = residualNorm2; R.result[2] = rhsNorm2; R.result[3] = threshold;
-        R.result[4] = c.ok ? 0.f : 1.f;
     }
-    // ---- Optimizer::updateDist (OptimizerAux.cpp:162-188) on the own rows; the new distances of the halo rows go to the peers
+    // ---- Optimizer::updateDist (OptimizerAux.cpp:162-188) on the own rows; the new distances of the boundary rows go to the peers
     const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
     const bool apply = c.ok && (!A.only_on_success || err <= tol);
     double acc = 0.0;
@@ -1015,11 +1436,17 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             const float x = V[17 * PS + s];
             if (fabs((double)x) < A.thr) { d -= x; R.vol.dist[lin] = d; acc += 1.0; }
         }
-        if (s >= R.inner_lo && s < R.inner_hi) continue;
-        for (int i = 0; i < R.nseg; ++i)
-            if (s >= R.seg[i].b && s < R.seg[i].e) A.peer[R.seg[i].peer].dist[lin] = d;
+        halo_push(c, HK_D, s, d);
     }
-    xbar(c, 0.0, 0.0, s_buf);
+    // the halo rows' distances into the own distance plane (the finite differences and the Laplacian read it by voxel index)
+    {
+        const unsigned td = c.tag_now();
+        for (int h = ltid; h < R.nh; h += T) {
+            const int row = h < lo - R.halo_lo ? R.halo_lo + h : hi + (h - (lo - R.halo_lo));
+            R.vol.dist[R.lin[row]] = halo_get(c, HK_D, row, td);
+        }
+    }
+    mg_barrier<false>(c, 0.0, 0.0, s_buf);
     // ---- Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records of the own slots
     if (apply) {
         for (int t = ltid; t < R.surf.nslots; t += T) {
@@ -1081,8 +1508,10 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     }
     // ---- bookkeeping for the next launch (every block has left its last barrier: nothing reads these any more)
     if (c.lb == 0 && threadIdx.x == 0) {
+        R.result[4] = ld_vol64(&R.xs->abort) ? 1.f : 0.f;
         R.xs->arrive = 0ull;
         R.xs->epoch = c.base + c.k;
+        R.xs->epoch_r = c.base_r + c.kr;
     }
 }
 
@@ -1410,6 +1839,7 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 
     constexpr int kClusterMax = 8, kClusterRows = 1 << 16;
     const bool use_cluster = o->pcg_mode == 1 && S <= kClusterRows;
+    o->last_pcg_kernel = use_cluster ? 1 : 0;
     const PcgGeometry& geo = pcg_geometry();
     const int sms = geo.sms;
     // grid kernel geometry: one row per thread while that still leaves SMs idle, four rows per thread beyond
@@ -1462,10 +1892,50 @@ void launch_dist_solve(psg_optimizer* o, float damping) {
 }
 
 // Fused path for surfaces with at most one row per resident thread (128^3, 256^3): returns false if it does not apply.
+// can a 16-CTA cluster of the DSMEM kernel be scheduled on this device? (queried once)
+template <int RPT>
+static bool cluster16_available() {
+    static int state = -1;
+    if (state < 0) {
+        state = 0;
+        const size_t smem = sizeof(ClSmem<RPT>);
+        if (cudaFuncSetAttribute(k_dist_solve_cluster16<RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
+            cudaFuncSetAttribute(k_dist_solve_cluster16<RPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(kClNC); cfg.blockDim = dim3(kClBS); cfg.dynamicSmemBytes = smem;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = kClNC; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, k_dist_solve_cluster16<RPT>, &cfg) == cudaSuccess && n >= 1) state = 1;
+        }
+        cudaGetLastError();   // a refusal is an answer, not an error of the caller
+    }
+    return state == 1;
+}
+
+template <int RPT>
+static void launch_cluster16(psg_optimizer* o, SolveSmallArgs& G) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kClNC); cfg.blockDim = dim3(kClBS); cfg.dynamicSmemBytes = sizeof(ClSmem<RPT>); cfg.stream = o->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kClNC; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    Prof pf(o->stream, KID_PCG_SOLVE);
+    PSG_CUDA(cudaLaunchKernelEx(&cfg, k_dist_solve_cluster16<RPT>, G));
+}
+
 bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_success, int reg_slot) {
     const int S = o->S;
-    if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3 && o->pcg_mode != 4)) return false;
+    if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3 && o->pcg_mode != 4 && o->pcg_mode != 6)) return false;
     const PcgGeometry& geo = pcg_geometry();
+    // up to 32 768 rows: one 16-CTA cluster with the vectors in distributed shared memory (modes 0 and 6)
+    const bool want_cluster = (o->pcg_mode == 0 || o->pcg_mode == 6) && S <= 2 * kClNC * kClBS;
+    const int cl_rpt = S <= kClNC * kClBS ? 1 : 2;
+    const bool use_cluster = want_cluster && (cl_rpt == 1 ? cluster16_available<1>() : cluster16_available<2>());
+    if (o->pcg_mode == 6 && !use_cluster) return false;
     // Block size: the solve is a chain of grid barriers (three per iteration), and a barrier costs more the more blocks take
     // part, while a row's arithmetic is negligible.  Measured (profiles/r1_summary.md section 8c): 128^3 (28 k rows) 125 / 114 /
     // 120 us with 256 / 512 / 1024 threads per block, 256^3 (113 k rows) 216 / 164 / 152 us.  So: the smallest block that
@@ -1514,6 +1984,12 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     G.only_on_success = only_on_success ? 1 : 0;
     G.reg_out = reg_slot >= 0 ? mail_dev(o) + 8 * reg_slot : nullptr;
     G.zbuf = A.r;   // plane 18 is free on this path (the residual lives in registers)
+    if (use_cluster) {
+        if (cl_rpt == 1) launch_cluster16<1>(o, G); else launch_cluster16<2>(o, G);
+        o->last_pcg_kernel = 3;
+        return true;
+    }
+    o->last_pcg_kernel = 2;
     void* args[] = { &G, &pbuf };
     Prof pf(o->stream, KID_PCG_SOLVE);
     if (bsz == 1024) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<1024>, dim3(grid), dim3(1024), args, 0, o->stream));
@@ -1543,19 +2019,29 @@ void launch_dist_update(psg_optimizer* o, bool only_on_success) {
 static void fill_mg_rank(psg_optimizer* o, MgRank* R) {
     memset(R, 0, sizeof(*R));
     R->rank = o->rank; R->lo = o->row_lo; R->hi = o->row_hi;
+    R->halo_lo = o->halo_lo[o->rank]; R->halo_hi = o->halo_hi[o->rank];
+    R->nh = (R->lo - R->halo_lo) + (R->halo_hi - R->hi);
     int inner_lo = R->lo, inner_hi = R->hi, n = 0;
     for (int q = 0; q < o->world; ++q) {
         if (q == o->rank) continue;
+        const int qlo = o->row_bounds[q], qhi = o->row_bounds[q + 1];
+        const int qnh = (qlo - o->halo_lo[q]) + (o->halo_hi[q] - qhi);
         // rows of mine below rank q's range that q needs (q's lower halo), and rows of mine above it (q's upper halo)
-        const int b0 = std::max(R->lo, o->halo_lo[q]), e0 = std::min(R->hi, o->row_bounds[q]);
-        if (e0 > b0) { R->seg[n].peer = q; R->seg[n].b = b0; R->seg[n].e = e0; ++n; if (q > o->rank) inner_hi = std::min(inner_hi, b0); else inner_lo = std::max(inner_lo, e0); }
-        const int b1 = std::max(R->lo, o->row_bounds[q + 1]), e1 = std::min(R->hi, o->halo_hi[q]);
-        if (e1 > b1) { R->seg[n].peer = q; R->seg[n].b = b1; R->seg[n].e = e1; ++n; if (q < o->rank) inner_lo = std::max(inner_lo, e1); else inner_hi = std::min(inner_hi, b1); }
+        const int b0 = std::max(R->lo, o->halo_lo[q]), e0 = std::min(R->hi, qlo);
+        if (e0 > b0) {
+            R->seg[n] = MgSeg{q, b0, e0, -o->halo_lo[q], qnh}; ++n;
+            if (q > o->rank) inner_hi = std::min(inner_hi, b0); else inner_lo = std::max(inner_lo, e0);
+        }
+        const int b1 = std::max(R->lo, qhi), e1 = std::min(R->hi, o->halo_hi[q]);
+        if (e1 > b1) {
+            R->seg[n] = MgSeg{q, b1, e1, (qlo - o->halo_lo[q]) - qhi, qnh}; ++n;
+            if (q < o->rank) inner_lo = std::max(inner_lo, e1); else inner_hi = std::min(inner_hi, b1);
+        }
     }
     R->nseg = n;
     if (inner_lo > inner_hi) { inner_lo = R->lo; inner_hi = R->lo; }
     R->inner_lo = inner_lo; R->inner_hi = inner_hi;
-    R->vecs = o->vecs.p; R->pbuf = o->pcg_pbuf.p; R->xs = reinterpret_cast<XState*>(o->xstate.p);
+    R->vecs = o->vecs.p; R->pbuf = o->pcg_pbuf.p; R->xs = reinterpret_cast<XState*>(o->xstate.p); R->halo = o->halo.p;
     R->nbr_row = o->nbr_row.p; R->inc = o->inc.p; R->lin = o->lin.p;
     R->vol = o->vol->view(); R->surf = surf_view(o);
     R->partials = o->pcg_partials.p + 1;
@@ -1588,6 +2074,7 @@ static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const
     if (A.nb > kPcgMaxBlocks / 2) A.nb = kPcgMaxBlocks / 2;
     A.damping = L.damping; A.vs_inv = on->vs_inv; A.thr = sqrt(3.0) * (double)on->vs;
     A.max_iters = 2 * on->S; A.only_on_success = L.only_on_success; A.want_reg = L.want_reg;
+    A.flags = on->pcg_mode == 7 ? 1 : 0;
     A.timeout_ns = 10ull * 1000ull * 1000ull * 1000ull;
     on->mg_args.alloc(sizeof(MgArgs));
     PSG_CUDA(cudaMemcpyAsync(on->mg_args.p, &A, sizeof(A), cudaMemcpyHostToDevice, on->stream));
@@ -1613,6 +2100,7 @@ void launch_dist_block_mg(psg_optimizer* o, float damping, bool only_on_success,
     MgLaunch L; L.damping = damping; L.only_on_success = only_on_success ? 1 : 0; L.want_reg = want_reg ? 1 : 0;
     if (o->group) group_run(o, &R, mg_leader, &L);
     else launch_mg(o, &R, 1, L);
+    o->last_pcg_kernel = 4;
     o->vol_unsynced = true;
 }
 

@@ -62,25 +62,22 @@ namespace psg {
 constexpr int kMaxRanks = 8;     // ranks of one sharded job (one 8-GPU NVSwitch box)
 
 // Per-rank synchronisation block of the distributed distance solve, in memory the peers can write (CUDA IPC mapping, or the
-// same address space when the ranks of a job live in one process).  Zeroed once when it is allocated; every counter is monotonic
-// across launches, so nothing is reset while a peer may still be writing.
+// same address space when the ranks of a job live in one process).  Zeroed once when it is allocated; every counter and tag is
+// monotonic across launches, so nothing is reset while a peer may still be writing.
 struct XState {
-    unsigned long long epoch;              // cross-rank barriers completed by earlier launches (written by the owner at the end of a launch)
-    unsigned long long arrive;             // arrivals of the owner's blocks at the current barrier (reset by the owner's leader block)
-    unsigned long long release;            // last barrier the owner's leader block has released to its own blocks
+    unsigned long long epoch;              // barriers completed by earlier launches (written by the owner at the end of a launch)
+    unsigned long long epoch_r;            // ... of which barriers with a cross-rank reduction (mailbox parity and packet tags)
+    unsigned long long arrive;             // arrivals of the owner's blocks at the current barrier (reset by the owner at the end of a launch)
     unsigned long long abort;              // sticky: a wait ran into its time limit
-    unsigned long long flag[kMaxRanks];    // flag[q]: last barrier rank q has signalled to the owner        (written by rank q)
-    double box[2][kMaxRanks][2];           // [barrier parity][sender]: the sender's two partial sums         (written by rank q)
-    double bcast[2][2];                    // totals of the current barrier, for the owner's other blocks
+    unsigned long long ll[2][kMaxRanks][4];   // [reduction parity][sender][word]: two doubles as four (tag << 32 | 32 data bits) packets, written by the sender
 };
 
 // what a rank exposes to its peers
 struct PeerView {
-    float* vecs = nullptr;      // normal-equation planes + PCG vectors, 25 planes of S rows (psg_optimizer::vecs)
-    float* pbuf = nullptr;      // double-buffered search direction, 2 x S
-    float* dist = nullptr;      // the volume's distance plane, N voxels
+    unsigned long long* halo = nullptr;   // kHaloKinds planes of nh (tag << 32 | float bits) packets: the owner's halo rows, written by their owners
     XState* xs = nullptr;
 };
+constexpr int kHaloKinds = 13;   // stencil planes 2, 5, 9, 11, 12, 13 | z | p (two buffers) | U1..U3 | distance
 }  // namespace psg
 
 struct psg_volume {
@@ -159,6 +156,7 @@ struct psg_optimizer {
     bool layout_dirty = true;                // slot list / peer tables must be rebuilt (mode switch, new surface)
     bool vol_unsynced = false;               // sharded: other ranks' rows of the volume planes are stale (psg_opt_sync_volume)
     psg::DevBuf<unsigned char> xstate;       // psg::XState of this rank
+    psg::DevBuf<unsigned long long> halo;    // this rank's halo packets (PeerView::halo), kHaloKinds x (rows of its halo)
     psg::PeerView peer[psg::kMaxRanks];      // peer[q]: rank q's buffers as addressable from this process (peer[rank] = own)
     std::vector<void*> ipc_opened;           // base pointers of the imported allocations (closed before anything is freed)
     int shard_policy = 0;                    // 0 = by work per rank, 1 = always, 2 = never
@@ -166,6 +164,7 @@ struct psg_optimizer {
     int reduce_lo = 1 << 30, reduce_hi = -1; // mail slots whose values are still per-rank partial sums
     size_t reduce_red = 0;                   // ... and how many doubles of o->red
     bool reduce_reg = false;                 // ... and the regulariser / accepted-count slot (kSlotReg)
+    int last_pcg_kernel = -1;                // which distance-solve kernel ran last: 0 general grid, 1 portable cluster, 2 fused grid, 3 16-CTA cluster (DSMEM), 4 distributed
     int pcg_mode = 0;                        // 0 / 2 = cooperative-grid kernel, 1 = cluster kernel for small surfaces
     int sweep_split = 0;                     // 0 = choose the keyframe split per launch; else force W (1, 2, 4, 8)
     psg::DevBuf<float> vecs;                 // per-voxel normal equations + PCG vectors

@@ -167,12 +167,13 @@ def test_out_of_image_projection():
 
 
 def test_pcg_kernels_agree():
-    """The three distance-solve kernels run the same iteration: fused small-surface kernel (0, the default), thread-block
-    cluster (1), general cooperative grid (2).  0 and 2 share the row -> thread map, hence the dot-product partials and every bit."""
+    """The distance-solve kernels run the same iteration: fused grid kernel (3 / 4), 8-CTA cluster over global memory (1), general
+    cooperative grid (2), 16-CTA cluster over distributed shared memory (0, the default at this size).  3 and 2 share the
+    row -> thread map, hence the dot-product partials and every bit."""
     model, G = "SH1", 40
     sc = scene(model)
     outs = []
-    for mode in (0, 1, 2, 3, 4):   # 3, 4: the fused kernel with 512- / 1024-thread blocks
+    for mode in (3, 1, 2, 0, 4):   # 3, 4: the fused grid kernel with 512- / 1024-thread blocks; 0: the 16-CTA cluster kernel at this size
         gv, go = make_gpu(model, G, sc)
         handoff(go, sc); go.init_albedo(); go.set_pcg_mode(mode)
         info = go.step("dist", damping=1.0, normal_reg=True)
