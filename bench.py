@@ -644,6 +644,9 @@ def main():
     # native libraries (NCCL prints its version banner) write to fd 1 directly; the contract is ONE JSON line on stdout
     global _JSON_OUT
     a = parse()
+    if os.environ.get("PSG_BENCH_WATCHDOG"):      # debugging aid: dump every thread's Python stack if the run is still going by then
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["PSG_BENCH_WATCHDOG"]), repeat=True, file=sys.stderr)
     sys.stdout.flush()
     _JSON_OUT = os.dup(1)
     os.dup2(2, 1)

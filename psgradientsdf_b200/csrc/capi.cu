@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 
 #include <atomic>
@@ -23,6 +24,16 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 void count_launch(int n) { g_launches += n; }
+void trace(const char* fmt, ...) {
+    static const int on = getenv("PSG_TRACE") ? 1 : 0;
+    if (!on) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vfprintf(stderr, fmt, ap);
+    va_end(ap);
+    fputc('\n', stderr);
+    fflush(stderr);
+}
 
 // ---- launch timer: CUDA events on the launching stream around every kernel, summed per kernel id on request
 static const char* const kKernelNames[KID_COUNT] = {
@@ -363,7 +374,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     o->upload_staging.release();
     o->images.release(); o->lin.release(); o->nbr_lin.release(); o->nbr_row.release(); o->inc.release();
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
-    o->pvis.release(); o->perm.release(); o->sort_keys.release(); o->sort_keys2.release(); o->sort_vals.release(); o->sort_tmp.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
+    o->pvis.release(); o->perm.release(); o->sort_hist.release(); o->perm2.release(); o->block_pairs.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);
     o->areg.release(); o->mg_args.release();
     o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
@@ -488,6 +499,7 @@ int psg_opt_init(psg_optimizer* o) {
         }
     }
     o->frames_dirty = true;
+    if (o->sharded && o->vol_unsynced) sync_volume(o);   // the new work list is made from the WHOLE volume: every rank needs the others' rows first
     build_surface(o, true);
     finish_upload(o);   // overlapped keyframe upload: the images are needed from here on
     o->inited = true;

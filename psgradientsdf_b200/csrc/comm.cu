@@ -347,6 +347,7 @@ void release_peers(psg_optimizer* o) {
 void exchange_peers(psg_optimizer* o) {
     for (int q = 0; q < kMaxRanks; ++q) o->peer[q] = PeerView();
     if (!o->sharded) return;
+    trace("[rank %d] exchange_peers: rows %d..%d of %d", o->rank, o->row_lo, o->row_hi, o->S);
     if (o->world > kMaxRanks) { set_error("a sharded job has at most %d ranks (%d given)", kMaxRanks, o->world); throw CudaError{-1}; }
     if (!o->xstate.p) {
         o->xstate.alloc(sizeof(XState));
@@ -388,6 +389,7 @@ void exchange_peers(psg_optimizer* o) {
         o->peer[q].xs = static_cast<XState*>(ipc_import(o, cache, all[q].xs));
     }
     comm_barrier(o);   // every rank has mapped everything before anyone launches a kernel that writes to a peer
+    trace("[rank %d] exchange_peers done", o->rank);
 }
 
 // ---- psg_opt_sync_volume: the rows every rank owns -> everybody ---------------------------------------------------------------

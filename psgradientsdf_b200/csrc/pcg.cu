@@ -1205,9 +1205,19 @@ __device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, doub
         if (lane < A.world) {
             const unsigned long long* src = &xs->ll[par][lane][0];
             unsigned long long w[4];
+            unsigned spins = 0;
+            unsigned long long t0 = 0;
+            for (;;) {   // the four packets of a sender are polled together: one round trip when they are there
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (!spin_until([&] { return ld_vol64(src + i); }, [&](unsigned long long x) { return (unsigned)(x >> 32) == tag; }, xs, A.timeout_ns, &w[i])) ok = false;
+                for (int i = 0; i < 4; ++i) w[i] = ld_vol64(src + i);
+                if ((unsigned)(w[0] >> 32) == tag && (unsigned)(w[1] >> 32) == tag && (unsigned)(w[2] >> 32) == tag && (unsigned)(w[3] >> 32) == tag) break;
+                if ((++spins & 255u) == 0) {
+                    if (ld_vol64(&xs->abort)) { ok = false; break; }
+                    const unsigned long long now = global_ns();
+                    if (!t0) t0 = now;
+                    else if (now - t0 > A.timeout_ns) { st_vol64(&xs->abort, 1ull); ok = false; break; }
+                }
+            }
             xa = __longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[1] << 32)));
             xb = __longlong_as_double((long long)((w[2] & 0xffffffffull) | (w[3] << 32)));
         }
@@ -2076,6 +2086,8 @@ static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const
     A.max_iters = 2 * on->S; A.only_on_success = L.only_on_success; A.want_reg = L.want_reg;
     A.flags = on->pcg_mode == 7 ? 1 : 0;
     A.timeout_ns = 10ull * 1000ull * 1000ull * 1000ull;
+    trace("[rank %d] distributed solve: %d rank(s) played, %d blocks per rank, rows %d..%d, halo %d..%d (%d), %d segments", on->rank, nplayed, A.nb,
+          ranks[0].lo, ranks[0].hi, ranks[0].halo_lo, ranks[0].halo_hi, ranks[0].nh, ranks[0].nseg);
     on->mg_args.alloc(sizeof(MgArgs));
     PSG_CUDA(cudaMemcpyAsync(on->mg_args.p, &A, sizeof(A), cudaMemcpyHostToDevice, on->stream));
     const MgArgs* dev = reinterpret_cast<const MgArgs*>(on->mg_args.p);

@@ -12,6 +12,7 @@
 namespace psg {
 
 void set_error(const char* fmt, ...);
+void trace(const char* fmt, ...);   // stderr, only when PSG_TRACE is set in the environment (debugging aid)
 void count_launch(int n = 1);
 
 // Kernel ids for the built-in launch timer (psg_profile_* in include/psg.h).
@@ -133,12 +134,12 @@ struct psg_optimizer {
     psg::DevBuf<unsigned long long> svis;
     psg::DevBuf<unsigned char> pos;
     psg::DevBuf<float4> rec0, rec1, rec2, rec3, rec4;   // slot-ordered voxel records (SurfView)
-    psg::DevBuf<unsigned long long> pvis, sort_keys, sort_keys2;
-    psg::DevBuf<int> perm, sort_vals;
-    psg::DevBuf<unsigned char> sort_tmp;
+    psg::DevBuf<unsigned long long> pvis;
+    psg::DevBuf<int> perm, perm2;
+    psg::DevBuf<unsigned> sort_hist;         // radix sort of the slot order: per-chunk bucket offsets of the pass in flight
     unsigned long long vol_gen_seen = 0;     // volume generation the records were gathered from
     psg::DevBuf<unsigned int> mask, prefix;  // membership bitmask over the volume + exclusive popcount prefix
-    psg::DevBuf<unsigned int> block_counts;
+    psg::DevBuf<unsigned int> block_counts, block_pairs;
     // reductions / systems
     psg::DevBuf<double> red;                 // scratch for reductions (energy, JtJ blocks)
     psg::DevBuf<double> sweep_partials;      // per-block scalar partials of the sweeps

@@ -8,8 +8,6 @@
 // Membership is a bitmask over the volume (1 bit / voxel) plus an exclusive popcount prefix per 32-voxel word
 // (a rank structure, 0.25 B / voxel instead of a 4 B / voxel row map): member(l) is a bit test and
 // row(l) = prefix[l/32] + popc(mask[l/32] below bit l%32), which is also what keeps the list in ascending lin order.
-#include <cub/device/device_radix_sort.cuh>
-
 #include "psg_host.h"
 
 namespace psg {
@@ -45,37 +43,56 @@ __device__ __forceinline__ unsigned long long select_vis(const VolView& v, long 
 // Pass 1: surface predicate per voxel -> membership words + per-block counts.
 // Each warp owns consecutive 32-voxel words; a block owns words [blockIdx.x * wpb, (blockIdx.x + 1) * wpb).
 __global__ void __launch_bounds__(256) k_surface_mask(VolView v, SelectParams P, unsigned* __restrict__ mask,
-                                                     unsigned* __restrict__ block_counts, long long nwords_total, int wpb) {
+                                                     unsigned* __restrict__ block_counts, unsigned* __restrict__ block_pairs,
+                                                     long long nwords_total, int wpb) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const long long w0 = (long long)blockIdx.x * wpb;
-    unsigned cnt = 0;
+    unsigned cnt = 0, pairs = 0;
     for (long long w = w0 + warp; w < w0 + wpb && w < nwords_total; w += nwarps) {
         const long long lin = w * 32 + lane;
-        bool on = false;
+        unsigned long long kv = 0ull;
         if (lin < v.N) {
             const float d = v.dist[lin];
-            if (fabs((double)d) <= P.thr) on = select_vis(v, lin, P) != 0ull;
+            if (fabs((double)d) <= P.thr) kv = select_vis(v, lin, P);
         }
-        const unsigned m = __ballot_sync(0xffffffffu, on);
+        const unsigned m = __ballot_sync(0xffffffffu, kv != 0ull);
+        pairs += (unsigned)__popcll(kv);
         if (lane == 0) { mask[w] = m; cnt += __popc(m); }
     }
-    __shared__ unsigned s_cnt[8];
-    if (lane == 0) s_cnt[warp] = cnt;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) pairs += __shfl_xor_sync(0xffffffffu, pairs, o);
+    __shared__ unsigned s_cnt[8], s_pairs[8];
+    if (lane == 0) { s_cnt[warp] = cnt; s_pairs[warp] = pairs; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        unsigned t = 0;
-        for (int i = 0; i < nwarps; ++i) t += s_cnt[i];
+        unsigned t = 0, tp = 0;
+        for (int i = 0; i < nwarps; ++i) { t += s_cnt[i]; tp += s_pairs[i]; }
         block_counts[blockIdx.x] = t;
+        block_pairs[blockIdx.x] = tp;      // visible (voxel, keyframe) pairs of the block's surface voxels
     }
 }
 
 // Pass 2: exclusive scan of the per-block counts (single block, chunked with a carry); total -> counts[n].
-__global__ void __launch_bounds__(1024) k_scan_counts(unsigned* __restrict__ counts, int n) {
+__global__ void __launch_bounds__(1024) k_scan_counts(unsigned* __restrict__ counts, int n, const unsigned* __restrict__ block_pairs,
+                                                     unsigned long long* __restrict__ totals /* [0] surface voxels, [1] visible pairs */) {
     __shared__ unsigned s_warp[32];
     __shared__ unsigned s_carry;
+    __shared__ unsigned long long s_pairs[32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_carry = 0;
+    {
+        unsigned long long tp = 0ull;
+        for (int i = threadIdx.x; i < n; i += 1024) tp += block_pairs[i];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) tp += __shfl_xor_sync(0xffffffffu, tp, o);
+        if (lane == 0) s_pairs[warp] = tp;
+    }
     __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long tp = 0ull;
+        for (int i = 0; i < 32; ++i) tp += s_pairs[i];
+        totals[1] = tp;
+    }
     for (int base = 0; base < n; base += 1024) {
         const int i = base + threadIdx.x;
         const unsigned x = i < n ? counts[i] : 0u;
@@ -98,7 +115,7 @@ __global__ void __launch_bounds__(1024) k_scan_counts(unsigned* __restrict__ cou
         if (threadIdx.x == 1023) s_carry = carry + warp_off + inc;
         __syncthreads();
     }
-    if (threadIdx.x == 0) counts[n] = s_carry;
+    if (threadIdx.x == 0) { counts[n] = s_carry; totals[0] = s_carry; }
 }
 
 // Pass 3: per-word exclusive prefix, then ordered scatter of lin and keyframe visibility.
@@ -271,30 +288,77 @@ SurfView surf_view(psg_optimizer* o) {
     return raw_view(o);
 }
 
-// sort key of a row: (64 - number of visible keyframes) above the visibility word, so that rows with equal masks are
-// adjacent and the rows with most work come first (no heavy blocks left for the tail of the launch)
-__global__ void __launch_bounds__(256) k_sort_keys(const unsigned long long* __restrict__ vis, unsigned long long* __restrict__ keys,
-                                                  int* __restrict__ vals, int row0, int n, int F) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned long long m = vis[row0 + i];
-    keys[i] = (F <= 57) ? (((unsigned long long)(64 - __popcll(m)) << F) | m) : m;
-    vals[i] = row0 + i;
+// ---- slot order: LSD radix sort of the rows by (64 - visible keyframes, visibility word) ---------------------------------------
+// The sweeps walk 32 slots per warp, all lanes on the same keyframe, over the union of the 32 visibility masks; lanes whose voxel
+// does not see the keyframe idle.  Sorting by the whole mask puts equal masks next to each other (measured: sorting by the
+// keyframe count alone, rows otherwise in voxel order, makes the sweeps 1.3-1.5x slower), and the count on top puts the rows
+// with most work first (no heavy blocks left for the tail of the launch).  ceil(F / 8) stable counting-sort passes over the mask
+// bytes, low to high, and a last one over the count; per pass: per-chunk histogram, one scan block, stable scatter (warp match +
+// per-warp offsets).  Rows are sorted as indices; the key is fetched through the index.
+constexpr int kSortBuckets = 256;
+constexpr int kSortChunk = 2048;     // rows per block
+
+__device__ __forceinline__ int sort_digit(unsigned long long m, int pass, int npass) {
+    return pass == npass - 1 ? 64 - __popcll(m) : (int)((m >> (8 * pass)) & 255ull);
 }
 
-// number of visible (surface voxel, keyframe) pairs: the size of a sweep, used to decide whether sharding it pays
-__global__ void __launch_bounds__(256) k_count_pairs(const unsigned long long* __restrict__ vis, int n, unsigned long long* __restrict__ out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    __shared__ int s_c[8];
-    int c = i < n ? __popcll(vis[i]) : 0;
-#pragma unroll
-    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+__global__ void __launch_bounds__(256) k_sort_hist(const unsigned long long* __restrict__ vis, const int* __restrict__ in, int row0, int n,
+                                                  int pass, int npass, unsigned* __restrict__ hist /* [nchunks][256] */) {
+    __shared__ unsigned s_h[kSortBuckets];
+    s_h[threadIdx.x] = 0u;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        int t = 0;
-        for (int w = 0; w < 8; ++w) t += s_c[w];
-        if (t) atomicAdd(out, (unsigned long long)t);
+    const int c0 = blockIdx.x * kSortChunk;
+    for (int i = c0 + threadIdx.x; i < c0 + kSortChunk && i < n; i += 256) {
+        const int row = in ? in[i] : row0 + i;
+        atomicAdd(&s_h[sort_digit(vis[row], pass, npass)], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)blockIdx.x * kSortBuckets + threadIdx.x] = s_h[threadIdx.x];
+}
+// hist[c][b] -> first output position of chunk c's rows of bucket b
+__global__ void __launch_bounds__(256) k_sort_scan(unsigned* __restrict__ hist, int nchunks) {
+    __shared__ unsigned s_tot[kSortBuckets];
+    const int b = threadIdx.x;
+    unsigned run = 0;
+    for (int c = 0; c < nchunks; ++c) { const unsigned v = hist[(size_t)c * kSortBuckets + b]; hist[(size_t)c * kSortBuckets + b] = run; run += v; }
+    s_tot[b] = run;
+    __syncthreads();
+    unsigned base = 0;
+    for (int k = 0; k < b; ++k) base += s_tot[k];
+    for (int c = 0; c < nchunks; ++c) hist[(size_t)c * kSortBuckets + b] += base;
+}
+__global__ void __launch_bounds__(256) k_sort_scatter(const unsigned long long* __restrict__ vis, const int* __restrict__ in, int row0, int n,
+                                                     int pass, int npass, const unsigned* __restrict__ hist, int* __restrict__ out) {
+    __shared__ unsigned s_off[kSortBuckets];          // next output position per bucket
+    __shared__ unsigned s_wcnt[8][kSortBuckets];      // rows of the current tile per warp and bucket
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    s_off[threadIdx.x] = hist[(size_t)blockIdx.x * kSortBuckets + threadIdx.x];
+    const int c0 = blockIdx.x * kSortChunk;
+    for (int t0 = c0; t0 < c0 + kSortChunk && t0 < n; t0 += 256) {
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s_wcnt[w][threadIdx.x] = 0u;
+        __syncthreads();
+        const int i = t0 + threadIdx.x;
+        const bool inr = i < n && i < c0 + kSortChunk;
+        const int row = inr ? (in ? in[i] : row0 + i) : -1;
+        const int b = inr ? sort_digit(vis[row], pass, npass) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, b);
+        const unsigned rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        if (inr && rank_in_warp == 0) s_wcnt[warp][b] = __popc(peers);
+        __syncthreads();
+        if (inr) {
+            unsigned pos = s_off[b] + rank_in_warp;
+            for (int w = 0; w < warp; ++w) pos += s_wcnt[w][b];
+            out[pos] = row;
+        }
+        __syncthreads();
+        {
+            unsigned add = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) add += s_wcnt[w][threadIdx.x];
+            s_off[threadIdx.x] += add;
+        }
+        __syncthreads();
     }
 }
 
@@ -315,19 +379,23 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
     o->prefix.alloc((size_t)nw);
     o->block_counts.alloc((size_t)nblocks + 1);
 
-    { Prof pf(o->stream, KID_SURF_MASK); k_surface_mask<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, nw, (int)wpb); }
+    o->block_pairs.alloc((size_t)nblocks + 8);
+    unsigned long long* totals_dev = reinterpret_cast<unsigned long long*>(o->block_pairs.p + (((size_t)nblocks + 1) & ~(size_t)1));   // 8-byte aligned
+    { Prof pf(o->stream, KID_SURF_MASK); k_surface_mask<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->block_pairs.p, nw, (int)wpb); }
     PSG_LAUNCH_CHECK();
-    { Prof pf(o->stream, KID_SURF_SCAN); k_scan_counts<<<1, 1024, 0, o->stream>>>(o->block_counts.p, nblocks); }
+    { Prof pf(o->stream, KID_SURF_SCAN); k_scan_counts<<<1, 1024, 0, o->stream>>>(o->block_counts.p, nblocks, o->block_pairs.p, totals_dev); }
     PSG_LAUNCH_CHECK();
-    unsigned total = 0;
-    PSG_CUDA(cudaMemcpyAsync(&total, o->block_counts.p + nblocks, sizeof(unsigned), cudaMemcpyDeviceToHost, o->stream));
+    // the one host round trip of the build: the row count sizes everything below, the pair count decides the sharding policy
+    unsigned long long totals[2] = {0ull, 0ull};
+    PSG_CUDA(cudaMemcpyAsync(totals, totals_dev, sizeof(totals), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
-    o->S = (int)total;
+    o->S = (int)totals[0];
+    o->vis_pairs = (long long)totals[1];
     const size_t S = (size_t)(o->S > 0 ? o->S : 1);
     o->lin.alloc(S); o->svis.alloc(S); o->nbr_lin.alloc(3 * S); o->nbr_row.alloc(3 * S); o->pos.alloc(S); o->inc.alloc(6 * S);
     o->rec0.alloc(S); o->rec1.alloc(S + 32 * 65);   // rec1 is all-gathered in equal, 32-aligned chunks (comm.cu)
     o->rec0.alloc(S); o->rec2.alloc(S); o->rec3.alloc(S); o->rec4.alloc(S);
-    o->pvis.alloc(S); o->perm.alloc(S); o->sort_keys.alloc(S); o->sort_vals.alloc(S);
+    o->pvis.alloc(S); o->perm.alloc(S);
     if (o->S > 0) {
         { Prof pf(o->stream, KID_SURF_SCATTER);
           k_surface_scatter<<<nblocks, 256, 0, o->stream>>>(v, P, o->mask.p, o->block_counts.p, o->prefix.p, nw, (int)wpb,
@@ -338,18 +406,6 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
                                                                  o->nbr_row.p, o->pos.p, o->inc.p); }
         PSG_LAUNCH_CHECK();
     }
-    o->vis_pairs = 0;
-    if (o->S > 0) {
-        unsigned long long* cnt = reinterpret_cast<unsigned long long*>(o->sort_keys.p);   // free again after the sort
-        PSG_CUDA(cudaMemsetAsync(cnt, 0, sizeof(*cnt), o->stream));
-        k_count_pairs<<<(o->S + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->S, cnt);
-        PSG_LAUNCH_CHECK();
-        count_launch(1);
-        unsigned long long h = 0;
-        PSG_CUDA(cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, o->stream));
-        PSG_CUDA(cudaStreamSynchronize(o->stream));
-        o->vis_pairs = (long long)h;
-    }
     PSG_CUDA(cudaStreamSynchronize(o->stream));
     update_shard_policy(o);
     o->layout_dirty = true;
@@ -357,26 +413,33 @@ void build_surface(psg_optimizer* o, bool /*reindex_vis*/) {
 }
 
 // Everything that depends on how the rows are divided among the ranks: the row range this rank owns (all rows unless the
-// work list is sharded), its slot list = its rows in sweep order (stable radix sort by keyframe visibility), the slot records,
+// work list is sharded), its slot list = its rows in sweep order (radix sort by keyframe visibility), the slot records,
 // the buffers an outer iteration uses, and -- sharded -- the peers' views of each other's buffers.  Collective when sharded.
 void build_layout(psg_optimizer* o) {
     o->layout_dirty = false;
     release_peers(o);                 // nothing below may reallocate a buffer a peer still maps
     partition_rows(o);                // row_lo / row_hi / n_slots, halo ranges (comm.cu); whole list when not sharded
     if (o->n_slots > 0) {
-        // slot order: stable radix sort of the rows by keyframe-visibility word (set-up time only; CUB library sort)
+        // slot order: radix sort by (64 - visible keyframes, visibility word), see above
         const int n = o->n_slots;
-        o->sort_keys2.alloc((size_t)n);
-        k_sort_keys<<<(n + 255) / 256, 256, 0, o->stream>>>(o->svis.p, o->sort_keys.p, o->sort_vals.p, o->row_lo, n, o->F);
-        PSG_LAUNCH_CHECK();
-        const int end_bit = o->F <= 57 ? o->F + 7 : 64;
-        size_t tmp_bytes = 0;
-        PSG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p, n,
-                                                 0, end_bit, o->stream));
-        o->sort_tmp.alloc(tmp_bytes);
-        PSG_CUDA(cub::DeviceRadixSort::SortPairs(o->sort_tmp.p, tmp_bytes, o->sort_keys.p, o->sort_keys2.p, o->sort_vals.p, o->perm.p,
-                                                 n, 0, end_bit, o->stream));
-        count_launch(4);
+        const int nchunks = (n + kSortChunk - 1) / kSortChunk;
+        const int npass = (o->F + 7) / 8 + 1;
+        o->sort_hist.alloc((size_t)nchunks * kSortBuckets);
+        o->perm2.alloc((size_t)(o->S > 0 ? o->S : 1));
+        // ping-pong so that the last pass lands in o->perm
+        int* bufs[2] = { (npass & 1) ? o->perm.p : o->perm2.p, (npass & 1) ? o->perm2.p : o->perm.p };
+        const int* in = nullptr;
+        for (int pass = 0; pass < npass; ++pass) {
+            int* out = bufs[pass & 1];
+            k_sort_hist<<<nchunks, 256, 0, o->stream>>>(o->svis.p, in, o->row_lo, n, pass, npass, o->sort_hist.p);
+            PSG_LAUNCH_CHECK();
+            k_sort_scan<<<1, 256, 0, o->stream>>>(o->sort_hist.p, nchunks);
+            PSG_LAUNCH_CHECK();
+            k_sort_scatter<<<nchunks, 256, 0, o->stream>>>(o->svis.p, in, o->row_lo, n, pass, npass, o->sort_hist.p, out);
+            PSG_LAUNCH_CHECK();
+            in = out;
+        }
+        count_launch(3 * npass);
     }
     refresh_records(o);
     // everything the blocks of an outer iteration use is sized here, once per work list, so that the iteration path itself

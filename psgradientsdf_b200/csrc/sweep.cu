@@ -827,6 +827,7 @@ double* red_dev(psg_optimizer* o) { return o->red.p + kMailDoubles; }
 const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
+    trace("[rank %d] fetch_mail: red %zu, slots %d..%d, reg %d, sharded %d", o->rank, o->reduce_red, o->reduce_lo, o->reduce_hi, (int)o->reduce_reg, (int)o->sharded);
     if (o->world > 1 && (o->reduce_hi >= o->reduce_lo || o->reduce_reg)) {
         if (o->sharded) {
             // one all-reduce for everything queued since the last round trip: per-keyframe sums, the scalar slots in flight and
@@ -845,6 +846,7 @@ const double* fetch_mail(psg_optimizer* o, size_t n) {
     }
     PSG_CUDA(cudaMemcpyAsync(h, o->red.p, (kMailDoubles + n) * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
+    trace("[rank %d] fetch_mail done", o->rank);
     return h;
 }
 const double* mail_slot(const psg_optimizer* o, int slot) { return o->host_staging + 8 * slot; }

@@ -157,3 +157,40 @@ def test_two_ranks_match_one_gpu(model, policy):
                         str(policy)], capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
     assert "multi-gpu check" in r.stdout
+
+
+def test_local_ranks_second_handoff():
+    """A sharded job that receives new keyframes (psg_opt_set_keyframes + psg_opt_init again: the work list, the partition and the
+    peers' mappings are rebuilt) continues like a fresh one."""
+    import psgradientsdf_b200 as psg
+    model, G, world = "SH1", 40, 2
+    sc = scene(model)
+    vols, opts = [], []
+    for r in range(world):
+        gv, go = make_gpu(model, G, sc)
+        vols.append(gv); opts.append(go)
+    psg.comm_init_local(opts)
+    psg.run_ranks(lambda r: opts[r].set_shard_policy(1), world)
+
+    def body(r):
+        o = opts[r]
+        out = []
+        for rep in range(3):
+            handoff(o, sc)
+            o.init_albedo()
+            info = o.iteration(damping=1.0, normal_reg=True)
+            out.append((info["energy_end"], info["n_active_end"], info["dist"]["iters"], o.row_range()))
+        return out
+
+    res = psg.run_ranks(body, world)
+    for rep in range(3):   # the volume moves between the hand-offs, so the lists differ from one to the next -- but never between ranks
+        assert res[0][rep][:3] == res[1][rep][:3], (rep, res[0][rep], res[1][rep])
+        assert res[0][rep][2] > 3 and res[0][rep][1] > 0
+        assert res[0][rep][3][0] == 0 and res[0][rep][3][1] == res[1][rep][3][0]
+    a, b = vols[0].download(), vols[1].download()     # the last psg_opt_init synchronised them; the last iteration did not
+    surf = opts[0].surface()
+    assert np.array_equal(surf, opts[1].surface())
+    psg.run_ranks(lambda r: opts[r].sync_volume(), world)
+    a, b = vols[0].download(), vols[1].download()
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    psg.run_ranks(lambda r: opts[r].comm_destroy(), world)
