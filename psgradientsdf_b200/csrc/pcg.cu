@@ -1049,7 +1049,7 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
 // fence anywhere.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers) instead of
 // hanging.  On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative launch: block
 // b belongs to rank b / nb.
-enum HaloKind { HK_B2 = 0, HK_B5, HK_B9, HK_B11, HK_B12, HK_B13, HK_Z, HK_P0, HK_P1, HK_U1, HK_U2, HK_U3, HK_D };
+enum HaloKind { HK_B2 = 0, HK_B5, HK_B9, HK_B11, HK_B12, HK_B13, HK_Z, HK_U1, HK_U2, HK_U3, HK_D };
 static_assert(HK_D + 1 == kHaloKinds, "halo kinds");
 
 struct MgSeg { int peer, b, e, hbase, nh; };   // own rows [b, e) are halo rows hbase + row of rank `peer`, whose halo has nh rows
@@ -1062,7 +1062,7 @@ struct MgRank {
     float* vecs; float* pbuf; XState* xs; unsigned long long* halo;
     const int* nbr_row; const int* inc; const int* lin;
     VolView vol; SurfView surf;
-    double* partials;               // [2][nb]
+    double* partials;               // [3][nb]
     float* result;                  // iterations, residualNorm2, rhsNorm2, threshold, abort flag
     double* regslot;                // {normal, laplacian, albedo energy sums, accepted updates}: partial sums over the own rows
 };
@@ -1142,15 +1142,15 @@ __device__ __forceinline__ float halo_get(MgCtx& c, int kind, int row, unsigned 
 // rank order -- identical bits in every block of every rank.  The own rank's packet doubles as the local release: it is sent
 // only after all local blocks have arrived.
 template <bool REDUCE>
-__device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, double* s_buf /* 2 * NW + 3 */) {
+__device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, double d, double* s_buf /* 3 * NW + 4 */) {
     constexpr int NW = kMgBlock / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const MgArgs& A = *c.A; const MgRank& R = *c.R;
     XState* xs = R.xs;
-    double* P0 = R.partials; double* P1 = R.partials + c.nb;
+    double* P0 = R.partials; double* P1 = R.partials + c.nb; double* P2 = R.partials + 2 * c.nb;
     if (REDUCE) {
-        a = warp_sum(a); b = warp_sum(b);
-        if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; }
+        a = warp_sum(a); b = warp_sum(b); d = warp_sum(d);
+        if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; s_buf[2 * NW + warp] = d; }
     }
     __syncthreads();
     ++c.k;
@@ -1161,12 +1161,12 @@ __device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, doub
             asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
             unsigned long long v;
             if (!spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v)) c.ok = false;
-            s_buf[2 * NW + 2] = c.ok ? 0.0 : 1.0;
+            s_buf[3 * NW + 3] = c.ok ? 0.0 : 1.0;
         }
         __syncthreads();
-        if (s_buf[2 * NW + 2] != 0.0) c.ok = false;
+        if (s_buf[3 * NW + 3] != 0.0) c.ok = false;
         __syncthreads();
-        return make_double2(0.0, 0.0);
+        return make_double3(0.0, 0.0, 0.0);
     }
     // mailbox parity and packet tag count REDUCTIONS: a peer can be at most one reduction ahead, so two buffers suffice
     ++c.kr;
@@ -1174,11 +1174,11 @@ __device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, doub
     const int par = (int)(er & 1ull);
     const unsigned tag = (unsigned)er;
     if (warp == 0) {
-        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0;
-        ta = warp_sum(ta); tb = warp_sum(tb);
+        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0, td = lane < NW ? s_buf[2 * NW + lane] : 0.0;
+        ta = warp_sum(ta); tb = warp_sum(tb); td = warp_sum(td);
         bool ok = true;
         if (lane == 0) {
-            P0[c.lb] = ta; P1[c.lb] = tb;
+            P0[c.lb] = ta; P1[c.lb] = tb; P2[c.lb] = td;
             asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
         }
         if (c.lb == 0) {
@@ -1187,30 +1187,36 @@ __device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, doub
                 ok = spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v);
             }
             ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
-            double xa = 0.0, xb = 0.0;
-            for (int i = lane; i < c.nb; i += 32) { xa += __ldcg(P0 + i); xb += __ldcg(P1 + i); }
-            xa = warp_sum(xa); xb = warp_sum(xb);
+            double xa = 0.0, xb = 0.0, xd = 0.0;
+            for (int i = lane; i < c.nb; i += 32) { xa += __ldcg(P0 + i); xb += __ldcg(P1 + i); xd += __ldcg(P2 + i); }
+            xa = warp_sum(xa); xb = warp_sum(xb); xd = warp_sum(xd);
             __threadfence();   // what the arrivals made visible to this block, before the packet that releases the others
             if (lane < A.world) {
                 unsigned long long* dst = &A.peer[lane].xs->ll[par][R.rank][0];
-                const unsigned long long ua = (unsigned long long)__double_as_longlong(xa), ub = (unsigned long long)__double_as_longlong(xb);
                 const unsigned long long th = (unsigned long long)tag << 32;
                 if (!ok) st_vol64(&A.peer[lane].xs->abort, 1ull);
-                st_vol64(dst + 0, th | (ua & 0xffffffffull)); st_vol64(dst + 1, th | (ua >> 32));
-                st_vol64(dst + 2, th | (ub & 0xffffffffull)); st_vol64(dst + 3, th | (ub >> 32));
+                const double v3[3] = { xa, xb, xd };
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    const unsigned long long u = (unsigned long long)__double_as_longlong(v3[i]);
+                    st_vol64(dst + 2 * i, th | (u & 0xffffffffull)); st_vol64(dst + 2 * i + 1, th | (u >> 32));
+                }
             }
         }
         // every block: the sums of all ranks from the own mailbox
-        double xa = 0.0, xb = 0.0;
+        double xa = 0.0, xb = 0.0, xd = 0.0;
         if (lane < A.world) {
             const unsigned long long* src = &xs->ll[par][lane][0];
-            unsigned long long w[4];
+            unsigned long long w[6];
             unsigned spins = 0;
             unsigned long long t0 = 0;
-            for (;;) {   // the four packets of a sender are polled together: one round trip when they are there
+            for (;;) {   // the packets of a sender are polled together: one round trip when they are there
+                bool all = true;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) w[i] = ld_vol64(src + i);
-                if ((unsigned)(w[0] >> 32) == tag && (unsigned)(w[1] >> 32) == tag && (unsigned)(w[2] >> 32) == tag && (unsigned)(w[3] >> 32) == tag) break;
+                for (int i = 0; i < 6; ++i) w[i] = ld_vol64(src + i);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) all = all && (unsigned)(w[i] >> 32) == tag;
+                if (all) break;
                 if ((++spins & 255u) == 0) {
                     if (ld_vol64(&xs->abort)) { ok = false; break; }
                     const unsigned long long now = global_ns();
@@ -1220,26 +1226,29 @@ __device__ __forceinline__ double2 mg_barrier(MgCtx& c, double a, double b, doub
             }
             xa = __longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[1] << 32)));
             xb = __longlong_as_double((long long)((w[2] & 0xffffffffull) | (w[3] << 32)));
+            xd = __longlong_as_double((long long)((w[4] & 0xffffffffull) | (w[5] << 32)));
         }
         ok = __all_sync(0xffffffffu, ok);
-        double sa = 0.0, sb = 0.0;
-        for (int q = 0; q < A.world; ++q) { sa += __shfl_sync(0xffffffffu, xa, q); sb += __shfl_sync(0xffffffffu, xb, q); }   // rank order
+        double sa = 0.0, sb = 0.0, sd = 0.0;
+        for (int q = 0; q < A.world; ++q) {   // rank order
+            sa += __shfl_sync(0xffffffffu, xa, q); sb += __shfl_sync(0xffffffffu, xb, q); sd += __shfl_sync(0xffffffffu, xd, q);
+        }
         __threadfence();   // the packet was a relaxed load: order the other blocks' data behind it
         if (lane == 0) {
-            s_buf[2 * NW] = sa; s_buf[2 * NW + 1] = sb;
+            s_buf[3 * NW] = sa; s_buf[3 * NW + 1] = sb; s_buf[3 * NW + 2] = sd;
             if (!ok) st_vol64(&xs->abort, 1ull);
-            s_buf[2 * NW + 2] = ok ? 0.0 : 1.0;
+            s_buf[3 * NW + 3] = ok ? 0.0 : 1.0;
         }
     }
     __syncthreads();
-    if (s_buf[2 * NW + 2] != 0.0) c.ok = false;
-    const double2 out = make_double2(s_buf[2 * NW], s_buf[2 * NW + 1]);
+    if (s_buf[3 * NW + 3] != 0.0) c.ok = false;
+    const double3 out = make_double3(s_buf[3 * NW], s_buf[3 * NW + 1], s_buf[3 * NW + 2]);
     __syncthreads();   // s_buf is reused by the next call
     return out;
 }
 
 __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
-    __shared__ double s_buf[2 * (kMgBlock / 32) + 4];
+    __shared__ double s_buf[3 * (kMgBlock / 32) + 4];
     __shared__ double s_reg[kMgBlock / 32][4];
     const MgArgs& A = *Ap;
     const int nb = A.nb;
@@ -1251,8 +1260,11 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     const int T = nb * kMgBlock, ltid = c.lb * kMgBlock + threadIdx.x;
     const size_t PS = (size_t)S;
     float* V = R.vecs;
+    float* Pp = R.pbuf;              // search direction p
+    float* Sp = R.pbuf + PS;         // s = A p
     const float tol = 1.1920929e-07f;
     auto own = [&](int row) { return row >= lo && row < hi; };
+    // vecs planes: 0..13 stencil blocks | 14 rhs | 15 1/diag | 16 damping*diag | 17 x | 18 u = r/diag | 19 r | 20 w = A u | 21..24 U
 
     // ---- the stencil planes the neighbours' assembly reads: rhs of slots 1..3 and the diagonal entries (a+1, a+1)
     for (int s = lo + ltid; s < hi; s += T) {
@@ -1261,9 +1273,8 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
 #pragma unroll
         for (int i = 0; i < 6; ++i) halo_push(c, HK_B2 + i, s, V[planes[i] * PS + s]);
     }
-    mg_barrier<false>(c, 0.0, 0.0, s_buf);
-    // ---- k_dist_assemble on the own rows; x = 0, r = b, z = b / diag, p = z
-    double a0 = 0.0, a1 = 0.0;
+    mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
+    // ---- k_dist_assemble on the own rows; x = 0, r = b, u = b / diag, p = s = 0
     {
         const unsigned tg = c.tag_prev();
         for (int s = lo + ltid; s < hi; s += T) {
@@ -1280,153 +1291,146 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             const float dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
             const float full = diag + dd;
             const float invd = (full != 0.f) ? 1.f / full : 1.f;
-            const float z = invd * rhs;
+            const float u = invd * rhs;
             V[14 * PS + s] = rhs; V[15 * PS + s] = invd; V[16 * PS + s] = dd; V[17 * PS + s] = 0.f; V[19 * PS + s] = rhs;
-            V[18 * PS + s] = z; R.pbuf[s] = z;
-            halo_push(c, HK_Z, s, z); halo_push(c, HK_P0, s, z);
-            a0 += (double)rhs * (double)rhs; a1 += (double)rhs * (double)z;
+            V[18 * PS + s] = u; Pp[s] = 0.f; Sp[s] = 0.f;
+            halo_push(c, HK_Z, s, u);
         }
     }
-    unsigned tag_pc = c.tag_now();   // tag of the packets of the current search direction
-    const double2 t01 = mg_barrier<true>(c, a0, a1, s_buf);
-    const float rhsNorm2 = (float)t01.x;
-    float absNew = (float)t01.y;
+    // The CG runs in the Chronopoulos-Gear arrangement: with u = M^-1 r, w = A u and the recurrences p = u + beta p, s = w + beta s
+    // (= A p), one fused reduction per iteration yields gamma = (r, u), delta = (w, u) and |r|^2, from which beta = gamma / gamma_old and
+    // alpha = gamma / (delta - beta gamma / alpha_old).  Same iterates as Eigen's loop in exact arithmetic, same iteration counts on
+    // every system tried (profiles/r2_summary.md); one cross-rank reduction per iteration instead of two.
+    // One "matrix pass" = stencil products from u (phase B), barrier, gather into w with the three dot products (phase C).
+    auto matrix_pass = [&](double& g_ru, double& d_wu, double& n_rr) {
+        mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
+        {   // ---- phase B: u_t = A_t * u[stencil(t)], rows in batches (all loads of a batch are issued before any is used)
+            const unsigned tu = c.tag_prev();
+            for (int base = lo + ltid; base < hi; base += T * kMgRows) {
+                int col[kMgRows][3];
+                float uc[kMgRows][4];
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j) {
+                    const int s = base + j * T;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) col[j][a] = s < hi ? __ldg(R.nbr_row + (size_t)a * S + s) : -1;
+                }
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j) {
+                    const int s = base + j * T;
+                    const int s0 = s < hi ? s : lo;
+                    uc[j][0] = __ldcg(V + 18 * PS + s0);
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int cc = col[j][a];
+                        uc[j][a + 1] = __ldcg(V + 18 * PS + ((cc >= 0 && own(cc)) ? cc : s0));
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j) {
+                    const int s = base + j * T;
+                    if (s >= hi) continue;
+                    float px[4];
+                    px[0] = uc[j][0];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int cc = col[j][a];
+                        px[a + 1] = cc < 0 ? 0.f : (own(cc) ? uc[j][a + 1] : halo_get(c, HK_Z, cc, tu));
+                    }
+                    float Ab[10];
+#pragma unroll
+                    for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float u = 0.f;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                            if (k == 0 || col[j][k - 1] >= 0) u += aik * px[k];
+                        }
+                        const bool valid = (i == 0) || col[j][i - 1] >= 0;
+                        const float uv = valid ? u : 0.f;
+                        V[(size_t)(21 + i) * PS + s] = uv;
+                        if (i > 0) halo_push(c, HK_U1 + i - 1, s, uv);
+                    }
+                }
+            }
+        }
+        mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
+        {   // ---- phase C: w = u_s[0] + incident u + damping * diag * u_s ; (r, u), (w, u), (r, r)
+            const unsigned tU = c.tag_prev();
+            for (int base = lo + ltid; base < hi; base += T * kMgRows) {
+                int tn[kMgRows][6];
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j)
+#pragma unroll
+                    for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < hi) ? __ldg(R.inc + (size_t)h * S + base + j * T) : -1;
+                float uu[kMgRows][7], us[kMgRows], dg[kMgRows], rs[kMgRows];
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j) {
+                    const int s = base + j * T;
+                    const int s0 = s < hi ? s : lo;
+                    uu[j][0] = V[21 * PS + s0]; us[j] = V[18 * PS + s0]; dg[j] = V[16 * PS + s0]; rs[j] = V[19 * PS + s0];
+#pragma unroll
+                    for (int h = 0; h < 6; ++h) {
+                        const int t = tn[j][h];
+                        uu[j][h + 1] = (t >= 0 && own(t)) ? __ldcg(V + (size_t)(22 + h % 3) * PS + t) : 0.f;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < kMgRows; ++j) {
+                    const int s = base + j * T;
+                    if (s >= hi) continue;
+                    float w = uu[j][0];
+#pragma unroll
+                    for (int h = 0; h < 6; ++h) {
+                        const int t = tn[j][h];
+                        if (t < 0) continue;
+                        w += own(t) ? uu[j][h + 1] : halo_get(c, HK_U1 + h % 3, t, tU);
+                    }
+                    w += dg[j] * us[j];
+                    V[20 * PS + s] = w;
+                    g_ru += (double)rs[j] * (double)us[j];
+                    d_wu += (double)w * (double)us[j];
+                    n_rr += (double)rs[j] * (double)rs[j];
+                }
+            }
+        }
+    };
+    double g0 = 0.0, d0 = 0.0, n0 = 0.0;
+    matrix_pass(g0, d0, n0);
+    const double3 t0 = mg_barrier<true>(c, g0, d0, n0, s_buf);
+    const float rhsNorm2 = (float)t0.z;
+    float gamma = (float)t0.x;
+    float alpha = gamma / (float)t0.y, beta = 0.f;
     float threshold = tol * tol * rhsNorm2;
     if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
     float residualNorm2 = rhsNorm2;
     int it = 0;
     if (c.ok && rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
-        float gamma = 0.f, beta = 1.f;   // first pass: the published p already is the search direction
-        int cur = 0;
         while (it < A.max_iters) {
-            const float* pc = R.pbuf + (size_t)cur * PS;
-            float* pn = R.pbuf + (size_t)(cur ^ 1) * PS;
-            // ---- phase 1: p <- z + beta p (neighbours recomputed from the published z and p), u_t = A_t * p[stencil(t)]
-            // rows in batches of kMgRows: all loads of a batch are issued before any is used; halo neighbours (rare) afterwards
-            {
-                const unsigned tz = c.tag_prev();
-                for (int base = lo + ltid; base < hi; base += T * kMgRows) {
-                    int col[kMgRows][3];
-                    float zc[kMgRows][4], pv[kMgRows][4];
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j) {
-                        const int s = base + j * T;
-                        const bool in = s < hi;
-#pragma unroll
-                        for (int a = 0; a < 3; ++a) col[j][a] = in ? __ldg(R.nbr_row + (size_t)a * S + s) : -1;
-                    }
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j) {
-                        const int s = base + j * T;
-                        const int s0 = s < hi ? s : lo;
-                        zc[j][0] = __ldcg(V + 18 * PS + s0); pv[j][0] = __ldcg(pc + s0);
-#pragma unroll
-                        for (int a = 0; a < 3; ++a) {
-                            const int cc = col[j][a];
-                            const int ci = (cc >= 0 && own(cc)) ? cc : s0;
-                            zc[j][a + 1] = __ldcg(V + 18 * PS + ci); pv[j][a + 1] = __ldcg(pc + ci);
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j) {
-                        const int s = base + j * T;
-                        if (s >= hi) continue;
-                        float px[4];
-                        px[0] = zc[j][0] * gamma + beta * pv[j][0];
-#pragma unroll
-                        for (int a = 0; a < 3; ++a) {
-                            const int cc = col[j][a];
-                            if (cc < 0) px[a + 1] = 0.f;
-                            else if (own(cc)) px[a + 1] = zc[j][a + 1] * gamma + beta * pv[j][a + 1];
-                            else px[a + 1] = halo_get(c, HK_Z, cc, tz) * gamma + beta * halo_get(c, HK_P0 + cur, cc, tag_pc);
-                        }
-                        pn[s] = px[0];
-                        halo_push(c, HK_P0 + (cur ^ 1), s, px[0]);
-                        float Ab[10];
-#pragma unroll
-                        for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            float u = 0.f;
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
-                                if (k == 0 || col[j][k - 1] >= 0) u += aik * px[k];
-                            }
-                            const bool valid = (i == 0) || col[j][i - 1] >= 0;
-                            const float uv = valid ? u : 0.f;
-                            V[(size_t)(21 + i) * PS + s] = uv;
-                            if (i > 0) halo_push(c, HK_U1 + i - 1, s, uv);
-                        }
-                    }
-                }
-            }
-            const unsigned tag_pn = c.tag_now();
-            mg_barrier<false>(c, 0.0, 0.0, s_buf);
-            if (!c.ok) break;
-            // ---- phase 2: y = u_s[0] + incident u + damping * diag * p_s ; p . y
-            double pAp = 0.0;
-            {
-                const unsigned tu = c.tag_prev();
-                for (int base = lo + ltid; base < hi; base += T * kMgRows) {
-                    int tn[kMgRows][6];
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j)
-#pragma unroll
-                        for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < hi) ? __ldg(R.inc + (size_t)h * S + base + j * T) : -1;
-                    float uu[kMgRows][7], ps[kMgRows], dg[kMgRows];
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j) {
-                        const int s = base + j * T;
-                        const int s0 = s < hi ? s : lo;
-                        uu[j][0] = V[21 * PS + s0]; ps[j] = pn[s0]; dg[j] = V[16 * PS + s0];
-#pragma unroll
-                        for (int h = 0; h < 6; ++h) {
-                            const int t = tn[j][h];
-                            uu[j][h + 1] = (t >= 0 && own(t)) ? __ldcg(V + (size_t)(22 + h % 3) * PS + t) : 0.f;
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < kMgRows; ++j) {
-                        const int s = base + j * T;
-                        if (s >= hi) continue;
-                        float y = uu[j][0];
-#pragma unroll
-                        for (int h = 0; h < 6; ++h) {
-                            const int t = tn[j][h];
-                            if (t < 0) continue;
-                            y += own(t) ? uu[j][h + 1] : halo_get(c, HK_U1 + h % 3, t, tu);
-                        }
-                        y += dg[j] * ps[j];
-                        V[20 * PS + s] = y;
-                        pAp += (double)ps[j] * (double)y;
-                    }
-                }
-            }
-            const float alpha = absNew / (float)mg_barrier<true>(c, pAp, 0.0, s_buf).x;
-            if (!c.ok) break;
-            // ---- phase 3 (own rows): x += alpha p ; r -= alpha y ; z = r / diag, published ; norms
-            double rn = 0.0, rz = 0.0;
+            // ---- phase A (own rows): p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; u = r / diag, published
             for (int s = lo + ltid; s < hi; s += T) {
-                const float ps = pn[s];
-                V[17 * PS + s] = V[17 * PS + s] + alpha * ps;
-                const float r2 = V[19 * PS + s] - alpha * V[20 * PS + s];
+                const float pnew = V[18 * PS + s] + beta * Pp[s];
+                const float snew = V[20 * PS + s] + beta * Sp[s];
+                Pp[s] = pnew; Sp[s] = snew;
+                V[17 * PS + s] = V[17 * PS + s] + alpha * pnew;
+                const float r2 = V[19 * PS + s] - alpha * snew;
                 V[19 * PS + s] = r2;
-                const float z = V[15 * PS + s] * r2;
-                V[18 * PS + s] = z;
-                halo_push(c, HK_Z, s, z);
-                rn += (double)r2 * (double)r2; rz += (double)r2 * (double)z;
+                const float u = V[15 * PS + s] * r2;
+                V[18 * PS + s] = u;
+                halo_push(c, HK_Z, s, u);
             }
-            const double2 t12 = mg_barrier<true>(c, rn, rz, s_buf);
+            double g1 = 0.0, d1 = 0.0, n1 = 0.0;
+            matrix_pass(g1, d1, n1);
+            const double3 t1 = mg_barrier<true>(c, g1, d1, n1, s_buf);
             if (!c.ok) break;
-            residualNorm2 = (float)t12.x;
+            residualNorm2 = (float)t1.z;
             if (residualNorm2 < threshold) break;
-            const float absOld = absNew;
-            absNew = (float)t12.y;
-            beta = absNew / absOld;
-            gamma = 1.f;
-            cur ^= 1;
-            tag_pc = tag_pn;
+            const float gnew = (float)t1.x;
+            beta = gnew / gamma;
+            alpha = gnew / ((float)t1.y - beta * gnew / alpha);
+            gamma = gnew;
             ++it;
         }
     } else if (rhsNorm2 == 0.f) {
@@ -1456,7 +1460,7 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             R.vol.dist[R.lin[row]] = halo_get(c, HK_D, row, td);
         }
     }
-    mg_barrier<false>(c, 0.0, 0.0, s_buf);
+    mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
     // ---- Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records of the own slots
     if (apply) {
         for (int t = ltid; t < R.surf.nslots; t += T) {

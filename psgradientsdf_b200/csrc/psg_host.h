@@ -70,7 +70,7 @@ struct XState {
     unsigned long long epoch_r;            // ... of which barriers with a cross-rank reduction (mailbox parity and packet tags)
     unsigned long long arrive;             // arrivals of the owner's blocks at the current barrier (reset by the owner at the end of a launch)
     unsigned long long abort;              // sticky: a wait ran into its time limit
-    unsigned long long ll[2][kMaxRanks][4];   // [reduction parity][sender][word]: two doubles as four (tag << 32 | 32 data bits) packets, written by the sender
+    unsigned long long ll[2][kMaxRanks][6];   // [reduction parity][sender][word]: three doubles as six (tag << 32 | 32 data bits) packets, written by the sender
 };
 
 // what a rank exposes to its peers
@@ -78,7 +78,7 @@ struct PeerView {
     unsigned long long* halo = nullptr;   // kHaloKinds planes of nh (tag << 32 | float bits) packets: the owner's halo rows, written by their owners
     XState* xs = nullptr;
 };
-constexpr int kHaloKinds = 13;   // stencil planes 2, 5, 9, 11, 12, 13 | z | p (two buffers) | U1..U3 | distance
+constexpr int kHaloKinds = 11;   // stencil planes 2, 5, 9, 11, 12, 13 | u = r / diag | U1..U3 | distance
 }  // namespace psg
 
 struct psg_volume {

@@ -44,6 +44,7 @@ opt.comm_init(ids[0], rank, world)
 opt.set_shard_policy(int(sys.argv[3]) if len(sys.argv) > 3 else 1)   # default: force sharding (the test scene is tiny)
 opt.init_albedo()
 log = [opt.energy()]
+psg.profile_reset(); psg.profile_enable(True)
 for it in range(2):
     for blk in block_order(model):
         info = opt.step(blk, damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
@@ -52,6 +53,8 @@ log.append(opt.energy())
 it_info = opt.iteration(damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))   # the three-wait pass, sharded
 log.append((it_info["energy_end"], it_info["n_active_end"]))
 regs = (it_info["reg_normal_after_dist"], it_info["reg_laplacian_after_dist"])
+prof = {k: round(1e3 * v[1] / v[0], 1) for k, v in psg.profile_table().items()}
+psg.profile_enable(False)
 opt.sync_volume()        # sharded: every rank receives the others' rows
 state = vol.download()
 # all ranks must hold the same state
@@ -83,6 +86,7 @@ if rank == 0:
     d_rms = float(np.sqrt(np.mean((state[surf, 0].astype(np.float64) - s1[surf, 0]) ** 2))) / vs
     a_rms = float(np.sqrt(np.mean((state[surf, 5:8].astype(np.float64) - s1[surf, 5:8]) ** 2)))
     print(f"multi-gpu check: world={world} model={model} G={G} S={opt1.S} sharded={opt.is_sharded()[0]} rows={opt.row_range()} "
+          f"kernel us {prof} CG iterations {[x[2] for x in log if len(x) == 3]} "
           f"worst relative energy difference {worst:.3e}, "
           f"final RMS distance {d_rms:.3e} voxels, albedo {a_rms:.3e}")
     assert worst < 5e-6 and d_rms < 1e-4 and a_rms < 1e-4
