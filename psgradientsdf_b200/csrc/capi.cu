@@ -376,7 +376,7 @@ int psg_opt_destroy(psg_optimizer* o) {
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_hist.release(); o->perm2.release(); o->block_pairs.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);
-    o->areg.release(); o->mg_args.release();
+    o->areg.release(); o->mg_args.release(); o->xplanes.release(); o->halo.release();
     o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
     delete o;
     return PSG_OK;
@@ -609,7 +609,7 @@ int psg_opt_set_upload_overlap(psg_optimizer* o, int on) {
 
 int psg_opt_set_pcg_mode(psg_optimizer* o, int mode) {
     if (!o) { set_error("null optimizer"); return PSG_ERR_INVALID; }
-    if (mode < 0 || mode > 7) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 7", mode); return PSG_ERR_INVALID; }
+    if (mode < 0 || mode > 8) { set_error("psg_opt_set_pcg_mode: %d is not 0 .. 8", mode); return PSG_ERR_INVALID; }
     o->pcg_mode = mode;
     return PSG_OK;
 }
@@ -748,7 +748,7 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
         launch_dist_sweep(o, flags, slot);
         // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242).  The
         // verdict stays on the device: the update kernels read it, the host learns it with the next round trip.
-        if (o->sharded) {
+        if (o->sharded || o->pcg_mode == 8) {   // 8: the dataflow kernel on one GPU
             launch_dist_block_mg(o, damping, /*only_on_success=*/!led, reg_energies_after);
         } else if (!launch_dist_block_small(o, damping, /*only_on_success=*/!led, reg_energies_after ? kSlotReg : -1)) {
             launch_dist_solve(o, damping);

@@ -349,11 +349,6 @@ void exchange_peers(psg_optimizer* o) {
     if (!o->sharded) return;
     trace("[rank %d] exchange_peers: rows %d..%d of %d", o->rank, o->row_lo, o->row_hi, o->S);
     if (o->world > kMaxRanks) { set_error("a sharded job has at most %d ranks (%d given)", kMaxRanks, o->world); throw CudaError{-1}; }
-    if (!o->xstate.p) {
-        o->xstate.alloc(sizeof(XState));
-        PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, sizeof(XState), o->stream));
-        PSG_CUDA(cudaStreamSynchronize(o->stream));
-    }
     // halo packets of this rank: one per halo row and kind, tags start at zero (= never written)
     const int nh = (o->row_lo - o->halo_lo[o->rank]) + (o->halo_hi[o->rank] - o->row_hi);
     const size_t hcount = (size_t)kHaloKinds * (size_t)(nh > 0 ? nh : 1);

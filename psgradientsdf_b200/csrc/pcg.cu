@@ -1033,22 +1033,25 @@ __global__ void __launch_bounds__(kClusterBlock) k_dist_pcg_cluster(PcgArgs A, f
     }
 }
 
-// ---- the distance block of a sharded job: one persistent kernel per rank, halo and reductions over peer memory ----------------
-// Rank g owns rows [lo, hi) of the surface list (a z-slab).  Its kernel runs k_dist_assemble, the CG, Optimizer::updateDist,
-// updateGrad and the regulariser energies on those rows.  What it needs from other ranks are the entries of a few vectors at its
-// HALO rows (other ranks' rows within one z-plane of its range).  Their owners push them: whoever computes a row that lies in a
-// peer's halo also stores it, through the peer's mapped pointer (NVLink), into the peer's halo buffer as ONE 8-byte packet
-// (tag << 32 | float bits).  An 8-byte store is indivisible, so the reader needs no fence and no barrier for halo data: it
-// polls the packet until it carries the tag of the phase that produced the value (tag = number of barriers the job has passed
-// when the value is produced, + 1 -- every rank counts the same barriers, launches included, so tags never repeat).  A packet is
-// overwritten only after a cross-rank reduction both sides took part in, i.e. after its reader has consumed it.
-// Barriers between phases are LOCAL (the rank's blocks; arrival counter + release word at gpu scope, as in the single-GPU
-// kernels); where the CG needs a dot product the rank's leader block adds the local partials, sends them to every rank as four
-// tagged packets (XState::ll, double-buffered by barrier parity), collects everybody's, adds them in rank order -- every rank
-// forms the same sum bit for bit, hence takes the same branches -- and releases its blocks with the totals.  No system-scope
-// fence anywhere.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers) instead of
-// hanging.  On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative launch: block
-// b belongs to rank b / nb.
+// ---- the distance block as a dataflow kernel: one persistent launch per rank, no barrier inside a CG iteration but its reduction
+// Rank g owns rows [lo, hi) of the surface list (a z-slab; all rows on one GPU).  Its kernel runs k_dist_assemble, the CG,
+// Optimizer::updateDist, updateGrad and the regulariser energies on those rows.
+// Every vector entry that ANOTHER thread reads -- u = r / diag at a row's finite-difference neighbours, the stencil products
+// U1..U3 at the stencils that contain a row -- is stored as ONE 8-byte packet (tag << 32 | float bits).  An 8-byte store is
+// indivisible, so a reader needs neither fence nor barrier: it polls the packet until it carries the tag of the phase that
+// produced the value (tags count the producing phases of the job, launches included: every rank counts the same, tags never
+// repeat).  Own rows' packets live in the rank's planes; rows in a peer's halo (other ranks' rows within one z-plane of its
+// range) are ALSO stored, through the peer's mapped pointer (NVLink), into the peer's halo buffer.  Threads therefore run
+// ahead as far as their inputs allow; the only barrier of an iteration is its dot-product reduction, which also protects the
+// packets: a packet is overwritten only after a reduction that its readers contributed to after reading it.
+// The CG runs in the Chronopoulos-Gear arrangement (u = M^-1 r, w = A u, p = u + beta p, s = w + beta s): ONE fused reduction per
+// iteration yields (r, u), (w, u) and |r|^2.  Reduction: blocks publish partial sums and arrive on the rank's counter; the rank's
+// leader block adds them and sends the rank's sums to every rank (its own included) as six tagged packets (XState::ll,
+// double-buffered by reduction parity); EVERY block polls its rank's mailbox until the packets of all ranks carry the
+// reduction's tag and adds them in rank order -- identical bits in every block of every rank, hence identical branches.
+// No system-scope fence anywhere.  Every wait gives up after `timeout_ns` and raises a sticky abort flag (here and at the peers)
+// instead of hanging.  On a single device the ranks of a job (threads of one process, comm.cu) are played by ONE cooperative
+// launch: block b belongs to rank b / nb.
 enum HaloKind { HK_B2 = 0, HK_B5, HK_B9, HK_B11, HK_B12, HK_B13, HK_Z, HK_U1, HK_U2, HK_U3, HK_D };
 static_assert(HK_D + 1 == kHaloKinds, "halo kinds");
 
@@ -1060,9 +1063,10 @@ struct MgRank {
     MgSeg seg[2 * (kMaxRanks - 1)];
     int inner_lo, inner_hi;         // rows in [inner_lo, inner_hi) are in nobody's halo
     float* vecs; float* pbuf; XState* xs; unsigned long long* halo;
+    unsigned long long* xp;         // 4 planes of S packets: u, U1, U2, U3 of the own rows
     const int* nbr_row; const int* inc; const int* lin;
     VolView vol; SurfView surf;
-    double* partials;               // [3][nb]
+    double* partials;               // [2][3][nb]
     float* result;                  // iterations, residualNorm2, rhsNorm2, threshold, abort flag
     double* regslot;                // {normal, laplacian, albedo energy sums, accepted updates}: partial sums over the own rows
 };
@@ -1078,7 +1082,7 @@ struct MgArgs {
 };
 
 constexpr int kMgBlock = 512;
-constexpr int kMgRows = 4;      // rows per thread and batch in the gather phases
+constexpr int kMgRows = 2;      // rows per thread and batch in the gather phases
 
 __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long* p) {
@@ -1087,6 +1091,13 @@ __device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long*
     return v;
 }
 __device__ __forceinline__ void st_vol64(unsigned long long* p, unsigned long long v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+// packets that only this GPU's threads exchange: gpu scope (read from / written to L2, never through an L1) is enough and cheaper
+__device__ __forceinline__ unsigned long long ld_gpu64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_gpu64(unsigned long long* p, unsigned long long v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
 // spin until pred(value) holds; false after the time limit or once the abort flag is up
 template <typename Load, typename Pred>
@@ -1111,27 +1122,59 @@ struct MgCtx {
     unsigned long long base;         // barriers completed by earlier launches
     unsigned long long base_r;       // ... of which reductions
     unsigned k, kr;                  // barriers / reductions completed by this launch
+    unsigned tg;                     // last value tag handed out (a producing phase takes the next one)
     bool ok;
-    __device__ __forceinline__ unsigned tag_now() const { return (unsigned)(base + k) + 1u; }   // tag of values produced in the current phase
-    __device__ __forceinline__ unsigned tag_prev() const { return (unsigned)(base + k); }       // ... in the phase before the last barrier
 };
 
 // push one value of an own row to every rank that has the row in its halo
-__device__ __forceinline__ void halo_push(const MgCtx& c, int kind, int s, float v) {
+__device__ __forceinline__ void halo_push(const MgCtx& c, int kind, int s, float v, unsigned tag) {
     const MgRank& R = *c.R;
     if (s >= R.inner_lo && s < R.inner_hi) return;
-    const unsigned long long pkt = ((unsigned long long)c.tag_now() << 32) | (unsigned long long)__float_as_uint(v);
+    const unsigned long long pkt = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
     for (int i = 0; i < R.nseg; ++i)
         if (s >= R.seg[i].b && s < R.seg[i].e)
             st_vol64(c.A->peer[R.seg[i].peer].halo + (size_t)kind * R.seg[i].nh + (R.seg[i].hbase + s), pkt);
 }
-// a halo row's value of `kind` carrying `tag`
+// poll a packet until it carries `tag`
+__device__ __noinline__ unsigned long long packet_spin(MgCtx& c, const unsigned long long* p, unsigned tag) {
+    unsigned long long v;
+    const bool local = p >= c.R->xp && p < c.R->xp + 4 * (size_t)c.A->S;   // own planes: gpu scope; halo buffer (written by peers): system scope
+    if (!spin_until([&] { return local ? ld_gpu64(p) : ld_vol64(p); }, [&](unsigned long long x) { return (unsigned)(x >> 32) == tag; }, c.R->xs, c.A->timeout_ns, &v)) c.ok = false;
+    return v;
+}
+__device__ __forceinline__ unsigned long long packet_load(const MgCtx& c, int kind, int row) {
+    const MgRank& R = *c.R;
+    if (row >= R.lo && row < R.hi) return ld_gpu64(R.xp + (size_t)kind * (size_t)c.A->S + row);
+    const int h = row < R.lo ? row - R.halo_lo : (R.lo - R.halo_lo) + (row - R.hi);
+    return ld_vol64(R.halo + (size_t)(HK_Z + kind) * R.nh + h);
+}
+// where the packet of `kind` (0 = u, 1..3 = U1..U3) of row `row` lives for this rank: its own planes, or its halo buffer
+__device__ __forceinline__ const unsigned long long* packet_addr(const MgCtx& c, int kind, int row) {
+    const MgRank& R = *c.R;
+    if (row >= R.lo && row < R.hi) return R.xp + (size_t)kind * (size_t)c.A->S + row;
+    const int h = row < R.lo ? row - R.halo_lo : (R.lo - R.halo_lo) + (row - R.hi);
+    return R.halo + (size_t)(HK_Z + kind) * R.nh + h;
+}
+// every 256th unsuccessful poll: give up (false) once the abort flag is up or the time limit has passed
+__device__ __noinline__ bool wait_may_continue(MgCtx& c, unsigned long long& t0) {
+    XState* xs = c.R->xs;
+    if (ld_vol64(&xs->abort)) { c.ok = false; return false; }
+    const unsigned long long now = global_ns();
+    if (!t0) { t0 = now; return true; }
+    if (now - t0 > c.A->timeout_ns) { st_vol64(&xs->abort, 1ull); c.ok = false; return false; }
+    return true;
+}
+__device__ __forceinline__ void packet_put(const MgCtx& c, int kind, int s, float v, unsigned tag) {
+    st_gpu64(c.R->xp + (size_t)kind * (size_t)c.A->S + s, ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v));
+    halo_push(c, HK_Z + kind, s, v, tag);
+}
+// a halo row's value of `kind` carrying `tag` (prologue / epilogue quantities, which have no planes of their own)
 __device__ __forceinline__ float halo_get(MgCtx& c, int kind, int row, unsigned tag) {
     const MgRank& R = *c.R;
     const int h = row < R.lo ? row - R.halo_lo : (R.lo - R.halo_lo) + (row - R.hi);
     const unsigned long long* p = R.halo + (size_t)kind * R.nh + h;
-    unsigned long long v;
-    if (!spin_until([&] { return ld_vol64(p); }, [&](unsigned long long x) { return (unsigned)(x >> 32) == tag; }, R.xs, c.A->timeout_ns, &v)) c.ok = false;
+    unsigned long long v = ld_vol64(p);
+    if ((unsigned)(v >> 32) != tag) v = packet_spin(c, p, tag);
     return __uint_as_float((unsigned)v);
 }
 
@@ -1147,7 +1190,8 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const MgArgs& A = *c.A; const MgRank& R = *c.R;
     XState* xs = R.xs;
-    double* P0 = R.partials; double* P1 = R.partials + c.nb; double* P2 = R.partials + 2 * c.nb;
+    // partial sums double-buffered by reduction parity: a block may publish for the next reduction while a slower one still adds up this one
+    double* P0 = R.partials + (size_t)((c.kr + 1) & 1u) * 3 * c.nb; double* P1 = P0 + c.nb; double* P2 = P0 + 2 * c.nb;
     if (REDUCE) {
         a = warp_sum(a); b = warp_sum(b); d = warp_sum(d);
         if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; s_buf[2 * NW + warp] = d; }
@@ -1155,12 +1199,14 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
     __syncthreads();
     ++c.k;
     const unsigned long long target = (unsigned long long)c.k * (unsigned long long)c.nb;
-    auto load_arrive = [&] { unsigned long long x; asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(x) : "l"(&xs->arrive) : "memory"); return x; };
+    // relaxed polls (an acquire per poll would invalidate the L1 every time); one fence after the wait orders what follows
+    auto load_arrive = [&] { return ld_gpu64(&xs->arrive); };
     if (!REDUCE) {
         if (threadIdx.x == 0) {
             asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
             unsigned long long v;
             if (!spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v)) c.ok = false;
+            __threadfence();
             s_buf[3 * NW + 3] = c.ok ? 0.0 : 1.0;
         }
         __syncthreads();
@@ -1173,7 +1219,24 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
     const unsigned long long er = c.base_r + c.kr;
     const int par = (int)(er & 1ull);
     const unsigned tag = (unsigned)er;
-    if (warp == 0) {
+    if (warp == 0 && A.world == 1) {
+        // one rank: every block waits for the arrivals and adds the partials itself, in block order (no mailbox round trip)
+        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0, td = lane < NW ? s_buf[2 * NW + lane] : 0.0;
+        ta = warp_sum(ta); tb = warp_sum(tb); td = warp_sum(td);
+        bool ok = true;
+        if (lane == 0) {
+            P0[c.lb] = ta; P1[c.lb] = tb; P2[c.lb] = td;
+            asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&xs->arrive) : "memory");
+            unsigned long long v;
+            ok = spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v);
+            __threadfence();
+        }
+        ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+        double xa = 0.0, xb = 0.0, xd = 0.0;
+        for (int i = lane; i < c.nb; i += 32) { xa += __ldcg(P0 + i); xb += __ldcg(P1 + i); xd += __ldcg(P2 + i); }
+        xa = warp_sum(xa); xb = warp_sum(xb); xd = warp_sum(xd);
+        if (lane == 0) { s_buf[3 * NW] = xa; s_buf[3 * NW + 1] = xb; s_buf[3 * NW + 2] = xd; s_buf[3 * NW + 3] = ok ? 0.0 : 1.0; }
+    } else if (warp == 0) {
         double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0, td = lane < NW ? s_buf[2 * NW + lane] : 0.0;
         ta = warp_sum(ta); tb = warp_sum(tb); td = warp_sum(td);
         bool ok = true;
@@ -1185,6 +1248,7 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
             if (lane == 0) {
                 unsigned long long v;
                 ok = spin_until(load_arrive, [&](unsigned long long x) { return x >= target; }, xs, A.timeout_ns, &v);
+                __threadfence();
             }
             ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
             double xa = 0.0, xb = 0.0, xd = 0.0;
@@ -1247,6 +1311,8 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
     return out;
 }
 
+// ONE_ROW: the rank has at most one row per thread; the row's whole CG state then lives in registers
+template <bool ONE_ROW>
 __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
     __shared__ double s_buf[3 * (kMgBlock / 32) + 4];
     __shared__ double s_reg[kMgBlock / 32][4];
@@ -1255,7 +1321,7 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     const MgRank& R = A.loc[blockIdx.x / nb];
     MgCtx c;
     c.A = &A; c.R = &R; c.lb = blockIdx.x % nb; c.nb = nb; c.k = 0; c.kr = 0; c.ok = true;
-    c.base = __ldcg(&R.xs->epoch); c.base_r = __ldcg(&R.xs->epoch_r);
+    c.base = __ldcg(&R.xs->epoch); c.base_r = __ldcg(&R.xs->epoch_r); c.tg = (unsigned)__ldcg(&R.xs->epoch_t);
     const int S = A.S, lo = R.lo, hi = R.hi;
     const int T = nb * kMgBlock, ltid = c.lb * kMgBlock + threadIdx.x;
     const size_t PS = (size_t)S;
@@ -1264,29 +1330,153 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     float* Sp = R.pbuf + PS;         // s = A p
     const float tol = 1.1920929e-07f;
     auto own = [&](int row) { return row >= lo && row < hi; };
-    // vecs planes: 0..13 stencil blocks | 14 rhs | 15 1/diag | 16 damping*diag | 17 x | 18 u = r/diag | 19 r | 20 w = A u | 21..24 U
+    // vecs planes: 0..13 stencil blocks | 14 rhs | 15 1/diag | 16 damping*diag | 17 x | 18 u = r/diag | 19 r | 20 w = A u | 21 U0
 
     // ---- the stencil planes the neighbours' assembly reads: rhs of slots 1..3 and the diagonal entries (a+1, a+1)
+    const unsigned t_stencil = ++c.tg;
     for (int s = lo + ltid; s < hi; s += T) {
         if (s >= R.inner_lo && s < R.inner_hi) continue;
         const int planes[6] = { 2, 5, 9, 11, 12, 13 };
 #pragma unroll
-        for (int i = 0; i < 6; ++i) halo_push(c, HK_B2 + i, s, V[planes[i] * PS + s]);
+        for (int i = 0; i < 6; ++i) halo_push(c, HK_B2 + i, s, V[planes[i] * PS + s], t_stencil);
     }
-    mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
-    // ---- k_dist_assemble on the own rows; x = 0, r = b, u = b / diag, p = s = 0
-    {
-        const unsigned tg = c.tag_prev();
+    unsigned t_u = 0;
+    float rhsNorm2 = 0.f, threshold = 0.f, residualNorm2 = 0.f;
+    int it = 0;
+    if constexpr (ONE_ROW) {
+        // ---- one row per thread: assembly, then the whole solve with the row's state in registers
+        const int s = lo + ltid;
+        const bool in = s < hi;
+        int col[3] = { -1, -1, -1 }, tn[6] = { -1, -1, -1, -1, -1, -1 };
+        const unsigned long long* pu[3] = { nullptr, nullptr, nullptr };     // u packets of the finite-difference neighbours
+        const unsigned long long* pU[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };   // U packets of the incident stencils
+        float Ab[10], invd = 0.f, dd = 0.f, x = 0.f, r = 0.f, u = 0.f, p = 0.f, sv = 0.f, w = 0.f;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) Ab[i] = 0.f;
+        t_u = ++c.tg;
+        if (in) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { col[a] = __ldg(R.nbr_row + (size_t)a * S + s); if (col[a] >= 0) pu[a] = packet_addr(c, 0, col[a]); }
+#pragma unroll
+            for (int h = 0; h < 6; ++h) { tn[h] = __ldg(R.inc + (size_t)h * S + s); if (tn[h] >= 0) pU[h] = packet_addr(c, 1 + h % 3, tn[h]); }
+#pragma unroll
+            for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
+            float rhs = __ldg(V + 10 * PS + s), diag = Ab[0];
+#pragma unroll
+            for (int h = 0; h < 6; ++h) {
+                const int t = tn[h], a = h % 3;
+                if (t < 0) continue;
+                if (own(t)) { rhs += __ldg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
+                else { rhs += halo_get(c, HK_B11 + a, t, t_stencil); diag += halo_get(c, HK_B2 + a, t, t_stencil); }
+            }
+            dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
+            const float full = diag + dd;
+            invd = (full != 0.f) ? 1.f / full : 1.f;
+            r = rhs; u = invd * rhs;
+            V[14 * PS + s] = rhs;          // diagnostics (psg_opt_last_vectors)
+            packet_put(c, 0, s, u, t_u);
+        }
+        auto matrix_pass1 = [&](double& g_ru, double& d_wu, double& n_rr) {
+            const unsigned tU = ++c.tg;
+            if (in) {
+                // all packets of a phase are polled TOGETHER: one round trip per attempt, however many of them are late
+                unsigned long long pk[3];
+                {
+                    unsigned spins = 0; unsigned long long t0 = 0;
+                    for (;;) {
+                        bool all = true;
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) pk[a] = pu[a] ? (own(col[a]) ? ld_gpu64(pu[a]) : ld_vol64(pu[a])) : 0ull;
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) all = all && (!pu[a] || (unsigned)(pk[a] >> 32) == t_u);
+                        if (all) break;
+                        if ((++spins & 255u) == 0 && !wait_may_continue(c, t0)) break;
+                    }
+                }
+                float px[4];
+                px[0] = u;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) px[a + 1] = pu[a] ? __uint_as_float((unsigned)pk[a]) : 0.f;
+                float u0 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float uu = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                        if (k == 0 || col[k - 1] >= 0) uu += aik * px[k];
+                    }
+                    const bool valid = (i == 0) || col[i - 1] >= 0;
+                    if (i == 0) u0 = uu; else packet_put(c, i, s, valid ? uu : 0.f, tU);
+                }
+                unsigned long long qk[6];
+                {
+                    unsigned spins = 0; unsigned long long t0 = 0;
+                    for (;;) {
+                        bool all = true;
+#pragma unroll
+                        for (int h = 0; h < 6; ++h) qk[h] = pU[h] ? (own(tn[h]) ? ld_gpu64(pU[h]) : ld_vol64(pU[h])) : 0ull;
+#pragma unroll
+                        for (int h = 0; h < 6; ++h) all = all && (!pU[h] || (unsigned)(qk[h] >> 32) == tU);
+                        if (all) break;
+                        if ((++spins & 255u) == 0 && !wait_may_continue(c, t0)) break;
+                    }
+                }
+                w = u0;
+#pragma unroll
+                for (int h = 0; h < 6; ++h)
+                    if (pU[h]) w += __uint_as_float((unsigned)qk[h]);
+                w += dd * u;
+                g_ru += (double)r * (double)u; d_wu += (double)w * (double)u; n_rr += (double)r * (double)r;
+            }
+        };
+        double g0 = 0.0, d0 = 0.0, n0 = 0.0;
+        matrix_pass1(g0, d0, n0);
+        const double3 t0 = mg_barrier<true>(c, g0, d0, n0, s_buf);
+        rhsNorm2 = (float)t0.z;
+        float gamma = (float)t0.x;
+        float alpha = gamma / (float)t0.y, beta = 0.f;
+        threshold = tol * tol * rhsNorm2;
+        if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+        residualNorm2 = rhsNorm2;
+        if (c.ok && rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+            while (it < A.max_iters) {
+                t_u = ++c.tg;
+                if (in) {
+                    p = u + beta * p; sv = w + beta * sv;
+                    x += alpha * p; r = r - alpha * sv;
+                    u = invd * r;
+                    packet_put(c, 0, s, u, t_u);
+                }
+                double g1 = 0.0, d1 = 0.0, n1 = 0.0;
+                matrix_pass1(g1, d1, n1);
+                const double3 t1 = mg_barrier<true>(c, g1, d1, n1, s_buf);
+                if (!c.ok) break;
+                residualNorm2 = (float)t1.z;
+                if (residualNorm2 < threshold) break;
+                const float gnew = (float)t1.x;
+                beta = gnew / gamma;
+                alpha = gnew / ((float)t1.y - beta * gnew / alpha);
+                gamma = gnew;
+                ++it;
+            }
+        } else if (rhsNorm2 == 0.f) {
+            residualNorm2 = 0.f;
+        }
+        if (in) V[17 * PS + s] = x;
+    } else {
+        // ---- k_dist_assemble on the own rows; x = 0, r = b, u = b / diag, p = s = 0
+        t_u = ++c.tg;
         for (int s = lo + ltid; s < hi; s += T) {
             float rhs = V[10 * PS + s], diag = V[s];
-#pragma unroll
+    #pragma unroll
             for (int h = 0; h < 2; ++h)
-#pragma unroll
+    #pragma unroll
                 for (int a = 0; a < 3; ++a) {
                     const int t = __ldg(R.inc + (size_t)(h * 3 + a) * S + s);
                     if (t < 0) continue;
-                    if (own(t)) { rhs += __ldcg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldcg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
-                    else { rhs += halo_get(c, HK_B11 + a, t, tg); diag += halo_get(c, HK_B2 + a, t, tg); }
+                    if (own(t)) { rhs += __ldg(V + (size_t)(10 + a + 1) * PS + t); diag += __ldg(V + (size_t)tri(a + 1, a + 1) * PS + t); }
+                    else { rhs += halo_get(c, HK_B11 + a, t, t_stencil); diag += halo_get(c, HK_B2 + a, t, t_stencil); }
                 }
             const float dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
             const float full = diag + dd;
@@ -1294,100 +1484,112 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             const float u = invd * rhs;
             V[14 * PS + s] = rhs; V[15 * PS + s] = invd; V[16 * PS + s] = dd; V[17 * PS + s] = 0.f; V[19 * PS + s] = rhs;
             V[18 * PS + s] = u; Pp[s] = 0.f; Sp[s] = 0.f;
-            halo_push(c, HK_Z, s, u);
+            packet_put(c, 0, s, u, t_u);
         }
-    }
-    // The CG runs in the Chronopoulos-Gear arrangement: with u = M^-1 r, w = A u and the recurrences p = u + beta p, s = w + beta s
-    // (= A p), one fused reduction per iteration yields gamma = (r, u), delta = (w, u) and |r|^2, from which beta = gamma / gamma_old and
-    // alpha = gamma / (delta - beta gamma / alpha_old).  Same iterates as Eigen's loop in exact arithmetic, same iteration counts on
-    // every system tried (profiles/r2_summary.md); one cross-rank reduction per iteration instead of two.
-    // One "matrix pass" = stencil products from u (phase B), barrier, gather into w with the three dot products (phase C).
-    auto matrix_pass = [&](double& g_ru, double& d_wu, double& n_rr) {
-        mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
-        {   // ---- phase B: u_t = A_t * u[stencil(t)], rows in batches (all loads of a batch are issued before any is used)
-            const unsigned tu = c.tag_prev();
+        // One "matrix pass" = stencil products from u (phase B), gather into w with the three dot products (phase C); no barrier
+        // in between: the gathers wait for the packets they need.
+        auto matrix_pass = [&](double& g_ru, double& d_wu, double& n_rr) {
+            const unsigned tU = ++c.tg;
+            // ---- phase B: u_t = A_t * u[stencil(t)], rows in batches (all loads of a batch are issued before any is used)
             for (int base = lo + ltid; base < hi; base += T * kMgRows) {
                 int col[kMgRows][3];
-                float uc[kMgRows][4];
-#pragma unroll
+                unsigned long long pk[kMgRows][3];
+                float u0[kMgRows];
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j) {
                     const int s = base + j * T;
-#pragma unroll
+    #pragma unroll
                     for (int a = 0; a < 3; ++a) col[j][a] = s < hi ? __ldg(R.nbr_row + (size_t)a * S + s) : -1;
                 }
-#pragma unroll
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j) {
                     const int s = base + j * T;
-                    const int s0 = s < hi ? s : lo;
-                    uc[j][0] = __ldcg(V + 18 * PS + s0);
+                    u0[j] = V[18 * PS + (s < hi ? s : lo)];
+    #pragma unroll
+                    for (int a = 0; a < 3; ++a) pk[j][a] = col[j][a] >= 0 ? packet_load(c, 0, col[j][a]) : 0ull;
+                }
+                {   // late packets: poll the whole batch together
+                    unsigned spins = 0; unsigned long long t0 = 0;
+                    for (;;) {
+                        bool all = true;
 #pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        const int cc = col[j][a];
-                        uc[j][a + 1] = __ldcg(V + 18 * PS + ((cc >= 0 && own(cc)) ? cc : s0));
+                        for (int j = 0; j < kMgRows; ++j)
+#pragma unroll
+                            for (int a = 0; a < 3; ++a) all = all && (col[j][a] < 0 || (unsigned)(pk[j][a] >> 32) == t_u);
+                        if (all) break;
+                        if ((++spins & 255u) == 0 && !wait_may_continue(c, t0)) break;
+#pragma unroll
+                        for (int j = 0; j < kMgRows; ++j)
+#pragma unroll
+                            for (int a = 0; a < 3; ++a) if (col[j][a] >= 0 && (unsigned)(pk[j][a] >> 32) != t_u) pk[j][a] = packet_load(c, 0, col[j][a]);
                     }
                 }
-#pragma unroll
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j) {
                     const int s = base + j * T;
                     if (s >= hi) continue;
                     float px[4];
-                    px[0] = uc[j][0];
-#pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        const int cc = col[j][a];
-                        px[a + 1] = cc < 0 ? 0.f : (own(cc) ? uc[j][a + 1] : halo_get(c, HK_Z, cc, tu));
-                    }
+                    px[0] = u0[j];
+    #pragma unroll
+                    for (int a = 0; a < 3; ++a) px[a + 1] = col[j][a] >= 0 ? __uint_as_float((unsigned)pk[j][a]) : 0.f;
                     float Ab[10];
-#pragma unroll
+    #pragma unroll
                     for (int i = 0; i < 10; ++i) Ab[i] = __ldg(V + (size_t)i * PS + s);
-#pragma unroll
+    #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         float u = 0.f;
-#pragma unroll
+    #pragma unroll
                         for (int k = 0; k < 4; ++k) {
                             const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
                             if (k == 0 || col[j][k - 1] >= 0) u += aik * px[k];
                         }
                         const bool valid = (i == 0) || col[j][i - 1] >= 0;
                         const float uv = valid ? u : 0.f;
-                        V[(size_t)(21 + i) * PS + s] = uv;
-                        if (i > 0) halo_push(c, HK_U1 + i - 1, s, uv);
+                        if (i == 0) V[21 * PS + s] = uv; else packet_put(c, i, s, uv, tU);
                     }
                 }
             }
-        }
-        mg_barrier<false>(c, 0.0, 0.0, 0.0, s_buf);
-        {   // ---- phase C: w = u_s[0] + incident u + damping * diag * u_s ; (r, u), (w, u), (r, r)
-            const unsigned tU = c.tag_prev();
+            // ---- phase C: w = u_s[0] + incident u + damping * diag * u_s ; (r, u), (w, u), (r, r)
             for (int base = lo + ltid; base < hi; base += T * kMgRows) {
                 int tn[kMgRows][6];
-#pragma unroll
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j)
-#pragma unroll
+    #pragma unroll
                     for (int h = 0; h < 6; ++h) tn[j][h] = (base + j * T < hi) ? __ldg(R.inc + (size_t)h * S + base + j * T) : -1;
-                float uu[kMgRows][7], us[kMgRows], dg[kMgRows], rs[kMgRows];
-#pragma unroll
+                unsigned long long pk[kMgRows][6];
+                float uu[kMgRows], us[kMgRows], dg[kMgRows], rs[kMgRows];
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j) {
                     const int s = base + j * T;
                     const int s0 = s < hi ? s : lo;
-                    uu[j][0] = V[21 * PS + s0]; us[j] = V[18 * PS + s0]; dg[j] = V[16 * PS + s0]; rs[j] = V[19 * PS + s0];
+                    uu[j] = V[21 * PS + s0]; us[j] = V[18 * PS + s0]; dg[j] = V[16 * PS + s0]; rs[j] = V[19 * PS + s0];
+    #pragma unroll
+                    for (int h = 0; h < 6; ++h) pk[j][h] = tn[j][h] >= 0 ? packet_load(c, 1 + h % 3, tn[j][h]) : 0ull;
+                }
+                {
+                    unsigned spins = 0; unsigned long long t0 = 0;
+                    for (;;) {
+                        bool all = true;
 #pragma unroll
-                    for (int h = 0; h < 6; ++h) {
-                        const int t = tn[j][h];
-                        uu[j][h + 1] = (t >= 0 && own(t)) ? __ldcg(V + (size_t)(22 + h % 3) * PS + t) : 0.f;
+                        for (int j = 0; j < kMgRows; ++j)
+#pragma unroll
+                            for (int h = 0; h < 6; ++h) all = all && (tn[j][h] < 0 || (unsigned)(pk[j][h] >> 32) == tU);
+                        if (all) break;
+                        if ((++spins & 255u) == 0 && !wait_may_continue(c, t0)) break;
+#pragma unroll
+                        for (int j = 0; j < kMgRows; ++j)
+#pragma unroll
+                            for (int h = 0; h < 6; ++h) if (tn[j][h] >= 0 && (unsigned)(pk[j][h] >> 32) != tU) pk[j][h] = packet_load(c, 1 + h % 3, tn[j][h]);
                     }
                 }
-#pragma unroll
+    #pragma unroll
                 for (int j = 0; j < kMgRows; ++j) {
                     const int s = base + j * T;
                     if (s >= hi) continue;
-                    float w = uu[j][0];
-#pragma unroll
-                    for (int h = 0; h < 6; ++h) {
-                        const int t = tn[j][h];
-                        if (t < 0) continue;
-                        w += own(t) ? uu[j][h + 1] : halo_get(c, HK_U1 + h % 3, t, tU);
-                    }
+                    float w = uu[j];
+    #pragma unroll
+                    for (int h = 0; h < 6; ++h)
+                        if (tn[j][h] >= 0) w += __uint_as_float((unsigned)pk[j][h]);
                     w += dg[j] * us[j];
                     V[20 * PS + s] = w;
                     g_ru += (double)rs[j] * (double)us[j];
@@ -1395,46 +1597,46 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
                     n_rr += (double)rs[j] * (double)rs[j];
                 }
             }
-        }
-    };
-    double g0 = 0.0, d0 = 0.0, n0 = 0.0;
-    matrix_pass(g0, d0, n0);
-    const double3 t0 = mg_barrier<true>(c, g0, d0, n0, s_buf);
-    const float rhsNorm2 = (float)t0.z;
-    float gamma = (float)t0.x;
-    float alpha = gamma / (float)t0.y, beta = 0.f;
-    float threshold = tol * tol * rhsNorm2;
-    if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
-    float residualNorm2 = rhsNorm2;
-    int it = 0;
-    if (c.ok && rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
-        while (it < A.max_iters) {
-            // ---- phase A (own rows): p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; u = r / diag, published
-            for (int s = lo + ltid; s < hi; s += T) {
-                const float pnew = V[18 * PS + s] + beta * Pp[s];
-                const float snew = V[20 * PS + s] + beta * Sp[s];
-                Pp[s] = pnew; Sp[s] = snew;
-                V[17 * PS + s] = V[17 * PS + s] + alpha * pnew;
-                const float r2 = V[19 * PS + s] - alpha * snew;
-                V[19 * PS + s] = r2;
-                const float u = V[15 * PS + s] * r2;
-                V[18 * PS + s] = u;
-                halo_push(c, HK_Z, s, u);
+        };
+        double g0 = 0.0, d0 = 0.0, n0 = 0.0;
+        matrix_pass(g0, d0, n0);
+        const double3 t0 = mg_barrier<true>(c, g0, d0, n0, s_buf);
+        rhsNorm2 = (float)t0.z;
+        float gamma = (float)t0.x;
+        float alpha = gamma / (float)t0.y, beta = 0.f;
+        threshold = tol * tol * rhsNorm2;
+        if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+        residualNorm2 = rhsNorm2;
+        if (c.ok && rhsNorm2 != 0.f && !(residualNorm2 < threshold)) {
+            while (it < A.max_iters) {
+                // ---- phase A (own rows): p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; u = r / diag, published
+                t_u = ++c.tg;
+                for (int s = lo + ltid; s < hi; s += T) {
+                    const float pnew = V[18 * PS + s] + beta * Pp[s];
+                    const float snew = V[20 * PS + s] + beta * Sp[s];
+                    Pp[s] = pnew; Sp[s] = snew;
+                    V[17 * PS + s] = V[17 * PS + s] + alpha * pnew;
+                    const float r2 = V[19 * PS + s] - alpha * snew;
+                    V[19 * PS + s] = r2;
+                    const float u = V[15 * PS + s] * r2;
+                    V[18 * PS + s] = u;
+                    packet_put(c, 0, s, u, t_u);
+                }
+                double g1 = 0.0, d1 = 0.0, n1 = 0.0;
+                matrix_pass(g1, d1, n1);
+                const double3 t1 = mg_barrier<true>(c, g1, d1, n1, s_buf);
+                if (!c.ok) break;
+                residualNorm2 = (float)t1.z;
+                if (residualNorm2 < threshold) break;
+                const float gnew = (float)t1.x;
+                beta = gnew / gamma;
+                alpha = gnew / ((float)t1.y - beta * gnew / alpha);
+                gamma = gnew;
+                ++it;
             }
-            double g1 = 0.0, d1 = 0.0, n1 = 0.0;
-            matrix_pass(g1, d1, n1);
-            const double3 t1 = mg_barrier<true>(c, g1, d1, n1, s_buf);
-            if (!c.ok) break;
-            residualNorm2 = (float)t1.z;
-            if (residualNorm2 < threshold) break;
-            const float gnew = (float)t1.x;
-            beta = gnew / gamma;
-            alpha = gnew / ((float)t1.y - beta * gnew / alpha);
-            gamma = gnew;
-            ++it;
+        } else if (rhsNorm2 == 0.f) {
+            residualNorm2 = 0.f;
         }
-    } else if (rhsNorm2 == 0.f) {
-        residualNorm2 = 0.f;
     }
     if (ltid == 0) {
         R.result[0] = (float)it; R.result[1] = residualNorm2; R.result[2] = rhsNorm2; R.result[3] = threshold;
@@ -1443,6 +1645,7 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
     const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
     const bool apply = c.ok && (!A.only_on_success || err <= tol);
     double acc = 0.0;
+    const unsigned t_dist = ++c.tg;
     for (int s = lo + ltid; s < hi; s += T) {
         const int lin = R.lin[s];
         float d = R.vol.dist[lin];
@@ -1450,11 +1653,11 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
             const float x = V[17 * PS + s];
             if (fabs((double)x) < A.thr) { d -= x; R.vol.dist[lin] = d; acc += 1.0; }
         }
-        halo_push(c, HK_D, s, d);
+        halo_push(c, HK_D, s, d, t_dist);
     }
     // the halo rows' distances into the own distance plane (the finite differences and the Laplacian read it by voxel index)
     {
-        const unsigned td = c.tag_now();
+        const unsigned td = t_dist;
         for (int h = ltid; h < R.nh; h += T) {
             const int row = h < lo - R.halo_lo ? R.halo_lo + h : hi + (h - (lo - R.halo_lo));
             R.vol.dist[R.lin[row]] = halo_get(c, HK_D, row, td);
@@ -1526,6 +1729,7 @@ __global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __r
         R.xs->arrive = 0ull;
         R.xs->epoch = c.base + c.k;
         R.xs->epoch_r = c.base_r + c.kr;
+        R.xs->epoch_t = (unsigned long long)c.tg;
     }
 }
 
@@ -2032,30 +2236,33 @@ void launch_dist_update(psg_optimizer* o, bool only_on_success) {
 // ---- sharded job: the distance block after the sweep -------------------------------------------------------------------------
 static void fill_mg_rank(psg_optimizer* o, MgRank* R) {
     memset(R, 0, sizeof(*R));
-    R->rank = o->rank; R->lo = o->row_lo; R->hi = o->row_hi;
-    R->halo_lo = o->halo_lo[o->rank]; R->halo_hi = o->halo_hi[o->rank];
+    const int world = o->sharded ? o->world : 1, rank = o->sharded ? o->rank : 0;
+    R->rank = rank; R->lo = o->row_lo; R->hi = o->row_hi;
+    R->halo_lo = o->halo_lo[rank]; R->halo_hi = o->halo_hi[rank];
+    if (!o->sharded) { R->halo_lo = R->lo; R->halo_hi = R->hi; }
     R->nh = (R->lo - R->halo_lo) + (R->halo_hi - R->hi);
     int inner_lo = R->lo, inner_hi = R->hi, n = 0;
-    for (int q = 0; q < o->world; ++q) {
-        if (q == o->rank) continue;
+    for (int q = 0; q < world; ++q) {
+        if (q == rank) continue;
         const int qlo = o->row_bounds[q], qhi = o->row_bounds[q + 1];
         const int qnh = (qlo - o->halo_lo[q]) + (o->halo_hi[q] - qhi);
         // rows of mine below rank q's range that q needs (q's lower halo), and rows of mine above it (q's upper halo)
         const int b0 = std::max(R->lo, o->halo_lo[q]), e0 = std::min(R->hi, qlo);
         if (e0 > b0) {
             R->seg[n] = MgSeg{q, b0, e0, -o->halo_lo[q], qnh}; ++n;
-            if (q > o->rank) inner_hi = std::min(inner_hi, b0); else inner_lo = std::max(inner_lo, e0);
+            if (q > rank) inner_hi = std::min(inner_hi, b0); else inner_lo = std::max(inner_lo, e0);
         }
         const int b1 = std::max(R->lo, qhi), e1 = std::min(R->hi, o->halo_hi[q]);
         if (e1 > b1) {
             R->seg[n] = MgSeg{q, b1, e1, (qlo - o->halo_lo[q]) - qhi, qnh}; ++n;
-            if (q < o->rank) inner_lo = std::max(inner_lo, e1); else inner_hi = std::min(inner_hi, b1);
+            if (q < rank) inner_lo = std::max(inner_lo, e1); else inner_hi = std::min(inner_hi, b1);
         }
     }
     R->nseg = n;
     if (inner_lo > inner_hi) { inner_lo = R->lo; inner_hi = R->lo; }
     R->inner_lo = inner_lo; R->inner_hi = inner_hi;
     R->vecs = o->vecs.p; R->pbuf = o->pcg_pbuf.p; R->xs = reinterpret_cast<XState*>(o->xstate.p); R->halo = o->halo.p;
+    R->xp = o->xplanes.p;
     R->nbr_row = o->nbr_row.p; R->inc = o->inc.p; R->lin = o->lin.p;
     R->vol = o->vol->view(); R->surf = surf_view(o);
     R->partials = o->pcg_partials.p + 1;
@@ -2069,7 +2276,7 @@ static int mg_blocks_cap() {
     static int cap = 0;
     if (!cap) {
         int per_sm = 0;
-        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_block_mg, kMgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_block_mg<false>, kMgBlock, 0));
         if (per_sm < 1) { set_error("distributed distance solve does not fit on an SM"); throw CudaError{-1}; }
         cap = pcg_geometry().sms;   // one block per SM: the barriers cost more with more blocks than the rows gain
     }
@@ -2079,8 +2286,9 @@ static int mg_blocks_cap() {
 static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const MgLaunch& L) {
     MgArgs A;
     memset(&A, 0, sizeof(A));
-    A.S = on->S; A.world = on->world; A.nplayed = nplayed;
-    for (int q = 0; q < on->world; ++q) A.peer[q] = on->peer[q];
+    A.S = on->S; A.world = on->sharded ? on->world : 1; A.nplayed = nplayed;
+    for (int q = 0; q < A.world; ++q) A.peer[q] = on->peer[q];
+    if (!on->sharded) { A.peer[0].halo = on->halo.p; A.peer[0].xs = reinterpret_cast<XState*>(on->xstate.p); }
     int need = 1;
     for (int i = 0; i < nplayed; ++i) { A.loc[i] = ranks[i]; need = std::max(need, (ranks[i].hi - ranks[i].lo + kMgBlock - 1) / kMgBlock); }
     const int cap = std::max(1, mg_blocks_cap() / nplayed);
@@ -2097,7 +2305,10 @@ static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const
     const MgArgs* dev = reinterpret_cast<const MgArgs*>(on->mg_args.p);
     void* args[] = { (void*)&dev };
     Prof pf(on->stream, KID_PCG_SOLVE);
-    PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
+    bool one_row = true;   // every rank played has at most one row per thread
+    for (int i = 0; i < nplayed; ++i) one_row = one_row && (ranks[i].hi - ranks[i].lo) <= A.nb * kMgBlock;
+    if (one_row) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg<true>, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
+    else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg<false>, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
 }
 
 static void mg_leader(psg_optimizer* on, void* const* args, int world, void* user) {
@@ -2109,12 +2320,16 @@ static void mg_leader(psg_optimizer* on, void* const* args, int world, void* use
 void launch_dist_block_mg(psg_optimizer* o, float damping, bool only_on_success, bool want_reg) {
     // verdict (identical on every rank), then the slot whose entries are partial sums over the rank's rows
     PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotReg, 0, 24 * sizeof(double), o->stream));
-    o->reduce_reg = true;
+    if (o->sharded) o->reduce_reg = true;
     if (o->S == 0) return;
+    if (!o->sharded && !o->halo.p) {   // one GPU: no halo, but the kernel's argument block wants valid pointers
+        o->halo.alloc(kHaloKinds);
+        PSG_CUDA(cudaMemsetAsync(o->halo.p, 0, kHaloKinds * sizeof(unsigned long long), o->stream));
+    }
     MgRank R;
     fill_mg_rank(o, &R);
     MgLaunch L; L.damping = damping; L.only_on_success = only_on_success ? 1 : 0; L.want_reg = want_reg ? 1 : 0;
-    if (o->group) group_run(o, &R, mg_leader, &L);
+    if (o->group && o->sharded) group_run(o, &R, mg_leader, &L);
     else launch_mg(o, &R, 1, L);
     o->last_pcg_kernel = 4;
     o->vol_unsynced = true;
@@ -2174,8 +2389,8 @@ void read_dist_verdict(const psg_optimizer* o, int* success, int* iters, float* 
     const float tol = 1.1920929e-07f;
     *err = res[2] != 0.f ? sqrtf(res[1] / res[2]) : 0.f;
     *success = (*err <= tol) ? 1 : 0;   // IterativeSolverBase: info = error <= tolerance ? Success : NoConvergence
-    if (o->sharded) {
-        if (res[4] != 0.f) { set_error("the distributed distance solve gave up waiting for a peer (10 s limit)"); throw CudaError{-1}; }
+    if (o->last_pcg_kernel == 4) {
+        if (res[4] != 0.f) { set_error("the distance solve gave up waiting for a peer (10 s limit)"); throw CudaError{-1}; }
         *accepted = (long long)(mail_slot(o, kSlotReg)[3] + 0.5);   // summed over the ranks by the flush
     } else {
         *accepted = (long long)*reinterpret_cast<const unsigned long long*>(mail_slot(o, kSlotCount));

@@ -68,6 +68,7 @@ constexpr int kMaxRanks = 8;     // ranks of one sharded job (one 8-GPU NVSwitch
 struct XState {
     unsigned long long epoch;              // barriers completed by earlier launches (written by the owner at the end of a launch)
     unsigned long long epoch_r;            // ... of which barriers with a cross-rank reduction (mailbox parity and packet tags)
+    unsigned long long epoch_t;            // value tags handed out by earlier launches (every vector entry that another thread reads carries one)
     unsigned long long arrive;             // arrivals of the owner's blocks at the current barrier (reset by the owner at the end of a launch)
     unsigned long long abort;              // sticky: a wait ran into its time limit
     unsigned long long ll[2][kMaxRanks][6];   // [reduction parity][sender][word]: three doubles as six (tag << 32 | 32 data bits) packets, written by the sender
@@ -158,6 +159,7 @@ struct psg_optimizer {
     bool vol_unsynced = false;               // sharded: other ranks' rows of the volume planes are stale (psg_opt_sync_volume)
     psg::DevBuf<unsigned char> xstate;       // psg::XState of this rank
     psg::DevBuf<unsigned long long> halo;    // this rank's halo packets (PeerView::halo), kHaloKinds x (rows of its halo)
+    psg::DevBuf<unsigned long long> xplanes; // u and U1..U3 of all rows as (tag, value) packets: what other threads of this rank read (pcg.cu)
     psg::PeerView peer[psg::kMaxRanks];      // peer[q]: rank q's buffers as addressable from this process (peer[rank] = own)
     std::vector<void*> ipc_opened;           // base pointers of the imported allocations (closed before anything is freed)
     int shard_policy = 0;                    // 0 = by work per rank, 1 = always, 2 = never

@@ -450,6 +450,13 @@ void build_layout(psg_optimizer* o) {
         o->vecs.alloc(Sr * 25 + 8);
         o->pcg_pbuf.alloc(2 * Sr);
         o->pcg_partials.alloc((size_t)4 * kPcgMaxBlocks + 1);
+        // dataflow distance solve (pcg.cu): packets of u, U1..U3 per row, tags start at zero (= never written)
+        if (o->xplanes.n < 4 * Sr) o->xplanes.alloc(4 * Sr);
+        PSG_CUDA(cudaMemsetAsync(o->xplanes.p, 0, o->xplanes.n * sizeof(unsigned long long), o->stream));
+        if (!o->xstate.p) {
+            o->xstate.alloc(sizeof(XState));
+            PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, sizeof(XState), o->stream));
+        }
         const size_t grid = (Sr + 31) / 32 + 1, ngroups = grid / 128 + 2;
         o->sweep_partials.alloc((grid + ngroups) * 8);
         if (o->sweep_counter.n < ngroups + 1) {

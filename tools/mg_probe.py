@@ -51,6 +51,15 @@ for _ in range(5):
 single = table()
 psg.profile_enable(False)
 out = {"grid": G, "S": go1.S, "single": single, "pcg_iters": info1["dist"]["iters"], "single_kernel": go1.last_pcg_kernel()}
+go1.set_pcg_mode(8)      # the dataflow kernel on one GPU
+for _ in range(3):
+    go1.iteration(damping=1.0, normal_reg=True)
+psg.profile_reset(); psg.profile_enable(True)
+for _ in range(5):
+    info8 = go1.iteration(damping=1.0, normal_reg=True)
+out["single_dataflow"] = {"k_dist_pcg": table().get("k_dist_pcg"), "pcg_iters": info8["dist"]["iters"], "kernel": go1.last_pcg_kernel()}
+psg.profile_enable(False)
+go1.set_pcg_mode(0)
 pairs = [build() for _ in range(world)]
 opts = [p[1] for p in pairs]
 psg.comm_init_local(opts)
