@@ -364,7 +364,7 @@ def run_ours(a):
 
     G, F = a.grid, a.frames
     peak, peak_src = peaks()
-    SHARD_MIN_PAIRS = 2_000_000       # kShardMinPairsPerRank (psgradientsdf_b200/csrc/comm.cu)
+    SHARD_MIN_PAIRS = 3_000_000       # kShardMinPairs (psgradientsdf_b200/csrc/comm.cu)
 
     def sync():
         torch.cuda.synchronize()
@@ -390,7 +390,7 @@ def run_ours(a):
         if rank == 0:
             job = Job(a, local, build_scene(a, 1234), G, a.model)
             job.go.set_keyframes(job.fi, job.poses_np, job.images_np); job.go.init()
-            verdict[0] = "shard" if job.go.is_sharded()[1] // world >= SHARD_MIN_PAIRS else "replicas"
+            verdict[0] = "shard" if job.go.is_sharded()[1] >= SHARD_MIN_PAIRS else "replicas"
         dist.broadcast_object_list(verdict, src=0)
         mode = verdict[0]
     seed = 1234 + (17 * rank if mode == "replicas" else 0)
@@ -606,7 +606,7 @@ def run_ours(a):
                             f"{world} independent keyframe sets, one per GPU (same geometry and camera orbit, lights and pose "
                             f"perturbations seeded per rank), no data-path collective; surface_voxels / active_pairs are sums "
                             f"over the ranks.  One such set has {vis_pairs} visible pairs, "
-                            f"below the {SHARD_MIN_PAIRS} per rank from which sharding one set pays "
+                            f"below the {SHARD_MIN_PAIRS} from which sharding one set pays "
                             f"(DESIGN.md section 7; --multi shard forces it); config.strong_512 is the sharded job")}
     if grids is not None:
         config["grids"] = grids

@@ -357,9 +357,10 @@ int psg_opt_comm_init(psg_optimizer* opt, const unsigned char id[128], int rank,
  * the distributed distance solve runs as one cooperative launch whose blocks play all ranks. */
 int psg_opt_comm_init_local(psg_optimizer* const* opts, int world);
 int psg_opt_comm_destroy(psg_optimizer* opt);
-/* Sharding policy.  0 (default): shard when the work list has at least 150 000 visible (voxel, keyframe) pairs per rank
- * (below that the exchange costs more than the split saves: 128^3 x 30 keyframes stays replicated, 512^3 x 30 is sharded on 8
- * GPUs), 1: always shard, 2: never.  Switching re-partitions at the next call that touches the work list. */
+/* Sharding policy.  0 (default): shard when the work list has at least three million visible (voxel, keyframe) pairs (below
+ * that the cross-GPU latency of the distance solve costs more than the split sweeps save: 128^3 and 256^3 x 30 keyframes stay
+ * replicated, 512^3 x 30 and 1024^3 x 64 are sharded), 1: always shard, 2: never.  Switching re-partitions at the next call
+ * that touches the work list. */
 int psg_opt_set_shard_policy(psg_optimizer* opt, int policy);
 int psg_opt_is_sharded(const psg_optimizer* opt, int* sharded, long long* visible_pairs);
 /* The rows [row_lo, row_hi) of the surface list this rank owns and the rows [halo_lo, row_lo) + [row_hi, halo_hi) it receives

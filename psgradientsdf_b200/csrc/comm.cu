@@ -225,17 +225,19 @@ void shard_blocks(int S, int rank, int world, int* first, int* stride, int* coun
     *count = rank < nblocks ? (nblocks - rank + world - 1) / world : 0;
 }
 
-// Sharding pays only when a rank's share of the work outweighs what the exchange adds (one small NCCL all-reduce per host
-// round trip, ~3 NVLink flag barriers per CG iteration): measured on B200 x 2..8 (profiles/r2_summary.md) the break-even is
-// around 150 000 visible pairs per rank.  Below it every rank sweeps the whole list and only rank 0's reduced sums are
-// broadcast, so that all ranks still solve identical small systems and stay in the same state bit for bit.
-constexpr long long kShardMinPairsPerRank = 150000;
+// Sharding divides the sweeps by the number of ranks but makes every CG iteration of the distance block wait for three
+// dependent NVLink hops (halo of u, halo of the stencil products, the reduction): measured on 8 x B200 that costs 150-250 us per
+// outer iteration whatever the size (profiles/r2_summary.md), so it pays once the sweeps of an iteration take more than about
+// twice that -- around three million visible pairs (512^3 x 30 keyframes has 4.2 million).  Below it every rank sweeps the whole
+// list and only rank 0's reduced sums are broadcast, so that all ranks still solve identical small systems and stay in the same
+// state bit for bit.
+constexpr long long kShardMinPairs = 3000000;
 void update_shard_policy(psg_optimizer* o) {
     bool want = false;
     if (o->world > 1 && (o->comm || o->group)) {
         if (o->shard_policy == 1) want = true;
         else if (o->shard_policy == 2) want = false;
-        else want = o->vis_pairs / o->world >= kShardMinPairsPerRank;
+        else want = o->vis_pairs >= kShardMinPairs;
     }
     if (want != o->sharded) { o->sharded = want; o->layout_dirty = true; }
 }
