@@ -437,7 +437,7 @@ def run_ours(a):
     prof, pinfo = profiled_steps(job, a.steps, flush, sync, peak)
     pcg_iters = int(pinfo.block[2].cg_iterations)
     pcg_kernel = {0: "general cooperative grid", 1: "8-CTA cluster", 2: "fused grid kernel", 3: "16-CTA cluster, vectors in distributed shared memory",
-                  4: "distributed (sharded job)"}.get(go.last_pcg_kernel(), "?")
+                  4: "distributed (sharded job)", 5: "fused grid kernel, Chronopoulos-Gear arrangement"}.get(go.last_pcg_kernel(), "?")
     t_max = allmax(t_dev)
     t_wall_max = allmax(t_wall)
     value = A_job * SWEEPS_PER_STEP * a.steps / t_max      # whole job: the shared list once, or the sum of the ranks' own lists

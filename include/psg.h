@@ -159,14 +159,15 @@ int psg_opt_set_upload_overlap(psg_optimizer* opt, int on);
  * voxels in the sweep kernels.  0 (default) = chosen per launch from the surface size; 1 = one warp walks all keyframes
  * in ascending order, which reproduces the reference's per-voxel float summation order bit for bit; 2, 4, 8 = split. */
 int psg_opt_set_sweep_split(psg_optimizer* opt, int warps);
-/* Distance solve: 0 (default) = up to 32 768 surface voxels one 16-CTA thread-block cluster with the CG vectors in distributed
- * shared memory (hardware cluster barrier, no global-memory traffic inside the solve); up to one row per resident thread the fused
- * cooperative-grid kernel (block size chosen from the row count: fewer, larger blocks make the grid barriers cheaper); beyond
- * that the general persistent cooperative-grid kernel.  2 = always the general kernel; 1 = one portable cluster of at most 8 CTAs
- * with the vectors in global memory (kept for comparison); 3 / 4 = the fused grid kernel with 512 / 1024 threads per block; 5 = the
- * general kernel with 256-thread blocks on large surfaces (default there: 1024); 6 = the 16-CTA cluster kernel or, where it does
- * not apply, the general kernel.  All run the same iteration and return the same iterates up to the order of the dot-product
- * partials. */
+/* Distance solve: 0 (default) = up to one row per resident thread (128^3, 256^3) the fused cooperative-grid kernel in the
+ * Chronopoulos-Gear arrangement (one fused reduction and two grid barriers per CG iteration; block size chosen from the row count:
+ * fewer, larger blocks make the grid barriers cheaper); beyond that the general persistent cooperative-grid kernel.  2 = always the
+ * general kernel; 3 / 4 = the fused grid kernel in Eigen's arrangement (three barriers per iteration) with 512 / 1024 threads per
+ * block; 6 = up to 32 768 rows one 16-CTA thread-block cluster with the CG vectors in distributed shared memory (hardware cluster
+ * barrier, no global-memory traffic inside the solve), else the general kernel; 1 = one portable cluster of at most 8 CTAs with the
+ * vectors in global memory; 5 = the general kernel with 256-thread blocks on large surfaces (default there: 1024); 8 = the dataflow
+ * kernel of the sharded path on one GPU; 7 = measurement switch of that kernel.  All run the same iteration (in exact arithmetic)
+ * and return the same iterates up to rounding, with the same iteration counts on every system tried. */
 int psg_opt_set_pcg_mode(psg_optimizer* opt, int mode);
 
 /* Optimizer::initAlbedo() (Optimizer.cpp:50-81) */
@@ -414,7 +415,8 @@ int psg_debug_host_times(double us[3], long long* iterations, int reset);
  * records an event; end records a second one, waits for it and returns the device time between the two in milliseconds:
  * the device-side duration of whatever was called in between (idle gaps while the host works included). */
 /* Diagnostic: which distance-solve kernel the last distance block used: 0 general cooperative grid, 1 portable 8-CTA cluster,
- * 2 fused grid kernel, 3 16-CTA cluster over distributed shared memory, 4 distributed (sharded job); -1 none yet. */
+ * 2 fused grid kernel, 3 16-CTA cluster over distributed shared memory, 4 dataflow kernel (sharded job, or mode 8), 5 fused grid
+ * kernel in the Chronopoulos-Gear arrangement; -1 none yet. */
 int psg_debug_last_pcg_kernel(const psg_optimizer* opt, int* kernel);
 int psg_debug_timer_begin(psg_optimizer* opt);
 int psg_debug_timer_end(psg_optimizer* opt, float* ms);

@@ -574,6 +574,257 @@ __global__ void __launch_bounds__(BS, (BS >= 1024) ? 1 : (BS >= 512) ? 2 : 4) k_
     }
 }
 
+// three sums at once: warp 0 forms the block's partials, publishes them with the arrival, waits for the other blocks and adds all
+// partials (fixed association: identical bits in every block)
+template <int BS>
+__device__ __forceinline__ double3 grid_reduce3(double a, double b, double d, double* Pa, double* Pb, double* Pd, unsigned long long* ctr,
+                                                unsigned long long& target, int nb, double* s_buf /* 3 * BS / 32 + 3 */) {
+    constexpr int NW = BS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b); d = warp_sum(d);
+    if (lane == 0) { s_buf[warp] = a; s_buf[NW + warp] = b; s_buf[2 * NW + warp] = d; }
+    target += (unsigned)nb;
+    __syncthreads();
+    if (warp == 0) {
+        double ta = lane < NW ? s_buf[lane] : 0.0, tb = lane < NW ? s_buf[NW + lane] : 0.0, td = lane < NW ? s_buf[2 * NW + lane] : 0.0;
+        ta = warp_sum(ta); tb = warp_sum(tb); td = warp_sum(td);
+        if (lane == 0) {
+            Pa[blockIdx.x] = ta; Pb[blockIdx.x] = tb; Pd[blockIdx.x] = td;
+            asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(ctr) : "memory");
+            unsigned long long v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+            } while (v < target);
+        }
+        __syncwarp();
+        double xa = 0.0, xb = 0.0, xd = 0.0;
+        for (int i = lane; i < nb; i += 32) { xa += __ldcg(Pa + i); xb += __ldcg(Pb + i); xd += __ldcg(Pd + i); }
+        xa = warp_sum(xa); xb = warp_sum(xb); xd = warp_sum(xd);
+        if (lane == 0) { s_buf[3 * NW] = xa; s_buf[3 * NW + 1] = xb; s_buf[3 * NW + 2] = xd; }
+    }
+    __syncthreads();
+    return make_double3(s_buf[3 * NW], s_buf[3 * NW + 1], s_buf[3 * NW + 2]);
+}
+
+// ---- the fused small-surface kernel in the Chronopoulos-Gear arrangement: TWO grid barriers per CG iteration ---------------------
+// With u = M^-1 r, w = A u and the recurrences p = u + beta p, s = w + beta s (= A p), x += alpha p, r -= alpha s, ONE fused
+// reduction per iteration yields gamma = (r, u), delta = (w, u) and |r|^2; beta = gamma / gamma_old, alpha = gamma / (delta - beta
+// gamma / alpha_old).  Same iterates as Eigen's loop in exact arithmetic and, in float, the same iteration counts on every system
+// tried.  The update of a row needs nothing from other rows, so a thread does NOT wait for its neighbours' new u: it recomputes
+// it from what they published one phase earlier (r, s double-buffered; w; 1/diag) with the very operations their owner
+// executes -- same bits.  An iteration is then: [update + stencil products] barrier [gather into w + three dot products] barrier.
+template <int BS>
+__global__ void __launch_bounds__(BS, (BS >= 1024) ? 1 : (BS >= 512) ? 2 : 4) k_dist_solve_small_cg(SolveSmallArgs G, float* pbuf /* 2 x S */) {
+    const PcgArgs& A = G.A;
+    __shared__ double s_buf[3 * (BS / 32) + 3];
+    __shared__ double s_reg[BS / 32][3];
+    const int S = A.S;
+    const int nb = gridDim.x;
+    const int row = blockIdx.x * BS + threadIdx.x;
+    const bool in = row < S;
+    double* P0 = A.partials;
+    double* P1 = A.partials + nb;
+    double* P2 = A.partials + 2 * nb;
+    unsigned long long bar_target = 0;
+    // published per row: r and s double-buffered (pbuf, planes p / tmp), w (plane r), 1/diag (plane invd), U1..U3 (plane U + 1..3)
+    // (A.p and A.tmp are consecutive planes of S floats, as are the two halves of pbuf)
+    float* const Rb0 = pbuf;
+    float* const Sb0 = A.p;
+    float* Wp = A.r;
+
+    // ---- prologue: assemble the row (k_dist_assemble) and keep it
+    int col[3] = { -1, -1, -1 }, tn[6] = { -1, -1, -1, -1, -1, -1 };
+    float Ab[10], invd = 0.f, dd = 0.f, b = 0.f;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) Ab[i] = 0.f;
+    if (in) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) col[a] = __ldg(A.nbr_row + a * S + row);
+#pragma unroll
+        for (int h = 0; h < 6; ++h) tn[h] = __ldg(A.inc + h * S + row);
+#pragma unroll
+        for (int i = 0; i < 10; ++i) Ab[i] = __ldg(A.blk + (long long)i * S + row);
+        float rhs = __ldg(A.blk + (long long)10 * S + row);
+        float diag = Ab[0];
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = tn[h * 3 + a];
+                if (t >= 0) {
+                    rhs += __ldg(A.blk + (long long)(10 + a + 1) * S + t);
+                    diag += __ldg(A.blk + (long long)tri(a + 1, a + 1) * S + t);
+                }
+            }
+        dd = (A.damping != 0.f) ? A.damping * diag : 0.f;
+        const float full = diag + dd;
+        invd = (full != 0.f) ? 1.f / full : 1.f;
+        b = rhs;
+        A.rhs[row] = rhs;          // diagnostics (psg_opt_last_vectors)
+        A.invd[row] = invd; Rb0[row] = rhs; Sb0[row] = 0.f; Wp[row] = 0.f;
+    }
+    float x = 0.f, r = b, u = invd * b, p = 0.f, sv = 0.f, w = 0.f, u0 = 0.f;
+    grid_barrier(A.barrier, bar_target, nb);
+    const float tol = 1.1920929e-07f;
+    float rhsNorm2 = 0.f, threshold = 0.f, residualNorm2 = 0.f, gamma = 0.f, alpha = 0.f, beta = 0.f;
+    int it = 0, cur = 0;
+    bool first = true;
+    for (;;) {
+        // ---- phase 1: own update (registers), neighbours' new u recomputed, stencil products
+        if (in) {
+            if (!first) {
+                p = u + beta * p; sv = w + beta * sv;
+                x += alpha * p; r = r - alpha * sv;
+                u = invd * r;
+                Rb0[(size_t)(cur ^ 1) * S + row] = r; Sb0[(size_t)(cur ^ 1) * S + row] = sv;
+            }
+            float px[4];
+            px[0] = u;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int c = col[a];
+                if (c < 0) { px[a + 1] = 0.f; continue; }
+                const float rc = __ldcg(Rb0 + (size_t)cur * S + c), ic = __ldcg(A.invd + c);
+                if (first) px[a + 1] = ic * rc;
+                else {
+                    const float sc = __ldcg(Wp + c) + beta * __ldcg(Sb0 + (size_t)cur * S + c);
+                    px[a + 1] = ic * (rc - alpha * sc);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float uu = 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float aik = (i >= k) ? Ab[i * (i + 1) / 2 + k] : Ab[k * (k + 1) / 2 + i];
+                    if (k == 0 || col[k - 1] >= 0) uu += aik * px[k];
+                }
+                const bool valid = (i == 0) || col[i - 1] >= 0;
+                if (i == 0) u0 = uu; else A.U[(long long)i * S + row] = valid ? uu : 0.f;
+            }
+        }
+        if (!first) cur ^= 1;
+        grid_barrier(A.barrier, bar_target, nb);
+        // ---- phase 2: w = u_s[0] + incident u + damping * diag * u_s, published ; (r, u), (w, u), (r, r)
+        double g = 0.0, d = 0.0, n = 0.0;
+        if (in) {
+            w = u0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const int t = tn[h * 3 + a];
+                    if (t >= 0) w += __ldcg(A.U + (long long)(a + 1) * S + t);
+                }
+            w += dd * u;
+            Wp[row] = w;
+            g = (double)r * (double)u; d = (double)w * (double)u; n = (double)r * (double)r;
+        }
+        const double3 t3 = grid_reduce3<BS>(g, d, n, P0, P1, P2, A.barrier, bar_target, nb, s_buf);
+        if (first) {
+            first = false;
+            rhsNorm2 = (float)t3.z;
+            threshold = tol * tol * rhsNorm2;
+            if (threshold < 1.17549435e-38f) threshold = 1.17549435e-38f;
+            residualNorm2 = rhsNorm2;
+            if (rhsNorm2 == 0.f) { residualNorm2 = 0.f; break; }
+            if (residualNorm2 < threshold) break;
+            gamma = (float)t3.x;
+            alpha = gamma / (float)t3.y; beta = 0.f;
+            if (it >= A.max_iters) break;
+            continue;
+        }
+        residualNorm2 = (float)t3.z;
+        if (residualNorm2 < threshold) break;
+        const float gnew = (float)t3.x;
+        beta = gnew / gamma;
+        alpha = gnew / ((float)t3.y - beta * gnew / alpha);
+        gamma = gnew;
+        ++it;
+        if (it >= A.max_iters) break;
+    }
+    if (in) A.x[row] = x;
+    if (row == 0) {
+        A.result[0] = (float)it;
+        A.result[1] = residualNorm2;
+        A.result[2] = rhsNorm2;
+        A.result[3] = threshold;
+    }
+    // ---- epilogue: Optimizer::updateDist (OptimizerAux.cpp:162-188), every block knows the verdict
+    const float err = rhsNorm2 != 0.f ? sqrtf(residualNorm2 / rhsNorm2) : 0.f;
+    const bool apply = !G.only_on_success || err <= tol;
+    if (apply) {
+        int acc = 0;
+        if (in && fabs((double)x) < G.thr) { G.vol.dist[G.lin[row]] -= x; acc = 1; }
+        const unsigned m = __ballot_sync(0xffffffffu, acc);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(G.accepted, (unsigned long long)__popc(m));
+    }
+    if (!apply && !G.reg_out) return;   // uniform over the grid
+    grid_barrier(A.barrier, bar_target, nb);
+    // Optimizer::updateGrad (OptimizerAux.cpp:152-160) + the slot records; any one-to-one thread -> slot map will do
+    if (apply && in) {
+        const int t = row;
+        const int s = __float_as_int(G.surf.rec2[t].w);
+        const int lin = __float_as_int(G.surf.rec3[t].w);
+        const float dist = __ldcg(G.vol.dist + lin);
+        const int pb = __float_as_int(G.surf.rec1[t].w);
+        float fd[3], nfd[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int nl = G.surf.nbr_lin[a * S + s];
+            const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+            const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+            fd[a] = (pp * (dn - dist)) * G.vs_inv;
+        }
+        G.vol.gx[lin] = fd[0]; G.vol.gy[lin] = fd[1]; G.vol.gz[lin] = fd[2];
+        normalized3(fd, nfd);
+        G.surf.rec0[t] = make_float4(dist, nfd[0], nfd[1], nfd[2]);
+        G.surf.rec2[t] = make_float4(fd[0], fd[1], fd[2], __int_as_float(s));
+        G.surf.rec4[t] = make_float4(nfd[0], nfd[1], nfd[2], 0.f);
+    }
+    // getNormalEnergy / getLaplacianEnergy / getAlbedoRegEnergy (Optimizer.cpp:86-136) on the updated distances
+    if (G.reg_out) {
+        double en = 0.0, el = 0.0, er = 0.0;
+        if (in) {
+            const int s = row;
+            const int lin = G.lin[s];
+            const float dist = __ldcg(G.vol.dist + lin);
+            const float rho[3] = { G.vol.r[lin], G.vol.g[lin], G.vol.b[lin] };
+            const unsigned char pb = G.surf.pos[s];
+            const long long stride[3] = { 1, G.vol.dims[0], (long long)G.vol.dims[0] * G.vol.dims[1] };
+            float fd[3], d2[3], Gr[9];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int nl = G.surf.nbr_lin[a * S + s];
+                const float pp = ((pb >> a) & 1) ? 1.f : -1.f;
+                const float dn = nl >= 0 ? __ldcg(G.vol.dist + nl) : dist;
+                fd[a] = (pp * (dn - dist)) * G.vs_inv;
+                const long long l1 = (long long)lin + stride[a], l0 = (long long)lin - stride[a];
+                const float d1 = (l1 < G.vol.N) ? __ldcg(G.vol.dist + l1) : dist;
+                const float d0 = (l0 >= 0) ? __ldcg(G.vol.dist + l0) : dist;
+                d2[a] = d1 + d0 - 2 * dist;
+                const float nr = nl >= 0 ? G.vol.r[nl] : rho[0], ng = nl >= 0 ? G.vol.g[nl] : rho[1], nbb = nl >= 0 ? G.vol.b[nl] : rho[2];
+                Gr[a] = (pp * (nr - rho[0])) * G.vs_inv; Gr[3 + a] = (pp * (ng - rho[1])) * G.vs_inv; Gr[6 + a] = (pp * (nbb - rho[2])) * G.vs_inv;
+            }
+            const float e = norm3(fd) - 1;
+            en = (double)(e * e);
+            const float lap = (d2[0] + d2[1] + d2[2]) * G.vs_inv * G.vs_inv;
+            el = (double)(lap * lap);
+            er = (double)((norm3(Gr) + norm3(Gr + 3)) + norm3(Gr + 6));
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        en = warp_sum(en); el = warp_sum(el); er = warp_sum(er);
+        if (lane == 0) { s_reg[warp][0] = en; s_reg[warp][1] = el; s_reg[warp][2] = er; }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < BS / 32; ++i) v += s_reg[i][threadIdx.x];
+            atomicAdd(&G.reg_out[threadIdx.x], v);
+        }
+    }
+}
+
 // ---- surfaces of at most 32 768 rows: the whole distance block inside ONE 16-CTA cluster, vectors in distributed shared memory --
 // The fused grid kernel above is a chain of grid barriers (~2 us each through L2, three per CG iteration) around a few hundred
 // nanoseconds of arithmetic.  A thread-block cluster has a hardware barrier (barrier.cluster, ~0.2 us) and can read its peers'
@@ -2019,7 +2270,8 @@ __global__ void __launch_bounds__(256) k_grad_update(VolView vol, SurfView surf,
 
 // launch geometry of the cooperative kernels, queried once per device (the queries cost microseconds each, the solve runs
 // every outer iteration)
-struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_small1024 = 0, per_sm_4_1024 = 0, per_sm_1 = 0, per_sm_4 = 0; };
+struct PcgGeometry { int sms = 0, per_sm_small = 0, per_sm_small512 = 0, per_sm_small1024 = 0, per_sm_4_1024 = 0, per_sm_1 = 0, per_sm_4 = 0,
+                     per_sm_cg = 0, per_sm_cg512 = 0, per_sm_cg1024 = 0; };
 static const PcgGeometry& pcg_geometry() {
     static PcgGeometry g[64];
     int dev = 0;
@@ -2030,6 +2282,9 @@ static const PcgGeometry& pcg_geometry() {
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small, k_dist_solve_small<kPcgBlock>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small512, k_dist_solve_small<512>, 512, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_small1024, k_dist_solve_small<1024>, 1024, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_cg, k_dist_solve_small_cg<kPcgBlock>, kPcgBlock, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_cg512, k_dist_solve_small_cg<512>, 512, 0));
+        PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_cg1024, k_dist_solve_small_cg<1024>, 1024, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_1, k_dist_pcg<kPcgBlock, 1>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4, k_dist_pcg<kPcgBlock, 4>, kPcgBlock, 0));
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&e.per_sm_4_1024, k_dist_pcg<1024, 4>, 1024, 0));
@@ -2149,8 +2404,9 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     const int S = o->S;
     if (S == 0 || (o->pcg_mode != 0 && o->pcg_mode != 3 && o->pcg_mode != 4 && o->pcg_mode != 6)) return false;
     const PcgGeometry& geo = pcg_geometry();
-    // up to 32 768 rows: one 16-CTA cluster with the vectors in distributed shared memory (modes 0 and 6)
-    const bool want_cluster = (o->pcg_mode == 0 || o->pcg_mode == 6) && S <= 2 * kClNC * kClBS;
+    // mode 6: up to 32 768 rows one 16-CTA cluster with the vectors in distributed shared memory
+    const bool want_cluster = o->pcg_mode == 6 && S <= 2 * kClNC * kClBS;
+    const bool cg = o->pcg_mode == 0;   // default: the fused kernel in the Chronopoulos-Gear arrangement (two barriers per iteration)
     const int cl_rpt = S <= kClNC * kClBS ? 1 : 2;
     const bool use_cluster = want_cluster && (cl_rpt == 1 ? cluster16_available<1>() : cluster16_available<2>());
     if (o->pcg_mode == 6 && !use_cluster) return false;
@@ -2165,12 +2421,13 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
         while (bsz < 1024 && (S + bsz - 1) / bsz > 64) bsz *= 2;
     }
     const int sms = geo.sms;
-    auto fits = [&](int b) {
-        const int per = b == 1024 ? geo.per_sm_small1024 : b == 512 ? geo.per_sm_small512 : geo.per_sm_small;
-        return per >= 1 && (S + b - 1) / b <= sms * per;
+    auto per_of = [&](int b) {
+        if (cg) return b == 1024 ? geo.per_sm_cg1024 : b == 512 ? geo.per_sm_cg512 : geo.per_sm_cg;
+        return b == 1024 ? geo.per_sm_small1024 : b == 512 ? geo.per_sm_small512 : geo.per_sm_small;
     };
+    auto fits = [&](int b) { const int per = per_of(b); return per >= 1 && (S + b - 1) / b <= sms * per; };
     while (bsz > kPcgBlock && !fits(bsz)) bsz /= 2;
-    const int per_sm = bsz == 1024 ? geo.per_sm_small1024 : bsz == 512 ? geo.per_sm_small512 : geo.per_sm_small;
+    const int per_sm = per_of(bsz);
     const int grid = (S + bsz - 1) / bsz;
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
@@ -2210,6 +2467,13 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     o->last_pcg_kernel = 2;
     void* args[] = { &G, &pbuf };
     Prof pf(o->stream, KID_PCG_SOLVE);
+    if (cg) {
+        o->last_pcg_kernel = 5;
+        if (bsz == 1024) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small_cg<1024>, dim3(grid), dim3(1024), args, 0, o->stream));
+        else if (bsz == 512) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small_cg<512>, dim3(grid), dim3(512), args, 0, o->stream));
+        else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small_cg<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));
+        return true;
+    }
     if (bsz == 1024) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<1024>, dim3(grid), dim3(1024), args, 0, o->stream));
     else if (bsz == 512) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<512>, dim3(grid), dim3(512), args, 0, o->stream));
     else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_solve_small<kPcgBlock>, dim3(grid), dim3(kPcgBlock), args, 0, o->stream));

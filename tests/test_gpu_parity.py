@@ -173,7 +173,7 @@ def test_pcg_kernels_agree():
     model, G = "SH1", 40
     sc = scene(model)
     outs = []
-    for mode in (3, 1, 2, 0, 4, 8):   # 3, 4: fused grid kernel, 512- / 1024-thread blocks; 0: 16-CTA cluster at this size; 8: dataflow kernel
+    for mode in (3, 1, 2, 0, 4, 8, 6):   # 3, 4: fused grid kernel (Eigen's arrangement); 0: the same in the Chronopoulos-Gear arrangement; 8: dataflow; 6: 16-CTA cluster
         gv, go = make_gpu(model, G, sc)
         handoff(go, sc); go.init_albedo(); go.set_pcg_mode(mode)
         info = go.step("dist", damping=1.0, normal_reg=True)
