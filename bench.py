@@ -499,7 +499,8 @@ def run_ours(a):
                 sc_big[model] = build_scene(a, 1234, model=model)
             return Job(a, local, sc_big[model], Gb, model)
 
-        def run_grid(model, Gb, nsteps=3, shard=False):
+        def run_grid(model, Gb, nsteps=3, shard=False, solo=False):
+            """solo: only the calling rank runs (no collective inside)."""
             j = big_job(model, Gb)
             if shard:
                 join_comm(j.go)
@@ -507,9 +508,11 @@ def run_ours(a):
             Eb, Ab = j.go.energy()
             for _ in range(2):
                 j.iteration()
-            barrier()
+            if not solo:
+                barrier()
             td, tw, inf = timed_steps(j, nsteps, flush, sync, barrier if shard else None)
-            td = allmax(td)
+            if not solo:
+                td = allmax(td)
             prof_b, pinf = profiled_steps(j, nsteps, flush, sync, peak)
             tab = kernel_table(prof_b, Ab // (world if shard else 1), j.go.S // (world if shard else 1), j.F,
                                int(pinf.block[2].cg_iterations), peak)
@@ -526,6 +529,12 @@ def run_ours(a):
             grids = {"256^3 LED": run_grid("LED", 256), "512^3 SH1": run_grid("SH1", 512)}
         else:
             strong = run_grid("SH1", 512, shard=True)
+            # the same job on ONE of these GPUs in the same run, for the ratio (the other ranks wait)
+            if rank == 0:
+                one = run_grid("SH1", 512, solo=True)
+                strong["one_gpu_same_run_ms_per_step"] = one["ms_per_step"]
+                strong["speedup_vs_one_gpu_same_run"] = round(one["ms_per_step"] / strong["ms_per_step"], 3)
+            barrier()
 
     if rank != 0:
         if world > 1:

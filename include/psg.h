@@ -114,7 +114,8 @@ int psg_volume_upload_vis(psg_volume* vol, const uint64_t* words, int frame_coun
 /* ------------------------------------------------------------------ optimizer (Optimizer / PsOptimizer / LedOptimizer) */
 
 /* PsOptimizer / LedOptimizer(tSDF, voxel_size, K, save_path, settings) (main_ps.cpp:193-202).  The optimizer
- * keeps a non-owning pointer to vol, like the reference. */
+ * keeps a non-owning pointer to vol, like the reference.  At most 10 optimizers can be alive per device at a time (each holds a
+ * copy of its per-keyframe pose / light table in the device's constant memory); psg_opt_destroy gives the place back. */
 int psg_opt_create(psg_optimizer** out, psg_volume* vol, float voxel_size, const float K[9],
                    const psg_settings* settings);
 int psg_opt_destroy(psg_optimizer* opt);

@@ -512,6 +512,12 @@ class Optimizer:
             lib().psg_opt_destroy(self.h)
             self.h = C.c_void_p()
 
+    def __del__(self):   # an optimizer holds one of the device's few keyframe-table slots (psg_opt_create): give it back
+        try:
+            self.close()
+        except Exception:
+            pass
+
     # setImages + setKeyframes + setPoses (main_ps.cpp:323-326)
     def set_keyframes(self, frame_idx, poses, images):
         F, H, W, _ = images.shape

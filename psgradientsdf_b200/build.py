@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libpsg_b200.so")
-SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu", "comm.cu", "normals.cu", "tracker.cu", "mesh.cu", "host_solve.cpp"]
+SOURCES = ["volume.cu", "surface.cu", "sweep.cu", "pcg.cu", "capi.cu", "host_loop.cu", "comm.cu", "normals.cu", "tracker.cu", "mesh.cu", "small_solve.cu", "host_solve.cpp"]
 HEADERS = ["psg_device.cuh", "psg_host.h", "mc_table.h", "host_solve.h", os.path.join("..", "..", "include", "psg.h")]
 
 

@@ -40,7 +40,7 @@ static const char* const kKernelNames[KID_COUNT] = {
     "k_fill_volume", "k_pack_frame", "k_integrate", "k_aos_soa", "k_surface_mask", "k_scan_counts", "k_surface_scatter",
     "k_neighbors", "k_upsample", "k_sweep<ENERGY>", "k_sweep<INIT_ALBEDO>", "k_sweep<LED_INIT>", "k_sweep<PROBE>",
     "k_sweep<ALBEDO>", "k_sweep<LIGHT>", "k_sweep<POSE>", "k_sweep<DIST>", "k_reg_energy", "k_dist_assemble", "k_dist_pcg",
-    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather", "k_track", "k_mesh_bbox", "k_mesh_cells<count>", "k_mesh_scan", "k_mesh_cells<emit>", "k_mesh_misc" };
+    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather", "k_track", "k_mesh_bbox", "k_mesh_cells<count>", "k_mesh_scan", "k_mesh_cells<emit>", "k_mesh_misc", "k_small_solve" };
 static bool g_prof_on = false;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof_recs;
@@ -75,44 +75,6 @@ static void prof_collect() {
         g_event_pool.push_back(r.e0); g_event_pool.push_back(r.e1);
     }
     g_prof_recs.clear();
-}
-
-// Sophus SO3::exp (third/Sophus/sophus/so3.hpp:583-619) followed by Eigen's Quaternion::toRotationMatrix
-static void so3_exp_matrix(const float* w, float* Rm) {
-    const float theta_sq = w[0] * w[0] + (w[1] * w[1] + w[2] * w[2]);
-    float imag, real;
-    if (theta_sq < 1e-10f * 1e-10f) {
-        const float t4 = theta_sq * theta_sq;
-        imag = 0.5f - (float)(1.0 / 48.0) * theta_sq + (float)(1.0 / 3840.0) * t4;
-        real = 1.f - (float)(1.0 / 8.0) * theta_sq + (float)(1.0 / 384.0) * t4;
-    } else {
-        const float theta = std::sqrt(theta_sq);
-        const float half = 0.5f * theta;
-        imag = std::sin(half) / theta;
-        real = std::cos(half);
-    }
-    const float qw = real, qx = imag * w[0], qy = imag * w[1], qz = imag * w[2];
-    const float tx = 2.f * qx, ty = 2.f * qy, tz = 2.f * qz;
-    const float twx = tx * qw, twy = ty * qw, twz = tz * qw, txx = tx * qx, txy = ty * qx, txz = tz * qx;
-    const float tyy = ty * qy, tyz = tz * qy, tzz = tz * qz;
-    Rm[0] = 1.f - (tyy + tzz); Rm[1] = txy - twz; Rm[2] = txz + twy;
-    Rm[3] = txy + twz; Rm[4] = 1.f - (txx + tzz); Rm[5] = tyz - twx;
-    Rm[6] = txz - twy; Rm[7] = tyz + twx; Rm[8] = 1.f - (txx + tyy);
-}
-
-// Optimizer::updatePose (OptimizerAux.cpp:190-205): t <- t - xi[0:3], R <- R * exp(-xi[3:6])
-static void update_poses(psg_optimizer* o, const float* d) {
-    for (int f = 0; f < o->F; ++f) {
-        float* P = o->poses.data() + 16 * f;
-        float R[9], E[9];
-        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) R[3 * a + b] = P[4 * a + b];
-        const float w[3] = { -d[6 * f + 3], -d[6 * f + 4], -d[6 * f + 5] };
-        so3_exp_matrix(w, E);
-        P[3] = P[3] - d[6 * f]; P[7] = P[7] - d[6 * f + 1]; P[11] = P[11] - d[6 * f + 2];
-        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b)
-            P[4 * a + b] = R[3 * a] * E[b] + (R[3 * a + 1] * E[3 + b] + R[3 * a + 2] * E[6 + b]);
-    }
-    o->frames_dirty = true;
 }
 
 static void sh_eval_host(const float* n, int nb, float* sh) {
@@ -158,6 +120,8 @@ void psg_optimizer::ensure_host_staging() {
     const size_t bytes = (kRedDoubles + kMailDoubles) * sizeof(double);
     PSG_CUDA(cudaMallocHost(&p, bytes));
     host_staging = static_cast<double*>(p);
+    PSG_CUDA(cudaMallocHost(&p, sizeof(psg::FrameTable)));
+    host_frames = static_cast<psg::FrameTable*>(p);
 }
 
 #define PSG_TRY try {
@@ -352,12 +316,16 @@ int psg_opt_create(psg_optimizer** out, psg_volume* vol, float voxel_size, const
     if (set->loss < 0 || set->loss > 4) { set_error("psg_opt_create: unknown loss %d", set->loss); return PSG_ERR_INVALID; }
     PSG_TRY
     PSG_CUDA(cudaSetDevice(vol->device));
+    const int cslot = psg::acquire_const_slot(vol->device);   // fails when kConstSlots optimizers are alive on this device
     psg_optimizer* o = new psg_optimizer;
+    o->cslot = cslot;
     o->vol = vol; o->set = *set;
     o->nb = set->model == PSG_MODEL_SH2 ? 9 : 4;
     o->vs = voxel_size; o->vs_inv = 1.f / voxel_size;   // Optimizer.cpp:22-23
     memcpy(o->K, K, sizeof(o->K));
     o->stream = vol->stream;
+    o->frames_dev.alloc(psg::kMaxFrames + 1);
+    o->small_sys.alloc((size_t)psg::kMaxFrames * 81 + 2 * psg::kMaxFrames * 9);
     *out = o;
     return PSG_OK;
     PSG_CATCH
@@ -376,6 +344,9 @@ int psg_opt_destroy(psg_optimizer* o) {
     o->svis.release(); o->pos.release(); o->rec0.release(); o->rec1.release(); o->rec2.release(); o->rec3.release(); o->rec4.release();
     o->pvis.release(); o->perm.release(); o->sort_hist.release(); o->perm2.release(); o->block_pairs.release(); o->mask.release(); o->prefix.release(); o->block_counts.release();
     if (o->host_staging) cudaFreeHost(o->host_staging);
+    if (o->host_frames) cudaFreeHost(o->host_frames);
+    o->frames_dev.release(); o->small_sys.release();
+    psg::release_const_slot(o->vol->device, o->cslot);
     o->areg.release(); o->mg_args.release(); o->xplanes.release(); o->halo.release();
     o->red.release(); o->sweep_partials.release(); o->sweep_counter.release(); o->vecs.release(); o->pcg_partials.release(); o->pcg_pbuf.release();
     delete o;
@@ -508,6 +479,7 @@ int psg_opt_init(psg_optimizer* o) {
         double sums[6];
         sweep_led_light_init(o, sums);
         for (int c = 0; c < 3; ++c) o->light[c] = (float)sums[c] / (float)sums[3 + c];
+        o->frames_dirty = true;
     }
     return PSG_OK;
     PSG_CATCH
@@ -721,7 +693,7 @@ struct HostClock {
 
 struct Pending { int block = -1; int slot = 0; size_t nred = 0; float damping = 0.f; bool albedo_reg = false; };
 
-// queues the kernels of one block; light / pose need their sums on the host before anything else may be queued
+// queues the kernels of one block (none of them waits for the host)
 Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int slot, bool reg_energies_after = false,
                     bool keep_vectors = true) {
     Pending p; p.block = block; p.slot = slot; p.damping = damping;
@@ -743,7 +715,11 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
         launch_albedo(o, damping, keep_vectors ? o->vecs.p : nullptr, keep_vectors ? o->vecs.p + n : nullptr, slot);
         if (!keep_vectors) o->last_block = -1;
     } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
-        p.nred = launch_small_block(o, block, slot);
+        // the sweep leaves the per-keyframe sums on the device; one thread block solves them there and updates the keyframe
+        // table (small_solve.cu), so the next block can be queued right behind
+        launch_small_block(o, block, slot);
+        reduce_pending(o);   // several ranks: the solve needs the job's sums
+        launch_small_solve(o, block, slot, damping);
     } else {
         launch_dist_sweep(o, flags, slot);
         // SH: updateDist only on Success (PsOptimizer.cpp:168-170); LED: unconditionally (LedOptimizer.cpp:242).  The
@@ -759,7 +735,7 @@ Pending queue_block(psg_optimizer* o, int block, float damping, int flags, int s
     return p;
 }
 
-// host part of a block once fetch_mail has brought its results: the small solves and their updates, the step record
+// host part of a block once fetch_mail has brought its results: the step record
 void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
     const bool led = o->set.model == PSG_MODEL_LED;
     const int block = p.block;
@@ -777,39 +753,13 @@ void finish_block(psg_optimizer* o, const Pending& p, psg_step_info* out) {
         inf.n_accepted = (long long)(mail_slot(o, p.slot)[5] + 0.5);
         o->last_n = (int)n;
     } else if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) {
-        // scratch kept across calls: the solve runs three times per outer iteration and must not pay for allocations
-        thread_local static std::vector<double> Hd, bd;
-        thread_local static std::vector<float> Hf, bf, x;
-        unpack_small_block(o, block, p.slot, Hd, bd);
+        // solved and applied on the device; fetch_mail has already brought the updated light / poses into the host copies
         const int bs = block == PSG_BLOCK_POSE ? 6 : (led ? 3 : o->nb);
         const int nblk = (block == PSG_BLOCK_LIGHT && led) ? 1 : o->F;
-        const int n = bs * nblk;
-        // H.diagonal() += damping * H.diagonal(): every block but the SH light block (PsOptimizer.cpp:175-203)
-        const bool damp = !(block == PSG_BLOCK_LIGHT && !led);
-        Hf.resize(Hd.size()); bf.resize(bd.size()); x.assign((size_t)n, 0.f);
-        for (size_t i = 0; i < Hd.size(); ++i) Hf[i] = (float)Hd[i];
-        for (size_t i = 0; i < bd.size(); ++i) bf[i] = (float)bd[i];
-        if (damp && p.damping != 0.f)
-            for (int blk = 0; blk < nblk; ++blk)
-                for (int k = 0; k < bs; ++k) {
-                    float& d = Hf[(size_t)blk * bs * bs + k * bs + k];
-                    d = d + p.damping * d;
-                }
-        const CgVerdict v = eigen_like_cg(nblk, bs, Hf.data(), bf.data(), x.data());
-        inf.n = n; inf.cg_success = v.success; inf.cg_iterations = v.iters; inf.cg_error = v.err;
-        o->lastH.assign(Hf.begin(), Hf.end());
-        o->lastb.assign(bf.begin(), bf.end());
-        o->lastdelta.assign(x.begin(), x.end());
-        o->last_n = n;
-        if (block == PSG_BLOCK_LIGHT) {
-            // light_[frame] -= delta (PsOptimizer.cpp:199-201, LedOptimizer.cpp:159), unconditionally
-            for (int i = 0; i < n; ++i) o->light[i] -= x[i];
-            o->frames_dirty = true;
-            inf.applied = 1;
-        } else {
-            // SH: updatePose unconditionally (PsOptimizer.cpp:232); LED: only on Success (LedOptimizer.cpp:271-273)
-            if (!led || v.success) { update_poses(o, x.data()); inf.applied = 1; }
-        }
+        int ok = 1, iters = 0, applied = 1; float err = 0.f;
+        read_small_verdict(o, block, &ok, &iters, &err, &applied);
+        inf.n = bs * nblk; inf.cg_success = ok; inf.cg_iterations = iters; inf.cg_error = err; inf.applied = applied;
+        o->last_n = bs * nblk;
     } else {
         int ok = 1, iters = 0; float err = 0.f; long long acc = 0;
         read_dist_verdict(o, &ok, &iters, &err, &acc);
@@ -845,10 +795,9 @@ int psg_opt_step(psg_optimizer* o, int block, float damping, int flags, psg_step
     PSG_CATCH
 }
 
-// One pass of the reference's while-body with as few host waits as the data flow allows: a block whose result the host
-// does not need before the next launch (albedo, distance) is queued behind it, and the host waits only where a small
-// system has to be solved (light, pose) and for the closing energy.  SH: albedo+light | distance+pose | energy;
-// LED: light | albedo+distance+pose | energy.
+// One pass of the reference's while-body as one queue of kernels and one host wait: every block's solve and update runs on the
+// device (albedo in its sweep, light and pose in k_small_solve, distance in the PCG kernels), each reporting into its own mail
+// slot; the closing energy rides behind them and a single round trip brings all of it back.
 int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_iteration_info* out) {
     PSG_NEED_INIT(o)
     if (!cfg) { set_error("psg_opt_iteration: null configuration"); return PSG_ERR_INVALID; }
@@ -873,22 +822,6 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
     int nq = 0, slot = 0;
     bool reg_queued = false;
     int last_run = -1;
-    auto flush = [&](size_t nred) {
-        { HostClock hc(1); fetch_mail(o, nred); }
-        HostClock hc(2);
-        for (int i = 0; i < nq; ++i) {
-            finish_block(o, queued[i], &R.block[queued[i].block]);
-            R.ran[queued[i].block] = 1;
-        }
-        if (reg_queued) {
-            const double* r = mail_slot(o, kSlotReg);
-            R.reg_normal_after_dist = o->S > 0 ? r[0] / (double)o->S : 0.0;
-            R.reg_laplacian_after_dist = o->S > 0 ? r[1] / (double)o->S : 0.0;
-            R.reg_albedo_after_albedo = o->S > 0 ? r[2] / (double)o->S : 0.0;
-            reg_queued = false;
-        }
-        nq = 0; slot = 0;
-    };
     for (int k = 0; k < 4; ++k) {
         const int block = order[k];
         if (!enabled[block]) continue;
@@ -900,19 +833,17 @@ int psg_opt_iteration(psg_optimizer* o, const psg_iteration_config* cfg, psg_ite
         const bool want_reg = (block == PSG_BLOCK_DIST && ((cfg->reg_flags & (PSG_REG_NORMAL | PSG_REG_LAPLACIAN)) || areg)) ||
                               (block == PSG_BLOCK_ALBEDO && areg);
         { HostClock hc(0); queued[nq] = queue_block(o, block, cfg->damping, flags, slot, want_reg, /*keep_vectors=*/false); }
-        const size_t nred = queued[nq].nred;
         ++nq; ++slot;
         last_run = block;
         if (want_reg) reg_queued = true;
-        if (block == PSG_BLOCK_LIGHT || block == PSG_BLOCK_POSE) flush(nred);   // the host solves this one now
     }
     // closing energy (the convergence test needs it); blocks still queued ride on the same round trip
     if (last_run >= 0 || cfg->closing_energy) {
         { HostClock hc(0); launch_energy(o, slot); }
-        const int eslot = slot;
-        // flush() resets `slot`, read the closing energy first
+        static_assert(kSlotAreg > 4, "four blocks and the closing energy use mail slots 0..4");
         { HostClock hc(1); fetch_mail(o, 0); }
-        const double* sc = mail_slot(o, eslot);
+        HostClock hc(2);
+        const double* sc = mail_slot(o, slot);
         R.energy_end = o->S > 0 ? sc[6] / (double)o->S : 0.0;
         R.n_active_end = (long long)(sc[7] + 0.5);
         for (int i = 0; i < nq; ++i) {
@@ -991,10 +922,20 @@ int psg_debug_timer_end(psg_optimizer* o, float* ms) {
 int psg_opt_last_system(psg_optimizer* o, double* H, double* b, double* delta) {
     PSG_NEED_INIT(o)
     if (o->last_block != PSG_BLOCK_LIGHT && o->last_block != PSG_BLOCK_POSE) { set_error("last step was not a light or pose block"); return PSG_ERR_STATE; }
-    if (H) memcpy(H, o->lastH.data(), o->lastH.size() * sizeof(double));
-    if (b) memcpy(b, o->lastb.data(), o->lastb.size() * sizeof(double));
-    if (delta) memcpy(delta, o->lastdelta.data(), o->lastdelta.size() * sizeof(double));
+    PSG_TRY
+    PSG_CUDA(cudaSetDevice(o->vol->device));
+    // the solve kernel keeps H | b | x of the last light / pose block on the device
+    const bool led = o->set.model == PSG_MODEL_LED;
+    const int bs = o->last_block == PSG_BLOCK_POSE ? 6 : (led ? 3 : o->nb);
+    const int nblk = (o->last_block == PSG_BLOCK_LIGHT && led) ? 1 : o->F;
+    const size_t nH = (size_t)nblk * bs * bs, n = (size_t)nblk * bs;
+    std::vector<float> sys(nH + 2 * n);
+    copy_sync(sys.data(), o->small_sys.p, sys.size() * sizeof(float), cudaMemcpyDeviceToHost, o->stream);
+    if (H) for (size_t i = 0; i < nH; ++i) H[i] = sys[i];
+    if (b) for (size_t i = 0; i < n; ++i) b[i] = sys[nH + i];
+    if (delta) for (size_t i = 0; i < n; ++i) delta[i] = sys[nH + n + i];
     return PSG_OK;
+    PSG_CATCH
 }
 
 int psg_opt_last_vectors(psg_optimizer* o, float* b, float* delta) {

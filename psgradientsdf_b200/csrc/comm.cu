@@ -210,7 +210,7 @@ void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n) {
 static void comm_barrier(psg_optimizer* o) {
     if (o->world <= 1) return;
     o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
-    double* p[1] = { o->red.p + kMailDoubles - 1 };   // last double of the mailbox: slot 7, never summed otherwise
+    double* p[1] = { o->red.p + kMailDoubles - 1 };   // last double of the mailbox (slot kSlotSmall holds floats in its first half only): never summed otherwise
     const size_t c[1] = { 1 };
     PSG_CUDA(cudaMemsetAsync(p[0], 0, sizeof(double), o->stream));
     comm_allreduce_doubles(o, p, c, 1);

@@ -1564,7 +1564,7 @@ __device__ __forceinline__ double3 mg_barrier(MgCtx& c, double a, double b, doub
 
 // ONE_ROW: the rank has at most one row per thread; the row's whole CG state then lives in registers
 template <bool ONE_ROW>
-__global__ void __launch_bounds__(kMgBlock, 1) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
+__global__ void __launch_bounds__(kMgBlock, ONE_ROW ? 1 : 2) k_dist_block_mg(const MgArgs* __restrict__ Ap) {
     __shared__ double s_buf[3 * (kMgBlock / 32) + 4];
     __shared__ double s_reg[kMgBlock / 32][4];
     const MgArgs& A = *Ap;
@@ -2432,7 +2432,7 @@ bool launch_dist_block_small(psg_optimizer* o, float damping, bool only_on_succe
     if (per_sm < 1 || grid > sms * per_sm) return false;
 
     o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
-    static_assert(kSlotReg + 1 == kSlotPcg && kSlotPcg + 1 == kSlotCount, "slots 5..7 are cleared with one memset");
+    static_assert(kSlotReg + 1 == kSlotPcg && kSlotPcg + 1 == kSlotCount, "the three slots are cleared with one memset");
     PSG_CUDA(cudaMemsetAsync(mail_dev(o) + 8 * kSlotReg, 0, 24 * sizeof(double), o->stream));   // reg energies, verdict, counter + barrier
     o->vecs.alloc((size_t)S * 25 + 8);
     float* base = o->vecs.p;
@@ -2541,7 +2541,7 @@ static int mg_blocks_cap() {
     if (!cap) {
         int per_sm = 0;
         PSG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dist_block_mg<false>, kMgBlock, 0));
-        if (per_sm < 1) { set_error("distributed distance solve does not fit on an SM"); throw CudaError{-1}; }
+        if (per_sm < 2) { set_error("distributed distance solve does not fit on an SM"); throw CudaError{-1}; }
         cap = pcg_geometry().sms;   // one block per SM: the barriers cost more with more blocks than the rows gain
     }
     return cap;
@@ -2555,9 +2555,11 @@ static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const
     if (!on->sharded) { A.peer[0].halo = on->halo.p; A.peer[0].xs = reinterpret_cast<XState*>(on->xstate.p); }
     int need = 1;
     for (int i = 0; i < nplayed; ++i) { A.loc[i] = ranks[i]; need = std::max(need, (ranks[i].hi - ranks[i].lo + kMgBlock - 1) / kMgBlock); }
-    const int cap = std::max(1, mg_blocks_cap() / nplayed);
-    A.nb = std::min(need, cap);
-    if (A.nb > kPcgMaxBlocks / 2) A.nb = kPcgMaxBlocks / 2;
+    // one row per thread if the rows fit one block per SM (state in registers); else the general variant, two blocks per SM
+    const int cap1 = std::max(1, mg_blocks_cap() / nplayed);
+    const bool one_row = need <= cap1;
+    A.nb = one_row ? need : std::min(need, std::max(1, 2 * mg_blocks_cap() / nplayed));
+    if (A.nb > 4 * kPcgMaxBlocks / 6) A.nb = 4 * kPcgMaxBlocks / 6;   // [2][3][nb] partial sums in 4 * kPcgMaxBlocks doubles
     A.damping = L.damping; A.vs_inv = on->vs_inv; A.thr = sqrt(3.0) * (double)on->vs;
     A.max_iters = 2 * on->S; A.only_on_success = L.only_on_success; A.want_reg = L.want_reg;
     A.flags = on->pcg_mode == 7 ? 1 : 0;
@@ -2569,8 +2571,6 @@ static void launch_mg(psg_optimizer* on, const MgRank* ranks, int nplayed, const
     const MgArgs* dev = reinterpret_cast<const MgArgs*>(on->mg_args.p);
     void* args[] = { (void*)&dev };
     Prof pf(on->stream, KID_PCG_SOLVE);
-    bool one_row = true;   // every rank played has at most one row per thread
-    for (int i = 0; i < nplayed; ++i) one_row = one_row && (ranks[i].hi - ranks[i].lo) <= A.nb * kMgBlock;
     if (one_row) PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg<true>, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
     else PSG_CUDA(cudaLaunchCooperativeKernel((void*)k_dist_block_mg<false>, dim3(A.nb * nplayed), dim3(kMgBlock), args, 0, on->stream));
 }

@@ -35,8 +35,11 @@ struct __align__(16) FrameParams {
     float light[9];   // SH coefficients of this keyframe (4 or 9 used); unused for LED
     float pad[3];
 };
-// all keyframes' parameters travel as a kernel parameter (constant bank, indexed by the warp-uniform keyframe)
-struct FrameTable { FrameParams f[kMaxFrames]; };
+// All keyframes' parameters: one table in device memory (psg_optimizer::frames_dev) that the small solves (small_solve.cu) update
+// in place, so that an outer iteration runs without a host round trip per block; the sweeps read a copy in constant memory
+// (sweep.cu: c_frames).  Entry kMaxFrames holds the LED model's global light colour in light[0..2].
+struct FrameTable { FrameParams f[kMaxFrames + 1]; };
+constexpr int kConstSlots = 10;  // copies of the table in constant memory: optimizers alive at a time per device (10 x 6240 B of the 64 KB)
 
 struct SurfView {
     int S;                              // number of surface voxels (rows)

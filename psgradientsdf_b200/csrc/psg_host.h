@@ -20,7 +20,7 @@ enum KernelId {
     KID_FILL = 0, KID_PACK_FRAME, KID_FUSE, KID_AOS, KID_SURF_MASK, KID_SURF_SCAN, KID_SURF_SCATTER, KID_SURF_NEIGHBORS,
     KID_UPSAMPLE, KID_SWEEP_ENERGY, KID_SWEEP_INIT_ALBEDO, KID_SWEEP_LED_INIT, KID_SWEEP_PROBE, KID_SWEEP_ALBEDO,
     KID_SWEEP_LIGHT, KID_SWEEP_POSE, KID_SWEEP_DIST, KID_REG_ENERGY, KID_PCG_ASSEMBLE, KID_PCG_SOLVE, KID_DIST_UPDATE,
-    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_MESH_BOX, KID_MESH_COUNT, KID_MESH_SCAN, KID_MESH_EMIT, KID_MESH_MISC, KID_COUNT
+    KID_GRAD_UPDATE, KID_PAD_IMAGES, KID_NORMALS, KID_COMM_SCATTER, KID_COMM_ALLREDUCE, KID_COMM_ALLGATHER, KID_TRACK, KID_MESH_BOX, KID_MESH_COUNT, KID_MESH_SCAN, KID_MESH_EMIT, KID_MESH_MISC, KID_SMALL_SOLVE, KID_COUNT
 };
 // Counts one launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
 struct Prof {
@@ -120,8 +120,16 @@ struct psg_optimizer {
     std::vector<float> poses;                // F x 16 (host copy, authoritative)
     std::vector<float> light;                // F x nb or 3
     psg::DevBuf<float4> images;              // F x H x W texels (b, g, r, 0)
-    psg::FrameTable frame_table;             // per-keyframe R, t, light (host copy; passed to the sweeps as a kernel parameter)
-    bool frames_dirty = true;
+    psg::FrameTable frame_table;             // per-keyframe R, t, light: host staging of the device table
+    psg::DevBuf<psg::FrameParams> frames_dev;  // the table the sweeps read and the small solves update (kMaxFrames + 1 entries)
+    bool frames_dirty = true;                // the host copy (poses / light) changed: upload before the next sweep
+    bool const_dirty = true;                 // frames_dev changed: refresh this optimizer's slot of the constant-memory copy
+    int cslot = -1;                          // that slot (sweep.cu: c_frames)
+    // light / pose blocks solved on the device (small_solve.cu): the dense blocks, rhs and solution of the last one, and what the
+    // next fetch_mail has to bring back into the host copies
+    psg::DevBuf<float> small_sys;            // H (nblk * bs * bs) | b (n) | x (n)
+    int small_pending = 0;                   // bit PSG_BLOCK_LIGHT / PSG_BLOCK_POSE: the device table holds newer values than the host
+    psg::FrameTable* host_frames = nullptr;  // pinned landing area of the table
     // overlapped keyframe upload (psg_opt_set_upload_overlap): copy + conversion on their own stream while psg_opt_init
     // builds the work list; the caller's image buffer must then stay valid until psg_opt_init returns
     bool upload_overlap = false, upload_pending = false;
@@ -189,16 +197,22 @@ struct psg_optimizer {
 
 namespace psg {
 
-// o->red: the mailbox, then kRedCopies x kRedDoubles of per-keyframe sums (copy 0 holds the result); the mailbox (8 slots x 8 doubles) every kernel of an outer iteration reports
+// o->red: the mailbox, then kRedCopies x kRedDoubles of per-keyframe sums (copy 0 holds the result); the mailbox (10 slots x 8 doubles) every kernel of an outer iteration reports
 // into: slots 0..4 sweep scalars (one per sweep in flight), then the three below
 constexpr int kRedDoubles = kMaxFrames * 64;
 constexpr int kRedCopies = 8;     // private copies of the per-keyframe sums on large grids (same-address fp64 atomics serialise in L2)
-constexpr int kMailDoubles = 64;
+constexpr int kMailDoubles = 80;
 constexpr int kPcgMaxBlocks = 1024;   // most blocks a cooperative distance-solve launch uses (4 per SM, <= 256 SMs)
-constexpr int kSlotAreg = 4;     // regularised albedo solve: 4 floats verdict (as kSlotPcg), [5] accepted updates, [6] grid-barrier counter
-constexpr int kSlotReg = 5;      // regulariser energies {normal, laplacian, albedo}
-constexpr int kSlotPcg = 6;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
-constexpr int kSlotCount = 7;    // [0] unsigned long long: accepted distance updates, [1] arrival counter of the PCG's grid barrier
+constexpr int kSlotAreg = 5;     // regularised albedo solve: 4 floats verdict (as kSlotPcg), [5] accepted updates, [6] grid-barrier counter
+constexpr int kSlotReg = 6;      // regulariser energies {normal, laplacian, albedo}
+constexpr int kSlotPcg = 7;      // 4 floats: iterations, residualNorm2, rhsNorm2, threshold
+constexpr int kSlotCount = 8;    // [0] unsigned long long: accepted distance updates, [1] arrival counter of the PCG's grid barrier
+constexpr int kSlotSmall = 9;    // small solves: 4 floats {success, iterations, error, applied} of the light block, 4 of the pose block; last double: comm.cu
+
+// ---- small_solve.cu: the light / pose blocks' Eigen-ordered CG and update on the device
+void launch_small_solve(psg_optimizer* o, int block, int slot, float damping);
+void read_small_verdict(const psg_optimizer* o, int block, int* success, int* iterations, float* error, int* applied);
+void adopt_device_frames(psg_optimizer* o);
 
 // ---- volume.cu
 void launch_fill_volume(psg_volume* v);
@@ -218,7 +232,10 @@ void launch_upsample(psg_optimizer* o);
 void launch_gather_voxels(psg_optimizer* o, float* out_dev);   // S x 8 floats (SdfVoxel layout) in surface-list order
 
 // ---- sweep.cu
+void reduce_pending(psg_optimizer* o);      // stream-ordered reduction over the ranks of the sums queued so far
 void refresh_frame_table(psg_optimizer* o);
+int acquire_const_slot(int device);
+void release_const_slot(int device, int slot);
 void shard_blocks(int S, int rank, int world, int* first, int* stride, int* count);
 void comm_allreduce_doubles(psg_optimizer* o, double* const* ptr, const size_t* count, int n);   // in place, n <= 3 arrays in one step
 void comm_broadcast_doubles(psg_optimizer* o, double* a, size_t n);   // rank 0's values to every rank
@@ -246,7 +263,6 @@ const double* fetch_mail(psg_optimizer* o, size_t n_red_doubles);
 const double* mail_slot(const psg_optimizer* o, int slot);
 void launch_albedo(psg_optimizer* o, float damping, float* b_dev, float* delta_dev, int slot, bool regularised = false);
 size_t launch_small_block(psg_optimizer* o, int block, int slot);
-void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<double>& H, std::vector<double>& b);
 void launch_dist_sweep(psg_optimizer* o, int flags, int slot);
 void launch_energy(psg_optimizer* o, int slot);
 void launch_reg_energies(psg_optimizer* o, int slot);

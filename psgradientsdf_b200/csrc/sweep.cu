@@ -14,6 +14,8 @@
 // (PsOptimizerJa.cpp, LedOptimizerJa.cpp), Optimizer::computeDistGrad / normalJacobian / distRegJacobian /
 // computeDistLaplacian / distLaplacianJacobian (Optimizer.cpp), Optimizer::initAlbedo (Optimizer.cpp:50-81),
 // LedOptimizer::computeLightIntensive (LedOptimizer.cpp:76-112), Optimizer::updateAlbedo (OptimizerAux.cpp:120-150).
+#include <mutex>
+
 #include "psg_host.h"
 
 namespace psg {
@@ -35,7 +37,7 @@ struct SweepArgs {
     int F;
     int blk_first, blk_stride, blk_count;   // 32-slot blocks of the work list this launch walks: blk_first + i * blk_stride, i < blk_count
     float vs_inv;
-    float led[3];
+    int cslot;          // which copy of the keyframe table in constant memory (c_frames) belongs to this optimizer
     float damping, reg_n, reg_l;
     int flags;
     double* red;        // per-keyframe reductions (zeroed by the launcher)
@@ -50,6 +52,12 @@ struct SweepArgs {
 };
 
 struct Footprint { int x, y; float4 t00, t01, t10, t11; };
+
+// Per-keyframe R, t, light of up to kConstSlots optimizers on this device, read through the constant bank with the warp-uniform
+// keyframe index (operands of the arithmetic instructions, no load instructions, no registers).  The authoritative table lives
+// in device memory (psg_optimizer::frames_dev), where the small solves update it; a 6 KB device-to-device copy refreshes the
+// optimizer's slot here whenever it changed (sync_const_table).
+__constant__ FrameParams c_frames[kConstSlots][kMaxFrames + 1];
 
 __device__ __forceinline__ const float4* texel_ptr(const SweepArgs& A, int f, int row, int col) {
     return A.images + ((long long)f * A.cam.H + row) * A.cam.W + col;
@@ -211,7 +219,7 @@ __device__ __forceinline__ void grid_sum_scalars(const double* block_vals, doubl
 }
 
 template <int MODEL, int MODE>
-__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE == M_POSE) ? 3 : 4)) k_sweep(const __grid_constant__ SweepArgs A, const __grid_constant__ FrameTable T) {
+__global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE == M_POSE) ? 3 : 4)) k_sweep(const __grid_constant__ SweepArgs A) {
     constexpr int NB = (MODEL == PSG_MODEL_SH2) ? 9 : 4;
     constexpr bool LED = (MODEL == PSG_MODEL_LED);
     // per-keyframe reduction width (padded to a power of two / multiple of 32 lanes)
@@ -305,6 +313,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     }
 
     const float fx = A.cam.fx, fy = A.cam.fy, cx = A.cam.cx, cy = A.cam.cy;
+    float led[3] = {0.f, 0.f, 0.f};
+    if constexpr (LED) { led[0] = c_frames[A.cslot][kMaxFrames].light[0]; led[1] = c_frames[A.cslot][kMaxFrames].light[1]; led[2] = c_frames[A.cslot][kMaxFrames].light[2]; }
 
     // ---- keyframe loop: ascending, every lane of a warp on the same keyframe; warp w takes every W-th visible keyframe
     if (W > 1) {   // keep every W-th set bit, starting with the warp-th (one pass over the bits, outside the hot loop)
@@ -321,7 +331,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
     while (uni) {
         const int f = __ffsll((long long)uni) - 1;
         uni &= uni - 1;
-        const FrameParams& P = T.f[f];   // kernel parameter space: no global load at the head of the iteration
+        const FrameParams& P = c_frames[A.cslot][f];   // constant bank: no load at the head of the iteration
         const bool act = live && ((vis >> f) & 1ull);
 
         bool ok = false;
@@ -345,7 +355,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                     irr = dot3(nR, pt);
                     irr /= (float)cube_d(norm3(pt));
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) rend[c] = rho[c] * A.led[c] * irr;
+                    for (int c = 0; c < 3; ++c) rend[c] = rho[c] * led[c] * irr;
                 } else {     // PsOptimizerJa.cpp:30-40
                     irr = dot_sh<NB>(P.light, sh_n);
 #pragma unroll
@@ -399,7 +409,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                     float refl = dot3(gR, pt);
                     refl /= (float)cube_d(norm3(pt));
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) Jr[c] = refl * A.led[c];
+                    for (int c = 0; c < 3; ++c) Jr[c] = refl * led[c];
                 } else {     // PsOptimizerJa.cpp:118-122
                     const float j = -dot_sh<NB>(P.light, sh_g);
                     Jr[0] = j; Jr[1] = j; Jr[2] = j;
@@ -512,8 +522,8 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                         const float nRp = dot3(nR, pt);
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
-                            const float kt = -(rho[c] * A.led[c] / l3);
-                            const float kr = -3 * rho[c] * A.led[c] / l5 * nRp;
+                            const float kt = -(rho[c] * led[c] / l3);
+                            const float kr = -3 * rho[c] * led[c] / l5 * nRp;
 #pragma unroll
                             for (int j = 0; j < 3; ++j) { J[c][j] = J[c][j] + kt * gh[j]; J[c][3 + j] = J[c][3 + j] + kr * skp[j]; }
                         }
@@ -563,7 +573,7 @@ __global__ void __launch_bounds__(32 * kMaxSplit, (MODE == M_DIST) ? 2 : ((MODE 
                         const float dm2 = (float)((double)(-3 * dot3(pRt, dx[k])) / r5);
                         dm = dm / radius + dm2 * gRp;
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) Jd[k][c] = Jd[k][c] + (rho[c] * A.led[c]) * dm;
+                        for (int c = 0; c < 3; ++c) Jd[k][c] = Jd[k][c] + (rho[c] * led[c]) * dm;
                     }
                 } else if constexpr (NB == 4) {   // PsOptimizerJa.cpp:225-240
 #pragma unroll
@@ -747,7 +757,7 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     A.images = o->images.p; A.F = o->F;
     shard_blocks(A.surf.nslots, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // a sharded rank's slot list holds its own rows only
     A.vs_inv = o->vs_inv;
-    if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
+    A.cslot = o->cslot;
     A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
     o->red.alloc((size_t)kRedDoubles * kRedCopies + kMailDoubles);
     A.red = red_dev(o);
@@ -765,17 +775,53 @@ static SweepArgs base_args(psg_optimizer* o, int slot = 0) {
     return A;
 }
 
-// per-keyframe R, t, light -> the table that every sweep launch passes by value
-void refresh_frame_table(psg_optimizer* o) {
-    if (!o->frames_dirty) return;
-    FrameParams* fr = o->frame_table.f;
-    memset(fr, 0, sizeof(FrameParams) * kMaxFrames);
-    for (int f = 0; f < o->F; ++f) {
-        const float* P = o->poses.data() + 16 * f;
-        for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
-        if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
+// ---- the keyframe table's copies in constant memory
+namespace {
+std::mutex g_slot_mutex;
+unsigned g_slots_used[16] = {0};          // per device: bit s set = slot s of c_frames taken
+FrameParams* g_const_base[16] = {nullptr};   // per device: address of c_frames
+}
+int acquire_const_slot(int device) {
+    std::lock_guard<std::mutex> lk(g_slot_mutex);
+    if (device < 0 || device >= 16) { set_error("device ordinal %d not supported", device); throw CudaError{-1}; }
+    if (!g_const_base[device]) {
+        void* p = nullptr;
+        PSG_CUDA(cudaGetSymbolAddress(&p, c_frames));   // the current device's instance of the symbol
+        g_const_base[device] = static_cast<FrameParams*>(p);
     }
-    o->frames_dirty = false;
+    for (int s = 0; s < kConstSlots; ++s)
+        if (!(g_slots_used[device] & (1u << s))) { g_slots_used[device] |= 1u << s; return s; }
+    set_error("at most %d optimizers per device can exist at a time (their keyframe tables live in constant memory)", kConstSlots);
+    throw CudaError{-1};
+}
+void release_const_slot(int device, int slot) {
+    std::lock_guard<std::mutex> lk(g_slot_mutex);
+    if (device >= 0 && device < 16 && slot >= 0) g_slots_used[device] &= ~(1u << slot);
+}
+
+// per-keyframe R, t, light -> the table the sweeps read.  The host's copy is uploaded when an API call changed it; the device
+// table (which the small solves update in place; fetch_mail brings their result back into o->poses / o->light, so the host copy
+// is current whenever an API call returns) is then copied into the optimizer's slot of constant memory, stream ordered.
+void refresh_frame_table(psg_optimizer* o) {
+    if (o->frames_dirty) {
+        FrameParams* fr = o->frame_table.f;
+        memset(fr, 0, sizeof(FrameTable));
+        for (int f = 0; f < o->F; ++f) {
+            const float* P = o->poses.data() + 16 * f;
+            for (int a = 0; a < 3; ++a) { for (int b = 0; b < 3; ++b) fr[f].R[3 * a + b] = P[4 * a + b]; fr[f].t[a] = P[4 * a + 3]; }
+            if (o->set.model != PSG_MODEL_LED) for (int i = 0; i < o->nb; ++i) fr[f].light[i] = o->light[(size_t)f * o->nb + i];
+        }
+        if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3 && c < (int)o->light.size(); ++c) fr[kMaxFrames].light[c] = o->light[c];
+        // pageable source: the driver stages the 6 KB before the call returns, the host copy may change right after
+        PSG_CUDA(cudaMemcpyAsync(o->frames_dev.p, fr, sizeof(FrameTable), cudaMemcpyHostToDevice, o->stream));
+        o->frames_dirty = false;
+        o->const_dirty = true;
+    }
+    if (o->const_dirty) {
+        PSG_CUDA(cudaMemcpyAsync(g_const_base[o->vol->device] + (size_t)o->cslot * (kMaxFrames + 1), o->frames_dev.p, sizeof(FrameTable),
+                                 cudaMemcpyDeviceToDevice, o->stream));
+        o->const_dirty = false;
+    }
 }
 
 template <int MODE>
@@ -799,7 +845,7 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
         if (dyn_smem > 48 * 1024)                                                                                      \
             PSG_CUDA(cudaFuncSetAttribute(k_sweep<MODEL, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem)); \
         Prof pf(o->stream, KID_SWEEP_ENERGY + MODE);                                                                   \
-        k_sweep<MODEL, MODE><<<grid, kBlockDim, dyn_smem, o->stream>>>(A, o->frame_table);                                                \
+        k_sweep<MODEL, MODE><<<grid, kBlockDim, dyn_smem, o->stream>>>(A);                                                \
     } break;
     switch (o->set.model) {
         PSG_SWEEP_CASE(PSG_MODEL_SH1)
@@ -824,28 +870,36 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
 double* mail_dev(psg_optimizer* o) { return o->red.p; }
 double* red_dev(psg_optimizer* o) { return o->red.p + kMailDoubles; }
 
+// Across ranks: what the kernels queued so far left as per-rank partial sums becomes the job's sums (stream ordered; called
+// before a kernel that consumes them on the device -- the small solves -- and by fetch_mail).
+void reduce_pending(psg_optimizer* o) {
+    if (o->world <= 1 || !(o->reduce_hi >= o->reduce_lo || o->reduce_reg)) return;
+    if (o->sharded) {
+        // one all-reduce for everything queued since the last one: per-keyframe sums, the scalar slots in flight and the
+        // regulariser energies / accepted-update count of the distance block (partial sums over each rank's rows)
+        double* ptr[3]; size_t cnt[3]; int k = 0;
+        if (o->reduce_red) { ptr[k] = red_dev(o); cnt[k++] = o->reduce_red; }
+        if (o->reduce_hi >= o->reduce_lo) { ptr[k] = mail_dev(o) + 8 * o->reduce_lo; cnt[k++] = (size_t)8 * (o->reduce_hi - o->reduce_lo + 1); }
+        if (o->reduce_reg) { ptr[k] = mail_dev(o) + 8 * kSlotReg; cnt[k++] = 8; }
+        comm_allreduce_doubles(o, ptr, cnt, k);
+    } else {
+        // replicated sweeps: every rank holds complete sums, equal up to the order of the fp64 atomics; rank 0's copy
+        // becomes everybody's, so that the small solves that follow are identical on all ranks
+        comm_broadcast_doubles(o, o->red.p, kMailDoubles + o->reduce_red);
+    }
+    o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0; o->reduce_reg = false;
+}
+
 const double* fetch_mail(psg_optimizer* o, size_t n) {
     o->ensure_host_staging();
     double* h = o->host_staging;
     trace("[rank %d] fetch_mail: red %zu, slots %d..%d, reg %d, sharded %d", o->rank, o->reduce_red, o->reduce_lo, o->reduce_hi, (int)o->reduce_reg, (int)o->sharded);
-    if (o->world > 1 && (o->reduce_hi >= o->reduce_lo || o->reduce_reg)) {
-        if (o->sharded) {
-            // one all-reduce for everything queued since the last round trip: per-keyframe sums, the scalar slots in flight and
-            // the regulariser energies / accepted-update count of the distance block (partial sums over each rank's rows)
-            double* ptr[3]; size_t cnt[3]; int k = 0;
-            if (o->reduce_red) { ptr[k] = red_dev(o); cnt[k++] = o->reduce_red; }
-            if (o->reduce_hi >= o->reduce_lo) { ptr[k] = mail_dev(o) + 8 * o->reduce_lo; cnt[k++] = (size_t)8 * (o->reduce_hi - o->reduce_lo + 1); }
-            if (o->reduce_reg) { ptr[k] = mail_dev(o) + 8 * kSlotReg; cnt[k++] = 8; }
-            comm_allreduce_doubles(o, ptr, cnt, k);
-        } else {
-            // replicated sweeps: every rank holds complete sums, equal up to the order of the fp64 atomics; rank 0's copy
-            // becomes everybody's, so that the host solves that follow are identical on all ranks
-            comm_broadcast_doubles(o, o->red.p, kMailDoubles + o->reduce_red);
-        }
-        o->reduce_lo = 1 << 30; o->reduce_hi = -1; o->reduce_red = 0; o->reduce_reg = false;
-    }
+    reduce_pending(o);
     PSG_CUDA(cudaMemcpyAsync(h, o->red.p, (kMailDoubles + n) * sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+    // a light / pose block solved on the device since the last round trip: its update lives in the keyframe table
+    if (o->small_pending) PSG_CUDA(cudaMemcpyAsync(o->host_frames, o->frames_dev.p, sizeof(FrameTable), cudaMemcpyDeviceToHost, o->stream));
     PSG_CUDA(cudaStreamSynchronize(o->stream));
+    if (o->small_pending) adopt_device_frames(o);
     trace("[rank %d] fetch_mail done", o->rank);
     return h;
 }
@@ -931,35 +985,6 @@ size_t launch_small_block(psg_optimizer* o, int block, int slot) {
     }
     reduce_over_ranks(o, nred, slot);
     return nred;
-}
-
-// unpacks what fetch_mail brought back: per-keyframe lower triangles + rhs as accumulated on the device (doubles)
-void unpack_small_block(psg_optimizer* o, int block, int slot, std::vector<double>& Hout, std::vector<double>& bout) {
-    const bool led = o->set.model == PSG_MODEL_LED;
-    if (block == PSG_BLOCK_LIGHT && led) {
-        const double* sc = mail_slot(o, slot);
-        Hout.assign(9, 0.0); bout.assign(3, 0.0);
-        for (int c = 0; c < 3; ++c) { Hout[4 * c] = sc[c]; bout[c] = sc[3 + c]; }
-        return;
-    }
-    const int nbk = block == PSG_BLOCK_POSE ? 6 : o->nb;
-    const int V = block == PSG_BLOCK_POSE ? 32 : (o->nb == 4 ? 16 : 64);
-    const int NT = nbk * (nbk + 1) / 2;
-    const double* r = red_host(o);
-    Hout.assign((size_t)o->F * nbk * nbk, 0.0);
-    bout.assign((size_t)o->F * nbk, 0.0);
-    for (int f = 0; f < o->F; ++f) {
-        const double* v = r + (size_t)f * V;
-        int t = 0;
-        for (int i = 0; i < nbk; ++i) {
-            for (int k = 0; k <= i; ++k) {
-                Hout[(size_t)f * nbk * nbk + i * nbk + k] = v[t];
-                Hout[(size_t)f * nbk * nbk + k * nbk + i] = v[t];
-                ++t;
-            }
-            bout[(size_t)f * nbk + i] = v[NT + i];
-        }
-    }
 }
 
 // distance: leaves the stencil blocks in o->vecs; the scalars (energy before the update) are fetched with the PCG result
@@ -1110,7 +1135,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         NoAllocScratch* sc = g_noalloc_dev[dev];
         if (o->S == 0) { const double zero = 0.0; if (E) *E = zero / zero; if (n_active) *n_active = 0; return PSG_OK; }   // E / S with S = 0, as psg_opt_energy
 
-        refresh_frame_table(o);   // per-keyframe parameters travel as a kernel parameter, not through device memory
+        refresh_frame_table(o);   // uploads the keyframe table if the host changed it (a copy into memory allocated at creation)
         // the array keeps whatever the previous call left: results and the arrival counter must start at zero
         PSG_CUDA(cudaMemsetAsync(sc, 0, sizeof(sc->red) + sizeof(sc->counter), o->stream));
 
@@ -1123,7 +1148,7 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         A.images = o->images.p; A.F = o->F;
         shard_blocks(A.surf.nslots, 0, 1, &A.blk_first, &A.blk_stride, &A.blk_count);   // this rank's whole slot list (no communication on this path)
         A.vs_inv = o->vs_inv;
-        if (o->set.model == PSG_MODEL_LED) for (int c = 0; c < 3; ++c) A.led[c] = o->light[c];
+        A.cslot = o->cslot;
         A.reg_n = o->set.reg_weight_n; A.reg_l = o->set.reg_weight_l;
         A.red = sc->red; A.red_copies = 1; A.scal = sc->red; A.partials = sc->partials; A.counter = sc->counter;
 
@@ -1133,9 +1158,9 @@ extern "C" int psg_opt_energy_noalloc(psg_optimizer* o, double* E, long long* n_
         if (o->sweep_split > 0) W = o->sweep_split;
         const size_t smem = W > 1 ? (size_t)W * 14 * 32 * sizeof(float) : 0;
         if (grid > 0) switch (o->set.model) {
-            case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
-            case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
-            default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A, o->frame_table); break;
+            case PSG_MODEL_SH1: k_sweep<PSG_MODEL_SH1, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+            case PSG_MODEL_SH2: k_sweep<PSG_MODEL_SH2, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
+            default: k_sweep<PSG_MODEL_LED, M_ENERGY><<<grid, 32 * W, smem, o->stream>>>(A); break;
         }
         count_launch();
         PSG_LAUNCH_CHECK();

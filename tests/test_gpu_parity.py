@@ -546,3 +546,62 @@ def test_albedo_regulariser_vs_oracle(model):
 def test_outer_loop_with_albedo_regulariser_matches_reference_log(tmp_path):
     """reg albedo = 0.05 through alternatingOptimize: the 'rho reg energy' column of optimizer_doc.txt against the reference's."""
     _outer_loop_vs_reference(tmp_path, "SH1", 24, dict(reg_rho=0.05, reg_n=10.0), 3, 1e-9, 1.0, False, tol=5e-5)
+
+
+@pytest.mark.parametrize("model", MODELS)
+def test_device_small_solve_matches_host_solve(model):
+    """The light and pose blocks are solved by one thread block on the device (k_small_solve).  Its iterates must be those of
+    the host restatement of Eigen's CG (psg_debug_small_cg, pinned bit for bit against the reference's systems in
+    tests/test_host_logic.py): same solution bits, iteration count and verdict on the system the device assembled; and the
+    update it applies to the keyframe table is the reference's (light -= delta; t -= xi[0:3], R <- R exp(-xi[3:6]))."""
+    import psgradientsdf_b200 as psg
+    G = 40
+    sc = scene(model)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc); go.init_albedo()
+    for it in range(2):
+        for blk in block_order(model):
+            light0, poses0 = go.light().copy(), go.poses().copy()
+            info = go.step(blk, damping=1.0, normal_reg=True, laplacian_reg=(model == "LED"))
+            if blk not in ("light", "pose"):
+                continue
+            H, b, delta = go.last_system(blk)
+            x, ok, iters, err = psg.small_cg(H.astype(np.float32), b.astype(np.float32))
+            assert np.array_equal(np.asarray(x, np.float32).view(np.uint32), delta.astype(np.float32).view(np.uint32)), (model, blk, it)
+            assert (bool(ok), iters) == (bool(info["cg_success"]), info["iters"]), (model, blk, ok, iters, info)
+            assert np.float32(err) == np.float32(info["err"])
+            d = delta.astype(np.float32)
+            if blk == "light":
+                assert info["applied"] == 1
+                assert np.array_equal(go.light().reshape(-1), (light0.reshape(-1) - d).astype(np.float32))
+                assert np.array_equal(go.poses(), poses0)
+            else:
+                assert info["applied"] == (1 if (model != "LED" or ok) else 0)
+                assert np.array_equal(go.light(), light0)
+                if not info["applied"]:
+                    assert np.array_equal(go.poses(), poses0)
+                    continue
+                P = go.poses().reshape(-1, 4, 4)
+                P0 = poses0.reshape(-1, 4, 4)
+                f32 = np.float32
+                for f in range(P.shape[0]):
+                    xi = d[6 * f:6 * f + 6]
+                    assert np.array_equal(P[f][:3, 3], (P0[f][:3, 3] - xi[:3]).astype(f32))
+                    assert np.array_equal(P[f][3], P0[f][3])
+                    w = (-xi[3:]).astype(f32)
+                    th2 = f32(w[0] * w[0]) + (f32(w[1] * w[1]) + f32(w[2] * w[2]))
+                    th = np.sqrt(f32(th2)); half = f32(0.5) * th
+                    imag = f32(f32(np.sin(np.float64(half))) / th); real = f32(np.cos(np.float64(half)))
+                    q = np.array([real, imag * w[0], imag * w[1], imag * w[2]], f32)
+                    qw, qx, qy, qz = q
+                    tx, ty, tz = f32(2) * qx, f32(2) * qy, f32(2) * qz
+                    twx, twy, twz, txx, txy, txz = tx * qw, ty * qw, tz * qw, tx * qx, ty * qx, tz * qx
+                    tyy, tyz, tzz = ty * qy, tz * qy, tz * qz
+                    E = np.array([[1 - (tyy + tzz), txy - twz, txz + twy], [txy + twz, 1 - (txx + tzz), tyz - twx],
+                                  [txz - twy, tyz + twx, 1 - (txx + tyy)]], f32)
+                    R0 = P0[f][:3, :3]
+                    R = np.empty((3, 3), f32)
+                    for a in range(3):
+                        for c in range(3):
+                            R[a, c] = f32(R0[a, 0] * E[0, c]) + (f32(R0[a, 1] * E[1, c]) + f32(R0[a, 2] * E[2, c]))
+                    assert np.array_equal(P[f][:3, :3], R), (model, f, np.abs(P[f][:3, :3] - R).max())
