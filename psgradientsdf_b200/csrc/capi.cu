@@ -40,7 +40,7 @@ static const char* const kKernelNames[KID_COUNT] = {
     "k_fill_volume", "k_pack_frame", "k_integrate", "k_aos_soa", "k_surface_mask", "k_scan_counts", "k_surface_scatter",
     "k_neighbors", "k_upsample", "k_sweep<ENERGY>", "k_sweep<INIT_ALBEDO>", "k_sweep<LED_INIT>", "k_sweep<PROBE>",
     "k_sweep<ALBEDO>", "k_sweep<LIGHT>", "k_sweep<POSE>", "k_sweep<DIST>", "k_reg_energy", "k_dist_assemble", "k_dist_pcg",
-    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "nccl_allreduce", "nccl_allgather", "k_track", "k_mesh_bbox", "k_mesh_cells<count>", "k_mesh_scan", "k_mesh_cells<emit>", "k_mesh_misc", "k_small_solve" };
+    "k_dist_update", "k_grad_update", "k_pad_images", "k_normals", "k_comm_scatter", "allreduce_small_sums", "nccl_allgather", "k_track", "k_mesh_bbox", "k_mesh_cells<count>", "k_mesh_scan", "k_mesh_cells<emit>", "k_mesh_misc", "k_small_solve" };
 static bool g_prof_on = false;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof_recs;

@@ -158,6 +158,57 @@ static PtrTable& ptr_table() { static thread_local PtrTable t; return t; }
 
 struct ReduceArg { double* ptr[3]; size_t cnt[3]; int n; };
 
+// ---- the small sums of a sharded job over peer memory ---------------------------------------------------------------------------
+// One thread per double.  It stores its value into every peer's inbox as two 8-byte packets (epoch << 32 | half of the bits:
+// value and tag travel in one aligned store, so no fence and no flag), then reads the packets the peers stored into its own
+// rank's inbox, polling until they carry this reduction's epoch, and adds the ranks' values in rank order -- the same
+// association on every rank, identical bits everywhere.  One NVLink hop; NCCL's all-reduce of the same ~1000 doubles takes
+// 17 us on two and 42 us on eight B200.  Inboxes alternate by epoch parity: a peer can be at most one reduction ahead (it
+// cannot finish reduction e + 1 without this rank's packets of e + 1, which are stored after this rank has read e).
+struct PacketReduceArgs {
+    double* ptr[3]; unsigned cnt[3]; int n;
+    unsigned long long* inbox[kMaxRanks];   // inbox[q]: rank q's inbox as addressable from here (inbox[rank] = own)
+    XState* own;
+    int rank, world;
+    unsigned epoch;                         // >= 1
+};
+__device__ __forceinline__ void ar_store(unsigned long long* p, unsigned long long v) { asm volatile("st.volatile.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ unsigned long long ar_load(const unsigned long long* p) { unsigned long long v; asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v; }
+__global__ void __launch_bounds__(256) k_packet_allreduce(const PacketReduceArgs A) {
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned flat = i;
+    int k = 0;
+    while (k < A.n && i >= A.cnt[k]) { i -= A.cnt[k]; ++k; }
+    if (k >= A.n) return;
+    double* mine = A.ptr[k] + i;
+    const double v = *mine;
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+    const unsigned long long tag = (unsigned long long)A.epoch << 32;
+    const size_t lane = ((size_t)(A.epoch & 1u) * kMaxRanks + (size_t)A.rank) * (2 * (size_t)kArMaxDoubles) + 2 * (size_t)flat;
+    for (int q = 0; q < A.world; ++q) {
+        if (q == A.rank) continue;
+        ar_store(A.inbox[q] + lane, tag | (bits & 0xffffffffull));
+        ar_store(A.inbox[q] + lane + 1, tag | (bits >> 32));
+    }
+    double t = 0.0;
+    const long long t0 = clock64();
+    for (int q = 0; q < A.world; ++q) {
+        if (q == A.rank) { t += v; continue; }
+        const unsigned long long* src = A.inbox[A.rank] + ((size_t)(A.epoch & 1u) * kMaxRanks + (size_t)q) * (2 * (size_t)kArMaxDoubles) + 2 * (size_t)flat;
+        unsigned long long lo, hi;
+        for (;;) {
+            lo = ar_load(src); hi = ar_load(src + 1);
+            if ((lo >> 32) == A.epoch && (hi >> 32) == A.epoch) break;
+            if (clock64() - t0 > 8000000000ll) {   // ~4 s: a peer is gone; make the failure loud instead of waiting forever
+                A.own->abort = 1ull;
+                __trap();
+            }
+        }
+        t += __longlong_as_double((long long)((hi << 32) | (lo & 0xffffffffull)));
+    }
+    *mine = t;
+}
+
 void comm_allreduce_doubles(psg_optimizer* o, double* const* ptr, const size_t* count, int n) {
     if (n <= 0) return;
     if (o->group) {
@@ -176,6 +227,26 @@ void comm_allreduce_doubles(psg_optimizer* o, double* const* ptr, const size_t* 
             }
             PSG_CUDA(cudaStreamSynchronize(o->stream));   // `host` lives on this frame
         });
+        return;
+    }
+    size_t total = 0;
+    for (int k = 0; k < n; ++k) total += count[k];
+    if (o->peers_ready && o->sharded && n <= 3 && total <= (size_t)kArMaxDoubles) {
+        // peers' inboxes are mapped: one kernel, one NVLink hop
+        PacketReduceArgs A;
+        memset(&A, 0, sizeof(A));
+        A.n = n;
+        for (int k = 0; k < n; ++k) { A.ptr[k] = ptr[k]; A.cnt[k] = (unsigned)count[k]; }
+        for (int q = 0; q < o->world; ++q)
+            A.inbox[q] = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(o->peer[q].xs) + kArInboxOffset);
+        A.own = reinterpret_cast<XState*>(o->xstate.p);
+        A.rank = o->rank; A.world = o->world;
+        A.epoch = ++o->ar_epoch;
+        if (total == 0) return;
+        Prof pf(o->stream, KID_COMM_ALLREDUCE);
+        k_packet_allreduce<<<(unsigned)((total + 255) / 256), 256, 0, o->stream>>>(A);
+        count_launch(1);
+        PSG_LAUNCH_CHECK();
         return;
     }
     ncclComm_t comm = static_cast<ncclComm_t>(o->comm);
@@ -336,6 +407,7 @@ static void* ipc_import(psg_optimizer* o, IpcCache& cache, const IpcRecord& r) {
 
 void release_peers(psg_optimizer* o) {
     bool had = false;
+    o->peers_ready = false;
     for (int q = 0; q < kMaxRanks; ++q) { if (o->peer[q].xs && q != o->rank) had = true; o->peer[q] = PeerView(); }
     if (!o->ipc_opened.empty()) {
         PSG_CUDA(cudaStreamSynchronize(o->stream));
@@ -347,6 +419,7 @@ void release_peers(psg_optimizer* o) {
 }
 
 void exchange_peers(psg_optimizer* o) {
+    o->peers_ready = false;
     for (int q = 0; q < kMaxRanks; ++q) o->peer[q] = PeerView();
     if (!o->sharded) return;
     trace("[rank %d] exchange_peers: rows %d..%d of %d", o->rank, o->row_lo, o->row_hi, o->S);
@@ -386,6 +459,7 @@ void exchange_peers(psg_optimizer* o) {
         o->peer[q].xs = static_cast<XState*>(ipc_import(o, cache, all[q].xs));
     }
     comm_barrier(o);   // every rank has mapped everything before anyone launches a kernel that writes to a peer
+    o->peers_ready = true;   // from here on the small sums travel as packets (k_packet_allreduce)
     trace("[rank %d] exchange_peers done", o->rank);
 }
 
@@ -520,6 +594,7 @@ int psg::comm_destroy(psg_optimizer* o, bool collective) {
             } else {
                 for (void* b : o->ipc_opened) cudaIpcCloseMemHandle(b);
                 o->ipc_opened.clear();
+                o->peers_ready = false;
                 for (int q = 0; q < kMaxRanks; ++q) o->peer[q] = PeerView();
             }
         }

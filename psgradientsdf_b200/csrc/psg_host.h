@@ -79,6 +79,11 @@ struct PeerView {
     unsigned long long* halo = nullptr;   // kHaloKinds planes of nh (tag << 32 | float bits) packets: the owner's halo rows, written by their owners
     XState* xs = nullptr;
 };
+// All-reduce of the small sums of a sharded job (comm.cu: k_packet_allreduce): behind a rank's XState, in the same peer-mapped
+// allocation, an inbox of (epoch << 32 | 32 data bits) packets per reduction parity and sender, two packets per double.
+constexpr int kArMaxDoubles = 64 * 64 + 64;        // per-keyframe sums (kRedDoubles) + mail slots in flight
+constexpr size_t kArInboxOffset = (sizeof(XState) + 255) / 256 * 256;
+constexpr size_t kArInboxBytes = (size_t)2 * kMaxRanks * 2 * kArMaxDoubles * sizeof(unsigned long long);
 constexpr int kHaloKinds = 11;   // stencil planes 2, 5, 9, 11, 12, 13 | u = r / diag | U1..U3 | distance
 }  // namespace psg
 
@@ -169,6 +174,8 @@ struct psg_optimizer {
     psg::DevBuf<unsigned long long> halo;    // this rank's halo packets (PeerView::halo), kHaloKinds x (rows of its halo)
     psg::DevBuf<unsigned long long> xplanes; // u and U1..U3 of all rows as (tag, value) packets: what other threads of this rank read (pcg.cu)
     psg::PeerView peer[psg::kMaxRanks];      // peer[q]: rank q's buffers as addressable from this process (peer[rank] = own)
+    bool peers_ready = false;                // every rank has mapped every rank's buffers (exchange_peers .. release_peers)
+    unsigned ar_epoch = 0;                   // packet all-reduces done so far (the same on every rank: collectives run in lockstep)
     std::vector<void*> ipc_opened;           // base pointers of the imported allocations (closed before anything is freed)
     int shard_policy = 0;                    // 0 = by work per rank, 1 = always, 2 = never
     long long vis_pairs = 0;                 // visible (surface voxel, keyframe) pairs of the current work list

@@ -454,8 +454,8 @@ void build_layout(psg_optimizer* o) {
         if (o->xplanes.n < 4 * Sr) o->xplanes.alloc(4 * Sr);
         PSG_CUDA(cudaMemsetAsync(o->xplanes.p, 0, o->xplanes.n * sizeof(unsigned long long), o->stream));
         if (!o->xstate.p) {
-            o->xstate.alloc(sizeof(XState));
-            PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, sizeof(XState), o->stream));
+            o->xstate.alloc(kArInboxOffset + kArInboxBytes);   // the XState, then the all-reduce inbox (comm.cu)
+            PSG_CUDA(cudaMemsetAsync(o->xstate.p, 0, kArInboxOffset + kArInboxBytes, o->stream));
         }
         const size_t grid = (Sr + 31) / 32 + 1, ngroups = grid / 128 + 2;
         o->sweep_partials.alloc((grid + ngroups) * 8);
