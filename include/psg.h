@@ -181,7 +181,9 @@ int psg_opt_energy(psg_optimizer* opt, double* E, long long* n_active);
  * memory already committed to another owner, or a loop that cannot absorb the stall of an allocation).  It has no
  * counterpart in the reference.  The kernel's scratch (results, per-block partial sums, arrival counters) lives in one
  * ~4.2 MB array inside the loaded module, present on every GPU that loads the library until exit; the per-keyframe
- * poses and light travel as a kernel parameter.  Nothing is allocated or freed.  Limits and rules:
+ * poses and light are read from the optimizer's table in constant memory, which (like its copy in device memory) was
+ * set aside when the optimizer was created and is refreshed by a 6 KB copy when poses or light changed.  Nothing is
+ * allocated or freed.  Limits and rules:
  *   - at most 2 097 152 surface voxels and device ordinals below 64; larger inputs are rejected with PSG_ERR_INVALID;
  *   - the first call on a device looks up the array's device address, and the driver may load the kernel's code then
  *     (a driver-side, one-time cost); make that first call before any stream capture and before the phase in which
@@ -242,10 +244,11 @@ int psg_opt_save_pointcloud(psg_optimizer* opt, const char* filename);
 
 /* One pass of the reference's while-body (PsOptimizer.cpp:303-360, LedOptimizer.cpp:343-403): the enabled blocks in the
  * reference's order (SH: albedo, light, distance, pose; LED: light, albedo, distance, pose), the regulariser energies after
- * the distance block and the closing getPSEnergy().  Same kernels and host solves as four psg_opt_step calls +
- * psg_opt_reg_energies + psg_opt_energy, but the host waits for the device only where it has to solve a small system
- * (light, pose) and for the closing energy: 3 waits instead of 8.  The distance update's CG gate (applied only on Success,
- * PsOptimizer.cpp:168-170) is evaluated on the device. */
+ * the distance block and the closing getPSEnergy().  Same kernels as four psg_opt_step calls + psg_opt_reg_energies +
+ * psg_opt_energy, queued back to back: every block's solve and update runs on the device (the light / pose systems are solved
+ * there by Eigen's CG in Eigen's operation order, the poses / light updated in the device's keyframe table), so the host waits
+ * once, for everything, instead of 8 times.  The distance update's CG gate (applied only on Success, PsOptimizer.cpp:168-170)
+ * and the LED pose update's (LedOptimizer.cpp:271-273) are evaluated on the device. */
 typedef struct {
     int light, albedo, distance, pose;   /* alternatingOptimize(bool light, bool albedo, bool distance, bool pose) */
     float damping;
@@ -410,7 +413,7 @@ typedef struct {
     float iteration_ms[64];
 } psg_loop_result;
 /* Diagnostic: microseconds the calling thread spent inside psg_opt_iteration since the last reset, split into
- * us[0] queuing kernels, us[1] waiting for the device's results, us[2] host solves (light / pose CG, pose update) and bookkeeping. */
+ * us[0] queuing kernels, us[1] waiting for the device's results, us[2] bookkeeping after the wait (the step records). */
 int psg_debug_host_times(double us[3], long long* iterations, int reset);
 /* Diagnostic: CUDA events on the optimizer's own stream (events of another library see only their own stream).  begin
  * records an event; end records a second one, waits for it and returns the device time between the two in milliseconds:

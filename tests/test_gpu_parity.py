@@ -405,7 +405,7 @@ def test_full_size_properties():
 @pytest.mark.gpu
 @pytest.mark.parametrize("model", MODELS)
 def test_iteration_matches_block_steps(model):
-    """psg_opt_iteration (3 host waits, distance gate on the device) against the same pass made of psg_opt_step calls."""
+    """psg_opt_iteration (all blocks queued, one host wait, gates on the device) against the same pass made of psg_opt_step calls."""
     G = 40
     sc = scene(model)
     lap = model == "LED"
