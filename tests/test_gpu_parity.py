@@ -605,3 +605,30 @@ def test_device_small_solve_matches_host_solve(model):
                         for c in range(3):
                             R[a, c] = f32(R0[a, 0] * E[0, c]) + (f32(R0[a, 1] * E[1, c]) + f32(R0[a, 2] * E[2, c]))
                     assert np.array_equal(P[f][:3, :3], R), (model, f, np.abs(P[f][:3, :3] - R).max())
+
+
+def test_optimizer_handles_per_device_are_limited_and_recycled():
+    """An optimizer keeps its keyframe table in one of ten slots of the device's constant memory: the eleventh live handle is
+    refused with an error (not a crash), and destroying a handle frees its slot."""
+    import gc
+    import psgradientsdf_b200 as psg
+    from psgradientsdf_b200 import synth
+    gc.collect()
+    sc = scene("SH1")
+    G = 16
+    vs, T = synth.grid_for_scene(G)
+    vol = psg.VolumetricGradSdf([G, G, G], vs, [0, 0, 0], T, 64)
+    made = []
+    with pytest.raises(psg.PsgError, match="optimizers per device"):
+        for _ in range(12):
+            made.append(psg.Optimizer(vol, vs, sc.K, model="SH1"))
+    assert 1 <= len(made) <= 10
+    n = len(made)
+    made.pop().close()
+    made.append(psg.Optimizer(vol, vs, sc.K, model="SH1"))      # the freed slot is taken again
+    assert len(made) == n
+    for o in made:
+        o.close()
+    gv, go = make_gpu("SH1", 32, sc)                             # and a normal job still runs
+    handoff(go, sc)
+    assert go.energy()[1] > 0
