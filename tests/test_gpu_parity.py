@@ -632,3 +632,32 @@ def test_optimizer_handles_per_device_are_limited_and_recycled():
     gv, go = make_gpu("SH1", 32, sc)                             # and a normal job still runs
     handoff(go, sc)
     assert go.energy()[1] > 0
+
+
+@pytest.mark.parametrize("model,nkeys", [("SH1", 1), ("SH1", 2), ("SH1", 3), ("SH1", 5), ("SH2", 1), ("SH2", 3), ("LED", 2)])
+def test_device_small_solve_odd_sizes(model, nkeys):
+    """System sizes that exercise every branch of Eigen's reduction order in the device solve: fewer than eight unknowns (no strided
+    range), exactly one stride, an extra packet of four, tails of one to three elements (n = 4, 6, 8, 9, 12, 18, 20, 27, 30)."""
+    import psgradientsdf_b200 as psg
+    G = 32
+    sc = scene(model)
+    gv, go = make_gpu(model, G, sc)
+    handoff(go, sc, keys=list(range(nkeys)))
+    go.init_albedo()
+    for blk in ("light", "pose"):
+        before = (go.light().copy(), go.poses().copy())
+        info = go.step(blk, damping=1.0)
+        H, b, delta = go.last_system(blk)
+        assert b.size == H.shape[0] * H.shape[1]
+        x, ok, iters, err = psg.small_cg(H.astype(np.float32), b.astype(np.float32))
+        assert np.array_equal(np.asarray(x, np.float32).view(np.uint32), delta.astype(np.float32).view(np.uint32)), (model, nkeys, blk)
+        assert (bool(ok), iters) == (bool(info["cg_success"]), info["iters"]) and np.float32(err) == np.float32(info["err"])
+        if blk == "light":
+            assert np.array_equal(go.light().reshape(-1), (before[0].reshape(-1) - delta.astype(np.float32)).astype(np.float32))
+        else:
+            assert np.array_equal(go.light(), before[0])
+            assert info["applied"] == (1 if (model != "LED" or ok) else 0)
+            if info["applied"]:
+                t_new = go.poses().reshape(-1, 4, 4)[:, :3, 3]
+                t_old = before[1].reshape(-1, 4, 4)[:, :3, 3]
+                assert np.array_equal(t_new, (t_old - delta.astype(np.float32).reshape(-1, 6)[:, :3]).astype(np.float32))
