@@ -346,9 +346,10 @@ int psg_tracker_optimize(psg_volume* vol, const float K[9], const float pose_in[
  * Sharded mode: the surface list is in ascending voxel order, so a contiguous ROW RANGE of it is a z-slab
  * of the volume; rank g owns one range (equal numbers of visible pairs per rank) and does all per-row work on it -- sweeps,
  * distance stencil blocks, the CG of the distance block, the gated updates, the regulariser energies.  Across ranks go: the
- * energies and the per-keyframe light / pose normal equations (one NCCL all-reduce per host round trip), and, inside the
- * persistent distance-solve kernel, the one-voxel halo of the CG vectors plus two scalars per reduction, written straight into
- * the peers' memory over NVLink (CUDA IPC mappings) with a flag barrier.  Energies, light, poses and CG verdicts are identical on
+ * energies and the per-keyframe light / pose normal equations (three small all-reduces per outer iteration, stream ordered, as
+ * tagged packets written into the peers' memory), and, inside the persistent distance-solve kernel, the one-voxel halo of the CG
+ * vectors plus three scalars per reduction, also written straight into the peers' memory over NVLink (CUDA IPC mappings) as
+ * tagged packets.  NCCL carries the set-up (unique id, handle exchange, barriers) and psg_opt_sync_volume's all-gather.  Energies, light, poses and CG verdicts are identical on
  * all ranks; of the VOLUME a rank keeps only its own rows (and the distance of its halo) current until psg_opt_sync_volume.
  * Diagnostics that return per-row data (psg_opt_probe_pairs, psg_opt_residual, psg_opt_last_vectors) cover the rank's own rows.
  * reg albedo != 0 is not provided in this mode.
