@@ -834,9 +834,12 @@ static void launch_sweep(psg_optimizer* o, SweepArgs& A, size_t red_doubles, siz
         PSG_CUDA(cudaMemsetAsync(A.scal, 0, 8 * sizeof(double), o->stream));
     if (o->S == 0 || A.blk_count <= 0) return;
     const int grid = A.blk_count;
-    // keyframe split: double W while the launch stays within ~32 warps per SM (beyond that the replicated prologue costs more than it hides)
+    // keyframe split: double W while the launch stays within ~32 warps per SM (beyond that the replicated prologue costs more than it
+    // hides).  The distance sweep (128 registers, 16 warps per SM) stops one doubling earlier than the 64-register modes: measured at
+    // 128^3 (888 blocks), W = 8 against 4: albedo 34.0 -> 32.2 us, light 25.8 -> 24.3, pose 31.7 -> 28.9, but distance 33.8 -> 41.1.
     int W = 1;
-    while (W < kMaxSplit && (long long)grid * W * 2 <= 148ll * 32) W *= 2;
+    const long long budget = (MODE == M_DIST) ? 148ll * 32 : 2 * 148ll * 32;
+    while (W < kMaxSplit && (long long)grid * W * 2 <= budget) W *= 2;
     if (o->sweep_split > 0) W = o->sweep_split;
     const int kBlockDim = 32 * W;
     if (W > 1 && dyn_smem < (size_t)W * 14 * 32 * sizeof(float)) dyn_smem = (size_t)W * 14 * 32 * sizeof(float);
